@@ -1,0 +1,293 @@
+"""ODE integrators — CPU oracle (TEST INFRASTRUCTURE, never shipped).
+
+Plain-PyTorch restatement of /root/reference/bayesflow/utils/integrate.py:24-489 (the deterministic half).
+The reference is written on ``keras.ops``; on the torch backend ``fori_loop`` / ``while_loop`` / ``cond``
+are Python control flow, python floats stay python doubles until they meet a tensor, and every reduction
+(`max`, `norm`) is a torch op on fp32 tensors.  This file keeps exactly those semantics.
+
+Pinned by the reference's own analytic tests (tests/test_utils/test_integrate.py:15-25, 47-93), restated in
+/root/repo/tests/test_oracle_integrate.py.
+"""
+from __future__ import annotations
+
+import math
+from typing import Callable, Dict
+
+import numpy as np
+import torch
+
+StateDict = Dict[str, torch.Tensor]
+
+DETERMINISTIC_METHODS = ["euler", "rk45", "tsit5"]
+
+# Dormand–Prince 5(4), integrate.py:74-96, 107-114
+RK45_C = (0.0, 1 / 5, 3 / 10, 4 / 5, 8 / 9, 1.0, 1.0)
+RK45_A = (
+    (),
+    (1 / 5,),
+    (3 / 40, 9 / 40),
+    (44 / 45, -56 / 15, 32 / 9),
+    (19372 / 6561, -25360 / 2187, 64448 / 6561, -212 / 729),
+    (9017 / 3168, -355 / 33, 46732 / 5247, 49 / 176, -5103 / 18656),
+)
+RK45_B5 = (35 / 384, 0.0, 500 / 1113, 125 / 192, -2187 / 6784, 11 / 84)
+RK45_B4 = (5179 / 57600, 0.0, 7571 / 16695, 393 / 640, -92097 / 339200, 187 / 2100, 1 / 40)
+
+# Tsitouras 5(4), integrate.py:139-142, 146-179, 184-191, 201-209
+TSIT5_C = (0.0, 0.161, 0.327, 0.9, 0.9800255409045097, 1.0, 1.0)
+TSIT5_A = (
+    (),
+    (0.161,),
+    (-0.0084806554923570, 0.3354806554923570),
+    (2.897153057105494, -6.359448489975075, 4.362295432869581),
+    (5.325864828439257, -11.74888356406283, 7.495539342889836, -0.09249506636175525),
+    (5.86145544294270, -12.92096931784711, 8.159367898576159, -0.07158497328140100, -0.02826905039406838),
+)
+TSIT5_B = (0.09646076681806523, 0.01, 0.4798896504144996, 1.379008574103742, -3.290069515436081, 2.324710524099774)
+# error = h * sum(e_i k_i), i = 1..7
+TSIT5_E = (
+    -0.00178001105222577714,
+    -0.0008164344596567469,
+    0.007880878010261995,
+    -0.1447110071732629,
+    0.5823571654525552,
+    -0.45808210592918697,
+    0.015151515151515152,
+)
+
+
+def _check_all_nans(state: StateDict) -> bool:
+    # integrate.py:24-28
+    return bool(all(bool(torch.all(torch.isnan(v))) for v in state.values()))
+
+
+def euler_step(fn: Callable, state: StateDict, time, step_size, **_):
+    # integrate.py:31-44
+    k1 = fn(time, **state)
+    new_state = dict(state)
+    for key in k1.keys():
+        new_state[key] = state[key] + step_size * k1[key]
+    return new_state, time + step_size, None, 0.0
+
+
+def add_scaled(state, ks, coeffs, h):
+    # integrate.py:47-54
+    out = {}
+    for key, y in state.items():
+        acc = torch.zeros_like(y)
+        for c, k in zip(coeffs, ks):
+            acc = acc + c * k[key]
+        out[key] = y + h * acc
+    return out
+
+
+def _err_max(err_state: StateDict):
+    # integrate.py:117-118 / 211-212: max over keys and rows of the row-wise L2 norm
+    err_norm = torch.stack([torch.linalg.vector_norm(v, ord=2, dim=-1).reshape(-1).max() for v in err_state.values()])
+    return err_norm.max()
+
+
+def rk45_step(fn, state, time, step_size, k1=None, use_adaptive_step_size=True):
+    # integrate.py:57-120
+    h = step_size
+    if k1 is None:
+        k1 = fn(time, **state)
+    k2 = fn(time + h * (1 / 5), **add_scaled(state, [k1], RK45_A[1], h))
+    k3 = fn(time + h * (3 / 10), **add_scaled(state, [k1, k2], RK45_A[2], h))
+    k4 = fn(time + h * (4 / 5), **add_scaled(state, [k1, k2, k3], RK45_A[3], h))
+    k5 = fn(time + h * (8 / 9), **add_scaled(state, [k1, k2, k3, k4], RK45_A[4], h))
+    k6 = fn(time + h, **add_scaled(state, [k1, k2, k3, k4, k5], RK45_A[5], h))
+
+    new_state = {}
+    for key in k1.keys():
+        new_state[key] = state[key] + h * (
+            35 / 384 * k1[key] + 500 / 1113 * k3[key] + 125 / 192 * k4[key] - 2187 / 6784 * k5[key] + 11 / 84 * k6[key]
+        )
+    new_time = time + h
+    if not use_adaptive_step_size:
+        return new_state, new_time, None, 0.0
+
+    k7 = fn(time + h, **new_state)
+    err_state = {}
+    for key in k1.keys():
+        y4 = state[key] + h * (
+            5179 / 57600 * k1[key]
+            + 7571 / 16695 * k3[key]
+            + 393 / 640 * k4[key]
+            - 92097 / 339200 * k5[key]
+            + 187 / 2100 * k6[key]
+            + 1 / 40 * k7[key]
+        )
+        err_state[key] = new_state[key] - y4
+    return new_state, new_time, k7, _err_max(err_state)
+
+
+def tsit5_step(fn, state, time, step_size, k1=None, use_adaptive_step_size=True):
+    # integrate.py:123-214
+    h = step_size
+    c2, c3, c4, c5 = TSIT5_C[1:5]
+    if k1 is None:
+        k1 = fn(time, **state)
+    k2 = fn(time + h * c2, **add_scaled(state, [k1], TSIT5_A[1], h))
+    k3 = fn(time + h * c3, **add_scaled(state, [k1, k2], TSIT5_A[2], h))
+    k4 = fn(time + h * c4, **add_scaled(state, [k1, k2, k3], TSIT5_A[3], h))
+    k5 = fn(time + h * c5, **add_scaled(state, [k1, k2, k3, k4], TSIT5_A[4], h))
+    k6 = fn(time + h, **add_scaled(state, [k1, k2, k3, k4, k5], TSIT5_A[5], h))
+
+    new_state = {}
+    for key in state.keys():
+        new_state[key] = state[key] + h * (
+            0.09646076681806523 * k1[key]
+            + 0.01 * k2[key]
+            + 0.4798896504144996 * k3[key]
+            + 1.379008574103742 * k4[key]
+            - 3.290069515436081 * k5[key]
+            + 2.324710524099774 * k6[key]
+        )
+    new_time = time + h
+    if not use_adaptive_step_size:
+        return new_state, new_time, None, 0.0
+
+    k7 = fn(time + h, **new_state)
+    err_state = {}
+    for key in state.keys():
+        err_state[key] = h * (
+            0.007880878010261995 * k3[key]
+            + 0.5823571654525552 * k5[key]
+            + 0.015151515151515152 * k7[key]
+            - 0.00178001105222577714 * k1[key]
+            - 0.0008164344596567469 * k2[key]
+            - 0.1447110071732629 * k4[key]
+            - 0.45808210592918697 * k6[key]
+        )
+    return new_state, new_time, k7, _err_max(err_state)
+
+
+def _select_step(method, adaptive):
+    # integrate.py:229-239 / 265-275 / 304-314
+    if method == "euler":
+        if adaptive:
+            raise ValueError("Adaptive step sizing is not supported for the 'euler' method.")
+        return euler_step
+    if method == "rk45":
+        return lambda fn, s, t, h, k1=None: rk45_step(fn, s, t, h, k1=k1, use_adaptive_step_size=adaptive)
+    if method == "tsit5":
+        return lambda fn, s, t, h, k1=None: tsit5_step(fn, s, t, h, k1=k1, use_adaptive_step_size=adaptive)
+    if isinstance(method, str):
+        raise ValueError(f"Unknown integration method name: {method!r}")
+    raise TypeError(f"Invalid integration method: {method!r}")
+
+
+def integrate_fixed(fn, state, start_time, stop_time, steps, method, **kwargs):
+    # integrate.py:217-254
+    if steps <= 0:
+        raise ValueError("Number of steps must be positive.")
+    step_fn = _select_step(method, adaptive=False)
+    step_size = (stop_time - start_time) / steps
+    time = start_time
+    for _ in range(steps):
+        state, time, _, _ = step_fn(fn, state, time, step_size)
+    return state
+
+
+def integrate_scheduled(fn, state, steps, method, **kwargs):
+    # integrate.py:257-288
+    step_fn = _select_step(method, adaptive=False)
+    n = int(steps.shape[0]) if hasattr(steps, "shape") else len(steps)
+    for i in range(n - 1):
+        time = steps[i]
+        step_size = steps[i + 1] - steps[i]
+        state, _, _, _ = step_fn(fn, state, time, step_size)
+    return state
+
+
+def integrate_adaptive(fn, state, start_time, stop_time, min_steps, max_steps, method, info: dict | None = None,
+                       **kwargs):
+    # integrate.py:291-406
+    if max_steps <= min_steps:
+        raise ValueError("Maximum number of steps must be greater than minimum number of steps.")
+    step_fn = _select_step(method, adaptive=True)
+
+    f32 = torch.float32
+    atol = torch.tensor(kwargs.get("atol", 1e-6), dtype=f32)
+    rtol = torch.tensor(kwargs.get("rtol", 1e-4), dtype=f32)
+    step_size = torch.tensor((stop_time - start_time) / float(min_steps), dtype=f32)
+    step = torch.tensor(0.0, dtype=f32)
+    count_not_accepted = 0.0
+    time = start_time
+    sign_dir = float(np.sign(stop_time - start_time))
+
+    k1 = fn(start_time, **state)  # FSAL, :323
+
+    def cond(_state, _time, _step_size, _step):
+        time_remaining = sign_dir * (stop_time - (_time + _step_size))
+        step_lt_min = bool(_step < float(min_steps))
+        step_lt_max = bool(_step < float(max_steps))
+        all_nans = _check_all_nans(_state)
+        end_now = step_lt_min or (bool(torch.all(torch.as_tensor(time_remaining) > 0)) and step_lt_max)
+        return (not all_nans) and end_now
+
+    while cond(state, time, step_size, step):
+        time_remaining = torch.abs(torch.as_tensor(stop_time - time, dtype=f32))
+        min_step_size = time_remaining / (max_steps - step)
+        max_step_size = time_remaining / torch.maximum(min_steps - step, torch.tensor(1.0))
+        h = torch.sign(step_size) * torch.clip(torch.abs(step_size), min_step_size, max_step_size)
+
+        new_state, new_time, new_k1, err = step_fn(fn, state, time, h, k1=k1)
+
+        max_abs = None
+        for v in state.values():
+            m = torch.max(torch.abs(v))
+            max_abs = m if max_abs is None else torch.maximum(max_abs, m)
+        scale = atol + rtol * max_abs
+        error_ratio = err / scale
+        new_step_size = h * torch.clip(0.9 * (1.0 / (error_ratio + 1e-12)) ** 0.2, 0.2, 5.0)
+        new_step_size = torch.sign(new_step_size) * torch.clip(torch.abs(new_step_size), min_step_size, max_step_size)
+
+        too_big = bool(error_ratio > 1.0)
+        at_min = bool(torch.abs(h) <= torch.abs(min_step_size))
+        accepted = (not too_big) or at_min
+
+        if accepted:
+            state, time, k1 = new_state, new_time, new_k1
+            step = step + 1.0
+        else:
+            count_not_accepted += 1.0
+        step_size = new_step_size
+
+    if _check_all_nans(state):
+        raise RuntimeError(f"All values are NaNs in state during integration at {time}.")
+
+    time_diff = stop_time - time
+    time_remaining = sign_dir * time_diff
+    if bool(torch.all(torch.as_tensor(time_remaining) > 0)):
+        state, time, _, _ = step_fn(fn, state, time, time_diff, k1=k1)
+        step = step + 1.0
+
+    if info is not None:
+        info["steps"] = float(step)
+        info["rejected"] = float(count_not_accepted)
+    return state
+
+
+def integrate(fn, state, start_time=None, stop_time=None, min_steps=50, max_steps=10_000, steps=100, method="rk45",
+              **kwargs):
+    # integrate.py:455-489 (scipy branch omitted: out of scope)
+    if isinstance(steps, str) and steps in ["adaptive", "dynamic"]:
+        if start_time is None or stop_time is None:
+            raise ValueError(
+                "Please provide start_time and stop_time for the integration, was "
+                f"'start_time={start_time}', 'stop_time={stop_time}'."
+            )
+        return integrate_adaptive(fn, state, start_time, stop_time, min_steps, max_steps, method, **kwargs)
+    elif isinstance(steps, int):
+        if start_time is None or stop_time is None:
+            raise ValueError(
+                "Please provide start_time and stop_time for the integration, was "
+                f"'start_time={start_time}', 'stop_time={stop_time}'."
+            )
+        return integrate_fixed(fn, state, start_time, stop_time, steps, method, **kwargs)
+    elif isinstance(steps, (list, tuple, np.ndarray)) or torch.is_tensor(steps):
+        return integrate_scheduled(fn, state, steps, method, **kwargs)
+    else:
+        raise RuntimeError(f"Type or value of `steps` not understood (steps={steps})")
