@@ -1,0 +1,9 @@
+"""bayesflow_b200 — B200-native (sm_100a) FlowMatching / DiffusionModel hot path behind the BayesFlow
+``InferenceNetwork`` surface.  See DESIGN.md."""
+from . import networks  # noqa: F401
+from .networks import (  # noqa: F401
+    FlowMatching, DiffusionModel, InferenceNetwork, TimeMLP, DiagonalNormal, EDMNoiseSchedule, CosineNoiseSchedule,
+)
+from .integrate import integrate  # noqa: F401
+
+__version__ = "0.1.0"

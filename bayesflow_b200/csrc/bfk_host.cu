@@ -1,0 +1,266 @@
+// libbfk: C-ABI entry points (include/bfk.h) over the sm_100a kernels.  No torch types, no exceptions.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "bfk_sampler.cuh"
+
+using namespace bfk;
+
+static thread_local char g_err[512] = "";
+static int fail(int code, const char* msg) {
+  snprintf(g_err, sizeof(g_err), "%s", msg);
+  return code;
+}
+static int cuda_fail(cudaError_t e, const char* where) {
+  snprintf(g_err, sizeof(g_err), "%s: %s", where, cudaGetErrorString(e));
+  return (int)e;
+}
+#define CK(call)                                              \
+  do {                                                        \
+    cudaError_t _e = (call);                                  \
+    if (_e != cudaSuccess) return cuda_fail(_e, #call);       \
+  } while (0)
+
+extern "C" int bfk_version(void) { return 100; }
+extern "C" const char* bfk_last_error_string(void) { return g_err; }
+
+extern "C" int bfk_num_sms(void) {
+  int dev = 0, n = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
+  return n;
+}
+
+static int check_cfg(const bfk_net_config* c) {
+  if (!c) return fail(-1, "null config");
+  if (c->D < 1 || c->W < 32 || c->L < 1 || c->L > BFK_MAX_BLOCKS) return fail(-2, "bad D/W/L");
+  if (c->T != 1 && (c->T < 3 || c->T > 65 || (c->T % 2) == 0)) return fail(-3, "time embedding size must be 1 or odd in [3,65]");
+  if (c->C < 0) return fail(-4, "bad C");
+  if (c->C > 0 && c->merge != BFK_MERGE_CONCAT && c->merge != BFK_MERGE_ADD) return fail(-5, "bad merge mode");
+  return 0;
+}
+
+extern "C" int bfk_fused_supported(const bfk_net_config* c) {
+  if (check_cfg(c)) return 0;
+  if (c->D > BFK_MAX_D) return 0;
+  if (c->W > 256 || (c->W % 32) != 0) return 0;
+  if (c->precision != BFK_PREC_FP16 && c->precision != BFK_PREC_BF16) return 0;
+  SmemPlan p = make_smem_plan(*c);
+  if (p.n_stage < 2) return 0;
+  return 1;
+}
+
+extern "C" size_t bfk_packed_bytes(const bfk_net_config* c) {
+  if (check_cfg(c)) return 0;
+  return make_layout(*c).total;
+}
+extern "C" size_t bfk_table_stride(const bfk_net_config* c) {
+  if (check_cfg(c)) return 0;
+  return (size_t)table_stride(*c);
+}
+
+static inline unsigned cdiv(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
+
+extern "C" int bfk_pack(const bfk_net_config* c, const bfk_weights* w, void* packed, void* stream_) {
+  if (int r = check_cfg(c)) return r;
+  if (!w || !packed) return fail(-10, "null pointer");
+  if ((c->W % 8) != 0) return fail(-11, "W must be a multiple of 8");
+  cudaStream_t st = (cudaStream_t)stream_;
+  const PackedLayout L = make_layout(*c);
+  unsigned char* P = (unsigned char*)packed;
+  const int W = c->W, bf = c->precision == BFK_PREC_BF16;
+  CK(cudaMemsetAsync(P, 0, L.total, st));
+  // GEMM operands
+  int g = 0;
+  if (L.has_merge) {
+    if (!w->m_k || !w->m_b || !w->c_k || !w->c_b) return fail(-12, "conditional net needs c_proj and merge_proj");
+    pack_gemm_kernel<<<cdiv((size_t)W / 8 * W, 256), 256, 0, st>>>(w->m_k, W, W, bf, (uint16_t*)(P + L.gemm));  // x half / whole (add)
+    ++g;
+  }
+  for (int l = 0; l < c->L; ++l, ++g) {
+    if (!w->dense_k[l] || !w->dense_b[l] || !w->film_b_k[l] || !w->film_b_b[l]) return fail(-13, "missing block weights");
+    pack_gemm_kernel<<<cdiv((size_t)W / 8 * W, 256), 256, 0, st>>>(w->dense_k[l], W, W, bf,
+                                                                  (uint16_t*)(P + L.gemm + (size_t)g * W * W * 2));
+  }
+  // constant vectors (SMEM image)
+  float* cv = (float*)(P + L.cvec);
+  pad2d_kernel<<<cdiv((size_t)L.DP * W, 256), 256, 0, st>>>(w->x_k, c->D, W, cv + L.cv_wx, L.DP, W);
+  copy_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(w->x_b, cv + L.cv_bx, W);
+  for (int l = 0; l < c->L; ++l) {
+    copy_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(w->dense_b[l], cv + L.cv_blk + (3 * l + 0) * W, W);
+    if (c->norm != BFK_NORM_NONE && w->norm_g[l])
+      copy_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(w->norm_g[l], cv + L.cv_blk + (3 * l + 1) * W, W);
+    else
+      fill_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(cv + L.cv_blk + (3 * l + 1) * W, 1.f, W);
+    copy_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(c->norm == BFK_NORM_LAYER ? w->norm_b[l] : nullptr,
+                                                  cv + L.cv_blk + (3 * l + 2) * W, W);
+  }
+  pad2d_kernel<<<cdiv((size_t)W * L.DP, 256), 256, 0, st>>>(w->out_k, W, c->D, cv + L.cv_wo, W, L.DP);
+  pad2d_kernel<<<1, 32, 0, st>>>(w->out_b, 1, c->D, cv + L.cv_bo, 1, L.DP);
+  // prologue parameters
+  if (L.Th > 0) copy_f32_kernel<<<1, 64, 0, st>>>(w->freq, (float*)(P + L.freq), L.Th);
+  for (int l = 0; l < c->L; ++l) {
+    const size_t n = (size_t)c->T * W;
+    copy_f32_kernel<<<cdiv(n, 256), 256, 0, st>>>(w->film_b_k[l], (float*)(P + L.film_b_k) + l * n, n);
+    copy_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(w->film_b_b[l], (float*)(P + L.film_b_b) + (size_t)l * W, W);
+    if (c->film_use_gamma) {
+      if (!w->film_g_k[l] || !w->film_g_b[l]) return fail(-14, "film_use_gamma set but to_gamma weights missing");
+      copy_f32_kernel<<<cdiv(n, 256), 256, 0, st>>>(w->film_g_k[l], (float*)(P + L.film_g_k) + l * n, n);
+      copy_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(w->film_g_b[l], (float*)(P + L.film_g_b) + (size_t)l * W, W);
+    }
+  }
+  if (L.has_merge) {
+    const size_t n = (size_t)c->C * W;
+    copy_f32_kernel<<<cdiv(n, 256), 256, 0, st>>>(w->c_k, (float*)(P + L.c_k), n);
+    copy_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(w->c_b, (float*)(P + L.c_b), W);
+    if (c->merge == BFK_MERGE_CONCAT)
+      copy_f32_kernel<<<cdiv((size_t)W * W, 256), 256, 0, st>>>(w->m_k + (size_t)W * W, (float*)(P + L.m_c), (size_t)W * W);
+    copy_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(w->m_b, (float*)(P + L.m_b), W);
+  }
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_cond_prologue(const bfk_net_config* c, const void* packed, const float* cond, int64_t G,
+                                 float* pre_add, float* post_add, void* stream_) {
+  if (int r = check_cfg(c)) return r;
+  if (c->C <= 0) return fail(-20, "network has no conditions");
+  if (!packed || !cond || !post_add || G <= 0) return fail(-21, "bad arguments");
+  if (c->merge == BFK_MERGE_ADD && !pre_add) return fail(-22, "merge='add' needs pre_add");
+  const PackedLayout L = make_layout(*c);
+  const unsigned grid = (unsigned)(G < 148 * 16 ? G : 148 * 16);
+  const size_t sh = (size_t)(c->C + c->W) * 4;
+  cond_prologue_kernel<<<grid, 256, sh, (cudaStream_t)stream_>>>(*c, (const unsigned char*)packed, L, cond, G, pre_add, post_add);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_eval_table(const bfk_net_config* c, const void* packed, const bfk_schedule* sched, const float* times,
+                              int64_t n, float* table, void* stream_) {
+  if (int r = check_cfg(c)) return r;
+  if (!packed || !sched || !times || !table || n <= 0) return fail(-30, "bad arguments");
+  const PackedLayout L = make_layout(*c);
+  const unsigned grid = (unsigned)(n < 148 * 8 ? n : 148 * 8);
+  eval_table_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>(*c, (const unsigned char*)packed, L, *sched, times, n,
+                                                           table_stride(*c), table);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------- tableaux
+// integrate.py:74-96 (Dormand-Prince) and :139-191 (Tsit5); coefficients are cast to fp32 exactly where torch casts
+// the python doubles (scalar * fp32 tensor).
+static void fill_tableau(int method, SamplerArgs& a) {
+  memset(a.rk_a, 0, sizeof(a.rk_a));
+  memset(a.rk_b, 0, sizeof(a.rk_b));
+  if (method == BFK_METHOD_EULER) {
+    a.S = 1;
+    a.rk_b[0] = 1.f;
+    return;
+  }
+  a.S = 6;
+  if (method == BFK_METHOD_RK45) {
+    const double A[6][5] = {{0},
+                            {1.0 / 5},
+                            {3.0 / 40, 9.0 / 40},
+                            {44.0 / 45, -56.0 / 15, 32.0 / 9},
+                            {19372.0 / 6561, -25360.0 / 2187, 64448.0 / 6561, -212.0 / 729},
+                            {9017.0 / 3168, -355.0 / 33, 46732.0 / 5247, 49.0 / 176, -5103.0 / 18656}};
+    const double Bc[6] = {35.0 / 384, 0.0, 500.0 / 1113, 125.0 / 192, -2187.0 / 6784, 11.0 / 84};
+    for (int i = 0; i < 6; ++i) {
+      for (int j = 0; j < 5; ++j) a.rk_a[i][j] = (float)A[i][j];
+      a.rk_b[i] = (float)Bc[i];
+    }
+  } else {
+    const double A[6][5] = {{0},
+                            {0.161},
+                            {-0.0084806554923570, 0.3354806554923570},
+                            {2.897153057105494, -6.359448489975075, 4.362295432869581},
+                            {5.325864828439257, -11.74888356406283, 7.495539342889836, -0.09249506636175525},
+                            {5.86145544294270, -12.92096931784711, 8.159367898576159, -0.07158497328140100, -0.02826905039406838}};
+    const double Bc[6] = {0.09646076681806523, 0.01, 0.4798896504144996, 1.379008574103742, -3.290069515436081, 2.324710524099774};
+    for (int i = 0; i < 6; ++i) {
+      for (int j = 0; j < 5; ++j) a.rk_a[i][j] = (float)A[i][j];
+      a.rk_b[i] = (float)Bc[i];
+    }
+  }
+}
+
+typedef void (*sampler_fn)(const SamplerArgs);
+static sampler_fn pick_kernel(const bfk_net_config* c) {
+  const int dp = dp_of(c->D);
+  const bool bf = c->precision == BFK_PREC_BF16;
+#define PICK(ACT_, DP_, BF_) \
+  if (c->activation == ACT_ && dp == DP_ && bf == BF_) return sampler_kernel<ACT_, DP_, BF_>;
+  PICK(BFK_ACT_MISH, 4, false)
+  PICK(BFK_ACT_MISH, 8, false)
+  PICK(BFK_ACT_MISH, 4, true)
+  PICK(BFK_ACT_SILU, 4, false)
+  PICK(BFK_ACT_RELU, 4, false)
+  PICK(BFK_ACT_GELU, 4, false)
+  PICK(BFK_ACT_TANH, 4, false)
+#undef PICK
+  return nullptr;
+}
+
+static int launch_sampler(const bfk_net_config* c, const void* packed, const float* table, const float* step_h, int method,
+                          int64_t n_steps, const float* pre_add, const float* post_add, int64_t rpg, const float* tmask,
+                          const float* x_in, float* x_out, int64_t B, int mode, cudaStream_t st) {
+  if (int r = check_cfg(c)) return r;
+  if (!bfk_fused_supported(c)) return fail(-40, "config not supported by the fused on-chip sampler (need D<=8, W<=256, W%32==0)");
+  if (!packed || !table || !step_h || !x_in || !x_out || B <= 0 || n_steps <= 0) return fail(-41, "bad arguments");
+  if (method < BFK_METHOD_EULER || method > BFK_METHOD_TSIT5) return fail(-42, "unknown method");
+  const PackedLayout L = make_layout(*c);
+  if (L.has_merge && !post_add) return fail(-43, "conditional net needs post_add from bfk_cond_prologue");
+  if (L.has_merge && c->merge == BFK_MERGE_ADD && !pre_add) return fail(-44, "merge='add' needs pre_add");
+  if (rpg <= 0) rpg = 1;
+  sampler_fn fn = pick_kernel(c);
+  if (!fn) return fail(-45, "no kernel instantiated for this activation / D / precision");
+
+  SamplerArgs a{};
+  a.wg = (const unsigned char*)packed + L.gemm;
+  a.cvec = (const float*)((const unsigned char*)packed + L.cvec);
+  a.table = table; a.step_h = step_h;
+  a.pre_add = (L.has_merge && c->merge == BFK_MERGE_ADD) ? pre_add : nullptr;
+  a.post_add = L.has_merge ? post_add : nullptr;
+  a.x_in = x_in; a.x_out = x_out; a.tmask = tmask;
+  a.B = B; a.rows_per_group = rpg; a.n_steps = n_steps;
+  a.D = c->D; a.W = c->W; a.L = c->L; a.NG = L.NG; a.has_merge = L.has_merge;
+  a.residual = c->residual; a.norm = c->norm; a.film_gamma = c->film_use_gamma;
+  a.mode = mode;
+  a.tstride = table_stride(*c); a.cvec_floats = L.cvec_floats;
+  a.cv_wx = L.cv_wx; a.cv_bx = L.cv_bx; a.cv_blk = L.cv_blk; a.cv_wo = L.cv_wo; a.cv_bo = L.cv_bo;
+  a.idesc = umma_idesc_f16(TILE_M, c->W, c->precision == BFK_PREC_BF16 ? 1 : 0);
+  a.plan = make_smem_plan(*c);
+  a.err_flag = nullptr;
+  fill_tableau(method, a);
+  if (mode == 1) { a.S = 1; }
+
+  int dev = 0, sms = 0;
+  CK(cudaGetDevice(&dev));
+  CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  CK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a.plan.total));
+  const long long n_pairs = (B + TILES_PER_CTA * TILE_M - 1) / (TILES_PER_CTA * TILE_M);
+  const unsigned grid = (unsigned)(n_pairs < sms ? n_pairs : sms);
+  fn<<<grid, NUM_THREADS, a.plan.total, st>>>(a);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_velocity(const bfk_net_config* c, const void* packed, const float* table, const float* pre_add,
+                            const float* post_add, int64_t rpg, const float* tmask, const float* xz, float* out, int64_t B,
+                            void* stream_) {
+  static const float one = 1.f;
+  (void)one;
+  // step_h is read once per step; any valid device float will do for the single evaluation: reuse the table
+  return launch_sampler(c, packed, table, table, BFK_METHOD_EULER, 1, pre_add, post_add, rpg, tmask, xz, out, B, 1,
+                        (cudaStream_t)stream_);
+}
+
+extern "C" int bfk_sample_fixed(const bfk_net_config* c, const void* packed, const float* table, const float* step_h,
+                                int32_t method, int64_t n_steps, const float* pre_add, const float* post_add, int64_t rpg,
+                                const float* tmask, const float* x_in, float* x_out, int64_t B, void* stream_) {
+  return launch_sampler(c, packed, table, step_h, method, n_steps, pre_add, post_add, rpg, tmask, x_in, x_out, B, 0,
+                        (cudaStream_t)stream_);
+}

@@ -1,0 +1,209 @@
+// Weight packing and the two per-call prologue kernels (conditions hoist, per-evaluation FiLM / schedule table).
+// All fp32 CUDA-core work: O(params + datasets + evaluations), not O(draws x steps).
+#pragma once
+#include <cuda_runtime.h>
+#include <math_constants.h>
+
+#include "bfk_layout.h"
+#include "bfk_ptx.cuh"
+
+namespace bfk {
+
+template <int ACT>
+__device__ __forceinline__ float act_fn(float x) {
+  if (ACT == BFK_ACT_MISH) {  // x*tanh(softplus(x)) = x*p/(p+2), p = e^x (e^x + 2)
+    float e = ex2_approx(fminf(x, 20.f) * 1.4426950408889634f);
+    float p = e * (e + 2.f);
+    return x * p * rcp_approx(p + 2.f);
+  } else if (ACT == BFK_ACT_SILU) {
+    float e = ex2_approx(fminf(-x, 80.f) * 1.4426950408889634f);
+    return x * rcp_approx(1.f + e);
+  } else if (ACT == BFK_ACT_RELU) {
+    return fmaxf(x, 0.f);
+  } else if (ACT == BFK_ACT_GELU) {
+    return 0.5f * x * (1.f + erff(x * 0.7071067811865476f));
+  } else {
+    return tanhf(x);
+  }
+}
+__device__ __forceinline__ float act_rt(int act, float x) {
+  switch (act) {
+    case BFK_ACT_MISH: return act_fn<BFK_ACT_MISH>(x);
+    case BFK_ACT_SILU: return act_fn<BFK_ACT_SILU>(x);
+    case BFK_ACT_RELU: return act_fn<BFK_ACT_RELU>(x);
+    case BFK_ACT_GELU: return act_fn<BFK_ACT_GELU>(x);
+    default: return act_fn<BFK_ACT_TANH>(x);
+  }
+}
+
+// (K,N) fp32 row-major (Keras (in,out))  ->  [K/8][N][8] 16-bit: the K-major no-swizzle UMMA operand image, so that any
+// slab of K rows is one contiguous byte range (bulk-copyable) and LBO = N*16, SBO = 128.
+__global__ void pack_gemm_kernel(const float* __restrict__ src, int K, int N, int bf16, uint16_t* __restrict__ dst) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;  // one thread per (k8, n)
+  if (idx >= (K / 8) * N) return;
+  int n = idx % N, k8 = idx / N;
+  uint16_t out[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    float v = src[(size_t)(k8 * 8 + i) * N + n];
+    if (bf16) {
+      __nv_bfloat16 b = __float2bfloat16_rn(v);
+      out[i] = *reinterpret_cast<uint16_t*>(&b);
+    } else {
+      __half h = __float2half_rn(v);
+      out[i] = *reinterpret_cast<uint16_t*>(&h);
+    }
+  }
+  *reinterpret_cast<uint4*>(dst + (size_t)idx * 8) = *reinterpret_cast<uint4*>(out);
+}
+
+__global__ void copy_f32_kernel(const float* __restrict__ src, float* __restrict__ dst, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = src ? src[i] : 0.f;
+}
+__global__ void fill_f32_kernel(float* __restrict__ dst, float v, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = v;
+}
+// src (rows, cols) -> dst (rows_pad, cols_pad) zero padded;  transpose=1: dst[c][r] = src[r][c] with dst (cols_pad? no: see use)
+__global__ void pad2d_kernel(const float* __restrict__ src, int rows, int cols, float* __restrict__ dst, int drows, int dcols) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= drows * dcols) return;
+  int r = i / dcols, c = i % dcols;
+  dst[i] = (r < rows && c < cols) ? src[(size_t)r * cols + c] : 0.f;
+}
+
+// conditions (G,C) -> pre_add (G,W), post_add (G,W)   [time_mlp.py:133-139 hoisted; SURVEY §7.3-2]
+//   concat: post = bm + act(c Wc + bc) Wm[W:2W,:],  pre = (unused)
+//   add   : pre  = c Wc + bc,                         post = bm
+__global__ void cond_prologue_kernel(bfk_net_config cfg, const unsigned char* __restrict__ packed, PackedLayout L,
+                                     const float* __restrict__ cond, long long G, float* __restrict__ pre_add,
+                                     float* __restrict__ post_add) {
+  extern __shared__ float sh[];  // [C] conditions, [W] act(hc)
+  const int W = cfg.W, C = cfg.C;
+  float* sc = sh;
+  float* sa = sh + C;
+  const float* ck = reinterpret_cast<const float*>(packed + L.c_k);
+  const float* cb = reinterpret_cast<const float*>(packed + L.c_b);
+  const float* mc = reinterpret_cast<const float*>(packed + L.m_c);
+  const float* mb = reinterpret_cast<const float*>(packed + L.m_b);
+  for (long long g = blockIdx.x; g < G; g += gridDim.x) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < C; i += blockDim.x) sc[i] = cond[g * C + i];
+    __syncthreads();
+    for (int k = threadIdx.x; k < W; k += blockDim.x) {
+      float hc = cb[k];
+      for (int i = 0; i < C; ++i) hc = fmaf(sc[i], ck[(size_t)i * W + k], hc);
+      if (cfg.merge == BFK_MERGE_ADD) {
+        pre_add[g * W + k] = hc;
+        post_add[g * W + k] = mb[k];
+      } else {
+        sa[k] = act_rt(cfg.activation, hc);
+      }
+    }
+    if (cfg.merge == BFK_MERGE_CONCAT) {
+      __syncthreads();
+      for (int k = threadIdx.x; k < W; k += blockDim.x) {
+        float acc = mb[k];
+        for (int j = 0; j < W; ++j) acc = fmaf(sa[j], mc[(size_t)j * W + k], acc);
+        post_add[g * W + k] = acc;
+      }
+    }
+  }
+}
+
+// DiffusionModel probability-flow velocity as  v = coefZ * z + coefP * pred  (diffusion_model.py:351-405, 466-489,
+// 539-552; noise_schedule.py:70-119; edm_noise_schedule.py:61-108; cosine_noise_schedule.py:60-82), evaluated in double.
+__device__ inline void schedule_coefs(const bfk_schedule& s, double t, double* coefZ, double* coefP, double* net_time) {
+  if (s.model == BFK_MODEL_FM) {
+    *coefZ = 0.0; *coefP = 1.0; *net_time = t;
+    return;
+  }
+  double lam, beta;
+  if (s.schedule == BFK_SCHED_EDM) {
+    double smin = pow(s.sigma_min, 1.0 / s.rho), smax = pow(s.sigma_max, 1.0 / s.rho);
+    double u = smax + (1.0 - t) * (smin - smax);
+    lam = -2.0 * s.rho * log(u);
+    double dsnr = 2.0 * s.rho * (smin - smax) / u;
+    double factor = exp(-lam) / (1.0 + exp(-lam));
+    beta = -factor * dsnr;
+  } else {
+    double tt = s.t_min + (s.t_max - s.t_min) * t;
+    lam = -2.0 * log(tan(CUDART_PI * tt * 0.5)) + 2.0 * s.shift;
+    // reference quirk kept: derivative_log_snr truncates the already truncated time again (cosine_noise_schedule.py:70-75)
+    double t_back = 2.0 / CUDART_PI * atan(exp((2.0 * s.shift - lam) * 0.5));
+    double t2 = s.t_min + (s.t_max - s.t_min) * t_back;
+    double dsnr_dt = -(2.0 * CUDART_PI) / sin(CUDART_PI * t2) * (s.t_max - s.t_min);
+    double factor = exp(-lam) / (1.0 + exp(-lam));
+    beta = -factor * dsnr_dt;
+  }
+  double alpha, sigma;
+  if (s.exploding) { alpha = 1.0; sigma = sqrt(exp(-lam)); }
+  else { alpha = sqrt(1.0 / (1.0 + exp(-lam))); sigma = sqrt(1.0 / (1.0 + exp(lam))); }
+  double pz, pp;  // x_pred = pz*z + pp*pred
+  switch (s.prediction) {
+    case BFK_PRED_VELOCITY: pz = alpha; pp = -sigma; break;
+    case BFK_PRED_NOISE: pz = 1.0 / alpha; pp = -sigma / alpha; break;
+    case BFK_PRED_F: {
+      double sd = s.sigma_data, e = exp(-lam);
+      pz = sd * sd * alpha / (e + sd * sd);
+      pp = exp(-lam * 0.5) * sd / sqrt(e + sd * sd);
+    } break;
+    case BFK_PRED_X: pz = 0.0; pp = 1.0; break;
+    default: pz = 1.0 / alpha; pp = sigma * sigma / alpha; break;
+  }
+  // score = ((alpha*pz - 1) z + alpha*pp pred)/sigma^2 ; v = f - 0.5 beta score, f = -0.5 beta z (preserving) or 0
+  double s2 = sigma * sigma;
+  double fz = s.exploding ? 0.0 : -0.5 * beta;
+  *coefZ = fz - 0.5 * beta * (alpha * pz - 1.0) / s2;
+  *coefP = -0.5 * beta * alpha * pp / s2;
+  *net_time = 2.0 * ((lam - s.log_snr_min) / (s.log_snr_max - s.log_snr_min)) - 1.0;  // diffusion_model.py:711-717
+}
+
+// times (n) -> table (n, stride): [L][W] FiLM beta, ([L][W] FiLM gamma), TABLE_SCALARS scalars
+__global__ void eval_table_kernel(bfk_net_config cfg, const unsigned char* __restrict__ packed, PackedLayout L,
+                                  bfk_schedule sched, const float* __restrict__ times, long long n, int stride,
+                                  float* __restrict__ table) {
+  __shared__ float emb[80];
+  __shared__ float sc[4];
+  const int W = cfg.W, T = cfg.T;
+  const float* freq = reinterpret_cast<const float*>(packed + L.freq);
+  for (long long e = blockIdx.x; e < n; e += gridDim.x) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double cz, cp, nt;
+      schedule_coefs(sched, (double)times[e], &cz, &cp, &nt);
+      sc[0] = (float)cz; sc[1] = (float)cp; sc[2] = times[e]; sc[3] = (float)nt;
+    }
+    __syncthreads();
+    const float t = sc[3];
+    // fourier_embedding.py:71-73: proj = t * w * 2 * pi * scale (left to right, fp32); emb = [t, sin, cos]
+    if (T == 1) {
+      if (threadIdx.x == 0) emb[0] = t;
+    } else {
+      for (int i = threadIdx.x; i < L.Th; i += blockDim.x) {
+        float proj = t * freq[i];
+        proj = proj * 2.f;
+        proj = proj * 3.14159265358979323846f;
+        proj = proj * cfg.fourier_scale;
+        emb[1 + i] = sinf(proj);
+        emb[1 + L.Th + i] = cosf(proj);
+      }
+      if (threadIdx.x == 0) emb[0] = t;
+    }
+    __syncthreads();
+    float* row = table + e * stride;
+    const int nv = cfg.film_use_gamma ? 2 : 1;
+    for (int idx = threadIdx.x; idx < nv * cfg.L * W; idx += blockDim.x) {
+      int which = idx / (cfg.L * W), rem = idx % (cfg.L * W), l = rem / W, k = rem % W;
+      const float* fk = reinterpret_cast<const float*>(packed + (which ? L.film_g_k : L.film_b_k)) + (size_t)l * T * W;
+      const float* fb = reinterpret_cast<const float*>(packed + (which ? L.film_g_b : L.film_b_b)) + (size_t)l * W;
+      float acc = 0.f;
+      for (int j = 0; j < T; ++j) acc = fmaf(emb[j], fk[(size_t)j * W + k], acc);
+      row[idx] = acc + fb[k];
+    }
+    if (threadIdx.x < TABLE_SCALARS) row[nv * cfg.L * W + threadIdx.x] = threadIdx.x < 4 ? sc[threadIdx.x] : 0.f;
+  }
+}
+
+}  // namespace bfk

@@ -1,0 +1,636 @@
+"""Host-side mirror of the reference's inference-network surface (torch ``nn.Module``s, no Keras):
+
+  InferenceNetwork  <- bayesflow/networks/inference/inference_network.py:12-138
+  TimeMLP           <- bayesflow/networks/subnets/mlp/time_mlp.py:14-216           (weights + config only)
+  FlowMatching      <- bayesflow/networks/inference/flow_matching/flow_matching.py:27-337
+  DiffusionModel    <- bayesflow/networks/inference/diffusion/diffusion_model.py:35-869 (probability-flow ODE path)
+  DiagonalNormal    <- bayesflow/distributions/diagonal_normal.py:17-105
+
+Same constructor keywords, method names, kwargs merge order and error types as the reference.  All arithmetic on
+the hot path runs in libbfk (sm_100a CUDA) through the C ABI in include/bfk.h; there is no eager / CPU path.
+Parameters are stored in the reference's variable order with (in, out) kernels so that ``state_dict()`` values
+can be exchanged with a Keras ``FlowMatching`` via get_weights()/set_weights().
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from collections.abc import Sequence
+
+import numpy as np
+import torch
+from torch import nn
+
+from . import _lib
+from .integrate import integrate as _integrate
+
+# networks/defaults.py:13-26, 50, 52
+TIME_MLP_DEFAULTS = {
+    "widths": (256, 256, 256, 256, 256), "time_embedding_dim": 32, "fourier_scale": 30.0, "activation": "mish",
+    "kernel_initializer": "he_normal", "residual": True, "dropout": 0.05, "norm": "layer", "merge": "concat",
+    "film_use_gamma": False,
+}
+FLOW_MATCHING_INTEGRATE_DEFAULTS = {"method": "tsit5", "steps": "adaptive"}
+DIFFUSION_INTEGRATE_DEFAULTS = {"method": "two_step_adaptive", "steps": "adaptive"}
+DETERMINISTIC_METHODS = ["euler", "rk45", "tsit5"]
+STOCHASTIC_METHODS = ["euler_maruyama", "sea", "shark", "two_step_adaptive", "langevin"]
+
+
+def _he_normal(fan_in, fan_out, generator=None):
+    std = math.sqrt(2.0 / fan_in) / 0.87962566103423978
+    w = torch.empty(fan_in, fan_out)
+    nn.init.trunc_normal_(w, 0.0, std, -2 * std, 2 * std, generator=generator)
+    return w
+
+
+def _glorot_uniform(fan_in, fan_out, generator=None):
+    lim = math.sqrt(6.0 / (fan_in + fan_out))
+    return (torch.rand(fan_in, fan_out, generator=generator) * 2 - 1) * lim
+
+
+class _Dense(nn.Module):
+    """Parameter holder for a keras.layers.Dense: kernel (in,out), bias (out)."""
+
+    def __init__(self, fan_in, units, init="he_normal"):
+        super().__init__()
+        self.kernel = nn.Parameter(_he_normal(fan_in, units) if init == "he_normal" else _glorot_uniform(fan_in, units))
+        self.bias = nn.Parameter(torch.zeros(units))
+
+
+class DiagonalNormal(nn.Module):
+    """distributions/diagonal_normal.py:17-105 (fixed mean / std)."""
+
+    def __init__(self, mean=0.0, std=1.0, **kwargs):
+        super().__init__()
+        self.mean, self.std, self.dim, self.built = mean, std, None, False
+
+    def build(self, input_shape):
+        if self.built:
+            return
+        self.dim = int(input_shape[-1])
+        self.register_buffer("_mean", torch.broadcast_to(torch.as_tensor(self.mean, dtype=torch.float32), (self.dim,)).clone())
+        self.register_buffer("_std", torch.broadcast_to(torch.as_tensor(self.std, dtype=torch.float32), (self.dim,)).clone())
+        self.built = True
+
+    def log_prob(self, samples, *, normalize=True):
+        result = -0.5 * torch.sum((samples - self._mean) ** 2 / self._std ** 2, dim=-1)
+        if normalize:
+            result = result + (-0.5 * self.dim * math.log(2.0 * math.pi) - torch.sum(torch.log(self._std)))
+        return result
+
+    def sample(self, batch_shape, seed=None):
+        if isinstance(batch_shape, int):
+            batch_shape = (batch_shape,)
+        dev = self._mean.device
+        gen = None
+        if seed is not None:
+            gen = seed if isinstance(seed, torch.Generator) else torch.Generator(device=dev).manual_seed(int(seed))
+        z = torch.randn(tuple(batch_shape) + (self.dim,), device=dev, generator=gen)
+        return self._mean + self._std * z
+
+
+class _Block(nn.Module):
+    def __init__(self, fan_in, width, T, film_use_gamma, norm):
+        super().__init__()
+        self.dense = _Dense(fan_in, width)
+        self.film = nn.Module()
+        if film_use_gamma:
+            self.film.to_gamma = _Dense(T, width)
+        self.film.to_beta = _Dense(T, width)
+        if norm == "layer":
+            self.norm = nn.Module()
+            self.norm.gamma = nn.Parameter(torch.ones(width))
+            self.norm.beta = nn.Parameter(torch.zeros(width))
+        elif norm == "rms":
+            self.norm = nn.Module()
+            self.norm.scale = nn.Parameter(torch.ones(width))
+
+
+class TimeMLP(nn.Module):
+    """Weights and configuration of the reference TimeMLP (time_mlp.py:54-183).  The arithmetic of ``call``
+    (time_mlp.py:125-147) lives in the CUDA kernels; this class only owns parameters in reference order."""
+
+    def __init__(self, widths: Sequence[int] = (256, 256), *, time_embedding_dim: int = 32, time_emb=None,
+                 fourier_scale: float = 30.0, activation="mish", kernel_initializer="he_normal", residual: bool = True,
+                 dropout=0.05, norm="layer", merge="concat", film_use_gamma: bool = False, **kwargs):
+        super().__init__()
+        if len(widths) == 0:
+            raise ValueError("TimeMLP requires at least one hidden width.")
+        if merge not in ("add", "concat"):
+            raise ValueError(f"Unknown merge mode: {merge!r} (expected 'add' or 'concat').")
+        if time_emb is not None:
+            raise NotImplementedError("custom time_emb layers are outside the accelerated path")
+        if not isinstance(activation, str) or activation not in _lib.ACT:
+            raise ValueError(f"activation {activation!r} is not supported by the CUDA path; one of {sorted(_lib.ACT)}")
+        if norm not in (None, "layer", "rms"):
+            if isinstance(norm, str) and norm != "batch":
+                raise ValueError(f"Unknown normalization strategy: {norm!r}.")
+            raise NotImplementedError(f"norm={norm!r} is outside the accelerated path (layer / rms / None)")
+        if kernel_initializer != "he_normal":
+            raise NotImplementedError("only kernel_initializer='he_normal' is implemented")
+        if time_embedding_dim != 1 and time_embedding_dim % 2 != 0:
+            raise ValueError(f"Embedding dimension must be even, but is {time_embedding_dim}.")
+        self.widths = tuple(int(w) for w in widths)
+        self.time_embedding_dim, self.fourier_scale = int(time_embedding_dim), float(fourier_scale)
+        self.activation, self.kernel_initializer, self.residual = activation, kernel_initializer, bool(residual)
+        self.dropout, self.norm, self.merge, self.film_use_gamma = dropout, norm, merge, bool(film_use_gamma)
+        self.built = False
+
+    @property
+    def T(self):
+        return self.time_embedding_dim + 1 if self.time_embedding_dim > 1 else 1
+
+    def build(self, input_shape):
+        if self.built:
+            return
+        x_shape, t_shape, conditions_shape = input_shape
+        D, W0 = int(x_shape[-1]), self.widths[0]
+        if self.time_embedding_dim > 1:
+            self.time_emb = nn.Module()
+            self.time_emb.frequencies = nn.Parameter(torch.randn(self.time_embedding_dim // 2) * 0.05)
+        self.x_proj = _Dense(D, W0)
+        self.c_proj = self.merge_proj = None
+        if conditions_shape is not None:
+            Cdim = int(conditions_shape[-1])
+            self.c_proj = _Dense(Cdim, W0)
+            self.merge_proj = _Dense(2 * W0 if self.merge == "concat" else W0, W0)
+        blocks, prev = [], W0
+        for w in self.widths:
+            if w != prev:
+                raise NotImplementedError("the accelerated path needs all hidden widths equal (no residual projector)")
+            blocks.append(_Block(prev, w, self.T, self.film_use_gamma, self.norm))
+            prev = w
+        self.blocks = nn.ModuleList(blocks)
+        self.built = True
+
+    def compute_output_shape(self, input_shape):
+        return tuple(input_shape[0][:-1]) + (self.widths[-1],)
+
+    def get_config(self):
+        return {"widths": self.widths, "time_embedding_dim": self.time_embedding_dim, "time_emb": None,
+                "fourier_scale": self.fourier_scale, "activation": self.activation,
+                "kernel_initializer": self.kernel_initializer, "residual": self.residual, "dropout": self.dropout,
+                "norm": self.norm, "merge": self.merge, "film_use_gamma": self.film_use_gamma}
+
+
+def find_network(arg, **kwargs):
+    """utils/dispatch/find_network.py:5-36 restricted to what the accelerated path covers."""
+    if isinstance(arg, str):
+        if arg == "time_mlp":
+            return TimeMLP(**kwargs)
+        raise ValueError(f"Unknown or unsupported network name for the accelerated path: {arg!r}")
+    if isinstance(arg, type):
+        if issubclass(arg, TimeMLP):
+            return arg(**kwargs)
+        raise TypeError(f"Cannot build a subnet from {arg!r}; the accelerated path needs a TimeMLP")
+    if isinstance(arg, TimeMLP):
+        return arg
+    raise TypeError(f"Cannot infer network from {arg!r}.")
+
+
+# ======================================================================================================================
+# CUDA engine: owns the packed weights and turns python calls into C-ABI calls
+# ======================================================================================================================
+class _Engine:
+    def __init__(self, net: "InferenceNetwork"):
+        self.net = net
+        self._packed = None
+        self._key = None
+        self.cfg = None
+
+    # -- configuration / weights -------------------------------------------------------------------------------------
+    def _make_cfg(self):
+        sub, net = self.net.subnet, self.net
+        cfg = _lib.NetConfig()
+        cfg.D, cfg.C = net._D, (net._C or 0)
+        cfg.W, cfg.L, cfg.T = sub.widths[0], len(sub.widths), sub.T
+        cfg.activation = _lib.ACT[sub.activation]
+        cfg.merge = _lib.MERGE[sub.merge] if net._C else 0
+        cfg.norm = _lib.NORM[sub.norm]
+        cfg.residual, cfg.film_use_gamma = int(sub.residual), int(sub.film_use_gamma)
+        cfg.precision = _lib.PREC[net.precision]
+        cfg.fourier_scale = sub.fourier_scale
+        return cfg
+
+    def prepare(self):
+        net, sub = self.net, self.net.subnet
+        params = list(net.parameters())
+        key = (net.precision,) + tuple((p.data_ptr(), p._version) for p in params)
+        if self._packed is not None and key == self._key:
+            return
+        L = _lib.lib()
+        dev = params[0].device
+        if dev.type != "cuda":
+            raise RuntimeError("bayesflow_b200: move the network to a CUDA device first (no CPU fallback)")
+        self.cfg = cfg = self._make_cfg()
+        if not L.bfk_fused_supported(C.byref(cfg)):
+            raise NotImplementedError(
+                f"config D={cfg.D} W={cfg.W} L={cfg.L} is not supported by the fused sampler (need D<=8, W<=256, W%32==0)")
+        w = _lib.Weights()
+        keep = []
+
+        def P(t):
+            t = t.detach().to(torch.float32).contiguous()
+            keep.append(t)
+            return t.data_ptr()
+
+        if sub.time_embedding_dim > 1:
+            w.freq = P(sub.time_emb.frequencies)
+        w.x_k, w.x_b = P(sub.x_proj.kernel), P(sub.x_proj.bias)
+        if net._C:
+            w.c_k, w.c_b = P(sub.c_proj.kernel), P(sub.c_proj.bias)
+            w.m_k, w.m_b = P(sub.merge_proj.kernel), P(sub.merge_proj.bias)
+        for i, b in enumerate(sub.blocks):
+            w.dense_k[i], w.dense_b[i] = P(b.dense.kernel), P(b.dense.bias)
+            if sub.film_use_gamma:
+                w.film_g_k[i], w.film_g_b[i] = P(b.film.to_gamma.kernel), P(b.film.to_gamma.bias)
+            w.film_b_k[i], w.film_b_b[i] = P(b.film.to_beta.kernel), P(b.film.to_beta.bias)
+            if sub.norm == "layer":
+                w.norm_g[i], w.norm_b[i] = P(b.norm.gamma), P(b.norm.beta)
+            elif sub.norm == "rms":
+                w.norm_g[i] = P(b.norm.scale)
+        w.out_k, w.out_b = P(net.output_projector.kernel), P(net.output_projector.bias)
+        nbytes = L.bfk_packed_bytes(C.byref(cfg))
+        packed = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        _lib.check(L.bfk_pack(C.byref(cfg), C.byref(w), _lib.ptr(packed), _lib.stream_ptr()), "bfk_pack")
+        self._packed, self._key = packed, key
+        self._tstride = int(L.bfk_table_stride(C.byref(cfg)))
+
+    # -- per-call prologues --------------------------------------------------------------------------------------------
+    def cond_tables(self, conditions, B, repeats=None):
+        """conditions -> (pre_add, post_add, rows_per_group).  Rows of a dataset share their condition vector
+        (approximators/helpers/samplers.py:51-63), so the conditions half of TimeMLP is computed once per dataset."""
+        net = self.net
+        if conditions is None or not net._C:
+            return None, None, 1
+        cond = conditions.detach().to(torch.float32)
+        if cond.ndim != 2 or cond.shape[-1] != net._C:
+            raise ValueError(f"conditions must have shape (rows, {net._C}), got {tuple(cond.shape)}")
+        if repeats is None:
+            if cond.shape[0] != B:
+                raise ValueError(f"conditions has {cond.shape[0]} rows, expected {B}")
+            repeats = 1
+            if net.detect_repeats and B > 1:
+                uniq, counts = torch.unique_consecutive(cond, dim=0, return_counts=True)
+                if uniq.shape[0] < B and bool((counts == counts[0]).all()):
+                    cond, repeats = uniq, int(counts[0])
+        elif cond.shape[0] * repeats != B:
+            raise ValueError(f"conditions rows ({cond.shape[0]}) x repeats ({repeats}) != batch ({B})")
+        cond = cond.contiguous()
+        G = cond.shape[0]
+        W = self.cfg.W
+        post = torch.empty(G, W, device=cond.device, dtype=torch.float32)
+        pre = torch.empty(G, W, device=cond.device, dtype=torch.float32) if net.subnet.merge == "add" else None
+        _lib.check(_lib.lib().bfk_cond_prologue(C.byref(self.cfg), _lib.ptr(self._packed), _lib.ptr(cond), G,
+                                                _lib.ptr(pre), _lib.ptr(post), _lib.stream_ptr()), "bfk_cond_prologue")
+        return pre, post, repeats
+
+    def eval_table(self, times: np.ndarray):
+        dev = self._packed.device
+        t = torch.from_numpy(np.ascontiguousarray(times, dtype=np.float32)).to(dev, non_blocking=True)
+        table = torch.empty(t.numel(), self._tstride, device=dev, dtype=torch.float32)
+        sched = self.net._schedule_struct()
+        _lib.check(_lib.lib().bfk_eval_table(C.byref(self.cfg), _lib.ptr(self._packed), C.byref(sched), _lib.ptr(t),
+                                             t.numel(), _lib.ptr(table), _lib.stream_ptr()), "bfk_eval_table")
+        return table
+
+
+class _Run:
+    """One sampling call: the engine plus the per-call hoisted tables."""
+
+    def __init__(self, engine, pre, post, rpg, target_mask):
+        self.e, self.pre, self.post, self.rpg = engine, pre, post, rpg
+        self.tmask = None
+        if target_mask is not None:
+            tm = torch.as_tensor(target_mask, dtype=torch.float32, device=engine._packed.device)
+            if tm.numel() != engine.cfg.D:
+                raise NotImplementedError("target_mask must be feature-level, shape (D,), on the accelerated path")
+            self.tmask = tm.reshape(-1).contiguous()
+        self.info = {}
+
+    def _check_x(self, x):
+        if not x.is_cuda:
+            raise RuntimeError("bayesflow_b200 runs on CUDA tensors only (no CPU fallback)")
+        if x.ndim != 2 or x.shape[-1] != self.e.cfg.D:
+            raise ValueError(f"expected (rows, {self.e.cfg.D}) state, got {tuple(x.shape)}")
+        return x.detach().to(torch.float32).contiguous()
+
+    def velocity(self, x, time: float):
+        e = self.e
+        x = self._check_x(x)
+        table = e.eval_table(np.asarray([time], dtype=np.float32))
+        out = torch.empty_like(x)
+        _lib.check(_lib.lib().bfk_velocity(C.byref(e.cfg), _lib.ptr(e._packed), _lib.ptr(table), _lib.ptr(self.pre),
+                                           _lib.ptr(self.post), self.rpg, _lib.ptr(self.tmask), _lib.ptr(x),
+                                           _lib.ptr(out), x.shape[0], _lib.stream_ptr()), "bfk_velocity")
+        return out
+
+    def run_fixed(self, x, times, hs, method):
+        e = self.e
+        x = self._check_x(x)
+        table = e.eval_table(times)
+        h = torch.from_numpy(np.ascontiguousarray(hs, dtype=np.float32)).to(x.device, non_blocking=True)
+        out = torch.empty_like(x)
+        _lib.check(_lib.lib().bfk_sample_fixed(C.byref(e.cfg), _lib.ptr(e._packed), _lib.ptr(table), _lib.ptr(h),
+                                               _lib.METHOD[method], h.numel(), _lib.ptr(self.pre), _lib.ptr(self.post),
+                                               self.rpg, _lib.ptr(self.tmask), _lib.ptr(x), _lib.ptr(out), x.shape[0],
+                                               _lib.stream_ptr()), "bfk_sample_fixed")
+        self.info = {"steps": int(h.numel()), "evals": int(len(times)), "rejected": 0}
+        return out
+
+    def run_adaptive(self, x, start_time, stop_time, min_steps, max_steps, method, atol=1e-6, rtol=1e-4):
+        raise NotImplementedError("adaptive stepping lands in the next milestone")
+
+
+# ======================================================================================================================
+# The reference's surface
+# ======================================================================================================================
+def _as_shape(batch_shape, kwargs):
+    # utils/decorators.py:102-114 allow_batch_size
+    if batch_shape is None and "batch_size" in kwargs:
+        batch_shape = kwargs.pop("batch_size")
+    if isinstance(batch_shape, (int, np.integer)):
+        batch_shape = (int(batch_shape),)
+    return tuple(batch_shape)
+
+
+class InferenceNetwork(nn.Module):
+    """inference_network.py:12-138."""
+
+    _SUBNET_MASK_KEYS = {"attention_mask", "mask"}
+
+    def __init__(self, base_distribution="normal", precision: str = "fp16", detect_repeats: bool = True, **kwargs):
+        super().__init__()
+        if isinstance(base_distribution, str):
+            if base_distribution != "normal":
+                raise NotImplementedError("only base_distribution='normal' is on the accelerated path")
+            base_distribution = DiagonalNormal()
+        self.base_distribution = base_distribution
+        if precision not in _lib.PREC:
+            raise ValueError(f"precision must be one of {sorted(_lib.PREC)}")
+        self.precision = precision  # tensor-core operand type (fp32 accumulate); B200-specific knob
+        self.detect_repeats = detect_repeats
+        self.built = False
+        self._metrics = []
+        self._engine = _Engine(self)
+
+    def call(self, xz, conditions=None, inverse=False, density=False, training=False, **kwargs):
+        if inverse:
+            return self._inverse(xz, conditions=conditions, density=density, training=training, **kwargs)
+        return self._forward(xz, conditions=conditions, density=density, training=training, **kwargs)
+
+    forward = call
+
+    def _forward(self, x, conditions=None, density=False, training=False, **kwargs):
+        raise NotImplementedError
+
+    def _inverse(self, z, conditions=None, density=False, training=False, **kwargs):
+        raise NotImplementedError
+
+    def sample(self, batch_shape=None, conditions=None, seed=None, **kwargs):
+        # inference_network.py:109-125
+        batch_shape = _as_shape(batch_shape, kwargs)
+        if "compute_prior_score" in kwargs:
+            raise NotImplementedError("compositional sampling is out of scope (SURVEY.md §2 row 2)")
+        samples = self.base_distribution.sample(batch_shape, seed=seed)
+        flat = samples.reshape(-1, samples.shape[-1])
+        out = self(flat, conditions=conditions, inverse=True, density=False, seed=seed, **kwargs)
+        return out.reshape(samples.shape)
+
+    def log_prob(self, samples, conditions=None, **kwargs):
+        _, log_density = self(samples, conditions=conditions, inverse=False, density=True, **kwargs)
+        return log_density
+
+    def compute_metrics(self, x, conditions=None, sample_weight=None, stage="training", **kwargs):
+        raise NotImplementedError
+
+    @property
+    def variables(self):
+        return list(self.parameters())
+
+    # -- shared build of subnet + projector (flow_matching.py:180-199, diffusion_model.py build) -----------------------
+    def _build_common(self, xz_shape, conditions_shape):
+        self._D = int(xz_shape[-1])
+        self._C = int(conditions_shape[-1]) if conditions_shape is not None else None
+        self.base_distribution.build(xz_shape)
+        time_shape = (xz_shape[0], 1)
+        self.subnet.build((xz_shape, time_shape, conditions_shape))
+        self.output_projector = _Dense(self.subnet.widths[-1], self._D, init="glorot_uniform")
+
+    def _run(self, conditions, B, kwargs) -> _Run:
+        if not self.built:
+            raise RuntimeError("network is not built; call build(xz_shape, conditions_shape) first")
+        if (conditions is None) != (self._C is None):
+            raise ValueError("network was built " + ("without" if self._C is None else "with") + " conditions")
+        self._engine.prepare()
+        if self.unconditional_mode and conditions is not None:
+            conditions = torch.zeros_like(conditions)
+        pre, post, rpg = self._engine.cond_tables(conditions, B, kwargs.get("conditions_repeats"))
+        return _Run(self._engine, pre, post, rpg, kwargs.get("target_mask"))
+
+    @staticmethod
+    def _apply_targets(x, kwargs):
+        target_mask, targets_fixed = kwargs.get("target_mask"), kwargs.get("targets_fixed")
+        if target_mask is not None:
+            tm = torch.broadcast_to(torch.as_tensor(target_mask, dtype=x.dtype, device=x.device), x.shape)
+            tf = torch.broadcast_to(torch.as_tensor(targets_fixed, dtype=x.dtype, device=x.device), x.shape)
+            x = tm * x + (1 - tm) * tf
+        return x
+
+    _INTEGRATE_KEYS = ("start_time", "stop_time", "min_steps", "max_steps", "steps", "method", "atol", "rtol")
+
+    def _integrate_call(self, run, x, integrate_kwargs):
+        ik = {k: v for k, v in integrate_kwargs.items() if k in self._INTEGRATE_KEYS}  # filter_kwargs, dict_utils.py:52-63
+        out = _integrate(run, x, **ik)
+        self.last_integration_info = run.info
+        return out
+
+
+class FlowMatching(InferenceNetwork):
+    """flow_matching.py:27-337.  Extra keywords (`precision`, `detect_repeats`) are B200-specific knobs."""
+
+    def __init__(self, subnet="time_mlp", base_distribution="normal", use_optimal_transport: bool = False, loss_fn="mse",
+                 integrate_kwargs=None, optimal_transport_kwargs=None, subnet_kwargs=None,
+                 time_power_law_alpha: float = 0.0, drop_cond_prob: float = 0.0, drop_target_prob: float = 0.0, **kwargs):
+        super().__init__(base_distribution, **kwargs)
+        self.use_optimal_transport = use_optimal_transport
+        if use_optimal_transport:
+            raise NotImplementedError("optimal-transport pairing is out of scope (SURVEY.md §8f rank 4)")
+        self.integrate_kwargs = FLOW_MATCHING_INTEGRATE_DEFAULTS | (integrate_kwargs or {})
+        self.optimal_transport_kwargs = optimal_transport_kwargs or {}
+        if loss_fn not in ("mse", "mae"):
+            raise NotImplementedError("loss_fn must be 'mse' or 'mae' on the accelerated path")
+        self.loss_fn = loss_fn
+        self.time_power_law_alpha = float(time_power_law_alpha)
+        if self.time_power_law_alpha <= -1.0:
+            raise ValueError("'time_power_law_alpha' must be greater than -1.0.")
+        subnet_kwargs = subnet_kwargs or {}
+        if subnet == "time_mlp":
+            subnet_kwargs = TIME_MLP_DEFAULTS | subnet_kwargs
+        self.subnet = find_network(subnet, **subnet_kwargs)
+        self.output_projector = None
+        self.drop_cond_prob = drop_cond_prob
+        self.unconditional_mode = False
+        self.drop_target_prob = drop_target_prob
+
+    def build(self, xz_shape, conditions_shape=None):
+        if self.built:
+            return
+        self._build_common(xz_shape, conditions_shape)
+        self.built = True
+
+    def _schedule_struct(self):
+        s = _lib.Schedule()
+        s.model = 0
+        return s
+
+    def get_config(self):
+        return {"subnet": self.subnet.get_config(), "base_distribution": "normal",
+                "use_optimal_transport": self.use_optimal_transport, "loss_fn": self.loss_fn,
+                "integrate_kwargs": self.integrate_kwargs, "optimal_transport_kwargs": self.optimal_transport_kwargs,
+                "time_power_law_alpha": self.time_power_law_alpha, "drop_cond_prob": self.drop_cond_prob,
+                "drop_target_prob": self.drop_target_prob}
+
+    def velocity(self, xz, time, conditions=None, training=False, **kwargs):
+        # flow_matching.py:220-236
+        if training:
+            raise NotImplementedError("training-mode velocity goes through compute_metrics")
+        if torch.is_tensor(time):
+            if time.numel() != 1 and not bool((time == time.reshape(-1)[0]).all()):
+                raise NotImplementedError("per-row time is only used by the training path (compute_metrics)")
+            time = float(time.reshape(-1)[0])
+        run = self._run(conditions, xz.shape[0], kwargs)
+        return run.velocity(xz, float(np.float32(time)))
+
+    def _forward(self, x, conditions=None, density=False, training=False, **kwargs):
+        # flow_matching.py:254-294
+        integrate_kwargs = self.integrate_kwargs | kwargs
+        x = self._apply_targets(x, kwargs)
+        if density:
+            raise NotImplementedError("log_prob (trace integration) is the next milestone (SURVEY.md §8f rank 1)")
+        run = self._run(conditions, x.shape[0], kwargs)
+        return self._integrate_call(run, x, integrate_kwargs | {"start_time": 1.0, "stop_time": 0.0})
+
+    def _inverse(self, z, conditions=None, density=False, training=False, **kwargs):
+        # flow_matching.py:296-337
+        kwargs.pop("seed", None)
+        integrate_kwargs = self.integrate_kwargs | kwargs
+        z = self._apply_targets(z, kwargs)
+        if density:
+            raise NotImplementedError("log_prob (trace integration) is the next milestone (SURVEY.md §8f rank 1)")
+        run = self._run(conditions, z.shape[0], kwargs)
+        return self._integrate_call(run, z, integrate_kwargs | {"start_time": 0.0, "stop_time": 1.0})
+
+
+class EDMNoiseSchedule:
+    """schedules/edm_noise_schedule.py:21-59 (parameters only; the scalar algebra runs in bfk_eval_table)."""
+    name = "edm_noise_schedule"
+
+    def __init__(self, sigma_data=1.0, sigma_min=1e-4, sigma_max=80.0, variance_type="preserving"):
+        self.sigma_data, self.sigma_min, self.sigma_max, self.rho = sigma_data, sigma_min, sigma_max, 7
+        self._variance_type = variance_type
+        self.log_snr_min, self.log_snr_max = -2 * math.log(sigma_max), -2 * math.log(sigma_min)
+
+    def validate(self):
+        if self.log_snr_min >= self.log_snr_max:
+            raise ValueError("min_log_snr must be less than max_log_snr.")
+
+
+class CosineNoiseSchedule:
+    """schedules/cosine_noise_schedule.py:26-55."""
+    name = "cosine_noise_schedule"
+
+    def __init__(self, min_log_snr=-15.0, max_log_snr=15.0, shift=0.0, weighting="sigmoid"):
+        self._variance_type, self._shift, self._weighting = "preserving", shift, weighting
+        self.log_snr_min, self.log_snr_max = float(min_log_snr), float(max_log_snr)
+        self._t_min = 2 / math.pi * math.atan(math.exp((2 * shift - self.log_snr_max) * 0.5))
+        self._t_max = 2 / math.pi * math.atan(math.exp((2 * shift - self.log_snr_min) * 0.5))
+
+    def validate(self):
+        if self.log_snr_min >= self.log_snr_max:
+            raise ValueError("min_log_snr must be less than max_log_snr.")
+
+
+def find_noise_schedule(arg, **kwargs):
+    # networks/inference/diffusion/dispatch.py:6-35
+    if isinstance(arg, str):
+        if arg == "edm":
+            return EDMNoiseSchedule(**kwargs)
+        if arg == "cosine":
+            return CosineNoiseSchedule(**kwargs)
+        raise ValueError(f"Unsupported noise schedule name: '{arg}'.")
+    if isinstance(arg, type):
+        return arg(**kwargs)
+    if isinstance(arg, (EDMNoiseSchedule, CosineNoiseSchedule)):
+        return arg
+    raise TypeError(f"Unknown noise schedule type: {type(arg)}.")
+
+
+class DiffusionModel(InferenceNetwork):
+    """diffusion_model.py:35-869, probability-flow ODE sampling path (deterministic methods)."""
+
+    def __init__(self, *, subnet="time_mlp", noise_schedule="edm", prediction_type="F", loss_type="noise",
+                 subnet_kwargs=None, schedule_kwargs=None, integrate_kwargs=None, drop_cond_prob: float = 0.0,
+                 drop_target_prob: float = 0.0, **kwargs):
+        super().__init__(base_distribution="normal", **kwargs)
+        if prediction_type not in ["noise", "velocity", "F", "x", "score", "potential"]:
+            raise ValueError(f"Unknown prediction type: {prediction_type}")
+        if loss_type not in ["noise", "velocity", "F"]:
+            raise ValueError(f"Unknown loss type: {loss_type}")
+        if prediction_type == "potential":
+            raise NotImplementedError("prediction_type='potential' is out of scope (SURVEY.md §2 row 2)")
+        self._prediction_type, self._loss_type = prediction_type, loss_type
+        self.noise_schedule = find_noise_schedule(noise_schedule, **(schedule_kwargs or {}))
+        self.noise_schedule.validate()
+        self.integrate_kwargs = DIFFUSION_INTEGRATE_DEFAULTS | (integrate_kwargs or {})
+        subnet_kwargs = subnet_kwargs or {}
+        if subnet == "time_mlp":
+            subnet_kwargs = TIME_MLP_DEFAULTS | subnet_kwargs
+        self.subnet = find_network(subnet, **subnet_kwargs)
+        self.output_projector = None
+        self.drop_cond_prob, self.drop_target_prob = drop_cond_prob, drop_target_prob
+        self.unconditional_mode = False
+
+    def build(self, xz_shape, conditions_shape=None):
+        if self.built:
+            return
+        self._build_common(xz_shape, conditions_shape)
+        self.built = True
+
+    def _schedule_struct(self):
+        ns, s = self.noise_schedule, _lib.Schedule()
+        s.model, s.prediction = 1, _lib.PRED[self._prediction_type]
+        s.exploding = int(ns._variance_type == "exploding")
+        s.log_snr_min, s.log_snr_max = ns.log_snr_min, ns.log_snr_max
+        if isinstance(ns, EDMNoiseSchedule):
+            s.schedule = 0
+            s.sigma_data, s.sigma_min, s.sigma_max, s.rho = ns.sigma_data, ns.sigma_min, ns.sigma_max, ns.rho
+        else:
+            s.schedule, s.sigma_data = 1, 1.0
+            s.shift, s.t_min, s.t_max = ns._shift, ns._t_min, ns._t_max
+        return s
+
+    def velocity(self, xz, time, stochastic_solver=False, conditions=None, training=False, **kwargs):
+        # diffusion_model.py:501-559
+        if stochastic_solver or training:
+            raise NotImplementedError("only the probability-flow ODE velocity is on the accelerated path")
+        if torch.is_tensor(time):
+            time = float(time.reshape(-1)[0])
+        run = self._run(conditions, xz.shape[0], kwargs)
+        return run.velocity(xz, float(np.float32(time)))
+
+    def _inverse(self, z, conditions=None, density=False, training=False, **kwargs):
+        # diffusion_model.py:782-869
+        kwargs.pop("seed", None)
+        integrate_kwargs = {"start_time": 1.0, "stop_time": 0.0}
+        integrate_kwargs |= self.integrate_kwargs
+        integrate_kwargs |= kwargs
+        z = self._apply_targets(z, kwargs)
+        if density:
+            raise NotImplementedError("log_prob (trace integration) is the next milestone (SURVEY.md §8f rank 1)")
+        if integrate_kwargs["method"] in STOCHASTIC_METHODS:
+            raise NotImplementedError(
+                f"method={integrate_kwargs['method']!r}: SDE samplers are out of scope this round (SURVEY.md §8f rank 2); "
+                f"pass one of {DETERMINISTIC_METHODS} for the probability-flow ODE")
+        run = self._run(conditions, z.shape[0], kwargs)
+        return self._integrate_call(run, z, integrate_kwargs)

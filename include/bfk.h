@@ -1,0 +1,119 @@
+/* bfk.h — C ABI of libbfk (B200 / sm_100a kernels for the BayesFlow generative-network hot path).
+ *
+ * The reference (bayesflow v2.0.11) has NO FFI: its extension points are Python objects.  The entry points below are
+ * what a `keras.Layer` shim on the torch backend binds (ctypes stub in INTEGRATION.md) to replace, on CUDA tensors:
+ *
+ *   bfk_velocity        <- FlowMatching.velocity / DiffusionModel.velocity(stochastic_solver=False)
+ *                          bayesflow/networks/inference/flow_matching/flow_matching.py:220-236
+ *                          bayesflow/networks/inference/diffusion/diffusion_model.py:501-559
+ *                          (= TimeMLP.call, bayesflow/networks/subnets/mlp/time_mlp.py:125-147, + output_projector)
+ *   bfk_sample_fixed    <- integrate_fixed / integrate_scheduled driven by FlowMatching._inverse/_forward and
+ *                          DiffusionModel._inverse: bayesflow/utils/integrate.py:217-288,
+ *                          flow_matching.py:254-337, diffusion_model.py:782-869
+ *   bfk_adaptive_*      <- integrate_adaptive, bayesflow/utils/integrate.py:291-406
+ *   bfk_cond_prologue   <- the conditions half of TimeMLP.call (time_mlp.py:133-139), hoisted per dataset
+ *   bfk_eval_table      <- FourierEmbedding.call + FiLM.call (fourier_embedding.py:57-76,
+ *                          featurewise_linear_modulation.py:25-33) and the noise-schedule scalars
+ *                          (diffusion_model.py:351-405, 466-489, 539-552, 711-717), per evaluation time
+ *   bfk_pack            <- weight import: Keras variable order / (in,out) kernels (time_mlp.py:149-183)
+ *
+ * Conventions: every pointer is a DEVICE pointer unless named host_*; tensors are dense row-major fp32; `stream`
+ * is a cudaStream_t passed as void*.  Return value: 0 ok, <0 argument error, >0 cudaError_t.  Nothing throws.
+ * Re-entrant; no global state besides the last-error string (thread-local).
+ */
+#ifndef BFK_H_
+#define BFK_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BFK_MAX_BLOCKS 16
+#define BFK_MAX_D 8      /* fused on-chip sampler: state dim <= 8 */
+#define BFK_MAX_STAGES 7 /* RK stages incl. the FSAL evaluation */
+
+enum { BFK_ACT_MISH = 0, BFK_ACT_SILU = 1, BFK_ACT_RELU = 2, BFK_ACT_GELU = 3, BFK_ACT_TANH = 4 };
+enum { BFK_MERGE_NONE = 0, BFK_MERGE_CONCAT = 1, BFK_MERGE_ADD = 2 };
+enum { BFK_NORM_NONE = 0, BFK_NORM_LAYER = 1, BFK_NORM_RMS = 2 };
+enum { BFK_PREC_FP16 = 0, BFK_PREC_BF16 = 1 };
+enum { BFK_METHOD_EULER = 0, BFK_METHOD_RK45 = 1, BFK_METHOD_TSIT5 = 2 };
+/* what the network output means (DiffusionModel prediction_type, diffusion_model.py:351-405); FM = velocity of x */
+enum { BFK_MODEL_FM = 0, BFK_MODEL_DM = 1 };
+enum { BFK_PRED_VELOCITY = 0, BFK_PRED_NOISE = 1, BFK_PRED_F = 2, BFK_PRED_X = 3, BFK_PRED_SCORE = 4 };
+enum { BFK_SCHED_EDM = 0, BFK_SCHED_COSINE = 1 };
+
+typedef struct bfk_net_config {
+  int32_t D;              /* state / parameter dim */
+  int32_t C;              /* condition dim, 0 = unconditional */
+  int32_t W;              /* hidden width (all blocks equal) */
+  int32_t L;              /* number of ConditionalDenseBlocks */
+  int32_t T;              /* time embedding size: time_embedding_dim+1 (33), or 1 for identity */
+  int32_t activation;     /* BFK_ACT_* */
+  int32_t merge;          /* BFK_MERGE_* */
+  int32_t norm;           /* BFK_NORM_* */
+  int32_t residual;       /* 0/1 */
+  int32_t film_use_gamma; /* 0/1 */
+  int32_t precision;      /* BFK_PREC_*: tensor-core operand type, fp32 accumulate */
+  float fourier_scale;
+} bfk_net_config;
+
+/* fp32 device pointers in the reference's variable order; Dense kernels are (in,out) row-major */
+typedef struct bfk_weights {
+  const float* freq;                 /* (T-1)/2 */
+  const float* x_k; const float* x_b; /* (D,W), (W) */
+  const float* c_k; const float* c_b; /* (C,W), (W)   or NULL */
+  const float* m_k; const float* m_b; /* (2W|W,W),(W) or NULL */
+  const float* dense_k[BFK_MAX_BLOCKS]; const float* dense_b[BFK_MAX_BLOCKS];   /* (W,W),(W) */
+  const float* film_g_k[BFK_MAX_BLOCKS]; const float* film_g_b[BFK_MAX_BLOCKS]; /* (T,W),(W) or NULL */
+  const float* film_b_k[BFK_MAX_BLOCKS]; const float* film_b_b[BFK_MAX_BLOCKS]; /* (T,W),(W) */
+  const float* norm_g[BFK_MAX_BLOCKS]; const float* norm_b[BFK_MAX_BLOCKS];     /* (W),(W) or NULL */
+  const float* out_k; const float* out_b; /* (W,D),(D) */
+} bfk_weights;
+
+typedef struct bfk_schedule {
+  int32_t model;       /* BFK_MODEL_* */
+  int32_t prediction;  /* BFK_PRED_* (DM only) */
+  int32_t schedule;    /* BFK_SCHED_* (DM only) */
+  int32_t exploding;   /* variance_type == "exploding" */
+  double sigma_data, sigma_min, sigma_max, rho; /* EDM */
+  double log_snr_min, log_snr_max, shift, t_min, t_max; /* cosine (and EDM bounds) */
+} bfk_schedule;
+
+int bfk_version(void);
+const char* bfk_last_error_string(void);
+
+/* ---- weights -------------------------------------------------------------------------------------------- */
+size_t bfk_packed_bytes(const bfk_net_config* cfg);
+int bfk_pack(const bfk_net_config* cfg, const bfk_weights* w, void* packed, void* stream);
+
+/* ---- per-call prologues --------------------------------------------------------------------------------- */
+/* conditions (G,C) -> pre_add (G,W) [added before the first activation] and post_add (G,W) [added to the merge GEMM] */
+int bfk_cond_prologue(const bfk_net_config* cfg, const void* packed, const float* conditions, int64_t G,
+                      float* pre_add, float* post_add, void* stream);
+size_t bfk_table_stride(const bfk_net_config* cfg); /* floats per evaluation */
+/* times (n) -> table (n, stride): FiLM shifts (and scales) of every block + velocity coefficients */
+int bfk_eval_table(const bfk_net_config* cfg, const void* packed, const bfk_schedule* sched, const float* times,
+                   int64_t n, float* table, void* stream);
+
+/* ---- the hot path ------------------------------------------------------------------------------------------ */
+/* One velocity evaluation at a single shared time (table holds 1 evaluation). */
+int bfk_velocity(const bfk_net_config* cfg, const void* packed, const float* table, const float* pre_add,
+                 const float* post_add, int64_t rows_per_group, const float* target_mask, const float* xz, float* out,
+                 int64_t B, void* stream);
+/* Fixed / scheduled stepping.  table holds n_steps*stages evaluations in execution order, step_h the n_steps step
+ * sizes.  x_in may equal x_out.  Rows keep their whole trajectory on chip. */
+int bfk_sample_fixed(const bfk_net_config* cfg, const void* packed, const float* table, const float* step_h,
+                     int32_t method, int64_t n_steps, const float* pre_add, const float* post_add,
+                     int64_t rows_per_group, const float* target_mask, const float* x_in, float* x_out, int64_t B,
+                     void* stream);
+
+/* ---- introspection ------------------------------------------------------------------------------------------- */
+int bfk_num_sms(void);
+int bfk_fused_supported(const bfk_net_config* cfg); /* 1 if the on-chip sampler handles this config */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BFK_H_ */
