@@ -197,6 +197,8 @@ class _Engine:
         self._packed = None
         self._key = None
         self.cfg = None
+        self.kernel_events = None  # set to a list to have CUDA events recorded around the sampler kernel
+        self.launches = 0          # kernels launched so far (bench.py reports it as gpu_launches)
 
     # -- configuration / weights -------------------------------------------------------------------------------------
     def _make_cfg(self):
@@ -283,6 +285,7 @@ class _Engine:
         pre = torch.empty(G, W, device=cond.device, dtype=torch.float32) if net.subnet.merge == "add" else None
         _lib.check(_lib.lib().bfk_cond_prologue(C.byref(self.cfg), _lib.ptr(self._packed), _lib.ptr(cond), G,
                                                 _lib.ptr(pre), _lib.ptr(post), _lib.stream_ptr()), "bfk_cond_prologue")
+        self.launches += 1
         return pre, post, repeats
 
     def eval_table(self, times: np.ndarray):
@@ -292,6 +295,7 @@ class _Engine:
         sched = self.net._schedule_struct()
         _lib.check(_lib.lib().bfk_eval_table(C.byref(self.cfg), _lib.ptr(self._packed), C.byref(sched), _lib.ptr(t),
                                              t.numel(), _lib.ptr(table), _lib.stream_ptr()), "bfk_eval_table")
+        self.launches += 1
         return table
 
 
@@ -323,6 +327,7 @@ class _Run:
         _lib.check(_lib.lib().bfk_velocity(C.byref(e.cfg), _lib.ptr(e._packed), _lib.ptr(table), _lib.ptr(self.pre),
                                            _lib.ptr(self.post), self.rpg, _lib.ptr(self.tmask), _lib.ptr(x),
                                            _lib.ptr(out), x.shape[0], _lib.stream_ptr()), "bfk_velocity")
+        e.launches += 1
         return out
 
     def run_fixed(self, x, times, hs, method):
@@ -331,10 +336,18 @@ class _Run:
         table = e.eval_table(times)
         h = torch.from_numpy(np.ascontiguousarray(hs, dtype=np.float32)).to(x.device, non_blocking=True)
         out = torch.empty_like(x)
+        ev = None
+        if e.kernel_events is not None:  # bench.py: CUDA events around the dominant kernel, on the launching stream
+            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            ev[0].record()
         _lib.check(_lib.lib().bfk_sample_fixed(C.byref(e.cfg), _lib.ptr(e._packed), _lib.ptr(table), _lib.ptr(h),
                                                _lib.METHOD[method], h.numel(), _lib.ptr(self.pre), _lib.ptr(self.post),
                                                self.rpg, _lib.ptr(self.tmask), _lib.ptr(x), _lib.ptr(out), x.shape[0],
                                                _lib.stream_ptr()), "bfk_sample_fixed")
+        if ev is not None:
+            ev[1].record()
+            e.kernel_events.append(ev)
+        e.launches += 1
         self.info = {"steps": int(h.numel()), "evals": int(len(times)), "rejected": 0}
         return out
 
