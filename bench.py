@@ -34,11 +34,6 @@ DEFAULT_WORKLOAD = "cfg2_sir_fm_euler100"
 EVALS_PER_STEP = {"euler": 1, "rk45": 6, "tsit5": 6}
 
 
-def flops_per_draw(w):
-    import oracle
-    return oracle.count_flops_per_eval(w["D"], w["C"], w["widths"]) * EVALS_PER_STEP[w["method"]] * w["ode_steps"]
-
-
 def workload_config(name, w, n_gpus):
     return {"workload": name, "network": "FlowMatching" if w["model"] == "fm" else "DiffusionModel(edm,F)",
             "subnet": f"time_mlp widths={w['widths'][0]}x{len(w['widths'])}", "D": w["D"], "C": w["C"],
@@ -78,3 +73,255 @@ class ClockSampler:
         reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower() == "active" for r in self.rows)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
                 "samples": len(sm)}
+
+
+def count_flops_per_eval(D, C, widths, T=33):
+    """2*in*out per dense layer exactly as the reference executes them (SURVEY.md §8d formula) — the NAIVE count: the
+    per-dataset conditions GEMMs and the per-row FiLM GEMMs are included although the kernel hoists them."""
+    W0 = widths[0]
+    f = 2 * D * W0
+    if C:
+        f += 2 * C * W0 + 2 * (2 * W0) * W0
+    prev = W0
+    for w in widths:
+        f += 2 * prev * w + 2 * T * w + (2 * prev * w if prev != w else 0)
+        prev = w
+    return f + 2 * prev * D
+
+
+def flops_per_draw(w):
+    return count_flops_per_eval(w["D"], w["C"], w["widths"]) * EVALS_PER_STEP[w["method"]] * w["ode_steps"]
+
+
+def measured_peaks():
+    """MEASURED_PEAKS.json (driver-written) else the fallback B200_PROFILING.md states."""
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return {"tflops": float(p.get("bf16_tflops_sustained") or p["bf16_tflops"]), "hbm_gbs": float(p["hbm_gbs"]),
+                "source": "MEASURED_PEAKS.json bf16_tflops_sustained (fp16 operands run at the bf16 rate)"}
+    return {"tflops": 1366.1, "hbm_gbs": 6548.8, "source": "fallback: B200_PROFILING.md sustained bf16 figure"}
+
+
+def ncu_traffic(name):
+    """dram bytes per launch of the sampler kernel from the committed `ncu --set full` capture (profiles/), or None."""
+    path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(path):
+        return json.load(open(path)).get(name)
+    return None
+
+
+# --------------------------------------------------------------------------------------------------- CPU arm
+def make_oracle(w, state_dict):
+    import oracle
+    kw = {"dropout": 0.0, "widths": w["widths"]}
+    cls = oracle.OracleFlowMatching if w["model"] == "fm" else oracle.OracleDiffusionModel
+    return cls(state_dict, w["D"], subnet_kwargs=kw)
+
+
+def cpu_rate(w, orc, n_datasets, threads):
+    """draws/s of the reference's CPU algorithm (oracle port: same ATen ops the Keras/torch backend issues, fp32,
+    autograd off as bayesflow/__init__.py:80) on `n_datasets` datasets of the SAME workload."""
+    import torch
+    torch.set_num_threads(threads)
+    g = torch.Generator().manual_seed(3456)
+    S = w["S"]
+    z = torch.randn(n_datasets * S, w["D"], generator=g)
+    c = torch.randn(n_datasets, w["C"], generator=g).repeat_interleave(S, dim=0) if w["C"] else None  # samplers.py:51-63
+    t0 = time.perf_counter()
+    with torch.no_grad():
+        out = orc.inverse(z, c, method=w["method"], steps=w["ode_steps"])
+    dt = time.perf_counter() - t0
+    assert bool(torch.isfinite(out).all())
+    return n_datasets * S / dt, dt
+
+
+def cpu_state_dict(w):
+    import oracle
+    return oracle.init_params(w["D"], w["C"] or None, w["widths"])
+
+
+def run_cpu_baseline(w, state_dict, budget_s=15.0):
+    orc = make_oracle(w, state_dict)
+    threads = os.cpu_count() or 1
+    rate, dt = cpu_rate(w, orc, 1, threads)  # calibration: one dataset
+    n = int(max(1, min(64, budget_s * rate / w["S"])))
+    if n > 1:
+        rate, dt = cpu_rate(w, orc, n, threads)
+    return {"value": rate, "unit": "draws/s", "cores": threads, "kind": "port",
+            "sample": f"{n} dataset(s) x {w['S']} draws of {w['method']}-{w['ode_steps']} ({dt:.1f} s); torch fp32 eager, "
+                      f"torch.set_num_threads({threads})"}
+
+
+def run_reference_arm(args, name, w):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sd = cpu_state_dict(w)
+    orc = make_oracle(w, sd)
+    threads = os.cpu_count() or 1
+    rate, dt = cpu_rate(w, orc, 1, threads)
+    n = int(max(1, min(32, 10.0 * rate / w["S"])))  # ~10 s per step
+    for _ in range(max(args.warmup - 1, 0)):
+        cpu_rate(w, orc, 1, threads)
+    tot_rows, tot_t = 0, 0.0
+    for _ in range(args.steps):
+        r, dt = cpu_rate(w, orc, n, threads)
+        tot_rows += n * w["S"]
+        tot_t += dt
+    value = tot_rows / tot_t
+    line = {"impl": "reference", "metric": "posterior draws/sec", "value": value, "unit": "draws/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(name, w, args.gpus),
+            "cpu_baseline": {"value": value, "unit": "draws/s", "cores": threads, "kind": "port",
+                             "sample": f"each step = {n} dataset(s) x {w['S']} draws of the workload on the host cores; the "
+                                       "reference needs Keras (absent), so this is the oracle port of its torch-CPU path"},
+            "e2e": {"value": value, "unit": "draws/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------------- GPU arm
+def run_ours(args, name, w):
+    import torch
+    import torch.distributed as dist
+    import bayesflow_b200 as bf
+    from bayesflow_b200 import _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.lib()  # fail loudly if libbfk.so is missing
+
+    # ---- network: random init of the named architecture (seed 1234), identical on every rank
+    torch.manual_seed(1234)
+    kw = {"dropout": 0.0, "widths": w["widths"]}
+    net = (bf.FlowMatching if w["model"] == "fm" else bf.DiffusionModel)(subnet_kwargs=kw)
+    net.build((None, w["D"]), (None, w["C"]) if w["C"] else None)
+    state_cpu = {k: v.detach().clone() for k, v in net.state_dict().items() if "base_distribution" not in k}
+    net.to(dev)
+
+    # ---- synthetic inputs: this rank's datasets (weak scaling: N datasets per GPU)
+    N, S, D, Cd = w["N"], w["S"], w["D"], w["C"]
+    g = torch.Generator().manual_seed(2345 + rank)
+    cond_host = torch.randn(N, Cd, generator=g).pin_memory() if Cd else None
+    z_host = torch.randn(N * S, D, generator=g).pin_memory()
+    out_host = torch.empty(N * S, D).pin_memory()
+    cond_dev = cond_host.to(dev) if Cd else None
+    z_dev = z_host.to(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    ikw = dict(method=w["method"], steps=w["ode_steps"])
+
+    def step_resident():
+        # the reference-facing call (InferenceNetwork.call(inverse=True)); conditions stay (N, C) + repeat count instead
+        # of the (N*S, C) tensor samplers.py:51-63 materialises
+        return net(z_dev, conditions=cond_dev, conditions_repeats=S if Cd else None, inverse=True, **ikw)
+
+    def step_e2e():
+        c = cond_host.to(dev, non_blocking=True) if Cd else None
+        z = z_host.to(dev, non_blocking=True)
+        out = net(z, conditions=c, conditions_repeats=S if Cd else None, inverse=True, **ikw)
+        out_host.copy_(out, non_blocking=True)
+        return out
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        eng = net._engine
+        barrier()
+        eng.kernel_events = []
+        launches0 = eng.launches
+        pairs = []
+        t_wall = time.perf_counter()
+        for _ in range(steps):
+            flush.fill_(1)  # L2 flush between timed iterations (outside the event pair)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            pairs.append((a, b))
+        barrier()
+        wall = time.perf_counter() - t_wall
+        total_ms = sum(a.elapsed_time(b) for a, b in pairs)
+        kern_ms = [a.elapsed_time(b) for a, b in eng.kernel_events]
+        launches = eng.launches - launches0
+        eng.kernel_events = None
+        if world > 1:
+            t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            total_ms = float(t.item())
+        return total_ms, kern_ms, launches, wall
+
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    total_ms, kern_ms, launches, wall = timed(step_resident, args.steps, args.warmup)
+    clk = clocks.stop() if rank == 0 else None
+    e2e_ms, _, _, _ = timed(step_e2e, args.steps, max(1, args.warmup // 2))
+    info = dict(net.last_integration_info)
+
+    rows_total = world * N * S * args.steps
+    value = rows_total / (total_ms * 1e-3)
+    e2e_value = rows_total / (e2e_ms * 1e-3)
+    fpd = flops_per_draw(w)
+    peaks = measured_peaks()
+    k_avg_ms = sum(kern_ms) / max(len(kern_ms), 1)
+    achieved = (N * S * fpd) / (k_avg_ms * 1e-3) / 1e12 if kern_ms else None
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = run_cpu_baseline(w, state_cpu)
+    if rank == 0:
+        line = {"metric": "posterior draws/sec", "value": value, "unit": "draws/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f16 tensor-core operands, f32 accumulate/state", "data": "synthetic",
+                "config": workload_config(name, w, world),
+                "clocks": clk,
+                "e2e": {"value": e2e_value, "unit": "draws/s", "h2d_bytes_per_step": int(z_host.numel() * 4 + (cond_host.numel() * 4 if Cd else 0)),
+                        "d2h_bytes_per_step": int(out_host.numel() * 4), "ms_per_step": e2e_ms / args.steps},
+                "gpu_launches": launches,
+                "roofline": {"bound": "tensor", "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",
+                             "frac": (achieved / peaks["tflops"]) if achieved else None, "traffic": ncu_traffic(name),
+                             "kernel": "bfk::sampler_kernel", "kernel_ms": k_avg_ms, "kernel_share_of_step": k_avg_ms * args.steps / total_ms,
+                             "flop_per_draw_naive": fpd, "peak_source": peaks["source"],
+                             "hbm_gbs_algorithmic": (N * S * D * 8) / (k_avg_ms * 1e-3) / 1e9 if kern_ms else None},
+                "cpu_baseline": cpu,
+                "integration": info, "wall_s_timed_region": wall}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    w = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference_arm(args, args.workload, w)
+    else:
+        if args.warmup < 3:
+            print("bench.py: note: fewer than 3 warm-up steps requested", file=sys.stderr)
+        run_ours(args, args.workload, w)
+
+
+if __name__ == "__main__":
+    main()

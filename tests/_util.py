@@ -35,3 +35,17 @@ def grouped_conditions(B, C, rows_per_group, seed=2345):
     g = torch.Generator().manual_seed(seed)
     G = (B + rows_per_group - 1) // rows_per_group
     return torch.randn(G, C, generator=g).repeat_interleave(rows_per_group, dim=0)[:B].contiguous()
+
+
+def as_float64(orc):
+    """The same oracle evaluated in float64 (weights up-cast): used where the reference's own fp32 algebra is
+    ill-conditioned (e.g. prediction_type='score' at small t computes (z + sigma^2 pred - z)/sigma^2 with
+    sigma^2 ~ 1e-7, diffusion_model.py:402-404, 489) so that the comparison measures the kernel, not fp32 cancellation."""
+    import copy
+    from collections import OrderedDict
+    p64 = OrderedDict((k, v.double()) for k, v in orc.p.items())
+    o = copy.copy(orc)
+    o.p = p64
+    o.subnet = copy.copy(orc.subnet)
+    o.subnet.p = p64
+    return o
