@@ -18,6 +18,9 @@ PREC = {"fp16": 0, "bf16": 1}
 METHOD = {"euler": 0, "rk45": 1, "tsit5": 2}
 PRED = {"velocity": 0, "noise": 1, "F": 2, "x": 3, "score": 4}
 SCHED = {"edm": 0, "cosine": 1}
+# include/bfk.h BFK_CTRL_*
+CTRL = {"time": 0, "step_size": 1, "h": 2, "step": 3, "rejected": 4, "sel": 11, "done": 12, "all_nan": 14, "trials": 15,
+        "acc": 20, "times": 24, "floats": 32}
 
 _fp = C.POINTER(C.c_float)
 
@@ -72,6 +75,13 @@ def lib():
     L.bfk_sample_fixed.argtypes = [C.POINTER(NetConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64,
                                    C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                    C.c_void_p]
+    L.bfk_adaptive_init.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_int64, C.c_int64, C.c_double, C.c_double,
+                                    C.c_void_p]
+    L.bfk_adaptive_plan.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
+    L.bfk_adaptive_plan_final.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
+    L.bfk_adaptive_commit.argtypes = [C.c_void_p, C.c_void_p]
+    L.bfk_adaptive_trial.argtypes = [C.POINTER(NetConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
+                                     C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
     _lib = L
     return L
 

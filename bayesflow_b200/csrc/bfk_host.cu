@@ -4,6 +4,7 @@
 #include <string.h>
 
 #include "bfk_sampler.cuh"
+#include "bfk_adaptive.cuh"
 
 using namespace bfk;
 
@@ -154,6 +155,8 @@ extern "C" int bfk_eval_table(const bfk_net_config* c, const void* packed, const
 static void fill_tableau(int method, SamplerArgs& a) {
   memset(a.rk_a, 0, sizeof(a.rk_a));
   memset(a.rk_b, 0, sizeof(a.rk_b));
+  memset(a.rk_e, 0, sizeof(a.rk_e));
+  a.s0 = 0; a.err_kind = 0;
   if (method == BFK_METHOD_EULER) {
     a.S = 1;
     a.rk_b[0] = 1.f;
@@ -168,10 +171,13 @@ static void fill_tableau(int method, SamplerArgs& a) {
                             {19372.0 / 6561, -25360.0 / 2187, 64448.0 / 6561, -212.0 / 729},
                             {9017.0 / 3168, -355.0 / 33, 46732.0 / 5247, 49.0 / 176, -5103.0 / 18656}};
     const double Bc[6] = {35.0 / 384, 0.0, 500.0 / 1113, 125.0 / 192, -2187.0 / 6784, 11.0 / 84};
+    const double B4[7] = {5179.0 / 57600, 0.0, 7571.0 / 16695, 393.0 / 640, -92097.0 / 339200, 187.0 / 2100, 1.0 / 40};
     for (int i = 0; i < 6; ++i) {
       for (int j = 0; j < 5; ++j) a.rk_a[i][j] = (float)A[i][j];
       a.rk_b[i] = (float)Bc[i];
     }
+    for (int i = 0; i < 7; ++i) a.rk_e[i] = (float)B4[i];
+    a.err_kind = 0;
   } else {
     const double A[6][5] = {{0},
                             {0.161},
@@ -180,11 +186,23 @@ static void fill_tableau(int method, SamplerArgs& a) {
                             {5.325864828439257, -11.74888356406283, 7.495539342889836, -0.09249506636175525},
                             {5.86145544294270, -12.92096931784711, 8.159367898576159, -0.07158497328140100, -0.02826905039406838}};
     const double Bc[6] = {0.09646076681806523, 0.01, 0.4798896504144996, 1.379008574103742, -3.290069515436081, 2.324710524099774};
+    const double E[7] = {-0.00178001105222577714, -0.0008164344596567469, 0.007880878010261995, -0.1447110071732629,
+                         0.5823571654525552, -0.45808210592918697, 0.015151515151515152};
     for (int i = 0; i < 6; ++i) {
       for (int j = 0; j < 5; ++j) a.rk_a[i][j] = (float)A[i][j];
       a.rk_b[i] = (float)Bc[i];
     }
+    for (int i = 0; i < 7; ++i) a.rk_e[i] = (float)E[i];
+    a.err_kind = 1;
   }
+}
+
+static StageC stage_c(int method) {
+  StageC sc{};
+  const double rk[6] = {1.0 / 5, 3.0 / 10, 4.0 / 5, 8.0 / 9, 1.0, 1.0};
+  const double ts[6] = {0.161, 0.327, 0.9, 0.9800255409045097, 1.0, 1.0};
+  for (int i = 0; i < 6; ++i) sc.c[i] = (float)(method == BFK_METHOD_RK45 ? rk[i] : ts[i]);
+  return sc;
 }
 
 typedef void (*sampler_fn)(const SamplerArgs);
@@ -206,10 +224,17 @@ static sampler_fn pick_kernel(const bfk_net_config* c) {
 
 static int launch_sampler(const bfk_net_config* c, const void* packed, const float* table, const float* step_h, int method,
                           int64_t n_steps, const float* pre_add, const float* post_add, int64_t rpg, const float* tmask,
-                          const float* x_in, float* x_out, int64_t B, int mode, cudaStream_t st) {
+                          const float* x_in, float* x_out, int64_t B, int mode, cudaStream_t st, float* ctrl = nullptr,
+                          float* ybuf = nullptr, float* kbuf = nullptr) {
   if (int r = check_cfg(c)) return r;
   if (!bfk_fused_supported(c)) return fail(-40, "config not supported by the fused on-chip sampler (need D<=8, W<=256, W%32==0)");
-  if (!packed || !table || !step_h || !x_in || !x_out || B <= 0 || n_steps <= 0) return fail(-41, "bad arguments");
+  if (mode == 2) {
+    if (!packed || !table || !ctrl || !ybuf || !kbuf || B <= 0) return fail(-41, "bad arguments");
+    if (method != BFK_METHOD_RK45 && method != BFK_METHOD_TSIT5)
+      return fail(-46, "Adaptive step sizing is not supported for the 'euler' method.");
+  } else if (!packed || !table || !step_h || !x_in || !x_out || B <= 0 || n_steps <= 0) {
+    return fail(-41, "bad arguments");
+  }
   if (method < BFK_METHOD_EULER || method > BFK_METHOD_TSIT5) return fail(-42, "unknown method");
   const PackedLayout L = make_layout(*c);
   if (L.has_merge && !post_add) return fail(-43, "conditional net needs post_add from bfk_cond_prologue");
@@ -236,6 +261,7 @@ static int launch_sampler(const bfk_net_config* c, const void* packed, const flo
   a.err_flag = nullptr;
   fill_tableau(method, a);
   if (mode == 1) { a.S = 1; }
+  if (mode == 2) { a.S = 7; a.s0 = 1; a.ctrl = ctrl; a.ybuf = ybuf; a.kbuf = kbuf; }
 
   int dev = 0, sms = 0;
   CK(cudaGetDevice(&dev));
@@ -263,4 +289,48 @@ extern "C" int bfk_sample_fixed(const bfk_net_config* c, const void* packed, con
                                 const float* tmask, const float* x_in, float* x_out, int64_t B, void* stream_) {
   return launch_sampler(c, packed, table, step_h, method, n_steps, pre_add, post_add, rpg, tmask, x_in, x_out, B, 0,
                         (cudaStream_t)stream_);
+}
+
+// ---------------------------------------------------------------------------------------------------- adaptive
+extern "C" int bfk_adaptive_init(float* ctrl, double start_time, double stop_time, int64_t min_steps, int64_t max_steps,
+                                 double atol, double rtol, void* stream_) {
+  if (!ctrl) return fail(-50, "null controller");
+  if (max_steps <= min_steps) return fail(-51, "Maximum number of steps must be greater than minimum number of steps.");
+  // integrate.py:316-321: python doubles cast to fp32 where they meet a tensor
+  const float step_size = (float)((stop_time - start_time) / (double)min_steps);
+  adaptive_init_kernel<<<1, 32, 0, (cudaStream_t)stream_>>>(ctrl, (float)start_time, (float)stop_time, (float)min_steps,
+                                                           (float)max_steps, (float)atol, (float)rtol, step_size);
+  CK(cudaGetLastError());
+  return 0;
+}
+static int check_adaptive_method(int method) {
+  if (method == BFK_METHOD_EULER) return fail(-46, "Adaptive step sizing is not supported for the 'euler' method.");
+  if (method != BFK_METHOD_RK45 && method != BFK_METHOD_TSIT5) return fail(-42, "unknown method");
+  return 0;
+}
+extern "C" int bfk_adaptive_plan(float* ctrl, int32_t method, void* stream_) {
+  if (!ctrl) return fail(-50, "null controller");
+  if (int r = check_adaptive_method(method)) return r;
+  adaptive_plan_kernel<<<1, 32, 0, (cudaStream_t)stream_>>>(ctrl, stage_c(method));
+  CK(cudaGetLastError());
+  return 0;
+}
+extern "C" int bfk_adaptive_plan_final(float* ctrl, int32_t method, void* stream_) {
+  if (!ctrl) return fail(-50, "null controller");
+  if (int r = check_adaptive_method(method)) return r;
+  adaptive_plan_final_kernel<<<1, 32, 0, (cudaStream_t)stream_>>>(ctrl, stage_c(method));
+  CK(cudaGetLastError());
+  return 0;
+}
+extern "C" int bfk_adaptive_commit(float* ctrl, void* stream_) {
+  if (!ctrl) return fail(-50, "null controller");
+  adaptive_commit_kernel<<<1, 32, 0, (cudaStream_t)stream_>>>(ctrl);
+  CK(cudaGetLastError());
+  return 0;
+}
+extern "C" int bfk_adaptive_trial(const bfk_net_config* c, const void* packed, const float* table, float* ctrl,
+                                  int32_t method, const float* pre_add, const float* post_add, int64_t rpg,
+                                  const float* tmask, float* ybuf, float* kbuf, int64_t B, void* stream_) {
+  return launch_sampler(c, packed, table, nullptr, method, 1, pre_add, post_add, rpg, tmask, nullptr, nullptr, B, 2,
+                        (cudaStream_t)stream_, ctrl, ybuf, kbuf);
 }

@@ -22,7 +22,14 @@ struct SamplerArgs {
   const float* tmask;       // [D] or null
   long long B, rows_per_group, n_steps;
   int D, W, L, NG, has_merge, residual, norm, film_gamma;
-  int S, mode;  // S = evaluations per step; mode 0 = integrate, 1 = write the velocity of the single evaluation
+  int S, mode;  // S = stages per step; mode 0 = integrate, 1 = write the velocity of the single evaluation,
+                // 2 = one adaptive trial step (stage 0 = FSAL slope read from kbuf, stage 6 = evaluation at the candidate)
+  int s0;       // first stage that is evaluated (1 in mode 2, else 0)
+  int err_kind; // mode 2: 0 = (y5 - y4) with rk_e = 4th-order weights (rk45), 1 = h * sum e_j k_j (tsit5)
+  float* ctrl;  // mode 2: device controller state (include/bfk.h BFK_CTRL_*)
+  float* ybuf;  // mode 2: [2][B][D] state slots
+  float* kbuf;  // mode 2: [2][B][D] FSAL slope slots
+  float rk_e[BFK_MAX_STAGES];
   int tstride, cvec_floats;
   int cv_wx, cv_bx, cv_blk, cv_wo, cv_bo;
   uint32_t idesc;
@@ -67,6 +74,7 @@ struct Bars {
 template <int ACT, int DP, bool BF16>
 __global__ void __launch_bounds__(NUM_THREADS, 1) sampler_kernel(const SamplerArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
+  if (a.mode == 2 && a.ctrl[BFK_CTRL_SKIP] != 0.f) return;  // controller says: loop finished, nothing to do
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int W = a.W;
   const uint32_t smem_base = smem_u32(smem);
@@ -95,7 +103,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) sampler_kernel(const SamplerAr
 
   const long long rows_per_pair = TILES_PER_CTA * TILE_M;
   const long long n_pairs = (a.B + rows_per_pair - 1) / rows_per_pair;
-  const long long n_evals = a.n_steps * a.S;
+  const long long n_evals = a.n_steps * (a.S - a.s0);
   const int n_chunks = W / KC;
 
   if (warp < EPI_WARPS) {
@@ -119,22 +127,36 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) sampler_kernel(const SamplerAr
       const long long grp = valid ? row / a.rows_per_group : 0;
       const float* g_pre = a.pre_add ? a.pre_add + grp * W : nullptr;
       const float* g_post = a.post_add ? a.post_add + grp * W : nullptr;
-      float y[DP], xs[DP], kst[BFK_MAX_STAGES][DP], msk[DP];
+      float y[DP], xs[DP], kst[BFK_MAX_STAGES][DP], msk[DP], ynew[DP];
+      const int sel = (a.mode == 2) ? (int)a.ctrl[BFK_CTRL_SEL] : 0;
+      const float* y_src = (a.mode == 2) ? a.ybuf + (size_t)sel * a.B * a.D : a.x_in;
 #pragma unroll
       for (int d = 0; d < DP; ++d) {
-        y[d] = (valid && d < a.D) ? a.x_in[row * a.D + d] : 0.f;
+        y[d] = (valid && d < a.D) ? y_src[row * a.D + d] : 0.f;
         msk[d] = (a.tmask && d < a.D) ? a.tmask[d] : 1.f;
+        ynew[d] = 0.f;
+        if (a.mode == 2) kst[0][d] = (valid && d < a.D) ? a.kbuf[(size_t)sel * a.B * a.D + row * a.D + d] : 0.f;
       }
 
       for (long long step = 0; step < a.n_steps; ++step) {
-        const float h = a.step_h[step];
-        for (int s = 0; s < a.S; ++s, ++q) {
+        const float h = (a.mode == 2) ? a.ctrl[BFK_CTRL_H] : a.step_h[step];
+        for (int s = a.s0; s < a.S; ++s, ++q) {
           // ---- stage input (integrate.py:47-54 add_scaled: acc = sum c_j k_j ; y + h*acc)
+          if (s == 6) {  // FSAL evaluation at the candidate state (integrate.py:94-102, 184-198)
 #pragma unroll
-          for (int d = 0; d < DP; ++d) {
-            float acc = 0.f;
-            for (int j = 0; j < s; ++j) acc = acc + a.rk_a[s][j] * kst[j][d];
-            xs[d] = (s == 0) ? y[d] : y[d] + h * acc;
+            for (int d = 0; d < DP; ++d) {
+              float acc = 0.f;
+              for (int j = 0; j < 6; ++j) acc = acc + a.rk_b[j] * kst[j][d];
+              ynew[d] = y[d] + h * acc;
+              xs[d] = ynew[d];
+            }
+          } else {
+#pragma unroll
+            for (int d = 0; d < DP; ++d) {
+              float acc = 0.f;
+              for (int j = 0; j < s; ++j) acc = acc + a.rk_a[s][j] * kst[j][d];
+              xs[d] = (s == 0) ? y[d] : y[d] + h * acc;
+            }
           }
           const int fb = (int)(q & 1);
           const float* s_film = reinterpret_cast<const float*>(smem + a.plan.film + fb * a.plan.film_bytes);
@@ -308,7 +330,45 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) sampler_kernel(const SamplerAr
           }
         }
       }
-      if (valid) {
+      if (a.mode == 2) {
+        // ---- embedded error estimate, row-wise L2 norm, max over rows (integrate.py:104-118, 199-212); max|state|
+        const float h = a.ctrl[BFK_CTRL_H];
+        float e2 = 0.f, mabs = 0.f;
+        bool nonnan = false;
+#pragma unroll
+        for (int d = 0; d < DP; ++d) {
+          float acc = 0.f, e;
+          for (int j = 0; j < 7; ++j) acc = acc + a.rk_e[j] * kst[j][d];
+          if (a.err_kind == 0) e = ynew[d] - (y[d] + h * acc);
+          else e = h * acc;
+          if (d < a.D) {
+            e2 = fmaf(e, e, e2);
+            mabs = (y[d] != y[d]) ? y[d] : ((mabs != mabs) ? mabs : fmaxf(mabs, fabsf(y[d])));
+            nonnan = nonnan || (ynew[d] == ynew[d]);
+          }
+        }
+        float en = valid ? sqrtf(e2) : 0.f;
+        if (!valid) { mabs = 0.f; nonnan = false; }
+        bool isnan_row = (en != en) || (mabs != mabs);
+        if (isnan_row) { en = 0.f; if (mabs != mabs) mabs = 0.f; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          en = fmaxf(en, __shfl_xor_sync(0xffffffffu, en, o));
+          mabs = fmaxf(mabs, __shfl_xor_sync(0xffffffffu, mabs, o));
+        }
+        const bool any_nan = __any_sync(0xffffffffu, isnan_row), any_nonnan = __any_sync(0xffffffffu, nonnan);
+        if (lane == 0) {
+          int* acc_i = reinterpret_cast<int*>(a.ctrl + BFK_CTRL_ACC);
+          atomicMax(acc_i + 0, __float_as_int(en));
+          atomicMax(acc_i + 1, __float_as_int(mabs));
+          if (any_nan) atomicMax(acc_i + 2, __float_as_int(1.f));
+          if (any_nonnan) atomicMax(acc_i + 3, __float_as_int(1.f));
+        }
+        if (valid) {
+          const size_t o = (size_t)(1 - sel) * a.B * a.D + row * a.D;
+          for (int d = 0; d < a.D; ++d) { a.ybuf[o + d] = ynew[d]; a.kbuf[o + d] = kst[6][d]; }
+        }
+      } else if (valid) {
         for (int d = 0; d < a.D; ++d) a.x_out[row * a.D + d] = (a.mode == 1) ? kst[0][d] : y[d];
       }
     }

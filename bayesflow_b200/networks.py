@@ -352,7 +352,66 @@ class _Run:
         return out
 
     def run_adaptive(self, x, start_time, stop_time, min_steps, max_steps, method, atol=1e-6, rtol=1e-4):
-        raise NotImplementedError("adaptive stepping lands in the next milestone")
+        """integrate_adaptive (integrate.py:291-406).  The step-size controller runs on the device (bfk_adaptive_plan);
+        the host only enqueues trial steps and polls the `done` flag every few trials."""
+        e, L, K = self.e, _lib.lib(), _lib.CTRL
+        if method == "euler":
+            raise ValueError("Adaptive step sizing is not supported for the 'euler' method.")  # integrate.py:304-306
+        if method not in ("rk45", "tsit5"):
+            if isinstance(method, str):
+                raise ValueError(f"Unknown integration method name: {method!r}")
+            raise TypeError(f"Invalid integration method: {method!r}")
+        if max_steps <= min_steps:
+            raise ValueError("Maximum number of steps must be greater than minimum number of steps.")
+        x = self._check_x(x)
+        B, m, st = x.shape[0], _lib.METHOD[method], _lib.stream_ptr
+        ybuf = torch.empty((2,) + tuple(x.shape), device=x.device, dtype=torch.float32)
+        kbuf = torch.empty_like(ybuf)
+        ybuf[0].copy_(x)
+        # FSAL slope k1 = fn(start_time, state), integrate.py:323
+        table1 = e.eval_table(np.asarray([start_time], dtype=np.float32))
+        _lib.check(L.bfk_velocity(C.byref(e.cfg), _lib.ptr(e._packed), _lib.ptr(table1), _lib.ptr(self.pre),
+                                  _lib.ptr(self.post), self.rpg, _lib.ptr(self.tmask), _lib.ptr(ybuf[0]),
+                                  _lib.ptr(kbuf[0]), B, st()), "bfk_velocity")
+        ctrl = torch.zeros(K["floats"], device=x.device, dtype=torch.float32)
+        _lib.check(L.bfk_adaptive_init(_lib.ptr(ctrl), float(start_time), float(stop_time), int(min_steps),
+                                       int(max_steps), float(atol), float(rtol), st()), "bfk_adaptive_init")
+        table = torch.empty(6, e._tstride, device=x.device, dtype=torch.float32)
+        times, acc = ctrl[K["times"]:K["times"] + 6], ctrl[K["acc"]:K["acc"] + 4]
+        sched = e.net._schedule_struct()
+        group = getattr(e.net, "step_control_group", None)
+        e.launches += 3
+
+        def trial():
+            _lib.check(L.bfk_eval_table(C.byref(e.cfg), _lib.ptr(e._packed), C.byref(sched), _lib.ptr(times), 6,
+                                        _lib.ptr(table), st()), "bfk_eval_table")
+            _lib.check(L.bfk_adaptive_trial(C.byref(e.cfg), _lib.ptr(e._packed), _lib.ptr(table), _lib.ptr(ctrl), m,
+                                            _lib.ptr(self.pre), _lib.ptr(self.post), self.rpg, _lib.ptr(self.tmask),
+                                            _lib.ptr(ybuf), _lib.ptr(kbuf), B, st()), "bfk_adaptive_trial")
+            if group is not None:  # the reference's GLOBAL step control over sharded rows (SURVEY §8e)
+                torch.distributed.all_reduce(acc, op=torch.distributed.ReduceOp.MAX, group=group)
+            e.launches += 3
+
+        n, next_check, cap = 0, int(min_steps), 8 * int(max_steps) + 64
+        while True:
+            _lib.check(L.bfk_adaptive_plan(_lib.ptr(ctrl), m, st()), "bfk_adaptive_plan")
+            trial()
+            n += 1
+            if n >= next_check:
+                if float(ctrl[K["done"]]) != 0.0:  # device -> host sync, once every 8 trials after min_steps
+                    break
+                next_check = n + 8
+            if n > cap:
+                raise RuntimeError("adaptive integration did not terminate")
+        _lib.check(L.bfk_adaptive_plan_final(_lib.ptr(ctrl), m, st()), "bfk_adaptive_plan_final")
+        trial()
+        _lib.check(L.bfk_adaptive_commit(_lib.ptr(ctrl), st()), "bfk_adaptive_commit")
+        c = ctrl.cpu()
+        if float(c[K["all_nan"]]) != 0.0:
+            raise RuntimeError(f"All values are NaNs in state during integration at {float(c[K['time']])}.")
+        self.info = {"steps": int(c[K["step"]]), "rejected": int(c[K["rejected"]]), "trials": int(c[K["trials"]]),
+                     "evals": 1 + 6 * int(c[K["trials"]]), "final_time": float(c[K["time"]])}
+        return ybuf[int(c[K["sel"]])].clone()
 
 
 # ======================================================================================================================

@@ -1,0 +1,60 @@
+"""Multi-GPU layout of the sampling path: one process per GPU (torchrun), rows sharded BY DATASET, weights replicated,
+no data-path collective.  The only exchanges are (i) an optional gather of the finished draws and (ii),
+for adaptive solvers with the reference's GLOBAL step control (integrate.py:117-118, 353-358), a MAX all-reduce of 4
+floats per trial step, which `networks._Run.run_adaptive` issues when `net.step_control_group` is set."""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+
+def dataset_shard(num_datasets: int, rank: int, world_size: int) -> tuple[int, int]:
+    """Contiguous range [lo, hi) of datasets owned by `rank` (dataset-major order as samplers.py:59-61); sizes differ by
+    at most one, earlier ranks take the remainder."""
+    if world_size < 1 or not (0 <= rank < world_size):
+        raise ValueError(f"bad rank/world_size: {rank}/{world_size}")
+    base, rem = divmod(num_datasets, world_size)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def sample_sharded(net, num_samples: int, conditions: torch.Tensor, *, group=None, gather: bool = False,
+                   global_step_control: bool = True, seed=None, **kwargs):
+    """`Sampler.sample` (approximators/helpers/samplers.py:71-148) for one rank: draws for this rank's datasets only,
+    shape (n_local, num_samples, D); with gather=True every rank returns all (N, num_samples, D) draws.
+
+    conditions: (N, C) for ALL datasets (every rank passes the same tensor) — only the local slice is used."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    N = conditions.shape[0]
+    lo, hi = dataset_shard(N, rank, world)
+    local = conditions[lo:hi].contiguous()
+    n_local = hi - lo
+    prev = getattr(net, "step_control_group", None)
+    if world > 1 and global_step_control:
+        net.step_control_group = group if group is not None else dist.group.WORLD
+    try:
+        if n_local > 0:
+            gen_seed = None if seed is None else int(seed) + rank
+            flat = net.sample((n_local * num_samples,), conditions=local, conditions_repeats=num_samples, seed=gen_seed,
+                              **kwargs)
+            out = flat.reshape(n_local, num_samples, -1)
+        else:
+            out = conditions.new_zeros((0, num_samples, net._D))
+    finally:
+        net.step_control_group = prev
+    if not gather or world == 1:
+        return out
+    return gather_rows(out, N, group=group)
+
+
+def gather_rows(local: torch.Tensor, num_datasets: int, *, group=None) -> torch.Tensor:
+    """all_gather of ragged dataset shards (sizes from dataset_shard) into one (N, ...) tensor on every rank."""
+    world = dist.get_world_size(group)
+    sizes = [dataset_shard(num_datasets, r, world) for r in range(world)]
+    biggest = max(hi - lo for lo, hi in sizes)
+    pad = local.new_zeros((biggest,) + tuple(local.shape[1:]))
+    pad[: local.shape[0]] = local
+    parts = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(parts, pad, group=group)
+    return torch.cat([p[: hi - lo] for p, (lo, hi) in zip(parts, sizes)], dim=0)

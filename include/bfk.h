@@ -109,6 +109,39 @@ int bfk_sample_fixed(const bfk_net_config* cfg, const void* packed, const float*
                      int64_t rows_per_group, const float* target_mask, const float* x_in, float* x_out, int64_t B,
                      void* stream);
 
+/* ---- adaptive stepping (integrate_adaptive, bayesflow/utils/integrate.py:291-406) ---------------------------------
+ * The controller state lives on the DEVICE as BFK_CTRL_FLOATS floats (indices below) so that the trial-step loop needs
+ * no host round trip: per trial the host enqueues  bfk_adaptive_plan -> bfk_eval_table(times = ctrl+BFK_CTRL_TIMES,
+ * n = 6) -> bfk_adaptive_trial  and polls ctrl[BFK_CTRL_DONE] every few trials; once done, the three calls are no-ops.
+ * ybuf / kbuf hold two (B,D) slots each: slot ctrl[SEL] is the current state / FSAL slope k1, the other slot receives
+ * the candidate.  acc = ctrl+BFK_CTRL_ACC holds {max row-L2 error, max|state|, any-NaN flag, any-non-NaN flag} of the
+ * last trial (non-negative floats, so a cross-rank MAX all-reduce of these 4 floats between trial and plan reproduces
+ * the reference's GLOBAL step control on sharded rows). */
+enum {
+  BFK_CTRL_TIME = 0, BFK_CTRL_STEP_SIZE = 1, BFK_CTRL_H = 2, BFK_CTRL_STEP = 3, BFK_CTRL_REJECTED = 4,
+  BFK_CTRL_START = 5, BFK_CTRL_STOP = 6, BFK_CTRL_ATOL = 7, BFK_CTRL_RTOL = 8, BFK_CTRL_MIN_STEPS = 9,
+  BFK_CTRL_MAX_STEPS = 10, BFK_CTRL_SEL = 11, BFK_CTRL_DONE = 12, BFK_CTRL_HAVE_TRIAL = 13, BFK_CTRL_ALL_NAN = 14,
+  BFK_CTRL_TRIALS = 15, BFK_CTRL_MIN_STEP_SIZE = 16, BFK_CTRL_FINAL = 17, BFK_CTRL_SKIP = 18,
+  BFK_CTRL_ACC = 20,   /* 4 floats */
+  BFK_CTRL_TIMES = 24, /* 8 floats: evaluation times of the planned trial (stages 2..6 and t+h) */
+  BFK_CTRL_FLOATS = 32
+};
+/* write the initial controller state (start/stop/min_steps/max_steps/atol/rtol; step_size = (stop-start)/min_steps) */
+int bfk_adaptive_init(float* ctrl, double start_time, double stop_time, int64_t min_steps, int64_t max_steps,
+                      double atol, double rtol, void* stream);
+/* digest the last trial (accept / reject, new step size: integrate.py:353-378), test the loop condition (:325-335),
+ * plan the next trial (:339-342) and write its evaluation times; method selects the stage abscissae */
+int bfk_adaptive_plan(float* ctrl, int32_t method, void* stream);
+/* after the loop: the final step that lands exactly on stop_time (integrate.py:393-403); then bfk_eval_table +
+ * bfk_adaptive_trial once more and bfk_adaptive_commit */
+int bfk_adaptive_plan_final(float* ctrl, int32_t method, void* stream);
+int bfk_adaptive_commit(float* ctrl, void* stream);
+/* one trial step over all rows (k2..k6, candidate state, FSAL k7, error norm): rk45_step / tsit5_step with
+ * use_adaptive_step_size=True, integrate.py:57-120, 123-214.  table holds the 6 evaluations planned in ctrl. */
+int bfk_adaptive_trial(const bfk_net_config* cfg, const void* packed, const float* table, float* ctrl, int32_t method,
+                       const float* pre_add, const float* post_add, int64_t rows_per_group, const float* target_mask,
+                       float* ybuf, float* kbuf, int64_t B, void* stream);
+
 /* ---- introspection ------------------------------------------------------------------------------------------- */
 int bfk_num_sms(void);
 int bfk_fused_supported(const bfk_net_config* cfg); /* 1 if the on-chip sampler handles this config */

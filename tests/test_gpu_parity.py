@@ -170,3 +170,91 @@ def test_no_cpu_fallback():
     net, _ = make_pair(2, 32)
     with pytest.raises(RuntimeError):
         net.velocity(torch.randn(4, 2), 0.5, conditions=torch.randn(4, 32))
+
+
+# ---------------------------------------------------------------------------------------------------- adaptive (I7)
+@pytest.mark.parametrize("method", ["tsit5", "rk45"])
+@pytest.mark.parametrize("D,C", [(2, 32), (4, 20)])
+def test_fm_adaptive_draws(method, D, C):
+    """integrate_adaptive (integrate.py:291-406) with the device-side controller: same draws within tolerance and the
+    same number of accepted steps as the oracle's global controller on the same rows (+-2: the embedded error estimate
+    sees the fp16-operand noise of the slopes)."""
+    net, orc = make_pair(D, C)
+    B = 600
+    z = torch.randn(B, D, generator=torch.Generator().manual_seed(3456))
+    c = grouped_conditions(B, C, 100)
+    info = {}
+    ref = orc.inverse(z, c, method=method, steps="adaptive", info=info)
+    out = net(z.cuda(), conditions=c.cuda(), inverse=True, method=method, steps="adaptive")
+    got = net.last_integration_info
+    assert rel_l2(out, ref) < TOL, rel_l2(out, ref)
+    assert abs(got["steps"] - info["steps"]) <= 2, (got, info)
+    assert abs(got["final_time"] - 1.0) < 1e-6
+
+
+def test_fm_default_sample_is_adaptive_tsit5():
+    """FlowMatching() with no integrate_kwargs samples with tsit5 / adaptive (defaults.py:52) through .sample()."""
+    net, orc = make_pair(2, 2)
+    c = grouped_conditions(300, 2, 100)
+    out = net.sample((300,), conditions=c.cuda(), seed=7)
+    assert out.shape == (300, 2) and torch.isfinite(out).all()
+    assert net.last_integration_info["steps"] >= 50  # min_steps
+    again = net.sample((300,), conditions=c.cuda(), seed=7)
+    assert torch.equal(out, again)  # tests/test_networks/test_sample.py:6-54 seed determinism
+
+
+def test_adaptive_tight_and_loose_tolerances():
+    """atol/rtol flow through kwargs (integrate.py:316-317); a loose tolerance still takes min_steps, a tight one
+    takes more trial steps; max_steps <= min_steps raises ValueError (:301-302)."""
+    net, orc = make_pair(2, 32)
+    z = torch.randn(300, 2)
+    c = grouped_conditions(300, 32, 100)
+    for kw in ({"atol": 1e-3, "rtol": 1e-2, "min_steps": 10}, {"atol": 1e-7, "rtol": 1e-5, "min_steps": 10}):
+        info = {}
+        ref = orc.inverse(z, c, method="rk45", steps="adaptive", info=info, **kw)
+        out = net(z.cuda(), conditions=c.cuda(), inverse=True, method="rk45", steps="adaptive", **kw)
+        assert rel_l2(out, ref) < TOL, (kw, rel_l2(out, ref))
+        assert net.last_integration_info["steps"] >= 10
+    with pytest.raises(ValueError):
+        net(z.cuda(), conditions=c.cuda(), inverse=True, method="rk45", steps="adaptive", min_steps=10, max_steps=10)
+    with pytest.raises(ValueError):
+        net(z.cuda(), conditions=c.cuda(), inverse=True, method="euler", steps="adaptive")
+
+
+def test_dm_adaptive_probability_flow():
+    net, orc = make_pair(4, 20, dm=True)
+    z = torch.randn(400, 4)
+    c = grouped_conditions(400, 20, 100)
+    info = {}
+    ref = orc.inverse(z, c, method="rk45", steps="adaptive", info=info)
+    out = net(z.cuda(), conditions=c.cuda(), inverse=True, method="rk45", steps="adaptive")
+    assert rel_l2(out, ref) < TOL, rel_l2(out, ref)
+
+
+@pytest.mark.parametrize("scale", [5.0, 15.0])
+def test_adaptive_with_rejections(scale):
+    """A stiffer field (output projector scaled up) with min_steps=5 makes the controller reject trial steps and end
+    with the exact-landing final step (integrate.py:365-378, 393-403)."""
+    import oracle
+    widths = (128,) * 3
+    params = oracle.perturb_params(oracle.init_params(2, 32, widths))
+    params["output_projector.kernel"] = params["output_projector.kernel"] * scale
+    import bayesflow_b200 as bf
+    kw = {"dropout": 0.0, "widths": widths}
+    net = bf.FlowMatching(subnet_kwargs=kw)
+    net.build((None, 2), (None, 32))
+    net.load_state_dict(params, strict=False)
+    net.cuda()
+    orc = oracle.OracleFlowMatching(params, 2, subnet_kwargs=kw)
+    z = torch.randn(300, 2, generator=torch.Generator().manual_seed(11))
+    c = grouped_conditions(300, 32, 100)
+    info = {}
+    ref = orc.inverse(z, c, method="rk45", steps="adaptive", info=info, min_steps=5)
+    out = net(z.cuda(), conditions=c.cuda(), inverse=True, method="rk45", steps="adaptive", min_steps=5)
+    got = net.last_integration_info
+    assert info["rejected"] > 0 and got["rejected"] > 0, (info, got)
+    assert abs(got["steps"] - info["steps"]) <= max(2, 0.15 * info["steps"]), (got, info)
+    assert abs(got["final_time"] - 1.0) < 1e-6
+    # the scaled field amplifies ANY perturbation (the solver's own rtol=1e-4 error included) by its Lipschitz constant:
+    # this is a controller stress test, held to the parity bar times the amplification seen between two oracle runs
+    assert rel_l2(out, ref) < (TOL if scale <= 5 else 3 * TOL), rel_l2(out, ref)
