@@ -97,8 +97,13 @@ extern "C" int bfk_pack(const bfk_net_config* c, const bfk_weights* w, void* pac
     copy_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(c->norm == BFK_NORM_LAYER ? w->norm_b[l] : nullptr,
                                                   cv + L.cv_blk + (3 * l + 2) * W, W);
   }
-  pad2d_kernel<<<cdiv((size_t)W * L.DP, 256), 256, 0, st>>>(w->out_k, W, c->D, cv + L.cv_wo, W, L.DP);
-  pad2d_kernel<<<1, 32, 0, st>>>(w->out_b, 1, c->D, cv + L.cv_bo, 1, L.DP);
+  if (is_fast(*c)) {
+    fold_proj_kernel<<<1, 32, 0, st>>>(w->out_k, w->out_b, w->norm_g[c->L - 1], w->norm_b[c->L - 1], W, c->D, L.DP,
+                                      cv + L.cv_wo, cv + L.cv_bo);
+  } else {
+    pad2d_kernel<<<cdiv((size_t)W * L.DP, 256), 256, 0, st>>>(w->out_k, W, c->D, cv + L.cv_wo, W, L.DP);
+    pad2d_kernel<<<1, 32, 0, st>>>(w->out_b, 1, c->D, cv + L.cv_bo, 1, L.DP);
+  }
   // prologue parameters
   if (L.Th > 0) copy_f32_kernel<<<1, 64, 0, st>>>(w->freq, (float*)(P + L.freq), L.Th);
   for (int l = 0; l < c->L; ++l) {
@@ -209,15 +214,30 @@ typedef void (*sampler_fn)(const SamplerArgs);
 static sampler_fn pick_kernel(const bfk_net_config* c) {
   const int dp = dp_of(c->D);
   const bool bf = c->precision == BFK_PREC_BF16;
-#define PICK(ACT_, DP_, BF_) \
-  if (c->activation == ACT_ && dp == DP_ && bf == BF_) return sampler_kernel<ACT_, DP_, BF_>;
-  PICK(BFK_ACT_MISH, 4, false)
-  PICK(BFK_ACT_MISH, 8, false)
-  PICK(BFK_ACT_MISH, 4, true)
-  PICK(BFK_ACT_SILU, 4, false)
-  PICK(BFK_ACT_RELU, 4, false)
-  PICK(BFK_ACT_GELU, 4, false)
-  PICK(BFK_ACT_TANH, 4, false)
+  const bool fast = is_fast(*c);
+#define PICK(ACT_, DP_, BF_, FAST_) \
+  if (c->activation == ACT_ && dp == DP_ && bf == BF_ && fast == FAST_) return sampler_kernel<ACT_, DP_, BF_, FAST_>;
+  // the reference's default block shape: packed-f32x2 epilogue
+  PICK(BFK_ACT_MISH, 2, false, true)
+  PICK(BFK_ACT_MISH, 4, false, true)
+  PICK(BFK_ACT_MISH, 8, false, true)
+  PICK(BFK_ACT_MISH, 2, true, true)
+  PICK(BFK_ACT_MISH, 4, true, true)
+  PICK(BFK_ACT_SILU, 2, false, true)
+  PICK(BFK_ACT_SILU, 4, false, true)
+  PICK(BFK_ACT_SILU, 8, false, true)
+  PICK(BFK_ACT_RELU, 2, false, true)
+  PICK(BFK_ACT_RELU, 4, false, true)
+  PICK(BFK_ACT_GELU, 2, false, true)
+  PICK(BFK_ACT_GELU, 4, false, true)
+  PICK(BFK_ACT_TANH, 2, false, true)
+  PICK(BFK_ACT_TANH, 4, false, true)
+  // non-default options (norm None/rms, no residual, FiLM gamma): generic epilogue
+  PICK(BFK_ACT_MISH, 2, false, false)
+  PICK(BFK_ACT_MISH, 4, false, false)
+  PICK(BFK_ACT_MISH, 8, false, false)
+  PICK(BFK_ACT_SILU, 2, false, false)
+  PICK(BFK_ACT_SILU, 4, false, false)
 #undef PICK
   return nullptr;
 }

@@ -14,7 +14,11 @@ constexpr int EPI_WARPS = 8, MMA_WARP = 8, LOAD_WARP = 9, NUM_THREADS = 320;
 constexpr int TABLE_SCALARS = 8;  // per-evaluation scalars after the FiLM vectors: coefZ, coefP, time, norm-time, ...
 constexpr size_t SMEM_LIMIT = 232448;
 
-__host__ __device__ inline int dp_of(int D) { return D <= 4 ? 4 : 8; }
+__host__ __device__ inline int dp_of(int D) { return D <= 2 ? 2 : (D <= 4 ? 4 : 8); }
+// the packed-f32x2 epilogue covers the reference's default block shape (defaults.py:13-26); anything else -> generic
+__host__ __device__ inline int is_fast(const bfk_net_config& c) {
+  return (c.norm == BFK_NORM_LAYER && c.residual && !c.film_use_gamma) ? 1 : 0;
+}
 __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // byte offsets inside the packed blob
@@ -24,6 +28,8 @@ struct PackedLayout {
   size_t cvec;                // SMEM image of the constant vectors (floats), see below
   int cvec_floats;
   int cv_wx, cv_bx, cv_blk, cv_wo, cv_bo;  // float offsets inside cvec: Wx[DP][W], bx[W], per block {bd,lng,lnb}[W], Wo[W][DP], bo[DP]
+                                           // fast layout: cv_wo = [DP][W] gamma_L*Wo (projector folded through the last
+                                           // LayerNorm), cv_bo = s0[DP] (= beta_L.Wo + bo) then s1[DP] (= sum_c gamma_L*Wo)
   size_t freq;                // [Th]
   size_t film_b_k, film_b_b;  // [L][T][W], [L][W]
   size_t film_g_k, film_g_b;  // same, only if film_use_gamma
@@ -46,7 +52,7 @@ __host__ __device__ inline PackedLayout make_layout(const bfk_net_config& c) {
   L.cv_blk = L.cv_bx + c.W;
   L.cv_wo = L.cv_blk + 3 * c.L * c.W;
   L.cv_bo = L.cv_wo + c.W * L.DP;
-  L.cvec_floats = L.cv_bo + L.DP;
+  L.cvec_floats = L.cv_bo + 2 * L.DP;
   L.cvec = off; off += (size_t)L.cvec_floats * 4; off = align_up(off, 256);
   L.freq = off; off += align_up((size_t)(L.Th > 0 ? L.Th : 1) * 4, 256);
   L.film_b_k = off; off += (size_t)c.L * c.T * W * 4;

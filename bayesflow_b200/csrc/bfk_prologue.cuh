@@ -73,6 +73,25 @@ __global__ void pad2d_kernel(const float* __restrict__ src, int rows, int cols, 
   dst[i] = (r < rows && c < cols) ? src[(size_t)r * cols + c] : 0.f;
 }
 
+// Output projector folded through the last block's LayerNorm affine (fast epilogue):
+//   wog[d][c] = gamma[c] * Wo[c][d];  s0[d] = sum_c beta[c] * Wo[c][d] + bo[d];  s1[d] = sum_c wog[d][c]
+__global__ void fold_proj_kernel(const float* __restrict__ out_k, const float* __restrict__ out_b,
+                                 const float* __restrict__ gamma, const float* __restrict__ beta, int W, int D, int DP,
+                                 float* __restrict__ wog, float* __restrict__ s0s1) {
+  const int d = threadIdx.x;
+  if (d >= DP) return;
+  double a0 = 0.0, a1 = 0.0;
+  for (int c = 0; c < W; ++c) {
+    const float w = d < D ? out_k[(size_t)c * D + d] : 0.f;
+    const float g = (gamma ? gamma[c] : 1.f) * w;
+    wog[(size_t)d * W + c] = g;
+    a1 += (double)g;
+    a0 += (double)(beta ? beta[c] : 0.f) * (double)w;
+  }
+  s0s1[d] = (float)(a0 + (d < D ? (double)out_b[d] : 0.0));
+  s0s1[DP + d] = (float)a1;
+}
+
 // conditions (G,C) -> pre_add (G,W), post_add (G,W)   [time_mlp.py:133-139 hoisted; SURVEY §7.3-2]
 //   concat: post = bm + act(c Wc + bc) Wm[W:2W,:],  pre = (unused)
 //   add   : pre  = c Wc + bc,                         post = bm
