@@ -2,8 +2,10 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 
 #include "bfk_sampler.cuh"
+#include "bfk_sampler_fast.cuh"
 #include "bfk_adaptive.cuh"
 
 using namespace bfk;
@@ -211,33 +213,29 @@ static StageC stage_c(int method) {
 }
 
 typedef void (*sampler_fn)(const SamplerArgs);
-static sampler_fn pick_kernel(const bfk_net_config* c) {
+static sampler_fn pick_kernel(const bfk_net_config* c, int* threads) {
   const int dp = dp_of(c->D);
   const bool bf = c->precision == BFK_PREC_BF16;
-  const bool fast = is_fast(*c);
-#define PICK(ACT_, DP_, BF_, FAST_) \
-  if (c->activation == ACT_ && dp == DP_ && bf == BF_ && fast == FAST_) return sampler_kernel<ACT_, DP_, BF_, FAST_>;
-  // the reference's default block shape: packed-f32x2 epilogue
-  PICK(BFK_ACT_MISH, 2, false, true)
-  PICK(BFK_ACT_MISH, 4, false, true)
-  PICK(BFK_ACT_MISH, 8, false, true)
-  PICK(BFK_ACT_MISH, 2, true, true)
-  PICK(BFK_ACT_MISH, 4, true, true)
-  PICK(BFK_ACT_SILU, 2, false, true)
-  PICK(BFK_ACT_SILU, 4, false, true)
-  PICK(BFK_ACT_SILU, 8, false, true)
-  PICK(BFK_ACT_RELU, 2, false, true)
-  PICK(BFK_ACT_RELU, 4, false, true)
-  PICK(BFK_ACT_GELU, 2, false, true)
-  PICK(BFK_ACT_GELU, 4, false, true)
-  PICK(BFK_ACT_TANH, 2, false, true)
-  PICK(BFK_ACT_TANH, 4, false, true)
-  // non-default options (norm None/rms, no residual, FiLM gamma): generic epilogue
-  PICK(BFK_ACT_MISH, 2, false, false)
-  PICK(BFK_ACT_MISH, 4, false, false)
-  PICK(BFK_ACT_MISH, 8, false, false)
-  PICK(BFK_ACT_SILU, 2, false, false)
-  PICK(BFK_ACT_SILU, 4, false, false)
+  if (is_fast(*c)) {
+    // the reference's default block shape: 18-warp packed-f32x2 kernel
+    *threads = F_NUM_THREADS;
+#define PICKF(ACT_, DP_, BF_) \
+  if (c->activation == ACT_ && dp == DP_ && bf == BF_) return sampler_fast_kernel<ACT_, DP_, BF_>;
+    PICKF(BFK_ACT_MISH, 2, false) PICKF(BFK_ACT_MISH, 4, false) PICKF(BFK_ACT_MISH, 8, false)
+    PICKF(BFK_ACT_MISH, 2, true) PICKF(BFK_ACT_MISH, 4, true)
+    PICKF(BFK_ACT_SILU, 2, false) PICKF(BFK_ACT_SILU, 4, false) PICKF(BFK_ACT_SILU, 8, false)
+    PICKF(BFK_ACT_RELU, 2, false) PICKF(BFK_ACT_RELU, 4, false)
+    PICKF(BFK_ACT_GELU, 2, false) PICKF(BFK_ACT_GELU, 4, false)
+    PICKF(BFK_ACT_TANH, 2, false) PICKF(BFK_ACT_TANH, 4, false)
+#undef PICKF
+    return nullptr;
+  }
+  // non-default options (norm None/rms, no residual, FiLM gamma): generic 10-warp kernel
+  *threads = NUM_THREADS;
+#define PICK(ACT_, DP_, BF_) \
+  if (c->activation == ACT_ && dp == DP_ && bf == BF_) return sampler_kernel<ACT_, DP_, BF_>;
+  PICK(BFK_ACT_MISH, 2, false) PICK(BFK_ACT_MISH, 4, false) PICK(BFK_ACT_MISH, 8, false)
+  PICK(BFK_ACT_SILU, 2, false) PICK(BFK_ACT_SILU, 4, false)
 #undef PICK
   return nullptr;
 }
@@ -260,7 +258,8 @@ static int launch_sampler(const bfk_net_config* c, const void* packed, const flo
   if (L.has_merge && !post_add) return fail(-43, "conditional net needs post_add from bfk_cond_prologue");
   if (L.has_merge && c->merge == BFK_MERGE_ADD && !pre_add) return fail(-44, "merge='add' needs pre_add");
   if (rpg <= 0) rpg = 1;
-  sampler_fn fn = pick_kernel(c);
+  int threads = 0;
+  sampler_fn fn = pick_kernel(c, &threads);
   if (!fn) return fail(-45, "no kernel instantiated for this activation / D / precision");
 
   SamplerArgs a{};
@@ -279,6 +278,7 @@ static int launch_sampler(const bfk_net_config* c, const void* packed, const flo
   a.idesc = umma_idesc_f16(TILE_M, c->W, c->precision == BFK_PREC_BF16 ? 1 : 0);
   a.plan = make_smem_plan(*c);
   a.err_flag = nullptr;
+  { const char* e = getenv("BFK_DEBUG"); a.dbg = e ? atoi(e) : 0; }
   fill_tableau(method, a);
   if (mode == 1) { a.S = 1; }
   if (mode == 2) { a.S = 7; a.s0 = 1; a.ctrl = ctrl; a.ybuf = ybuf; a.kbuf = kbuf; }
@@ -289,7 +289,7 @@ static int launch_sampler(const bfk_net_config* c, const void* packed, const flo
   CK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a.plan.total));
   const long long n_pairs = (B + TILES_PER_CTA * TILE_M - 1) / (TILES_PER_CTA * TILE_M);
   const unsigned grid = (unsigned)(n_pairs < sms ? n_pairs : sms);
-  fn<<<grid, NUM_THREADS, a.plan.total, st>>>(a);
+  fn<<<grid, threads, a.plan.total, st>>>(a);
   CK(cudaGetLastError());
   return 0;
 }

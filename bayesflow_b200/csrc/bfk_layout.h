@@ -11,6 +11,8 @@ constexpr int TILE_M = 128;       // rows (draws) per tile = UMMA M = TMEM lanes
 constexpr int TILES_PER_CTA = 2;  // two tiles ping-pong through TMEM
 constexpr int KC = 32;            // K rows of a weight stage (2 UMMAs of K=16)
 constexpr int EPI_WARPS = 8, MMA_WARP = 8, LOAD_WARP = 9, NUM_THREADS = 320;
+// fast kernel: 16 epilogue warps (tile = (w>>2)&1, TMEM lane quarter = w&3, column half = w>>3) + issuer + producer
+constexpr int F_EPI_WARPS = 16, F_MMA_WARP = 16, F_LOAD_WARP = 17, F_NUM_THREADS = 576;
 constexpr int TABLE_SCALARS = 8;  // per-evaluation scalars after the FiLM vectors: coefZ, coefP, time, norm-time, ...
 constexpr size_t SMEM_LIMIT = 232448;
 
@@ -73,7 +75,8 @@ __host__ __device__ inline int table_stride(const bfk_net_config& c) {
 
 struct SmemPlan {
   int n_stage;
-  uint32_t a_tile, ring, film, cvec, bars, total;  // byte offsets
+  uint32_t a_tile, ring, film, cvec, bars, xch, total;  // byte offsets
+  uint32_t xch_stride;                                  // floats per (tile, half, row) exchange slot (fast kernel)
   uint32_t a_bytes, stage_bytes, film_bytes;
 };
 
@@ -88,6 +91,9 @@ __host__ __device__ inline SmemPlan make_smem_plan(const bfk_net_config& c) {
   p.film = off; off += 2 * p.film_bytes;
   p.cvec = off; off += (uint32_t)align_up((size_t)L.cvec_floats * 4, 16);
   p.bars = off; off += 256;
+  p.xch = off;
+  p.xch_stride = (uint32_t)((2 + L.DP + 3) / 4 * 4);  // row sum, sum of squares, DP projector partials
+  if (is_fast(c)) off += 2 * 2 * TILE_M * p.xch_stride * 4;
   p.ring = (uint32_t)align_up(off, 128);
   int n = (int)((SMEM_LIMIT - p.ring) / p.stage_bytes);
   if (n > 8) n = 8;

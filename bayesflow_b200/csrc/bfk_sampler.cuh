@@ -7,7 +7,14 @@
 // warp 8 UMMA issuer (one lane) + TMEM owner, warp 9 bulk-copy producer (one lane).
 #pragma once
 #include "bfk_prologue.cuh"
-#include "bfk_fast_epilogue.cuh"
+
+// Timing experiments (profiles/r01c_summary.md): compile with -DBFK_TIMING_EXPERIMENTS and set BFK_DEBUG=<bits> at run
+// time to switch parts of the kernel off (results are then garbage).  Compiled out of the product build.
+#ifdef BFK_TIMING_EXPERIMENTS
+#define BFK_DBG(bits) ((a.dbg & (bits)) != 0)
+#else
+#define BFK_DBG(bits) false
+#endif
 
 namespace bfk {
 
@@ -31,6 +38,7 @@ struct SamplerArgs {
   float* ybuf;  // mode 2: [2][B][D] state slots
   float* kbuf;  // mode 2: [2][B][D] FSAL slope slots
   float rk_e[BFK_MAX_STAGES];
+  int dbg;      // BFK_DEBUG env (timing experiments only): bit0 = skip epilogue arithmetic, bit1 = skip pass 2
   int tstride, cvec_floats;
   int cv_wx, cv_bx, cv_blk, cv_wo, cv_bo;
   uint32_t idesc;
@@ -72,7 +80,93 @@ struct Bars {
   __device__ uint32_t tmem_slot() const { return base + 8 * 24; }
 };
 
-template <int ACT, int DP, bool BF16, bool FAST>
+// UMMA issuer (one warp; lane 0 issues): for every evaluation and GEMM layer, for each of the two tiles, wait for the
+// tile's A operand, stream through the weight ring, commit to acc_ready.  Shared by the generic and the fast kernel.
+__device__ __forceinline__ void mma_issuer_loop(const SamplerArgs& a, const Bars& bars, uint32_t smem_base,
+                                                uint32_t tmem_base, long long n_pairs, long long n_evals, int lane) {
+  const int W = a.W;
+  const int n_chunks = W / KC;
+  if (lane == 0) {
+    uint32_t ph_a[2] = {0, 0};
+    uint32_t ph_full = 0;  // bit s = parity of stage s
+    int stage = 0;
+    const uint32_t a_lbo = TILE_M * 16, b_lbo = (uint32_t)W * 16;
+    for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+      for (long long e = 0; e < n_evals; ++e) {
+        for (int g = 0; g < a.NG; ++g) {
+          for (int t = 0; t < TILES_PER_CTA; ++t) {
+            mbar_wait(bars.a_ready(t), ph_a[t], a.err_flag, 3);
+            ph_a[t] ^= 1;
+            tc_fence_after();
+            const uint32_t a_base = smem_base + a.plan.a_tile + t * a.plan.a_bytes;
+            const uint32_t d_tmem = tmem_base + t * W;
+            for (int c = 0; c < n_chunks; ++c) {
+              mbar_wait(bars.w_full(stage), (ph_full >> stage) & 1, a.err_flag, 4);
+              ph_full ^= (1u << stage);
+              tc_fence_after();
+              const uint32_t b_base = smem_base + a.plan.ring + stage * a.plan.stage_bytes;
+#pragma unroll
+              for (int kk = 0; kk < KC / 16; ++kk) {
+                const uint64_t ad = umma_smem_desc(a_base + (uint32_t)(c * (KC / 8) + kk * 2) * a_lbo, a_lbo, 128);
+                const uint64_t bd = umma_smem_desc(b_base + (uint32_t)(kk * 2) * b_lbo, b_lbo, 128);
+                umma_f16(d_tmem, ad, bd, a.idesc, (uint32_t)((c | kk) != 0));
+              }
+              umma_commit(bars.w_empty(stage));
+              stage = (stage + 1 == a.plan.n_stage) ? 0 : stage + 1;
+            }
+            umma_commit(bars.acc_ready(t));
+          }
+        }
+      }
+    }
+  }
+  __syncwarp();
+}
+
+// Bulk-copy producer (one warp; lane 0 drives the TMA engine): weight K-slabs into the ring, one table row per evaluation.
+__device__ __forceinline__ void producer_loop(const SamplerArgs& a, const Bars& bars, uint32_t smem_base,
+                                              long long n_pairs, long long n_evals, int lane) {
+  const int W = a.W;
+  const int n_chunks = W / KC;
+  if (lane == 0) {
+    uint32_t ph_empty = 0;
+    int stage = 0;
+    long long q = 0, q_film = 0;
+    long long my_pairs = 0;
+    for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) ++my_pairs;
+    const long long Q = my_pairs * n_evals;
+    auto load_film = [&](long long qq) {
+      const int fb = (int)(qq & 1);
+      mbar_wait(bars.film_empty(fb), (uint32_t)(((qq >> 1) & 1) ^ 1), a.err_flag, 5);
+      mbar_arrive_expect_tx(bars.film_full(fb), (uint32_t)a.tstride * 4);
+      bulk_g2s(smem_base + a.plan.film + fb * a.plan.film_bytes, a.table + (qq % n_evals) * a.tstride,
+               (uint32_t)a.tstride * 4, bars.film_full(fb));
+    };
+    if (Q > 0) { load_film(0); q_film = 1; }
+    for (; q < Q; ++q) {
+      for (int g = 0; g < a.NG; ++g) {
+        for (int t = 0; t < TILES_PER_CTA; ++t) {
+          for (int c = 0; c < n_chunks; ++c) {
+            mbar_wait(bars.w_empty(stage), ((ph_empty >> stage) & 1) ^ 1, a.err_flag, 6);
+            ph_empty ^= (1u << stage);
+            if (BFK_DBG(4) && (q > 0 || g > 0 || t > 0)) {  // timing experiment: no weight streaming after the first fills
+              mbar_arrive(bars.w_full(stage));
+            } else {
+              mbar_arrive_expect_tx(bars.w_full(stage), a.plan.stage_bytes);
+              bulk_g2s(smem_base + a.plan.ring + stage * a.plan.stage_bytes,
+                       a.wg + ((size_t)g * W * W + (size_t)c * KC * W) * 2, a.plan.stage_bytes, bars.w_full(stage));
+            }
+            stage = (stage + 1 == a.plan.n_stage) ? 0 : stage + 1;
+          }
+        }
+        if (g == 0 && q_film < Q && q_film == q + 1) { load_film(q_film); ++q_film; }
+      }
+    }
+  }
+  __syncwarp();
+}
+
+template <int ACT, int DP, bool BF16>
 __global__ void __launch_bounds__(NUM_THREADS, 1) sampler_kernel(const SamplerArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
   if (a.mode == 2 && a.ctrl[BFK_CTRL_SKIP] != 0.f) return;  // controller says: loop finished, nothing to do
@@ -105,7 +199,6 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) sampler_kernel(const SamplerAr
   const long long rows_per_pair = TILES_PER_CTA * TILE_M;
   const long long n_pairs = (a.B + rows_per_pair - 1) / rows_per_pair;
   const long long n_evals = a.n_steps * (a.S - a.s0);
-  const int n_chunks = W / KC;
 
   if (warp < EPI_WARPS) {
     // =========================================================== EPILOGUE / ODE warps
@@ -164,192 +257,107 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) sampler_kernel(const SamplerAr
           mbar_wait(bars.film_full(fb), (uint32_t)((q >> 1) & 1), a.err_flag, 1);
 
           float pred[DP];
-          if constexpr (FAST) {
-            // ================= packed-f32x2 path (LayerNorm + residual + FiLM shift: the reference defaults)
-            // ---- x_proj (+ conditions for merge="add") + activation -> A tile          time_mlp.py:131,137,140
-            float2 xb[DP];
+          // ---- x_proj (+ conditions for merge="add") + activation  -> A tile      time_mlp.py:131,137,140
+          for (int j = 0; j < W / 8; ++j) {
+            float v[8];
 #pragma unroll
-            for (int d = 0; d < DP; ++d) xb[d] = f2(xs[d]);
-            for (int j = 0; j < W / 8; ++j) {
-              const float4 b0 = *reinterpret_cast<const float4*>(c_bx + j * 8);
-              const float4 b1 = *reinterpret_cast<const float4*>(c_bx + j * 8 + 4);
-              float2 v4[4] = {make_float2(b0.x, b0.y), make_float2(b0.z, b0.w), make_float2(b1.x, b1.y), make_float2(b1.z, b1.w)};
-              if (a.has_merge && g_pre) {
-                const float4 p0 = __ldg(reinterpret_cast<const float4*>(g_pre + j * 8));
-                const float4 p1 = __ldg(reinterpret_cast<const float4*>(g_pre + j * 8 + 4));
-                v4[0] = __fadd2_rn(v4[0], make_float2(p0.x, p0.y)); v4[1] = __fadd2_rn(v4[1], make_float2(p0.z, p0.w));
-                v4[2] = __fadd2_rn(v4[2], make_float2(p1.x, p1.y)); v4[3] = __fadd2_rn(v4[3], make_float2(p1.z, p1.w));
-              }
-#pragma unroll
-              for (int d = 0; d < DP; ++d) {
-                const float4 w0 = *reinterpret_cast<const float4*>(c_wx + d * W + j * 8);
-                const float4 w1 = *reinterpret_cast<const float4*>(c_wx + d * W + j * 8 + 4);
-                v4[0] = __ffma2_rn(xb[d], make_float2(w0.x, w0.y), v4[0]); v4[1] = __ffma2_rn(xb[d], make_float2(w0.z, w0.w), v4[1]);
-                v4[2] = __ffma2_rn(xb[d], make_float2(w1.x, w1.y), v4[2]); v4[3] = __ffma2_rn(xb[d], make_float2(w1.z, w1.w), v4[3]);
-              }
-              *reinterpret_cast<uint4*>(sA + j * (TILE_M * 16)) =
-                  make_uint4(pack2f<BF16>(act2<ACT>(v4[0])), pack2f<BF16>(act2<ACT>(v4[1])), pack2f<BF16>(act2<ACT>(v4[2])),
-                             pack2f<BF16>(act2<ACT>(v4[3])));
+            for (int i = 0; i < 8; ++i) v[i] = c_bx[j * 8 + i];
+            if (a.has_merge && g_pre) {
+              const float4 p0 = __ldg(reinterpret_cast<const float4*>(g_pre + j * 8));
+              const float4 p1 = __ldg(reinterpret_cast<const float4*>(g_pre + j * 8 + 4));
+              v[0] += p0.x; v[1] += p0.y; v[2] += p0.z; v[3] += p0.w;
+              v[4] += p1.x; v[5] += p1.y; v[6] += p1.z; v[7] += p1.w;
             }
-            fence_proxy_async_smem();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bars.a_ready(tile));
+#pragma unroll
+            for (int d = 0; d < DP; ++d) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) v[i] = fmaf(xs[d], c_wx[d * W + j * 8 + i], v[i]);
+            }
+            uint4 pk;
+            pk.x = pack2<BF16>(act_fn<ACT>(v[0]), act_fn<ACT>(v[1]));
+            pk.y = pack2<BF16>(act_fn<ACT>(v[2]), act_fn<ACT>(v[3]));
+            pk.z = pack2<BF16>(act_fn<ACT>(v[4]), act_fn<ACT>(v[5]));
+            pk.w = pack2<BF16>(act_fn<ACT>(v[6]), act_fn<ACT>(v[7]));
+            *reinterpret_cast<uint4*>(sA + j * (TILE_M * 16)) = pk;
+          }
+          fence_proxy_async_smem();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bars.a_ready(tile));
 
-            const int nch = W / 32;
-            for (int g = 0; g < a.NG; ++g) {
-              mbar_wait(bars.acc_ready(tile), ph_acc, a.err_flag, 2);
-              ph_acc ^= 1;
-              tc_fence_after();
-              const bool last = (g == a.NG - 1);
-              float2 va[16], vb[16];
-              if (a.has_merge && g == 0) {
-                // ---- merge_proj epilogue: h = act(acc + [m_c + bm])                    time_mlp.py:139-140
-                auto merge_chunk = [&](float2* v, int col) {
+#pragma unroll
+          for (int d = 0; d < DP; ++d) pred[d] = c_bo[d];
+
+          for (int g = 0; g < a.NG; ++g) {
+            mbar_wait(bars.acc_ready(tile), ph_acc, a.err_flag, 2);
+            ph_acc ^= 1;
+            tc_fence_after();
+            const bool last = (g == a.NG - 1);
+            if (a.has_merge && g == 0) {
+              // ---- merge_proj epilogue: h = act(acc + [m_c + bm])                  time_mlp.py:139-140
+              for (int c = 0; c < W / 32; ++c) {
+                float v[32];
+                tmem_ld32(t_acc + c * 32, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                  const float4 p = __ldg(reinterpret_cast<const float4*>(g_post + c * 32 + i));
+                  v[i] = act_fn<ACT>(v[i] + p.x); v[i + 1] = act_fn<ACT>(v[i + 1] + p.y);
+                  v[i + 2] = act_fn<ACT>(v[i + 2] + p.z); v[i + 3] = act_fn<ACT>(v[i + 3] + p.w);
+                }
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) {
+                  uint4 pk;
+                  pk.x = pack2<BF16>(v[jj * 8 + 0], v[jj * 8 + 1]); pk.y = pack2<BF16>(v[jj * 8 + 2], v[jj * 8 + 3]);
+                  pk.z = pack2<BF16>(v[jj * 8 + 4], v[jj * 8 + 5]); pk.w = pack2<BF16>(v[jj * 8 + 6], v[jj * 8 + 7]);
+                  *reinterpret_cast<uint4*>(sA + (c * 4 + jj) * (TILE_M * 16)) = pk;
+                }
+              }
+            } else {
+              // ---- ConditionalDenseBlock epilogue                          conditional_dense_block.py:114-131
+              const int l = g - a.has_merge;
+              const float* bd = c_blk + (3 * l + 0) * W;
+              const float* lng = c_blk + (3 * l + 1) * W;
+              const float* lnb = c_blk + (3 * l + 2) * W;
+              const float* fbeta = s_film + l * W;
+              const float* fgam = s_film + (a.L + l) * W;
+              float sum = 0.f, sumsq = 0.f;
+              // pass 1: v = skip + film(act(acc + bd)); row statistics; v parked in TMEM (or finished if no norm)
+              for (int c = 0; c < W / 32; ++c) {
+                float v[32];
+                tmem_ld32(t_acc + c * 32, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = act_fn<ACT>(v[i] + bd[c * 32 + i]);
+                if (a.film_gamma) {
+#pragma unroll
+                  for (int i = 0; i < 32; ++i) v[i] = (1.f + fgam[c * 32 + i]) * v[i];
+                }
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] += fbeta[c * 32 + i];
+                if (a.residual) {
 #pragma unroll
                   for (int jj = 0; jj < 4; ++jj) {
-                    const float4 p0 = __ldg(reinterpret_cast<const float4*>(g_post + col + jj * 8));
-                    const float4 p1 = __ldg(reinterpret_cast<const float4*>(g_post + col + jj * 8 + 4));
-                    const uint32_t k0 = pack2f<BF16>(act2<ACT>(__fadd2_rn(v[jj * 4 + 0], make_float2(p0.x, p0.y))));
-                    const uint32_t k1 = pack2f<BF16>(act2<ACT>(__fadd2_rn(v[jj * 4 + 1], make_float2(p0.z, p0.w))));
-                    const uint32_t k2 = pack2f<BF16>(act2<ACT>(__fadd2_rn(v[jj * 4 + 2], make_float2(p1.x, p1.y))));
-                    const uint32_t k3 = pack2f<BF16>(act2<ACT>(__fadd2_rn(v[jj * 4 + 3], make_float2(p1.z, p1.w))));
-                    *reinterpret_cast<uint4*>(sA + (size_t)((col >> 3) + jj) * (TILE_M * 16)) = make_uint4(k0, k1, k2, k3);
-                  }
-                };
-                tmem_ld32(t_acc, reinterpret_cast<float*>(va));
-                for (int c = 0; c < nch; c += 2) {
-                  tmem_ld_wait32(reinterpret_cast<float*>(va));
-                  if (c + 1 < nch) tmem_ld32(t_acc + (c + 1) * 32, reinterpret_cast<float*>(vb));
-                  merge_chunk(va, c * 32);
-                  if (c + 1 < nch) {
-                    tmem_ld_wait32(reinterpret_cast<float*>(vb));
-                    if (c + 2 < nch) tmem_ld32(t_acc + (c + 2) * 32, reinterpret_cast<float*>(va));
-                    merge_chunk(vb, (c + 1) * 32);
+                    const uint4 sk = *reinterpret_cast<const uint4*>(sA + (c * 4 + jj) * (TILE_M * 16));
+                    float2 f;
+                    f = unpack2<BF16>(sk.x); v[jj * 8 + 0] += f.x; v[jj * 8 + 1] += f.y;
+                    f = unpack2<BF16>(sk.y); v[jj * 8 + 2] += f.x; v[jj * 8 + 3] += f.y;
+                    f = unpack2<BF16>(sk.z); v[jj * 8 + 4] += f.x; v[jj * 8 + 5] += f.y;
+                    f = unpack2<BF16>(sk.w); v[jj * 8 + 6] += f.x; v[jj * 8 + 7] += f.y;
                   }
                 }
-              } else {
-                // ---- ConditionalDenseBlock epilogue                            conditional_dense_block.py:114-131
-                const int l = g - a.has_merge;
-                const float* bd = c_blk + (3 * l + 0) * W;
-                const float* lng = c_blk + (3 * l + 1) * W;
-                const float* lnb = c_blk + (3 * l + 2) * W;
-                const float* fbeta = s_film + l * W;
-                float2 sum2[4], sq2[4], pa[DP];
+                if (a.norm != BFK_NORM_NONE) {
 #pragma unroll
-                for (int p = 0; p < 4; ++p) { sum2[p] = f2(0.f); sq2[p] = f2(0.f); }
+                  for (int i = 0; i < 32; ++i) { sum += v[i]; sumsq = fmaf(v[i], v[i], sumsq); }
+                  tmem_st32(t_acc + c * 32, v);
+                } else if (last) {
 #pragma unroll
-                for (int d = 0; d < DP; ++d) pa[d] = f2(0.f);
-                auto p1 = [&](float2* v, int c) {
-                  fast_pass1_chunk<ACT, BF16>(v, c * 32, bd, fbeta, sA, sum2, sq2);
-                  if (last) {
+                  for (int i = 0; i < 32; ++i) {
 #pragma unroll
-                    for (int d = 0; d < DP; ++d) {
-                      const float* wg = c_wo + d * W + c * 32;
-#pragma unroll
-                      for (int i = 0; i < 16; i += 2) {
-                        const float4 w = *reinterpret_cast<const float4*>(wg + i * 2);
-                        pa[d] = __ffma2_rn(v[i], make_float2(w.x, w.y), pa[d]);
-                        pa[d] = __ffma2_rn(v[i + 1], make_float2(w.z, w.w), pa[d]);
-                      }
-                    }
-                  } else {
-                    tmem_st32(t_acc + c * 32, reinterpret_cast<const float*>(v));
+                    for (int d = 0; d < DP; ++d) pred[d] = fmaf(v[i], c_wo[(c * 32 + i) * DP + d], pred[d]);
                   }
-                };
-                tmem_ld32(t_acc, reinterpret_cast<float*>(va));
-                for (int c = 0; c < nch; c += 2) {
-                  tmem_ld_wait32(reinterpret_cast<float*>(va));
-                  if (c + 1 < nch) tmem_ld32(t_acc + (c + 1) * 32, reinterpret_cast<float*>(vb));
-                  p1(va, c);
-                  if (c + 1 < nch) {
-                    tmem_ld_wait32(reinterpret_cast<float*>(vb));
-                    if (c + 2 < nch) tmem_ld32(t_acc + (c + 2) * 32, reinterpret_cast<float*>(va));
-                    p1(vb, c + 1);
-                  }
-                }
-                const float2 s01 = __fadd2_rn(__fadd2_rn(sum2[0], sum2[1]), __fadd2_rn(sum2[2], sum2[3]));
-                const float2 q01 = __fadd2_rn(__fadd2_rn(sq2[0], sq2[1]), __fadd2_rn(sq2[2], sq2[3]));
-                const float mean = (s01.x + s01.y) * inv_w;
-                const float var = fmaxf((q01.x + q01.y) * inv_w - mean * mean, 0.f);
-                const float rstd = rsqrtf(var + 1e-3f);  // keras LayerNormalization epsilon
-                if (last) {
-                  // output projector folded through the LayerNorm affine (flow_matching.py:229-230)
-#pragma unroll
-                  for (int d = 0; d < DP; ++d) pred[d] = fmaf(rstd, (pa[d].x + pa[d].y) - mean * c_bo[DP + d], c_bo[d]);
                 } else {
-                  tmem_st_wait();
-                  const float nmr = -mean * rstd;
-                  tmem_ld32(t_acc, reinterpret_cast<float*>(va));
-                  for (int c = 0; c < nch; c += 2) {
-                    tmem_ld_wait32(reinterpret_cast<float*>(va));
-                    if (c + 1 < nch) tmem_ld32(t_acc + (c + 1) * 32, reinterpret_cast<float*>(vb));
-                    fast_pass2_chunk<BF16>(va, c * 32, rstd, nmr, lng, lnb, sA);
-                    if (c + 1 < nch) {
-                      tmem_ld_wait32(reinterpret_cast<float*>(vb));
-                      if (c + 2 < nch) tmem_ld32(t_acc + (c + 2) * 32, reinterpret_cast<float*>(va));
-                      fast_pass2_chunk<BF16>(vb, (c + 1) * 32, rstd, nmr, lng, lnb, sA);
-                    }
-                  }
-                }
-              }
-              if (!last) {
-                fence_proxy_async_smem();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bars.a_ready(tile));
-              }
-            }
-          } else {
-            // ---- x_proj (+ conditions for merge="add") + activation  -> A tile      time_mlp.py:131,137,140
-            for (int j = 0; j < W / 8; ++j) {
-              float v[8];
-  #pragma unroll
-              for (int i = 0; i < 8; ++i) v[i] = c_bx[j * 8 + i];
-              if (a.has_merge && g_pre) {
-                const float4 p0 = __ldg(reinterpret_cast<const float4*>(g_pre + j * 8));
-                const float4 p1 = __ldg(reinterpret_cast<const float4*>(g_pre + j * 8 + 4));
-                v[0] += p0.x; v[1] += p0.y; v[2] += p0.z; v[3] += p0.w;
-                v[4] += p1.x; v[5] += p1.y; v[6] += p1.z; v[7] += p1.w;
-              }
-  #pragma unroll
-              for (int d = 0; d < DP; ++d) {
-  #pragma unroll
-                for (int i = 0; i < 8; ++i) v[i] = fmaf(xs[d], c_wx[d * W + j * 8 + i], v[i]);
-              }
-              uint4 pk;
-              pk.x = pack2<BF16>(act_fn<ACT>(v[0]), act_fn<ACT>(v[1]));
-              pk.y = pack2<BF16>(act_fn<ACT>(v[2]), act_fn<ACT>(v[3]));
-              pk.z = pack2<BF16>(act_fn<ACT>(v[4]), act_fn<ACT>(v[5]));
-              pk.w = pack2<BF16>(act_fn<ACT>(v[6]), act_fn<ACT>(v[7]));
-              *reinterpret_cast<uint4*>(sA + j * (TILE_M * 16)) = pk;
-            }
-            fence_proxy_async_smem();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bars.a_ready(tile));
-
-  #pragma unroll
-            for (int d = 0; d < DP; ++d) pred[d] = c_bo[d];
-
-            for (int g = 0; g < a.NG; ++g) {
-              mbar_wait(bars.acc_ready(tile), ph_acc, a.err_flag, 2);
-              ph_acc ^= 1;
-              tc_fence_after();
-              const bool last = (g == a.NG - 1);
-              if (a.has_merge && g == 0) {
-                // ---- merge_proj epilogue: h = act(acc + [m_c + bm])                  time_mlp.py:139-140
-                for (int c = 0; c < W / 32; ++c) {
-                  float v[32];
-                  tmem_ld32(t_acc + c * 32, v);
-                  tmem_ld_wait();
-  #pragma unroll
-                  for (int i = 0; i < 32; i += 4) {
-                    const float4 p = __ldg(reinterpret_cast<const float4*>(g_post + c * 32 + i));
-                    v[i] = act_fn<ACT>(v[i] + p.x); v[i + 1] = act_fn<ACT>(v[i + 1] + p.y);
-                    v[i + 2] = act_fn<ACT>(v[i + 2] + p.z); v[i + 3] = act_fn<ACT>(v[i + 3] + p.w);
-                  }
-  #pragma unroll
+#pragma unroll
                   for (int jj = 0; jj < 4; ++jj) {
                     uint4 pk;
                     pk.x = pack2<BF16>(v[jj * 8 + 0], v[jj * 8 + 1]); pk.y = pack2<BF16>(v[jj * 8 + 2], v[jj * 8 + 3]);
@@ -357,51 +365,32 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) sampler_kernel(const SamplerAr
                     *reinterpret_cast<uint4*>(sA + (c * 4 + jj) * (TILE_M * 16)) = pk;
                   }
                 }
-              } else {
-                // ---- ConditionalDenseBlock epilogue                          conditional_dense_block.py:114-131
-                const int l = g - a.has_merge;
-                const float* bd = c_blk + (3 * l + 0) * W;
-                const float* lng = c_blk + (3 * l + 1) * W;
-                const float* lnb = c_blk + (3 * l + 2) * W;
-                const float* fbeta = s_film + l * W;
-                const float* fgam = s_film + (a.L + l) * W;
-                float sum = 0.f, sumsq = 0.f;
-                // pass 1: v = skip + film(act(acc + bd)); row statistics; v parked in TMEM (or finished if no norm)
+              }
+              if (a.norm != BFK_NORM_NONE) {
+                tmem_st_wait();
+                float mean = 0.f, rstd;
+                if (a.norm == BFK_NORM_LAYER) {
+                  mean = sum * inv_w;
+                  const float var = fmaxf(sumsq * inv_w - mean * mean, 0.f);
+                  rstd = rsqrtf(var + 1e-3f);  // keras LayerNormalization epsilon
+                } else {
+                  rstd = rsqrtf(sumsq * inv_w + 1e-6f);  // keras RMSNormalization epsilon
+                }
+                // pass 2: h = (v - mean) * rstd * gamma + beta  -> next A tile, or straight into the output projector
                 for (int c = 0; c < W / 32; ++c) {
                   float v[32];
                   tmem_ld32(t_acc + c * 32, v);
                   tmem_ld_wait();
-  #pragma unroll
-                  for (int i = 0; i < 32; ++i) v[i] = act_fn<ACT>(v[i] + bd[c * 32 + i]);
-                  if (a.film_gamma) {
-  #pragma unroll
-                    for (int i = 0; i < 32; ++i) v[i] = (1.f + fgam[c * 32 + i]) * v[i];
-                  }
-  #pragma unroll
-                  for (int i = 0; i < 32; ++i) v[i] += fbeta[c * 32 + i];
-                  if (a.residual) {
-  #pragma unroll
-                    for (int jj = 0; jj < 4; ++jj) {
-                      const uint4 sk = *reinterpret_cast<const uint4*>(sA + (c * 4 + jj) * (TILE_M * 16));
-                      float2 f;
-                      f = unpack2<BF16>(sk.x); v[jj * 8 + 0] += f.x; v[jj * 8 + 1] += f.y;
-                      f = unpack2<BF16>(sk.y); v[jj * 8 + 2] += f.x; v[jj * 8 + 3] += f.y;
-                      f = unpack2<BF16>(sk.z); v[jj * 8 + 4] += f.x; v[jj * 8 + 5] += f.y;
-                      f = unpack2<BF16>(sk.w); v[jj * 8 + 6] += f.x; v[jj * 8 + 7] += f.y;
-                    }
-                  }
-                  if (a.norm != BFK_NORM_NONE) {
-  #pragma unroll
-                    for (int i = 0; i < 32; ++i) { sum += v[i]; sumsq = fmaf(v[i], v[i], sumsq); }
-                    tmem_st32(t_acc + c * 32, v);
-                  } else if (last) {
-  #pragma unroll
+#pragma unroll
+                  for (int i = 0; i < 32; ++i) v[i] = fmaf((v[i] - mean) * rstd, lng[c * 32 + i], lnb[c * 32 + i]);
+                  if (last) {
+#pragma unroll
                     for (int i = 0; i < 32; ++i) {
-  #pragma unroll
+#pragma unroll
                       for (int d = 0; d < DP; ++d) pred[d] = fmaf(v[i], c_wo[(c * 32 + i) * DP + d], pred[d]);
                     }
                   } else {
-  #pragma unroll
+#pragma unroll
                     for (int jj = 0; jj < 4; ++jj) {
                       uint4 pk;
                       pk.x = pack2<BF16>(v[jj * 8 + 0], v[jj * 8 + 1]); pk.y = pack2<BF16>(v[jj * 8 + 2], v[jj * 8 + 3]);
@@ -410,47 +399,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) sampler_kernel(const SamplerAr
                     }
                   }
                 }
-                if (a.norm != BFK_NORM_NONE) {
-                  tmem_st_wait();
-                  float mean = 0.f, rstd;
-                  if (a.norm == BFK_NORM_LAYER) {
-                    mean = sum * inv_w;
-                    const float var = fmaxf(sumsq * inv_w - mean * mean, 0.f);
-                    rstd = rsqrtf(var + 1e-3f);  // keras LayerNormalization epsilon
-                  } else {
-                    rstd = rsqrtf(sumsq * inv_w + 1e-6f);  // keras RMSNormalization epsilon
-                  }
-                  // pass 2: h = (v - mean) * rstd * gamma + beta  -> next A tile, or straight into the output projector
-                  for (int c = 0; c < W / 32; ++c) {
-                    float v[32];
-                    tmem_ld32(t_acc + c * 32, v);
-                    tmem_ld_wait();
-  #pragma unroll
-                    for (int i = 0; i < 32; ++i) v[i] = fmaf((v[i] - mean) * rstd, lng[c * 32 + i], lnb[c * 32 + i]);
-                    if (last) {
-  #pragma unroll
-                      for (int i = 0; i < 32; ++i) {
-  #pragma unroll
-                        for (int d = 0; d < DP; ++d) pred[d] = fmaf(v[i], c_wo[(c * 32 + i) * DP + d], pred[d]);
-                      }
-                    } else {
-  #pragma unroll
-                      for (int jj = 0; jj < 4; ++jj) {
-                        uint4 pk;
-                        pk.x = pack2<BF16>(v[jj * 8 + 0], v[jj * 8 + 1]); pk.y = pack2<BF16>(v[jj * 8 + 2], v[jj * 8 + 3]);
-                        pk.z = pack2<BF16>(v[jj * 8 + 4], v[jj * 8 + 5]); pk.w = pack2<BF16>(v[jj * 8 + 6], v[jj * 8 + 7]);
-                        *reinterpret_cast<uint4*>(sA + (c * 4 + jj) * (TILE_M * 16)) = pk;
-                      }
-                    }
-                  }
-                }
               }
-              if (!last) {
-                fence_proxy_async_smem();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bars.a_ready(tile));
-              }
+            }
+            if (!last) {
+              fence_proxy_async_smem();
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(bars.a_ready(tile));
             }
           }
           // ---- velocity of this evaluation (FM: pred; DM: coefZ*z + coefP*pred), inference-time target mask
@@ -513,76 +468,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) sampler_kernel(const SamplerAr
     }
     tc_fence_before();
   } else if (warp == MMA_WARP) {
-    // =========================================================== UMMA issuer
-    if (lane == 0) {
-      uint32_t ph_a[2] = {0, 0};
-      uint32_t ph_full = 0;  // bit s = parity of stage s
-      int stage = 0;
-      const uint32_t a_lbo = TILE_M * 16, b_lbo = (uint32_t)W * 16;
-      for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
-        for (long long e = 0; e < n_evals; ++e) {
-          for (int g = 0; g < a.NG; ++g) {
-            for (int t = 0; t < TILES_PER_CTA; ++t) {
-              mbar_wait(bars.a_ready(t), ph_a[t], a.err_flag, 3);
-              ph_a[t] ^= 1;
-              tc_fence_after();
-              const uint32_t a_base = smem_base + a.plan.a_tile + t * a.plan.a_bytes;
-              const uint32_t d_tmem = tmem_base + t * W;
-              for (int c = 0; c < n_chunks; ++c) {
-                mbar_wait(bars.w_full(stage), (ph_full >> stage) & 1, a.err_flag, 4);
-                ph_full ^= (1u << stage);
-                tc_fence_after();
-                const uint32_t b_base = smem_base + a.plan.ring + stage * a.plan.stage_bytes;
-#pragma unroll
-                for (int kk = 0; kk < KC / 16; ++kk) {
-                  const uint64_t ad = umma_smem_desc(a_base + (uint32_t)(c * (KC / 8) + kk * 2) * a_lbo, a_lbo, 128);
-                  const uint64_t bd = umma_smem_desc(b_base + (uint32_t)(kk * 2) * b_lbo, b_lbo, 128);
-                  umma_f16(d_tmem, ad, bd, a.idesc, (uint32_t)((c | kk) != 0));
-                }
-                umma_commit(bars.w_empty(stage));
-                stage = (stage + 1 == a.plan.n_stage) ? 0 : stage + 1;
-              }
-              umma_commit(bars.acc_ready(t));
-            }
-          }
-        }
-      }
-    }
-    __syncwarp();
+    mma_issuer_loop(a, bars, smem_base, tmem_base, n_pairs, n_evals, lane);
   } else {
-    // =========================================================== bulk-copy producer (TMA engine)
-    if (lane == 0) {
-      uint32_t ph_empty = 0;
-      int stage = 0;
-      long long q = 0, q_film = 0;
-      long long my_pairs = 0;
-      for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) ++my_pairs;
-      const long long Q = my_pairs * n_evals;
-      auto load_film = [&](long long qq) {
-        const int fb = (int)(qq & 1);
-        mbar_wait(bars.film_empty(fb), (uint32_t)(((qq >> 1) & 1) ^ 1), a.err_flag, 5);
-        mbar_arrive_expect_tx(bars.film_full(fb), (uint32_t)a.tstride * 4);
-        bulk_g2s(smem_base + a.plan.film + fb * a.plan.film_bytes, a.table + (qq % n_evals) * a.tstride,
-                 (uint32_t)a.tstride * 4, bars.film_full(fb));
-      };
-      if (Q > 0) { load_film(0); q_film = 1; }
-      for (; q < Q; ++q) {
-        for (int g = 0; g < a.NG; ++g) {
-          for (int t = 0; t < TILES_PER_CTA; ++t) {
-            for (int c = 0; c < n_chunks; ++c) {
-              mbar_wait(bars.w_empty(stage), ((ph_empty >> stage) & 1) ^ 1, a.err_flag, 6);
-              ph_empty ^= (1u << stage);
-              mbar_arrive_expect_tx(bars.w_full(stage), a.plan.stage_bytes);
-              bulk_g2s(smem_base + a.plan.ring + stage * a.plan.stage_bytes,
-                       a.wg + ((size_t)g * W * W + (size_t)c * KC * W) * 2, a.plan.stage_bytes, bars.w_full(stage));
-              stage = (stage + 1 == a.plan.n_stage) ? 0 : stage + 1;
-            }
-          }
-          if (g == 0 && q_film < Q && q_film == q + 1) { load_film(q_film); ++q_film; }
-        }
-      }
-    }
-    __syncwarp();
+    producer_loop(a, bars, smem_base, n_pairs, n_evals, lane);
   }
 
   __syncthreads();

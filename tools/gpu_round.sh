@@ -17,6 +17,6 @@ $SHORT > $O/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/${TAG}_launches.csv $SHORT > $O/${TAG}_ncu1.log 2>&1
 echo "ncu launches exit=$?"
 $SHORT > $O/${TAG}_plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:sampler_kernel -s 1 -c 1 -f -o $O/${TAG}_sampler $SHORT > $O/${TAG}_ncu2.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:sampler_ -s 1 -c 1 -f -o $O/${TAG}_sampler $SHORT > $O/${TAG}_ncu2.log 2>&1
 echo "ncu full exit=$?"
 ls -la $O
