@@ -82,6 +82,14 @@ def lib():
     L.bfk_adaptive_commit.argtypes = [C.c_void_p, C.c_void_p]
     L.bfk_adaptive_trial.argtypes = [C.POINTER(NetConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
                                      C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+    L.bfk_packed_operand_bytes.restype = C.c_size_t
+    L.bfk_packed_operand_bytes.argtypes = [C.c_int64, C.c_int64, C.c_int32]
+    L.bfk_pack_kmajor.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
+                                  C.c_void_p]
+    L.bfk_pack_kmajor_t.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
+                                    C.c_void_p, C.c_void_p]
+    L.bfk_gemm.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
+                           C.c_int32, C.c_int32, C.c_void_p, C.c_float, C.c_int32, C.c_void_p]
     _lib = L
     return L
 

@@ -1,0 +1,183 @@
+// Layer-wise tensor-core GEMM for the paths that cannot live in one SM (training forward/backward with per-row time,
+// widths > 256):  C[M,N] (fp32, row-major)  (+)=  alpha * A[M,K] * B[K,N]  (+ bias[N]),  fp16/bf16 operands, fp32
+// accumulate in TMEM.  Both operands arrive PRE-PACKED in the K-major no-swizzle UMMA image
+//     P[r / RT][k / 8][r % RT][k % 8]            (RT = 128 for the A role, RT = NT for the B role)
+// so that any (row tile, K slab) is one contiguous byte range: one cp.async.bulk per operand per stage, LBO = RT*16,
+// SBO = 128.  The producers of activations write this layout directly (bfk_train.cuh), weights are packed once.
+//
+// One CTA per (M tile of 128, N tile of NT, K split); 192 threads: warps 0-3 epilogue (thread == row == TMEM lane),
+// warp 4 UMMA issuer + TMEM owner, warp 5 bulk-copy producer.  4-stage ring of K=32 slabs (24 KB per stage at NT=256)
+// so that two CTAs share an SM and one CTA's epilogue overlaps the other's main loop.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "bfk_ptx.cuh"
+
+namespace bfk {
+
+constexpr int G_KC = 32, G_STAGES = 4, G_THREADS = 192, G_TM = 128;
+enum { GEMM_ATOMIC = 1, GEMM_ADD_EXISTING = 2 };
+
+struct GemmArgs {
+  const unsigned char* A;  // packed, row tile 128
+  const unsigned char* B;  // packed, row tile NT
+  float* C;
+  const float* bias;  // [N] or null (added once: by split 0)
+  long long M, ldc;   // valid rows of C, leading dimension
+  int N, K, NT, k_per_split, flags;
+  float alpha;
+  uint32_t idesc;
+};
+
+__host__ __device__ inline size_t gemm_smem_bytes(int NT) { return (size_t)G_STAGES * (G_KC * G_TM * 2 + G_KC * NT * 2) + 256; }
+
+template <bool BF16_UNUSED = false>
+__global__ void __launch_bounds__(G_THREADS, 2) gemm_kernel(const GemmArgs a) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int NT = a.NT;
+  const uint32_t a_bytes = G_KC * G_TM * 2, b_bytes = (uint32_t)G_KC * NT * 2, st_bytes = a_bytes + b_bytes;
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t bar0 = smem_base + G_STAGES * st_bytes;  // full[s] at +8s, empty[s] at +8(4+s), acc at +64, tmem slot +72
+  volatile uint32_t* s_tmem = reinterpret_cast<volatile uint32_t*>(smem + G_STAGES * st_bytes + 72);
+  const int m_tile = blockIdx.x, n_tile = blockIdx.y, split = blockIdx.z;
+  const int k0 = split * a.k_per_split;
+  const int k1 = min(a.K, k0 + a.k_per_split);
+  const int n_slabs = (k1 - k0) / G_KC;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < G_STAGES; ++s) { mbar_init(bar0 + 8 * s, 1); mbar_init(bar0 + 8 * (4 + s), 1); }
+    mbar_init(bar0 + 64, 1);
+    fence_barrier_init();
+  }
+  const uint32_t tmem_cols = NT <= 32 ? 32 : NT <= 64 ? 64 : NT <= 128 ? 128 : 256;
+  if (warp == 4) tmem_alloc(bar0 + 72, tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 5) {
+    if (lane == 0) {
+      const size_t K8 = (size_t)a.K / 8;
+      for (int i = 0; i < n_slabs; ++i) {
+        const int s = i % G_STAGES;
+        mbar_wait(bar0 + 8 * (4 + s), ((i / G_STAGES) & 1) ^ 1, nullptr, 0);
+        mbar_arrive_expect_tx(bar0 + 8 * s, st_bytes);
+        const size_t k8 = (size_t)(k0 + i * G_KC) / 8;
+        bulk_g2s(smem_base + s * st_bytes, a.A + ((size_t)m_tile * K8 + k8) * G_TM * 16, a_bytes, bar0 + 8 * s);
+        bulk_g2s(smem_base + s * st_bytes + a_bytes, a.B + ((size_t)n_tile * K8 + k8) * NT * 16, b_bytes, bar0 + 8 * s);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 4) {
+    if (lane == 0) {
+      for (int i = 0; i < n_slabs; ++i) {
+        const int s = i % G_STAGES;
+        mbar_wait(bar0 + 8 * s, (i / G_STAGES) & 1, nullptr, 0);
+        tc_fence_after();
+        const uint32_t sa = smem_base + s * st_bytes, sb = sa + a_bytes;
+#pragma unroll
+        for (int kk = 0; kk < G_KC / 16; ++kk) {
+          const uint64_t ad = umma_smem_desc(sa + (uint32_t)(kk * 2) * (G_TM * 16), G_TM * 16, 128);
+          const uint64_t bd = umma_smem_desc(sb + (uint32_t)(kk * 2) * (NT * 16), (uint32_t)NT * 16, 128);
+          umma_f16(tmem_base, ad, bd, a.idesc, (uint32_t)((i | kk) != 0));
+        }
+        umma_commit(bar0 + 8 * (4 + s));
+      }
+      umma_commit(bar0 + 64);
+    }
+    __syncwarp();
+  } else {
+    // epilogue: thread == row
+    const long long row = (long long)m_tile * G_TM + warp * 32 + lane;
+    const uint32_t t_acc = tmem_base + ((uint32_t)(warp * 32) << 16);
+    if (n_slabs > 0) {
+      mbar_wait(bar0 + 64, 0, nullptr, 0);
+      tc_fence_after();
+    }
+    const bool valid = row < a.M;
+    float* crow = a.C + row * a.ldc + (size_t)n_tile * NT;
+    const float* bias = (a.bias && split == 0) ? a.bias + (size_t)n_tile * NT : nullptr;
+    for (int c = 0; c < NT / 32; ++c) {
+      float v[32];
+      if (n_slabs > 0) {
+        tmem_ld32(t_acc + c * 32, v);
+        tmem_ld_wait32(v);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = 0.f;
+      }
+      if (!valid) continue;
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        float4 o = make_float4(v[i] * a.alpha, v[i + 1] * a.alpha, v[i + 2] * a.alpha, v[i + 3] * a.alpha);
+        if (bias) {
+          const float4 b = *reinterpret_cast<const float4*>(bias + c * 32 + i);
+          o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+        }
+        float4* dst = reinterpret_cast<float4*>(crow + c * 32 + i);
+        if (a.flags & GEMM_ATOMIC) {
+          atomicAdd(dst, o);
+        } else if (a.flags & GEMM_ADD_EXISTING) {
+          const float4 e = *dst;
+          *dst = make_float4(e.x + o.x, e.y + o.y, e.z + o.z, e.w + o.w);
+        } else {
+          *dst = o;
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 4) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+// src[R][ld] fp32 row-major, contraction along columns (Kc) -> P[r/RT][k/8][r%RT][k%8]; rows >= R are zero filled up to
+// R_pad (multiple of RT); columns >= Kc_valid zero filled up to Kc (multiple of 8).
+__global__ void pack_kmajor_kernel(const float* __restrict__ src, long long ld, long long R, long long R_pad, int Kc_valid,
+                                   int Kc, int RT, int bf16, uint16_t* __restrict__ dst) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // one thread per (r, k8): 16 bytes out
+  const int K8 = Kc / 8;
+  if (idx >= R_pad * K8) return;
+  // consecutive threads -> consecutive rows of the same k8 (coalesced 16-byte stores)
+  const long long tile = idx / ((long long)K8 * RT);
+  const long long rem = idx % ((long long)K8 * RT);
+  const int k8 = (int)(rem / RT), rin = (int)(rem % RT);
+  const long long r = tile * RT + rin;
+  uint16_t out[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int k = k8 * 8 + i;
+    const float v = (r < R && k < Kc_valid) ? src[r * ld + k] : 0.f;
+    if (bf16) { __nv_bfloat16 b = __float2bfloat16_rn(v); out[i] = *reinterpret_cast<uint16_t*>(&b); }
+    else { __half h = __float2half_rn(v); out[i] = *reinterpret_cast<uint16_t*>(&h); }
+  }
+  *reinterpret_cast<uint4*>(dst + (size_t)idx * 8) = *reinterpret_cast<uint4*>(out);
+}
+
+// src[Kc][ld] fp32 row-major, contraction along ROWS (Kc), operand rows = columns f of src (F of them)
+//   -> P[f/RT][k/8][f%RT][k%8];  f >= F zero filled up to F_pad, k >= Kc_valid zero filled up to Kc.
+__global__ void pack_kmajor_t_kernel(const float* __restrict__ src, long long ld, long long Kc_valid, long long Kc, int F,
+                                     int F_pad, int RT, int bf16, uint16_t* __restrict__ dst) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // one thread per (f, k8)
+  const long long K8 = Kc / 8;
+  if (idx >= (long long)F_pad * K8) return;
+  const long long tile = idx / (K8 * RT);
+  const long long rem = idx % (K8 * RT);
+  const long long k8 = rem / RT;
+  const int fin = (int)(rem % RT);
+  const int f = (int)(tile * RT + fin);  // consecutive threads -> consecutive f: coalesced reads of src rows
+  uint16_t out[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const long long k = k8 * 8 + i;
+    const float v = (f < F && k < Kc_valid) ? src[k * ld + f] : 0.f;
+    if (bf16) { __nv_bfloat16 b = __float2bfloat16_rn(v); out[i] = *reinterpret_cast<uint16_t*>(&b); }
+    else { __half h = __float2half_rn(v); out[i] = *reinterpret_cast<uint16_t*>(&h); }
+  }
+  *reinterpret_cast<uint4*>(dst + (size_t)idx * 8) = *reinterpret_cast<uint4*>(out);
+}
+
+}  // namespace bfk

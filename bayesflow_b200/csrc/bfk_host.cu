@@ -7,6 +7,7 @@
 #include "bfk_sampler.cuh"
 #include "bfk_sampler_fast.cuh"
 #include "bfk_adaptive.cuh"
+#include "bfk_gemm.cuh"
 
 using namespace bfk;
 
@@ -353,4 +354,62 @@ extern "C" int bfk_adaptive_trial(const bfk_net_config* c, const void* packed, c
                                   const float* tmask, float* ybuf, float* kbuf, int64_t B, void* stream_) {
   return launch_sampler(c, packed, table, nullptr, method, 1, pre_add, post_add, rpg, tmask, nullptr, nullptr, B, 2,
                         (cudaStream_t)stream_, ctrl, ybuf, kbuf);
+}
+
+// ---------------------------------------------------------------------------------------------------- layer-wise GEMM
+static inline int64_t round_up64(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
+
+extern "C" size_t bfk_packed_operand_bytes(int64_t rows, int64_t k, int32_t row_tile) {
+  if (rows <= 0 || k <= 0 || row_tile <= 0) return 0;
+  return (size_t)round_up64(rows, row_tile) * (size_t)round_up64(k, 32) * 2;
+}
+
+extern "C" int bfk_pack_kmajor(const float* src, int64_t ld, int64_t R, int32_t k_valid, int32_t k_pad, int32_t row_tile,
+                               int32_t precision, void* dst, void* stream_) {
+  if (!src || !dst || R <= 0 || k_valid <= 0 || k_pad < k_valid || (k_pad % 32) || row_tile <= 0 || (row_tile % 8))
+    return fail(-60, "bfk_pack_kmajor: bad arguments");
+  const int64_t R_pad = round_up64(R, row_tile);
+  const int64_t n = R_pad * (k_pad / 8);
+  pack_kmajor_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream_>>>(src, ld, R, R_pad, k_valid, k_pad, row_tile,
+                                                                                   precision == BFK_PREC_BF16, (uint16_t*)dst);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_pack_kmajor_t(const float* src, int64_t ld, int64_t k_valid, int64_t k_pad, int32_t F, int32_t row_tile,
+                                 int32_t precision, void* dst, void* stream_) {
+  if (!src || !dst || F <= 0 || k_valid <= 0 || k_pad < k_valid || (k_pad % 32) || row_tile <= 0 || (row_tile % 8))
+    return fail(-61, "bfk_pack_kmajor_t: bad arguments");
+  const int F_pad = (int)round_up64(F, row_tile);
+  const int64_t n = (int64_t)F_pad * (k_pad / 8);
+  pack_kmajor_t_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream_>>>(src, ld, k_valid, k_pad, F, F_pad, row_tile,
+                                                                                     precision == BFK_PREC_BF16, (uint16_t*)dst);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_gemm(const void* A, const void* B, float* Cm, int64_t ldc, int64_t M, int32_t N, int32_t K, int32_t NT,
+                        int32_t k_splits, int32_t flags, const float* bias, float alpha, int32_t precision, void* stream_) {
+  if (!A || !B || !Cm || M <= 0 || N <= 0 || K <= 0) return fail(-62, "bfk_gemm: bad arguments");
+  if (NT != 64 && NT != 128 && NT != 256) return fail(-63, "bfk_gemm: NT must be 64, 128 or 256");
+  if ((N % NT) || (K % G_KC) || (ldc % 4)) return fail(-64, "bfk_gemm: need N % NT == 0, K % 32 == 0, ldc % 4 == 0");
+  if (k_splits < 1) k_splits = 1;
+  if (k_splits > 1 && !(flags & GEMM_ATOMIC)) return fail(-65, "bfk_gemm: k_splits > 1 needs the atomic flag");
+  GemmArgs a{};
+  a.A = (const unsigned char*)A; a.B = (const unsigned char*)B; a.C = Cm; a.bias = bias;
+  a.M = M; a.ldc = ldc; a.N = N; a.K = K; a.NT = NT; a.flags = flags; a.alpha = alpha;
+  int kps = (int)round_up64((K + k_splits - 1) / k_splits, G_KC);
+  a.k_per_split = kps;
+  k_splits = (K + kps - 1) / kps;
+  a.idesc = umma_idesc_f16(G_TM, NT, precision == BFK_PREC_BF16 ? 1 : 0);
+  const size_t sh = gemm_smem_bytes(NT);
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem_bytes(256)));
+    attr_set = true;
+  }
+  dim3 grid((unsigned)((M + G_TM - 1) / G_TM), (unsigned)(N / NT), (unsigned)k_splits);
+  gemm_kernel<false><<<grid, G_THREADS, sh, (cudaStream_t)stream_>>>(a);
+  CK(cudaGetLastError());
+  return 0;
 }

@@ -142,6 +142,23 @@ int bfk_adaptive_trial(const bfk_net_config* cfg, const void* packed, const floa
                        const float* pre_add, const float* post_add, int64_t rows_per_group, const float* target_mask,
                        float* ybuf, float* kbuf, int64_t B, void* stream);
 
+/* ---- layer-wise tensor-core GEMM (training forward/backward, widths > 256) ------------------------------------------
+ * Operands are fp16 (precision 0) or bf16 (1) in the packed K-major image P[r/RT][k/8][r%RT][k%8] (row tile RT = 128
+ * for A, = NT for B; NT in {64,128,256} and N % NT == 0; K % 32 == 0; rows zero-padded to the tile).  These replace
+ * the `keras.layers.Dense` matmuls of TimeMLP / ConditionalDenseBlock (time_mlp.py:131-139,
+ * conditional_dense_block.py:117) and their autograd transposes (torch_approximator.py:88-99). */
+size_t bfk_packed_operand_bytes(int64_t rows, int64_t k, int32_t row_tile);
+/* src (R, ld) fp32 row-major, contraction along columns -> packed (rows padded to row_tile, k padded to k_pad) */
+int bfk_pack_kmajor(const float* src, int64_t ld, int64_t R, int32_t k_valid, int32_t k_pad, int32_t row_tile,
+                    int32_t precision, void* dst, void* stream);
+/* src (Kc, ld) fp32 row-major, contraction along ROWS; operand rows are the F columns of src -> packed */
+int bfk_pack_kmajor_t(const float* src, int64_t ld, int64_t k_valid, int64_t k_pad, int32_t F, int32_t row_tile,
+                      int32_t precision, void* dst, void* stream);
+/* C (M, ldc) fp32 = alpha * A * B (+ bias) ; flags: 1 = atomic accumulate (use with k_splits > 1), 2 = add to existing */
+int bfk_gemm(const void* A_packed, const void* B_packed, float* C, int64_t ldc, int64_t M, int32_t N, int32_t K,
+             int32_t NT, int32_t k_splits, int32_t flags, const float* bias, float alpha, int32_t precision,
+             void* stream);
+
 /* ---- introspection ------------------------------------------------------------------------------------------- */
 int bfk_num_sms(void);
 int bfk_fused_supported(const bfk_net_config* cfg); /* 1 if the on-chip sampler handles this config */
