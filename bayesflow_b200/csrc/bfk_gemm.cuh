@@ -134,6 +134,119 @@ __global__ void __launch_bounds__(G_THREADS, 2) gemm_kernel(const GemmArgs a) {
   if (warp == 4) tmem_dealloc(tmem_base, tmem_cols);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// dW GEMM: C[Mf, N] += alpha * X^T * Y with the contraction over the BATCH rows.  X and Y are activation images
+// IMG[r/128][k/8][r%128][k%8] (r = batch row, k = feature).  Read as an MN-major UMMA operand (MN = feature, K = batch
+// row) the very same bytes are the canonical no-swizzle layout: core matrix = 8 batch rows x 8 features (128 B), next
+// 8 batch rows +128 B (LBO), next feature octet +2048 B (SBO) - so the images the forward pass wrote are consumed
+// without a transposed re-pack.  One stage = one 128-row batch tile: X part 16 octets (32 KB), Y part NT/8 octets,
+// each ONE contiguous bulk copy.  Split over batch tiles (blockIdx.z), fp32 atomics into a zeroed C.
+constexpr int DW_STAGES = 3;
+struct GemmDwArgs {
+  const unsigned char* X; const unsigned char* Y;
+  float* C; long long ldc;
+  int XK8, YK8;  // feature octets per row in the images
+  int Mv, Nv;    // valid rows / columns of C
+  int NT, n_btiles, tiles_per_split, swap;
+  float alpha;
+  uint32_t idesc;
+};
+__host__ __device__ inline size_t gemm_dw_smem_bytes(int NT) { return (size_t)DW_STAGES * (32768 + (size_t)NT * 256) + 256; }
+__host__ __device__ constexpr uint32_t umma_idesc_f16_mn(int M, int N, int ab_format) {
+  return umma_idesc_f16(M, N, ab_format) | (1u << 15) | (1u << 16);  // a_major = b_major = MN
+}
+
+__global__ void __launch_bounds__(G_THREADS, 1) gemm_dw_kernel(const GemmDwArgs a) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int NT = a.NT;
+  const uint32_t a_bytes = 32768, b_bytes = (uint32_t)NT * 256, st_bytes = a_bytes + b_bytes;
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t bar0 = smem_base + DW_STAGES * st_bytes;
+  volatile uint32_t* s_tmem = reinterpret_cast<volatile uint32_t*>(smem + DW_STAGES * st_bytes + 72);
+  const int m_tile = blockIdx.x, n_tile = blockIdx.y, split = blockIdx.z;
+  const int t0 = split * a.tiles_per_split;
+  const int n_it = min(a.n_btiles, t0 + a.tiles_per_split) - t0;
+  if (n_it <= 0) return;
+  const int a_oct = min(16, a.XK8 - m_tile * 16), b_oct = min(NT / 8, a.YK8 - n_tile * (NT / 8));
+  if (a_oct < 16 || b_oct < NT / 8) {  // partial tiles: the never-written octets must read as zero
+    for (uint32_t i = threadIdx.x; i < DW_STAGES * st_bytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+    fence_proxy_async_smem();
+  }
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < DW_STAGES; ++s) { mbar_init(bar0 + 8 * s, 1); mbar_init(bar0 + 8 * (4 + s), 1); }
+    mbar_init(bar0 + 64, 1);
+    fence_barrier_init();
+  }
+  const uint32_t tmem_cols = NT <= 32 ? 32 : NT <= 64 ? 64 : NT <= 128 ? 128 : 256;
+  if (warp == 4) tmem_alloc(bar0 + 72, tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 5) {
+    if (lane == 0) {
+      for (int i = 0; i < n_it; ++i) {
+        const int s = i % DW_STAGES;
+        mbar_wait(bar0 + 8 * (4 + s), ((i / DW_STAGES) & 1) ^ 1, nullptr, 0);
+        mbar_arrive_expect_tx(bar0 + 8 * s, (uint32_t)(a_oct + b_oct) * 2048);
+        const size_t t = (size_t)(t0 + i);
+        bulk_g2s(smem_base + s * st_bytes, a.X + (t * a.XK8 + (size_t)m_tile * 16) * 2048, (uint32_t)a_oct * 2048, bar0 + 8 * s);
+        bulk_g2s(smem_base + s * st_bytes + a_bytes, a.Y + (t * a.YK8 + (size_t)n_tile * (NT / 8)) * 2048, (uint32_t)b_oct * 2048,
+                 bar0 + 8 * s);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 4) {
+    if (lane == 0) {
+      const uint32_t lbo = a.swap ? 2048 : 128, sbo = a.swap ? 128 : 2048;
+      for (int i = 0; i < n_it; ++i) {
+        const int s = i % DW_STAGES;
+        mbar_wait(bar0 + 8 * s, (i / DW_STAGES) & 1, nullptr, 0);
+        tc_fence_after();
+        const uint32_t sa = smem_base + s * st_bytes, sb = sa + a_bytes;
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) {  // 16 batch rows per UMMA = two 128-byte core-matrix rows
+          const uint64_t ad = umma_smem_desc(sa + (uint32_t)kk * 256, lbo, sbo);
+          const uint64_t bd = umma_smem_desc(sb + (uint32_t)kk * 256, lbo, sbo);
+          umma_f16(tmem_base, ad, bd, a.idesc, (uint32_t)((i | kk) != 0));
+        }
+        umma_commit(bar0 + 8 * (4 + s));
+      }
+      umma_commit(bar0 + 64);
+    }
+    __syncwarp();
+  } else {
+    const int m = m_tile * G_TM + warp * 32 + lane;
+    const uint32_t t_acc = tmem_base + ((uint32_t)(warp * 32) << 16);
+    mbar_wait(bar0 + 64, 0, nullptr, 0);
+    tc_fence_after();
+    const bool vec = (a.ldc % 4 == 0) && (a.Nv % 4 == 0);
+    for (int c = 0; c < NT / 32; ++c) {
+      float v[32];
+      tmem_ld32(t_acc + c * 32, v);
+      tmem_ld_wait32(v);
+      if (m >= a.Mv) continue;
+      const int n0 = n_tile * NT + c * 32;
+      float* crow = a.C + (long long)m * a.ldc + n0;
+      if (vec) {
+#pragma unroll
+        for (int i = 0; i < 32; i += 4)
+          if (n0 + i < a.Nv) atomicAdd(reinterpret_cast<float4*>(crow + i), make_float4(v[i] * a.alpha, v[i + 1] * a.alpha, v[i + 2] * a.alpha, v[i + 3] * a.alpha));
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          if (n0 + i < a.Nv) atomicAdd(crow + i, v[i] * a.alpha);
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 4) tmem_dealloc(tmem_base, tmem_cols);
+}
+
 // src[R][ld] fp32 row-major, contraction along columns (Kc) -> P[r/RT][k/8][r%RT][k%8]; rows >= R are zero filled up to
 // R_pad (multiple of RT); columns >= Kc_valid zero filled up to Kc (multiple of 8).
 __global__ void pack_kmajor_kernel(const float* __restrict__ src, long long ld, long long R, long long R_pad, int Kc_valid,

@@ -413,3 +413,5 @@ extern "C" int bfk_gemm(const void* A, const void* B, float* Cm, int64_t ldc, in
   CK(cudaGetLastError());
   return 0;
 }
+
+#include "bfk_train_host.cuh"

@@ -1,0 +1,591 @@
+// Layer-wise training path (FlowMatching.compute_metrics / DiffusionModel.compute_metrics, flow_matching.py:132-178,
+// diffusion_model.py:142-232, and the torch autograd transposes the reference gets from torch_approximator.py:88-99).
+// The dense contractions run in bfk_gemm.cuh (tcgen05); the kernels here are everything BETWEEN two GEMMs, each one a
+// single pass over a (rows, width) activation: they read the fp32 GEMM output and write (a) what backward needs in fp32
+// and (b) the next GEMM's operand directly in the packed fp16 K-major image
+//     IMG[r/128][k/8][r%128][k%8]
+// which serves three roles without re-packing: A operand (K-major) of the next forward GEMM / of the dX GEMM, and BOTH
+// operands (MN-major) of the dW GEMM whose contraction runs over the batch rows (gemm_dw_kernel).
+// Gradients are propagated UN-normalised (the 1/(B*D) of the mean is applied where a gradient leaves the chain), which
+// keeps the fp16 gradient operands at O(1) magnitudes.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "bfk_ptx.cuh"
+#include "../../include/bfk.h"
+
+namespace bfk {
+
+constexpr float LN_EPS = 1e-3f;  // keras.layers.LayerNormalization default epsilon
+
+// value and derivative of the Keras activation (time_mlp.py:106-109), fp32, full-range libm functions
+__device__ __forceinline__ float t_act(int act, float x, float& d) {
+  switch (act) {
+    case BFK_ACT_MISH: {
+      const float sp = x > 20.f ? x : log1pf(expf(x));
+      const float t = tanhf(sp);
+      const float sg = 1.f / (1.f + expf(-x));
+      d = t + x * (1.f - t * t) * sg;
+      return x * t;
+    }
+    case BFK_ACT_SILU: {
+      const float sg = 1.f / (1.f + expf(-x));
+      d = sg * (1.f + x * (1.f - sg));
+      return x * sg;
+    }
+    case BFK_ACT_RELU:
+      d = x > 0.f ? 1.f : 0.f;
+      return x > 0.f ? x : 0.f;
+    case BFK_ACT_GELU: {
+      const float cdf = 0.5f * (1.f + erff(x * 0.70710678118654752f));
+      d = cdf + x * 0.3989422804014327f * expf(-0.5f * x * x);
+      return x * cdf;
+    }
+    default: {  // tanh
+      const float t = tanhf(x);
+      d = 1.f - t * t;
+      return t;
+    }
+  }
+}
+
+// counter-based keep mask for Dropout (conditional_dense_block.py:120-121): identical in forward and backward
+__device__ __forceinline__ float drop_scale(unsigned long long seed, int layer, long long row, int col, float rate, float inv_keep) {
+  unsigned long long z = seed + 0x9E3779B97F4A7C15ull * (unsigned long long)(row * 4096 + col + 1) + ((unsigned long long)layer << 56);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  const float u = (float)(unsigned)(z >> 40) * (1.f / 16777216.f);
+  return u >= rate ? inv_keep : 0.f;
+}
+
+__device__ __forceinline__ uint32_t h2pack(float a, float b) {
+  __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ uint4 pack8(const float* v) {
+  return make_uint4(h2pack(v[0], v[1]), h2pack(v[2], v[3]), h2pack(v[4], v[5]), h2pack(v[6], v[7]));
+}
+// byte offset of the 16-byte chunk (row r, octet k8) in an image with K8 octets per row
+__device__ __forceinline__ size_t img_off(long long r, int k8, int K8) {
+  return (((size_t)(r >> 7) * K8 + k8) * 128 + (size_t)(r & 127)) * 16;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ void ld8(const float* p, float* v) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+__device__ __forceinline__ void st8(float* p, const float* v) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Inputs: u = [x | conditions] image (KU8 octets) and the Fourier time embedding image (KT8 octets):
+//   emb = concat[t, sin(t*w*2pi*scale), cos(..)]   fourier_embedding.py:71-73 (same left-to-right product)
+// One thread per row (rows >= B are zero filled: they are the K padding of the dW contraction).
+__global__ void train_input_kernel(const float* __restrict__ x, const float* __restrict__ cond, const float* __restrict__ t,
+                                   const float* __restrict__ freq, float fscale, long long B, long long R_pad, int D, int C,
+                                   int T, int KU8, int KT8, unsigned char* __restrict__ u_img, unsigned char* __restrict__ te_img) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= R_pad) return;
+  const bool valid = r < B;
+  for (int k8 = 0; k8 < KU8; ++k8) {
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int k = k8 * 8 + i;
+      float e = 0.f;
+      if (valid) {
+        if (k < D) e = x[r * D + k];
+        else if (k < D + C) e = cond[r * C + (k - D)];
+      }
+      v[i] = e;
+    }
+    *reinterpret_cast<uint4*>(u_img + img_off(r, k8, KU8)) = pack8(v);
+  }
+  const float tt = valid ? t[r] : 0.f;
+  const int Th = (T - 1) / 2;
+  for (int k8 = 0; k8 < KT8; ++k8) {
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int k = k8 * 8 + i;
+      float e = 0.f;
+      if (valid) {
+        if (T == 1) e = k == 0 ? tt : 0.f;
+        else if (k == 0) e = tt;
+        else if (k <= Th) e = sinf(tt * freq[k - 1] * 2.f * 3.14159265358979323846f * fscale);
+        else if (k < T) e = cosf(tt * freq[k - 1 - Th] * 2.f * 3.14159265358979323846f * fscale);
+      }
+      v[i] = e;
+    }
+    *reinterpret_cast<uint4*>(te_img + img_off(r, k8, KT8)) = pack8(v);
+  }
+}
+
+// out = act(P): packed image (+ optional fp32 copy).  grid (K8, chunks), 128 threads = the rows of one 128-row tile.
+__global__ void act_pack_kernel(const float* __restrict__ P, long long ld, long long B, long long n_tiles, int K8, int act,
+                                unsigned char* __restrict__ img, float* __restrict__ out_f32) {
+  const int k8 = blockIdx.x;
+  for (long long tile = blockIdx.y; tile < n_tiles; tile += gridDim.y) {
+    const long long r = tile * 128 + threadIdx.x;
+    float v[8];
+    if (r < B) {
+      ld8(P + r * ld + k8 * 8, v);
+      float d;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = t_act(act, v[i], d);
+      if (out_f32) st8(out_f32 + r * ld + k8 * 8, v);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = 0.f;
+    }
+    *reinterpret_cast<uint4*>(img + img_off(r, k8, K8)) = pack8(v);
+  }
+}
+
+// dP = dY * act'(P): packed image, column sums of dP -> bias gradient (scaled).  Same grid as act_pack_kernel.
+__global__ void act_bwd_kernel(const float* __restrict__ dY, const float* __restrict__ P, long long ld, long long B,
+                               long long n_tiles, int K8, int act, unsigned char* __restrict__ img, float* __restrict__ dbias,
+                               float gscale) {
+  __shared__ float red[4][8];
+  const int k8 = blockIdx.x;
+  float cs[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) cs[i] = 0.f;
+  for (long long tile = blockIdx.y; tile < n_tiles; tile += gridDim.y) {
+    const long long r = tile * 128 + threadIdx.x;
+    float v[8];
+    if (r < B) {
+      float p[8];
+      ld8(P + r * ld + k8 * 8, p);
+      ld8(dY + r * ld + k8 * 8, v);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float d;
+        t_act(act, p[i], d);
+        v[i] *= d;
+        cs[i] += v[i];
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = 0.f;
+    }
+    *reinterpret_cast<uint4*>(img + img_off(r, k8, K8)) = pack8(v);
+  }
+  if (dbias) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) cs[i] = warp_sum(cs[i]);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) red[warp][i] = cs[i];
+    }
+    __syncthreads();
+    if (threadIdx.x < 8) atomicAdd(dbias + k8 * 8 + threadIdx.x, gscale * (red[0][threadIdx.x] + red[1][threadIdx.x] + red[2][threadIdx.x] + red[3][threadIdx.x]));
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// ConditionalDenseBlock forward between its GEMMs (conditional_dense_block.py:117-130):
+//   u = dropout(act(P));  v = skip + film(u);  out = LayerNorm(v)          one warp per row, lane owns octets lane+32j
+struct BlockFwdArgs {
+  const float* P;       // (B,W) dense output incl. bias
+  const float* FB;      // FiLM shift: (B,W) per row, or one vector (fb_stride 0)
+  const float* FG;      // FiLM scale (film_use_gamma) or null
+  long long fb_stride;
+  const float* prev;    // (B,W) skip source: previous block's normalised activations (or h0), or null (residual off)
+  const float* pg; const float* pb;  // affine of the previous LayerNorm applied to prev (null: prev is used as is)
+  const float* gamma; const float* beta;  // this block's LayerNorm parameters (null with norm none)
+  float* xhat;          // (B,W) normalised activations before the affine (saved for backward / next skip), or null
+  float* rstd;          // (B) or null
+  unsigned char* img;   // packed fp16 image of the block output
+  float* out_f32;       // optional fp32 copy of the block output
+  long long B, R_pad;
+  int W, act, norm, layer;
+  float drop_rate, inv_keep; unsigned long long seed;
+};
+
+template <int NJ>
+__global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
+  const int K8 = a.W / 8;
+  for (long long r = warp0; r < a.R_pad; r += nwarps) {
+    if (r >= a.B) {
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) {
+        const int o = j * 32 + lane;
+        if (o < K8) *reinterpret_cast<uint4*>(a.img + img_off(r, o, K8)) = make_uint4(0, 0, 0, 0);
+      }
+      continue;
+    }
+    float v[NJ][8];
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int o = j * 32 + lane;
+      if (o < K8) {
+        const int c0 = o * 8;
+        float p[8], f[8];
+        ld8(a.P + r * a.W + c0, p);
+        ld8(a.FB + r * a.fb_stride + c0, f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float d;
+          float u = t_act(a.act, p[i], d);
+          if (a.drop_rate > 0.f) u *= drop_scale(a.seed, a.layer, r, c0 + i, a.drop_rate, a.inv_keep);
+          v[j][i] = u;
+        }
+        if (a.FG) {
+          float g[8];
+          ld8(a.FG + r * a.fb_stride + c0, g);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[j][i] *= 1.f + g[i];
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[j][i] += f[i];
+        if (a.prev) {
+          float s[8];
+          ld8(a.prev + r * a.W + c0, s);
+          if (a.pg) {
+            float g[8], b[8];
+            ld8(a.pg + c0, g);
+            ld8(a.pb + c0, b);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) s[i] = fmaf(s[i], g[i], b[i]);
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[j][i] += s[i];
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) sum += v[j][i];
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[j][i] = 0.f;
+      }
+    }
+    float mean = 0.f, rs = 1.f;
+    if (a.norm == BFK_NORM_LAYER) {
+      mean = warp_sum(sum) / (float)a.W;
+      float sq = 0.f;
+#pragma unroll
+      for (int j = 0; j < NJ; ++j)
+        if (j * 32 + lane < K8) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { const float d = v[j][i] - mean; sq = fmaf(d, d, sq); }
+        }
+      rs = rsqrtf(warp_sum(sq) / (float)a.W + LN_EPS);
+    }
+    if (a.rstd && lane == 0) a.rstd[r] = rs;
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int o = j * 32 + lane;
+      if (o < K8) {
+        const int c0 = o * 8;
+        float xh[8], h[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) xh[i] = (v[j][i] - mean) * rs;
+        if (a.xhat) st8(a.xhat + r * a.W + c0, xh);
+        if (a.gamma) {
+          float g[8], b[8];
+          ld8(a.gamma + c0, g);
+          ld8(a.beta + c0, b);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) h[i] = fmaf(xh[i], g[i], b[i]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) h[i] = xh[i];
+        }
+        if (a.out_f32) st8(a.out_f32 + r * a.W + c0, h);
+        *reinterpret_cast<uint4*>(a.img + img_off(r, o, K8)) = pack8(h);
+      }
+    }
+  }
+}
+
+// ConditionalDenseBlock backward between its GEMMs.  In: dH (gradient wrt the block output, fp32, overwritten by dV =
+// gradient wrt the pre-norm sum, which is also the skip gradient the dX GEMM adds onto).  Out: dP and dV images, column
+// sums -> d(norm.gamma), d(norm.beta), d(dense.bias), d(film.to_beta.bias).
+struct BlockBwdArgs {
+  float* dH;
+  const float* xhat; const float* rstd; const float* P;
+  const float* gamma;
+  unsigned char* dP_img; unsigned char* dV_img;
+  float* d_gamma; float* d_beta; float* d_bd; float* d_bfilm;
+  long long B, R_pad;
+  int W, act, norm, layer;
+  float drop_rate, inv_keep; unsigned long long seed;
+  float gscale;
+};
+
+template <int NJ>
+__global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
+  extern __shared__ float s_red[];  // [4][W]
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
+  const int K8 = a.W / 8, W = a.W;
+  for (int i = threadIdx.x; i < 4 * W; i += blockDim.x) s_red[i] = 0.f;
+  __syncthreads();
+  float ag[NJ][8], ab[NJ][8], ad[NJ][8], af[NJ][8];
+#pragma unroll
+  for (int j = 0; j < NJ; ++j)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) ag[j][i] = ab[j][i] = ad[j][i] = af[j][i] = 0.f;
+
+  for (long long r = warp0; r < a.R_pad; r += nwarps) {
+    if (r >= a.B) {
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) {
+        const int o = j * 32 + lane;
+        if (o < K8) {
+          *reinterpret_cast<uint4*>(a.dP_img + img_off(r, o, K8)) = make_uint4(0, 0, 0, 0);
+          *reinterpret_cast<uint4*>(a.dV_img + img_off(r, o, K8)) = make_uint4(0, 0, 0, 0);
+        }
+      }
+      continue;
+    }
+    float g[NJ][8], xh[NJ][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int o = j * 32 + lane;
+      if (o < K8) {
+        const int c0 = o * 8;
+        float dh[8];
+        ld8(a.dH + r * W + c0, dh);
+        ld8(a.xhat + r * W + c0, xh[j]);
+        if (a.gamma) {
+          float gm[8];
+          ld8(a.gamma + c0, gm);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            ag[j][i] = fmaf(dh[i], xh[j][i], ag[j][i]);
+            ab[j][i] += dh[i];
+            g[j][i] = dh[i] * gm[i];
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) g[j][i] = dh[i];
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { s1 += g[j][i]; s2 = fmaf(g[j][i], xh[j][i], s2); }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) g[j][i] = xh[j][i] = 0.f;
+      }
+    }
+    float m1 = 0.f, m2 = 0.f, rs = 1.f;
+    if (a.norm == BFK_NORM_LAYER) {
+      m1 = warp_sum(s1) / (float)W;
+      m2 = warp_sum(s2) / (float)W;
+      rs = a.rstd[r];
+    }
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int o = j * 32 + lane;
+      if (o < K8) {
+        const int c0 = o * 8;
+        float dv[8], dp[8], p[8];
+        ld8(a.P + r * W + c0, p);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          dv[i] = a.norm == BFK_NORM_LAYER ? rs * (g[j][i] - m1 - xh[j][i] * m2) : g[j][i];
+          float d;
+          t_act(a.act, p[i], d);
+          if (a.drop_rate > 0.f) d *= drop_scale(a.seed, a.layer, r, c0 + i, a.drop_rate, a.inv_keep);
+          dp[i] = dv[i] * d;
+          ad[j][i] += dp[i];
+          af[j][i] += dv[i];
+        }
+        st8(a.dH + r * W + c0, dv);
+        *reinterpret_cast<uint4*>(a.dP_img + img_off(r, o, K8)) = pack8(dp);
+        *reinterpret_cast<uint4*>(a.dV_img + img_off(r, o, K8)) = pack8(dv);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < NJ; ++j) {
+    const int o = j * 32 + lane;
+    if (o < K8) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int c = o * 8 + i;
+        if (a.gamma) { atomicAdd(&s_red[c], ag[j][i]); atomicAdd(&s_red[W + c], ab[j][i]); }
+        atomicAdd(&s_red[2 * W + c], ad[j][i]);
+        atomicAdd(&s_red[3 * W + c], af[j][i]);
+      }
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < W; c += blockDim.x) {
+    if (a.gamma) { atomicAdd(a.d_gamma + c, a.gscale * s_red[c]); atomicAdd(a.d_beta + c, a.gscale * s_red[W + c]); }
+    atomicAdd(a.d_bd + c, a.gscale * s_red[2 * W + c]);
+    atomicAdd(a.d_bfilm + c, a.gscale * s_red[3 * W + c]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Loss head.  resid = a_b*pred - target;  loss_b = w_b * mean_i resid^2 (mse) | mean_i |resid| (mae)
+//   FlowMatching: a = 1, target = x1 - x0 (flow_matching.py:170-176);  DiffusionModel: a_b and target from the schedule
+//   (diffusion_model.py:197-230).  Writes the un-normalised dLoss/dpred image (64 features, zeros beyond D), adds
+//   loss_scale * sum_b loss_b to *loss and gscale * column sums to d_bo.  One thread per row.
+__global__ void loss_kernel(const float* __restrict__ pred, long long ldp, const float* __restrict__ target,
+                            const float* __restrict__ a_row, const float* __restrict__ w_row, long long B, long long R_pad,
+                            int D, int mae, unsigned char* __restrict__ dout_img, int KO8, float* __restrict__ loss,
+                            float loss_scale, float* __restrict__ d_bo, float gscale) {
+  __shared__ float s_loss;
+  __shared__ float s_db[64];
+  if (threadIdx.x == 0) s_loss = 0.f;
+  if (threadIdx.x < 64) s_db[threadIdx.x] = 0.f;
+  __syncthreads();
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  float lrow = 0.f;
+  if (r < R_pad) {
+    const bool valid = r < B;
+    const float av = (valid && a_row) ? a_row[r] : 1.f;
+    const float wv = (valid && w_row) ? w_row[r] : 1.f;
+    for (int k8 = 0; k8 < KO8; ++k8) {
+      float v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int k = k8 * 8 + i;
+        float g = 0.f;
+        if (valid && k < D) {
+          const float res = av * pred[r * ldp + k] - target[r * D + k];
+          if (mae) { lrow += fabsf(res); g = wv * av * (res > 0.f ? 1.f : (res < 0.f ? -1.f : 0.f)); }
+          else { lrow = fmaf(res, res, lrow); g = 2.f * wv * av * res; }
+          atomicAdd(&s_db[k], g);
+        }
+        v[i] = g;
+      }
+      *reinterpret_cast<uint4*>(dout_img + img_off(r, k8, KO8)) = pack8(v);
+    }
+    lrow *= wv;
+  }
+  lrow = warp_sum(lrow);
+  if ((threadIdx.x & 31) == 0) atomicAdd(&s_loss, lrow);
+  __syncthreads();
+  if (threadIdx.x == 0) atomicAdd(loss, s_loss * loss_scale);
+  if (d_bo && threadIdx.x < D) atomicAdd(d_bo + threadIdx.x, gscale * s_db[threadIdx.x]);
+}
+
+// d(frequencies) from d(time embedding) (fourier_embedding.py:71-73): one thread per row, block reduction.
+__global__ void freq_bwd_kernel(const float* __restrict__ dte, long long ld, const float* __restrict__ t,
+                                const float* __restrict__ freq, float fscale, long long B, int Th, float* __restrict__ dfreq,
+                                float gscale) {
+  __shared__ float s[32];
+  if (threadIdx.x < 32) s[threadIdx.x] = 0.f;
+  __syncthreads();
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const float c = 2.f * 3.14159265358979323846f * fscale;
+  for (int j = 0; j < Th; ++j) {
+    float g = 0.f;
+    if (r < B) {
+      const float tt = t[r];
+      const float p = tt * freq[j] * 2.f * 3.14159265358979323846f * fscale;
+      g = tt * c * (dte[r * ld + 1 + j] * cosf(p) - dte[r * ld + 1 + Th + j] * sinf(p));
+    }
+    g = warp_sum(g);
+    if ((threadIdx.x & 31) == 0) atomicAdd(&s[j], g);
+  }
+  __syncthreads();
+  if (threadIdx.x < Th) atomicAdd(dfreq + threadIdx.x, gscale * s[threadIdx.x]);
+}
+
+// First layer as ONE contraction over u = [x | c]:  concat: W1 = blockdiag(Wx, Wc) (KU x 2W), b1 = [bx, bc];
+// add: W1 = [Wx; Wc] (KU x W), b1 = bx + bc; unconditional: W1 = Wx.      time_mlp.py:131-137
+__global__ void build_w1_kernel(const float* __restrict__ Wx, const float* __restrict__ bx, const float* __restrict__ Wc,
+                                const float* __restrict__ bc, int D, int C, int W, int merge, int KU, int N1,
+                                float* __restrict__ W1, float* __restrict__ b1) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < KU * N1) {
+    const int k = idx / N1, n = idx % N1;
+    float v = 0.f;
+    if (k < D) { if (n < W) v = Wx[k * W + n]; }
+    else if (k < D + C) {
+      if (merge == BFK_MERGE_CONCAT) { if (n >= W) v = Wc[(k - D) * W + (n - W)]; }
+      else v = Wc[(k - D) * W + n];
+    }
+    W1[idx] = v;
+  }
+  if (idx < N1) {
+    float b = 0.f;
+    if (merge == BFK_MERGE_CONCAT) b = idx < W ? bx[idx] : bc[idx - W];
+    else b = bx[idx] + (C > 0 ? bc[idx] : 0.f);
+    b1[idx] = b;
+  }
+}
+__global__ void scatter_w1_grad_kernel(const float* __restrict__ dW1, const float* __restrict__ db1, int D, int C, int W,
+                                       int merge, int N1, float gscale, float* __restrict__ dWx, float* __restrict__ dbx,
+                                       float* __restrict__ dWc, float* __restrict__ dbc) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < (D + C) * W) {
+    const int k = idx / W, n = idx % W;
+    if (k < D) dWx[k * W + n] += gscale * dW1[k * N1 + n];
+    else dWc[(k - D) * W + n] += gscale * dW1[k * N1 + (merge == BFK_MERGE_CONCAT ? W + n : n)];
+  }
+  if (idx < W) {
+    dbx[idx] += gscale * db1[idx];
+    if (C > 0) dbc[idx] += gscale * db1[merge == BFK_MERGE_CONCAT ? W + idx : idx];
+  }
+}
+
+// FlowMatching.compute_metrics inputs (flow_matching.py:159-168): x = t*x1 + (1-t)*x0, target = x1 - x0
+__global__ void fm_interp_kernel(const float* __restrict__ x0, const float* __restrict__ x1, const float* __restrict__ t,
+                                 long long B, int D, float* __restrict__ x, float* __restrict__ target) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * D) return;
+  const float tt = t[i / D];
+  x[i] = tt * x1[i] + (1.f - tt) * x0[i];
+  target[i] = x1[i] - x0[i];
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Optimizer (keras.optimizers.Adam as BasicWorkflow builds it, basic_workflow.py:514-526: per-variable clipnorm).
+// Segments = parameter tensors inside one flat buffer.
+__global__ void seg_sqnorm_kernel(const float* __restrict__ g, const long long* __restrict__ seg_off, int n_seg,
+                                  float* __restrict__ sq) {
+  const int s = blockIdx.x;
+  const long long a = seg_off[s], b = seg_off[s + 1];
+  float acc = 0.f;
+  for (long long i = a + blockIdx.y * blockDim.x + threadIdx.x; i < b; i += (long long)gridDim.y * blockDim.x) acc = fmaf(g[i], g[i], acc);
+  acc = warp_sum(acc);
+  __shared__ float red[32];
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+    v = warp_sum(v);
+    if (threadIdx.x == 0) atomicAdd(sq + s, v);
+  }
+}
+__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                            const long long* __restrict__ seg_off, const float* __restrict__ sq, float clipnorm, float lr_t,
+                            float b1, float b2, float eps, float wd_lr) {
+  const int s = blockIdx.x;
+  const long long a = seg_off[s], b = seg_off[s + 1];
+  float clip = 1.f;
+  if (clipnorm > 0.f) {
+    const float nrm = sqrtf(sq[s]);
+    if (nrm > clipnorm) clip = clipnorm / nrm;
+  }
+  for (long long i = a + blockIdx.y * blockDim.x + threadIdx.x; i < b; i += (long long)gridDim.y * blockDim.x) {
+    const float gi = g[i] * clip;
+    const float mi = m[i] + (gi - m[i]) * (1.f - b1);
+    const float vi = v[i] + (gi * gi - v[i]) * (1.f - b2);
+    m[i] = mi; v[i] = vi;
+    float pi = p[i];
+    if (wd_lr > 0.f) pi -= wd_lr * pi;
+    p[i] = pi - lr_t * mi / (sqrtf(vi) + eps);
+  }
+}
+
+}  // namespace bfk

@@ -1,0 +1,291 @@
+// Host orchestration of one training step (forward + loss + backward) of the velocity network, and the optimizer.
+// Included by bfk_host.cu (uses its fail()/CK helpers).  Reference: flow_matching.py:132-178 (compute_metrics),
+// time_mlp.py:125-147, conditional_dense_block.py:114-131, torch_approximator.py:88-99 (autograd + optimizer step).
+#pragma once
+#include "bfk_train.cuh"
+
+namespace {
+
+struct Arena {
+  unsigned char* base; size_t off, cap;
+  void* take(size_t bytes) {
+    off = (off + 255) / 256 * 256;
+    void* p = base ? base + off : nullptr;
+    off += bytes;
+    return p;
+  }
+};
+
+struct TrainBufs {
+  int KU, KT, KTN, N1, NO, has_merge;
+  long long Rp;
+  unsigned char *u_img, *te_img, *w1_pk, *a1_img, *wm_f, *wm_b, *h0_img, *wo_f, *wo_b, *dout_img, *dP_img, *dV_img, *dh0pre_img;
+  float *w1, *b1, *h0pre, *m, *h0, *FB, *bo_pad, *out, *dH, *dte, *da1, *dW1, *db1;
+  unsigned char *wd_f[BFK_MAX_BLOCKS], *wd_b[BFK_MAX_BLOCKS], *wb_f[BFK_MAX_BLOCKS], *wb_b[BFK_MAX_BLOCKS], *h_img[BFK_MAX_BLOCKS];
+  float *P[BFK_MAX_BLOCKS], *xhat[BFK_MAX_BLOCKS], *rstd[BFK_MAX_BLOCKS];
+};
+
+inline int r32(int x) { return (x + 31) / 32 * 32; }
+inline int r64(int x) { return (x + 63) / 64 * 64; }
+inline int nt_of(int N) { return (N % 256) == 0 ? 256 : ((N % 128) == 0 ? 128 : 64); }
+
+void plan_train(const bfk_net_config* c, long long B, bool backward, Arena& ar, TrainBufs& b) {
+  const int W = c->W;
+  b.has_merge = (c->C > 0) ? 1 : 0;
+  b.KU = r32(c->D + c->C);
+  b.KT = r32(c->T);
+  b.KTN = r64(c->T);
+  b.N1 = (b.has_merge && c->merge == BFK_MERGE_CONCAT) ? 2 * W : W;
+  b.NO = r64(c->D);
+  b.Rp = (B + 127) / 128 * 128;
+  const size_t Rp = (size_t)b.Rp, Bs = (size_t)B;
+  b.u_img = (unsigned char*)ar.take(Rp * b.KU * 2);
+  b.te_img = (unsigned char*)ar.take(Rp * b.KT * 2);
+  b.w1 = (float*)ar.take((size_t)b.KU * b.N1 * 4);
+  b.b1 = (float*)ar.take((size_t)b.N1 * 4);
+  b.w1_pk = (unsigned char*)ar.take((size_t)b.N1 * b.KU * 2);
+  b.h0pre = (float*)ar.take(Bs * b.N1 * 4);
+  if (b.has_merge) {
+    b.a1_img = (unsigned char*)ar.take(Rp * b.N1 * 2);
+    b.wm_f = (unsigned char*)ar.take((size_t)W * b.N1 * 2);
+    b.wm_b = (unsigned char*)ar.take((size_t)W * b.N1 * 2);
+    b.m = (float*)ar.take(Bs * W * 4);
+  }
+  b.h0 = (float*)ar.take(Bs * W * 4);
+  b.h0_img = (unsigned char*)ar.take(Rp * W * 2);
+  for (int l = 0; l < c->L; ++l) {
+    b.wd_f[l] = (unsigned char*)ar.take((size_t)W * W * 2);
+    b.wd_b[l] = (unsigned char*)ar.take((size_t)W * W * 2);
+    b.wb_f[l] = (unsigned char*)ar.take((size_t)W * b.KT * 2);
+    b.wb_b[l] = (unsigned char*)ar.take((size_t)r64(c->T) * W * 2);
+    b.P[l] = (float*)ar.take(Bs * W * 4);
+    b.xhat[l] = (float*)ar.take(Bs * W * 4);
+    b.rstd[l] = (float*)ar.take(Bs * 4);
+    b.h_img[l] = (unsigned char*)ar.take(Rp * W * 2);
+  }
+  b.FB = (float*)ar.take(Bs * W * 4);
+  b.wo_f = (unsigned char*)ar.take((size_t)b.NO * W * 2);
+  b.wo_b = (unsigned char*)ar.take((size_t)W * b.NO * 2);
+  b.bo_pad = (float*)ar.take((size_t)b.NO * 4);
+  b.out = (float*)ar.take(Bs * b.NO * 4);
+  b.dout_img = (unsigned char*)ar.take(Rp * b.NO * 2);
+  if (backward) {
+    b.dH = (float*)ar.take(Bs * W * 4);
+    b.dP_img = (unsigned char*)ar.take(Rp * W * 2);
+    b.dV_img = (unsigned char*)ar.take(Rp * W * 2);
+    b.dte = (float*)ar.take(Bs * b.KTN * 4);
+    if (b.has_merge) b.da1 = (float*)ar.take(Bs * b.N1 * 4);
+    b.dh0pre_img = (unsigned char*)ar.take(Rp * b.N1 * 2);
+    b.dW1 = (float*)ar.take((size_t)b.KU * b.N1 * 4);
+    b.db1 = (float*)ar.take((size_t)b.N1 * 4);
+  }
+}
+
+int check_train_cfg(const bfk_net_config* c) {
+  if (int r = check_cfg(c)) return r;
+  if ((c->W % 64) != 0 || c->W > 1024) return fail(-70, "layer-wise path: W must be a multiple of 64, <= 1024");
+  if (c->D > 64) return fail(-71, "layer-wise path: D <= 64");
+  if (c->norm == BFK_NORM_RMS) return fail(-72, "layer-wise path: norm must be 'layer' or None");
+  if (c->film_use_gamma) return fail(-73, "layer-wise path: film_use_gamma is not supported");
+  if (c->precision != BFK_PREC_FP16) return fail(-74, "layer-wise path: fp16 operands only (bf16 cannot meet the 2e-3 gradient gate)");
+  return 0;
+}
+
+int launch_gemm_dw(const unsigned char* X, int XK8, const unsigned char* Y, int YK8, float* Cm, long long ldc, int Mv, int Nv,
+                   long long Rp, float alpha, int swap, cudaStream_t st) {
+  GemmDwArgs a{};
+  a.X = X; a.Y = Y; a.C = Cm; a.ldc = ldc; a.XK8 = XK8; a.YK8 = YK8; a.Mv = Mv; a.Nv = Nv; a.alpha = alpha; a.swap = swap;
+  a.NT = (YK8 * 8 >= 128) ? 128 : 64;
+  a.n_btiles = (int)(Rp / 128);
+  const int mt = (XK8 + 15) / 16, nt = (YK8 * 8 + a.NT - 1) / a.NT;
+  int sms = bfk_num_sms();
+  if (sms <= 0) sms = 148;
+  int splits = sms / (mt * nt);
+  if (splits < 1) splits = 1;
+  if (splits > a.n_btiles) splits = a.n_btiles;
+  a.tiles_per_split = (a.n_btiles + splits - 1) / splits;
+  splits = (a.n_btiles + a.tiles_per_split - 1) / a.tiles_per_split;
+  a.idesc = umma_idesc_f16_mn(G_TM, a.NT, 0);
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(gemm_dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_dw_smem_bytes(128)));
+    attr_set = true;
+  }
+  gemm_dw_kernel<<<dim3(mt, nt, splits), G_THREADS, gemm_dw_smem_bytes(a.NT), st>>>(a);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+template <typename A>
+int launch_block_fwd(const A& a, cudaStream_t st) {
+  const int nj = (a.W / 8 + 31) / 32;
+  const unsigned grid = 148 * 8;
+  if (nj == 1) block_fwd_kernel<1><<<grid, 256, 0, st>>>(a);
+  else if (nj == 2) block_fwd_kernel<2><<<grid, 256, 0, st>>>(a);
+  else block_fwd_kernel<4><<<grid, 256, 0, st>>>(a);
+  CK(cudaGetLastError());
+  return 0;
+}
+int launch_block_bwd(const BlockBwdArgs& a, cudaStream_t st) {
+  const int nj = (a.W / 8 + 31) / 32;
+  const unsigned grid = 148 * 4;
+  const size_t sh = (size_t)4 * a.W * 4;
+  if (nj == 1) block_bwd_kernel<1><<<grid, 256, sh, st>>>(a);
+  else if (nj == 2) block_bwd_kernel<2><<<grid, 256, sh, st>>>(a);
+  else block_bwd_kernel<4><<<grid, 256, sh, st>>>(a);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+#define GP(p) const_cast<float*>(p) /* `grads` shares the layout of bfk_weights; its tensors are written */
+#define RC(call)            \
+  do {                      \
+    int _r = (call);        \
+    if (_r) return _r;      \
+  } while (0)
+
+}  // namespace
+
+extern "C" size_t bfk_train_workspace_bytes(const bfk_net_config* c, int64_t B, int32_t backward) {
+  if (check_train_cfg(c) || B <= 0) return 0;
+  Arena ar{nullptr, 0, 0};
+  TrainBufs b{};
+  plan_train(c, B, backward != 0, ar, b);
+  return ar.off + 256;
+}
+
+extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, const bfk_weights* g, const bfk_train_args* ta,
+                              float* loss, float* pred_out, void* workspace, size_t workspace_bytes, void* stream_) {
+  RC(check_train_cfg(c));
+  if (!w || !ta || !workspace || !ta->x || !ta->t || ta->B <= 0) return fail(-75, "bfk_train_step: bad arguments");
+  if (c->C > 0 && !ta->cond) return fail(-76, "bfk_train_step: conditional network needs conditions");
+  if ((loss || g) && !ta->target) return fail(-77, "bfk_train_step: loss / gradients need a target");
+  if (ta->dropout < 0.f || ta->dropout >= 1.f) return fail(-78, "bfk_train_step: dropout rate must be in [0, 1)");
+  cudaStream_t st = (cudaStream_t)stream_;
+  const long long B = ta->B;
+  const int W = c->W, D = c->D, C = c->C, L = c->L, T = c->T, act = c->activation, P16 = BFK_PREC_FP16;
+  const bool bwd = g != nullptr;
+  Arena ar{(unsigned char*)workspace, 0, workspace_bytes};
+  TrainBufs b{};
+  plan_train(c, B, bwd, ar, b);
+  if (ar.off > workspace_bytes) return fail(-79, "bfk_train_step: workspace too small (bfk_train_workspace_bytes)");
+  const long long Rp = b.Rp, n_tiles = Rp / 128;
+  const int KU = b.KU, KT = b.KT, KTN = b.KTN, N1 = b.N1, NO = b.NO, NTW = nt_of(W), NT1 = nt_of(N1);
+  const unsigned tchunks = (unsigned)(n_tiles < 64 ? n_tiles : 64);
+  const float gs = ta->grad_scale, inv_keep = 1.f / (1.f - ta->dropout);
+
+  // ---- forward ---------------------------------------------------------------------------------------------------
+  train_input_kernel<<<(unsigned)((Rp + 127) / 128), 128, 0, st>>>(ta->x, ta->cond, ta->t, w->freq, c->fourier_scale, B, Rp, D, C, T,
+                                                                 KU / 8, KT / 8, b.u_img, b.te_img);
+  build_w1_kernel<<<cdiv((size_t)KU * N1, 256), 256, 0, st>>>(w->x_k, w->x_b, w->c_k, w->c_b, D, C, W, b.has_merge ? c->merge : 0, KU, N1,
+                                                             b.w1, b.b1);
+  CK(cudaGetLastError());
+  RC(bfk_pack_kmajor_t(b.w1, N1, D + C, KU, N1, NT1, P16, b.w1_pk, st));
+  RC(bfk_gemm(b.u_img, b.w1_pk, b.h0pre, N1, B, N1, KU, NT1, 1, 0, b.b1, 1.f, P16, st));
+  if (b.has_merge) {
+    act_pack_kernel<<<dim3(N1 / 8, tchunks), 128, 0, st>>>(b.h0pre, N1, B, n_tiles, N1 / 8, act, b.a1_img, nullptr);
+    RC(bfk_pack_kmajor_t(w->m_k, W, N1, N1, W, NTW, P16, b.wm_f, st));
+    RC(bfk_gemm(b.a1_img, b.wm_f, b.m, W, B, W, N1, NTW, 1, 0, w->m_b, 1.f, P16, st));
+    act_pack_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.m, W, B, n_tiles, W / 8, act, b.h0_img, b.h0);
+  } else {
+    act_pack_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.h0pre, W, B, n_tiles, W / 8, act, b.h0_img, b.h0);
+  }
+  CK(cudaGetLastError());
+  for (int l = 0; l < L; ++l) {
+    RC(bfk_pack_kmajor_t(w->dense_k[l], W, W, W, W, NTW, P16, b.wd_f[l], st));
+    RC(bfk_pack_kmajor_t(w->film_b_k[l], W, T, KT, W, NTW, P16, b.wb_f[l], st));
+    RC(bfk_gemm(l == 0 ? b.h0_img : b.h_img[l - 1], b.wd_f[l], b.P[l], W, B, W, W, NTW, 1, 0, w->dense_b[l], 1.f, P16, st));
+    RC(bfk_gemm(b.te_img, b.wb_f[l], b.FB, W, B, W, KT, NTW, 1, 0, w->film_b_b[l], 1.f, P16, st));
+    BlockFwdArgs a{};
+    a.P = b.P[l]; a.FB = b.FB; a.FG = nullptr; a.fb_stride = W;
+    a.prev = c->residual ? (l == 0 ? b.h0 : b.xhat[l - 1]) : nullptr;
+    a.pg = (l > 0 && c->norm == BFK_NORM_LAYER) ? w->norm_g[l - 1] : nullptr;
+    a.pb = (l > 0 && c->norm == BFK_NORM_LAYER) ? w->norm_b[l - 1] : nullptr;
+    a.gamma = c->norm == BFK_NORM_LAYER ? w->norm_g[l] : nullptr;
+    a.beta = c->norm == BFK_NORM_LAYER ? w->norm_b[l] : nullptr;
+    a.xhat = b.xhat[l]; a.rstd = b.rstd[l]; a.img = b.h_img[l]; a.out_f32 = nullptr;
+    a.B = B; a.R_pad = Rp; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
+    a.drop_rate = ta->dropout; a.inv_keep = inv_keep; a.seed = ta->seed;
+    RC(launch_block_fwd(a, st));
+  }
+  RC(bfk_pack_kmajor_t(w->out_k, D, W, W, D, 64, P16, b.wo_f, st));
+  CK(cudaMemsetAsync(b.bo_pad, 0, (size_t)NO * 4, st));
+  CK(cudaMemcpyAsync(b.bo_pad, w->out_b, (size_t)D * 4, cudaMemcpyDeviceToDevice, st));
+  RC(bfk_gemm(b.h_img[L - 1], b.wo_f, b.out, NO, B, NO, W, 64, 1, 0, b.bo_pad, 1.f, P16, st));
+  if (pred_out) CK(cudaMemcpy2DAsync(pred_out, (size_t)D * 4, b.out, (size_t)NO * 4, (size_t)D * 4, (size_t)B, cudaMemcpyDeviceToDevice, st));
+  if (!loss && !bwd) return 0;
+  float* loss_dst = loss ? loss : b.FB;  // FB is free by now: scratch float when the caller does not want the loss
+  loss_kernel<<<(unsigned)((Rp + 255) / 256), 256, 0, st>>>(b.out, NO, ta->target, ta->pred_scale, ta->row_weight, B, Rp, D, ta->loss,
+                                                           b.dout_img, NO / 8, loss_dst, ta->loss_scale, bwd ? GP(g->out_b) : (float*)nullptr, gs);
+  CK(cudaGetLastError());
+  if (!bwd) return 0;
+
+  // ---- backward --------------------------------------------------------------------------------------------------
+  const int sw = ta->dw_swap;
+  RC(launch_gemm_dw(b.h_img[L - 1], W / 8, b.dout_img, NO / 8, GP(g->out_k), D, W, D, Rp, gs, sw, st));
+  RC(bfk_pack_kmajor(w->out_k, D, W, D, NO, NTW, P16, b.wo_b, st));
+  RC(bfk_gemm(b.dout_img, b.wo_b, b.dH, W, B, W, NO, NTW, 1, 0, nullptr, 1.f, P16, st));
+  const bool want_dte = T > 1;
+  for (int l = L - 1; l >= 0; --l) {
+    BlockBwdArgs a{};
+    a.dH = b.dH; a.xhat = b.xhat[l]; a.rstd = b.rstd[l]; a.P = b.P[l];
+    a.gamma = c->norm == BFK_NORM_LAYER ? w->norm_g[l] : nullptr;
+    a.dP_img = b.dP_img; a.dV_img = b.dV_img;
+    a.d_gamma = GP(g->norm_g[l]); a.d_beta = GP(g->norm_b[l]); a.d_bd = GP(g->dense_b[l]); a.d_bfilm = GP(g->film_b_b[l]);
+    a.B = B; a.R_pad = Rp; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
+    a.drop_rate = ta->dropout; a.inv_keep = inv_keep; a.seed = ta->seed; a.gscale = gs;
+    RC(launch_block_bwd(a, st));
+    RC(launch_gemm_dw(l == 0 ? b.h0_img : b.h_img[l - 1], W / 8, b.dP_img, W / 8, GP(g->dense_k[l]), W, W, W, Rp, gs, sw, st));
+    RC(launch_gemm_dw(b.te_img, KT / 8, b.dV_img, W / 8, GP(g->film_b_k[l]), W, T, W, Rp, gs, sw, st));
+    if (want_dte) {
+      RC(bfk_pack_kmajor(w->film_b_k[l], W, T, W, W, 64, P16, b.wb_b[l], st));
+      RC(bfk_gemm(b.dV_img, b.wb_b[l], b.dte, KTN, B, KTN, W, 64, 1, l == L - 1 ? 0 : GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
+    }
+    if (!c->residual) CK(cudaMemsetAsync(b.dH, 0, (size_t)B * W * 4, st));
+    RC(bfk_pack_kmajor(w->dense_k[l], W, W, W, W, NTW, P16, b.wd_b[l], st));
+    RC(bfk_gemm(b.dP_img, b.wd_b[l], b.dH, W, B, W, W, NTW, 1, GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
+  }
+  CK(cudaMemsetAsync(b.db1, 0, (size_t)N1 * 4, st));
+  if (b.has_merge) {
+    act_bwd_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.dH, b.m, W, B, n_tiles, W / 8, act, b.dP_img, GP(g->m_b), gs);
+    RC(launch_gemm_dw(b.a1_img, N1 / 8, b.dP_img, W / 8, GP(g->m_k), W, N1, W, Rp, gs, sw, st));
+    RC(bfk_pack_kmajor(w->m_k, W, N1, W, W, NT1, P16, b.wm_b, st));
+    RC(bfk_gemm(b.dP_img, b.wm_b, b.da1, N1, B, N1, W, NT1, 1, 0, nullptr, 1.f, P16, st));
+    act_bwd_kernel<<<dim3(N1 / 8, tchunks), 128, 0, st>>>(b.da1, b.h0pre, N1, B, n_tiles, N1 / 8, act, b.dh0pre_img, b.db1, 1.f);
+  } else {
+    act_bwd_kernel<<<dim3(N1 / 8, tchunks), 128, 0, st>>>(b.dH, b.h0pre, N1, B, n_tiles, N1 / 8, act, b.dh0pre_img, b.db1, 1.f);
+  }
+  CK(cudaGetLastError());
+  CK(cudaMemsetAsync(b.dW1, 0, (size_t)KU * N1 * 4, st));
+  RC(launch_gemm_dw(b.u_img, KU / 8, b.dh0pre_img, N1 / 8, b.dW1, N1, D + C, N1, Rp, 1.f, sw, st));
+  scatter_w1_grad_kernel<<<cdiv((size_t)(D + C) * W, 256), 256, 0, st>>>(b.dW1, b.db1, D, C, W, b.has_merge ? c->merge : 0, N1, gs,
+                                                                        GP(g->x_k), GP(g->x_b), GP(g->c_k), GP(g->c_b));
+  if (want_dte && GP(g->freq))
+    freq_bwd_kernel<<<(unsigned)((B + 255) / 256), 256, 0, st>>>(b.dte, KTN, ta->t, w->freq, c->fourier_scale, B, (T - 1) / 2, GP(g->freq), gs);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_fm_interpolate(const float* x0, const float* x1, const float* t, int64_t B, int32_t D, float* x,
+                                  float* target, void* stream_) {
+  if (!x0 || !x1 || !t || !x || !target || B <= 0 || D <= 0) return fail(-80, "bfk_fm_interpolate: bad arguments");
+  fm_interp_kernel<<<cdiv((size_t)B * D, 256), 256, 0, (cudaStream_t)stream_>>>(x0, x1, t, B, D, x, target);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_adam_step(float* params, const float* grads, float* m, float* v, const int64_t* seg_offsets, int32_t n_seg,
+                             float* seg_sqnorm, float clipnorm, float lr_t, float beta1, float beta2, float eps, float wd_lr,
+                             void* stream_) {
+  if (!params || !grads || !m || !v || !seg_offsets || n_seg <= 0 || !seg_sqnorm) return fail(-81, "bfk_adam_step: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream_;
+  static_assert(sizeof(long long) == sizeof(int64_t), "");
+  if (clipnorm > 0.f) {
+    CK(cudaMemsetAsync(seg_sqnorm, 0, (size_t)n_seg * 4, st));
+    seg_sqnorm_kernel<<<dim3(n_seg, 16), 256, 0, st>>>(grads, (const long long*)seg_offsets, n_seg, seg_sqnorm);
+  }
+  adam_kernel<<<dim3(n_seg, 16), 256, 0, st>>>(params, grads, m, v, (const long long*)seg_offsets, seg_sqnorm, clipnorm, lr_t, beta1,
+                                              beta2, eps, wd_lr);
+  CK(cudaGetLastError());
+  return 0;
+}

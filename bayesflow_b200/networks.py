@@ -574,6 +574,44 @@ class FlowMatching(InferenceNetwork):
         run = self._run(conditions, xz.shape[0], kwargs)
         return run.velocity(xz, float(np.float32(time)))
 
+    # -- training (flow_matching.py:132-178) ------------------------------------------------------------------------------
+    def _loss_and_grads(self, x, conditions=None, sample_weight=None, stage="training", seed=None, world=1, backward=True):
+        from .training import train_engine
+        if self.drop_cond_prob > 0 or self.drop_target_prob > 0:
+            raise NotImplementedError("drop_cond_prob / drop_target_prob > 0 are outside the accelerated training path")
+        if (conditions is None) != (self._C is None):
+            raise ValueError("network was built " + ("without" if self._C is None else "with") + " conditions")
+        eng = train_engine(self)
+        if isinstance(x, Sequence) and not torch.is_tensor(x):
+            x0, x1, t, x, target = x  # bypasses all RNG (flow_matching.py:140-141)
+        else:
+            x1 = x
+            if not x1.is_cuda:
+                raise RuntimeError("bayesflow_b200 runs on CUDA tensors only (no CPU fallback)")
+            x0 = self.base_distribution.sample(tuple(x1.shape[:-1]))
+            u = torch.rand((x0.shape[0],), device=x1.device)
+            t = u ** (1 + self.time_power_law_alpha)
+            x, target = eng.interpolate(x0, x1, t)
+        training = stage == "training"
+        rate = float(self.subnet.dropout or 0.0) if training else 0.0
+        if seed is None:
+            self._drop_calls = getattr(self, "_drop_calls", 0) + 1
+            seed = (torch.initial_seed() * 0x9E3779B1 + self._drop_calls) & (2 ** 63 - 1)
+        loss, _ = eng.step(x, t, conditions, target, row_weight=sample_weight, loss=self.loss_fn, dropout=rate, seed=seed,
+                           global_batch=x.shape[0] * world, backward=backward)
+        return loss
+
+    def compute_metrics(self, x, conditions=None, sample_weight=None, stage="training", **kwargs):
+        """{"loss": 0-d tensor}.  With grad mode on and stage == "training" the kernels also produce every parameter
+        gradient; ``loss.backward()`` then fills ``p.grad`` exactly like the reference's autograd path."""
+        from .training import _LossWithGrads, train_engine
+        backward = torch.is_grad_enabled() and stage == "training"
+        loss = self._loss_and_grads(x, conditions, sample_weight, stage=stage, seed=kwargs.get("seed"), backward=backward)
+        if backward:
+            eng = train_engine(self)
+            loss = _LossWithGrads.apply(loss, eng, *eng.params)
+        return {"loss": loss}
+
     def _forward(self, x, conditions=None, density=False, training=False, **kwargs):
         # flow_matching.py:254-294
         integrate_kwargs = self.integrate_kwargs | kwargs

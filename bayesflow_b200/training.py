@@ -1,0 +1,272 @@
+"""Training side of the hot path: forward + loss + backward of the velocity network on the layer-wise tcgen05 path
+(``bfk_train_step``), the optimizer (``bfk_adam_step``) and the data-parallel gradient exchange.
+
+  TrainEngine.loss_and_grads  <- FlowMatching.compute_metrics + autograd backward
+                                 flow_matching.py:132-178, torch_approximator.py:88-99
+  Adam                        <- keras.optimizers.Adam(lr, clipnorm=1.5) / AdamW as BasicWorkflow builds them
+                                 workflows/basic_workflow.py:514-526
+  Trainer.train_step          <- TorchApproximator.train_step (zero_grad, compute_metrics, backward, optimizer step)
+                                 approximators/backend_approximators/torch_approximator.py:62-113
+
+Parameters live in ONE flat fp32 buffer (the nn.Parameters are views into it) and so do the gradients: the
+data-parallel exchange is a single NCCL all-reduce and the optimizer a single kernel over all variables.
+No CPU or eager fallback: everything below raises unless libbfk.so is loaded and the tensors are CUDA tensors.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import torch
+
+from . import _lib
+
+
+class TrainArgs(C.Structure):
+    _fields_ = [("x", C.c_void_p), ("t", C.c_void_p), ("cond", C.c_void_p), ("target", C.c_void_p),
+                ("pred_scale", C.c_void_p), ("row_weight", C.c_void_p), ("B", C.c_int64), ("loss", C.c_int32),
+                ("dw_swap", C.c_int32), ("dropout", C.c_float), ("loss_scale", C.c_float), ("grad_scale", C.c_float),
+                ("seed", C.c_uint64)]
+
+
+def _bind(L):
+    if getattr(L, "_train_bound", False):
+        return L
+    L.bfk_train_workspace_bytes.restype = C.c_size_t
+    L.bfk_train_workspace_bytes.argtypes = [C.POINTER(_lib.NetConfig), C.c_int64, C.c_int32]
+    L.bfk_train_step.argtypes = [C.POINTER(_lib.NetConfig), C.POINTER(_lib.Weights), C.POINTER(_lib.Weights),
+                                 C.POINTER(TrainArgs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    L.bfk_fm_interpolate.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
+                                     C.c_void_p]
+    L.bfk_adam_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
+                                C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p]
+    L._train_bound = True
+    return L
+
+
+def fill_weights(net, get):
+    """bfk_weights struct whose pointers are ``get(parameter)`` (the parameter itself or its gradient view)."""
+    sub, w, keep = net.subnet, _lib.Weights(), []
+
+    def P(p):
+        t = get(p)
+        if t.dtype != torch.float32 or not t.is_contiguous() or not t.is_cuda:
+            raise RuntimeError("training needs contiguous fp32 CUDA parameters (no CPU fallback)")
+        keep.append(t)
+        return t.data_ptr()
+
+    if sub.time_embedding_dim > 1:
+        w.freq = P(sub.time_emb.frequencies)
+    w.x_k, w.x_b = P(sub.x_proj.kernel), P(sub.x_proj.bias)
+    if net._C:
+        w.c_k, w.c_b = P(sub.c_proj.kernel), P(sub.c_proj.bias)
+        w.m_k, w.m_b = P(sub.merge_proj.kernel), P(sub.merge_proj.bias)
+    for i, b in enumerate(sub.blocks):
+        w.dense_k[i], w.dense_b[i] = P(b.dense.kernel), P(b.dense.bias)
+        w.film_b_k[i], w.film_b_b[i] = P(b.film.to_beta.kernel), P(b.film.to_beta.bias)
+        if sub.norm == "layer":
+            w.norm_g[i], w.norm_b[i] = P(b.norm.gamma), P(b.norm.beta)
+    w.out_k, w.out_b = P(net.output_projector.kernel), P(net.output_projector.bias)
+    return w, keep
+
+
+class TrainEngine:
+    """Flat parameter / gradient storage + the C-ABI training step for one built inference network."""
+
+    def __init__(self, net):
+        if not net.built:
+            raise RuntimeError("build the network before training it")
+        params = list(net.parameters())
+        dev = params[0].device
+        if dev.type != "cuda":
+            raise RuntimeError("bayesflow_b200: move the network to a CUDA device first (no CPU fallback)")
+        self.net, self.params, self.device = net, params, dev
+        self.L = _bind(_lib.lib())
+        sizes = [p.numel() for p in params]
+        offs = [0]
+        for n in sizes:
+            offs.append(offs[-1] + n)
+        self.flat = torch.empty(offs[-1], device=dev, dtype=torch.float32)
+        self.grad = torch.zeros_like(self.flat)
+        self._gviews = {}
+        for p, a, b in zip(params, offs[:-1], offs[1:]):
+            self.flat[a:b].copy_(p.data.reshape(-1).to(torch.float32))
+            p.data = self.flat[a:b].view(p.shape)
+            self._gviews[p] = self.grad[a:b].view(p.shape)
+        self.seg_offsets = torch.tensor(offs, device=dev, dtype=torch.int64)
+        self.offsets = offs[:-1]
+        self.n_seg = len(sizes)
+        self.cfg = net._engine._make_cfg()
+        if net.precision != "fp16":
+            raise NotImplementedError("the training path uses fp16 operands (bf16 cannot meet the 2e-3 gradient tolerance)")
+        self.w, self._keep_w = fill_weights(net, lambda p: p.data)
+        self.g, self._keep_g = fill_weights(net, lambda p: self._gviews[p])
+        self._ws, self._ws_key = None, None
+        self.launches = 0
+
+    def grad_of(self, p):
+        return self._gviews[p]
+
+    def _workspace(self, B, backward):
+        key = (int(B), bool(backward))
+        if self._ws is None or self._ws_key != key:
+            n = self.L.bfk_train_workspace_bytes(C.byref(self.cfg), int(B), int(backward))
+            if n == 0:
+                raise NotImplementedError("bfk_train_workspace_bytes: " + self.L.bfk_last_error_string().decode())
+            if self._ws is None or self._ws.numel() < n:
+                self._ws = torch.empty(n, device=self.device, dtype=torch.uint8)
+            self._ws_key = key
+        return self._ws
+
+    @staticmethod
+    def _f32(t, shape=None):
+        if t is None:
+            return None
+        if not t.is_cuda:
+            raise RuntimeError("bayesflow_b200 runs on CUDA tensors only (no CPU fallback)")
+        t = t.detach().to(torch.float32).contiguous()
+        if shape is not None and tuple(t.shape) != tuple(shape):
+            raise ValueError(f"expected shape {tuple(shape)}, got {tuple(t.shape)}")
+        return t
+
+    def step(self, x, t, conditions, target, *, pred_scale=None, row_weight=None, loss="mse", dropout=0.0, seed=0,
+             global_batch=None, backward=True, zero_grad=True, want_pred=False, want_loss=True, _dw_swap=0):
+        """One forward (+ loss, + backward).  Gradients are accumulated into ``self.grad`` (zeroed first unless
+        ``zero_grad=False``) scaled by 1/(global_batch*D).  Returns (loss 0-d device tensor or None, pred or None)."""
+        net = self.net
+        D = net._D
+        x = self._f32(x)
+        B = x.shape[0]
+        if x.ndim != 2 or x.shape[1] != D:
+            raise ValueError(f"expected (rows, {D}) inputs, got {tuple(x.shape)}")
+        t = self._f32(t).reshape(-1)
+        if t.numel() != B:
+            raise ValueError("time must have one entry per row")
+        cond = self._f32(conditions, (B, net._C)) if net._C else None
+        if net._C and cond is None:
+            raise ValueError("network was built with conditions")
+        target = self._f32(target, (B, D)) if target is not None else None
+        pred_scale = self._f32(pred_scale, (B,)) if pred_scale is not None else None
+        row_weight = self._f32(row_weight.reshape(-1), (B,)) if row_weight is not None else None
+        gb = int(global_batch or B)
+        a = TrainArgs()
+        a.x, a.t, a.cond, a.target = x.data_ptr(), t.data_ptr(), (cond.data_ptr() if cond is not None else None), \
+            (target.data_ptr() if target is not None else None)
+        a.pred_scale = pred_scale.data_ptr() if pred_scale is not None else None
+        a.row_weight = row_weight.data_ptr() if row_weight is not None else None
+        a.B, a.loss, a.dw_swap = B, {"mse": 0, "mae": 1}[loss], int(_dw_swap)
+        a.dropout, a.seed = float(dropout), int(seed) & (2 ** 64 - 1)
+        a.loss_scale, a.grad_scale = 1.0 / (gb * (D if loss in ("mse", "mae") else 1)), 1.0 / (gb * D)
+        ws = self._workspace(B, backward)
+        if backward and zero_grad:
+            self.grad.zero_()
+        loss_t = torch.zeros((), device=self.device, dtype=torch.float32) if want_loss else None
+        pred = torch.empty(B, D, device=self.device, dtype=torch.float32) if want_pred else None
+        rc = self.L.bfk_train_step(C.byref(self.cfg), C.byref(self.w), C.byref(self.g) if backward else None, C.byref(a),
+                                   _lib.ptr(loss_t), _lib.ptr(pred), _lib.ptr(ws), ws.numel(), _lib.stream_ptr())
+        _lib.check(rc, "bfk_train_step")
+        self.launches += self.launches_per_step(backward)
+        return loss_t, pred
+
+    def launches_per_step(self, backward=True):
+        """Kernels bfk_train_step enqueues (counted from csrc/bfk_train_host.cuh)."""
+        Lb, merge = self.cfg.L, 1 if self.net._C else 0
+        fwd = 2 + 2 + (4 if merge else 1) + 5 * Lb + 2 + 1
+        if not backward:
+            return fwd
+        bwd = 3 + Lb * 7 + (5 if merge else 1) + 3
+        return fwd + bwd
+
+    def interpolate(self, x0, x1, t):
+        x0, x1, t = self._f32(x0), self._f32(x1), self._f32(t).reshape(-1)
+        x, target = torch.empty_like(x1), torch.empty_like(x1)
+        _lib.check(self.L.bfk_fm_interpolate(_lib.ptr(x0), _lib.ptr(x1), _lib.ptr(t), x1.shape[0], x1.shape[1], _lib.ptr(x),
+                                             _lib.ptr(target), _lib.stream_ptr()), "bfk_fm_interpolate")
+        self.launches += 1
+        return x, target
+
+
+class _LossWithGrads(torch.autograd.Function):
+    """Makes ``compute_metrics(...)["loss"].backward()`` work like the reference's torch path: the kernels already
+    produced every parameter gradient; backward() hands them to autograd."""
+
+    @staticmethod
+    def forward(ctx, loss, eng, *params):
+        ctx.eng = eng
+        ctx.n = len(params)
+        return loss.clone()
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        eng = ctx.eng
+        return (None, None) + tuple(eng.grad_of(p) * grad_out for p in eng.params)
+
+
+def train_engine(net) -> TrainEngine:
+    eng = getattr(net, "_train_engine", None)
+    if eng is None or any(p.data_ptr() != eng.flat.data_ptr() + 4 * a for p, a in zip(eng.params, eng.offsets)):
+        eng = TrainEngine(net)
+        object.__setattr__(net, "_train_engine", eng)
+    return eng
+
+
+class Adam:
+    """keras.optimizers.Adam / AdamW semantics (Keras 3 `adam.py`: m += (g-m)(1-b1); v += (g^2-v)(1-b2);
+    p -= lr*sqrt(1-b2^t)/(1-b1^t) * m/(sqrt(v)+eps)); `clipnorm` clips every variable's gradient separately, as Keras
+    does; `learning_rate` may be a float or a callable of the (0-based) step (e.g. cosine_decay)."""
+
+    def __init__(self, net, learning_rate=5e-4, beta_1=0.9, beta_2=0.999, epsilon=1e-7, clipnorm=None, weight_decay=0.0):
+        self.eng = train_engine(net)
+        self.learning_rate, self.beta_1, self.beta_2, self.epsilon = learning_rate, beta_1, beta_2, epsilon
+        self.clipnorm, self.weight_decay = clipnorm, weight_decay
+        self.m = torch.zeros_like(self.eng.flat)
+        self.v = torch.zeros_like(self.eng.flat)
+        self._sq = torch.zeros(self.eng.n_seg, device=self.eng.device, dtype=torch.float32)
+        self.iterations = 0
+
+    def step(self):
+        e = self.eng
+        t = self.iterations + 1
+        lr = self.learning_rate(self.iterations) if callable(self.learning_rate) else self.learning_rate
+        lr_t = lr * math.sqrt(1.0 - self.beta_2 ** t) / (1.0 - self.beta_1 ** t)
+        _lib.check(e.L.bfk_adam_step(_lib.ptr(e.flat), _lib.ptr(e.grad), _lib.ptr(self.m), _lib.ptr(self.v),
+                                     C.c_void_p(e.seg_offsets.data_ptr()), e.n_seg, _lib.ptr(self._sq),
+                                     float(self.clipnorm or 0.0), lr_t, self.beta_1, self.beta_2, self.epsilon,
+                                     float(self.weight_decay) * lr, _lib.stream_ptr()), "bfk_adam_step")
+        e.launches += 2 if self.clipnorm else 1
+        self.iterations = t
+        e.net._engine._key = None  # the kernel wrote the parameters in place: the sampler must re-pack its weight blob
+
+
+def cosine_decay(initial_learning_rate, decay_steps, alpha=0.0):
+    """keras.optimizers.schedules.CosineDecay without warmup (basic_workflow.py:514-520)."""
+    def lr(step):
+        s = min(step, decay_steps)
+        return initial_learning_rate * ((1 - alpha) * 0.5 * (1 + math.cos(math.pi * s / decay_steps)) + alpha)
+    return lr
+
+
+class Trainer:
+    """TorchApproximator.train_step for the accelerated network (torch_approximator.py:62-113): zero grads,
+    compute_metrics, backward, (all-reduce), optimizer step - without autograd in the loop."""
+
+    def __init__(self, net, optimizer=None, process_group=None, world_size=None):
+        self.net, self.eng = net, train_engine(net)
+        self.opt = optimizer or Adam(net, 5e-4, clipnorm=1.5)
+        self.group = process_group
+        if world_size is None:
+            world_size = torch.distributed.get_world_size(process_group) if torch.distributed.is_initialized() else 1
+        self.world = world_size
+
+    def train_step(self, x, conditions=None, sample_weight=None, seed=None):
+        """x: this rank's shard of the batch (or the (x0, x1, t, x, target) tuple).  Returns the GLOBAL mean loss as a
+        0-d device tensor (after the all-reduce when world_size > 1)."""
+        net, eng = self.net, self.eng
+        loss = net._loss_and_grads(x, conditions, sample_weight, stage="training", seed=seed, world=self.world)
+        if self.world > 1:
+            # ONE bucket: gradients and the loss ride the same all-reduce (SUM); scaling by 1/B_global happened on device
+            buf = eng.grad
+            torch.distributed.all_reduce(buf, op=torch.distributed.ReduceOp.SUM, group=self.group)
+            torch.distributed.all_reduce(loss, op=torch.distributed.ReduceOp.SUM, group=self.group)
+        self.opt.step()
+        return loss

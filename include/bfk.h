@@ -159,6 +159,39 @@ int bfk_gemm(const void* A_packed, const void* B_packed, float* C, int64_t ldc, 
              int32_t NT, int32_t k_splits, int32_t flags, const float* bias, float alpha, int32_t precision,
              void* stream);
 
+/* ---- training step (FlowMatching.compute_metrics flow_matching.py:132-178, DiffusionModel.compute_metrics
+ * diffusion_model.py:142-232; gradients = what torch autograd returns in torch_approximator.py:88-99) ----------------
+ * The network sees x (B,D), the per-row subnet time t (B) and conditions (B,C).  The loss head is
+ *     loss = loss_scale * sum_b w_b * mean_i L(a_b * pred_bi - target_bi),  L = square (0) or abs (1)
+ * which covers FlowMatching (a = 1, target = x1 - x0) and every DiffusionModel prediction/loss type (a_b, target from
+ * the noise schedule).  Gradients are ADDED to the tensors in `grads` (same struct as the weights; zero them first),
+ * already multiplied by grad_scale (= 1/(B_global*D) for the reference's mean).  grads == NULL: forward (+ loss) only.
+ * pred_out (B,D) optional.  dropout: rate of the blocks' Dropout layers (conditional_dense_block.py:120-121), mask
+ * derived from seed.  Operands are fp16 with fp32 accumulation. */
+typedef struct bfk_train_args {
+  const float* x; const float* t; const float* cond; const float* target;
+  const float* pred_scale; /* (B) or NULL */
+  const float* row_weight; /* (B) or NULL */
+  int64_t B;
+  int32_t loss;            /* 0 mse, 1 mae */
+  int32_t dw_swap;         /* debug: swap LBO/SBO of the MN-major descriptors; must be 0 */
+  float dropout;
+  float loss_scale, grad_scale;
+  uint64_t seed;
+} bfk_train_args;
+size_t bfk_train_workspace_bytes(const bfk_net_config* cfg, int64_t B, int32_t backward);
+int bfk_train_step(const bfk_net_config* cfg, const bfk_weights* weights, const bfk_weights* grads,
+                   const bfk_train_args* args, float* loss, float* pred_out, void* workspace, size_t workspace_bytes,
+                   void* stream);
+/* x = t*x1 + (1-t)*x0, target = x1 - x0 (flow_matching.py:159-168) */
+int bfk_fm_interpolate(const float* x0, const float* x1, const float* t, int64_t B, int32_t D, float* x, float* target,
+                       void* stream);
+/* keras.optimizers.Adam / AdamW with per-variable clipnorm (basic_workflow.py:514-526) over one flat parameter buffer;
+ * seg_offsets (n_seg+1, device int64) delimit the variables, seg_sqnorm (n_seg) is scratch.  lr_t = lr*sqrt(1-b2^t)/(1-b1^t). */
+int bfk_adam_step(float* params, const float* grads, float* m, float* v, const int64_t* seg_offsets, int32_t n_seg,
+                  float* seg_sqnorm, float clipnorm, float lr_t, float beta1, float beta2, float eps, float wd_lr,
+                  void* stream);
+
 /* ---- introspection ------------------------------------------------------------------------------------------- */
 int bfk_num_sms(void);
 int bfk_fused_supported(const bfk_net_config* cfg); /* 1 if the on-chip sampler handles this config */
