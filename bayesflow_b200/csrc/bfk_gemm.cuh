@@ -89,43 +89,61 @@ __global__ void __launch_bounds__(G_THREADS, 2) gemm_kernel(const GemmArgs a) {
     }
     __syncwarp();
   } else {
-    // epilogue: thread == row
-    const long long row = (long long)m_tile * G_TM + warp * 32 + lane;
+    // epilogue.  TMEM hands each thread one ROW; written straight to global that is 32 rows x 16 B per store
+    // instruction (32 half-used sectors).  So 64-column panels are transposed through the (now idle) ring: thread == row
+    // on the way in, 16 lanes x float4 == 256 contiguous bytes of one row on the way out.
     const uint32_t t_acc = tmem_base + ((uint32_t)(warp * 32) << 16);
     if (n_slabs > 0) {
       mbar_wait(bar0 + 64, 0, nullptr, 0);
       tc_fence_after();
     }
-    const bool valid = row < a.M;
-    float* crow = a.C + row * a.ldc + (size_t)n_tile * NT;
+    float* stg = reinterpret_cast<float*>(smem) + warp * (32 * 68);
+    const long long row0 = (long long)m_tile * G_TM + warp * 32;
+    const int sub = lane >> 4, c4 = (lane & 15) * 4;
     const float* bias = (a.bias && split == 0) ? a.bias + (size_t)n_tile * NT : nullptr;
-    for (int c = 0; c < NT / 32; ++c) {
-      float v[32];
-      if (n_slabs > 0) {
-        tmem_ld32(t_acc + c * 32, v);
-        tmem_ld_wait32(v);
-      } else {
+    for (int p = 0; p < NT / 64; ++p) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = 0.f;
-      }
-      if (!valid) continue;
-#pragma unroll
-      for (int i = 0; i < 32; i += 4) {
-        float4 o = make_float4(v[i] * a.alpha, v[i + 1] * a.alpha, v[i + 2] * a.alpha, v[i + 3] * a.alpha);
-        if (bias) {
-          const float4 b = *reinterpret_cast<const float4*>(bias + c * 32 + i);
-          o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
-        }
-        float4* dst = reinterpret_cast<float4*>(crow + c * 32 + i);
-        if (a.flags & GEMM_ATOMIC) {
-          atomicAdd(dst, o);
-        } else if (a.flags & GEMM_ADD_EXISTING) {
-          const float4 e = *dst;
-          *dst = make_float4(e.x + o.x, e.y + o.y, e.z + o.z, e.w + o.w);
+      for (int h = 0; h < 2; ++h) {
+        float v[32];
+        if (n_slabs > 0) {
+          tmem_ld32(t_acc + p * 64 + h * 32, v);
+          tmem_ld_wait32(v);
         } else {
-          *dst = o;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = 0.f;
         }
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) *reinterpret_cast<float4*>(stg + lane * 68 + h * 32 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
       }
+      __syncwarp();
+      float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (bias) b4 = *reinterpret_cast<const float4*>(bias + p * 64 + c4);
+      float4* dst[16];
+      float4 o[16];
+#pragma unroll
+      for (int it = 0; it < 16; ++it) {
+        const int rr = it * 2 + sub;
+        dst[it] = reinterpret_cast<float4*>(a.C + (row0 + rr) * a.ldc + (size_t)n_tile * NT + p * 64 + c4);
+        const float4 t = *reinterpret_cast<const float4*>(stg + rr * 68 + c4);
+        o[it] = make_float4(fmaf(t.x, a.alpha, b4.x), fmaf(t.y, a.alpha, b4.y), fmaf(t.z, a.alpha, b4.z), fmaf(t.w, a.alpha, b4.w));
+      }
+      if (a.flags & GEMM_ATOMIC) {
+#pragma unroll
+        for (int it = 0; it < 16; ++it)
+          if (row0 + it * 2 + sub < a.M) atomicAdd(dst[it], o[it]);
+      } else {
+        if (a.flags & GEMM_ADD_EXISTING) {  // all 16 loads of the existing tile in flight before the first add
+          float4 e[16];
+#pragma unroll
+          for (int it = 0; it < 16; ++it) e[it] = (row0 + it * 2 + sub < a.M) ? *dst[it] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int it = 0; it < 16; ++it) { o[it].x += e[it].x; o[it].y += e[it].y; o[it].z += e[it].z; o[it].w += e[it].w; }
+        }
+#pragma unroll
+        for (int it = 0; it < 16; ++it)
+          if (row0 + it * 2 + sub < a.M) *dst[it] = o[it];
+      }
+      __syncwarp();
     }
     tc_fence_before();
   }

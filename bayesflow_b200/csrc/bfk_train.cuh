@@ -18,19 +18,23 @@ namespace bfk {
 
 constexpr float LN_EPS = 1e-3f;  // keras.layers.LayerNormalization default epsilon
 
-// value and derivative of the Keras activation (time_mlp.py:106-109), fp32, full-range libm functions
+// value and derivative of the Keras activation (time_mlp.py:106-109), fp32
 __device__ __forceinline__ float t_act(int act, float x, float& d) {
   switch (act) {
     case BFK_ACT_MISH: {
-      const float sp = x > 20.f ? x : log1pf(expf(x));
-      const float t = tanhf(sp);
-      const float sg = 1.f / (1.f + expf(-x));
-      d = t + x * (1.f - t * t) * sg;
+      // x*tanh(softplus(x)) with tanh(ln(1+e)) = w/(w+2), w = e*(e+2), e = exp(x): one ex2 + two rcp (fp32 accurate to a
+      // few ulp; libm tanhf/log1pf made the block kernels issue-bound)
+      if (x > 15.f) { d = 1.f; return x; }
+      const float e = __expf(x);
+      const float w = e * (e + 2.f);
+      const float t = __fdividef(w, w + 2.f);
+      const float sg = __fdividef(e, 1.f + e);
+      d = fmaf(x * (1.f - t * t), sg, t);
       return x * t;
     }
     case BFK_ACT_SILU: {
-      const float sg = 1.f / (1.f + expf(-x));
-      d = sg * (1.f + x * (1.f - sg));
+      const float sg = __fdividef(1.f, 1.f + __expf(-x));
+      d = sg * fmaf(x, 1.f - sg, 1.f);
       return x * sg;
     }
     case BFK_ACT_RELU:
@@ -38,7 +42,7 @@ __device__ __forceinline__ float t_act(int act, float x, float& d) {
       return x > 0.f ? x : 0.f;
     case BFK_ACT_GELU: {
       const float cdf = 0.5f * (1.f + erff(x * 0.70710678118654752f));
-      d = cdf + x * 0.3989422804014327f * expf(-0.5f * x * x);
+      d = cdf + x * 0.3989422804014327f * __expf(-0.5f * x * x);
       return x * cdf;
     }
     default: {  // tanh
@@ -51,11 +55,12 @@ __device__ __forceinline__ float t_act(int act, float x, float& d) {
 
 // counter-based keep mask for Dropout (conditional_dense_block.py:120-121): identical in forward and backward
 __device__ __forceinline__ float drop_scale(unsigned long long seed, int layer, long long row, int col, float rate, float inv_keep) {
-  unsigned long long z = seed + 0x9E3779B97F4A7C15ull * (unsigned long long)(row * 4096 + col + 1) + ((unsigned long long)layer << 56);
-  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-  z ^= z >> 31;
-  const float u = (float)(unsigned)(z >> 40) * (1.f / 16777216.f);
+  uint32_t h = (uint32_t)(row * 1024 + col) ^ (uint32_t)seed;
+  h *= 0x9E3779B1u; h ^= h >> 15;
+  h *= 0x85EBCA77u; h ^= h >> 13;
+  h += (uint32_t)(seed >> 32) + (uint32_t)layer * 0xC2B2AE3Du;
+  h *= 0x27D4EB2Fu; h ^= h >> 16;
+  const float u = (float)(h >> 8) * (1.f / 16777216.f);
   return u >= rate ? inv_keep : 0.f;
 }
 

@@ -30,6 +30,11 @@ WORKLOADS = {
     "cfg3_lv_dm_euler100": dict(model="dm", D=4, C=20, widths=(256,) * 5, N=1000, S=4000, method="euler", ode_steps=100),
     "cfg3_lv_dm_rk45x100": dict(model="dm", D=4, C=20, widths=(256,) * 5, N=1000, S=4000, method="rk45", ode_steps=100),
 }
+# training workloads (BASELINE.json configs[4]): GLOBAL batch, split evenly over the ranks (strong scaling)
+TRAIN_WORKLOADS = {
+    "cfg5_fm_train": dict(model="fm", D=2, C=32, widths=(256,) * 5, batch=65536, dropout=0.05),
+    "cfg5_fm_train_wide": dict(model="fm", D=64, C=32, widths=(1024,) * 8, batch=65536, dropout=0.05),
+}
 DEFAULT_WORKLOAD = "cfg2_sir_fm_euler100"
 EVALS_PER_STEP = {"euler": 1, "rk45": 6, "tsit5": 6}
 
@@ -284,6 +289,15 @@ def run_ours(args, name, w):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = run_cpu_baseline(w, state_cpu)
+    train = None
+    if not args.no_train:
+        # second half of BASELINE.json's metric: FlowMatching train samples/sec (configs[4]), same run, same ranks
+        del flush
+        torch.cuda.empty_cache()
+        tw = TRAIN_WORKLOADS["cfg5_fm_train"]
+        train = measure_training(tw, dev, world, rank, max(args.steps, 5), 3, False)
+        train["config"] = train_config("cfg5_fm_train", tw, world)
+        train["metric"] = "FlowMatching train samples/sec"
     if rank == 0:
         line = {"metric": "posterior draws/sec", "value": value, "unit": "draws/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -299,7 +313,167 @@ def run_ours(args, name, w):
                              "flop_per_draw_naive": fpd, "peak_source": peaks["source"],
                              "hbm_gbs_algorithmic": (N * S * D * 8) / (k_avg_ms * 1e-3) / 1e9 if kern_ms else None},
                 "cpu_baseline": cpu,
-                "integration": info, "wall_s_timed_region": wall}
+                "integration": info, "wall_s_timed_region": wall, "train": train}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# --------------------------------------------------------------------------------------------------- training arms
+def train_config(name, w, world):
+    return {"workload": name, "network": "FlowMatching", "subnet": f"time_mlp widths={w['widths'][0]}x{len(w['widths'])}",
+            "D": w["D"], "C": w["C"], "global_batch": w["batch"], "per_gpu_batch": w["batch"] // world,
+            "dropout": w["dropout"], "step": "compute_metrics (x0~N, t~U on device) + backward + gradient all-reduce + "
+            "Adam(clipnorm=1.5)", "parallelism": f"dp{world}",
+            "l2": "activations of one step (>1 GB) exceed L2; 256 MB L2 flush between steps"}
+
+
+def train_flops_per_sample(w):
+    return 3 * count_flops_per_eval(w["D"], w["C"], w["widths"])  # forward + dX + dW, naive count
+
+
+def cpu_train_rate(w, n_rows, threads, steps=1):
+    """samples/s of the reference's CPU training step (oracle port + torch autograd + torch Adam)."""
+    import torch
+    import oracle
+    torch.set_num_threads(threads)
+    params = oracle.init_params(w["D"], w["C"] or None, w["widths"])
+    ps = {k: v.clone().requires_grad_(True) for k, v in params.items()}
+    orc = oracle.OracleFlowMatching(ps, w["D"], subnet_kwargs={"dropout": w["dropout"], "widths": w["widths"]})
+    opt = torch.optim.Adam(list(ps.values()), 5e-4)
+    g = torch.Generator().manual_seed(4567)
+    x, c = torch.randn(n_rows, w["D"], generator=g), torch.randn(n_rows, w["C"], generator=g)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        opt.zero_grad()
+        loss = orc.compute_metrics(x, conditions=c, stage="training")["loss"]
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(list(ps.values()), 1.5)
+        opt.step()
+    dt = time.perf_counter() - t0
+    return steps * n_rows / dt, dt
+
+
+def run_train_reference_arm(args, name, w):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    threads = os.cpu_count() or 1
+    rate, _ = cpu_train_rate(w, 2048, threads)
+    n = int(max(2048, min(w["batch"], 10.0 * rate)) // 1024 * 1024)
+    for _ in range(max(args.warmup - 1, 0)):
+        cpu_train_rate(w, 2048, threads)
+    rate, dt = cpu_train_rate(w, n, threads, steps=args.steps)
+    line = {"impl": "reference", "metric": "FlowMatching train samples/sec", "value": rate, "unit": "samples/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": train_config(name, w, args.gpus),
+            "cpu_baseline": {"value": rate, "unit": "samples/s", "cores": threads, "kind": "port",
+                             "sample": f"each step = one optimizer step on {n} rows (of the 65536-row batch), oracle port + torch "
+                                       "autograd + torch Adam on the host cores"},
+            "e2e": {"value": rate, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def measure_training(w, dev, world, rank, steps, warmup, want_cpu):
+    """-> dict with the training numbers (device-timed, max over ranks)."""
+    import torch
+    import torch.distributed as dist
+    import bayesflow_b200 as bf
+    from bayesflow_b200.training import Adam, Trainer, cosine_decay
+
+    torch.manual_seed(1234)
+    net = bf.FlowMatching(subnet_kwargs={"dropout": w["dropout"], "widths": w["widths"]})
+    net.build((None, w["D"]), (None, w["C"]))
+    net.to(dev)
+    tr = Trainer(net, Adam(net, cosine_decay(5e-4, 10000), clipnorm=1.5), world_size=world)
+    Bl = w["batch"] // world
+    g = torch.Generator().manual_seed(4567 + rank)
+    x_host = torch.randn(Bl, w["D"], generator=g).pin_memory()
+    c_host = torch.randn(Bl, w["C"], generator=g).pin_memory()
+    x_dev, c_dev = x_host.to(dev), c_host.to(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    loss_host = torch.empty((), dtype=torch.float32).pin_memory()
+
+    def step_resident():
+        return tr.train_step(x_dev, c_dev)
+
+    def step_e2e():
+        loss = tr.train_step(x_host.to(dev, non_blocking=True), c_host.to(dev, non_blocking=True))
+        loss_host.copy_(loss, non_blocking=True)
+        return loss
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k, wu):
+        for _ in range(wu):
+            fn()
+        barrier()
+        l0 = tr.eng.launches
+        pairs = []
+        for _ in range(k):
+            flush.fill_(1)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            last = fn()
+            b.record()
+            pairs.append((a, b))
+        barrier()
+        ms = sum(a.elapsed_time(b) for a, b in pairs)
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, tr.eng.launches - l0, float(last)
+
+    ms, launches, loss = timed(step_resident, steps, warmup)
+    e2e_ms, _, _ = timed(step_e2e, steps, max(1, warmup // 2))
+    fps = train_flops_per_sample(w)
+    peaks = measured_peaks()
+    achieved = w["batch"] / world * fps / (ms / steps * 1e-3) / 1e12
+    out = {"value": w["batch"] * steps / (ms * 1e-3), "unit": "samples/s", "ms_per_step": ms / steps,
+           "e2e": {"value": w["batch"] * steps / (e2e_ms * 1e-3), "unit": "samples/s", "ms_per_step": e2e_ms / steps,
+                   "h2d_bytes_per_step": int((x_host.numel() + c_host.numel()) * 4), "d2h_bytes_per_step": 4},
+           "gpu_launches": launches, "loss_last": loss,
+           "roofline": {"bound": "tensor", "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",
+                        "frac": achieved / peaks["tflops"], "traffic": None, "kernel": "whole step (bfk::gemm_kernel + "
+                        "bfk::gemm_dw_kernel + block kernels), per GPU", "flop_per_sample_naive": fps,
+                        "peak_source": peaks["source"]}}
+    if want_cpu:
+        threads = os.cpu_count() or 1
+        rate, dt = cpu_train_rate(w, 8192, threads)
+        out["cpu_baseline"] = {"value": rate, "unit": "samples/s", "cores": threads, "kind": "port",
+                               "sample": f"one optimizer step on 8192 rows ({dt:.1f} s): oracle port + torch autograd + torch Adam"}
+    return out
+
+
+def run_train_ours(args, name, w):
+    import torch
+    import torch.distributed as dist
+    from bayesflow_b200 import _lib
+    world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.lib()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    m = measure_training(w, dev, world, rank, args.steps, args.warmup, rank == 0 and world == 1 and not args.no_cpu_baseline)
+    clk = clocks.stop() if rank == 0 else None
+    if rank == 0:
+        line = {"metric": "FlowMatching train samples/sec", "value": m["value"], "unit": "samples/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": m["ms_per_step"], "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f16 tensor-core operands, f32 accumulate/master weights",
+                "data": "synthetic", "config": train_config(name, w, world), "clocks": clk, "e2e": m["e2e"],
+                "gpu_launches": m["gpu_launches"], "roofline": m["roofline"], "cpu_baseline": m.get("cpu_baseline"),
+                "loss_last": m["loss_last"]}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -310,10 +484,15 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + sorted(TRAIN_WORKLOADS))
+    ap.add_argument("--no-train", action="store_true", help="skip the short training measurement added to the default line")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    if args.workload in TRAIN_WORKLOADS:
+        w = TRAIN_WORKLOADS[args.workload]
+        (run_train_reference_arm if args.impl == "reference" else run_train_ours)(args, args.workload, w)
+        return
     w = WORKLOADS[args.workload]
     if args.impl == "reference":
         run_reference_arm(args, args.workload, w)

@@ -134,3 +134,29 @@ def test_product_never_imports_oracle():
             if f.endswith(".py"):
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(import|from)\s+oracle", src, flags=re.M), f
+
+
+def test_training_workspace_query_and_config_gate():
+    """bfk_train_workspace_bytes is pure host arithmetic: it must size the cfg2 / cfg4 nets and refuse what the
+    layer-wise path does not cover (it never silently falls back)."""
+    from bayesflow_b200.training import _bind
+    L = _bind(_lib.lib())
+    cfg = _lib.NetConfig()
+    cfg.D, cfg.C, cfg.W, cfg.L, cfg.T = 2, 32, 256, 5, 33
+    cfg.activation, cfg.merge, cfg.norm, cfg.residual, cfg.precision = 0, 1, 1, 1, 0
+    fwd = L.bfk_train_workspace_bytes(ctypes.byref(cfg), 65536, 0)
+    both = L.bfk_train_workspace_bytes(ctypes.byref(cfg), 65536, 1)
+    assert 65536 * 256 * 4 * 10 < fwd < both < 4 << 30
+    cfg.D, cfg.W, cfg.L = 64, 1024, 8
+    assert L.bfk_train_workspace_bytes(ctypes.byref(cfg), 65536, 1) > both
+    cfg.W = 250
+    assert L.bfk_train_workspace_bytes(ctypes.byref(cfg), 1024, 1) == 0
+    cfg.W, cfg.precision = 256, 1
+    assert L.bfk_train_workspace_bytes(ctypes.byref(cfg), 1024, 1) == 0 and b"fp16" in L.bfk_last_error_string()
+
+
+def test_cosine_decay_matches_keras_formula():
+    from bayesflow_b200.training import cosine_decay
+    lr = cosine_decay(5e-4, 1000)
+    assert lr(0) == pytest.approx(5e-4) and lr(500) == pytest.approx(2.5e-4) and lr(1000) == pytest.approx(0.0, abs=1e-12)
+    assert lr(2000) == lr(1000)
