@@ -206,6 +206,7 @@ struct BlockFwdArgs {
   long long fb_stride;
   const float* prev;    // (B,W) skip source: previous block's normalised activations (or h0), or null (residual off)
   const float* pg; const float* pb;  // affine of the previous LayerNorm applied to prev (null: prev is used as is)
+  const unsigned char* prev_img;     // inference: skip source = the fp16 operand image itself (may equal img: in place)
   const float* gamma; const float* beta;  // this block's LayerNorm parameters (null with norm none)
   float* xhat;          // (B,W) normalised activations before the affine (saved for backward / next skip), or null
   float* rstd;          // (B) or null
@@ -268,6 +269,15 @@ __global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
           }
 #pragma unroll
           for (int i = 0; i < 8; ++i) v[j][i] += s[i];
+        }
+        if (a.prev_img) {
+          const uint4 raw = *reinterpret_cast<const uint4*>(a.prev_img + img_off(r, o, K8));
+          const __half2* hp = reinterpret_cast<const __half2*>(&raw);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float2 f = __half22float2(hp[i]);
+            v[j][2 * i] += f.x; v[j][2 * i + 1] += f.y;
+          }
         }
 #pragma unroll
         for (int i = 0; i < 8; ++i) sum += v[j][i];
@@ -357,8 +367,13 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
       }
       continue;
     }
-    float g[NJ][8], xh[NJ][8];
+    float g[NJ][8], xh[NJ][8], pp[NJ][8];
     float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {  // all three streams of this row in flight before the first reduction
+      const int o = j * 32 + lane;
+      if (o < K8) ld8(a.P + r * W + o * 8, pp[j]);
+    }
 #pragma unroll
     for (int j = 0; j < NJ; ++j) {
       const int o = j * 32 + lane;
@@ -398,13 +413,12 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
       const int o = j * 32 + lane;
       if (o < K8) {
         const int c0 = o * 8;
-        float dv[8], dp[8], p[8];
-        ld8(a.P + r * W + c0, p);
+        float dv[8], dp[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           dv[i] = a.norm == BFK_NORM_LAYER ? rs * (g[j][i] - m1 - xh[j][i] * m2) : g[j][i];
           float d;
-          t_act(a.act, p[i], d);
+          t_act(a.act, pp[j][i], d);
           if (a.drop_rate > 0.f) d *= drop_scale(a.seed, a.layer, r, c0 + i, a.drop_rate, a.inv_keep);
           dp[i] = dv[i] * d;
           ad[j][i] += dp[i];

@@ -116,23 +116,36 @@ int launch_gemm_dw(const unsigned char* X, int XK8, const unsigned char* Y, int 
   return 0;
 }
 
-template <typename A>
-int launch_block_fwd(const A& a, cudaStream_t st) {
+// one resident wave: a grid that is not a multiple of what fits leaves a half-empty second wave (r01u: 592 blocks on 444
+// slots cost 2 waves)
+template <typename K>
+unsigned resident_grid(K kernel, int threads, size_t smem) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+  int sms = bfk_num_sms();
+  return (unsigned)((sms > 0 ? sms : 148) * per_sm);
+}
+int launch_block_fwd(const BlockFwdArgs& a, cudaStream_t st) {
   const int nj = (a.W / 8 + 31) / 32;
-  const unsigned grid = 148 * 8;
-  if (nj == 1) block_fwd_kernel<1><<<grid, 256, 0, st>>>(a);
-  else if (nj == 2) block_fwd_kernel<2><<<grid, 256, 0, st>>>(a);
-  else block_fwd_kernel<4><<<grid, 256, 0, st>>>(a);
+  static unsigned grid[3] = {0, 0, 0};
+  if (!grid[0]) {
+    grid[0] = resident_grid(block_fwd_kernel<1>, 256, 0);
+    grid[1] = resident_grid(block_fwd_kernel<2>, 256, 0);
+    grid[2] = resident_grid(block_fwd_kernel<4>, 256, 0);
+  }
+  if (nj == 1) block_fwd_kernel<1><<<grid[0], 256, 0, st>>>(a);
+  else if (nj == 2) block_fwd_kernel<2><<<grid[1], 256, 0, st>>>(a);
+  else block_fwd_kernel<4><<<grid[2], 256, 0, st>>>(a);
   CK(cudaGetLastError());
   return 0;
 }
 int launch_block_bwd(const BlockBwdArgs& a, cudaStream_t st) {
   const int nj = (a.W / 8 + 31) / 32;
-  const unsigned grid = 148 * 4;
   const size_t sh = (size_t)4 * a.W * 4;
-  if (nj == 1) block_bwd_kernel<1><<<grid, 256, sh, st>>>(a);
-  else if (nj == 2) block_bwd_kernel<2><<<grid, 256, sh, st>>>(a);
-  else block_bwd_kernel<4><<<grid, 256, sh, st>>>(a);
+  unsigned grid;
+  if (nj == 1) { grid = resident_grid(block_bwd_kernel<1>, 256, sh); block_bwd_kernel<1><<<grid, 256, sh, st>>>(a); }
+  else if (nj == 2) { grid = resident_grid(block_bwd_kernel<2>, 256, sh); block_bwd_kernel<2><<<grid, 256, sh, st>>>(a); }
+  else { grid = resident_grid(block_bwd_kernel<4>, 256, sh); block_bwd_kernel<4><<<grid, 256, sh, st>>>(a); }
   CK(cudaGetLastError());
   return 0;
 }

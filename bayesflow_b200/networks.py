@@ -197,6 +197,7 @@ class _Engine:
         self._packed = None
         self._key = None
         self.cfg = None
+        self.layerwise = False
         self.kernel_events = None  # set to a list to have CUDA events recorded around the sampler kernel
         self.launches = 0          # kernels launched so far (bench.py reports it as gpu_launches)
 
@@ -225,9 +226,18 @@ class _Engine:
         if dev.type != "cuda":
             raise RuntimeError("bayesflow_b200: move the network to a CUDA device first (no CPU fallback)")
         self.cfg = cfg = self._make_cfg()
-        if not L.bfk_fused_supported(C.byref(cfg)):
-            raise NotImplementedError(
-                f"config D={cfg.D} W={cfg.W} L={cfg.L} is not supported by the fused sampler (need D<=8, W<=256, W%32==0)")
+        self.layerwise = not L.bfk_fused_supported(C.byref(cfg))
+        if self.layerwise:
+            # W > 256 or D > 8: the layer-wise tcgen05 path (bfk_sample_layerwise) reads the fp32 weights directly
+            from .training import _bind, fill_weights
+            _bind(L)
+            if L.bfk_train_workspace_bytes(C.byref(cfg), 128, 0) == 0:
+                raise NotImplementedError(f"config D={cfg.D} W={cfg.W} L={cfg.L}: neither the fused sampler (D<=8, W<=256, "
+                                          f"W%32==0) nor the layer-wise path covers it: " + L.bfk_last_error_string().decode())
+            self.w, self._keep_w = fill_weights(net, lambda p: p.detach())
+            self._packed, self._key = torch.empty(1, dtype=torch.uint8, device=dev), key
+            self._ws = None
+            return
         w = _lib.Weights()
         keep = []
 
@@ -262,9 +272,23 @@ class _Engine:
     def cond_tables(self, conditions, B, repeats=None):
         """conditions -> (pre_add, post_add, rows_per_group).  Rows of a dataset share their condition vector
         (approximators/helpers/samplers.py:51-63), so the conditions half of TimeMLP is computed once per dataset."""
+        cond, repeats = self.group_conditions(conditions, B, repeats)
+        if cond is None:
+            return None, None, 1
+        G = cond.shape[0]
+        W = self.cfg.W
+        post = torch.empty(G, W, device=cond.device, dtype=torch.float32)
+        pre = torch.empty(G, W, device=cond.device, dtype=torch.float32) if self.net.subnet.merge == "add" else None
+        _lib.check(_lib.lib().bfk_cond_prologue(C.byref(self.cfg), _lib.ptr(self._packed), _lib.ptr(cond), G,
+                                                _lib.ptr(pre), _lib.ptr(post), _lib.stream_ptr()), "bfk_cond_prologue")
+        self.launches += 1
+        return pre, post, repeats
+
+    def group_conditions(self, conditions, B, repeats=None):
+        """-> ((G, C) conditions, rows per dataset): consecutive rows sharing one condition vector are one dataset."""
         net = self.net
         if conditions is None or not net._C:
-            return None, None, 1
+            return None, 1
         cond = conditions.detach().to(torch.float32)
         if cond.ndim != 2 or cond.shape[-1] != net._C:
             raise ValueError(f"conditions must have shape (rows, {net._C}), got {tuple(cond.shape)}")
@@ -278,15 +302,7 @@ class _Engine:
                     cond, repeats = uniq, int(counts[0])
         elif cond.shape[0] * repeats != B:
             raise ValueError(f"conditions rows ({cond.shape[0]}) x repeats ({repeats}) != batch ({B})")
-        cond = cond.contiguous()
-        G = cond.shape[0]
-        W = self.cfg.W
-        post = torch.empty(G, W, device=cond.device, dtype=torch.float32)
-        pre = torch.empty(G, W, device=cond.device, dtype=torch.float32) if net.subnet.merge == "add" else None
-        _lib.check(_lib.lib().bfk_cond_prologue(C.byref(self.cfg), _lib.ptr(self._packed), _lib.ptr(cond), G,
-                                                _lib.ptr(pre), _lib.ptr(post), _lib.stream_ptr()), "bfk_cond_prologue")
-        self.launches += 1
-        return pre, post, repeats
+        return cond.contiguous(), repeats
 
     def eval_table(self, times: np.ndarray):
         dev = self._packed.device
@@ -414,6 +430,76 @@ class _Run:
         return ybuf[int(c[K["sel"]])].clone()
 
 
+class _RunLW:
+    """One sampling call on the layer-wise path (bfk_sample_layerwise): same interface as _Run."""
+
+    CHUNK_ROWS = 8192  # rows per L2-resident chunk (activations of a chunk: 8192 x 1024 x (4 + 2) B = 48 MB)
+
+    def __init__(self, engine, cond, rpg, target_mask):
+        self.e, self.cond, self.rpg = engine, cond, rpg
+        self.tmask = None
+        if target_mask is not None:
+            tm = torch.as_tensor(target_mask, dtype=torch.float32, device=engine._packed.device)
+            if tm.numel() != engine.cfg.D:
+                raise NotImplementedError("target_mask must be feature-level, shape (D,), on the accelerated path")
+            self.tmask = tm.reshape(-1).contiguous()
+        self.info = {}
+
+    _check_x = _Run._check_x
+
+    def _call(self, x, times, hs, method, velocity_only):
+        import os
+        e, L = self.e, _lib.lib()
+        dev = x.device
+        t = torch.from_numpy(np.ascontiguousarray(times, dtype=np.float32)).to(dev, non_blocking=True)
+        h = None if hs is None else torch.from_numpy(np.ascontiguousarray(hs, dtype=np.float32)).to(dev, non_blocking=True)
+        n_steps = 1 if hs is None else int(h.numel())
+        B = x.shape[0]
+        chunk = int(os.environ.get("BFK_LW_CHUNK_ROWS", self.CHUNK_ROWS))
+        chunk = min(chunk, (B + 127) // 128 * 128)
+        G = 0 if self.cond is None else self.cond.shape[0]
+        L.bfk_layerwise_workspace_bytes.restype = C.c_size_t
+        L.bfk_layerwise_workspace_bytes.argtypes = [C.POINTER(_lib.NetConfig), C.c_int64, C.c_int64, C.c_int64]
+        need = L.bfk_layerwise_workspace_bytes(C.byref(e.cfg), chunk, int(t.numel()), G)
+        if need == 0:
+            raise NotImplementedError("bfk_layerwise_workspace_bytes: " + L.bfk_last_error_string().decode())
+        if e._ws is None or e._ws.numel() < need:
+            e._ws = torch.empty(need, dtype=torch.uint8, device=dev)
+        out = torch.empty_like(x)
+        sched = e.net._schedule_struct()
+        L.bfk_sample_layerwise.argtypes = [C.POINTER(_lib.NetConfig), C.POINTER(_lib.Weights), C.POINTER(_lib.Schedule),
+                                           C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int64, C.c_int64,
+                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p,
+                                           C.c_size_t, C.c_void_p]
+        ev = None
+        if e.kernel_events is not None:
+            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            ev[0].record()
+        _lib.check(L.bfk_sample_layerwise(C.byref(e.cfg), C.byref(e.w), C.byref(sched), _lib.ptr(t), _lib.ptr(h),
+                                          _lib.METHOD[method], n_steps, _lib.ptr(self.cond), G, self.rpg, _lib.ptr(self.tmask),
+                                          _lib.ptr(x), _lib.ptr(out), B, int(velocity_only), chunk, _lib.ptr(e._ws),
+                                          e._ws.numel(), _lib.stream_ptr()), "bfk_sample_layerwise")
+        if ev is not None:
+            ev[1].record()
+            e.kernel_events.append(ev)
+        cfg = e.cfg
+        per_eval = 2 + (4 if cfg.C else 1) + 2 * cfg.L + 1 + (1 if (sched.model == 1 or self.tmask is not None) else 0)
+        n_chunks = (B + chunk - 1) // chunk
+        e.launches += cfg.L + 4 + n_chunks * (int(t.numel()) * per_eval + (0 if velocity_only else n_steps))
+        self.info = {"steps": n_steps, "evals": int(t.numel()), "rejected": 0, "path": "layerwise", "chunk_rows": chunk}
+        return out
+
+    def velocity(self, x, time: float):
+        return self._call(self._check_x(x), np.asarray([time], dtype=np.float32), None, "euler", True)
+
+    def run_fixed(self, x, times, hs, method):
+        return self._call(self._check_x(x), times, hs, method, False)
+
+    def run_adaptive(self, *args, **kwargs):
+        raise NotImplementedError("adaptive step sizes on the layer-wise path (W > 256 or D > 8) are not built yet; pass an "
+                                  "integer `steps` (fixed) or a time grid (scheduled)")
+
+
 # ======================================================================================================================
 # The reference's surface
 # ======================================================================================================================
@@ -497,6 +583,9 @@ class InferenceNetwork(nn.Module):
         self._engine.prepare()
         if self.unconditional_mode and conditions is not None:
             conditions = torch.zeros_like(conditions)
+        if self._engine.layerwise:
+            cond, rpg = self._engine.group_conditions(conditions, B, kwargs.get("conditions_repeats"))
+            return _RunLW(self._engine, cond, rpg, kwargs.get("target_mask"))
         pre, post, rpg = self._engine.cond_tables(conditions, B, kwargs.get("conditions_repeats"))
         return _Run(self._engine, pre, post, rpg, kwargs.get("target_mask"))
 

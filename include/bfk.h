@@ -192,6 +192,20 @@ int bfk_adam_step(float* params, const float* grads, float* m, float* v, const i
                   float* seg_sqnorm, float clipnorm, float lr_t, float beta1, float beta2, float eps, float wd_lr,
                   void* stream);
 
+/* ---- layer-wise sampler: networks the fused on-chip kernel cannot hold (W > 256 or D > 8; BASELINE configs[3]) --------
+ * Same contract as bfk_sample_fixed (integrate.py:217-288 driven by flow_matching.py:254-337 / diffusion_model.py:782-869)
+ * but taking the fp32 weights directly: one tcgen05 GEMM per Dense layer, rows processed in chunks of `chunk_rows` whose
+ * activations stay L2-resident; each chunk runs its whole trajectory.  times: n_steps*stages evaluation times (device,
+ * execution order), step_h: n_steps (device).  conditions (G,C): row r uses dataset r / rows_per_group (the Sampler's
+ * repeat, samplers.py:51-63, without materialising it).  velocity_only != 0: one evaluation at times[0], x_out = velocity.
+ * W % 64 == 0, W <= 1024, D <= 64, fp16 operands. */
+size_t bfk_layerwise_workspace_bytes(const bfk_net_config* cfg, int64_t chunk_rows, int64_t n_evals, int64_t G);
+int bfk_sample_layerwise(const bfk_net_config* cfg, const bfk_weights* weights, const bfk_schedule* sched,
+                         const float* times, const float* step_h, int32_t method, int64_t n_steps,
+                         const float* conditions, int64_t G, int64_t rows_per_group, const float* target_mask,
+                         const float* x_in, float* x_out, int64_t B, int32_t velocity_only, int64_t chunk_rows,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- introspection ------------------------------------------------------------------------------------------- */
 int bfk_num_sms(void);
 int bfk_fused_supported(const bfk_net_config* cfg); /* 1 if the on-chip sampler handles this config */
