@@ -153,6 +153,145 @@ __global__ void __launch_bounds__(G_THREADS, 2) gemm_kernel(const GemmArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// Persistent form of the same GEMM (no split-K): one CTA per SM walks the output tiles (n fastest, so the CTAs that run
+// together share an A tile in L2), TWO accumulators in TMEM so that the epilogue of tile i runs under the main loop of
+// tile i+1, K = 64 per ring stage (4 UMMAs per hand-shake), 8 epilogue warps (TMEM lane quarter = warp % 4, odd / even
+// 64-column panels = warp / 4).  r01w: the one-tile-per-CTA kernel reached 34 % tensor-pipe at 8192 x 1024 x 1024
+// because prologue and epilogue of co-resident CTAs coincide instead of overlapping.
+constexpr int P_KC = 64, P_STAGES = 3, P_THREADS = 320, P_EPI_WARPS = 8;
+__host__ __device__ inline size_t gemm_persist_smem_bytes(int NT) {
+  return (size_t)P_STAGES * (P_KC * G_TM * 2 + P_KC * NT * 2) + (size_t)P_EPI_WARPS * 32 * 68 * 4 + 256;
+}
+
+__global__ void __launch_bounds__(P_THREADS, 1) gemm_persist_kernel(const GemmArgs a) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int NT = a.NT;
+  const uint32_t a_bytes = P_KC * G_TM * 2, b_bytes = (uint32_t)P_KC * NT * 2, st_bytes = a_bytes + b_bytes;
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t stg_off = P_STAGES * st_bytes;
+  const uint32_t bar0 = smem_base + stg_off + P_EPI_WARPS * 32 * 68 * 4;
+  // full[s] +8s, empty[s] +8(3+s), acc_full[b] +48+8b, acc_empty[b] +64+8b, tmem slot +80
+  volatile uint32_t* s_tmem = reinterpret_cast<volatile uint32_t*>(smem + stg_off + P_EPI_WARPS * 32 * 68 * 4 + 80);
+  const int n_tiles_n = a.N / NT;
+  const long long m_tiles = (a.M + G_TM - 1) / G_TM;
+  const long long total = m_tiles * n_tiles_n;
+  const int n_slabs = a.K / P_KC;
+  const size_t K8 = (size_t)a.K / 8;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < P_STAGES; ++s) { mbar_init(bar0 + 8 * s, 1); mbar_init(bar0 + 8 * (3 + s), 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(bar0 + 48 + 8 * b, 1); mbar_init(bar0 + 64 + 8 * b, P_EPI_WARPS); }
+    fence_barrier_init();
+  }
+  const uint32_t tmem_cols = NT <= 64 ? 128 : (NT <= 128 ? 256 : 512);
+  const uint32_t acc_stride = tmem_cols / 2;
+  if (warp == 8) tmem_alloc(bar0 + 80, tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 9) {
+    if (lane == 0) {
+      uint32_t g = 0;
+      for (long long t = blockIdx.x; t < total; t += gridDim.x) {
+        const long long m_tile = t / n_tiles_n;
+        const int n_tile = (int)(t % n_tiles_n);
+        for (int i = 0; i < n_slabs; ++i, ++g) {
+          const uint32_t s = g % P_STAGES;
+          mbar_wait(bar0 + 8 * (3 + s), ((g / P_STAGES) & 1) ^ 1, nullptr, 0);
+          mbar_arrive_expect_tx(bar0 + 8 * s, st_bytes);
+          const size_t k8 = (size_t)i * (P_KC / 8);
+          bulk_g2s(smem_base + s * st_bytes, a.A + ((size_t)m_tile * K8 + k8) * G_TM * 16, a_bytes, bar0 + 8 * s);
+          bulk_g2s(smem_base + s * st_bytes + a_bytes, a.B + ((size_t)n_tile * K8 + k8) * NT * 16, b_bytes, bar0 + 8 * s);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 8) {
+    if (lane == 0) {
+      uint32_t g = 0, j = 0;
+      for (long long t = blockIdx.x; t < total; t += gridDim.x, ++j) {
+        const uint32_t acc = j & 1;
+        mbar_wait(bar0 + 64 + 8 * acc, ((j >> 1) & 1) ^ 1, nullptr, 0);  // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * acc_stride;
+        for (int i = 0; i < n_slabs; ++i, ++g) {
+          const uint32_t s = g % P_STAGES;
+          mbar_wait(bar0 + 8 * s, (g / P_STAGES) & 1, nullptr, 0);
+          tc_fence_after();
+          const uint32_t sa = smem_base + s * st_bytes, sb = sa + a_bytes;
+#pragma unroll
+          for (int kk = 0; kk < P_KC / 16; ++kk) {
+            const uint64_t ad = umma_smem_desc(sa + (uint32_t)(kk * 2) * (G_TM * 16), G_TM * 16, 128);
+            const uint64_t bd = umma_smem_desc(sb + (uint32_t)(kk * 2) * (NT * 16), (uint32_t)NT * 16, 128);
+            umma_f16(d_tmem, ad, bd, a.idesc, (uint32_t)((i | kk) != 0));
+          }
+          umma_commit(bar0 + 8 * (3 + s));
+        }
+        umma_commit(bar0 + 48 + 8 * acc);
+      }
+    }
+    __syncwarp();
+  } else {
+    const int q = warp & 3, half = warp >> 2;
+    float* stg = reinterpret_cast<float*>(smem + stg_off) + warp * (32 * 68);
+    const int sub = lane >> 4, c4 = (lane & 15) * 4;
+    uint32_t j = 0;
+    for (long long t = blockIdx.x; t < total; t += gridDim.x, ++j) {
+      const long long m_tile = t / n_tiles_n;
+      const int n_tile = (int)(t % n_tiles_n);
+      const uint32_t acc = j & 1;
+      mbar_wait(bar0 + 48 + 8 * acc, (j >> 1) & 1, nullptr, 0);
+      tc_fence_after();
+      const uint32_t t_acc = tmem_base + acc * acc_stride + ((uint32_t)(q * 32) << 16);
+      const long long row0 = m_tile * G_TM + q * 32;
+      const float* bias = a.bias ? a.bias + (size_t)n_tile * NT : nullptr;
+      for (int p = half; p < NT / 64; p += 2) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          float v[32];
+          tmem_ld32(t_acc + p * 64 + h * 32, v);
+          tmem_ld_wait32(v);
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) *reinterpret_cast<float4*>(stg + lane * 68 + h * 32 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+        }
+        __syncwarp();
+        float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (bias) b4 = *reinterpret_cast<const float4*>(bias + p * 64 + c4);
+        float4* dst[16];
+        float4 o[16];
+#pragma unroll
+        for (int it = 0; it < 16; ++it) {
+          const int rr = it * 2 + sub;
+          dst[it] = reinterpret_cast<float4*>(a.C + (row0 + rr) * a.ldc + (size_t)n_tile * NT + p * 64 + c4);
+          const float4 tt = *reinterpret_cast<const float4*>(stg + rr * 68 + c4);
+          o[it] = make_float4(fmaf(tt.x, a.alpha, b4.x), fmaf(tt.y, a.alpha, b4.y), fmaf(tt.z, a.alpha, b4.z), fmaf(tt.w, a.alpha, b4.w));
+        }
+        if (a.flags & GEMM_ADD_EXISTING) {
+          float4 e[16];
+#pragma unroll
+          for (int it = 0; it < 16; ++it) e[it] = (row0 + it * 2 + sub < a.M) ? *dst[it] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int it = 0; it < 16; ++it) { o[it].x += e[it].x; o[it].y += e[it].y; o[it].z += e[it].z; o[it].w += e[it].w; }
+        }
+#pragma unroll
+        for (int it = 0; it < 16; ++it)
+          if (row0 + it * 2 + sub < a.M) *dst[it] = o[it];
+        __syncwarp();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar0 + 64 + 8 * acc);
+    }
+  }
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 8) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // dW GEMM: C[Mf, N] += alpha * X^T * Y with the contraction over the BATCH rows.  X and Y are activation images
 // IMG[r/128][k/8][r%128][k%8] (r = batch row, k = feature).  Read as an MN-major UMMA operand (MN = feature, K = batch
 // row) the very same bytes are the canonical no-swizzle layout: core matrix = 8 batch rows x 8 features (128 B), next

@@ -402,6 +402,23 @@ extern "C" int bfk_gemm(const void* A, const void* B, float* Cm, int64_t ldc, in
   a.k_per_split = kps;
   k_splits = (K + kps - 1) / kps;
   a.idesc = umma_idesc_f16(G_TM, NT, precision == BFK_PREC_BF16 ? 1 : 0);
+  static int use_persist = -1;
+  if (use_persist < 0) { const char* e = getenv("BFK_GEMM_PERSIST"); use_persist = e ? atoi(e) : 1; }
+  if (use_persist && k_splits == 1 && !(flags & GEMM_ATOMIC) && (K % P_KC) == 0) {
+    // persistent, double-buffered-accumulator kernel: whenever there is no split-K
+    static bool p_attr = false;
+    if (!p_attr) {
+      CK(cudaFuncSetAttribute(gemm_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_persist_smem_bytes(256)));
+      p_attr = true;
+    }
+    const long long tiles = ((M + G_TM - 1) / G_TM) * (N / NT);
+    int sms = bfk_num_sms();
+    if (sms <= 0) sms = 148;
+    const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
+    gemm_persist_kernel<<<grid, P_THREADS, gemm_persist_smem_bytes(NT), (cudaStream_t)stream_>>>(a);
+    CK(cudaGetLastError());
+    return 0;
+  }
   const size_t sh = gemm_smem_bytes(NT);
   static bool attr_set = false;
   if (!attr_set) {

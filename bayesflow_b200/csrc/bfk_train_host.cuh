@@ -130,12 +130,13 @@ int launch_block_fwd(const BlockFwdArgs& a, cudaStream_t st) {
   static unsigned grid[3] = {0, 0, 0};
   if (!grid[0]) {
     grid[0] = resident_grid(block_fwd_kernel<1>, 256, 0);
-    grid[1] = resident_grid(block_fwd_kernel<2>, 256, 0);
-    grid[2] = resident_grid(block_fwd_kernel<4>, 256, 0);
+    grid[1] = resident_grid(block_fwd_wide_kernel<2>, 256, 0);
+    grid[2] = resident_grid(block_fwd_wide_kernel<4>, 256, 0);
   }
+  if (a.FG) return fail(-73, "layer-wise path: film_use_gamma is not supported");
   if (nj == 1) block_fwd_kernel<1><<<grid[0], 256, 0, st>>>(a);
-  else if (nj == 2) block_fwd_kernel<2><<<grid[1], 256, 0, st>>>(a);
-  else block_fwd_kernel<4><<<grid[2], 256, 0, st>>>(a);
+  else if (nj == 2) block_fwd_wide_kernel<2><<<grid[1], 256, 0, st>>>(a);
+  else block_fwd_wide_kernel<4><<<grid[2], 256, 0, st>>>(a);
   CK(cudaGetLastError());
   return 0;
 }
