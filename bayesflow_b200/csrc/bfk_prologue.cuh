@@ -133,7 +133,7 @@ __global__ void cond_prologue_kernel(bfk_net_config cfg, const unsigned char* __
 
 // DiffusionModel probability-flow velocity as  v = coefZ * z + coefP * pred  (diffusion_model.py:351-405, 466-489,
 // 539-552; noise_schedule.py:70-119; edm_noise_schedule.py:61-108; cosine_noise_schedule.py:60-82), evaluated in double.
-__device__ inline void schedule_coefs(const bfk_schedule& s, double t, double* coefZ, double* coefP, double* net_time) {
+__host__ __device__ inline void schedule_coefs(const bfk_schedule& s, double t, double* coefZ, double* coefP, double* net_time) {
   if (s.model == BFK_MODEL_FM) {
     *coefZ = 0.0; *coefP = 1.0; *net_time = t;
     return;

@@ -555,6 +555,7 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
     }
   }
   __syncthreads();
+  if (!a.d_bd) return;  // cotangent-only pass (bfk_train_vjp): no parameter gradients
   for (int c = threadIdx.x; c < W; c += blockDim.x) {
     if (a.gamma) { atomicAdd(a.d_gamma + c, a.gscale * s_red[c]); atomicAdd(a.d_beta + c, a.gscale * s_red[W + c]); }
     atomicAdd(a.d_bd + c, a.gscale * s_red[2 * W + c]);
@@ -676,6 +677,75 @@ __global__ void fm_interp_kernel(const float* __restrict__ x0, const float* __re
   const float tt = t[i / D];
   x[i] = tt * x1[i] + (1.f - tt) * x0[i];
   target[i] = x1[i] - x0[i];
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Vector-Jacobian products of the velocity w.r.t. its input (utils/jacobian/vjp.py:44-68, jacobian_trace.py:44-55):
+// the cotangent enters where the loss head would (dout image), the dX chain of the training backward carries it to the
+// first layer's pre-activation, and dx = d(h0pre)[:, :W] . Wx^T closes it.
+// cotangent image: row r gets dout[r,:] (or the one-hot e_col when dout == nullptr); K padding and rows >= B are zero.
+__global__ void cotangent_pack_kernel(const float* __restrict__ dout, int col, long long B, long long R_pad, int D, int KO8,
+                                      unsigned char* __restrict__ img) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= R_pad) return;
+  for (int k8 = 0; k8 < KO8; ++k8) {
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int k = k8 * 8 + i;
+      v[i] = (r < B && k < D) ? (dout ? dout[r * D + k] : (k == col ? 1.f : 0.f)) : 0.f;
+    }
+    *reinterpret_cast<uint4*>(img + img_off(r, k8, KO8)) = pack8(v);
+  }
+}
+
+// dx[r,d] = sum_k g[r,k] * Wx[d,k] for the first W columns of the d(h0pre) image; one thread per row, DC outputs per pass.
+// trace[r] += dx[r,col] when asked (exact Jacobian trace accumulates one diagonal entry per reverse pass).
+template <int DC>
+__global__ void __launch_bounds__(128) vjp_input_kernel(const unsigned char* __restrict__ g_img, int K8, const float* __restrict__ Wx,
+                                                        long long B, int D, int W, float* __restrict__ dx, float* __restrict__ trace,
+                                                        int col) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= B) return;
+  for (int d0 = 0; d0 < D; d0 += DC) {
+    if (!dx && (col < d0 || col >= d0 + DC)) continue;  // trace only: one diagonal entry is needed
+    float acc[DC];
+#pragma unroll
+    for (int d = 0; d < DC; ++d) acc[d] = 0.f;
+    for (int k8 = 0; k8 < W / 8; ++k8) {
+      const uint4 q = *reinterpret_cast<const uint4*>(g_img + img_off(r, k8, K8));
+      const __half2* h = reinterpret_cast<const __half2*>(&q);
+      float v[8];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { const float2 f = __half22float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+#pragma unroll
+      for (int d = 0; d < DC; ++d) {
+        if (d0 + d < D) {
+          const float* wrow = Wx + (size_t)(d0 + d) * W + k8 * 8;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[d] = fmaf(v[i], __ldg(wrow + i), acc[d]);
+        }
+      }
+    }
+#pragma unroll
+    for (int d = 0; d < DC; ++d) {
+      if (d0 + d < D) {
+        if (dx) dx[r * D + d0 + d] = acc[d];
+        if (trace && d0 + d == col) trace[r] += acc[d];
+      }
+    }
+  }
+}
+
+// out = y + h * sum_j c_j k_j (integrate.py:47-54): products and sums rounded separately, left to right, as torch does.
+struct RkCombineArgs { const float* k[8]; float c[8]; int n; };
+__global__ void rk_combine_kernel(const float* __restrict__ y, const RkCombineArgs a, float h, long long numel,
+                                  float* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= numel) return;
+  float acc = 0.f;
+  for (int j = 0; j < a.n; ++j) acc = __fadd_rn(acc, __fmul_rn(a.c[j], a.k[j][i]));
+  out[i] = __fadd_rn(y[i], __fmul_rn(h, acc));
 }
 
 // ---------------------------------------------------------------------------------------------------------------

@@ -280,6 +280,80 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   return 0;
 }
 
+// One reverse pass of the velocity network w.r.t. its INPUT over the activations a preceding
+// bfk_train_step(c, w, NULL, ta, NULL, pred, workspace /* sized with backward=1 */) left in `workspace`.
+// Cotangent = dout (B,D) or, when dout == NULL, the one-hot e_col.  Writes dx (B,D) if non-NULL and adds dx[:,col] to
+// trace (B,) if non-NULL.  No parameter gradients are touched.  Reference: utils/jacobian/vjp.py:44-68 (torch.autograd.grad
+// through the subnet), utils/jacobian/jacobian_trace.py:44-55.
+extern "C" int bfk_train_vjp(const bfk_net_config* c, const bfk_weights* w, const bfk_train_args* ta, const float* dout,
+                             int32_t col, float* dx, float* trace, void* workspace, size_t workspace_bytes, void* stream_) {
+  RC(check_train_cfg(c));
+  if (!w || !ta || !workspace || ta->B <= 0) return fail(-82, "bfk_train_vjp: bad arguments");
+  if (!dout && (col < 0 || col >= c->D)) return fail(-83, "bfk_train_vjp: one-hot column out of range");
+  if (!dx && !trace) return fail(-84, "bfk_train_vjp: nothing to compute (dx and trace are NULL)");
+  cudaStream_t st = (cudaStream_t)stream_;
+  const long long B = ta->B;
+  const int W = c->W, D = c->D, L = c->L, act = c->activation, P16 = BFK_PREC_FP16;
+  Arena ar{(unsigned char*)workspace, 0, workspace_bytes};
+  TrainBufs b{};
+  plan_train(c, B, true, ar, b);
+  if (ar.off > workspace_bytes) return fail(-79, "bfk_train_vjp: workspace too small (bfk_train_workspace_bytes, backward=1)");
+  const long long Rp = b.Rp, n_tiles = Rp / 128;
+  const int N1 = b.N1, NO = b.NO, NTW = nt_of(W), NT1 = nt_of(N1);
+  const unsigned tchunks = (unsigned)(n_tiles < 64 ? n_tiles : 64);
+  cotangent_pack_kernel<<<(unsigned)((Rp + 127) / 128), 128, 0, st>>>(dout, col, B, Rp, D, NO / 8, b.dout_img);
+  CK(cudaGetLastError());
+  // wo_b / wd_b / wm_b: the MN-major weight images; packed here so the pass does not depend on an earlier backward
+  RC(bfk_pack_kmajor(w->out_k, D, W, D, NO, NTW, P16, b.wo_b, st));
+  RC(bfk_gemm(b.dout_img, b.wo_b, b.dH, W, B, W, NO, NTW, 1, 0, nullptr, 1.f, P16, st));
+  for (int l = L - 1; l >= 0; --l) {
+    BlockBwdArgs a{};
+    a.dH = b.dH; a.xhat = b.xhat[l]; a.rstd = b.rstd[l]; a.P = b.P[l];
+    a.gamma = c->norm == BFK_NORM_LAYER ? w->norm_g[l] : nullptr;
+    a.dP_img = b.dP_img; a.dV_img = b.dV_img;
+    a.d_gamma = a.d_beta = a.d_bd = a.d_bfilm = nullptr;
+    a.B = B; a.R_pad = Rp; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
+    a.drop_rate = 0.f; a.inv_keep = 1.f; a.seed = 0; a.gscale = 1.f;
+    RC(launch_block_bwd(a, st));
+    if (!c->residual) CK(cudaMemsetAsync(b.dH, 0, (size_t)B * W * 4, st));
+    RC(bfk_pack_kmajor(w->dense_k[l], W, W, W, W, NTW, P16, b.wd_b[l], st));
+    RC(bfk_gemm(b.dP_img, b.wd_b[l], b.dH, W, B, W, W, NTW, 1, GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
+  }
+  if (b.has_merge) {
+    act_bwd_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.dH, b.m, W, B, n_tiles, W / 8, act, b.dP_img, nullptr, 1.f);
+    RC(bfk_pack_kmajor(w->m_k, W, N1, W, W, NT1, P16, b.wm_b, st));
+    RC(bfk_gemm(b.dP_img, b.wm_b, b.da1, N1, B, N1, W, NT1, 1, 0, nullptr, 1.f, P16, st));
+    act_bwd_kernel<<<dim3(N1 / 8, tchunks), 128, 0, st>>>(b.da1, b.h0pre, N1, B, n_tiles, N1 / 8, act, b.dh0pre_img, nullptr, 1.f);
+  } else {
+    act_bwd_kernel<<<dim3(N1 / 8, tchunks), 128, 0, st>>>(b.dH, b.h0pre, N1, B, n_tiles, N1 / 8, act, b.dh0pre_img, nullptr, 1.f);
+  }
+  CK(cudaGetLastError());
+  const unsigned gb = (unsigned)((B + 127) / 128);
+  if (D <= 2) vjp_input_kernel<2><<<gb, 128, 0, st>>>(b.dh0pre_img, N1 / 8, w->x_k, B, D, W, dx, trace, col);
+  else vjp_input_kernel<8><<<gb, 128, 0, st>>>(b.dh0pre_img, N1 / 8, w->x_k, B, D, W, dx, trace, col);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+// Host-side evaluation of the same double-precision schedule algebra the evaluation tables use (density path of
+// DiffusionModel: velocity = coefZ*z + coefP*pred, so trace(dv/dz) = D*coefZ + coefP*trace(dpred/dz)).
+extern "C" int bfk_schedule_coefs(const bfk_schedule* sched, double t, double* coefZ, double* coefP, double* net_time) {
+  if (!sched || !coefZ || !coefP || !net_time) return fail(-86, "bfk_schedule_coefs: bad arguments");
+  bfk::schedule_coefs(*sched, t, coefZ, coefP, net_time);
+  return 0;
+}
+
+extern "C" int bfk_rk_combine(const float* y, const float* const* k, const float* coef, int32_t n, float h, int64_t numel,
+                              float* out, void* stream_) {
+  if (!y || !k || !coef || !out || n < 0 || n > 8 || numel <= 0) return fail(-85, "bfk_rk_combine: bad arguments");
+  RkCombineArgs a{};
+  a.n = n;
+  for (int j = 0; j < n; ++j) { a.k[j] = k[j]; a.c[j] = coef[j]; }
+  rk_combine_kernel<<<cdiv((size_t)numel, 256), 256, 0, (cudaStream_t)stream_>>>(y, a, h, numel, out);
+  CK(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int bfk_fm_interpolate(const float* x0, const float* x1, const float* t, int64_t B, int32_t D, float* x,
                                   float* target, void* stream_) {
   if (!x0 || !x1 || !t || !x || !target || B <= 0 || D <= 0) return fail(-80, "bfk_fm_interpolate: bad arguments");

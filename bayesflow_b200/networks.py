@@ -559,8 +559,28 @@ class InferenceNetwork(nn.Module):
         _, log_density = self(samples, conditions=conditions, inverse=False, density=True, **kwargs)
         return log_density
 
-    def compute_metrics(self, x, conditions=None, sample_weight=None, stage="training", **kwargs):
+    def _loss_and_grads(self, x, conditions=None, sample_weight=None, stage="training", seed=None, world=1, backward=True,
+                        **kwargs):
         raise NotImplementedError
+
+    def compute_metrics(self, x, conditions=None, sample_weight=None, stage="training", **kwargs):
+        """{"loss": 0-d tensor}.  With grad mode on and stage == "training" the kernels also produce every parameter
+        gradient; ``loss.backward()`` then fills ``p.grad`` exactly like the reference's autograd path."""
+        from .training import _LossWithGrads, train_engine
+        backward = torch.is_grad_enabled() and stage == "training"
+        extra = {k: kwargs[k] for k in ("fixed", "row_offset") if k in kwargs}
+        loss = self._loss_and_grads(x, conditions, sample_weight, stage=stage, seed=kwargs.get("seed"), backward=backward,
+                                    **extra)
+        if backward:
+            eng = train_engine(self)
+            loss = _LossWithGrads.apply(loss, eng, *eng.params)
+        return {"loss": loss}
+
+    def _dropout_seed(self, seed):
+        if seed is None:
+            self._drop_calls = getattr(self, "_drop_calls", 0) + 1
+            seed = (torch.initial_seed() * 0x9E3779B1 + self._drop_calls) & (2 ** 63 - 1)
+        return seed
 
     @property
     def variables(self):
@@ -599,6 +619,33 @@ class InferenceNetwork(nn.Module):
         return x
 
     _INTEGRATE_KEYS = ("start_time", "stop_time", "min_steps", "max_steps", "steps", "method", "atol", "rtol")
+
+    def _velocity_trace_fn(self, conditions, B, kwargs):
+        from .density import VelocityTrace
+        return VelocityTrace(self, conditions, B, max_steps=kwargs.get("max_steps"), target_mask=kwargs.get("target_mask"),
+                             seed=kwargs.get("seed"))
+
+    def _integrate_density(self, x, conditions, integrate_kwargs, kwargs):
+        """integrate({"xz", "trace"}) with the Jacobian trace of the velocity (flow_matching.py:272-284,
+        diffusion_model.py:755-771) -> (xz_end (B,D), trace_end (B,))."""
+        from .density import integrate_density
+        if not self.built:
+            raise RuntimeError("network is not built; call build(xz_shape, conditions_shape) first")
+        if (conditions is None) != (self._C is None):
+            raise ValueError("network was built " + ("without" if self._C is None else "with") + " conditions")
+        if not x.is_cuda:
+            raise RuntimeError("bayesflow_b200 runs on CUDA tensors only (no CPU fallback)")
+        x = x.detach().to(torch.float32).contiguous()
+        if x.ndim != 2 or x.shape[-1] != self._D:
+            raise ValueError(f"expected (rows, {self._D}) inputs, got {tuple(x.shape)}")
+        fn = self._velocity_trace_fn(conditions, x.shape[0], kwargs)
+        ik = {k: v for k, v in integrate_kwargs.items() if k in self._INTEGRATE_KEYS}
+        info = {}
+        state = (x, torch.zeros(x.shape[0], 1, device=x.device, dtype=torch.float32))
+        xz, trace = integrate_density(fn, state, info=info, **ik)
+        info["evals"] = fn.evals
+        self.last_integration_info = info
+        return xz, trace.squeeze(-1)
 
     def _integrate_call(self, run, x, integrate_kwargs):
         ik = {k: v for k, v in integrate_kwargs.items() if k in self._INTEGRATE_KEYS}  # filter_kwargs, dict_utils.py:52-63
@@ -664,7 +711,8 @@ class FlowMatching(InferenceNetwork):
         return run.velocity(xz, float(np.float32(time)))
 
     # -- training (flow_matching.py:132-178) ------------------------------------------------------------------------------
-    def _loss_and_grads(self, x, conditions=None, sample_weight=None, stage="training", seed=None, world=1, backward=True):
+    def _loss_and_grads(self, x, conditions=None, sample_weight=None, stage="training", seed=None, world=1, backward=True,
+                        **kwargs):
         from .training import train_engine
         if self.drop_cond_prob > 0 or self.drop_target_prob > 0:
             raise NotImplementedError("drop_cond_prob / drop_target_prob > 0 are outside the accelerated training path")
@@ -683,30 +731,19 @@ class FlowMatching(InferenceNetwork):
             x, target = eng.interpolate(x0, x1, t)
         training = stage == "training"
         rate = float(self.subnet.dropout or 0.0) if training else 0.0
-        if seed is None:
-            self._drop_calls = getattr(self, "_drop_calls", 0) + 1
-            seed = (torch.initial_seed() * 0x9E3779B1 + self._drop_calls) & (2 ** 63 - 1)
+        seed = self._dropout_seed(seed)
         loss, _ = eng.step(x, t, conditions, target, row_weight=sample_weight, loss=self.loss_fn, dropout=rate, seed=seed,
                            global_batch=x.shape[0] * world, backward=backward)
         return loss
-
-    def compute_metrics(self, x, conditions=None, sample_weight=None, stage="training", **kwargs):
-        """{"loss": 0-d tensor}.  With grad mode on and stage == "training" the kernels also produce every parameter
-        gradient; ``loss.backward()`` then fills ``p.grad`` exactly like the reference's autograd path."""
-        from .training import _LossWithGrads, train_engine
-        backward = torch.is_grad_enabled() and stage == "training"
-        loss = self._loss_and_grads(x, conditions, sample_weight, stage=stage, seed=kwargs.get("seed"), backward=backward)
-        if backward:
-            eng = train_engine(self)
-            loss = _LossWithGrads.apply(loss, eng, *eng.params)
-        return {"loss": loss}
 
     def _forward(self, x, conditions=None, density=False, training=False, **kwargs):
         # flow_matching.py:254-294
         integrate_kwargs = self.integrate_kwargs | kwargs
         x = self._apply_targets(x, kwargs)
         if density:
-            raise NotImplementedError("log_prob (trace integration) is the next milestone (SURVEY.md §8f rank 1)")
+            # flow_matching.py:272-284
+            z, trace = self._integrate_density(x, conditions, integrate_kwargs | {"start_time": 1.0, "stop_time": 0.0}, kwargs)
+            return z, self.base_distribution.log_prob(z) + trace
         run = self._run(conditions, x.shape[0], kwargs)
         return self._integrate_call(run, x, integrate_kwargs | {"start_time": 1.0, "stop_time": 0.0})
 
@@ -716,7 +753,9 @@ class FlowMatching(InferenceNetwork):
         integrate_kwargs = self.integrate_kwargs | kwargs
         z = self._apply_targets(z, kwargs)
         if density:
-            raise NotImplementedError("log_prob (trace integration) is the next milestone (SURVEY.md §8f rank 1)")
+            # flow_matching.py:316-326
+            x, trace = self._integrate_density(z, conditions, integrate_kwargs | {"start_time": 0.0, "stop_time": 1.0}, kwargs)
+            return x, self.base_distribution.log_prob(z) - trace
         run = self._run(conditions, z.shape[0], kwargs)
         return self._integrate_call(run, z, integrate_kwargs | {"start_time": 0.0, "stop_time": 1.0})
 
@@ -734,6 +773,24 @@ class EDMNoiseSchedule:
         if self.log_snr_min >= self.log_snr_max:
             raise ValueError("min_log_snr must be less than max_log_snr.")
 
+    # Training-time schedule algebra on (B,) device vectors (float64, then cast): O(B) plumbing next to the O(B*W*W)
+    # kernels.  edm_noise_schedule.py:61-113, noise_schedule.py:100-119.
+    def get_log_snr(self, t, training):
+        if training:
+            loc, scale = 2 * 1.2, 2 * 1.2  # -2*p_mean, 2*p_std
+            snr = loc + scale * torch.erfinv(2 * (1 - t) - 1) * math.sqrt(2)
+            return torch.clip(snr, self.log_snr_min - 1, self.log_snr_max + 1)
+        smin, smax = self.sigma_min ** (1 / self.rho), self.sigma_max ** (1 / self.rho)
+        return -2 * self.rho * torch.log(smax + (1 - t) * (smin - smax))
+
+    def get_alpha_sigma(self, log_snr_t):
+        if self._variance_type == "preserving":
+            return torch.sqrt(torch.sigmoid(log_snr_t)), torch.sqrt(torch.sigmoid(-log_snr_t))
+        return torch.ones_like(log_snr_t), torch.sqrt(torch.exp(-log_snr_t))
+
+    def get_weights_for_snr(self, log_snr_t):
+        return 1 + torch.exp(-log_snr_t) / self.sigma_data ** 2
+
 
 class CosineNoiseSchedule:
     """schedules/cosine_noise_schedule.py:26-55."""
@@ -748,6 +805,25 @@ class CosineNoiseSchedule:
     def validate(self):
         if self.log_snr_min >= self.log_snr_max:
             raise ValueError("min_log_snr must be less than max_log_snr.")
+
+    # cosine_noise_schedule.py:57-82
+    def get_log_snr(self, t, training):
+        tt = self._t_min + (self._t_max - self._t_min) * t
+        return -2 * torch.log(torch.tan(math.pi * tt * 0.5)) + 2 * self._shift
+
+    def get_alpha_sigma(self, log_snr_t):
+        return torch.sqrt(torch.sigmoid(log_snr_t)), torch.sqrt(torch.sigmoid(-log_snr_t))
+
+    def get_weights_for_snr(self, log_snr_t):
+        if self._weighting == "sigmoid":
+            return torch.sigmoid(-log_snr_t + 2)
+        if self._weighting == "likelihood_weighting":
+            t = 2 / math.pi * torch.arctan(torch.exp((2 * self._shift - log_snr_t) * 0.5))
+            tt = self._t_min + (self._t_max - self._t_min) * t
+            dsnr_dt = -(2 * math.pi) / torch.sin(math.pi * tt) * (self._t_max - self._t_min)
+            beta = -(torch.exp(-log_snr_t) / (1 + torch.exp(-log_snr_t))) * dsnr_dt
+            return beta / torch.sigmoid(-log_snr_t)
+        return torch.ones_like(log_snr_t)
 
 
 def find_noise_schedule(arg, **kwargs):
@@ -809,6 +885,101 @@ class DiffusionModel(InferenceNetwork):
             s.shift, s.t_min, s.t_max = ns._shift, ns._t_min, ns._t_max
         return s
 
+    # -- training (diffusion_model.py:142-232) ---------------------------------------------------------------------------
+    def _x_pred_coefs(self, alpha, sigma, log_snr):
+        """convert_prediction_to_x (diffusion_model.py:351-405) is affine in (pred, z): x_pred = cP*pred + cZ*z."""
+        pt = self._prediction_type
+        if pt == "velocity":
+            return -sigma, alpha
+        if pt == "noise":
+            return -sigma / alpha, 1 / alpha
+        if pt == "F":
+            sd = getattr(self.noise_schedule, "sigma_data", 1.0)
+            e = torch.exp(-log_snr)
+            return torch.exp(-log_snr / 2) * sd / torch.sqrt(e + sd ** 2), (sd ** 2 * alpha) / (e + sd ** 2)
+        if pt == "x":
+            return torch.ones_like(alpha), torch.zeros_like(alpha)
+        return sigma ** 2 / alpha, 1 / alpha  # score
+
+    def _loss_and_grads(self, x, conditions=None, sample_weight=None, stage="training", seed=None, world=1, backward=True,
+                        fixed=None, row_offset=0, **kwargs):
+        """One DM training step through bfk_train_step.  Every loss_type is `w * mean_d (a*pred - target)^2` with a
+        per-row scalar `a` and a per-element target assembled here from the schedule; the network forward/backward,
+        the loss reduction and all parameter gradients are the C-ABI kernels.  `fixed=(u0, eps_t)` bypasses the RNG
+        (parity runs); `row_offset` is this rank's first GLOBAL row (low-discrepancy t uses the global index,
+        diffusion_model.py:159-161)."""
+        from .training import train_engine
+        if self.drop_cond_prob > 0 or self.drop_target_prob > 0:
+            raise NotImplementedError("drop_cond_prob / drop_target_prob > 0 are outside the accelerated training path")
+        if (conditions is None) != (self._C is None):
+            raise ValueError("network was built " + ("without" if self._C is None else "with") + " conditions")
+        if not torch.is_tensor(x) or not x.is_cuda:
+            raise RuntimeError("bayesflow_b200 runs on CUDA tensors only (no CPU fallback)")
+        eng = train_engine(self)
+        ns, dev, f64 = self.noise_schedule, x.device, torch.float64
+        B = x.shape[0]
+        Bg = B * world
+        if fixed is None:
+            u0 = torch.rand((1,), device=dev, dtype=torch.float32)
+            if world > 1:
+                torch.distributed.broadcast(u0, src=0)
+            eps = torch.randn(x.shape, device=dev, dtype=torch.float32)
+        else:
+            u0, eps = (torch.as_tensor(v, device=dev, dtype=torch.float32) for v in fixed)
+        sched_training = stage in ("training", "validation")
+        # fp32 t exactly as the reference forms it, then the schedule in double
+        tg = (u0 + torch.arange(0, Bg, device=dev, dtype=torch.float32) / float(Bg)) % 1
+        lam_g = ns.get_log_snr(tg.to(f64), training=sched_training)
+        w_mean = ns.get_weights_for_snr(lam_g).mean()  # the reference's (B,1)*(B,) broadcast: mean(w) * mean(per-row)
+        lam = lam_g[row_offset:row_offset + B].unsqueeze(-1)
+        alpha, sigma = ns.get_alpha_sigma(lam)
+        x64, eps64 = x.to(f64), eps.to(f64)
+        z = (alpha * x64 + sigma * eps64).to(torch.float32)
+        z64 = z.to(f64)
+        cP, cZ = self._x_pred_coefs(alpha, sigma, lam)
+        if self._loss_type == "noise":
+            a, target = -alpha * cP / sigma, eps64 - ((1 - alpha * cZ) / sigma) * z64
+        elif self._loss_type == "velocity":
+            a, target = -cP / sigma, (alpha * eps64 - sigma * x64) - ((alpha - cZ) / sigma) * z64
+        else:
+            sd = getattr(ns, "sigma_data", 1.0)
+            x1 = torch.sqrt(torch.exp(-lam) + sd ** 2) / (torch.exp(-lam / 2) * sd)
+            a, target = x1 * cP, x1 * (x64 - cZ * z64)
+        t_net = 2 * ((lam - ns.log_snr_min) / (ns.log_snr_max - ns.log_snr_min)) - 1  # _transform_log_snr, :711-717
+        row_w = w_mean.to(torch.float32).expand(B)
+        if sample_weight is not None:
+            row_w = row_w * sample_weight.reshape(-1).to(torch.float32)
+        rate = float(self.subnet.dropout or 0.0) if stage == "training" else 0.0
+        # The cotangent 2*w*a*resid enters the backward as an fp16 image; some (prediction, loss) pairs have |a| ~ 600 at
+        # the noisy end, so it is pre-scaled by a power of two (bounded on a fixed time grid, no device sync) and every
+        # gradient un-scaled by grad_scale - exact in floating point.
+        row_w, cot_scale = row_w * self._cotangent_scale(stage), self._cotangent_scale(stage)
+        loss, _ = eng.step(z, t_net.reshape(-1).to(torch.float32), conditions, target.to(torch.float32),
+                           pred_scale=a.reshape(-1).to(torch.float32), row_weight=row_w.contiguous(), loss="mse",
+                           dropout=rate, seed=self._dropout_seed(seed), global_batch=Bg, backward=backward,
+                           cotangent_scale=cot_scale)
+        return loss
+
+    def _cotangent_scale(self, stage):
+        key = (stage in ("training", "validation"), self._loss_type, self._prediction_type)
+        cache = self.__dict__.setdefault("_cot_scale_cache", {})
+        if key not in cache:
+            ns = self.noise_schedule
+            t = (torch.arange(0, 4096, dtype=torch.float64) + 0.5) / 4096
+            lam = ns.get_log_snr(t, training=key[0])
+            alpha, sigma = ns.get_alpha_sigma(lam)
+            cP, _ = self._x_pred_coefs(alpha, sigma, lam)
+            if self._loss_type == "noise":
+                a = alpha * cP / sigma
+            elif self._loss_type == "velocity":
+                a = cP / sigma
+            else:
+                sd = getattr(ns, "sigma_data", 1.0)
+                a = torch.sqrt(torch.exp(-lam) + sd ** 2) / (torch.exp(-lam / 2) * sd) * cP
+            bound = float(ns.get_weights_for_snr(lam).mean() * a.abs().max())
+            cache[key] = 2.0 ** -max(0, math.ceil(math.log2(max(bound, 1e-30))))
+        return cache[key]
+
     def velocity(self, xz, time, stochastic_solver=False, conditions=None, training=False, **kwargs):
         # diffusion_model.py:501-559
         if stochastic_solver or training:
@@ -818,6 +989,35 @@ class DiffusionModel(InferenceNetwork):
         run = self._run(conditions, xz.shape[0], kwargs)
         return run.velocity(xz, float(np.float32(time)))
 
+    def _velocity_trace_fn(self, conditions, B, kwargs):
+        fn = super()._velocity_trace_fn(conditions, B, kwargs)
+        L, sched = _lib.lib(), self._schedule_struct()
+        L.bfk_schedule_coefs.argtypes = [C.POINTER(_lib.Schedule), C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                         C.POINTER(C.c_double)]
+
+        def affine(time):
+            cz, cp, nt = C.c_double(), C.c_double(), C.c_double()
+            _lib.check(L.bfk_schedule_coefs(C.byref(sched), float(np.float32(time)), C.byref(cz), C.byref(cp), C.byref(nt)),
+                       "bfk_schedule_coefs")
+            return cz.value, cp.value, nt.value
+        fn.affine = affine
+        return fn
+
+    def _forward(self, x, conditions=None, density=False, training=False, **kwargs):
+        # diffusion_model.py:719-780
+        integrate_kwargs = {"start_time": 0.0, "stop_time": 1.0}
+        integrate_kwargs |= self.integrate_kwargs
+        integrate_kwargs |= kwargs
+        if integrate_kwargs["method"] in STOCHASTIC_METHODS:
+            # "Stochastic methods are not supported for density evaluation. Falling back to tsit5 ODE solver." (:733-739)
+            integrate_kwargs["method"] = "tsit5"
+        x = self._apply_targets(x, kwargs)
+        if density:
+            z, trace = self._integrate_density(x, conditions, integrate_kwargs, kwargs)
+            return z, self.base_distribution.log_prob(z) + trace
+        run = self._run(conditions, x.shape[0], kwargs)
+        return self._integrate_call(run, x, integrate_kwargs)
+
     def _inverse(self, z, conditions=None, density=False, training=False, **kwargs):
         # diffusion_model.py:782-869
         kwargs.pop("seed", None)
@@ -826,7 +1026,11 @@ class DiffusionModel(InferenceNetwork):
         integrate_kwargs |= kwargs
         z = self._apply_targets(z, kwargs)
         if density:
-            raise NotImplementedError("log_prob (trace integration) is the next milestone (SURVEY.md §8f rank 1)")
+            # diffusion_model.py:804-826 (stochastic methods fall back to tsit5 for the density)
+            if integrate_kwargs["method"] in STOCHASTIC_METHODS:
+                integrate_kwargs["method"] = "tsit5"
+            x, trace = self._integrate_density(z, conditions, integrate_kwargs, kwargs)
+            return x, self.base_distribution.log_prob(z) - trace
         if integrate_kwargs["method"] in STOCHASTIC_METHODS:
             raise NotImplementedError(
                 f"method={integrate_kwargs['method']!r}: SDE samplers are out of scope this round (SURVEY.md §8f rank 2); "

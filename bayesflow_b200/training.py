@@ -40,6 +40,10 @@ def _bind(L):
                                      C.c_void_p]
     L.bfk_adam_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
                                 C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p]
+    L.bfk_train_vjp.argtypes = [C.POINTER(_lib.NetConfig), C.POINTER(_lib.Weights), C.POINTER(TrainArgs), C.c_void_p,
+                                C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    L.bfk_rk_combine.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_float, C.c_int64, C.c_void_p,
+                                 C.c_void_p]
     L._train_bound = True
     return L
 
@@ -130,7 +134,8 @@ class TrainEngine:
         return t
 
     def step(self, x, t, conditions, target, *, pred_scale=None, row_weight=None, loss="mse", dropout=0.0, seed=0,
-             global_batch=None, backward=True, zero_grad=True, want_pred=False, want_loss=True, _dw_swap=0):
+             global_batch=None, backward=True, zero_grad=True, want_pred=False, want_loss=True, _dw_swap=0,
+             cotangent_scale=1.0):
         """One forward (+ loss, + backward).  Gradients are accumulated into ``self.grad`` (zeroed first unless
         ``zero_grad=False``) scaled by 1/(global_batch*D).  Returns (loss 0-d device tensor or None, pred or None)."""
         net = self.net
@@ -156,7 +161,10 @@ class TrainEngine:
         a.row_weight = row_weight.data_ptr() if row_weight is not None else None
         a.B, a.loss, a.dw_swap = B, {"mse": 0, "mae": 1}[loss], int(_dw_swap)
         a.dropout, a.seed = float(dropout), int(seed) & (2 ** 64 - 1)
-        a.loss_scale, a.grad_scale = 1.0 / (gb * (D if loss in ("mse", "mae") else 1)), 1.0 / (gb * D)
+        # `cotangent_scale` (a power of two already folded into row_weight by the caller) keeps the fp16 cotangent image
+        # in range; loss and gradients are un-scaled here
+        a.loss_scale = 1.0 / (gb * (D if loss in ("mse", "mae") else 1)) / cotangent_scale
+        a.grad_scale = 1.0 / (gb * D) / cotangent_scale
         ws = self._workspace(B, backward)
         if backward and zero_grad:
             self.grad.zero_()
@@ -167,6 +175,38 @@ class TrainEngine:
         _lib.check(rc, "bfk_train_step")
         self.launches += self.launches_per_step(backward)
         return loss_t, pred
+
+    # -- density path (density.py): forward that keeps its activations, then reverse passes w.r.t. the input ----------
+    def forward_keep(self, x, t, conditions):
+        """Forward only (no dropout); activations stay in the backward-sized workspace.  -> (pred, args, workspace)."""
+        net, D = self.net, self.net._D
+        x = self._f32(x)
+        B = x.shape[0]
+        if x.ndim != 2 or x.shape[1] != D:
+            raise ValueError(f"expected (rows, {D}) inputs, got {tuple(x.shape)}")
+        t = self._f32(t).reshape(-1)
+        cond = self._f32(conditions, (B, net._C)) if net._C else None
+        a = TrainArgs()
+        a.x, a.t, a.cond, a.B = x.data_ptr(), t.data_ptr(), (cond.data_ptr() if cond is not None else None), B
+        a.dropout, a.loss_scale, a.grad_scale = 0.0, 1.0, 1.0
+        a._keep = (x, t, cond)
+        ws = self._workspace(B, True)
+        pred = torch.empty(B, D, device=self.device, dtype=torch.float32)
+        _lib.check(self.L.bfk_train_step(C.byref(self.cfg), C.byref(self.w), None, C.byref(a), None, _lib.ptr(pred),
+                                         _lib.ptr(ws), ws.numel(), _lib.stream_ptr()), "bfk_train_step")
+        self.launches += self.launches_per_step(False) - 1
+        return pred, a, ws
+
+    def vjp(self, args, ws, *, col=-1, dout=None, trace=None, want_dx=False):
+        """One reverse pass over the activations of the last forward_keep (bfk_train_vjp)."""
+        dx = torch.empty(args.B, self.net._D, device=self.device, dtype=torch.float32) if want_dx else None
+        dout = self._f32(dout, (args.B, self.net._D)) if dout is not None else None
+        _lib.check(self.L.bfk_train_vjp(C.byref(self.cfg), C.byref(self.w), C.byref(args), _lib.ptr(dout), int(col),
+                                        _lib.ptr(dx), _lib.ptr(trace), _lib.ptr(ws), ws.numel(), _lib.stream_ptr()),
+                   "bfk_train_vjp")
+        Lb, merge = self.cfg.L, 1 if self.net._C else 0
+        self.launches += 3 + 3 * Lb + (4 if merge else 1) + 1
+        return dx
 
     def launches_per_step(self, backward=True):
         """Kernels bfk_train_step enqueues (counted from csrc/bfk_train_host.cuh)."""
@@ -262,7 +302,11 @@ class Trainer:
         """x: this rank's shard of the batch (or the (x0, x1, t, x, target) tuple).  Returns the GLOBAL mean loss as a
         0-d device tensor (after the all-reduce when world_size > 1)."""
         net, eng = self.net, self.eng
-        loss = net._loss_and_grads(x, conditions, sample_weight, stage="training", seed=seed, world=self.world)
+        extra = {}
+        if self.world > 1 and torch.is_tensor(x):
+            # global row index of this rank's first row (DiffusionModel's low-discrepancy times, diffusion_model.py:159-161)
+            extra["row_offset"] = torch.distributed.get_rank(self.group) * x.shape[0]
+        loss = net._loss_and_grads(x, conditions, sample_weight, stage="training", seed=seed, world=self.world, **extra)
         if self.world > 1:
             # ONE bucket: gradients and the loss ride the same all-reduce (SUM); scaling by 1/B_global happened on device
             buf = eng.grad

@@ -183,6 +183,21 @@ size_t bfk_train_workspace_bytes(const bfk_net_config* cfg, int64_t B, int32_t b
 int bfk_train_step(const bfk_net_config* cfg, const bfk_weights* weights, const bfk_weights* grads,
                    const bfk_train_args* args, float* loss, float* pred_out, void* workspace, size_t workspace_bytes,
                    void* stream);
+/* Vector-Jacobian product of the velocity network w.r.t. its input, for the density path
+ * (FlowMatching._velocity_trace, flow_matching.py:238-252 -> utils/jacobian/jacobian_trace.py:10-55 -> utils/jacobian/vjp.py:44-68;
+ * the reference runs D torch.autograd.grad passes per evaluation).  Consumes the activations the preceding
+ * bfk_train_step(cfg, weights, NULL, args, NULL, pred, workspace, ...) left in `workspace` (sized with backward = 1).
+ * Cotangent: dout (B,D), or the one-hot e_col when dout == NULL.  dx (B,D) is written when non-NULL; trace (B) gets
+ * dx[:,col] ADDED when non-NULL.  Touches no parameter gradient. */
+int bfk_train_vjp(const bfk_net_config* cfg, const bfk_weights* weights, const bfk_train_args* args, const float* dout,
+                  int32_t col, float* dx, float* trace, void* workspace, size_t workspace_bytes, void* stream);
+/* DiffusionModel probability-flow velocity as v = coefZ*z + coefP*pred(z, net_time) at time t, in double
+ * (diffusion_model.py:351-405, 466-489, 539-552, 711-717; schedules/*.py) - the host-side twin of the table builder. */
+int bfk_schedule_coefs(const bfk_schedule* sched, double t, double* coefZ, double* coefP, double* net_time);
+/* Runge-Kutta linear combination for host-driven integration (utils/integrate.py:47-54 add_scaled, :31-44, :98-105):
+ * out[i] = y[i] + h * sum_j coef[j] * k[j][i], j < n (n <= 8), accumulated left to right in fp32 like the reference. */
+int bfk_rk_combine(const float* y, const float* const* k, const float* coef, int32_t n, float h, int64_t numel, float* out,
+                   void* stream);
 /* x = t*x1 + (1-t)*x0, target = x1 - x0 (flow_matching.py:159-168) */
 int bfk_fm_interpolate(const float* x0, const float* x1, const float* t, int64_t B, int32_t D, float* x, float* target,
                        void* stream);

@@ -484,11 +484,51 @@ class OracleDiffusionModel:
             out = _mask(out, kwargs.get("target_mask", None))
         return out
 
-    def inverse(self, z, conditions=None, **kwargs):
-        # diffusion_model.py:782-869, deterministic branch :857-866
+    def _velocity_trace(self, xz, time, conditions=None, **kwargs):
+        # diffusion_model.py `_velocity_trace` -> utils/jacobian/jacobian_trace.py:10-55 (exact trace, D reverse passes)
+        with torch.enable_grad():
+            x = xz.detach().clone().requires_grad_(True)
+            v = self.velocity(x, time=time, stochastic_solver=False, conditions=conditions, **kwargs)
+            trace = torch.zeros(x.shape[:-1], dtype=x.dtype)
+            for d in range(x.shape[-1]):
+                (g,) = torch.autograd.grad(v[..., d].sum(), x, retain_graph=True)
+                trace = trace + g[..., d]
+        return v.detach(), trace.detach().unsqueeze(-1)
+
+    _IK = ("start_time", "stop_time", "method", "steps", "min_steps", "max_steps", "atol", "rtol", "info")
+
+    def _density_integrate(self, x, conditions, ik):
+        def deltas(time, xz, trace):
+            v, tr = self._velocity_trace(xz, time=time, conditions=conditions)
+            return {"xz": v, "trace": tr}
+        state = {"xz": x, "trace": torch.zeros(x.shape[:-1] + (1,), dtype=x.dtype)}
+        state = integrate(deltas, state, **ik)
+        return state["xz"], state["trace"].squeeze(-1)
+
+    def forward(self, x, conditions=None, density=False, **kwargs):
+        # diffusion_model.py:719-780
+        ik = {"start_time": 0.0, "stop_time": 1.0} | self.integrate_kwargs | kwargs
+        if ik["method"] not in ("euler", "rk45", "tsit5"):
+            ik["method"] = "tsit5"  # :733-739
+        ik = {k: v for k, v in ik.items() if k in self._IK}
+        if density:
+            z, trace = self._density_integrate(x, conditions, ik)
+            return z, self.base_distribution.log_prob(z) + trace
+
+        def deltas(time, xz):
+            return {"xz": self.velocity(xz, time=time, stochastic_solver=False, conditions=conditions)}
+        return integrate(deltas, {"xz": x}, **ik)["xz"]
+
+    def inverse(self, z, conditions=None, density=False, **kwargs):
+        # diffusion_model.py:782-869, deterministic branch :857-866; density branch :804-826
         kwargs.pop("seed", None)
         ik = {"start_time": 1.0, "stop_time": 0.0} | self.integrate_kwargs | kwargs
-        ik = {k: v for k, v in ik.items() if k in ("start_time", "stop_time", "method", "steps", "min_steps", "max_steps", "atol", "rtol", "info")}
+        ik = {k: v for k, v in ik.items() if k in self._IK}
+        if density:
+            if ik["method"] not in ("euler", "rk45", "tsit5"):
+                ik["method"] = "tsit5"
+            x, trace = self._density_integrate(z, conditions, ik)
+            return x, self.base_distribution.log_prob(z) - trace
         if ik["method"] not in ("euler", "rk45", "tsit5"):
             raise NotImplementedError("oracle covers the probability-flow ODE branch only")
 

@@ -95,3 +95,22 @@ def test_dm_schedule_scalars():
     cs = oracle.CosineNoiseSchedule()
     lam = cs.get_log_snr(t, training=False)
     np.testing.assert_allclose(lam[[0, 2]], [15.0, -15.0], rtol=1e-3)
+
+
+def test_oracle_density_matches_the_numerical_jacobian():
+    """Pin of the oracle's density path, as the reference pins its own (tests/test_networks/test_inference_networks.py:
+    114-150): log_density from forward(density=True) == log N(z) + log|det dz/dx| with the Jacobian of the WHOLE
+    integrated map taken numerically (autograd), FlowMatching and DiffusionModel."""
+    import oracle
+    torch.manual_seed(1)
+    D, C = 2, 3
+    p = oracle.perturb_params(oracle.init_params(D, C, (32, 32)))
+    x, c = torch.randn(3, D), torch.randn(3, C)
+    for orc in (oracle.OracleFlowMatching(p, D, subnet_kwargs={"widths": (32, 32), "dropout": 0.0}),
+                oracle.OracleDiffusionModel(p, D, subnet_kwargs={"widths": (32, 32), "dropout": 0.0})):
+        z, lp = orc.forward(x, c, density=True, method="rk45", steps=40)
+        for i in range(x.shape[0]):
+            J = torch.autograd.functional.jacobian(
+                lambda xi: orc.forward(xi[None], c[i:i + 1], method="rk45", steps=40)[0], x[i])
+            ref = orc.base_distribution.log_prob(z[i]) + torch.log(torch.abs(torch.det(J)))
+            assert abs(float(lp[i] - ref)) < 2e-3 * max(1.0, abs(float(ref))), (i, float(lp[i]), float(ref))
