@@ -505,4 +505,10 @@ def main():
 
 
 if __name__ == "__main__":
+    # stdout carries exactly ONE JSON line: libraries that write to fd 1 (NCCL prints its version banner there) are sent to
+    # stderr, and the line is written to the saved descriptor
+    sys.stdout.flush()
+    _real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(_real_stdout, "w")
     main()
