@@ -2,6 +2,7 @@
 // after bfk_train_host.cuh (uses its Arena / RC / nt_of helpers and fill_tableau from bfk_host.cu).
 #pragma once
 #include "bfk_layerwise.cuh"
+#include "bfk_lw_fused.cuh"
 
 namespace {
 
@@ -9,8 +10,9 @@ struct LwBufs {
   int KU, NO, has_merge;
   long long chunk, Rp;
   unsigned char *wx_pk, *wm_pk, *wo_pk, *wd_pk[BFK_MAX_BLOCKS];
-  unsigned char *x_img, *a_img, *h_img;
+  unsigned char *x_img, *a_img, *h_img, *h_img2;
   float *bo_pad, *pre_add, *post_add, *table, *P, *y, *ys, *k[BFK_MAX_STAGES];
+  float *stats[2], *gcol[BFK_MAX_BLOCKS], *ccol[BFK_MAX_BLOCKS], *gcol_o, *ccol_o;  // fused block kernels (bfk_lw_fused.cuh)
 };
 
 void plan_lw(const bfk_net_config* c, long long chunk, long long n_evals, long long G, Arena& ar, LwBufs& b) {
@@ -32,6 +34,11 @@ void plan_lw(const bfk_net_config* c, long long chunk, long long n_evals, long l
   b.x_img = (unsigned char*)ar.take(Rp * b.KU * 2);
   b.a_img = b.has_merge ? (unsigned char*)ar.take(Rp * W * 2) : nullptr;
   b.h_img = (unsigned char*)ar.take(Rp * W * 2);
+  b.h_img2 = (unsigned char*)ar.take(Rp * W * 2);
+  for (int i = 0; i < 2; ++i) b.stats[i] = (float*)ar.take(Rp * 2 * 4);
+  for (int l = 0; l < c->L; ++l) { b.gcol[l] = (float*)ar.take(W * 4); b.ccol[l] = (float*)ar.take(W * 4); }
+  b.gcol_o = (float*)ar.take((size_t)b.NO * 4);
+  b.ccol_o = (float*)ar.take((size_t)b.NO * 4);
   b.P = (float*)ar.take(Rp * W * 4);
   b.y = (float*)ar.take(Rp * c->D * 4);
   b.ys = (float*)ar.take(Rp * c->D * 4);
@@ -78,8 +85,30 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
   // ---- once per call: weights -> operand images, per-dataset and per-evaluation constants ---------------------------
   RC(bfk_pack_kmajor_t(w->x_k, W, D, KU, W, NTW, P16, b.wx_pk, st));
   if (b.has_merge) RC(bfk_pack_kmajor_t(w->m_k, W, W, W, W, NTW, P16, b.wm_pk, st));  // x half (concat) / whole (add)
-  for (int l = 0; l < L; ++l) RC(bfk_pack_kmajor_t(w->dense_k[l], W, W, W, W, NTW, P16, b.wd_pk[l], st));
-  RC(bfk_pack_kmajor_t(w->out_k, D, W, W, D, 64, P16, b.wo_pk, st));
+  static int fused = -1;
+  if (fused < 0) { const char* e = getenv("BFK_LW_FUSED"); fused = e ? atoi(e) : 1; }
+  const bool ln = c->norm == BFK_NORM_LAYER;
+  if (fused) {
+    // block l consumes the un-normalised output of block l-1: its LayerNorm is folded into W_l (bfk_lw_fused.cuh)
+    for (int l = 0; l < L; ++l)
+      lw_fold_pack_kernel<<<cdiv((size_t)W, 128), 128, 0, st>>>(w->dense_k[l], W, W, W, (l > 0 && ln) ? w->norm_g[l - 1] : nullptr,
+                                                              (l > 0 && ln) ? w->norm_b[l - 1] : nullptr, w->dense_b[l], NTW,
+                                                              b.wd_pk[l], b.gcol[l], b.ccol[l]);
+    // output projector: consumes the last block's un-normalised output with that block's LayerNorm folded in
+    lw_fold_pack_kernel<<<1, 128, 0, st>>>(w->out_k, W, NO, D, ln ? w->norm_g[L - 1] : nullptr, ln ? w->norm_b[L - 1] : nullptr,
+                                           w->out_b, 64, b.wo_pk, b.gcol_o, b.ccol_o);
+    CK(cudaGetLastError());
+    static bool attr = false;
+    if (!attr) {
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lw_fused_smem_bytes(256)));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lw_fused_smem_bytes(256)));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lw_fused_smem_bytes(256)));
+      attr = true;
+    }
+  } else {
+    for (int l = 0; l < L; ++l) RC(bfk_pack_kmajor_t(w->dense_k[l], W, W, W, W, NTW, P16, b.wd_pk[l], st));
+  }
+  if (!fused) RC(bfk_pack_kmajor_t(w->out_k, D, W, W, D, 64, P16, b.wo_pk, st));  // fused: folded pack above
   CK(cudaMemsetAsync(b.bo_pad, 0, (size_t)NO * 4, st));
   CK(cudaMemcpyAsync(b.bo_pad, w->out_b, (size_t)D * 4, cudaMemcpyDeviceToDevice, st));
   if (b.has_merge) {
@@ -105,27 +134,71 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
         ca.out = dm ? b.ys : nullptr; ca.ldo = D; ca.x_out = nullptr;
         ca.img = b.x_img; ca.KU8 = KU / 8; ca.rows = rows; ca.n_tiles = n_tiles; ca.D = D;
         lw_combine_kernel<<<dim3(KU / 8, tch), 128, 0, st>>>(ca);
-        RC(bfk_gemm(b.x_img, b.wx_pk, b.P, W, rows, W, KU, NTW, 1, 0, w->x_b, 1.f, P16, st));
-        if (b.has_merge) {
-          lw_act_kernel<<<dim3(W / 8, tch), 128, 0, st>>>(b.P, W, rows, n_tiles, W / 8, act, b.pre_add, row0, rpg, b.a_img);
-          RC(bfk_gemm(b.a_img, b.wm_pk, b.P, W, rows, W, W, NTW, 1, 0, nullptr, 1.f, P16, st));
-          lw_act_kernel<<<dim3(W / 8, tch), 128, 0, st>>>(b.P, W, rows, n_tiles, W / 8, act, b.post_add, row0, rpg, b.h_img);
+        int sms = bfk_num_sms();
+        if (sms <= 0) sms = 148;
+        const long long wtiles = n_tiles * (W / NTW);
+        const unsigned wgrid = (unsigned)(wtiles < sms ? wtiles : sms);
+        if (fused && (KU % P_KC) == 0) {
+          // x_proj (+ merge_proj) with their activations in the GEMM epilogue (time_mlp.py:131-140)
+          LwFusedArgs fa{};
+          fa.A = b.x_img; fa.B = b.wx_pk; fa.ccol = w->x_b; fa.out_img = b.has_merge ? b.a_img : b.h_img;
+          fa.rowbias = b.has_merge ? b.pre_add : nullptr; fa.row0 = row0; fa.rpg = rpg;
+          fa.M = rows; fa.N = W; fa.K = KU; fa.NT = NTW; fa.act = act; fa.idesc = umma_idesc_f16(G_TM, NTW, 0);
+          lw_block_gemm_kernel<LWF_ACT><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
+          if (b.has_merge) {
+            fa.A = b.a_img; fa.B = b.wm_pk; fa.ccol = nullptr; fa.out_img = b.h_img; fa.rowbias = b.post_add; fa.K = W;
+            lw_block_gemm_kernel<LWF_ACT><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
+          }
+          CK(cudaGetLastError());
         } else {
-          lw_act_kernel<<<dim3(W / 8, tch), 128, 0, st>>>(b.P, W, rows, n_tiles, W / 8, act, nullptr, row0, rpg, b.h_img);
+          RC(bfk_gemm(b.x_img, b.wx_pk, b.P, W, rows, W, KU, NTW, 1, 0, w->x_b, 1.f, P16, st));
+          if (b.has_merge) {
+            lw_act_kernel<<<dim3(W / 8, tch), 128, 0, st>>>(b.P, W, rows, n_tiles, W / 8, act, b.pre_add, row0, rpg, b.a_img);
+            RC(bfk_gemm(b.a_img, b.wm_pk, b.P, W, rows, W, W, NTW, 1, 0, nullptr, 1.f, P16, st));
+            lw_act_kernel<<<dim3(W / 8, tch), 128, 0, st>>>(b.P, W, rows, n_tiles, W / 8, act, b.post_add, row0, rpg, b.h_img);
+          } else {
+            lw_act_kernel<<<dim3(W / 8, tch), 128, 0, st>>>(b.P, W, rows, n_tiles, W / 8, act, nullptr, row0, rpg, b.h_img);
+          }
         }
-        for (int l = 0; l < L; ++l) {
-          RC(bfk_gemm(b.h_img, b.wd_pk[l], b.P, W, rows, W, W, NTW, 1, 0, w->dense_b[l], 1.f, P16, st));
-          BlockFwdArgs a{};
-          a.P = b.P; a.FB = trow + (size_t)l * W; a.FG = nullptr; a.fb_stride = 0;
-          a.prev = nullptr; a.pg = a.pb = nullptr; a.prev_img = c->residual ? b.h_img : nullptr;
-          a.gamma = c->norm == BFK_NORM_LAYER ? w->norm_g[l] : nullptr;
-          a.beta = c->norm == BFK_NORM_LAYER ? w->norm_b[l] : nullptr;
-          a.xhat = nullptr; a.rstd = nullptr; a.img = b.h_img; a.out_f32 = nullptr;
-          a.B = rows; a.R_pad = n_tiles * 128; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
-          a.drop_rate = 0.f; a.inv_keep = 1.f; a.seed = 0;
-          RC(launch_block_fwd(a, st));
+        const unsigned char* h_last = b.h_img;
+        if (fused) {
+          unsigned char* img[2] = {b.h_img, b.h_img2};
+          for (int l = 0; l < L; ++l) {
+            LwFusedArgs fa{};
+            fa.A = img[l & 1]; fa.B = b.wd_pk[l]; fa.out_img = img[(l + 1) & 1];
+            const bool fold = l > 0 && ln;
+            fa.stats_prev = fold ? b.stats[l & 1] : nullptr;
+            fa.gprev = fold ? w->norm_g[l - 1] : nullptr; fa.bprev = fold ? w->norm_b[l - 1] : nullptr;
+            fa.gcol = b.gcol[l]; fa.ccol = b.ccol[l]; fa.film = trow + (size_t)l * W;
+            fa.stats_out = ln ? b.stats[(l + 1) & 1] : nullptr;
+            fa.M = rows; fa.N = W; fa.K = W; fa.NT = NTW; fa.act = act; fa.residual = c->residual ? 1 : 0;
+            fa.idesc = umma_idesc_f16(G_TM, NTW, 0);
+            if (ln) CK(cudaMemsetAsync(fa.stats_out, 0, (size_t)n_tiles * 128 * 2 * 4, st));
+            lw_block_gemm_kernel<LWF_BLOCK><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
+          }
+          CK(cudaGetLastError());
+          LwFusedArgs fo{};
+          fo.A = img[L & 1]; fo.B = b.wo_pk; fo.stats_prev = ln ? b.stats[L & 1] : nullptr;
+          fo.gcol = b.gcol_o; fo.ccol = b.ccol_o; fo.out_f32 = b.k[s]; fo.ldo = NO;
+          fo.M = rows; fo.N = NO; fo.K = W; fo.NT = 64; fo.act = act; fo.idesc = umma_idesc_f16(G_TM, 64, 0);
+          const long long otiles = n_tiles * (NO / 64);
+          lw_block_gemm_kernel<LWF_OUT><<<(unsigned)(otiles < sms ? otiles : sms), LWF_THREADS, lw_fused_smem_bytes(64), st>>>(fo);
+          CK(cudaGetLastError());
+        } else {
+          for (int l = 0; l < L; ++l) {
+            RC(bfk_gemm(b.h_img, b.wd_pk[l], b.P, W, rows, W, W, NTW, 1, 0, w->dense_b[l], 1.f, P16, st));
+            BlockFwdArgs a{};
+            a.P = b.P; a.FB = trow + (size_t)l * W; a.FG = nullptr; a.fb_stride = 0;
+            a.prev = nullptr; a.pg = a.pb = nullptr; a.prev_img = c->residual ? b.h_img : nullptr;
+            a.gamma = c->norm == BFK_NORM_LAYER ? w->norm_g[l] : nullptr;
+            a.beta = c->norm == BFK_NORM_LAYER ? w->norm_b[l] : nullptr;
+            a.xhat = nullptr; a.rstd = nullptr; a.img = b.h_img; a.out_f32 = nullptr;
+            a.B = rows; a.R_pad = n_tiles * 128; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
+            a.drop_rate = 0.f; a.inv_keep = 1.f; a.seed = 0;
+            RC(launch_block_fwd(a, st));
+          }
         }
-        RC(bfk_gemm(b.h_img, b.wo_pk, b.k[s], NO, rows, NO, W, 64, 1, 0, b.bo_pad, 1.f, P16, st));
+        if (!fused) RC(bfk_gemm(h_last, b.wo_pk, b.k[s], NO, rows, NO, W, 64, 1, 0, b.bo_pad, 1.f, P16, st));
         if (dm || tmask)
           lw_finish_kernel<<<cdiv((size_t)rows * D, 256), 256, 0, st>>>(b.k[s], NO, dm ? b.ys : nullptr, D, trow + (size_t)L * W, tmask, rows, D);
       }

@@ -433,7 +433,10 @@ class _Run:
 class _RunLW:
     """One sampling call on the layer-wise path (bfk_sample_layerwise): same interface as _Run."""
 
-    CHUNK_ROWS = 8192  # rows per L2-resident chunk (activations of a chunk: 8192 x 1024 x (4 + 2) B = 48 MB)
+    # rows per chunk = 16 x 4736: at W = 1024 a chunk is 592 x 4 output tiles per layer = a whole number of waves of the
+    # 148 persistent CTAs, and enough tiles per CTA to hide the pipeline fill / last-epilogue tail (r01ae sweep: 439 us
+    # per evaluation per 8192 rows at 8192-row chunks, 300 us at 75776)
+    CHUNK_ROWS = 75776
 
     def __init__(self, engine, cond, rpg, target_mask):
         self.e, self.cond, self.rpg = engine, cond, rpg
@@ -483,7 +486,11 @@ class _RunLW:
             ev[1].record()
             e.kernel_events.append(ev)
         cfg = e.cfg
-        per_eval = 2 + (4 if cfg.C else 1) + 2 * cfg.L + 1 + (1 if (sched.model == 1 or self.tmask is not None) else 0)
+        # combine + x_proj (+ merge_proj) + L fused blocks + output projector (+ finish); the small stats memsets are not
+        # counted as kernels
+        per_eval = 1 + (2 if cfg.C else 1) + cfg.L + 1 + (1 if (sched.model == 1 or self.tmask is not None) else 0)
+        if ((cfg.D + 31) // 32 * 32) % 64:  # x_proj K (D padded to 32) not a multiple of 64: GEMM + activation kernels instead of the fused stage
+            per_eval += (2 if cfg.C else 1)
         n_chunks = (B + chunk - 1) // chunk
         e.launches += cfg.L + 4 + n_chunks * (int(t.numel()) * per_eval + (0 if velocity_only else n_steps))
         self.info = {"steps": n_steps, "evals": int(t.numel()), "rejected": 0, "path": "layerwise", "chunk_rows": chunk}
