@@ -90,13 +90,19 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
   const bool ln = c->norm == BFK_NORM_LAYER;
   if (fused) {
     // block l consumes the un-normalised output of block l-1: its LayerNorm is folded into W_l (bfk_lw_fused.cuh)
-    for (int l = 0; l < L; ++l)
-      lw_fold_pack_kernel<<<cdiv((size_t)W, 128), 128, 0, st>>>(w->dense_k[l], W, W, W, (l > 0 && ln) ? w->norm_g[l - 1] : nullptr,
-                                                              (l > 0 && ln) ? w->norm_b[l - 1] : nullptr, w->dense_b[l], NTW,
-                                                              b.wd_pk[l], b.gcol[l], b.ccol[l]);
+    const unsigned kslices = (unsigned)((W / 8 + 7) / 8);
+    for (int l = 0; l < L; ++l) {
+      CK(cudaMemsetAsync(b.gcol[l], 0, (size_t)W * 4, st));
+      CK(cudaMemsetAsync(b.ccol[l], 0, (size_t)W * 4, st));
+      lw_fold_pack_kernel<<<dim3(cdiv((size_t)W, 128), kslices), 128, 0, st>>>(
+          w->dense_k[l], W, W, W, (l > 0 && ln) ? w->norm_g[l - 1] : nullptr, (l > 0 && ln) ? w->norm_b[l - 1] : nullptr,
+          w->dense_b[l], NTW, b.wd_pk[l], b.gcol[l], b.ccol[l]);
+    }
     // output projector: consumes the last block's un-normalised output with that block's LayerNorm folded in
-    lw_fold_pack_kernel<<<1, 128, 0, st>>>(w->out_k, W, NO, D, ln ? w->norm_g[L - 1] : nullptr, ln ? w->norm_b[L - 1] : nullptr,
-                                           w->out_b, 64, b.wo_pk, b.gcol_o, b.ccol_o);
+    CK(cudaMemsetAsync(b.gcol_o, 0, (size_t)NO * 4, st));
+    CK(cudaMemsetAsync(b.ccol_o, 0, (size_t)NO * 4, st));
+    lw_fold_pack_kernel<<<dim3(1, kslices), 128, 0, st>>>(w->out_k, W, NO, D, ln ? w->norm_g[L - 1] : nullptr,
+                                                          ln ? w->norm_b[L - 1] : nullptr, w->out_b, 64, b.wo_pk, b.gcol_o, b.ccol_o);
     CK(cudaGetLastError());
     static bool attr = false;
     if (!attr) {

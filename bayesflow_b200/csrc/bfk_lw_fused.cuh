@@ -315,9 +315,11 @@ __global__ void lw_fold_pack_kernel(const float* __restrict__ Wk, int K, int N, 
   if (n >= N) return;
   const bool on = n < N_valid;  // W is (K, N_valid) row-major (in, out); columns up to N are zero padding
   const int K8 = K / 8;
-  float gs = 0.f, cs = (bias && on) ? bias[n] : 0.f;
+  // blockIdx.y = slice of 8 octets of K; partial column sums meet in gcol / ccol (zeroed by the host) through atomics
+  const int k8_lo = blockIdx.y * 8, k8_hi = min(K8, k8_lo + 8);
+  float gs = 0.f, cs = (bias && on && blockIdx.y == 0) ? bias[n] : 0.f;
   unsigned char* base = img + ((size_t)(n / NT) * K8 * NT + (size_t)(n % NT)) * 16;
-  for (int k8 = 0; k8 < K8; ++k8) {
+  for (int k8 = k8_lo; k8 < k8_hi; ++k8) {
     float v[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -332,8 +334,8 @@ __global__ void lw_fold_pack_kernel(const float* __restrict__ Wk, int K, int N, 
     for (int i = 0; i < 4; ++i) { const float2 f = __half22float2(hp[i]); gs += f.x + f.y; }
     *reinterpret_cast<uint4*>(base + (size_t)k8 * NT * 16) = pk;
   }
-  gcol[n] = gs;
-  ccol[n] = cs;
+  atomicAdd(gcol + n, gs);
+  atomicAdd(ccol + n, cs);
 }
 
 }  // namespace bfk

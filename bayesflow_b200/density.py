@@ -168,7 +168,7 @@ def integrate_density(fn, state, start_time=None, stop_time=None, min_steps: int
     raise RuntimeError(f"Type or value of `steps` not understood (steps={steps})")
 
 
-def _integrate_adaptive(fn, state, start_time, stop_time, min_steps, max_steps, method, info, atol, rtol):
+def _integrate_adaptive(fn, state, start_time, stop_time, min_steps, max_steps, method, info, atol, rtol, group=None):
     """integrate.py:291-406 with its global (all rows, both keys) step controller, fp32 controller arithmetic."""
     if max_steps <= min_steps:
         raise ValueError("Maximum number of steps must be greater than minimum number of steps.")
@@ -193,7 +193,10 @@ def _integrate_adaptive(fn, state, start_time, stop_time, min_steps, max_steps, 
         h = f32(np.sign(step_size) * np.clip(abs(step_size), min_h, max_h))
         new_state, new_time, new_k1, err = _step(fn, state, time, float(h), method, k1=k1, adaptive=True)
         max_abs = torch.stack([v.abs().max() for v in state]).max()
-        err_f, max_abs_f = (f32(v) for v in torch.stack([err, max_abs]).tolist())  # the one sync per trial step
+        ctl = torch.stack([err, max_abs])
+        if group is not None:  # rows sharded over ranks: the reference's GLOBAL controller needs the global maxima
+            torch.distributed.all_reduce(ctl, op=torch.distributed.ReduceOp.MAX, group=group)
+        err_f, max_abs_f = (f32(v) for v in ctl.tolist())  # the one sync per trial step
         scale = f32(f32(atol) + f32(rtol) * max_abs_f)
         ratio = f32(err_f / scale)
         with np.errstate(all="ignore"):

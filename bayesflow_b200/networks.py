@@ -502,14 +502,25 @@ class _RunLW:
     def run_fixed(self, x, times, hs, method):
         return self._call(self._check_x(x), times, hs, method, False)
 
-    def run_adaptive(self, *args, **kwargs):
-        raise NotImplementedError("adaptive step sizes on the layer-wise path (W > 256 or D > 8) are not built yet; pass an "
-                                  "integer `steps` (fixed) or a time grid (scheduled)")
+    def run_adaptive(self, x, start_time, stop_time, min_steps, max_steps, method, atol=1e-6, rtol=1e-4):
+        """integrate_adaptive (integrate.py:291-406) on the layer-wise path: every velocity evaluation is one
+        bfk_sample_layerwise(velocity_only) pass, the Runge-Kutta combinations are bfk_rk_combine, and the host runs the
+        reference's global step controller in fp32 (one (err, max|state|) read per trial step)."""
+        from .density import _integrate_adaptive
+        x = self._check_x(x)
+        evals = [0]
+
+        def fn(time, xz):
+            evals[0] += 1
+            return (self.velocity(xz, float(np.float32(time))),)
+
+        info = {}
+        (out,) = _integrate_adaptive(fn, (x,), float(start_time), float(stop_time), int(min_steps), int(max_steps), method,
+                                     info, atol, rtol, group=getattr(self.e.net, "step_control_group", None))
+        self.info = {"steps": int(info["steps"]), "rejected": int(info["rejected"]), "evals": evals[0], "path": "layerwise"}
+        return out
 
 
-# ======================================================================================================================
-# The reference's surface
-# ======================================================================================================================
 def _as_shape(batch_shape, kwargs):
     # utils/decorators.py:102-114 allow_batch_size
     if batch_shape is None and "batch_size" in kwargs:

@@ -90,7 +90,20 @@ def test_diffusion_model_probability_flow():
     assert rel_l2(out, ref) < TOL, rel_l2(out, ref)
 
 
-def test_adaptive_is_refused_loudly():
-    net, _ = make_pair(12, None, (128,) * 2)
-    with pytest.raises(NotImplementedError):
-        net(torch.randn(10, 12).cuda(), inverse=True)  # default: tsit5 adaptive
+@pytest.mark.parametrize("method", ["tsit5", "rk45"])
+def test_adaptive_on_the_layerwise_path(method):
+    """integrate_adaptive (integrate.py:291-406) with the reference's global controller; default FlowMatching sampling
+    (tsit5, adaptive) must work for wide / high-dimensional networks too."""
+    net, orc = make_pair(12, 5, (512,) * 2)
+    z, c = torch.randn(260, 12), grouped_conditions(260, 5, 65)
+    info = {}
+    ref = orc.inverse(z, c, method=method, steps="adaptive", info=info)
+    out = net(z.cuda(), conditions=c.cuda(), inverse=True, method=method, steps="adaptive")
+    assert rel_l2(out, ref) < TOL, rel_l2(out, ref)
+    got = net.last_integration_info
+    assert abs(got["steps"] - info["steps"]) <= max(2, 0.1 * info["steps"]), (got, info)
+    if method == "tsit5":  # the network default (defaults.py:52) takes the same route
+        out2 = net(z.cuda(), conditions=c.cuda(), inverse=True)
+        assert rel_l2(out2, out) < 1e-3  # not bit-identical: the LayerNorm statistics are fp32 atomics across column tiles
+    with pytest.raises(ValueError):
+        net(z.cuda(), conditions=c.cuda(), inverse=True, method="euler", steps="adaptive")

@@ -1,8 +1,10 @@
 #!/bin/bash
-TAG=${1:-r01w}
+# Layer-wise (cfg4) round: parity tests, one ncu --set full capture of the fused block kernel, launch list.
+TAG=${1:-r01ai}
 O=gpurun_out
 mkdir -p $O
-python -m pytest tests/test_gpu_layerwise.py -x -q > $O/${TAG}_pytest_lw.log 2>&1; echo "pytest lw exit=$?"; tail -8 $O/${TAG}_pytest_lw.log
-python -m pytest tests/test_gpu_train.py tests/test_gpu_gemm.py -x -q > $O/${TAG}_pytest.log 2>&1; echo "pytest train exit=$?"; tail -3 $O/${TAG}_pytest.log
-python bench.py --workload cfg5_fm_train --steps 10 --warmup 3 --no-cpu-baseline > $O/${TAG}_bench_train.json 2> $O/${TAG}_bench.err; echo "bench exit=$?"; cut -c1-200 $O/${TAG}_bench_train.json
-timeout 600 python bench.py --workload cfg4_wide_fm_euler100 --steps 2 --warmup 1 --no-train > $O/${TAG}_bench_cfg4.json 2>> $O/${TAG}_bench.err; echo "bench cfg4 exit=$?"; cut -c1-1800 $O/${TAG}_bench_cfg4.json; tail -3 $O/${TAG}_bench.err
+timeout 600 python -m pytest tests/test_gpu_layerwise.py -q --tb=short > $O/${TAG}_pytest_lw.log 2>&1; echo "pytest lw exit=$?"; tail -6 $O/${TAG}_pytest_lw.log | cut -c1-300
+B=75776 STEPS=3 python tools/gpu_lw_prof.py | tail -1
+B=75776 STEPS=2 ncu --set full --clock-control none --import-source on -k regex:lw_block_gemm -s 20 -c 1 -f -o $O/${TAG}_lw_block python tools/gpu_lw_prof.py > $O/${TAG}_ncu_full.log 2>&1; echo "ncu full exit=$?"
+B=75776 STEPS=2 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,lts__t_bytes.sum,sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed --cache-control none --clock-control none -c 300 --csv --log-file $O/${TAG}_lw_launches.csv python tools/gpu_lw_prof.py > $O/${TAG}_ncu_list.log 2>&1; echo "ncu list exit=$?"
+ls -la $O | grep $TAG
