@@ -131,13 +131,9 @@ __global__ void cond_prologue_kernel(bfk_net_config cfg, const unsigned char* __
   }
 }
 
-// DiffusionModel probability-flow velocity as  v = coefZ * z + coefP * pred  (diffusion_model.py:351-405, 466-489,
-// 539-552; noise_schedule.py:70-119; edm_noise_schedule.py:61-108; cosine_noise_schedule.py:60-82), evaluated in double.
-__host__ __device__ inline void schedule_coefs(const bfk_schedule& s, double t, double* coefZ, double* coefP, double* net_time) {
-  if (s.model == BFK_MODEL_FM) {
-    *coefZ = 0.0; *coefP = 1.0; *net_time = t;
-    return;
-  }
+// log-SNR lambda(t) and beta(t) = g(t)^2 of the inference-time schedule (noise_schedule.py:70-99;
+// edm_noise_schedule.py:61-108; cosine_noise_schedule.py:60-82), in double.
+__host__ __device__ inline void schedule_lam_beta(const bfk_schedule& s, double t, double* lam_out, double* beta_out) {
   double lam, beta;
   if (s.schedule == BFK_SCHED_EDM) {
     double smin = pow(s.sigma_min, 1.0 / s.rho), smax = pow(s.sigma_max, 1.0 / s.rho);
@@ -156,6 +152,19 @@ __host__ __device__ inline void schedule_coefs(const bfk_schedule& s, double t, 
     double factor = exp(-lam) / (1.0 + exp(-lam));
     beta = -factor * dsnr_dt;
   }
+  *lam_out = lam;
+  *beta_out = beta;
+}
+
+// DiffusionModel probability-flow velocity as  v = coefZ * z + coefP * pred  (diffusion_model.py:351-405, 466-489,
+// 539-552; noise_schedule.py:70-119; edm_noise_schedule.py:61-108; cosine_noise_schedule.py:60-82), evaluated in double.
+__host__ __device__ inline void schedule_coefs(const bfk_schedule& s, double t, double* coefZ, double* coefP, double* net_time) {
+  if (s.model == BFK_MODEL_FM) {
+    *coefZ = 0.0; *coefP = 1.0; *net_time = t;
+    return;
+  }
+  double lam, beta;
+  schedule_lam_beta(s, t, &lam, &beta);
   double alpha, sigma;
   if (s.exploding) { alpha = 1.0; sigma = sqrt(exp(-lam)); }
   else { alpha = sqrt(1.0 / (1.0 + exp(-lam))); sigma = sqrt(1.0 / (1.0 + exp(lam))); }

@@ -343,6 +343,17 @@ extern "C" int bfk_schedule_coefs(const bfk_schedule* sched, double t, double* c
   return 0;
 }
 
+// SDE sampling terms (diffusion_model.py:539-552 with stochastic_solver=True, :561-595): beta = g^2 and the coefficient
+// fz of the linear drift f = fz * z (-beta/2 variance preserving, 0 variance exploding).  With the probability-flow
+// velocity v_ode = f - beta/2 * score the reverse-SDE drift is f - beta * score = 2 * v_ode - fz * z.
+extern "C" int bfk_schedule_sde_terms(const bfk_schedule* sched, double t, double* fz, double* beta) {
+  if (!sched || !fz || !beta || sched->model != BFK_MODEL_DM) return fail(-87, "bfk_schedule_sde_terms: bad arguments");
+  double lam;
+  bfk::schedule_lam_beta(*sched, t, &lam, beta);
+  *fz = sched->exploding ? 0.0 : -0.5 * *beta;
+  return 0;
+}
+
 extern "C" int bfk_rk_combine(const float* y, const float* const* k, const float* coef, int32_t n, float h, int64_t numel,
                               float* out, void* stream_) {
   if (!y || !k || !coef || !out || n < 0 || n > 8 || numel <= 0) return fail(-85, "bfk_rk_combine: bad arguments");

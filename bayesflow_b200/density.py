@@ -43,7 +43,8 @@ _TSIT5_E = ((2, 0.007880878010261995), (4, 0.5823571654525552), (6, 0.0151515151
 
 def _combine(y: torch.Tensor, ks, pairs, h: float) -> torch.Tensor:
     """y + h * sum_j c_j k_j   (integrate.py:47-54) through bfk_rk_combine."""
-    L = _lib.lib()
+    from .training import _bind
+    L = _bind(_lib.lib())
     n = len(pairs)
     ptrs = (C.c_void_p * n)(*[ks[i].data_ptr() for i, _ in pairs])
     coef = (C.c_float * n)(*[float(np.float32(c)) for _, c in pairs])

@@ -1038,7 +1038,7 @@ class DiffusionModel(InferenceNetwork):
 
     def _inverse(self, z, conditions=None, density=False, training=False, **kwargs):
         # diffusion_model.py:782-869
-        kwargs.pop("seed", None)
+        seed = kwargs.pop("seed", None)
         integrate_kwargs = {"start_time": 1.0, "stop_time": 0.0}
         integrate_kwargs |= self.integrate_kwargs
         integrate_kwargs |= kwargs
@@ -1050,8 +1050,18 @@ class DiffusionModel(InferenceNetwork):
             x, trace = self._integrate_density(z, conditions, integrate_kwargs, kwargs)
             return x, self.base_distribution.log_prob(z) - trace
         if integrate_kwargs["method"] in STOCHASTIC_METHODS:
-            raise NotImplementedError(
-                f"method={integrate_kwargs['method']!r}: SDE samplers are out of scope this round (SURVEY.md §8f rank 2); "
-                f"pass one of {DETERMINISTIC_METHODS} for the probability-flow ODE")
+            # diffusion_model.py:830-856: reverse SDE (the network default is two_step_adaptive, defaults.py:50)
+            from .stochastic import ReverseSDE, integrate_stochastic
+            if not z.is_cuda:
+                raise RuntimeError("bayesflow_b200 runs on CUDA tensors only (no CPU fallback)")
+            run = self._run(conditions, z.shape[0], kwargs)
+            sde = ReverseSDE(self, run, kwargs.get("target_mask"))
+            keys = ("start_time", "stop_time", "steps", "method", "min_steps", "max_steps", "corrector_steps", "e_rel",
+                    "e_abs", "r", "adapt_safety", "noise_fn")
+            info = {}
+            out = integrate_stochastic(sde, run._check_x(z), seed=seed, info=info,
+                                       **{k: v for k, v in integrate_kwargs.items() if k in keys})
+            self.last_integration_info = info
+            return out
         run = self._run(conditions, z.shape[0], kwargs)
         return self._integrate_call(run, z, integrate_kwargs)

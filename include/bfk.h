@@ -194,6 +194,9 @@ int bfk_train_vjp(const bfk_net_config* cfg, const bfk_weights* weights, const b
 /* DiffusionModel probability-flow velocity as v = coefZ*z + coefP*pred(z, net_time) at time t, in double
  * (diffusion_model.py:351-405, 466-489, 539-552, 711-717; schedules/*.py) - the host-side twin of the table builder. */
 int bfk_schedule_coefs(const bfk_schedule* sched, double t, double* coefZ, double* coefP, double* net_time);
+/* Reverse-SDE terms at time t (DiffusionModel.velocity with stochastic_solver=True, diffusion_model.py:539-552, and
+ * diffusion_term, :561-595): beta = g(t)^2 and fz with f = fz*z; SDE drift = 2*v_ode - fz*z. */
+int bfk_schedule_sde_terms(const bfk_schedule* sched, double t, double* fz, double* beta);
 /* Runge-Kutta linear combination for host-driven integration (utils/integrate.py:47-54 add_scaled, :31-44, :98-105):
  * out[i] = y[i] + h * sum_j coef[j] * k[j][i], j < n (n <= 8), accumulated left to right in fp32 like the reference. */
 int bfk_rk_combine(const float* y, const float* const* k, const float* coef, int32_t n, float h, int64_t numel, float* out,

@@ -291,3 +291,152 @@ def integrate(fn, state, start_time=None, stop_time=None, min_steps=50, max_step
         return integrate_scheduled(fn, state, steps, method, **kwargs)
     else:
         raise RuntimeError(f"Type or value of `steps` not understood (steps={steps})")
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Stochastic half (integrate.py:495-743, 964-1165, 1254-1451): euler_maruyama and two_step_adaptive, no corrector.
+# `noise_fn(i, state) -> dict` replaces generate_noise (what the reference's z_history does on the JAX backend) so that a
+# parity run can feed the SAME normals to the oracle and to the CUDA path; default: torch.randn from `generator`.
+STOCHASTIC_METHODS = ["euler_maruyama", "sea", "shark", "two_step_adaptive", "langevin"]
+TRACE = None  # tests may set this to a list: (time, step, E2, accepted) per two_step_adaptive trial
+
+
+def generate_noise(state: StateDict, generator=None) -> StateDict:
+    # integrate.py:495-499
+    return {k: torch.randn(v.shape, dtype=v.dtype, generator=generator) for k, v in state.items()}
+
+
+def stochastic_adaptive_step_size_controller(state, drift, adaptive_factor, min_step_size=-float("inf"),
+                                             max_step_size=float("inf")):
+    # integrate.py:502-537
+    state_norm = torch.stack([torch.linalg.vector_norm(state[k], ord=2, dim=-1).max() for k in state])
+    drift_norm = torch.stack([torch.linalg.vector_norm(drift[k], ord=2, dim=-1).max() for k in state])
+    max_state_norm = torch.maximum(torch.tensor(1.0), state_norm.max() ** 2)
+    max_drift_norm = torch.maximum(torch.tensor(1.0), drift_norm.max() ** 2)
+    new_step_size = max_state_norm / max_drift_norm * adaptive_factor
+    return torch.clip(new_step_size, min_step_size, max_step_size)
+
+
+def euler_maruyama_step(drift_fn, diffusion_fn, state, time, step_size, noise, use_adaptive_step_size=False,
+                        min_step_size=-float("inf"), max_step_size=float("inf"), **_):
+    # integrate.py:540-596
+    drift = drift_fn(time, **state)
+    diffusion = diffusion_fn(time, **state)
+    new_step_size = step_size
+    if use_adaptive_step_size:
+        sign_step = torch.sign(torch.as_tensor(step_size))
+        new_step_size = stochastic_adaptive_step_size_controller(state, drift, max_step_size, min_step_size, max_step_size)
+        new_step_size = sign_step * torch.abs(new_step_size)
+    sqrt_step_size = torch.sqrt(torch.abs(torch.as_tensor(new_step_size, dtype=torch.float32)))
+    new_state = {}
+    for key, d in drift.items():
+        base = state[key] + new_step_size * d
+        if key in diffusion:
+            base = base + diffusion[key] * sqrt_step_size * noise[key]
+        new_state[key] = base
+    if use_adaptive_step_size:
+        return new_state, time + new_step_size, new_step_size, state
+    return new_state, time + new_step_size, new_step_size
+
+
+def two_step_adaptive_step(drift_fn, diffusion_fn, state, time, step_size, noise, last_state=None,
+                           use_adaptive_step_size=True, min_step_size=-float("inf"), max_step_size=float("inf"),
+                           e_rel=0.1, e_abs=None, r=0.9, adapt_safety=0.9, **_):
+    # integrate.py:599-743
+    state_euler, time_mid, _ = euler_maruyama_step(drift_fn, diffusion_fn, state, time, step_size, noise,
+                                                   use_adaptive_step_size=False)
+    drift_mid = drift_fn(time_mid, **state_euler)
+    diffusion_mid = diffusion_fn(time_mid, **state_euler)
+    sqrt_step_size = torch.sqrt(torch.abs(torch.as_tensor(step_size, dtype=torch.float32)))
+    state_euler_mid = {}
+    for key, d in drift_mid.items():
+        base = state[key] + step_size * d
+        if key in diffusion_mid:
+            base = base + diffusion_mid[key] * sqrt_step_size * noise[key]
+        state_euler_mid[key] = base
+    state_heun = {key: 0.5 * (state_euler[key] + state_euler_mid[key]) for key in state}
+    if not use_adaptive_step_size:
+        return state_heun, time_mid, step_size
+    if e_abs is None:
+        e_abs = 0.02576
+    at_min_step = bool(torch.abs(torch.as_tensor(step_size)) <= min_step_size)
+    max_error = torch.tensor(0.0)
+    for key in state:
+        error_estimate = torch.abs(state_heun[key] - state_euler[key])
+        delta = torch.maximum(torch.tensor(e_abs, dtype=torch.float32),
+                              e_rel * torch.maximum(torch.abs(state_euler[key]), torch.abs(last_state[key])))
+        max_error = torch.maximum(max_error, torch.max(error_estimate / (delta + 1e-10)))
+    E2 = 1 * max_error
+    accepted = bool(E2 <= 1.0) or at_min_step
+    E2_safe = torch.maximum(E2, torch.tensor(1e-10))
+    new_step_candidate = step_size * (adapt_safety * torch.pow(E2_safe, -r))
+    new_step_size = torch.clip(torch.abs(new_step_candidate), min_step_size, max_step_size)
+    new_step_size = torch.sign(torch.as_tensor(step_size)) * new_step_size
+    if TRACE is not None:
+        TRACE.append((float(time), float(step_size), float(E2), accepted))
+    if accepted:
+        return state_heun, time_mid, new_step_size, state_euler
+    return state, time, new_step_size, state
+
+
+def integrate_stochastic(drift_fn, diffusion_fn, state, start_time, stop_time, generator=None, steps=100,
+                         method="euler_maruyama", min_steps=50, max_steps=1_000, noise_fn=None, info=None, **kwargs):
+    # integrate.py:1254-1451 (dispatch), :964-1046 (fixed), :1049-1164 (adaptive); corrector_steps = 0
+    is_adaptive = isinstance(steps, str) and steps in ["adaptive", "dynamic"]
+    if is_adaptive:
+        if start_time is None or stop_time is None:
+            raise ValueError("Please provide start_time and stop_time for adaptive integration.")
+        if min_steps <= 0 or max_steps <= 0 or max_steps < min_steps:
+            raise ValueError("min_steps and max_steps must be positive, and max_steps >= min_steps.")
+        initial_step = (stop_time - start_time) / float(min_steps)
+        span_mag = abs(stop_time - start_time)
+        min_step_size, max_step_size = span_mag / max_steps, span_mag / min_steps
+    else:
+        if steps <= 0:
+            raise ValueError("Number of steps must be positive.")
+        initial_step = (stop_time - start_time) / float(int(steps))
+        min_step_size = max_step_size = initial_step
+    if method == "euler_maruyama":
+        step_fn = euler_maruyama_step
+    elif method == "two_step_adaptive":
+        step_fn = two_step_adaptive_step
+    elif method in ("sea", "shark", "langevin"):
+        raise NotImplementedError(f"oracle: method {method!r} is outside the restated subset")
+    else:
+        raise TypeError(f"Invalid integration method: {method!r}")
+    skw = {k: v for k, v in kwargs.items() if k in ("e_rel", "e_abs", "r", "adapt_safety")}
+    noise_of = noise_fn if noise_fn is not None else (lambda i, s: generate_noise(s, generator))
+    f32 = torch.float32
+    sign_dir = float(np.sign(stop_time - start_time))
+    i, time, step, last = 0, start_time, initial_step, state
+    if not is_adaptive:
+        while i < int(steps) and not _check_all_nans(state):
+            remaining = abs(stop_time - float(time))
+            dt = float(np.sign(float(step))) * min(abs(float(step)), remaining)
+            state, time, _ = step_fn(drift_fn, diffusion_fn, state, time, dt, noise_of(i, state), use_adaptive_step_size=False,
+                                     min_step_size=min_step_size, max_step_size=min(max_step_size, remaining), **skw)[:3]
+            step = initial_step
+            i += 1
+        if _check_all_nans(state):
+            raise RuntimeError(f"All values are NaNs in state during integration at {time}.")
+        return state
+    while True:
+        time_remaining = sign_dir * (stop_time - (float(time) + float(step)))
+        if not (time_remaining > 0 and i < max_steps) or _check_all_nans(state):
+            break
+        remaining = abs(stop_time - float(time))
+        dt = float(np.sign(float(step))) * min(abs(float(step)), remaining)
+        state, time, step, last = step_fn(drift_fn, diffusion_fn, state, time, torch.tensor(dt, dtype=f32), noise_of(i, state),
+                                          last_state=last, use_adaptive_step_size=True, min_step_size=min_step_size,
+                                          max_step_size=min(max_step_size, remaining), **skw)
+        i += 1
+    if _check_all_nans(state):
+        raise RuntimeError(f"All values are NaNs in state during integration at {time}.")
+    time_diff = stop_time - float(time)
+    if sign_dir * time_diff > 0:
+        state = step_fn(drift_fn, diffusion_fn, state, time, time_diff, noise_of(i, state), last_state=last,
+                        use_adaptive_step_size=False, min_step_size=min_step_size, max_step_size=sign_dir * time_diff, **skw)[0]
+        i += 1
+    if info is not None:
+        info["steps"] = i
+    return state

@@ -484,6 +484,17 @@ class OracleDiffusionModel:
             out = _mask(out, kwargs.get("target_mask", None))
         return out
 
+    def diffusion_term(self, xz, time, training=False, **kwargs):
+        # diffusion_model.py:561-595
+        log_snr_t = self.noise_schedule.get_log_snr(torch.as_tensor(time, dtype=xz.dtype), training=training)
+        while log_snr_t.ndim < xz.ndim:
+            log_snr_t = log_snr_t.unsqueeze(-1)
+        log_snr_t = torch.broadcast_to(log_snr_t, xz.shape[:-1] + (1,))
+        g = torch.sqrt(self.noise_schedule.get_drift(log_snr_t))
+        if not training:
+            g = _mask(g, kwargs.get("target_mask", None))
+        return g
+
     def _velocity_trace(self, xz, time, conditions=None, **kwargs):
         # diffusion_model.py `_velocity_trace` -> utils/jacobian/jacobian_trace.py:10-55 (exact trace, D reverse passes)
         with torch.enable_grad():
@@ -530,7 +541,17 @@ class OracleDiffusionModel:
             x, trace = self._density_integrate(z, conditions, ik)
             return x, self.base_distribution.log_prob(z) - trace
         if ik["method"] not in ("euler", "rk45", "tsit5"):
-            raise NotImplementedError("oracle covers the probability-flow ODE branch only")
+            # SDE branch, diffusion_model.py:830-856 (no corrector)
+            from .integrate import integrate_stochastic
+
+            def sde_drift(time, xz):
+                return {"xz": self.velocity(xz, time=time, stochastic_solver=True, conditions=conditions,
+                                            target_mask=kwargs.get("target_mask"))}
+
+            def sde_diffusion(time, xz):
+                return {"xz": self.diffusion_term(xz, time=time, target_mask=kwargs.get("target_mask"))}
+            extra = {k: kwargs[k] for k in ("noise_fn", "generator", "e_rel", "e_abs", "r", "adapt_safety") if k in kwargs}
+            return integrate_stochastic(sde_drift, sde_diffusion, {"xz": z}, **ik, **extra)["xz"]
 
         def deltas(time, xz):
             return {"xz": self.velocity(xz, time=time, stochastic_solver=False, conditions=conditions,

@@ -73,3 +73,23 @@ def test_all_nan_raises():
     fn = lambda t, x: {"x": x * float("nan")}
     with pytest.raises(RuntimeError):
         integrate(fn, {"x": torch.ones(3, 2)}, start_time=0.0, stop_time=1.0, steps="adaptive", method="rk45")
+
+
+# ---- stochastic half: the reference's Ornstein-Uhlenbeck weak-accuracy tests (tests/test_utils/test_integrate.py:96-222,
+# TOL_MEAN / TOL_VAR as there) restated for the oracle's euler_maruyama / two_step_adaptive
+@pytest.mark.parametrize("method,use_adapt", [("euler_maruyama", False), ("euler_maruyama", True),
+                                              ("two_step_adaptive", False), ("two_step_adaptive", True)])
+@pytest.mark.parametrize("backward", [False, True])
+def test_oracle_sde_ou_weak_means_and_vars(method, use_adapt, backward):
+    import numpy as np
+    from oracle.integrate import integrate_stochastic
+    a, sigma, x0, T, N = -1.0, 0.5, 1.2, 1.0, 10000
+    gen = torch.Generator().manual_seed(42)
+    out = integrate_stochastic(lambda t, x: {"x": a * x}, lambda t, x: {"x": torch.tensor([sigma])},
+                               {"x": torch.ones(N) * x0}, start_time=T if backward else 0.0, stop_time=0.0 if backward else T,
+                               steps="adaptive" if use_adapt else 200, generator=gen, method=method)["x"].numpy()
+    s = -1.0 if backward else 1.0
+    exp_mean = x0 * np.exp(s * a * T)
+    exp_var = sigma ** 2 * (np.exp(2.0 * s * a * T) - 1.0) / (2.0 * s * a)
+    np.testing.assert_allclose(out.mean(), exp_mean, atol=5e-2)
+    np.testing.assert_allclose(out.var(), exp_var, atol=5e-2)
