@@ -3,6 +3,7 @@
 // time_mlp.py:125-147, conditional_dense_block.py:114-131, torch_approximator.py:88-99 (autograd + optimizer step).
 #pragma once
 #include "bfk_train.cuh"
+#include "bfk_train_fused.cuh"
 
 namespace {
 
@@ -20,7 +21,8 @@ struct TrainBufs {
   int KU, KT, KTN, N1, NO, has_merge;
   long long Rp;
   unsigned char *u_img, *te_img, *w1_pk, *a1_img, *wm_f, *wm_b, *h0_img, *wo_f, *wo_b, *dout_img, *dP_img, *dV_img, *dh0pre_img;
-  float *w1, *b1, *h0pre, *m, *h0, *FB, *bo_pad, *out, *dH, *dte, *da1, *dW1, *db1;
+  float *w1, *b1, *h0pre, *m, *h0, *FB, *bo_pad, *out, *dH, *dte, *da1, *dW1, *db1, *stats;
+  unsigned char* v_img;  // fused forward (bfk_train_fused.cuh): un-normalised block output + row statistics
   unsigned char *wd_f[BFK_MAX_BLOCKS], *wd_b[BFK_MAX_BLOCKS], *wb_f[BFK_MAX_BLOCKS], *wb_b[BFK_MAX_BLOCKS], *h_img[BFK_MAX_BLOCKS];
   float *P[BFK_MAX_BLOCKS], *xhat[BFK_MAX_BLOCKS], *rstd[BFK_MAX_BLOCKS];
 };
@@ -64,6 +66,8 @@ void plan_train(const bfk_net_config* c, long long B, bool backward, Arena& ar, 
     b.h_img[l] = (unsigned char*)ar.take(Rp * W * 2);
   }
   b.FB = (float*)ar.take(Bs * W * 4);
+  b.v_img = (unsigned char*)ar.take(Rp * W * 2);
+  b.stats = (float*)ar.take(Rp * 2 * 4);
   b.wo_f = (unsigned char*)ar.take((size_t)b.NO * W * 2);
   b.wo_b = (unsigned char*)ar.take((size_t)W * b.NO * 2);
   b.bo_pad = (float*)ar.take((size_t)b.NO * 4);
@@ -205,6 +209,41 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
     act_pack_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.h0pre, W, B, n_tiles, W / 8, act, b.h0_img, b.h0);
   }
   CK(cudaGetLastError());
+  // Opt-in (BFK_TRAIN_FUSED=1): one tcgen05 kernel per block (Dense + FiLM contractions, block epilogue) + a normalisation
+  // pass, bfk_train_fused.cuh.  Parity-green but NOT faster yet (r01an/r01ao: 82.7 + 37.3 us per block against
+  // 25.6 + 25.6 + 71.5 us: the 16-warp epilogue issues 69 instructions per element), and its row statistics are fp32
+  // atomics (run-to-run bit differences) - so the three-kernel forward stays the default.
+  const char* fused_env = getenv("BFK_TRAIN_FUSED");
+  const int fused_fwd = fused_env ? atoi(fused_env) : 0;
+  const bool use_fused = fused_fwd && (W % TF_NT) == 0 && KT == TF_KC && !c->film_use_gamma;
+  if (use_fused) {
+    static bool attr = false;
+    if (!attr) {
+      CK(cudaFuncSetAttribute(train_block_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)train_fused_smem_bytes()));
+      attr = true;
+    }
+    int sms = bfk_num_sms();
+    if (sms <= 0) sms = 148;
+    const long long tiles = n_tiles * (W / TF_NT);
+    const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
+    for (int l = 0; l < L; ++l) {
+      RC(bfk_pack_kmajor_t(w->dense_k[l], W, W, W, W, TF_NT, P16, b.wd_f[l], st));
+      RC(bfk_pack_kmajor_t(w->film_b_k[l], W, T, KT, W, TF_NT, P16, b.wb_f[l], st));
+      CK(cudaMemsetAsync(b.stats, 0, (size_t)Rp * 2 * 4, st));
+      TrainFusedArgs fa{};
+      fa.A = l == 0 ? b.h0_img : b.h_img[l - 1]; fa.Bd = b.wd_f[l]; fa.T = b.te_img; fa.Bf = b.wb_f[l];
+      fa.bias_d = w->dense_b[l]; fa.bias_f = w->film_b_b[l]; fa.P = b.P[l]; fa.v_img = b.v_img; fa.stats = b.stats;
+      fa.M = B; fa.W = W; fa.act = act; fa.residual = c->residual ? 1 : 0; fa.layer = l;
+      fa.drop_rate = ta->dropout; fa.inv_keep = inv_keep; fa.seed = ta->seed;
+      fa.idesc = umma_idesc_f16(G_TM, TF_NT, 0);
+      train_block_gemm_kernel<<<grid, TF_THREADS, train_fused_smem_bytes(), st>>>(fa);
+      const bool lnl = c->norm == BFK_NORM_LAYER;
+      train_norm_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.v_img, b.stats, lnl ? w->norm_g[l] : nullptr,
+                                                            lnl ? w->norm_b[l] : nullptr, B, n_tiles, W / 8, c->norm, b.xhat[l],
+                                                            b.rstd[l], b.h_img[l]);
+      CK(cudaGetLastError());
+    }
+  } else
   for (int l = 0; l < L; ++l) {
     RC(bfk_pack_kmajor_t(w->dense_k[l], W, W, W, W, NTW, P16, b.wd_f[l], st));
     RC(bfk_pack_kmajor_t(w->film_b_k[l], W, T, KT, W, NTW, P16, b.wb_f[l], st));

@@ -211,7 +211,10 @@ class TrainEngine:
     def launches_per_step(self, backward=True):
         """Kernels bfk_train_step enqueues (counted from csrc/bfk_train_host.cuh)."""
         Lb, merge = self.cfg.L, 1 if self.net._C else 0
-        fwd = 2 + 2 + (4 if merge else 1) + 5 * Lb + 2 + 1
+        import os
+        fused = (os.environ.get("BFK_TRAIN_FUSED", "0") not in ("", "0") and self.cfg.W % 128 == 0
+                 and (self.cfg.T + 31) // 32 * 32 == 64 and not self.cfg.film_use_gamma)
+        fwd = 2 + 2 + (4 if merge else 1) + (4 if fused else 5) * Lb + 2 + 1  # fused: 2 packs + block GEMM + norm per block
         if not backward:
             return fwd
         bwd = 3 + Lb * 7 + (5 if merge else 1) + 3
