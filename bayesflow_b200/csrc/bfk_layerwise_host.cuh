@@ -35,7 +35,7 @@ void plan_lw(const bfk_net_config* c, long long chunk, long long n_evals, long l
   b.a_img = b.has_merge ? (unsigned char*)ar.take(Rp * W * 2) : nullptr;
   b.h_img = (unsigned char*)ar.take(Rp * W * 2);
   b.h_img2 = (unsigned char*)ar.take(Rp * W * 2);
-  for (int i = 0; i < 2; ++i) b.stats[i] = (float*)ar.take(Rp * 2 * 4);
+  for (int i = 0; i < 2; ++i) b.stats[i] = (float*)ar.take(Rp * 2 * 4 * ((W + 63) / 64));  // one plane per 64-column panel
   for (int l = 0; l < c->L; ++l) { b.gcol[l] = (float*)ar.take(W * 4); b.ccol[l] = (float*)ar.take(W * 4); }
   b.gcol_o = (float*)ar.take((size_t)b.NO * 4);
   b.ccol_o = (float*)ar.take((size_t)b.NO * 4);
@@ -90,19 +90,14 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
   const bool ln = c->norm == BFK_NORM_LAYER;
   if (fused) {
     // block l consumes the un-normalised output of block l-1: its LayerNorm is folded into W_l (bfk_lw_fused.cuh)
-    const unsigned kslices = (unsigned)((W / 8 + 7) / 8);
-    for (int l = 0; l < L; ++l) {
-      CK(cudaMemsetAsync(b.gcol[l], 0, (size_t)W * 4, st));
-      CK(cudaMemsetAsync(b.ccol[l], 0, (size_t)W * 4, st));
-      lw_fold_pack_kernel<<<dim3(cdiv((size_t)W, 128), kslices), 128, 0, st>>>(
+    for (int l = 0; l < L; ++l)
+      lw_fold_pack_kernel<<<cdiv((size_t)W, 32), dim3(32, 32), 0, st>>>(
           w->dense_k[l], W, W, W, (l > 0 && ln) ? w->norm_g[l - 1] : nullptr, (l > 0 && ln) ? w->norm_b[l - 1] : nullptr,
           w->dense_b[l], NTW, b.wd_pk[l], b.gcol[l], b.ccol[l]);
-    }
     // output projector: consumes the last block's un-normalised output with that block's LayerNorm folded in
-    CK(cudaMemsetAsync(b.gcol_o, 0, (size_t)NO * 4, st));
-    CK(cudaMemsetAsync(b.ccol_o, 0, (size_t)NO * 4, st));
-    lw_fold_pack_kernel<<<dim3(1, kslices), 128, 0, st>>>(w->out_k, W, NO, D, ln ? w->norm_g[L - 1] : nullptr,
-                                                          ln ? w->norm_b[L - 1] : nullptr, w->out_b, 64, b.wo_pk, b.gcol_o, b.ccol_o);
+    lw_fold_pack_kernel<<<cdiv((size_t)NO, 32), dim3(32, 32), 0, st>>>(w->out_k, W, NO, D, ln ? w->norm_g[L - 1] : nullptr,
+                                                                       ln ? w->norm_b[L - 1] : nullptr, w->out_b, 64, b.wo_pk,
+                                                                       b.gcol_o, b.ccol_o);
     CK(cudaGetLastError());
     static bool attr = false;
     if (!attr) {
@@ -178,15 +173,14 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
             fa.gcol = b.gcol[l]; fa.ccol = b.ccol[l]; fa.film = trow + (size_t)l * W;
             fa.stats_out = ln ? b.stats[(l + 1) & 1] : nullptr;
             fa.M = rows; fa.N = W; fa.K = W; fa.NT = NTW; fa.act = act; fa.residual = c->residual ? 1 : 0;
-            fa.idesc = umma_idesc_f16(G_TM, NTW, 0);
-            if (ln) CK(cudaMemsetAsync(fa.stats_out, 0, (size_t)n_tiles * 128 * 2 * 4, st));
+            fa.idesc = umma_idesc_f16(G_TM, NTW, 0); fa.rows_pad = n_tiles * 128;
             lw_block_gemm_kernel<LWF_BLOCK><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
           }
           CK(cudaGetLastError());
           LwFusedArgs fo{};
           fo.A = img[L & 1]; fo.B = b.wo_pk; fo.stats_prev = ln ? b.stats[L & 1] : nullptr;
           fo.gcol = b.gcol_o; fo.ccol = b.ccol_o; fo.out_f32 = b.k[s]; fo.ldo = NO;
-          fo.M = rows; fo.N = NO; fo.K = W; fo.NT = 64; fo.act = act; fo.idesc = umma_idesc_f16(G_TM, 64, 0);
+          fo.rows_pad = n_tiles * 128; fo.M = rows; fo.N = NO; fo.K = W; fo.NT = 64; fo.act = act; fo.idesc = umma_idesc_f16(G_TM, 64, 0);
           const long long otiles = n_tiles * (NO / 64);
           lw_block_gemm_kernel<LWF_OUT><<<(unsigned)(otiles < sms ? otiles : sms), LWF_THREADS, lw_fused_smem_bytes(64), st>>>(fo);
           CK(cudaGetLastError());

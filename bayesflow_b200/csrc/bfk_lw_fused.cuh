@@ -27,14 +27,15 @@ namespace bfk {
 struct LwFusedArgs {
   const unsigned char* A;      // v_prev (or h0) image: rows x K, K-major, row tile 128
   const unsigned char* B;      // folded weights (gamma_prev o W), row tile NT
-  const float* stats_prev;     // [rows][2] (sum, sumsq) of v_prev, or null: A already holds h_prev
+  const float* stats_prev;     // [K/64][rows_pad][2] partial (sum, sumsq) of v_prev per 64-column panel, or null: A holds h_prev
   const float* gprev;          // LayerNorm gamma / beta of the producer (null with stats_prev)
   const float* bprev;
   const float* gcol;           // [N] g_j (read only with stats_prev)
   const float* ccol;           // [N] c_j (bias folded in)
   const float* film;           // [N] FiLM shift of this block at this evaluation
   unsigned char* out_img;      // v image of this block
-  float* stats_out;            // [rows][2], zeroed by the host before the launch; null: no LayerNorm follows
+  float* stats_out;            // [N/64][rows_pad][2] partials, every entry written (no atomics: bit-reproducible); null: no LayerNorm follows
+  long long rows_pad;          // rows rounded up to 128 (stride of the partial-statistics planes)
   long long M;                 // valid rows
   int N, K, NT, act, residual;
   uint32_t idesc;
@@ -152,9 +153,14 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
       const long long row = m_tile * G_TM + q * 32 + lane;
       float mu = 0.f, rs = 1.f;
       if (folded && row < a.M) {
-        const float2 st = *reinterpret_cast<const float2*>(a.stats_prev + row * 2);
-        mu = st.x * inv_w;
-        const float var = fmaxf(fmaf(st.y, inv_w, -mu * mu), 0.f);
+        float sx = 0.f, sy = 0.f;
+        for (int pl = 0; pl < a.K / 64; ++pl) {  // fixed order: the row statistics are bit-reproducible
+          const float2 st = *reinterpret_cast<const float2*>(a.stats_prev + ((size_t)pl * a.rows_pad + row) * 2);
+          sx += st.x;
+          sy += st.y;
+        }
+        mu = sx * inv_w;
+        const float var = fmaxf(fmaf(sy, inv_w, -mu * mu), 0.f);
         rs = rsqrtf(var + LN_EPS);
       }
       const float mur = mu * rs;
@@ -261,9 +267,10 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
         __syncwarp();
         if (lane == 0) mbar_arrive(bar0 + 64 + 8 * acc);
       }
-      if (MODE == LWF_BLOCK && a.stats_out && n_chunks && row < a.M) {
-        atomicAdd(a.stats_out + row * 2, s1);
-        atomicAdd(a.stats_out + row * 2 + 1, s2);
+      if (MODE == LWF_BLOCK && a.stats_out && n_chunks) {
+        // one 64-column panel per warp and tile (NT <= 256): its partial sums go to plane (n_tile * NT / 64 + pq)
+        const int plane = n_tile * (NT / 64) + pq;
+        *reinterpret_cast<float2*>(a.stats_out + ((size_t)plane * a.rows_pad + row) * 2) = make_float2(s1, s2);
       }
     }
   }
@@ -286,9 +293,14 @@ __global__ void lw_norm_img_kernel(const unsigned char* __restrict__ in_img, con
     const long long r = tile * 128 + threadIdx.x;
     float v[8];
     if (r < rows) {
-      const float2 st = *reinterpret_cast<const float2*>(stats + r * 2);
-      const float mu = st.x * inv_w;
-      const float rs = rsqrtf(fmaxf(fmaf(st.y, inv_w, -mu * mu), 0.f) + LN_EPS);
+      float sx = 0.f, sy = 0.f;
+      for (int pl = 0; pl < K8 / 8; ++pl) {
+        const float2 st = *reinterpret_cast<const float2*>(stats + ((size_t)pl * n_tiles * 128 + r) * 2);
+        sx += st.x;
+        sy += st.y;
+      }
+      const float mu = sx * inv_w;
+      const float rs = rsqrtf(fmaxf(fmaf(sy, inv_w, -mu * mu), 0.f) + LN_EPS);
       const uint4 raw = *reinterpret_cast<const uint4*>(in_img + img_off(r, k8, K8));
       const __half2* hp = reinterpret_cast<const __half2*>(&raw);
 #pragma unroll
@@ -308,34 +320,44 @@ __global__ void lw_norm_img_kernel(const unsigned char* __restrict__ in_img, con
 // Once per call and block: Wf = fp16(gamma_prev o W) in the B-operand image P[n/NT][k/8][n%NT][k%8],
 // g_j = sum_k float(Wf_kj) (the very values the tensor cores multiply, so that r*(acc - mu*g) cancels exactly for a
 // constant row), c_j = b_j + sum_k beta_prev_k W_kj.  One thread per output column n; W is (K, N) row-major (in, out).
-__global__ void lw_fold_pack_kernel(const float* __restrict__ Wk, int K, int N, int N_valid, const float* __restrict__ gprev,
-                                    const float* __restrict__ bprev, const float* __restrict__ bias, int NT,
-                                    unsigned char* __restrict__ img, float* __restrict__ gcol, float* __restrict__ ccol) {
-  const int n = blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= N) return;
+__global__ void __launch_bounds__(1024) lw_fold_pack_kernel(const float* __restrict__ Wk, int K, int N, int N_valid,
+                                                            const float* __restrict__ gprev, const float* __restrict__ bprev,
+                                                            const float* __restrict__ bias, int NT, unsigned char* __restrict__ img,
+                                                            float* __restrict__ gcol, float* __restrict__ ccol) {
+  // block = 32 columns (threadIdx.x) x 32 slices of K (threadIdx.y); the slice partials meet in shared memory and are
+  // summed in slice order by the y = 0 threads, so g and c are bit-reproducible
+  __shared__ float sg[32][33], sc[32][33];
+  const int n = blockIdx.x * 32 + threadIdx.x;
   const bool on = n < N_valid;  // W is (K, N_valid) row-major (in, out); columns up to N are zero padding
   const int K8 = K / 8;
-  // blockIdx.y = slice of 8 octets of K; partial column sums meet in gcol / ccol (zeroed by the host) through atomics
-  const int k8_lo = blockIdx.y * 8, k8_hi = min(K8, k8_lo + 8);
-  float gs = 0.f, cs = (bias && on && blockIdx.y == 0) ? bias[n] : 0.f;
-  unsigned char* base = img + ((size_t)(n / NT) * K8 * NT + (size_t)(n % NT)) * 16;
-  for (int k8 = k8_lo; k8 < k8_hi; ++k8) {
-    float v[8];
+  float gs = 0.f, cs = 0.f;
+  if (n < N) {
+    unsigned char* base = img + ((size_t)(n / NT) * K8 * NT + (size_t)(n % NT)) * 16;
+    for (int k8 = threadIdx.y; k8 < K8; k8 += 32) {
+      float v[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int k = k8 * 8 + i;
-      const float w = on ? Wk[(size_t)k * N_valid + n] : 0.f;
-      v[i] = gprev ? gprev[k] * w : w;
-      if (bprev) cs = fmaf(bprev[k], w, cs);
+      for (int i = 0; i < 8; ++i) {
+        const int k = k8 * 8 + i;
+        const float w = on ? Wk[(size_t)k * N_valid + n] : 0.f;
+        v[i] = gprev ? gprev[k] * w : w;
+        if (bprev) cs = fmaf(bprev[k], w, cs);
+      }
+      const uint4 pk = pack8(v);
+      const __half2* hp = reinterpret_cast<const __half2*>(&pk);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { const float2 f = __half22float2(hp[i]); gs += f.x + f.y; }
+      *reinterpret_cast<uint4*>(base + (size_t)k8 * NT * 16) = pk;
     }
-    const uint4 pk = pack8(v);
-    const __half2* hp = reinterpret_cast<const __half2*>(&pk);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) { const float2 f = __half22float2(hp[i]); gs += f.x + f.y; }
-    *reinterpret_cast<uint4*>(base + (size_t)k8 * NT * 16) = pk;
   }
-  atomicAdd(gcol + n, gs);
-  atomicAdd(ccol + n, cs);
+  sg[threadIdx.y][threadIdx.x] = gs;
+  sc[threadIdx.y][threadIdx.x] = cs;
+  __syncthreads();
+  if (threadIdx.y == 0 && n < N) {
+    float g = 0.f, c = (bias && on) ? bias[n] : 0.f;
+    for (int y = 0; y < 32; ++y) { g += sg[y][threadIdx.x]; c += sc[y][threadIdx.x]; }
+    gcol[n] = g;
+    ccol[n] = c;
+  }
 }
 
 }  // namespace bfk

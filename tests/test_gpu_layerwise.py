@@ -104,6 +104,6 @@ def test_adaptive_on_the_layerwise_path(method):
     assert abs(got["steps"] - info["steps"]) <= max(2, 0.1 * info["steps"]), (got, info)
     if method == "tsit5":  # the network default (defaults.py:52) takes the same route
         out2 = net(z.cuda(), conditions=c.cuda(), inverse=True)
-        assert rel_l2(out2, out) < 1e-3  # not bit-identical: the LayerNorm statistics are fp32 atomics across column tiles
+        assert torch.equal(out2, out)  # bit-reproducible: the LayerNorm statistics are per-panel partials, no atomics
     with pytest.raises(ValueError):
         net(z.cuda(), conditions=c.cuda(), inverse=True, method="euler", steps="adaptive")
