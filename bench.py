@@ -310,7 +310,7 @@ def run_ours(args, name, w):
                 "gpu_launches": launches,
                 "roofline": {"bound": "tensor", "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",
                              "frac": (achieved / peaks["tflops"]) if achieved else None, "traffic": ncu_traffic(name),
-                             "kernel": ("bfk::gemm_kernel + block kernels (layer-wise path: all launches of one call)"
+                             "kernel": ("bfk::lw_block_gemm_kernel<0> (fused Dense+block epilogue, 83 % of the call) + x_proj/merge/out stages: all launches of one bfk_sample_layerwise call"
                                         if net._engine.layerwise else "bfk::sampler_kernel"), "kernel_ms": k_avg_ms, "kernel_share_of_step": k_avg_ms * args.steps / total_ms,
                              "flop_per_draw_naive": fpd, "peak_source": peaks["source"],
                              "hbm_gbs_algorithmic": (N * S * D * 8) / (k_avg_ms * 1e-3) / 1e9 if kern_ms else None},
