@@ -101,9 +101,12 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
     CK(cudaGetLastError());
     static bool attr = false;
     if (!attr) {
-      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lw_fused_smem_bytes(256)));
-      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lw_fused_smem_bytes(256)));
-      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lw_fused_smem_bytes(256)));
+      const int sm = (int)lw_fused_smem_bytes(256);
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_MISH>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_SILU>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_ACT, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_OUT, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
       attr = true;
     }
   } else {
@@ -145,10 +148,10 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
           fa.A = b.x_img; fa.B = b.wx_pk; fa.ccol = w->x_b; fa.out_img = b.has_merge ? b.a_img : b.h_img;
           fa.rowbias = b.has_merge ? b.pre_add : nullptr; fa.row0 = row0; fa.rpg = rpg;
           fa.M = rows; fa.N = W; fa.K = KU; fa.NT = NTW; fa.act = act; fa.idesc = umma_idesc_f16(G_TM, NTW, 0);
-          lw_block_gemm_kernel<LWF_ACT><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
+          lw_block_gemm_kernel<LWF_ACT, -1><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
           if (b.has_merge) {
             fa.A = b.a_img; fa.B = b.wm_pk; fa.ccol = nullptr; fa.out_img = b.h_img; fa.rowbias = b.post_add; fa.K = W;
-            lw_block_gemm_kernel<LWF_ACT><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
+            lw_block_gemm_kernel<LWF_ACT, -1><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
           }
           CK(cudaGetLastError());
         } else {
@@ -174,7 +177,9 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
             fa.stats_out = ln ? b.stats[(l + 1) & 1] : nullptr;
             fa.M = rows; fa.N = W; fa.K = W; fa.NT = NTW; fa.act = act; fa.residual = c->residual ? 1 : 0;
             fa.idesc = umma_idesc_f16(G_TM, NTW, 0); fa.rows_pad = n_tiles * 128;
-            lw_block_gemm_kernel<LWF_BLOCK><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
+            if (act == BFK_ACT_MISH) lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_MISH><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
+            else if (act == BFK_ACT_SILU) lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_SILU><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
+            else lw_block_gemm_kernel<LWF_BLOCK, -1><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
           }
           CK(cudaGetLastError());
           LwFusedArgs fo{};
@@ -182,7 +187,7 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
           fo.gcol = b.gcol_o; fo.ccol = b.ccol_o; fo.out_f32 = b.k[s]; fo.ldo = NO;
           fo.rows_pad = n_tiles * 128; fo.M = rows; fo.N = NO; fo.K = W; fo.NT = 64; fo.act = act; fo.idesc = umma_idesc_f16(G_TM, 64, 0);
           const long long otiles = n_tiles * (NO / 64);
-          lw_block_gemm_kernel<LWF_OUT><<<(unsigned)(otiles < sms ? otiles : sms), LWF_THREADS, lw_fused_smem_bytes(64), st>>>(fo);
+          lw_block_gemm_kernel<LWF_OUT, -1><<<(unsigned)(otiles < sms ? otiles : sms), LWF_THREADS, lw_fused_smem_bytes(64), st>>>(fo);
           CK(cudaGetLastError());
         } else {
           for (int l = 0; l < L; ++l) {

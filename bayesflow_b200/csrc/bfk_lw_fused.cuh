@@ -21,6 +21,7 @@
 
 #include "bfk_gemm.cuh"
 #include "bfk_train.cuh"
+#include "bfk_fast_epilogue.cuh"
 
 namespace bfk {
 
@@ -53,7 +54,67 @@ __host__ __device__ inline size_t lw_fused_smem_bytes(int NT) {
   return (size_t)P_STAGES * (P_KC * G_TM * 2 + P_KC * NT * 2) + (size_t)2 * F_VEC * NT * 4 + 256;
 }
 
-template <int MODE>
+// LWF_BLOCK arithmetic of one 16-column chunk in packed fp32 (FFMA2 / FADD2, staged MUFU: bfk_fast_epilogue.cuh), for the
+// activations that have a packed form.  vc: 16 accumulator columns; rc: the 16 skip values (fp16); vb: the five staged
+// per-column vectors.  Adds to the packed row statistics and returns the two 16-byte chunks of the next operand image.
+template <int ACT>
+__device__ __forceinline__ void lwf_block_chunk16(const float* vc, const uint4* rc, const float* vb, int NT, int c0, float rs,
+                                                  float mur, bool residual, float2& s1, float2& s2, uint4* out) {
+  const float2 rs2 = f2(rs), nmur2 = f2(-mur);
+  float2 P[8];
+#pragma unroll
+  for (int jj = 0; jj < 2; ++jj) {
+    const float4 g0 = *reinterpret_cast<const float4*>(vb + 0 * NT + c0 + jj * 8);
+    const float4 g1 = *reinterpret_cast<const float4*>(vb + 0 * NT + c0 + jj * 8 + 4);
+    const float4 k0 = *reinterpret_cast<const float4*>(vb + 1 * NT + c0 + jj * 8);
+    const float4 k1 = *reinterpret_cast<const float4*>(vb + 1 * NT + c0 + jj * 8 + 4);
+    const float2 gg[4] = {make_float2(g0.x, g0.y), make_float2(g0.z, g0.w), make_float2(g1.x, g1.y), make_float2(g1.z, g1.w)};
+    const float2 cc[4] = {make_float2(k0.x, k0.y), make_float2(k0.z, k0.w), make_float2(k1.x, k1.y), make_float2(k1.z, k1.w)};
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      const int i = jj * 4 + p;
+      // P = r (acc - mu g) + c
+      P[i] = __ffma2_rn(rs2, make_float2(vc[2 * i], vc[2 * i + 1]), __ffma2_rn(nmur2, gg[p], cc[p]));
+    }
+  }
+  act2x8<ACT>(P);
+#pragma unroll
+  for (int jj = 0; jj < 2; ++jj) {
+    const float4 f0 = *reinterpret_cast<const float4*>(vb + 2 * NT + c0 + jj * 8);
+    const float4 f1 = *reinterpret_cast<const float4*>(vb + 2 * NT + c0 + jj * 8 + 4);
+    const float2 ff[4] = {make_float2(f0.x, f0.y), make_float2(f0.z, f0.w), make_float2(f1.x, f1.y), make_float2(f1.z, f1.w)};
+    uint32_t pk[4];
+    if (residual) {
+      const float4 a0 = *reinterpret_cast<const float4*>(vb + 3 * NT + c0 + jj * 8);
+      const float4 a1 = *reinterpret_cast<const float4*>(vb + 3 * NT + c0 + jj * 8 + 4);
+      const float4 b0 = *reinterpret_cast<const float4*>(vb + 4 * NT + c0 + jj * 8);
+      const float4 b1 = *reinterpret_cast<const float4*>(vb + 4 * NT + c0 + jj * 8 + 4);
+      const float2 gp[4] = {make_float2(a0.x, a0.y), make_float2(a0.z, a0.w), make_float2(a1.x, a1.y), make_float2(a1.z, a1.w)};
+      const float2 bp[4] = {make_float2(b0.x, b0.y), make_float2(b0.z, b0.w), make_float2(b1.x, b1.y), make_float2(b1.z, b1.w)};
+      const uint32_t su[4] = {rc[jj].x, rc[jj].y, rc[jj].z, rc[jj].w};
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        // h_prev = gamma (v_prev - mu) r + beta
+        const float2 hp = __ffma2_rn(gp[p], __ffma2_rn(unpack2f<false>(su[p]), rs2, nmur2), bp[p]);
+        const float2 u = __fadd2_rn(__fadd2_rn(P[jj * 4 + p], ff[p]), hp);
+        s1 = __fadd2_rn(s1, u);
+        s2 = __ffma2_rn(u, u, s2);
+        pk[p] = pack2f<false>(u);
+      }
+    } else {
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        const float2 u = __fadd2_rn(P[jj * 4 + p], ff[p]);
+        s1 = __fadd2_rn(s1, u);
+        s2 = __ffma2_rn(u, u, s2);
+        pk[p] = pack2f<false>(u);
+      }
+    }
+    out[jj] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+  }
+}
+
+template <int MODE, int ACT>
 __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwFusedArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -181,6 +242,7 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
       tc_fence_after();
       const uint32_t t_acc = tmem_base + acc * acc_stride + ((uint32_t)(q * 32) << 16);
       float s1 = 0.f, s2 = 0.f;
+      float2 s1p = make_float2(0.f, 0.f), s2p = make_float2(0.f, 0.f);  // packed path
       // one chunk: wait for its accumulator columns, put the next chunk's loads in flight, then the block arithmetic
       auto step = [&](int ci, float* vc, uint4* rc, float* vn, uint4* rn) {
         tmem_ld_wait16(vc);
@@ -195,6 +257,13 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
         }
         const int c0 = col_of(ci);
         const int o0 = (n_tile * NT + c0) / 8;
+        if (MODE == LWF_BLOCK && ACT >= 0) {  // packed-fp32 arithmetic for mish / silu (compile-time activation)
+          uint4 o16[2];
+          lwf_block_chunk16<(ACT >= 0 ? ACT : 0)>(vc, rc, vb, NT, c0, rs, mur, a.residual != 0, s1p, s2p, o16);
+          *reinterpret_cast<uint4*>(a.out_img + img_off(row, o0, N8)) = o16[0];
+          *reinterpret_cast<uint4*>(a.out_img + img_off(row, o0 + 1, N8)) = o16[1];
+          return;
+        }
         const float* rb = nullptr;
         if (MODE == LWF_ACT && a.rowbias) rb = a.rowbias + ((a.row0 + (row < a.M ? row : a.M - 1)) / a.rpg) * a.N + n_tile * NT + c0;
 #pragma unroll
@@ -270,7 +339,8 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
       if (MODE == LWF_BLOCK && a.stats_out && n_chunks) {
         // one 64-column panel per warp and tile (NT <= 256): its partial sums go to plane (n_tile * NT / 64 + pq)
         const int plane = n_tile * (NT / 64) + pq;
-        *reinterpret_cast<float2*>(a.stats_out + ((size_t)plane * a.rows_pad + row) * 2) = make_float2(s1, s2);
+        *reinterpret_cast<float2*>(a.stats_out + ((size_t)plane * a.rows_pad + row) * 2) =
+            make_float2(s1 + (s1p.x + s1p.y), s2 + (s2p.x + s2p.y));
       }
     }
   }
