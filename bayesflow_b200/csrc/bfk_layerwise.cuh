@@ -111,6 +111,27 @@ __global__ void lw_combine_kernel(const LwCombArgs a) {
   for (long long tile = blockIdx.y; tile < a.n_tiles; tile += gridDim.y) {
     const long long r = tile * 128 + threadIdx.x;
     float v[8];
+    if (r < a.rows && k8 * 8 + 8 <= a.D && !((a.ldy | a.ldk | a.ldo | a.ldx) & 3)) {
+      // whole octet inside the state: 128-bit loads / stores (the scalar path below costs 8 strided sectors per value)
+      ld8(a.y + r * a.ldy + k8 * 8, v);
+      if (a.nk > 0) {
+        float acc[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+        for (int j = 0; j < a.nk; ++j) {
+          float kk[8];
+          ld8(a.k[j] + r * a.ldk + k8 * 8, kk);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], __fmul_rn(a.coef[j], kk[i]));
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = __fadd_rn(v[i], __fmul_rn(h, acc[i]));
+      }
+      if (a.out) st8(a.out + r * a.ldo + k8 * 8, v);
+      if (a.x_out) st8(a.x_out + r * a.ldx + k8 * 8, v);
+      if (a.img) *reinterpret_cast<uint4*>(a.img + img_off(r, k8, a.KU8)) = pack8(v);
+      continue;
+    }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int c = k8 * 8 + i;

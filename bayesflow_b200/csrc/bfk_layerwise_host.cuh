@@ -106,6 +106,8 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
       CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_MISH>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
       CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_SILU>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
       CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_ACT, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_ACT, BFK_ACT_MISH>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_ACT, BFK_ACT_SILU>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
       CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_OUT, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
       attr = true;
     }
@@ -127,6 +129,7 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
     const long long rows = (B - row0 < chunk_rows) ? B - row0 : chunk_rows;
     const long long n_tiles = (rows + 127) / 128;
     const unsigned tch = (unsigned)(n_tiles < 32 ? n_tiles : 32);
+    const unsigned tch_c = (unsigned)(n_tiles < 148 ? n_tiles : 148);  // combine: few octet columns, so more row chunks
     CK(cudaMemcpyAsync(b.y, x_in + row0 * D, (size_t)rows * D * 4, cudaMemcpyDeviceToDevice, st));
     for (long long i = 0; i < n_steps; ++i) {
       for (int s = 0; s < S; ++s) {
@@ -137,7 +140,7 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
         if (!step_h) ca.nk = 0;
         ca.out = dm ? b.ys : nullptr; ca.ldo = D; ca.x_out = nullptr;
         ca.img = b.x_img; ca.KU8 = KU / 8; ca.rows = rows; ca.n_tiles = n_tiles; ca.D = D;
-        lw_combine_kernel<<<dim3(KU / 8, tch), 128, 0, st>>>(ca);
+        lw_combine_kernel<<<dim3(KU / 8, tch_c), 128, 0, st>>>(ca);
         int sms = bfk_num_sms();
         if (sms <= 0) sms = 148;
         const long long wtiles = n_tiles * (W / NTW);
@@ -148,10 +151,15 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
           fa.A = b.x_img; fa.B = b.wx_pk; fa.ccol = w->x_b; fa.out_img = b.has_merge ? b.a_img : b.h_img;
           fa.rowbias = b.has_merge ? b.pre_add : nullptr; fa.row0 = row0; fa.rpg = rpg;
           fa.M = rows; fa.N = W; fa.K = KU; fa.NT = NTW; fa.act = act; fa.idesc = umma_idesc_f16(G_TM, NTW, 0);
-          lw_block_gemm_kernel<LWF_ACT, -1><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
+          auto launch_act = [&](const LwFusedArgs& f) {
+            if (act == BFK_ACT_MISH) lw_block_gemm_kernel<LWF_ACT, BFK_ACT_MISH><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(f);
+            else if (act == BFK_ACT_SILU) lw_block_gemm_kernel<LWF_ACT, BFK_ACT_SILU><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(f);
+            else lw_block_gemm_kernel<LWF_ACT, -1><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(f);
+          };
+          launch_act(fa);
           if (b.has_merge) {
             fa.A = b.a_img; fa.B = b.wm_pk; fa.ccol = nullptr; fa.out_img = b.h_img; fa.rowbias = b.post_add; fa.K = W;
-            lw_block_gemm_kernel<LWF_ACT, -1><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
+            launch_act(fa);
           }
           CK(cudaGetLastError());
         } else {
@@ -217,7 +225,7 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
       ua.out = b.y; ua.ldo = D;
       ua.x_out = (i == n_steps - 1) ? x_out + row0 * D : nullptr; ua.ldx = D;
       ua.img = nullptr; ua.KU8 = KU / 8; ua.rows = rows; ua.n_tiles = n_tiles; ua.D = D;
-      lw_combine_kernel<<<dim3((D + 7) / 8, tch), 128, 0, st>>>(ua);
+      lw_combine_kernel<<<dim3((D + 7) / 8, tch_c), 128, 0, st>>>(ua);
     }
     CK(cudaGetLastError());
   }

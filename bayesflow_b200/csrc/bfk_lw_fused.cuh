@@ -114,6 +114,33 @@ __device__ __forceinline__ void lwf_block_chunk16(const float* vc, const uint4* 
   }
 }
 
+// LWF_ACT arithmetic of one 16-column chunk in packed fp32: act(acc + c + rowbias) -> two 16-byte image chunks.
+template <int ACT>
+__device__ __forceinline__ void lwf_act_chunk16(const float* vc, const float* vb, int NT, int c0, const float* rb, uint4* out) {
+  float2 P[8];
+#pragma unroll
+  for (int jj = 0; jj < 2; ++jj) {
+    const float4 k0 = *reinterpret_cast<const float4*>(vb + 1 * NT + c0 + jj * 8);
+    const float4 k1 = *reinterpret_cast<const float4*>(vb + 1 * NT + c0 + jj * 8 + 4);
+    float2 cc[4] = {make_float2(k0.x, k0.y), make_float2(k0.z, k0.w), make_float2(k1.x, k1.y), make_float2(k1.z, k1.w)};
+    if (rb) {
+      const float4 r0 = *reinterpret_cast<const float4*>(rb + jj * 8);
+      const float4 r1 = *reinterpret_cast<const float4*>(rb + jj * 8 + 4);
+      cc[0] = __fadd2_rn(cc[0], make_float2(r0.x, r0.y)); cc[1] = __fadd2_rn(cc[1], make_float2(r0.z, r0.w));
+      cc[2] = __fadd2_rn(cc[2], make_float2(r1.x, r1.y)); cc[3] = __fadd2_rn(cc[3], make_float2(r1.z, r1.w));
+    }
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      const int i = jj * 4 + p;
+      P[i] = __fadd2_rn(make_float2(vc[2 * i], vc[2 * i + 1]), cc[p]);
+    }
+  }
+  act2x8<ACT>(P);
+#pragma unroll
+  for (int jj = 0; jj < 2; ++jj)
+    out[jj] = make_uint4(pack2f<false>(P[jj * 4]), pack2f<false>(P[jj * 4 + 1]), pack2f<false>(P[jj * 4 + 2]), pack2f<false>(P[jj * 4 + 3]));
+}
+
 template <int MODE, int ACT>
 __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwFusedArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -266,6 +293,13 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
         }
         const float* rb = nullptr;
         if (MODE == LWF_ACT && a.rowbias) rb = a.rowbias + ((a.row0 + (row < a.M ? row : a.M - 1)) / a.rpg) * a.N + n_tile * NT + c0;
+        if (MODE == LWF_ACT && ACT >= 0) {
+          uint4 o16[2];
+          lwf_act_chunk16<(ACT >= 0 ? ACT : 0)>(vc, vb, NT, c0, rb, o16);
+          *reinterpret_cast<uint4*>(a.out_img + img_off(row, o0, N8)) = o16[0];
+          *reinterpret_cast<uint4*>(a.out_img + img_off(row, o0 + 1, N8)) = o16[1];
+          return;
+        }
 #pragma unroll
         for (int o = 0; o < 2; ++o) {
           float sk[8];
