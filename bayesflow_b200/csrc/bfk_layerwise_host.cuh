@@ -45,6 +45,19 @@ void plan_lw(const bfk_net_config* c, long long chunk, long long n_evals, long l
   for (int s = 0; s < BFK_MAX_STAGES; ++s) b.k[s] = (float*)ar.take(Rp * b.NO * 4);
 }
 
+// launch as clusters of two CTAs (bfk_lw_fused.cuh, CL = 2)
+template <typename Kern>
+int launch_pairs(Kern kernel, unsigned grid, size_t smem, cudaStream_t st, const LwFusedArgs& fa) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid & ~1u); cfg.blockDim = dim3(LWF_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  CK(cudaLaunchKernelEx(&cfg, kernel, fa));
+  return 0;
+}
+
 }  // namespace
 
 extern "C" size_t bfk_layerwise_workspace_bytes(const bfk_net_config* c, int64_t chunk_rows, int64_t n_evals, int64_t G) {
@@ -88,6 +101,8 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
   static int fused = -1;
   if (fused < 0) { const char* e = getenv("BFK_LW_FUSED"); fused = e ? atoi(e) : 1; }
   const bool ln = c->norm == BFK_NORM_LAYER;
+  const char* cl_env = getenv("BFK_LW_CLUSTER");
+  const bool pairs = (cl_env ? atoi(cl_env) : 1) == 2 && (act == BFK_ACT_MISH || act == BFK_ACT_SILU);
   if (fused) {
     // block l consumes the un-normalised output of block l-1: its LayerNorm is folded into W_l (bfk_lw_fused.cuh)
     for (int l = 0; l < L; ++l)
@@ -102,13 +117,17 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
     static bool attr = false;
     if (!attr) {
       const int sm = (int)lw_fused_smem_bytes(256);
-      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
-      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_MISH>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
-      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_SILU>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
-      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_ACT, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
-      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_ACT, BFK_ACT_MISH>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
-      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_ACT, BFK_ACT_SILU>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
-      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_OUT, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK, -1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_MISH, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_SILU, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_ACT, -1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_ACT, BFK_ACT_MISH, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_ACT, BFK_ACT_SILU, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_OUT, -1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_MISH, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_SILU, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_ACT, BFK_ACT_MISH, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_ACT, BFK_ACT_SILU, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
       attr = true;
     }
   } else {
@@ -151,15 +170,21 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
           fa.A = b.x_img; fa.B = b.wx_pk; fa.ccol = w->x_b; fa.out_img = b.has_merge ? b.a_img : b.h_img;
           fa.rowbias = b.has_merge ? b.pre_add : nullptr; fa.row0 = row0; fa.rpg = rpg;
           fa.M = rows; fa.N = W; fa.K = KU; fa.NT = NTW; fa.act = act; fa.idesc = umma_idesc_f16(G_TM, NTW, 0);
-          auto launch_act = [&](const LwFusedArgs& f) {
-            if (act == BFK_ACT_MISH) lw_block_gemm_kernel<LWF_ACT, BFK_ACT_MISH><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(f);
-            else if (act == BFK_ACT_SILU) lw_block_gemm_kernel<LWF_ACT, BFK_ACT_SILU><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(f);
-            else lw_block_gemm_kernel<LWF_ACT, -1><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(f);
+          auto launch_act = [&](const LwFusedArgs& f) -> int {
+            const unsigned pgrid = (unsigned)(2 * ((n_tiles + 1) / 2) * (W / NTW) < sms ? 2 * ((n_tiles + 1) / 2) * (W / NTW) : sms);
+            if (pairs && pgrid >= 2) {
+              if (act == BFK_ACT_MISH) return launch_pairs(lw_block_gemm_kernel<LWF_ACT, BFK_ACT_MISH, 2>, pgrid, lw_fused_smem_bytes(NTW), st, f);
+              return launch_pairs(lw_block_gemm_kernel<LWF_ACT, BFK_ACT_SILU, 2>, pgrid, lw_fused_smem_bytes(NTW), st, f);
+            }
+            if (act == BFK_ACT_MISH) lw_block_gemm_kernel<LWF_ACT, BFK_ACT_MISH, 1><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(f);
+            else if (act == BFK_ACT_SILU) lw_block_gemm_kernel<LWF_ACT, BFK_ACT_SILU, 1><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(f);
+            else lw_block_gemm_kernel<LWF_ACT, -1, 1><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(f);
+            return 0;
           };
-          launch_act(fa);
+          RC(launch_act(fa));
           if (b.has_merge) {
             fa.A = b.a_img; fa.B = b.wm_pk; fa.ccol = nullptr; fa.out_img = b.h_img; fa.rowbias = b.post_add; fa.K = W;
-            launch_act(fa);
+            RC(launch_act(fa));
           }
           CK(cudaGetLastError());
         } else {
@@ -185,9 +210,14 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
             fa.stats_out = ln ? b.stats[(l + 1) & 1] : nullptr;
             fa.M = rows; fa.N = W; fa.K = W; fa.NT = NTW; fa.act = act; fa.residual = c->residual ? 1 : 0;
             fa.idesc = umma_idesc_f16(G_TM, NTW, 0); fa.rows_pad = n_tiles * 128;
-            if (act == BFK_ACT_MISH) lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_MISH><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
-            else if (act == BFK_ACT_SILU) lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_SILU><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
-            else lw_block_gemm_kernel<LWF_BLOCK, -1><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
+            const unsigned pgrid = (unsigned)(2 * ((n_tiles + 1) / 2) * (W / NTW) < sms ? 2 * ((n_tiles + 1) / 2) * (W / NTW) : sms);
+            if (pairs && pgrid >= 2) {
+              if (act == BFK_ACT_MISH) RC(launch_pairs(lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_MISH, 2>, pgrid, lw_fused_smem_bytes(NTW), st, fa));
+              else RC(launch_pairs(lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_SILU, 2>, pgrid, lw_fused_smem_bytes(NTW), st, fa));
+            } else
+            if (act == BFK_ACT_MISH) lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_MISH, 1><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
+            else if (act == BFK_ACT_SILU) lw_block_gemm_kernel<LWF_BLOCK, BFK_ACT_SILU, 1><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
+            else lw_block_gemm_kernel<LWF_BLOCK, -1, 1><<<wgrid, LWF_THREADS, lw_fused_smem_bytes(NTW), st>>>(fa);
           }
           CK(cudaGetLastError());
           LwFusedArgs fo{};
@@ -195,7 +225,7 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
           fo.gcol = b.gcol_o; fo.ccol = b.ccol_o; fo.out_f32 = b.k[s]; fo.ldo = NO;
           fo.rows_pad = n_tiles * 128; fo.M = rows; fo.N = NO; fo.K = W; fo.NT = 64; fo.act = act; fo.idesc = umma_idesc_f16(G_TM, 64, 0);
           const long long otiles = n_tiles * (NO / 64);
-          lw_block_gemm_kernel<LWF_OUT, -1><<<(unsigned)(otiles < sms ? otiles : sms), LWF_THREADS, lw_fused_smem_bytes(64), st>>>(fo);
+          lw_block_gemm_kernel<LWF_OUT, -1, 1><<<(unsigned)(otiles < sms ? otiles : sms), LWF_THREADS, lw_fused_smem_bytes(64), st>>>(fo);
           CK(cudaGetLastError());
         } else {
           for (int l = 0; l < L; ++l) {

@@ -141,9 +141,16 @@ __device__ __forceinline__ void lwf_act_chunk16(const float* vc, const float* vb
     out[jj] = make_uint4(pack2f<false>(P[jj * 4]), pack2f<false>(P[jj * 4 + 1]), pack2f<false>(P[jj * 4 + 2]), pack2f<false>(P[jj * 4 + 3]));
 }
 
-template <int MODE, int ACT>
+// CL = 2: CTA pairs (a cluster of two) work on two ROW tiles of the same column tile in lockstep and share the weight
+// slab - each CTA fetches half of it and multicasts it into both shared memories - which cuts the L2 -> SMEM operand
+// traffic per tile from 768 KB to 512 KB (r01as: 2.0 GB of L2 traffic per launch, 11.9 TB/s, was the limiter).
+template <int MODE, int ACT, int CL>
 __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwFusedArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
+  const uint32_t crank = CL == 2 ? cluster_ctarank() : 0;
+  // work items: CL == 1: (row tile, column tile); CL == 2: (row-tile PAIR, column tile), this CTA takes row tile 2*pair + rank
+  // (clamped: with an odd number of row tiles the last pair computes the same tile twice and stores identical values)
+  const long long w_first = CL == 2 ? blockIdx.x / 2 : blockIdx.x, w_step = CL == 2 ? gridDim.x / 2 : gridDim.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int NT = a.NT;
   const uint32_t a_bytes = P_KC * G_TM * 2, b_bytes = (uint32_t)P_KC * NT * 2, st_bytes = a_bytes + b_bytes;
@@ -155,12 +162,17 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
   volatile uint32_t* s_tmem = reinterpret_cast<volatile uint32_t*>(smem + bar_off + 80);
   const int n_tiles_n = a.N / NT;
   const long long m_tiles = (a.M + G_TM - 1) / G_TM;
-  const long long total = m_tiles * n_tiles_n;
+  const long long total = (CL == 2 ? (m_tiles + 1) / 2 : m_tiles) * n_tiles_n;
   const int n_slabs = a.K / P_KC;
   const size_t K8 = (size_t)a.K / 8;
+  auto m_tile_of = [&](long long t) -> long long {
+    const long long mt = CL == 2 ? 2 * (t / n_tiles_n) + crank : t / n_tiles_n;
+    return mt < m_tiles ? mt : m_tiles - 1;
+  };
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < P_STAGES; ++s) { mbar_init(bar0 + 8 * s, 1); mbar_init(bar0 + 8 * (3 + s), 1); }
+    // empty[s] collects the UMMA commits of BOTH CTAs of a pair: a stage is refilled (partly by the peer) only when both are done
+    for (int s = 0; s < P_STAGES; ++s) { mbar_init(bar0 + 8 * s, 1); mbar_init(bar0 + 8 * (3 + s), CL); }
     for (int b = 0; b < 2; ++b) { mbar_init(bar0 + 48 + 8 * b, 1); mbar_init(bar0 + 64 + 8 * b, LWF_EPI_WARPS); }
     fence_barrier_init();
   }
@@ -169,14 +181,15 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
   if (warp == LWF_EPI_WARPS) tmem_alloc(bar0 + 80, tmem_cols);
   tc_fence_before();
   __syncthreads();
+  if (CL == 2) cluster_sync_all();  // the peer's barriers are initialised before anything is multicast into them
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
 
   if (warp == LWF_EPI_WARPS + 1) {
     if (lane == 0) {
       uint32_t g = 0;
-      for (long long t = blockIdx.x; t < total; t += gridDim.x) {
-        const long long m_tile = t / n_tiles_n;
+      for (long long t = w_first; t < total; t += w_step) {
+        const long long m_tile = m_tile_of(t);
         const int n_tile = (int)(t % n_tiles_n);
         for (int i = 0; i < n_slabs; ++i, ++g) {
           const uint32_t s = g % P_STAGES;
@@ -184,7 +197,13 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
           mbar_arrive_expect_tx(bar0 + 8 * s, st_bytes);
           const size_t k8 = (size_t)i * (P_KC / 8);
           bulk_g2s(smem_base + s * st_bytes, a.A + ((size_t)m_tile * K8 + k8) * G_TM * 16, a_bytes, bar0 + 8 * s);
-          bulk_g2s(smem_base + s * st_bytes + a_bytes, a.B + ((size_t)n_tile * K8 + k8) * NT * 16, b_bytes, bar0 + 8 * s);
+          const unsigned char* bsrc = a.B + ((size_t)n_tile * K8 + k8) * NT * 16;
+          if (CL == 2) {  // my half of the weight slab (4 of its 8 K octets) into both CTAs
+            const uint32_t hb = b_bytes / 2;
+            bulk_g2s_multicast(smem_base + s * st_bytes + a_bytes + crank * hb, bsrc + (size_t)crank * hb, hb, bar0 + 8 * s, 0x3);
+          } else {
+            bulk_g2s(smem_base + s * st_bytes + a_bytes, bsrc, b_bytes, bar0 + 8 * s);
+          }
         }
       }
     }
@@ -192,7 +211,7 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
   } else if (warp == LWF_EPI_WARPS) {
     if (lane == 0) {
       uint32_t g = 0, j = 0;
-      for (long long t = blockIdx.x; t < total; t += gridDim.x, ++j) {
+      for (long long t = w_first; t < total; t += w_step, ++j) {
         const uint32_t acc = j & 1;
         mbar_wait(bar0 + 64 + 8 * acc, ((j >> 1) & 1) ^ 1, nullptr, 0);  // epilogue has drained this accumulator
         tc_fence_after();
@@ -208,7 +227,8 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
             const uint64_t bd = umma_smem_desc(sb + (uint32_t)(kk * 2) * (NT * 16), (uint32_t)NT * 16, 128);
             umma_f16(d_tmem, ad, bd, a.idesc, (uint32_t)((i | kk) != 0));
           }
-          umma_commit(bar0 + 8 * (3 + s));
+          if (CL == 2) umma_commit_multicast(bar0 + 8 * (3 + s), 0x3);
+          else umma_commit(bar0 + 8 * (3 + s));
         }
         umma_commit(bar0 + 48 + 8 * acc);
       }
@@ -224,8 +244,8 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
     const int N8 = a.N / 8;
     const int n_chunks = (NT / 64 > pq) ? ((NT / 64 - pq + 3) / 4) * 4 : 0;  // 16-column chunks this warp owns per tile
     uint32_t j = 0;
-    for (long long t = blockIdx.x; t < total; t += gridDim.x, ++j) {
-      const long long m_tile = t / n_tiles_n;
+    for (long long t = w_first; t < total; t += w_step, ++j) {
+      const long long m_tile = m_tile_of(t);
       const int n_tile = (int)(t % n_tiles_n);
       const uint32_t acc = j & 1;
       // per-column vectors of this column tile -> shared (double buffered by tile parity, one barrier per tile)
@@ -379,6 +399,7 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
     }
   }
   __syncthreads();
+  if (CL == 2) cluster_sync_all();  // no CTA leaves while its peer can still multicast into it or signal its barriers
   tc_fence_after();
   if (warp == LWF_EPI_WARPS) tmem_dealloc(tmem_base, tmem_cols);
 }

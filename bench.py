@@ -299,6 +299,21 @@ def run_ours(args, name, w):
         train = measure_training(tw, dev, world, rank, max(args.steps, 5), 3, False)
         train["config"] = train_config("cfg5_fm_train", tw, world)
         train["metric"] = "FlowMatching train samples/sec"
+    is_layerwise = bool(net._engine.layerwise)
+    wide = None
+    if not args.no_train and world == 1 and name == DEFAULT_WORKLOAD:
+        # configs[3] (wide subnet, 1M draws) measured in the same run as a secondary line: a fresh process of this script
+        # with the same timing rules (3 warm-ups, L2 flush, device events), 2 timed steps of ~2.6 s
+        del net
+        torch.cuda.empty_cache()
+        try:
+            r = subprocess.run([sys.executable, os.path.abspath(__file__), "--workload", "cfg4_wide_fm_euler100", "--steps", "2",
+                                "--warmup", "3", "--no-train", "--no-cpu-baseline"], capture_output=True, text=True, timeout=600)
+            wide = json.loads(r.stdout.strip().splitlines()[-1])
+            wide = {k: wide[k] for k in ("metric", "value", "unit", "ms_per_step", "steps", "warmup", "config", "e2e",
+                                         "gpu_launches", "roofline", "clocks")}
+        except Exception as exc:  # the headline line must not depend on the secondary one
+            wide = {"unavailable": repr(exc)[:200]}
     if rank == 0:
         line = {"metric": "posterior draws/sec", "value": value, "unit": "draws/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -311,11 +326,11 @@ def run_ours(args, name, w):
                 "roofline": {"bound": "tensor", "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",
                              "frac": (achieved / peaks["tflops"]) if achieved else None, "traffic": ncu_traffic(name),
                              "kernel": ("bfk::lw_block_gemm_kernel<0> (fused Dense+block epilogue, 83 % of the call) + x_proj/merge/out stages: all launches of one bfk_sample_layerwise call"
-                                        if net._engine.layerwise else "bfk::sampler_kernel"), "kernel_ms": k_avg_ms, "kernel_share_of_step": k_avg_ms * args.steps / total_ms,
+                                        if is_layerwise else "bfk::sampler_kernel"), "kernel_ms": k_avg_ms, "kernel_share_of_step": k_avg_ms * args.steps / total_ms,
                              "flop_per_draw_naive": fpd, "peak_source": peaks["source"],
                              "hbm_gbs_algorithmic": (N * S * D * 8) / (k_avg_ms * 1e-3) / 1e9 if kern_ms else None},
                 "cpu_baseline": cpu,
-                "integration": info, "wall_s_timed_region": wall, "train": train}
+                "integration": info, "wall_s_timed_region": wall, "train": train, "wide_cfg4": wide}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
