@@ -1,0 +1,311 @@
+// bfk_edge.cuh — the approximator edge of the sampling path: running-moment standardization
+// (networks/helpers/standardization/standardize.py:50-170) and base-distribution noise generated in HBM
+// (distributions/diagonal_normal.py:100-105).  All three kernels are HBM-bound elementwise / reduction work: the rules
+// that matter are coalescing, 16-byte accesses where alignment allows and grids sized from the SM count.
+// Included at the end of bfk_host.cu (uses its fail()/CK helpers).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace bfk {
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al., "Parallel random numbers: as easy as 1, 2, 3", SC'11; same generator as curand /
+// torch.cuda).  Counter = {q_lo, q_hi, 0, 0} with q = global element index / 4, key = seed.  The stream depends only on
+// (seed, global element index), so a row shard generated on any rank equals the same rows of a single-GPU run.
+// ---------------------------------------------------------------------------------------------------------------------
+__host__ __device__ inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint64_t p0 = (uint64_t)M0 * c[0], p1 = (uint64_t)M1 * c[2];
+    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c[1] ^ k0, n2 = (uint32_t)(p0 >> 32) ^ c[3] ^ k1;
+    c[1] = (uint32_t)p1;
+    c[3] = (uint32_t)p0;
+    c[0] = n0;
+    c[2] = n2;
+    k0 += W0;
+    k1 += W1;
+  }
+}
+
+// uniform in (0,1): 24 random bits + 1/2, exactly representable, never 0 or 1
+__device__ __forceinline__ float u01(uint32_t r) { return ((float)(r >> 8) + 0.5f) * 5.9604644775390625e-8f; }
+
+// 4 standard normals of quad q (Box-Muller on (r0,r1) and (r2,r3))
+__device__ __forceinline__ void normal_quad(uint64_t q, uint64_t seed, float z[4]) {
+  uint32_t c[4] = {(uint32_t)q, (uint32_t)(q >> 32), 0u, 0u};
+  philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+#pragma unroll
+  for (int p = 0; p < 2; ++p) {
+    const float rad = sqrtf(-2.0f * logf(u01(c[2 * p])));
+    float s, co;
+    sincospif(2.0f * u01(c[2 * p + 1]), &s, &co);
+    z[2 * p] = rad * co;
+    z[2 * p + 1] = rad * s;
+  }
+}
+
+// out[e] = mean[(e0+e) % D] + std[(e0+e) % D] * z(e0 + e),  e in [0, n): e0 = global element offset of this shard.
+// One thread per quad of the GLOBAL stream; float4 stores when the quad lies inside the shard and is 16-byte aligned.
+__global__ void __launch_bounds__(256) normal_fill_kernel(float* __restrict__ out, long long n, long long e0, int D,
+                                                          const float* __restrict__ mean, const float* __restrict__ stdv,
+                                                          unsigned long long seed, uint32_t* __restrict__ raw) {
+  const long long q_first = e0 >> 2, q_last = (e0 + n - 1) >> 2;
+  const bool vec = ((e0 & 3) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+  for (long long q = q_first + (long long)blockIdx.x * blockDim.x + threadIdx.x; q <= q_last;
+       q += (long long)gridDim.x * blockDim.x) {
+    float z[4];
+    normal_quad((uint64_t)q, seed, z);
+    if (raw) {  // known-answer hook: the raw Philox words of this quad
+      uint32_t c[4] = {(uint32_t)q, (uint32_t)((uint64_t)q >> 32), 0u, 0u};
+      philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const long long e = (q << 2) + j - e0;
+        if (e >= 0 && e < n) raw[e] = c[j];
+      }
+    }
+    const long long g = q << 2;
+    if (mean || stdv) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int d = (int)((g + j) % D);
+        z[j] = (mean ? mean[d] : 0.0f) + (stdv ? stdv[d] : 1.0f) * z[j];
+      }
+    }
+    const long long e = g - e0;
+    if (vec && e >= 0 && e + 4 <= n) {
+      *reinterpret_cast<float4*>(out + e) = make_float4(z[0], z[1], z[2], z[3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (e + j >= 0 && e + j < n) out[e + j] = z[j];
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Standardize.call (standardize.py:50-133), transformation_type == "location_scale":
+//   forward: (x - mean) / std      inverse: x * std + mean      std = m2 > 0 ? sqrt(m2 / count) : 1   (:27-37)
+// x is (rows, F) row-major, flat index i -> feature i % F.  In place allowed.
+// ---------------------------------------------------------------------------------------------------------------------
+template <bool FWD>
+__global__ void __launch_bounds__(256) standardize_kernel(const float* __restrict__ x, float* __restrict__ out,
+                                                          long long n, int F, const float* __restrict__ mean,
+                                                          const float* __restrict__ m2, const float* __restrict__ count) {
+  extern __shared__ float sm[];  // mean[F], std[F]
+  float* s_mean = sm;
+  float* s_std = sm + F;
+  const float cnt = count[0];
+  for (int f = threadIdx.x; f < F; f += blockDim.x) {
+    const float v = m2[f];
+    s_mean[f] = mean[f];
+    s_std[f] = v > 0.0f ? sqrtf(v / cnt) : 1.0f;
+  }
+  __syncthreads();
+  const bool vec = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  const long long nq = vec ? (n >> 2) : 0;
+  const long long stride = (long long)gridDim.x * blockDim.x, t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  for (long long q = t0; q < nq; q += stride) {
+    float4 v = reinterpret_cast<const float4*>(x)[q];
+    float* p = reinterpret_cast<float*>(&v);
+    int f = (int)((q << 2) % F);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      p[j] = FWD ? (p[j] - s_mean[f]) / s_std[f] : p[j] * s_std[f] + s_mean[f];
+      f = (f + 1 == F) ? 0 : f + 1;
+    }
+    reinterpret_cast<float4*>(out)[q] = v;
+  }
+  for (long long i = (nq << 2) + t0; i < n; i += stride) {
+    const int f = (int)(i % F);
+    out[i] = FWD ? (x[i] - s_mean[f]) / s_std[f] : x[i] * s_std[f] + s_mean[f];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Standardize._update_moments (standardize.py:135-170).  The reference takes the batch mean, then the batch M2 about
+// it (two reads of x), then merges with the running totals.  Here x is read ONCE: each thread takes shifted sums over its
+// rows of one feature, threads of a block and then the blocks are combined with the same pairwise merge the reference
+// uses between batch and running totals (:159-166) — always in a fixed order, so the result is bit-reproducible.
+// Thread layout: tx = tid % F is the feature, ty = tid / F the row lane, so a warp reads consecutive floats.
+// ---------------------------------------------------------------------------------------------------------------------
+struct Moments {
+  float n, mean, m2;
+};
+__host__ __device__ inline Moments merge_moments(Moments a, Moments b) {
+  if (b.n == 0.0f) return a;
+  if (a.n == 0.0f) return b;
+  const float tot = a.n + b.n, delta = b.mean - a.mean;
+  Moments r;
+  r.n = tot;
+  r.mean = a.mean + delta * (b.n / tot);
+  r.m2 = a.m2 + b.m2 + delta * delta * (a.n * b.n / tot);
+  return r;
+}
+
+// partial (gridDim.x, 3, F): per-block count / mean / M2 of each feature
+__global__ void moments_partial_kernel(const float* __restrict__ x, long long rows, int F, float* __restrict__ partial) {
+  extern __shared__ float sm[];  // [3][TY][F]
+  const int TY = blockDim.x / F, tx = threadIdx.x % F, ty = threadIdx.x / F;
+  const long long rows_per_block = (rows + gridDim.x - 1) / gridDim.x;
+  const long long r_lo = (long long)blockIdx.x * rows_per_block;
+  const long long r_hi = r_lo + rows_per_block < rows ? r_lo + rows_per_block : rows;
+  Moments m = {0.0f, 0.0f, 0.0f};
+  if (ty < TY) {
+    // shifted sums about the thread's first value K: no division and no dependent chain in the loop
+    float K = 0.0f, s1 = 0.0f, s2 = 0.0f, cnt = 0.0f;
+    if (r_lo + ty < r_hi) K = x[(r_lo + ty) * F + tx];
+#pragma unroll 4
+    for (long long r = r_lo + ty; r < r_hi; r += TY) {
+      const float d = x[r * F + tx] - K;
+      s1 += d;
+      s2 = fmaf(d, d, s2);
+      cnt += 1.0f;
+    }
+    if (cnt > 0.0f) {
+      m.n = cnt;
+      m.mean = K + s1 / cnt;
+      m.m2 = fmaxf(s2 - s1 * s1 / cnt, 0.0f);
+    }
+    sm[(0 * TY + ty) * F + tx] = m.n;
+    sm[(1 * TY + ty) * F + tx] = m.mean;
+    sm[(2 * TY + ty) * F + tx] = m.m2;
+  }
+  __syncthreads();
+  int span = 1;
+  while (span < TY) span <<= 1;
+  for (int s = span >> 1; s >= 1; s >>= 1) {
+    if (ty < s && ty + s < TY) {
+      Moments a = {sm[(0 * TY + ty) * F + tx], sm[(1 * TY + ty) * F + tx], sm[(2 * TY + ty) * F + tx]};
+      Moments b = {sm[(0 * TY + ty + s) * F + tx], sm[(1 * TY + ty + s) * F + tx], sm[(2 * TY + ty + s) * F + tx]};
+      a = merge_moments(a, b);
+      sm[(0 * TY + ty) * F + tx] = a.n;
+      sm[(1 * TY + ty) * F + tx] = a.mean;
+      sm[(2 * TY + ty) * F + tx] = a.m2;
+    }
+    __syncthreads();
+  }
+  if (ty == 0) {
+    float* p = partial + (size_t)blockIdx.x * 3 * F;
+    p[tx] = sm[tx];
+    p[F + tx] = sm[(1 * TY) * F + tx];
+    p[2 * F + tx] = sm[(2 * TY) * F + tx];
+  }
+}
+
+// stats (2F+1): mean[F], m2[F], count — the batch moments, blocks merged in index order
+__global__ void moments_finish_kernel(const float* __restrict__ partial, int n_blocks, int F, float* __restrict__ stats) {
+  for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < F; f += gridDim.x * blockDim.x) {
+    Moments a = {0.0f, 0.0f, 0.0f};
+    for (int b = 0; b < n_blocks; ++b) {
+      const float* p = partial + (size_t)b * 3 * F;
+      a = merge_moments(a, Moments{p[f], p[F + f], p[2 * F + f]});
+    }
+    stats[f] = a.mean;
+    stats[F + f] = a.m2;
+    if (f == 0) stats[2 * F] = a.n;
+  }
+}
+
+// running (mean, m2, count) <- merge(running, parts[0], parts[1], ...) in index order (standardize.py:153-170); parts
+// are (n_parts, 2F+1) batch-moment records, e.g. one per data-parallel rank after an all-gather
+__global__ void moments_merge_kernel(float* __restrict__ mean, float* __restrict__ m2, float* __restrict__ count,
+                                     const float* __restrict__ parts, int n_parts, int F) {
+  const float cnt0 = count[0];
+  __syncthreads();
+  float cnt = cnt0;
+  for (int f = threadIdx.x; f < F; f += blockDim.x) {
+    Moments a = {cnt0, mean[f], m2[f]};
+    for (int p = 0; p < n_parts; ++p) {
+      const float* s = parts + (size_t)p * (2 * F + 1);
+      a = merge_moments(a, Moments{s[2 * F], s[f], s[F + f]});
+    }
+    mean[f] = a.mean;
+    m2[f] = a.m2;
+    cnt = a.n;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) count[0] = cnt;
+}
+
+static inline int moments_blocks(long long rows, int F, int n_sms) {
+  const int tpb = F <= 256 ? 256 : 1024, TY = tpb / F;
+  long long want = (rows + (long long)TY * 8 - 1) / ((long long)TY * 8);  // >= 8 rows per thread
+  long long cap = (long long)n_sms * (tpb == 256 ? 8 : 2);
+  if (want < 1) want = 1;
+  return (int)(want < cap ? want : cap);
+}
+
+}  // namespace bfk
+
+// ---- C ABI ------------------------------------------------------------------------------------------------------------
+extern "C" int bfk_normal_fill(float* out, int64_t rows, int32_t D, int64_t row_offset, const float* mean,
+                               const float* stdv, uint64_t seed, uint32_t* raw_words, void* stream) {
+  if (rows < 0 || D < 1 || row_offset < 0) return fail(-60, "bfk_normal_fill: bad rows/D/row_offset");
+  if (rows == 0) return 0;
+  if (!out) return fail(-61, "bfk_normal_fill: null output");
+  const long long n = (long long)rows * D, e0 = (long long)row_offset * D;
+  const long long quads = ((e0 + n - 1) >> 2) - (e0 >> 2) + 1;
+  const int sms = bfk_num_sms();
+  if (sms <= 0) return fail(-62, "bfk_normal_fill: no CUDA device");
+  long long blocks = (quads + 255) / 256, cap = (long long)sms * 8;
+  if (blocks > cap) blocks = cap;
+  bfk::normal_fill_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(out, n, e0, D, mean, stdv,
+                                                                             (unsigned long long)seed, raw_words);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_standardize(const float* x, float* out, int64_t rows, int32_t F, const float* mean, const float* m2,
+                               const float* count, int32_t forward, void* stream) {
+  if (rows < 0 || F < 1 || F > 4096) return fail(-63, "bfk_standardize: bad rows/F (F <= 4096)");
+  if (rows == 0) return 0;
+  if (!x || !out || !mean || !m2 || !count) return fail(-64, "bfk_standardize: null pointer");
+  const long long n = (long long)rows * F;
+  const int sms = bfk_num_sms();
+  if (sms <= 0) return fail(-62, "bfk_standardize: no CUDA device");
+  long long blocks = ((n + 3) / 4 + 255) / 256, cap = (long long)sms * 8;
+  if (blocks > cap) blocks = cap;
+  const size_t smem = 2 * (size_t)F * sizeof(float);
+  if (forward)
+    bfk::standardize_kernel<true><<<(unsigned)blocks, 256, smem, (cudaStream_t)stream>>>(x, out, n, F, mean, m2, count);
+  else
+    bfk::standardize_kernel<false><<<(unsigned)blocks, 256, smem, (cudaStream_t)stream>>>(x, out, n, F, mean, m2, count);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" size_t bfk_moments_workspace_floats(int64_t rows, int32_t F) {
+  if (rows < 0 || F < 1 || F > 1024) return 0;
+  int sms = bfk_num_sms();
+  if (sms <= 0) sms = 148;
+  return (size_t)bfk::moments_blocks(rows, F, sms) * 3 * F;
+}
+
+extern "C" int bfk_batch_moments(const float* x, int64_t rows, int32_t F, float* workspace, float* stats, void* stream) {
+  if (rows < 0 || F < 1 || F > 1024) return fail(-65, "bfk_batch_moments: bad rows/F (F <= 1024)");
+  if (!stats || !workspace || (rows > 0 && !x)) return fail(-66, "bfk_batch_moments: null pointer");
+  const int sms = bfk_num_sms();
+  if (sms <= 0) return fail(-62, "bfk_batch_moments: no CUDA device");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int tpb = F <= 256 ? 256 : 1024, TY = tpb / F;
+  const int blocks = bfk::moments_blocks(rows, F, sms);
+  const size_t smem = 3 * (size_t)TY * F * sizeof(float);
+  bfk::moments_partial_kernel<<<blocks, tpb, smem, st>>>(x, rows, F, workspace);
+  CK(cudaGetLastError());
+  bfk::moments_finish_kernel<<<(F + 127) / 128, 128, 0, st>>>(workspace, blocks, F, stats);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_moments_merge(float* mean, float* m2, float* count, const float* parts, int32_t n_parts, int32_t F,
+                                 void* stream) {
+  if (n_parts < 0 || F < 1 || F > 1024) return fail(-67, "bfk_moments_merge: bad n_parts/F");
+  if (n_parts == 0) return 0;
+  if (!mean || !m2 || !count || !parts) return fail(-68, "bfk_moments_merge: null pointer");
+  bfk::moments_merge_kernel<<<1, F < 256 ? 256 : 1024, 0, (cudaStream_t)stream>>>(mean, m2, count, parts, n_parts, F);
+  CK(cudaGetLastError());
+  return 0;
+}

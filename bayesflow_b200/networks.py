@@ -78,15 +78,26 @@ class DiagonalNormal(nn.Module):
             result = result + (-0.5 * self.dim * math.log(2.0 * math.pi) - torch.sum(torch.log(self._std)))
         return result
 
-    def sample(self, batch_shape, seed=None):
+    def sample(self, batch_shape, seed=None, row_offset: int = 0):
+        """mean + std * z with z written in HBM by `bfk_normal_fill` (Philox4x32-10 keyed by `seed`; the counter is the
+        GLOBAL element index, so rows [row_offset, row_offset + rows) equal the same rows of one big call)."""
         if isinstance(batch_shape, int):
             batch_shape = (batch_shape,)
         dev = self._mean.device
-        gen = None
-        if seed is not None:
-            gen = seed if isinstance(seed, torch.Generator) else torch.Generator(device=dev).manual_seed(int(seed))
-        z = torch.randn(tuple(batch_shape) + (self.dim,), device=dev, generator=gen)
-        return self._mean + self._std * z
+        if dev.type != "cuda":
+            raise RuntimeError("bayesflow_b200 generates base samples on CUDA only (no CPU fallback); move the network "
+                               "to a CUDA device")
+        if isinstance(seed, torch.Generator):
+            seed = int(torch.randint(0, 2 ** 62, (1,), generator=seed, device=seed.device).item())
+        elif seed is None:
+            seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        out = torch.empty(tuple(batch_shape) + (self.dim,), device=dev, dtype=torch.float32)
+        rows = out.numel() // self.dim
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().bfk_normal_fill(_lib.ptr(out), rows, self.dim, int(row_offset), _lib.ptr(self._mean),
+                                                  _lib.ptr(self._std), C.c_uint64(int(seed) & (2 ** 64 - 1)), None,
+                                                  _lib.stream_ptr()), "bfk_normal_fill")
+        return out
 
 
 class _Block(nn.Module):
@@ -568,7 +579,7 @@ class InferenceNetwork(nn.Module):
         batch_shape = _as_shape(batch_shape, kwargs)
         if "compute_prior_score" in kwargs:
             raise NotImplementedError("compositional sampling is out of scope (SURVEY.md §2 row 2)")
-        samples = self.base_distribution.sample(batch_shape, seed=seed)
+        samples = self.base_distribution.sample(batch_shape, seed=seed, row_offset=kwargs.pop("row_offset", 0))
         flat = samples.reshape(-1, samples.shape[-1])
         out = self(flat, conditions=conditions, inverse=True, density=False, seed=seed, **kwargs)
         return out.reshape(samples.shape)

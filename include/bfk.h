@@ -228,6 +228,30 @@ int bfk_sample_layerwise(const bfk_net_config* cfg, const bfk_weights* weights, 
 int bfk_num_sms(void);
 int bfk_fused_supported(const bfk_net_config* cfg); /* 1 if the on-chip sampler handles this config */
 
+/* ---- the approximator edge of the sampling path ---------------------------------------------
+ * bfk_normal_fill replaces DiagonalNormal.sample (bayesflow/distributions/diagonal_normal.py:100-105: mean + std *
+ * keras.random.normal) for the z of InferenceNetwork.sample (inference_network.py:109-125): out (rows, D) written in
+ * HBM, no host copy.  Philox4x32-10 keyed by `seed`, counter = global element index / 4, Box-Muller; element (r, d) of
+ * the stream is a function of (seed, (row_offset + r) * D + d) only, so a rank that passes its row_offset draws exactly
+ * the rows a single-GPU run would.  mean / stdv are (D) or NULL (0 / 1).  raw_words (rows*D uint32) or NULL: the raw
+ * generator output, for known-answer tests.
+ * bfk_standardize replaces Standardize.call with transformation_type="location_scale"
+ * (bayesflow/networks/helpers/standardization/standardize.py:50-133): forward (x - mean) / std, inverse x * std + mean,
+ * std = m2 > 0 ? sqrt(m2 / count) : 1 (:27-37); x, out are (rows, F), may alias.
+ * bfk_batch_moments + bfk_moments_merge replace Standardize._update_moments (:135-170): stats (2F+1 floats: mean[F],
+ * m2[F], count) are the batch moments of x (rows, F), computed in ONE read of x; bfk_moments_merge folds n_parts such
+ * records (n_parts, 2F+1) into the running (mean, m2, count) with the reference's pairwise update, in index order — one
+ * record for a single process, world_size records after an all-gather for data-parallel training.
+ * workspace: bfk_moments_workspace_floats(rows, F) floats. */
+int bfk_normal_fill(float* out, int64_t rows, int32_t D, int64_t row_offset, const float* mean, const float* stdv,
+                    uint64_t seed, uint32_t* raw_words, void* stream);
+int bfk_standardize(const float* x, float* out, int64_t rows, int32_t F, const float* mean, const float* m2,
+                    const float* count, int32_t forward, void* stream);
+size_t bfk_moments_workspace_floats(int64_t rows, int32_t F);
+int bfk_batch_moments(const float* x, int64_t rows, int32_t F, float* workspace, float* stats, void* stream);
+int bfk_moments_merge(float* mean, float* m2, float* count, const float* parts, int32_t n_parts, int32_t F,
+                      void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -18,3 +18,6 @@ from .networks import (  # noqa: F401
     OracleTimeMLP, OracleFlowMatching, OracleDiffusionModel, EDMNoiseSchedule, CosineNoiseSchedule,
     DiagonalNormal, init_params, perturb_params, count_flops_per_eval,
 )
+from .edge import (  # noqa: F401
+    OracleStandardize, philox4x32_10, philox_words, normal_stream, repeat_and_flatten_conditions, unflatten_samples,
+)

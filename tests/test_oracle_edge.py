@@ -1,0 +1,105 @@
+"""CPU tests for the approximator-edge oracle (oracle/edge.py): Philox known answers, and the reference's own
+Standardize tests (tests/test_networks/test_standardization.py) restated against the oracle."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+
+
+# Random123 kat_vectors, philox4x32 10 rounds: counter | key | expected
+PHILOX_KAT = [
+    ((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+    ((0xffffffff,) * 4, (0xffffffff,) * 2, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+    ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0),
+     (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1)),
+]
+
+
+@pytest.mark.parametrize("ctr,key,want", PHILOX_KAT)
+def test_philox_known_answers(ctr, key, want):
+    got = oracle.philox4x32_10(np.array([ctr], dtype=np.uint32), np.array(key, dtype=np.uint32))[0]
+    assert tuple(int(v) for v in got) == want
+
+
+def test_philox_words_offsets_are_slices_of_one_stream():
+    full = oracle.philox_words(64, seed=1234567890123)
+    for off, n in [(0, 64), (1, 7), (4, 8), (13, 30), (63, 1)]:
+        assert np.array_equal(oracle.philox_words(n, 1234567890123, off), full[off:off + n])
+    assert not np.array_equal(full, oracle.philox_words(64, seed=1234567890124))
+
+
+def test_normal_stream_moments_and_sharding():
+    z = oracle.normal_stream(50000, 4, seed=11)
+    assert abs(z.mean()) < 0.01 and abs(z.std() - 1.0) < 0.01
+    # excess kurtosis and tails of a standard normal
+    assert abs((z ** 4).mean() - 3.0) < 0.1 and 0.0015 < (np.abs(z) > 3).mean() < 0.004
+    part = oracle.normal_stream(100, 4, seed=11, row_offset=777)
+    assert np.array_equal(part, z[777:877])
+    shifted = oracle.normal_stream(100, 4, seed=11, row_offset=777, mean=[1, 2, 3, 4], std=[1, 2, 1, 0.5])
+    assert np.allclose(shifted, part * np.array([1, 2, 1, 0.5]) + np.array([1, 2, 3, 4]))
+
+
+# ---- reference tests for Standardize, restated (test_standardization.py) ------------------------------------------------
+def test_forward_standardization_training():
+    # test_standardization.py:11-30
+    x = torch.randn(8, 4)
+    layer = oracle.OracleStandardize(4)
+    out = layer(x, stage="training")
+    np.testing.assert_allclose(layer.moving_mean.numpy(), x.numpy().mean(0), atol=1e-5)
+    assert out.shape == x.shape and not torch.isnan(out).any()
+    np.testing.assert_allclose(out.numpy().std(0), 1.0, atol=1e-5)
+
+
+def test_forward_standardization_training_constant_batch():
+    # test_standardization.py:33-53: M2 == 0 -> std 1, output 0
+    x = torch.ones(8, 4)
+    layer = oracle.OracleStandardize(4)
+    out = layer(x, stage="training")
+    np.testing.assert_allclose(layer.moving_mean.numpy(), 1.0, atol=1e-5)
+    np.testing.assert_allclose(out.numpy(), 0.0, atol=1e-5)
+
+
+def test_inverse_standardization_ldj():
+    # test_standardization.py:56-69
+    x = torch.randn(1, 3)
+    layer = oracle.OracleStandardize(3)
+    layer(x, stage="training", forward=True)
+    inv, ldj = layer(x, stage="inference", forward=False, log_det_jac=True)
+    assert inv.shape == x.shape and ldj.shape == x.shape[:-1]
+
+
+def test_consistency_forward_inverse():
+    # test_standardization.py:72-89
+    x = torch.randn(4, 20, 5)
+    layer = oracle.OracleStandardize(5)
+    layer(x, stage="training", forward=True)
+    rec = layer(layer(x, stage="inference", forward=True), stage="inference", forward=False)
+    np.testing.assert_allclose(x.numpy(), rec.numpy(), atol=1e-4)
+
+
+def test_two_training_passes_equal_whole_data_moments():
+    # test_standardization.py:121-170 (nested_accuracy_forward): after two passes the combined data has mean 0 / std 1
+    a1, a2 = torch.randn(2, 3, 5) * 3 + 1, torch.randn(3, 3, 5) * 3 + 1
+    layer = oracle.OracleStandardize(5)
+    layer(a1, stage="training")
+    layer(a2, stage="training")
+    out = layer(torch.cat([a1, a2], 0), stage="inference").numpy()
+    np.testing.assert_allclose(out.mean((0, 1)), 0.0, atol=1e-4)
+    np.testing.assert_allclose(out.std((0, 1)), 1.0, atol=1e-4)
+    assert float(layer.count) == 15.0
+
+
+def test_non_default_transformation_is_rejected_forward():
+    # standardize.py:79-83
+    layer = oracle.OracleStandardize(3)
+    with pytest.raises(ValueError):
+        layer(torch.randn(2, 3), forward=True, transformation_type="both_sides_scale")
+
+
+def test_repeat_and_flatten_is_dataset_major():
+    # samplers.py:51-69
+    c = torch.arange(6.0).reshape(3, 2)
+    flat = oracle.repeat_and_flatten_conditions(c, 4)
+    assert flat.shape == (12, 2) and torch.equal(flat[4:8], c[1].expand(4, 2))
+    assert torch.equal(oracle.unflatten_samples(flat, 4)[:, 0], c)
