@@ -32,17 +32,18 @@ __host__ __device__ inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32
 // uniform in (0,1): 24 random bits + 1/2, exactly representable, never 0 or 1
 __device__ __forceinline__ float u01(uint32_t r) { return ((float)(r >> 8) + 0.5f) * 5.9604644775390625e-8f; }
 
-// 4 standard normals of quad q (Box-Muller on (r0,r1) and (r2,r3))
+// 4 standard normals of quad q: Box-Muller on word pairs (0,1) and (2,3), z = rad * (cos, sin)(2*pi*(u2 - 1/2)) with
+// rad = sqrt(-2 ln u1).  lg2 / sin / cos go to the MUFU pipe (the angle is centred so |theta| <= pi, where sin.approx and
+// cos.approx have 2^-21.4 absolute error); with libm calls the kernel is issue-bound at 0.28 of the HBM roofline.
 __device__ __forceinline__ void normal_quad(uint64_t q, uint64_t seed, float z[4]) {
   uint32_t c[4] = {(uint32_t)q, (uint32_t)(q >> 32), 0u, 0u};
   philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
 #pragma unroll
   for (int p = 0; p < 2; ++p) {
-    const float rad = sqrtf(-2.0f * logf(u01(c[2 * p])));
-    float s, co;
-    sincospif(2.0f * u01(c[2 * p + 1]), &s, &co);
-    z[2 * p] = rad * co;
-    z[2 * p + 1] = rad * s;
+    const float rad = sqrtf(-1.3862943611198906f * __log2f(u01(c[2 * p])));  // -2 ln u = -2 ln2 * lg2 u
+    const float th = 6.283185307179586f * (u01(c[2 * p + 1]) - 0.5f);
+    z[2 * p] = rad * __cosf(th);
+    z[2 * p + 1] = rad * __sinf(th);
   }
 }
 
@@ -94,33 +95,46 @@ template <bool FWD>
 __global__ void __launch_bounds__(256) standardize_kernel(const float* __restrict__ x, float* __restrict__ out,
                                                           long long n, int F, const float* __restrict__ mean,
                                                           const float* __restrict__ m2, const float* __restrict__ count) {
-  extern __shared__ float sm[];  // mean[F], std[F]
+  extern __shared__ float sm[];  // mean[F], std[F] (forward: 1/std)
   float* s_mean = sm;
   float* s_std = sm + F;
   const float cnt = count[0];
   for (int f = threadIdx.x; f < F; f += blockDim.x) {
     const float v = m2[f];
     s_mean[f] = mean[f];
-    s_std[f] = v > 0.0f ? sqrtf(v / cnt) : 1.0f;
+    const float sd = v > 0.0f ? sqrtf(v / cnt) : 1.0f;
+    s_std[f] = FWD ? 1.0f / sd : sd;  // forward multiplies by 1/std (<= 1 ulp from the reference's division; the IEEE
+                                      // division sequence holds the kernel at 0.71 of the copy bandwidth)
   }
   __syncthreads();
   const bool vec = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
   const long long nq = vec ? (n >> 2) : 0;
   const long long stride = (long long)gridDim.x * blockDim.x, t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  for (long long q = t0; q < nq; q += stride) {
-    float4 v = reinterpret_cast<const float4*>(x)[q];
-    float* p = reinterpret_cast<float*>(&v);
-    int f = (int)((q << 2) % F);
+  // four independent 16-byte loads in flight per thread (Little's law: ~40 KB per SM must be outstanding at 7.7 TB/s)
+  for (long long q0 = t0; q0 < nq; q0 += 4 * stride) {
+    float4 v[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      p[j] = FWD ? (p[j] - s_mean[f]) / s_std[f] : p[j] * s_std[f] + s_mean[f];
-      f = (f + 1 == F) ? 0 : f + 1;
+    for (int u = 0; u < 4; ++u) {
+      const long long q = q0 + u * stride;
+      if (q < nq) v[u] = __ldcs(reinterpret_cast<const float4*>(x) + q);
     }
-    reinterpret_cast<float4*>(out)[q] = v;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long q = q0 + u * stride;
+      if (q >= nq) break;
+      float* p = reinterpret_cast<float*>(&v[u]);
+      int f = (int)((q << 2) % F);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        p[j] = FWD ? (p[j] - s_mean[f]) * s_std[f] : p[j] * s_std[f] + s_mean[f];
+        f = (f + 1 == F) ? 0 : f + 1;
+      }
+      __stcs(reinterpret_cast<float4*>(out) + q, v[u]);
+    }
   }
   for (long long i = (nq << 2) + t0; i < n; i += stride) {
     const int f = (int)(i % F);
-    out[i] = FWD ? (x[i] - s_mean[f]) / s_std[f] : x[i] * s_std[f] + s_mean[f];
+    out[i] = FWD ? (x[i] - s_mean[f]) * s_std[f] : x[i] * s_std[f] + s_mean[f];
   }
 }
 
@@ -195,17 +209,91 @@ __global__ void moments_partial_kernel(const float* __restrict__ x, long long ro
   }
 }
 
-// stats (2F+1): mean[F], m2[F], count — the batch moments, blocks merged in index order
-__global__ void moments_finish_kernel(const float* __restrict__ partial, int n_blocks, int F, float* __restrict__ stats) {
-  for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < F; f += gridDim.x * blockDim.x) {
-    Moments a = {0.0f, 0.0f, 0.0f};
-    for (int b = 0; b < n_blocks; ++b) {
-      const float* p = partial + (size_t)b * 3 * F;
-      a = merge_moments(a, Moments{p[f], p[F + f], p[2 * F + f]});
+// 16-byte variant (x 16-byte aligned).  The float4 stream has period P = F / gcd(F, 4): float4 number i holds features
+// (4 i + j) % F, which depends only on i % P.  Thread (tx = tid % P, ty = tid / P) reads float4s {g * P + tx} for its
+// period groups g, so each of its four lanes always sees ONE feature.  Lanes are merged through shared memory: a tree
+// over ty, then the 4P/F replicas of every feature in index order.  Block 0 also takes the < 4P floats left over.
+__global__ void moments_partial_vec_kernel(const float* __restrict__ x, long long n, int F, int P,
+                                           float* __restrict__ partial) {
+  extern __shared__ float sm[];  // [3][TY][4P]
+  const int TY = blockDim.x / P, tx = threadIdx.x % P, ty = threadIdx.x / P, LP = 4 * P;
+  const long long groups = n / LP;  // whole periods
+  const long long per_block = (groups + gridDim.x - 1) / gridDim.x;
+  const long long g_lo = (long long)blockIdx.x * per_block;
+  const long long g_hi = g_lo + per_block < groups ? g_lo + per_block : groups;
+  const float4* x4 = reinterpret_cast<const float4*>(x);
+  if (ty < TY) {
+    float K[4] = {0.f, 0.f, 0.f, 0.f}, s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f}, cnt = 0.0f;
+    if (g_lo + ty < g_hi) {
+      const float4 v = x4[(g_lo + ty) * P + tx];
+      K[0] = v.x, K[1] = v.y, K[2] = v.z, K[3] = v.w;
     }
-    stats[f] = a.mean;
-    stats[F + f] = a.m2;
-    if (f == 0) stats[2 * F] = a.n;
+#pragma unroll 4
+    for (long long g = g_lo + ty; g < g_hi; g += TY) {
+      const float4 v = __ldcs(x4 + g * P + tx);
+      const float d0 = v.x - K[0], d1 = v.y - K[1], d2 = v.z - K[2], d3 = v.w - K[3];
+      s1[0] += d0, s1[1] += d1, s1[2] += d2, s1[3] += d3;
+      s2[0] = fmaf(d0, d0, s2[0]), s2[1] = fmaf(d1, d1, s2[1]), s2[2] = fmaf(d2, d2, s2[2]), s2[3] = fmaf(d3, d3, s2[3]);
+      cnt += 1.0f;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int pos = ty * LP + 4 * tx + j;
+      sm[pos] = cnt;
+      sm[TY * LP + pos] = cnt > 0.0f ? K[j] + s1[j] / cnt : 0.0f;
+      sm[2 * TY * LP + pos] = cnt > 0.0f ? fmaxf(s2[j] - s1[j] * s1[j] / cnt, 0.0f) : 0.0f;
+    }
+  }
+  __syncthreads();
+  int span = 1;
+  while (span < TY) span <<= 1;
+  for (int s = span >> 1; s >= 1; s >>= 1) {
+    if (ty < s && ty + s < TY) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int a_ = ty * LP + 4 * tx + j, b_ = (ty + s) * LP + 4 * tx + j;
+        Moments a = {sm[a_], sm[TY * LP + a_], sm[2 * TY * LP + a_]};
+        a = merge_moments(a, Moments{sm[b_], sm[TY * LP + b_], sm[2 * TY * LP + b_]});
+        sm[a_] = a.n, sm[TY * LP + a_] = a.mean, sm[2 * TY * LP + a_] = a.m2;
+      }
+    }
+    __syncthreads();
+  }
+  for (int f = threadIdx.x; f < F; f += blockDim.x) {
+    Moments a = {0.0f, 0.0f, 0.0f};
+    for (int pos = f; pos < LP; pos += F) a = merge_moments(a, Moments{sm[pos], sm[TY * LP + pos], sm[2 * TY * LP + pos]});
+    if (blockIdx.x == 0)  // leftover rows (fewer than 4P / F of them)
+      for (long long i = groups * LP + f; i < n; i += F) a = merge_moments(a, Moments{1.0f, x[i], 0.0f});
+    float* p = partial + (size_t)blockIdx.x * 3 * F;
+    p[f] = a.n, p[F + f] = a.mean, p[2 * F + f] = a.m2;
+  }
+}
+
+// stats (2F+1): mean[F], m2[F], count — the batch moments, blocks merged in index order
+__global__ void __launch_bounds__(256) moments_finish_kernel(const float* __restrict__ partial, int n_blocks, int F,
+                                                             float* __restrict__ stats) {
+  // one block per feature: thread i folds partials i, i+256, ... (index order), then a fixed-order tree over threads —
+  // a single thread walking all ~1200 partials is a 0.4 ms chain of dependent L2 round trips
+  __shared__ float s_n[256], s_mean[256], s_m2[256];
+  const int f = blockIdx.x, t = threadIdx.x;
+  Moments a = {0.0f, 0.0f, 0.0f};
+  for (int b = t; b < n_blocks; b += 256) {
+    const float* p = partial + (size_t)b * 3 * F;
+    a = merge_moments(a, Moments{p[f], p[F + f], p[2 * F + f]});
+  }
+  s_n[t] = a.n, s_mean[t] = a.mean, s_m2[t] = a.m2;
+  __syncthreads();
+  for (int s = 128; s >= 1; s >>= 1) {
+    if (t < s) {
+      a = merge_moments(Moments{s_n[t], s_mean[t], s_m2[t]}, Moments{s_n[t + s], s_mean[t + s], s_m2[t + s]});
+      s_n[t] = a.n, s_mean[t] = a.mean, s_m2[t] = a.m2;
+    }
+    __syncthreads();
+  }
+  if (t == 0) {
+    stats[f] = s_mean[0];
+    stats[F + f] = s_m2[0];
+    if (f == 0) stats[2 * F] = s_n[0];
   }
 }
 
@@ -290,12 +378,19 @@ extern "C" int bfk_batch_moments(const float* x, int64_t rows, int32_t F, float*
   const int sms = bfk_num_sms();
   if (sms <= 0) return fail(-62, "bfk_batch_moments: no CUDA device");
   cudaStream_t st = (cudaStream_t)stream;
-  const int tpb = F <= 256 ? 256 : 1024, TY = tpb / F;
   const int blocks = bfk::moments_blocks(rows, F, sms);
-  const size_t smem = 3 * (size_t)TY * F * sizeof(float);
-  bfk::moments_partial_kernel<<<blocks, tpb, smem, st>>>(x, rows, F, workspace);
+  const int P = F / ((F % 4 == 0) ? 4 : (F % 2 == 0) ? 2 : 1);  // float4 period of the feature pattern
+  if ((reinterpret_cast<uintptr_t>(x) & 15) == 0 && rows > 0) {
+    const int tpb = P <= 256 ? 256 : 1024, TY = tpb / P;
+    const size_t smem = 3 * (size_t)TY * 4 * P * sizeof(float);  // <= 48 KB: TY * P <= 1024
+    bfk::moments_partial_vec_kernel<<<blocks, tpb, smem, st>>>(x, (long long)rows * F, F, P, workspace);
+  } else {
+    const int tpb = F <= 256 ? 256 : 1024, TY = tpb / F;
+    const size_t smem = 3 * (size_t)TY * F * sizeof(float);
+    bfk::moments_partial_kernel<<<blocks, tpb, smem, st>>>(x, rows, F, workspace);
+  }
   CK(cudaGetLastError());
-  bfk::moments_finish_kernel<<<(F + 127) / 128, 128, 0, st>>>(workspace, blocks, F, stats);
+  bfk::moments_finish_kernel<<<F, 256, 0, st>>>(workspace, blocks, F, stats);
   CK(cudaGetLastError());
   return 0;
 }

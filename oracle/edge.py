@@ -57,7 +57,7 @@ def normal_stream(rows: int, D: int, seed: int, row_offset: int = 0, mean=None, 
     q0, q1 = e0 // 4, (e0 + n - 1) // 4
     words = philox_words(4 * (q1 - q0 + 1), seed, 4 * q0).reshape(-1, 2, 2)
     rad = np.sqrt(-2.0 * np.log(_u01(words[..., 0])))
-    ang = 2.0 * np.pi * _u01(words[..., 1])
+    ang = 2.0 * np.pi * (_u01(words[..., 1]) - 0.5)  # centred: |angle| <= pi
     z = np.stack([rad * np.cos(ang), rad * np.sin(ang)], axis=-1).reshape(-1)
     z = z[e0 - 4 * q0: e0 - 4 * q0 + n].reshape(rows, D)
     if std is not None:
