@@ -7,6 +7,7 @@ from .networks import (  # noqa: F401
 from .integrate import integrate  # noqa: F401
 from .standardization import Standardize, Standardization  # noqa: F401
 from .samplers import Sampler  # noqa: F401
+from .consistency import ConsistencyModel  # noqa: F401
 from .parallel import dataset_shard, sample_sharded, gather_rows  # noqa: F401
 
 __version__ = "0.1.0"

@@ -94,6 +94,8 @@ def lib():
                                   C.c_void_p, C.c_void_p]
     L.bfk_standardize.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                   C.c_int32, C.c_void_p]
+    L.bfk_lincomb3.argtypes = [C.c_void_p, C.c_float, C.c_void_p, C.c_float, C.c_void_p, C.c_float, C.c_void_p, C.c_int64,
+                               C.c_void_p]
     L.bfk_moments_workspace_floats.restype = C.c_size_t
     L.bfk_moments_workspace_floats.argtypes = [C.c_int64, C.c_int32]
     L.bfk_batch_moments.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]

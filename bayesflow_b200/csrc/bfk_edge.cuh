@@ -326,6 +326,19 @@ static inline int moments_blocks(long long rows, int F, int n_sms) {
   return (int)(want < cap ? want : cap);
 }
 
+// out = a*x + b*y + c*z over a flat fp32 buffer (y, z optional)
+__global__ void __launch_bounds__(256) lincomb3_kernel(float* __restrict__ out, float a, const float* __restrict__ x, float b,
+                                                       const float* __restrict__ y, float c, const float* __restrict__ z,
+                                                       long long n) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    float v = a * x[i];
+    if (y) v = fmaf(b, y[i], v);
+    if (z) v = fmaf(c, z[i], v);
+    out[i] = v;
+  }
+}
+
 }  // namespace bfk
 
 // ---- C ABI ------------------------------------------------------------------------------------------------------------
@@ -401,6 +414,20 @@ extern "C" int bfk_moments_merge(float* mean, float* m2, float* count, const flo
   if (n_parts == 0) return 0;
   if (!mean || !m2 || !count || !parts) return fail(-68, "bfk_moments_merge: null pointer");
   bfk::moments_merge_kernel<<<1, F < 256 ? 256 : 1024, 0, (cudaStream_t)stream>>>(mean, m2, count, parts, n_parts, F);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_lincomb3(float* out, float a, const float* x, float b, const float* y, float c, const float* z,
+                            int64_t numel, void* stream) {
+  if (numel < 0) return fail(-69, "bfk_lincomb3: bad numel");
+  if (numel == 0) return 0;
+  if (!out || !x) return fail(-70, "bfk_lincomb3: null pointer");
+  const int sms = bfk_num_sms();
+  if (sms <= 0) return fail(-62, "bfk_lincomb3: no CUDA device");
+  long long blocks = (numel + 255) / 256, cap = (long long)sms * 8;
+  if (blocks > cap) blocks = cap;
+  bfk::lincomb3_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(out, a, x, b, y, c, z, numel);
   CK(cudaGetLastError());
   return 0;
 }

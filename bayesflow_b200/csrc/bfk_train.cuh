@@ -565,13 +565,15 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
 
 // ---------------------------------------------------------------------------------------------------------------
 // Loss head.  resid = a_b*pred - target;  loss_b = w_b * mean_i resid^2 (mse) | mean_i |resid| (mae)
+//   | mean_i (sqrt(resid^2 + c^2) - c) (kind 2, pseudo-Huber: ConsistencyModel, consistency_model.py:413-414 with
+//   a = c_out(t2), target = teacher - c_skip(t2) * input, w = 1 / (t2 - t1))
 //   FlowMatching: a = 1, target = x1 - x0 (flow_matching.py:170-176);  DiffusionModel: a_b and target from the schedule
 //   (diffusion_model.py:197-230).  Writes the un-normalised dLoss/dpred image (64 features, zeros beyond D), adds
 //   loss_scale * sum_b loss_b to *loss and gscale * column sums to d_bo.  One thread per row.
 __global__ void loss_kernel(const float* __restrict__ pred, long long ldp, const float* __restrict__ target,
                             const float* __restrict__ a_row, const float* __restrict__ w_row, long long B, long long R_pad,
-                            int D, int mae, unsigned char* __restrict__ dout_img, int KO8, float* __restrict__ loss,
-                            float loss_scale, float* __restrict__ d_bo, float gscale) {
+                            int D, int kind, unsigned char* __restrict__ dout_img, int KO8, float* __restrict__ loss,
+                            float loss_scale, float* __restrict__ d_bo, float gscale, float huber_c) {
   __shared__ float s_loss;
   __shared__ float s_db[64];
   if (threadIdx.x == 0) s_loss = 0.f;
@@ -591,7 +593,12 @@ __global__ void loss_kernel(const float* __restrict__ pred, long long ldp, const
         float g = 0.f;
         if (valid && k < D) {
           const float res = av * pred[r * ldp + k] - target[r * D + k];
-          if (mae) { lrow += fabsf(res); g = wv * av * (res > 0.f ? 1.f : (res < 0.f ? -1.f : 0.f)); }
+          if (kind == 1) { lrow += fabsf(res); g = wv * av * (res > 0.f ? 1.f : (res < 0.f ? -1.f : 0.f)); }
+          else if (kind == 2) {
+            const float rt = sqrtf(fmaf(res, res, huber_c * huber_c));
+            lrow += rt - huber_c;
+            g = wv * av * res / rt;
+          }
           else { lrow = fmaf(res, res, lrow); g = 2.f * wv * av * res; }
           atomicAdd(&s_db[k], g);
         }

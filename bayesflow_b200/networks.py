@@ -579,7 +579,10 @@ class InferenceNetwork(nn.Module):
         batch_shape = _as_shape(batch_shape, kwargs)
         if "compute_prior_score" in kwargs:
             raise NotImplementedError("compositional sampling is out of scope (SURVEY.md §2 row 2)")
-        samples = self.base_distribution.sample(batch_shape, seed=seed, row_offset=kwargs.pop("row_offset", 0))
+        row_offset = kwargs.pop("row_offset", 0)
+        if getattr(self, "_wants_noise_offset", False):  # samplers that draw more noise after z (ConsistencyModel)
+            kwargs["noise_row_offset"] = row_offset
+        samples = self.base_distribution.sample(batch_shape, seed=seed, row_offset=row_offset)
         flat = samples.reshape(-1, samples.shape[-1])
         out = self(flat, conditions=conditions, inverse=True, density=False, seed=seed, **kwargs)
         return out.reshape(samples.shape)

@@ -26,7 +26,7 @@ class TrainArgs(C.Structure):
     _fields_ = [("x", C.c_void_p), ("t", C.c_void_p), ("cond", C.c_void_p), ("target", C.c_void_p),
                 ("pred_scale", C.c_void_p), ("row_weight", C.c_void_p), ("B", C.c_int64), ("loss", C.c_int32),
                 ("dw_swap", C.c_int32), ("dropout", C.c_float), ("loss_scale", C.c_float), ("grad_scale", C.c_float),
-                ("seed", C.c_uint64)]
+                ("seed", C.c_uint64), ("huber_c", C.c_float)]
 
 
 def _bind(L):
@@ -135,7 +135,7 @@ class TrainEngine:
 
     def step(self, x, t, conditions, target, *, pred_scale=None, row_weight=None, loss="mse", dropout=0.0, seed=0,
              global_batch=None, backward=True, zero_grad=True, want_pred=False, want_loss=True, _dw_swap=0,
-             cotangent_scale=1.0):
+             cotangent_scale=1.0, huber_c=0.0):
         """One forward (+ loss, + backward).  Gradients are accumulated into ``self.grad`` (zeroed first unless
         ``zero_grad=False``) scaled by 1/(global_batch*D).  Returns (loss 0-d device tensor or None, pred or None)."""
         net = self.net
@@ -159,11 +159,12 @@ class TrainEngine:
             (target.data_ptr() if target is not None else None)
         a.pred_scale = pred_scale.data_ptr() if pred_scale is not None else None
         a.row_weight = row_weight.data_ptr() if row_weight is not None else None
-        a.B, a.loss, a.dw_swap = B, {"mse": 0, "mae": 1}[loss], int(_dw_swap)
+        a.B, a.loss, a.dw_swap = B, {"mse": 0, "mae": 1, "pseudo_huber": 2}[loss], int(_dw_swap)
         a.dropout, a.seed = float(dropout), int(seed) & (2 ** 64 - 1)
+        a.huber_c = float(huber_c)
         # `cotangent_scale` (a power of two already folded into row_weight by the caller) keeps the fp16 cotangent image
         # in range; loss and gradients are un-scaled here
-        a.loss_scale = 1.0 / (gb * (D if loss in ("mse", "mae") else 1)) / cotangent_scale
+        a.loss_scale = 1.0 / (gb * (D if loss in ("mse", "mae", "pseudo_huber") else 1)) / cotangent_scale
         a.grad_scale = 1.0 / (gb * D) / cotangent_scale
         ws = self._workspace(B, backward)
         if backward and zero_grad:

@@ -162,7 +162,8 @@ int bfk_gemm(const void* A_packed, const void* B_packed, float* C, int64_t ldc, 
 /* ---- training step (FlowMatching.compute_metrics flow_matching.py:132-178, DiffusionModel.compute_metrics
  * diffusion_model.py:142-232; gradients = what torch autograd returns in torch_approximator.py:88-99) ----------------
  * The network sees x (B,D), the per-row subnet time t (B) and conditions (B,C).  The loss head is
- *     loss = loss_scale * sum_b w_b * mean_i L(a_b * pred_bi - target_bi),  L = square (0) or abs (1)
+ *     loss = loss_scale * sum_b w_b * mean_i L(a_b * pred_bi - target_bi),  L = square (0), abs (1) or the
+ *     pseudo-Huber sqrt(r^2 + huber_c^2) - huber_c (2; ConsistencyModel.compute_metrics, consistency_model.py:405-416)
  * which covers FlowMatching (a = 1, target = x1 - x0) and every DiffusionModel prediction/loss type (a_b, target from
  * the noise schedule).  Gradients are ADDED to the tensors in `grads` (same struct as the weights; zero them first),
  * already multiplied by grad_scale (= 1/(B_global*D) for the reference's mean).  grads == NULL: forward (+ loss) only.
@@ -173,11 +174,12 @@ typedef struct bfk_train_args {
   const float* pred_scale; /* (B) or NULL */
   const float* row_weight; /* (B) or NULL */
   int64_t B;
-  int32_t loss;            /* 0 mse, 1 mae */
+  int32_t loss;            /* 0 mse, 1 mae, 2 pseudo-Huber */
   int32_t dw_swap;         /* debug: swap LBO/SBO of the MN-major descriptors; must be 0 */
   float dropout;
   float loss_scale, grad_scale;
   uint64_t seed;
+  float huber_c;           /* loss == 2 only */
 } bfk_train_args;
 size_t bfk_train_workspace_bytes(const bfk_net_config* cfg, int64_t B, int32_t backward);
 int bfk_train_step(const bfk_net_config* cfg, const bfk_weights* weights, const bfk_weights* grads,
@@ -247,6 +249,11 @@ int bfk_normal_fill(float* out, int64_t rows, int32_t D, int64_t row_offset, con
                     uint64_t seed, uint32_t* raw_words, void* stream);
 int bfk_standardize(const float* x, float* out, int64_t rows, int32_t F, const float* mean, const float* m2,
                     const float* count, int32_t forward, void* stream);
+/* out[i] = a*x[i] + b*y[i] + c*z[i] (y, z may be NULL; out may alias any input): the state updates of the
+ * ConsistencyModel multistep sampler (consistency_model.py:300-306: x_n = x + sqrt(t_n^2 - eps^2) * noise) and of its
+ * consistency function (:336-342: c_skip(t) * x + c_out(t) * f). */
+int bfk_lincomb3(float* out, float a, const float* x, float b, const float* y, float c, const float* z, int64_t numel,
+                 void* stream);
 size_t bfk_moments_workspace_floats(int64_t rows, int32_t F);
 int bfk_batch_moments(const float* x, int64_t rows, int32_t F, float* workspace, float* stats, void* stream);
 int bfk_moments_merge(float* mean, float* m2, float* count, const float* parts, int32_t n_parts, int32_t F,

@@ -1,0 +1,120 @@
+"""GPU parity tests for ConsistencyModel (consistency_model.py:21-416) against
+oracle/consistency.py on identical weights: consistency function, multistep sampling with the SAME per-step noise
+(the product's Philox stream restated by oracle.normal_stream), pseudo-Huber training loss and every gradient."""
+import pytest
+import torch
+
+import oracle
+from oracle.consistency import GOLDEN
+from _util import rel_l2
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-3
+
+
+def make_cm(D, C, widths=(256,) * 5, total_steps=100, **sk):
+    import bayesflow_b200 as bf
+    params = oracle.perturb_params(oracle.init_params(D, C, widths, **{k: v for k, v in sk.items() if k in ("merge", "norm")}))
+    kw = {"dropout": 0.0, "widths": widths} | sk
+    net = bf.ConsistencyModel(total_steps, subnet_kwargs=kw)
+    orc = oracle.OracleConsistencyModel(params, D, total_steps, subnet_kwargs=kw)
+    assert not net.built
+    net.build((None, D), (None, C) if C else None)
+    assert net.built and net.variables  # test_consistency_model.py:16-24
+    res = net.load_state_dict(params, strict=False)
+    assert not res.unexpected_keys and not [k for k in res.missing_keys if "base_distribution" not in k], res
+    return net.cuda(), orc
+
+
+SHAPES = [(2, 32, (256,) * 5), (4, None, (128,) * 3), (16, 8, (512,) * 2), (64, 32, (1024,) * 2)]
+
+
+@pytest.mark.parametrize("D,C,widths", SHAPES)
+def test_consistency_function_matches_oracle(D, C, widths):
+    net, orc = make_cm(D, C, widths)
+    B = 300
+    x = torch.randn(B, D) * 3
+    c = torch.randn(3, C).repeat_interleave(100, 0) if C else None
+    for t in (80.0, 3.7, 0.05, net.eps):
+        out = net.consistency_function(x.cuda(), t, conditions=c.cuda() if C else None)
+        ref = orc.consistency_function(x, t, c)
+        assert rel_l2(out, ref) < TOL, t
+    # boundary condition f(x, eps) = x holds exactly up to fp32 rounding
+    assert rel_l2(net.consistency_function(x.cuda(), net.eps, conditions=c.cuda() if C else None), x) < 1e-6
+
+
+@pytest.mark.parametrize("D,C,widths", SHAPES)
+@pytest.mark.parametrize("steps", [2, 3, 11])
+def test_multistep_sampling_fixed_noise_matches_oracle(D, C, widths, steps):
+    net, orc = make_cm(D, C, widths)
+    B, seed = 256, 1234
+    z = torch.randn(B, D)
+    c = torch.randn(B, C) if C else None
+
+    def noise_fn(n, shape):
+        return torch.from_numpy(oracle.normal_stream(shape[0], shape[1], (seed + n * GOLDEN) % 2 ** 64)).float()
+
+    out = net(z.cuda(), conditions=c.cuda() if C else None, inverse=True, steps=steps, seed=seed)
+    ref = orc.inverse(z, c, steps=steps, noise_fn=noise_fn)
+    assert out.shape == z.shape
+    assert rel_l2(out, ref) < TOL
+    again = net(z.cuda(), conditions=c.cuda() if C else None, inverse=True, steps=steps, seed=seed)
+    assert torch.equal(out, again)  # deterministic under a seed (test_consistency_model.py seed tests)
+
+
+def test_reference_surface_behaviour():
+    net, orc = make_cm(2, 3, (64, 64))
+    x, c = torch.randn(5, 2).cuda(), torch.randn(5, 3).cuda()
+    with pytest.raises(NotImplementedError):  # test_consistency_model.py:30-37
+        net(x, conditions=c)
+    for bs in (1, 4, 7):  # :55-67
+        assert net(torch.randn(bs, 2).cuda(), conditions=torch.randn(bs, 3).cuda(), inverse=True).shape == (bs, 2)
+    draws = net.sample((9,), conditions=torch.randn(9, 3).cuda(), seed=3)
+    assert draws.shape == (9, 2) and torch.isfinite(draws).all()
+    with pytest.raises(ValueError):
+        import bayesflow_b200 as bf
+        bf.ConsistencyModel(total_steps=5)
+    # target mask: masked coordinates are held at targets_fixed through every step (:278-306)
+    mask, fixed = torch.tensor([1.0, 0.0]).cuda(), torch.tensor([0.0, 0.25]).cuda()
+    out = net(torch.randn(6, 2).cuda(), conditions=torch.randn(6, 3).cuda(), inverse=True, steps=3, seed=1,
+              target_mask=mask, targets_fixed=fixed)
+    assert torch.allclose(out[:, 1], torch.full((6,), 0.25).cuda())
+
+
+def oracle_loss_and_grads(orc, x, c, fixed, w=None):
+    ps = {k: v.clone().requires_grad_(True) for k, v in orc.p.items()}
+    old = orc.p, orc.subnet.p
+    orc.p = orc.subnet.p = ps
+    try:
+        loss = orc.compute_metrics(x, conditions=c, sample_weight=w, stage="training", fixed=fixed)["loss"]
+        loss.backward()
+    finally:
+        orc.p, orc.subnet.p = old
+    return float(loss.detach()), {k: v.grad for k, v in ps.items()}
+
+
+@pytest.mark.parametrize("D,C,widths,B", [(2, 32, (256,) * 5, 1000), (4, None, (128,) * 3, 513), (64, 32, (1024,) * 2, 512)])
+def test_training_loss_and_all_gradients(D, C, widths, B):
+    net, orc = make_cm(D, C, widths)
+    g = torch.Generator().manual_seed(77)
+    x = torch.randn(B, D, generator=g)
+    c = torch.randn(B, C, generator=g) if C else None
+    idx = torch.randint(0, 10, (B,), generator=g)  # N(k=1) = 11 discretisation points -> 10 intervals
+    noise = torch.randn(B, D, generator=g)
+    w = torch.rand(B, generator=g) + 0.5
+    ref_loss, ref = oracle_loss_and_grads(orc, x, c, (idx, noise), w)
+    out = net.compute_metrics(x.cuda(), conditions=c.cuda() if C else None, sample_weight=w.cuda(), stage="training",
+                              fixed=(idx, noise))
+    loss = out["loss"]
+    loss.backward()
+    assert net.current_step == orc.current_step == 1
+    assert abs(float(loss) - ref_loss) <= TOL * abs(ref_loss), (float(loss), ref_loss)
+    checked = 0
+    for name, p in net.named_parameters():
+        if name in ref and ref[name] is not None:
+            assert p.grad is not None, name
+            # the pseudo-Huber derivative r / sqrt(r^2 + c^2) with c = 0.00054 sqrt(D) is a smoothed sign function:
+            # residuals within the fp16-operand error of 0 flip it, so the gate is looser than for the smooth losses
+            assert rel_l2(p.grad, ref[name]) < 2e-2, (name, rel_l2(p.grad, ref[name]))
+            checked += 1
+    assert checked >= 10

@@ -103,3 +103,33 @@ def test_repeat_and_flatten_is_dataset_major():
     flat = oracle.repeat_and_flatten_conditions(c, 4)
     assert flat.shape == (12, 2) and torch.equal(flat[4:8], c[1].expand(4, 2))
     assert torch.equal(oracle.unflatten_samples(flat, 4)[:, 0], c)
+
+
+# ---- ConsistencyModel oracle anchors (closed-form properties of the parameterisation) ---------------------------------
+def test_consistency_boundary_condition_and_discretisation_end_points():
+    D, Cd = 3, 4
+    params = oracle.perturb_params(oracle.init_params(D, Cd, (64, 64)))
+    cm = oracle.OracleConsistencyModel(params, D, total_steps=100, subnet_kwargs={"widths": (64, 64), "dropout": 0.0})
+    x, c = torch.randn(7, D), torch.randn(7, Cd)
+    # f(x, eps) = x: c_skip(eps) = 1, c_out(eps) = 0 (Song et al. 2023 eq. 5; consistency_model.py:336-342)
+    assert torch.allclose(cm.consistency_function(x, cm.eps, c), x, atol=1e-6)
+    dt = cm.discretize_time(11, dtype=torch.float64)
+    assert abs(float(dt[0]) - cm.eps) < 1e-12 and abs(float(dt[-1]) - cm.max_time) < 1e-9 and bool((dt[1:] > dt[:-1]).all())
+    # N(k) doubles from s0 + 1 to s1 + 1 (consistency_model.py:153-162, :201-203)
+    assert cm.schedule_discretization(0) == 11.0 and cm.schedule_discretization(100) == 151.0
+    assert sorted({int(cm.schedule_discretization(s)) for s in range(100)}) == [11, 21, 41, 81, 151]
+    with pytest.raises(ValueError):
+        oracle.OracleConsistencyModel(params, D, total_steps=5)
+
+
+def test_consistency_loss_and_one_step_sampling_are_finite():
+    D = 2
+    params = oracle.perturb_params(oracle.init_params(D, None, (64, 64)))
+    cm = oracle.OracleConsistencyModel(params, D, total_steps=100, subnet_kwargs={"widths": (64, 64), "dropout": 0.0})
+    x = torch.randn(16, D)
+    idx, noise = torch.randint(0, 9, (16,)), torch.randn(16, D)
+    loss = cm.compute_metrics(x, stage="validation", fixed=(idx, noise))["loss"]
+    assert float(loss) > 0 and torch.isfinite(loss)
+    # two-step sampling (steps=1 divides 0 by 0 in _discretize_time, in the reference too): c_skip(T) ~ 1.6e-4, so the draw is c_out(T) * f, not the T-scaled input
+    out = cm.inverse(torch.randn(64, D), steps=2)
+    assert out.shape == (64, D) and bool(torch.isfinite(out).all())
