@@ -100,6 +100,15 @@ def lib():
     L.bfk_moments_workspace_floats.argtypes = [C.c_int64, C.c_int32]
     L.bfk_batch_moments.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
     L.bfk_moments_merge.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
+    L.bfk_ot_cost.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
+    L.bfk_ot_ratio.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]
+    L.bfk_ot_scale.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_int64, C.c_void_p]
+    L.bfk_ot_work_floats.restype = C.c_size_t
+    L.bfk_ot_work_floats.argtypes = [C.c_int64, C.c_int64]
+    L.bfk_ot_init.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_float, C.c_int64, C.c_void_p]
+    L.bfk_ot_log_sinkhorn_step.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.c_void_p]
+    L.bfk_ot_sample.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_uint64, C.c_void_p, C.c_void_p]
     _lib = L
     return L
 

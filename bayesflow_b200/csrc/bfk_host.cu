@@ -434,3 +434,4 @@ extern "C" int bfk_gemm(const void* A, const void* B, float* Cm, int64_t ldc, in
 #include "bfk_train_host.cuh"
 #include "bfk_layerwise_host.cuh"
 #include "bfk_edge.cuh"
+#include "bfk_ot.cuh"

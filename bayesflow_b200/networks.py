@@ -600,7 +600,7 @@ class InferenceNetwork(nn.Module):
         gradient; ``loss.backward()`` then fills ``p.grad`` exactly like the reference's autograd path."""
         from .training import _LossWithGrads, train_engine
         backward = torch.is_grad_enabled() and stage == "training"
-        extra = {k: kwargs[k] for k in ("fixed", "row_offset") if k in kwargs}
+        extra = {k: kwargs[k] for k in ("fixed", "row_offset", "ot_seed") if k in kwargs}
         loss = self._loss_and_grads(x, conditions, sample_weight, stage=stage, seed=kwargs.get("seed"), backward=backward,
                                     **extra)
         if backward:
@@ -694,10 +694,9 @@ class FlowMatching(InferenceNetwork):
                  time_power_law_alpha: float = 0.0, drop_cond_prob: float = 0.0, drop_target_prob: float = 0.0, **kwargs):
         super().__init__(base_distribution, **kwargs)
         self.use_optimal_transport = use_optimal_transport
-        if use_optimal_transport:
-            raise NotImplementedError("optimal-transport pairing is out of scope (SURVEY.md §8f rank 4)")
         self.integrate_kwargs = FLOW_MATCHING_INTEGRATE_DEFAULTS | (integrate_kwargs or {})
-        self.optimal_transport_kwargs = optimal_transport_kwargs or {}
+        from .optimal_transport import OPTIMAL_TRANSPORT_DEFAULTS
+        self.optimal_transport_kwargs = OPTIMAL_TRANSPORT_DEFAULTS | (optimal_transport_kwargs or {})  # flow_matching.py:113
         if loss_fn not in ("mse", "mae"):
             raise NotImplementedError("loss_fn must be 'mse' or 'mae' on the accelerated path")
         self.loss_fn = loss_fn
@@ -758,6 +757,11 @@ class FlowMatching(InferenceNetwork):
             if not x1.is_cuda:
                 raise RuntimeError("bayesflow_b200 runs on CUDA tensors only (no CPU fallback)")
             x0 = self.base_distribution.sample(tuple(x1.shape[:-1]))
+            if self.use_optimal_transport:
+                # flow_matching.py:146-157: x1 (and its conditions) are re-drawn along the transport plan, x0 is kept
+                from .optimal_transport import optimal_transport
+                x0, x1, conditions = optimal_transport(x0, x1, conditions=conditions, seed=kwargs.get("ot_seed"),
+                                                       **self.optimal_transport_kwargs)
             u = torch.rand((x0.shape[0],), device=x1.device)
             t = u ** (1 + self.time_power_law_alpha)
             x, target = eng.interpolate(x0, x1, t)

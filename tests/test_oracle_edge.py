@@ -133,3 +133,39 @@ def test_consistency_loss_and_one_step_sampling_are_finite():
     # two-step sampling (steps=1 divides 0 by 0 in _discretize_time, in the reference too): c_skip(T) ~ 1.6e-4, so the draw is c_out(T) * f, not the T-scaled input
     out = cm.inverse(torch.randn(64, D), steps=2)
     assert out.shape == (64, D) and bool(torch.isfinite(out).all())
+
+
+# ---- optimal transport oracle, pinned by the reference's closed-form tests (test_optimal_transport.py) ------------------
+def test_log_sinkhorn_plan_correct_marginals():
+    # test_optimal_transport.py:215-224
+    from oracle.optimal_transport import log_sinkhorn_plan
+    x1, x2 = torch.randn(10, 2), torch.randn(20, 2)
+    lp = log_sinkhorn_plan(x1, x2, atol=1e-5, max_steps=1000)
+    assert torch.allclose(torch.logsumexp(lp, 0), torch.full((20,), -np.log(20.0)), atol=1e-3)
+    assert torch.allclose(torch.logsumexp(lp, 1), torch.full((10,), -np.log(10.0)), atol=1e-3)
+
+
+def test_log_sinkhorn_plan_matches_analytical_result():
+    # test_optimal_transport.py:249-263: identical points -> outer product of the marginals
+    from oracle.optimal_transport import log_sinkhorn_plan
+    plan = torch.exp(log_sinkhorn_plan(torch.ones(16), torch.ones(64), regularization=0.1))
+    np.testing.assert_allclose(plan.numpy(), np.full((16, 64), 1 / (16 * 64)), rtol=1e-4)
+
+
+def test_assignment_of_a_shuffled_copy_is_recovered():
+    # test_optimal_transport.py:98-116
+    from oracle.optimal_transport import optimal_transport
+    y = torch.randn(16, 2)
+    p = torch.randperm(16)
+    _, _, _, a = optimal_transport(y[p], y, regularization=0.01, seed=0, max_steps=10_000, return_assignments=True)
+    assert int((a == p).sum()) >= 14
+
+
+def test_conditional_weight_search_hits_the_ratio():
+    # ot_utils.py:95-164: mean((M + w C) <= diag(M)) ~ condition_ratio
+    from oracle.optimal_transport import squared_euclidean, cosine_distance, search_for_conditional_weight
+    x0, x1, c = torch.randn(64, 2), torch.randn(64, 2), torch.randn(64, 5)
+    M, Cm = squared_euclidean(x0, x1), cosine_distance(c, c)
+    cost, w = search_for_conditional_weight(M, Cm, 0.1)
+    ratio = float((cost <= M.diagonal().unsqueeze(1)).float().mean())
+    assert w > 0 and abs(ratio - 0.1) < 0.02
