@@ -1,19 +1,19 @@
 #!/bin/bash
-# usage: gpurun --timeout 900 -- 'bash tools/gpu_edge_ncu.sh TAG'   (ncu --set full of the edge kernels, F = 32)
-TAG=${1:-r01bc}
+# usage: gpurun --timeout 900 -- 'bash tools/gpu_edge_ncu.sh TAG'   (ncu --set full, one launch of each edge kernel, F = 32)
+TAG=${1:-r01bf}
 O=gpurun_out
 mkdir -p $O
 CMD="python tools/gpu_edge_bench.py 4194304 32"
 $CMD > $O/${TAG}_edge_plain.log 2>&1 || { echo "plain run failed"; tail -5 $O/${TAG}_edge_plain.log; exit 1; }
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:'standardize_kernel|moments_partial_vec_kernel|normal_fill_kernel' -s 12 -c 6 -f -o $O/${TAG}_edge $CMD > $O/${TAG}_edge_ncu.log 2>&1
-echo "ncu exit=$?"
-ncu -i $O/${TAG}_edge.ncu-rep --page raw --csv > $O/${TAG}_edge_ncu_raw.csv 2>/dev/null
-python - <<PY
-import csv
-rows = list(csv.reader(open("$O/${TAG}_edge_ncu_raw.csv")))
-hdr = rows[0]
-want = ["Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__throughput.avg.pct_of_peak_sustained_elapsed", "sm__throughput.avg.pct_of_peak_sustained_elapsed", "launch__registers_per_thread", "sm__warps_active.avg.pct_of_peak_sustained_active"]
-idx = [hdr.index(w) for w in want if w in hdr]
-for r in rows[1:]:
-    print(" | ".join(r[i][:60] for i in idx))
+for K in standardize_kernel moments_partial_vec_kernel normal_fill_kernel; do
+  timeout 300 ncu --set full --clock-control none --import-source on -k regex:$K -s 4 -c 1 -f -o $O/${TAG}_$K $CMD > $O/${TAG}_${K}_ncu.log 2>&1
+  echo "ncu $K exit=$?"
+  ncu -i $O/${TAG}_$K.ncu-rep --page raw --csv > $O/${TAG}_${K}_raw.csv 2>/dev/null
+  echo "== $K"; python tools/ncu_brief.py $O/${TAG}_$K.ncu-rep 2>&1 | grep -E "gpu__time|dram__bytes|issue_active.avg.pct|registers|warps_active|pipe_xu|pipe_alu|pipe_fma\\.|lts__throughput"
+done
+timeout 900 python bench.py > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench exit=$?"; python - <<PY
+import json
+d = json.loads(open("$O/${TAG}_bench.json").read().strip().splitlines()[-1])
+print(json.dumps({k: d.get(k) for k in ("value", "e2e", "sampler_api", "edge_kernels")}, indent=1)[:3000])
 PY
+tail -3 $O/${TAG}_bench.err
