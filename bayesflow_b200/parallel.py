@@ -33,11 +33,18 @@ def sample_sharded(net, num_samples: int, conditions: torch.Tensor, *, group=Non
     prev = getattr(net, "step_control_group", None)
     if world > 1 and global_step_control:
         net.step_control_group = group if group is not None else dist.group.WORLD
+    # the noise stream is a function of (seed, GLOBAL row): every rank passes the same seed and its first global row, so the
+    # sharded draws are exactly the rows a single-GPU call with this seed produces (all ranks take part in the broadcast)
+    if seed is None:
+        seed_t = torch.randint(0, 2 ** 62, (1,), dtype=torch.int64)
+        if world > 1:
+            seed_t = seed_t.to(conditions.device) if dist.get_backend(group) == "nccl" else seed_t
+            dist.broadcast(seed_t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        seed = int(seed_t.item())
     try:
         if n_local > 0:
-            gen_seed = None if seed is None else int(seed) + rank
-            flat = net.sample((n_local * num_samples,), conditions=local, conditions_repeats=num_samples, seed=gen_seed,
-                              **kwargs)
+            flat = net.sample((n_local * num_samples,), conditions=local, conditions_repeats=num_samples, seed=int(seed),
+                              row_offset=lo * num_samples, **kwargs)
             out = flat.reshape(n_local, num_samples, -1)
         else:
             out = conditions.new_zeros((0, num_samples, net._D))

@@ -125,6 +125,7 @@ def measure_edge(dev, peak_gbs):
     """HBM roofline of the HBM-bound edge kernels (bfk_standardize, bfk_batch_moments, bfk_normal_fill) on 1 GiB inputs
     (larger than L2), CUDA events on the launching stream, median of 10 after 3 warm-ups."""
     import ctypes as C
+    import torch
     import bayesflow_b200 as bf
     from bayesflow_b200 import _lib
     F, rows = 32, 8 * 1024 * 1024
