@@ -78,8 +78,8 @@ __device__ __forceinline__ void lse_merge(float& mx, float& sm, float mx2, float
 
 // u_next[i] = log_a - logsumexp_j(S[i,j] + v[j]);  err = max_i |u_next - u|   (log_sinkhorn.py:131-137).  One warp per row.
 __global__ void __launch_bounds__(256) ot_row_lse_kernel(const float* __restrict__ S, long long n, long long m, float log_a,
-                                                         float* __restrict__ u, const float* __restrict__ v,
-                                                         float* __restrict__ ctrl) {
+                                                         const float* __restrict__ log_a_vec, float* __restrict__ u,
+                                                         const float* __restrict__ v, float* __restrict__ ctrl) {
   if (ctrl[OT_DONE] != 0.f) return;
   const int lane = threadIdx.x & 31;
   const long long i = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(256) ot_row_lse_kernel(const float* __restrict
     mx = a, sm = b;
   }
   if (lane == 0) {
-    const float un = log_a - (mx + logf(sm));
+    const float un = (log_a_vec ? log_a_vec[i] : log_a) - (mx + logf(sm));
     const float d = fabsf(un - u[i]);
     u[i] = un;
     atomicMax(reinterpret_cast<unsigned int*>(ctrl + OT_ACC), __float_as_uint(d == d ? d : INFINITY));
@@ -118,13 +118,14 @@ __global__ void __launch_bounds__(256) ot_col_partial_kernel(const float* __rest
 }
 // stage 2: chunks merged in index order; v_next[j] = log_b - logsumexp  (log_sinkhorn.py:133)
 __global__ void __launch_bounds__(256) ot_col_finish_kernel(const float* __restrict__ part, int chunks, long long m, float log_b,
-                                                            float* __restrict__ v, const float* __restrict__ ctrl) {
+                                                            const float* __restrict__ log_b_vec, float* __restrict__ v,
+                                                            const float* __restrict__ ctrl) {
   if (ctrl[OT_DONE] != 0.f) return;
   const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= m) return;
   float mx = -INFINITY, sm = 0.f;
   for (int c = 0; c < chunks; ++c) lse_merge(mx, sm, part[((long long)c * 2) * m + j], part[((long long)c * 2 + 1) * m + j]);
-  v[j] = log_b - (mx + logf(sm));
+  v[j] = (log_b_vec ? log_b_vec[j] : log_b) - (mx + logf(sm));
 }
 // loop bookkeeping of keras.ops.while_loop(cond, body, ..., maximum_iterations)  (log_sinkhorn.py:125-141)
 __global__ void ot_ctrl_kernel(float* __restrict__ ctrl) {
@@ -138,8 +139,9 @@ __global__ void ot_ctrl_kernel(float* __restrict__ ctrl) {
 
 // assignments[i] ~ Categorical(softmax_j(S[i,j] + u[i] + v[j]))  (log_sinkhorn.py:33-35) by the Gumbel-max trick:
 // argmax_j S[i,j] + v[j] - log(-log U_ij), U_ij = word (i*m+j) of the Philox stream keyed by seed; ties -> smallest j.
-__global__ void __launch_bounds__(256) ot_sample_kernel(const float* __restrict__ S, const float* __restrict__ v, long long n,
-                                                        long long m, unsigned long long seed, long long* __restrict__ out) {
+__global__ void __launch_bounds__(256) ot_sample_kernel(const float* __restrict__ S, long long ld, const float* __restrict__ v,
+                                                        long long n, long long m, unsigned long long seed,
+                                                        long long* __restrict__ out) {
   const int lane = threadIdx.x & 31;
   const long long i = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (i >= n) return;
@@ -150,7 +152,7 @@ __global__ void __launch_bounds__(256) ot_sample_kernel(const float* __restrict_
     uint32_t c[4] = {(uint32_t)(e >> 2), (uint32_t)(e >> 34), 0u, 0u};
     philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
     const float g = -logf(-logf(u01(c[e & 3])));
-    const float val = S[i * m + j] + v[j] + g;
+    const float val = S[i * ld + j] + v[j] + g;
     if (val > best) { best = val; arg = j; }
   }
   for (int o = 16; o > 0; o >>= 1) {
@@ -222,27 +224,27 @@ extern "C" int bfk_ot_init(float* ctrl, float* u, float* v, int64_t n, int64_t m
   return 0;
 }
 
-extern "C" int bfk_ot_log_sinkhorn_step(const float* S, int64_t n, int64_t m, float* u, float* v, float* ctrl, float* work,
-                                        void* stream) {
+extern "C" int bfk_ot_log_sinkhorn_step(const float* S, int64_t n, int64_t m, const float* log_a_vec, const float* log_b_vec,
+                                        float* u, float* v, float* ctrl, float* work, void* stream) {
   if (n < 1 || m < 1) return fail(-88, "bfk_ot_log_sinkhorn_step: bad n/m");
   if (!S || !u || !v || !ctrl || !work) return fail(-89, "bfk_ot_log_sinkhorn_step: null pointer");
   cudaStream_t st = (cudaStream_t)stream;
   const float log_a = -logf((float)n), log_b = -logf((float)m);
   const int chunks = bfk::ot_chunks(n);
-  bfk::ot_row_lse_kernel<<<(unsigned)((n + 7) / 8), 256, 0, st>>>(S, n, m, log_a, u, v, ctrl);
+  bfk::ot_row_lse_kernel<<<(unsigned)((n + 7) / 8), 256, 0, st>>>(S, n, m, log_a, log_a_vec, u, v, ctrl);
   dim3 g2((unsigned)((m + 255) / 256), (unsigned)chunks);
   bfk::ot_col_partial_kernel<<<g2, 256, 0, st>>>(S, n, m, u, work, ctrl);
-  bfk::ot_col_finish_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(work, chunks, m, log_b, v, ctrl);
+  bfk::ot_col_finish_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(work, chunks, m, log_b, log_b_vec, v, ctrl);
   bfk::ot_ctrl_kernel<<<1, 1, 0, st>>>(ctrl);
   CK(cudaGetLastError());
   return 0;
 }
 
-extern "C" int bfk_ot_sample(const float* S, const float* v, int64_t n, int64_t m, uint64_t seed, int64_t* assignments,
-                             void* stream) {
-  if (n < 1 || m < 1) return fail(-90, "bfk_ot_sample: bad n/m");
+extern "C" int bfk_ot_sample(const float* S, int64_t ld, const float* v, int64_t n, int64_t m, uint64_t seed,
+                             int64_t* assignments, void* stream) {
+  if (n < 1 || m < 1 || ld < m) return fail(-90, "bfk_ot_sample: bad n/m/ld");
   if (!S || !v || !assignments) return fail(-91, "bfk_ot_sample: null pointer");
-  bfk::ot_sample_kernel<<<(unsigned)((n + 7) / 8), 256, 0, (cudaStream_t)stream>>>(S, v, n, m, (unsigned long long)seed,
+  bfk::ot_sample_kernel<<<(unsigned)((n + 7) / 8), 256, 0, (cudaStream_t)stream>>>(S, ld, v, n, m, (unsigned long long)seed,
                                                                                   (long long*)assignments);
   CK(cudaGetLastError());
   return 0;

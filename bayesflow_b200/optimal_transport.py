@@ -2,8 +2,8 @@
 and log_sinkhorn.py:14-172 behind the same names and arguments, on the `bfk_ot_*` kernels (include/bfk.h).  No CPU path.
 
 Supported: method "log_sinkhorn" / "log_sinkhorn_knopp" (the FlowMatching default, networks/defaults.py:54-63), balanced
-marginals, squared-Euclidean cost, conditional cost weighting (`condition_ratio < 0.5`, ot_utils.py:95-164).  Partial OT
-(`partial_factor < 1`) and the un-stabilised "sinkhorn" method raise NotImplementedError."""
+and partial (`partial_factor < 1`, ot_utils.py:37-92) marginals, squared-Euclidean cost, conditional cost weighting
+(`condition_ratio < 0.5`, ot_utils.py:95-164).  The un-stabilised "sinkhorn" method raises NotImplementedError."""
 from __future__ import annotations
 
 import ctypes as C
@@ -68,8 +68,7 @@ def log_sinkhorn_plan(x1, x2, conditions=None, regularization: float = 1.0, atol
     """log_sinkhorn.py:38-172 -> (n, m) log transport plan."""
     if not (0.0 < partial_factor <= 1.0):
         raise ValueError(f"s must be in (0, 1] for partial OT, got {partial_factor}")
-    if partial_factor < 1.0:
-        raise NotImplementedError("partial optimal transport is outside the accelerated path (SURVEY.md §8f rank 4)")
+    partial = partial_factor < 1.0
     if regularization <= 0.0:
         raise ValueError(f"regularization must be positive, got {regularization}")
     a, b = _flat2(x1, "x1"), _flat2(x2, "x2")
@@ -87,6 +86,19 @@ def log_sinkhorn_plan(x1, x2, conditions=None, regularization: float = 1.0, atol
     _lib.check(L.bfk_ot_scale(_lib.ptr(S), _lib.ptr(Cm) if w != 0.0 else None, float(w), float(regularization), S.numel(),
                               _lib.stream_ptr()), "bfk_ot_scale")
     dev = S.device
+    n0, m0, log_a, log_b = n, m, None, None
+    if partial:
+        # augment_for_partial_ot (ot_utils.py:37-92): a dummy row / column of zeros, corner -A / reg with
+        # A = max(cost) + 1 (or `dummy_cost`), marginals (1/n0, ..., 1 - s) and (1/m0, ..., 1 - s)
+        dummy = kwargs.get("dummy_cost")
+        corner = (S.min() - 1.0 / regularization) if dummy is None else torch.tensor(-float(dummy) / regularization, device=dev)
+        aug = torch.zeros(n0 + 1, m0 + 1, device=dev, dtype=torch.float32)
+        aug[:n0, :m0] = S
+        aug[n0, m0] = corner
+        S, n, m = aug, n0 + 1, m0 + 1
+        one_minus_s = float(torch.tensor(1.0, dtype=torch.float32) - torch.tensor(partial_factor, dtype=torch.float32))
+        log_a = torch.log(torch.cat([torch.full((n0,), 1.0 / n0), torch.tensor([one_minus_s])]).to(torch.float32)).to(dev)
+        log_b = torch.log(torch.cat([torch.full((m0,), 1.0 / m0), torch.tensor([one_minus_s])]).to(torch.float32)).to(dev)
     ctrl = torch.empty(8, device=dev, dtype=torch.float32)
     u, v = torch.empty(n, device=dev, dtype=torch.float32), torch.empty(m, device=dev, dtype=torch.float32)
     work = torch.empty(max(1, L.bfk_ot_work_floats(n, m)), device=dev, dtype=torch.float32)
@@ -96,27 +108,28 @@ def log_sinkhorn_plan(x1, x2, conditions=None, regularization: float = 1.0, atol
     enq = 0
     while not done:
         for _ in range(min(POLL_EVERY, max_steps - enq)):
-            _lib.check(L.bfk_ot_log_sinkhorn_step(_lib.ptr(S), n, m, _lib.ptr(u), _lib.ptr(v), _lib.ptr(ctrl), _lib.ptr(work),
-                                                  _lib.stream_ptr()), "bfk_ot_log_sinkhorn_step")
+            _lib.check(L.bfk_ot_log_sinkhorn_step(_lib.ptr(S), n, m, _lib.ptr(log_a), _lib.ptr(log_b), _lib.ptr(u), _lib.ptr(v),
+                                                  _lib.ptr(ctrl), _lib.ptr(work), _lib.stream_ptr()),
+                       "bfk_ot_log_sinkhorn_step")
             enq += 1
         state = ctrl.tolist()
         done = state[2] != 0.0 or enq >= max_steps
     log_sinkhorn_plan.last_info = {"steps": int(ctrl[1].item()), "err": float(ctrl[0].item()), "w": w}
     if _parts:
-        return S, u, v
-    return S + u.unsqueeze(1) + v.unsqueeze(0)
+        return S, u, v, n0, m0
+    return (S + u.unsqueeze(1) + v.unsqueeze(0))[:n0, :m0]
 
 
 def log_sinkhorn(x1, x2, conditions=None, seed=None, **kwargs):
     """log_sinkhorn.py:14-35 -> (n,) int64 indices into x2."""
-    S, u, v = log_sinkhorn_plan(x1, x2, conditions=conditions, _parts=True, **kwargs)
+    S, u, v, n, m = log_sinkhorn_plan(x1, x2, conditions=conditions, _parts=True, **kwargs)
     if isinstance(seed, torch.Generator):
         seed = int(torch.randint(0, 2 ** 62, (1,), generator=seed, device=seed.device).item())
     elif seed is None:
         seed = int(torch.randint(0, 2 ** 62, (1,)).item())
-    n, m = S.shape
     out = torch.empty(n, device=S.device, dtype=torch.int64)
-    _lib.check(_lib.lib().bfk_ot_sample(_lib.ptr(S), _lib.ptr(v), n, m, C.c_uint64(int(seed) & (2 ** 64 - 1)),
+    # partial OT: rows / columns of the real samples only (log_sinkhorn.py:169-170)
+    _lib.check(_lib.lib().bfk_ot_sample(_lib.ptr(S), S.shape[1], _lib.ptr(v), n, m, C.c_uint64(int(seed) & (2 ** 64 - 1)),
                                         C.c_void_p(out.data_ptr()), _lib.stream_ptr()), "bfk_ot_sample")
     return out
 

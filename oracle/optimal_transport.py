@@ -57,19 +57,41 @@ def search_for_conditional_weight(M, Cm, condition_ratio, initial_w=1.0, max_ite
     return M + best_w * Cm, best_w
 
 
+def augment_for_partial_ot(cost_scaled, regularization, s, dummy_cost=None):
+    # ot_utils.py:37-92
+    if dummy_cost is None:
+        dummy_cost = float((-cost_scaled * regularization).max()) + 1
+    n0, m0 = cost_scaled.shape
+    aug = torch.zeros(n0 + 1, m0 + 1, dtype=cost_scaled.dtype)
+    aug[:n0, :m0] = cost_scaled
+    aug[n0, m0] = -dummy_cost / regularization
+    one_minus_s = 1.0 - torch.tensor(s, dtype=cost_scaled.dtype)
+    a = torch.cat([torch.full((n0,), 1.0 / n0, dtype=cost_scaled.dtype), one_minus_s.reshape(1)])
+    b = torch.cat([torch.full((m0,), 1.0 / m0, dtype=cost_scaled.dtype), one_minus_s.reshape(1)])
+    return aug, a, b
+
+
 def log_sinkhorn_plan(x1, x2, conditions=None, regularization=1.0, atol=1e-5, max_steps=1000, condition_ratio=0.5,
-                      info=None, **kwargs):
-    # log_sinkhorn.py:38-172 (balanced marginals)
+                      partial_factor=1.0, info=None, **kwargs):
+    # log_sinkhorn.py:38-172
+    if not (0.0 < partial_factor <= 1.0):
+        raise ValueError(f"s must be in (0, 1] for partial OT, got {partial_factor}")
+    partial = partial_factor < 1.0
+    cost = squared_euclidean(x1, x2)
     if regularization <= 0.0:
         raise ValueError(f"regularization must be positive, got {regularization}")
-    cost = squared_euclidean(x1, x2)
     w = 0.0
     if conditions is not None and condition_ratio < 0.5:
         cost, w = search_for_conditional_weight(cost, cosine_distance(conditions, conditions), condition_ratio)
     S = -cost / regularization
-    n, m = S.shape
-    log_a = torch.full((n,), -float(np.log(n)), dtype=S.dtype)
-    log_b = torch.full((m,), -float(np.log(m)), dtype=S.dtype)
+    if partial:
+        S, a, b = augment_for_partial_ot(S, regularization, partial_factor, kwargs.get("dummy_cost"))
+        log_a, log_b = torch.log(a), torch.log(b)
+        n, m = S.shape
+    else:
+        n, m = S.shape
+        log_a = torch.full((n,), -float(np.log(n)), dtype=S.dtype)
+        log_b = torch.full((m,), -float(np.log(m)), dtype=S.dtype)
     u, v = torch.zeros(n, dtype=S.dtype), torch.zeros(m, dtype=S.dtype)
     err, steps = 1e30, 0
     while err > atol and steps < max_steps:
@@ -79,7 +101,8 @@ def log_sinkhorn_plan(x1, x2, conditions=None, regularization=1.0, atol=1e-5, ma
         u, steps = u_next, steps + 1
     if info is not None:
         info.update(steps=steps, err=err, w=w)
-    return S + u.unsqueeze(1) + v.unsqueeze(0)
+    log_plan = S + u.unsqueeze(1) + v.unsqueeze(0)
+    return log_plan[:-1, :-1] if partial else log_plan
 
 
 def gumbel_argmax(log_plan, seed):
@@ -93,7 +116,6 @@ def gumbel_argmax(log_plan, seed):
 def optimal_transport(x1, x2, conditions=None, seed=0, return_assignments=False, **kwargs):
     # optimal_transport.py:12-72 with method = "log_sinkhorn"
     kwargs.pop("method", None)
-    kwargs.pop("partial_factor", None)
     a = gumbel_argmax(log_sinkhorn_plan(x1, x2, conditions, **kwargs), seed)
     out = (x1, x2[a], conditions[a] if conditions is not None else None)
     return out + (a,) if return_assignments else out

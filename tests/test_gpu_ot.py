@@ -46,7 +46,9 @@ def test_reference_closed_form_tests_on_the_kernels():
     with pytest.raises(ValueError):
         bf.log_sinkhorn_plan(x.cuda(), z.cuda(), regularization=0.0)
     with pytest.raises(NotImplementedError):
-        bf.optimal_transport(x.cuda(), z.cuda(), method="log_sinkhorn", partial_factor=0.5)
+        bf.optimal_transport(x.cuda(), z.cuda(), method="sinkhorn")
+    with pytest.raises(ValueError):
+        bf.log_sinkhorn_plan(x.cuda(), z.cuda(), partial_factor=1.5)
     with pytest.raises(RuntimeError):
         bf.log_sinkhorn_plan(x, z)  # no CPU fallback
 
@@ -85,3 +87,22 @@ def test_flow_matching_trains_with_optimal_transport():
     assert torch.isfinite(out["loss"]) and all(p.grad is not None and torch.isfinite(p.grad).all() for p in net.parameters())
     plain = bf.FlowMatching(subnet_kwargs={"widths": (128, 128), "dropout": 0.0})
     assert plain.optimal_transport_kwargs["method"] == "log_sinkhorn" and not plain.use_optimal_transport
+
+
+@pytest.mark.parametrize("s", [0.3, 0.8])
+def test_partial_ot_matches_oracle_and_leaves_unmatched_mass(s):
+    """log_sinkhorn.py:110-122, 169-170 + ot_utils.py:37-92; reference test test_optimal_transport.py:289-327."""
+    import bayesflow_b200 as bf
+    g = torch.Generator().manual_seed(42)
+    x, y = torch.randn(20, 2, generator=g), torch.randn(20, 2, generator=g)
+    ref = torch.exp(oot.log_sinkhorn_plan(x.double(), y.double(), regularization=0.1, max_steps=10_000, partial_factor=s))
+    plan = torch.exp(bf.log_sinkhorn_plan(x.cuda(), y.cuda(), regularization=0.1, max_steps=10_000, partial_factor=s)).cpu()
+    assert plan.shape == (20, 20)
+    np.testing.assert_allclose(plan.numpy(), ref.numpy(), rtol=5e-3, atol=1e-7)
+    assert bool(((plan.sum(1) - s / 20).abs() < 0.05).all()) and bool(((plan.sum(0) - s / 20).abs() < 0.05).all())
+    assert abs(float(plan.sum()) - s) < 1e-3
+    # assignments stay inside the real columns
+    _, _, _, a = bf.optimal_transport(x.cuda(), y.cuda(), method="log_sinkhorn", regularization=0.1, partial_factor=s, seed=2,
+                                      return_assignments=True)
+    a_ref = oot.gumbel_argmax(oot.log_sinkhorn_plan(x, y, regularization=0.1, partial_factor=s), seed=2)
+    assert int(a.min()) >= 0 and int(a.max()) < 20 and float((a.cpu() == a_ref).float().mean()) >= 0.9

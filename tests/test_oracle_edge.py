@@ -169,3 +169,14 @@ def test_conditional_weight_search_hits_the_ratio():
     cost, w = search_for_conditional_weight(M, Cm, 0.1)
     ratio = float((cost <= M.diagonal().unsqueeze(1)).float().mean())
     assert w > 0 and abs(ratio - 0.1) < 0.02
+
+
+@pytest.mark.parametrize("s", [0.3, 0.8])
+def test_partial_ot_leaves_unmatched_mass(s):
+    # test_optimal_transport.py:289-327
+    from oracle.optimal_transport import log_sinkhorn_plan
+    x, y = torch.randn(20, 2), torch.randn(20, 2)
+    plan = torch.exp(log_sinkhorn_plan(x, y, regularization=0.1, max_steps=10_000, partial_factor=s))
+    assert plan.shape == (20, 20)
+    assert bool(((plan.sum(1) - s / 20).abs() < 0.05).all()) and bool(((plan.sum(0) - s / 20).abs() < 0.05).all())
+    assert abs(float(plan.sum()) - s) < 1e-3
