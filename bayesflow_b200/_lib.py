@@ -107,7 +107,7 @@ def lib():
     L.bfk_ot_work_floats.argtypes = [C.c_int64, C.c_int64]
     L.bfk_ot_init.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_float, C.c_int64, C.c_void_p]
     L.bfk_ot_log_sinkhorn_step.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
-                                           C.c_void_p, C.c_void_p, C.c_void_p]
+                                           C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
     L.bfk_ot_sample.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_uint64, C.c_void_p, C.c_void_p]
     _lib = L
     return L

@@ -14,7 +14,7 @@ from . import _lib
 
 OPTIMAL_TRANSPORT_DEFAULTS = {"method": "log_sinkhorn", "regularization": 0.1, "max_steps": 100, "atol": 1e-5,
                               "partial_factor": 1.0, "condition_ratio": 0.01}  # networks/defaults.py:54-63
-POLL_EVERY = 8  # Sinkhorn steps enqueued between two reads of the device-side loop state
+POLL_EVERY = 16  # Sinkhorn steps enqueued between two reads of the device-side loop state
 
 
 def _flat2(x, what):
@@ -107,11 +107,10 @@ def log_sinkhorn_plan(x1, x2, conditions=None, regularization: float = 1.0, atol
     done = max_steps <= 0
     enq = 0
     while not done:
-        for _ in range(min(POLL_EVERY, max_steps - enq)):
-            _lib.check(L.bfk_ot_log_sinkhorn_step(_lib.ptr(S), n, m, _lib.ptr(log_a), _lib.ptr(log_b), _lib.ptr(u), _lib.ptr(v),
-                                                  _lib.ptr(ctrl), _lib.ptr(work), _lib.stream_ptr()),
-                       "bfk_ot_log_sinkhorn_step")
-            enq += 1
+        k = min(POLL_EVERY, max_steps - enq)
+        _lib.check(L.bfk_ot_log_sinkhorn_step(_lib.ptr(S), n, m, _lib.ptr(log_a), _lib.ptr(log_b), _lib.ptr(u), _lib.ptr(v),
+                                              _lib.ptr(ctrl), _lib.ptr(work), k, _lib.stream_ptr()), "bfk_ot_log_sinkhorn_step")
+        enq += k
         state = ctrl.tolist()
         done = state[2] != 0.0 or enq >= max_steps
     log_sinkhorn_plan.last_info = {"steps": int(ctrl[1].item()), "err": float(ctrl[0].item()), "w": w}

@@ -267,7 +267,7 @@ int bfk_moments_merge(float* mean, float* m2, float* count, const float* parts, 
  *   bfk_ot_ratio     *count = #{(i,j): w * C_ij <= M_ii - M_ij} over (n,n)  (get_ratio numerator, ot_utils.py:117-121)
  *   bfk_ot_scale     M <- -(M + w * C) / regularization in place (C may be NULL)
  *   bfk_ot_init      ctrl (8 floats: err, steps, done, atol, max_steps, ...), u = 0 (n), v = 0 (m)
- *   bfk_ot_log_sinkhorn_step  one body of the while loop (log_sinkhorn.py:131-137); log marginals log_a_vec (n) /
+ *   bfk_ot_log_sinkhorn_step  n_steps bodies of the while loop (log_sinkhorn.py:131-137); log marginals log_a_vec (n) /
  *                    log_b_vec (m), or NULL for the uniform -log n / -log m (partial OT passes the augmented ones,
  *                    ot_utils.py:37-92, with S the (n0+1, m0+1) augmented matrix); a no-op once
  *                    ctrl[2] (done) is set, so the host may enqueue several steps between polls of ctrl
@@ -280,7 +280,7 @@ int bfk_ot_scale(float* M, const float* Cm, float w, float regularization, int64
 size_t bfk_ot_work_floats(int64_t n, int64_t m);
 int bfk_ot_init(float* ctrl, float* u, float* v, int64_t n, int64_t m, float atol, int64_t max_steps, void* stream);
 int bfk_ot_log_sinkhorn_step(const float* S, int64_t n, int64_t m, const float* log_a_vec, const float* log_b_vec,
-                             float* u, float* v, float* ctrl, float* work, void* stream);
+                             float* u, float* v, float* ctrl, float* work, int32_t n_steps, void* stream);
 int bfk_ot_sample(const float* S, int64_t ld, const float* v, int64_t n, int64_t m, uint64_t seed, int64_t* assignments,
                   void* stream);
 
