@@ -21,7 +21,8 @@ __device__ __forceinline__ float act_fn(float x) {
   } else if (ACT == BFK_ACT_RELU) {
     return fmaxf(x, 0.f);
   } else if (ACT == BFK_ACT_GELU) {
-    return 0.5f * x * (1.f + erff(x * 0.7071067811865476f));
+    // keras.activations.gelu defaults to approximate=True: 0.5 x (1 + tanh(sqrt(2/pi) (x + 0.044715 x^3)))
+    return 0.5f * x * (1.f + tanhf(0.7978845608028654f * (x + 0.044715f * x * x * x)));
   } else {
     return tanhf(x);
   }

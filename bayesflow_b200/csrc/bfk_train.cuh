@@ -41,8 +41,11 @@ __device__ __forceinline__ float t_act(int act, float x, float& d) {
       d = x > 0.f ? 1.f : 0.f;
       return x > 0.f ? x : 0.f;
     case BFK_ACT_GELU: {
-      const float cdf = 0.5f * (1.f + erff(x * 0.70710678118654752f));
-      d = cdf + x * 0.3989422804014327f * __expf(-0.5f * x * x);
+      // keras.activations.gelu defaults to approximate=True (tanh form)
+      const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
+      const float t = tanhf(u);
+      const float cdf = 0.5f * (1.f + t);
+      d = cdf + 0.5f * x * (1.f - t * t) * 0.7978845608028654f * (1.f + 3.f * 0.044715f * x * x);
       return x * cdf;
     }
     default: {  // tanh

@@ -14,7 +14,7 @@ Plain-PyTorch FP32 restatement of the reference's Keras/torch path, statement by
 Keras (>=3.12, unpinned, not installed here) semantics ASSUMED — "parity unpinned" at this boundary:
   Dense: y = x @ kernel(in,out) + bias;  he_normal = truncated normal(±2σ), σ = sqrt(2/fan_in)/0.87962566103423978;
   LayerNormalization: last axis, epsilon=1e-3, biased variance, gamma*(x-mean)*rsqrt(var+eps)+beta;
-  mish(x) = x*tanh(softplus(x));  silu/gelu(exact, erf)/relu/tanh/elu as in keras.activations;
+  mish(x) = x*tanh(softplus(x));  silu/gelu(approximate=True, the keras 3 default)/relu/tanh/elu as in keras.activations;
   Dropout = inverted dropout, identity at inference;  "mse" = mean((y_pred-y_true)^2, axis=-1);
   random_normal initializer = N(0, 0.05^2).
 """
@@ -41,7 +41,7 @@ def activation_fn(name: str):
     if name in ("silu", "swish"):
         return F.silu
     if name == "gelu":
-        return lambda x: F.gelu(x, approximate="none")
+        return lambda x: F.gelu(x, approximate="tanh")  # keras.activations.gelu(x, approximate=True) is the keras 3 default
     if name == "relu":
         return F.relu
     if name == "tanh":
