@@ -6,6 +6,8 @@
 
 #include "bfk_sampler.cuh"
 #include "bfk_sampler_fast.cuh"
+#include "bfk_sampler_chase.cuh"
+#include "bfk_sampler_fold.cuh"
 #include "bfk_adaptive.cuh"
 #include "bfk_gemm.cuh"
 
@@ -45,14 +47,34 @@ static int check_cfg(const bfk_net_config* c) {
   return 0;
 }
 
+typedef void (*sampler_fn)(const SamplerArgs);
+static sampler_fn pick_kernel(const bfk_net_config* c, int* threads);
+
+// Which fused kernel serves the reference's default block shape: the chase schedule (bfk_sampler_chase.cuh, default) or
+// the two-tile ping-pong kernel it replaced (BFK_SAMPLER=fast, kept for A/B timing).  Read once per process: the packed
+// blob and the per-evaluation table are laid out for the kernel that will read them.
+// BFK_SAMPLER: "fold" (default: two-tile ping-pong, folded single-pass epilogue), "chase" (one tile, UMMAs chase the
+// epilogue slab by slab), "fast" (the round-1 two-pass kernel).  fold and chase share the folded weight / table layout.
+static int sampler_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("BFK_SAMPLER");
+    v = (e && strcmp(e, "fast") == 0) ? 0 : (e && strcmp(e, "chase") == 0) ? 1 : 2;
+  }
+  return v;
+}
+static bool use_chase(const bfk_net_config* c) { return is_fast(*c) && sampler_variant() != 0; }  // folded layout
+static bool one_tile(const bfk_net_config* c) { return is_fast(*c) && sampler_variant() == 1; }
+
 extern "C" int bfk_fused_supported(const bfk_net_config* c) {
   if (check_cfg(c)) return 0;
   if (c->D > BFK_MAX_D) return 0;
   if (c->W > 256 || (c->W % 32) != 0) return 0;
   if (c->precision != BFK_PREC_FP16 && c->precision != BFK_PREC_BF16) return 0;
-  SmemPlan p = make_smem_plan(*c);
+  SmemPlan p = one_tile(c) ? make_chase_plan(*c) : use_chase(c) ? make_fold_plan(*c) : make_smem_plan(*c);
   if (p.n_stage < 2) return 0;
-  return 1;
+  int threads = 0;
+  return pick_kernel(c, &threads) != nullptr;  // configurations without an instantiation take the layer-wise path
 }
 
 extern "C" size_t bfk_packed_bytes(const bfk_net_config* c) {
@@ -79,19 +101,34 @@ extern "C" int bfk_pack(const bfk_net_config* c, const bfk_weights* w, void* pac
   int g = 0;
   if (L.has_merge) {
     if (!w->m_k || !w->m_b || !w->c_k || !w->c_b) return fail(-12, "conditional net needs c_proj and merge_proj");
-    pack_gemm_kernel<<<cdiv((size_t)W / 8 * W, 256), 256, 0, st>>>(w->m_k, W, W, bf, (uint16_t*)(P + L.gemm));  // x half / whole (add)
+    // x half / whole (add); the chase kernel carries pre-activations times log2(e)
+    pack_gemm_kernel<<<cdiv((size_t)W / 8 * W, 256), 256, 0, st>>>(w->m_k, W, W, bf, (uint16_t*)(P + L.gemm),
+                                                                  use_chase(c) ? 1.4426950408889634f : 1.f);
     ++g;
   }
+  const bool chase = use_chase(c);
+  float* cv = (float*)(P + L.cvec);
   for (int l = 0; l < c->L; ++l, ++g) {
     if (!w->dense_k[l] || !w->dense_b[l] || !w->film_b_k[l] || !w->film_b_b[l]) return fail(-13, "missing block weights");
-    pack_gemm_kernel<<<cdiv((size_t)W / 8 * W, 256), 256, 0, st>>>(w->dense_k[l], W, W, bf,
-                                                                  (uint16_t*)(P + L.gemm + (size_t)g * W * W * 2));
+    if (chase) {
+      // LayerNorm of block l-1 folded into the Dense kernel of block l (see chase_fold_kernel)
+      if (!w->norm_g[l] || !w->norm_b[l]) return fail(-15, "LayerNorm weights missing");
+      chase_fold_kernel<<<cdiv(W, 128), 128, 0, st>>>(w->dense_k[l], w->dense_b[l], l ? w->norm_g[l - 1] : nullptr,
+                                                     l ? w->norm_b[l - 1] : nullptr, W, W, bf,
+                                                     (uint16_t*)(P + L.gemm + (size_t)g * W * W * 2),
+                                                     cv + L.cv_blk + (3 * l + 0) * W, cv + L.cv_blk + (3 * l + 1) * W,
+                                                     cv + L.cv_blk + (3 * l + 2) * W);
+      copy_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(w->norm_b[l], (float*)(P + L.ln_beta) + (size_t)l * W, W);
+    } else {
+      pack_gemm_kernel<<<cdiv((size_t)W / 8 * W, 256), 256, 0, st>>>(w->dense_k[l], W, W, bf,
+                                                                    (uint16_t*)(P + L.gemm + (size_t)g * W * W * 2));
+    }
   }
   // constant vectors (SMEM image)
-  float* cv = (float*)(P + L.cvec);
   pad2d_kernel<<<cdiv((size_t)L.DP * W, 256), 256, 0, st>>>(w->x_k, c->D, W, cv + L.cv_wx, L.DP, W);
   copy_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(w->x_b, cv + L.cv_bx, W);
-  for (int l = 0; l < c->L; ++l) {
+  if (chase) scale_f32_kernel<<<cdiv((size_t)(L.DP + 1) * W, 256), 256, 0, st>>>(cv + L.cv_wx, 1.4426950408889634f, (size_t)(L.DP + 1) * W);
+  for (int l = 0; l < c->L && !chase; ++l) {
     copy_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(w->dense_b[l], cv + L.cv_blk + (3 * l + 0) * W, W);
     if (c->norm != BFK_NORM_NONE && w->norm_g[l])
       copy_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(w->norm_g[l], cv + L.cv_blk + (3 * l + 1) * W, W);
@@ -140,7 +177,8 @@ extern "C" int bfk_cond_prologue(const bfk_net_config* c, const void* packed, co
   const PackedLayout L = make_layout(*c);
   const unsigned grid = (unsigned)(G < 148 * 16 ? G : 148 * 16);
   const size_t sh = (size_t)(c->C + c->W) * 4;
-  cond_prologue_kernel<<<grid, 256, sh, (cudaStream_t)stream_>>>(*c, (const unsigned char*)packed, L, cond, G, pre_add, post_add);
+  cond_prologue_kernel<<<grid, 256, sh, (cudaStream_t)stream_>>>(*c, (const unsigned char*)packed, L, cond, G, pre_add, post_add,
+                                                                use_chase(c) ? 1.4426950408889634f : 1.f);
   CK(cudaGetLastError());
   return 0;
 }
@@ -152,7 +190,7 @@ extern "C" int bfk_eval_table(const bfk_net_config* c, const void* packed, const
   const PackedLayout L = make_layout(*c);
   const unsigned grid = (unsigned)(n < 148 * 8 ? n : 148 * 8);
   eval_table_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>(*c, (const unsigned char*)packed, L, *sched, times, n,
-                                                           table_stride(*c), table);
+                                                           table_stride(*c), table, use_chase(c) ? 1 : 0);
   CK(cudaGetLastError());
   return 0;
 }
@@ -213,21 +251,55 @@ static StageC stage_c(int method) {
   return sc;
 }
 
-typedef void (*sampler_fn)(const SamplerArgs);
 static sampler_fn pick_kernel(const bfk_net_config* c, int* threads) {
   const int dp = dp_of(c->D);
   const bool bf = c->precision == BFK_PREC_BF16;
+  if (use_chase(c) && !one_tile(c)) {
+    *threads = F_NUM_THREADS;
+#define PICKD(ACT_, DP_, BF_) \
+  if (c->activation == ACT_ && dp == DP_ && bf == BF_) return sampler_fold_kernel<ACT_, DP_, BF_>;
+    PICKD(BFK_ACT_MISH, 2, false)
+#ifndef BFK_DEV_BUILD
+    PICKD(BFK_ACT_MISH, 4, false) PICKD(BFK_ACT_MISH, 8, false)
+    PICKD(BFK_ACT_MISH, 2, true) PICKD(BFK_ACT_MISH, 4, true) PICKD(BFK_ACT_MISH, 8, true)
+    PICKD(BFK_ACT_SILU, 2, false) PICKD(BFK_ACT_SILU, 4, false) PICKD(BFK_ACT_SILU, 8, false)
+    PICKD(BFK_ACT_RELU, 2, false) PICKD(BFK_ACT_RELU, 4, false) PICKD(BFK_ACT_RELU, 8, false)
+    PICKD(BFK_ACT_GELU, 2, false) PICKD(BFK_ACT_GELU, 4, false) PICKD(BFK_ACT_GELU, 8, false)
+    PICKD(BFK_ACT_TANH, 2, false) PICKD(BFK_ACT_TANH, 4, false) PICKD(BFK_ACT_TANH, 8, false)
+#endif
+#undef PICKD
+    return nullptr;
+  }
+  if (one_tile(c)) {
+    *threads = C_NUM_THREADS;
+#define PICKC(ACT_, DP_, BF_) \
+  if (c->activation == ACT_ && dp == DP_ && bf == BF_) return sampler_chase_kernel<ACT_, DP_, BF_>;
+    PICKC(BFK_ACT_MISH, 2, false)
+#ifndef BFK_DEV_BUILD
+    PICKC(BFK_ACT_MISH, 4, false) PICKC(BFK_ACT_MISH, 8, false)
+    PICKC(BFK_ACT_MISH, 2, true) PICKC(BFK_ACT_MISH, 4, true) PICKC(BFK_ACT_MISH, 8, true)
+    PICKC(BFK_ACT_SILU, 2, false) PICKC(BFK_ACT_SILU, 4, false) PICKC(BFK_ACT_SILU, 8, false)
+    PICKC(BFK_ACT_RELU, 2, false) PICKC(BFK_ACT_RELU, 4, false) PICKC(BFK_ACT_RELU, 8, false)
+    PICKC(BFK_ACT_GELU, 2, false) PICKC(BFK_ACT_GELU, 4, false) PICKC(BFK_ACT_GELU, 8, false)
+    PICKC(BFK_ACT_TANH, 2, false) PICKC(BFK_ACT_TANH, 4, false) PICKC(BFK_ACT_TANH, 8, false)
+#endif
+#undef PICKC
+    return nullptr;
+  }
   if (is_fast(*c)) {
     // the reference's default block shape: 18-warp packed-f32x2 kernel
     *threads = F_NUM_THREADS;
 #define PICKF(ACT_, DP_, BF_) \
   if (c->activation == ACT_ && dp == DP_ && bf == BF_) return sampler_fast_kernel<ACT_, DP_, BF_>;
-    PICKF(BFK_ACT_MISH, 2, false) PICKF(BFK_ACT_MISH, 4, false) PICKF(BFK_ACT_MISH, 8, false)
+    PICKF(BFK_ACT_MISH, 2, false)
+#ifndef BFK_DEV_BUILD
+    PICKF(BFK_ACT_MISH, 4, false) PICKF(BFK_ACT_MISH, 8, false)
     PICKF(BFK_ACT_MISH, 2, true) PICKF(BFK_ACT_MISH, 4, true)
     PICKF(BFK_ACT_SILU, 2, false) PICKF(BFK_ACT_SILU, 4, false) PICKF(BFK_ACT_SILU, 8, false)
     PICKF(BFK_ACT_RELU, 2, false) PICKF(BFK_ACT_RELU, 4, false)
     PICKF(BFK_ACT_GELU, 2, false) PICKF(BFK_ACT_GELU, 4, false)
     PICKF(BFK_ACT_TANH, 2, false) PICKF(BFK_ACT_TANH, 4, false)
+#endif
 #undef PICKF
     return nullptr;
   }
@@ -235,8 +307,11 @@ static sampler_fn pick_kernel(const bfk_net_config* c, int* threads) {
   *threads = NUM_THREADS;
 #define PICK(ACT_, DP_, BF_) \
   if (c->activation == ACT_ && dp == DP_ && bf == BF_) return sampler_kernel<ACT_, DP_, BF_>;
-  PICK(BFK_ACT_MISH, 2, false) PICK(BFK_ACT_MISH, 4, false) PICK(BFK_ACT_MISH, 8, false)
+  PICK(BFK_ACT_MISH, 2, false)
+#ifndef BFK_DEV_BUILD
+  PICK(BFK_ACT_MISH, 4, false) PICK(BFK_ACT_MISH, 8, false)
   PICK(BFK_ACT_SILU, 2, false) PICK(BFK_ACT_SILU, 4, false)
+#endif
 #undef PICK
   return nullptr;
 }
@@ -277,7 +352,8 @@ static int launch_sampler(const bfk_net_config* c, const void* packed, const flo
   a.tstride = table_stride(*c); a.cvec_floats = L.cvec_floats;
   a.cv_wx = L.cv_wx; a.cv_bx = L.cv_bx; a.cv_blk = L.cv_blk; a.cv_wo = L.cv_wo; a.cv_bo = L.cv_bo;
   a.idesc = umma_idesc_f16(TILE_M, c->W, c->precision == BFK_PREC_BF16 ? 1 : 0);
-  a.plan = make_smem_plan(*c);
+  const bool chase = one_tile(c);
+  a.plan = chase ? make_chase_plan(*c) : use_chase(c) ? make_fold_plan(*c) : make_smem_plan(*c);
   a.err_flag = nullptr;
   { const char* e = getenv("BFK_DEBUG"); a.dbg = e ? atoi(e) : 0; }
   fill_tableau(method, a);
@@ -288,7 +364,8 @@ static int launch_sampler(const bfk_net_config* c, const void* packed, const flo
   CK(cudaGetDevice(&dev));
   CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   CK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a.plan.total));
-  const long long n_pairs = (B + TILES_PER_CTA * TILE_M - 1) / (TILES_PER_CTA * TILE_M);
+  const long long rows_per_cta = chase ? TILE_M : TILES_PER_CTA * TILE_M;  // chase: one tile per CTA
+  const long long n_pairs = (B + rows_per_cta - 1) / rows_per_cta;
   const unsigned grid = (unsigned)(n_pairs < sms ? n_pairs : sms);
   fn<<<grid, threads, a.plan.total, st>>>(a);
   CK(cudaGetLastError());
@@ -311,6 +388,15 @@ extern "C" int bfk_sample_fixed(const bfk_net_config* c, const void* packed, con
   return launch_sampler(c, packed, table, step_h, method, n_steps, pre_add, post_add, rpg, tmask, x_in, x_out, B, 0,
                         (cudaStream_t)stream_);
 }
+
+#ifdef BFK_PROFILE
+// timing builds only (-DBFK_PROFILE): per-CTA, per-warp cycle counters of the last chase-kernel launch -> host
+extern "C" int bfk_debug_read_prof(long long* host_out) {
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpyFromSymbol(host_out, g_bfk_prof, sizeof(long long) * 148 * 18 * 8));
+  return 0;
+}
+#endif
 
 // ---------------------------------------------------------------------------------------------------- adaptive
 extern "C" int bfk_adaptive_init(float* ctrl, double start_time, double stop_time, int64_t min_steps, int64_t max_steps,

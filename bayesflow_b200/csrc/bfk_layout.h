@@ -37,6 +37,7 @@ struct PackedLayout {
   size_t film_g_k, film_g_b;  // same, only if film_use_gamma
   size_t c_k, c_b;            // [C][W], [W]
   size_t m_c, m_b;            // conditions half of merge_proj [W][W] (concat only), [W]
+  size_t ln_beta;             // [L][W] LayerNorm beta of every block (chase layout: folded into the per-evaluation table)
   size_t total;
 };
 
@@ -65,6 +66,7 @@ __host__ __device__ inline PackedLayout make_layout(const bfk_net_config& c) {
   L.c_b = off; off += W * 4;
   L.m_c = off; off += W * W * 4;
   L.m_b = off; off += W * 4;
+  L.ln_beta = off; off += (size_t)c.L * W * 4;
   L.total = align_up(off, 256);
   return L;
 }
@@ -94,6 +96,55 @@ __host__ __device__ inline SmemPlan make_smem_plan(const bfk_net_config& c) {
   p.xch = off;
   p.xch_stride = (uint32_t)((2 + L.DP + 3) / 4 * 4);  // row sum, sum of squares, DP projector partials
   if (is_fast(c)) off += 2 * 2 * TILE_M * p.xch_stride * 4;
+  p.ring = (uint32_t)align_up(off, 128);
+  int n = (int)((SMEM_LIMIT - p.ring) / p.stage_bytes);
+  if (n > 8) n = 8;
+  p.n_stage = n;
+  p.total = p.ring + (n > 0 ? n : 0) * p.stage_bytes;
+  return p;
+}
+
+// "chase" schedule (bfk_sampler_chase.cuh): ONE tile per CTA, double-buffered accumulator, slab barriers; the ring takes
+// what is left (up to 8 stages: more than one whole layer at W = 256).
+__host__ __device__ inline SmemPlan make_chase_plan(const bfk_net_config& c) {
+  SmemPlan p{};
+  PackedLayout L = make_layout(c);
+  p.a_bytes = TILE_M * c.W * 2;
+  p.stage_bytes = KC * c.W * 2;
+  p.film_bytes = (uint32_t)align_up((size_t)table_stride(c) * 4, 16);
+  uint32_t off = 0;
+  p.a_tile = off; off += p.a_bytes;
+  p.film = off; off += 2 * p.film_bytes;
+  p.cvec = off; off += (uint32_t)align_up((size_t)L.cvec_floats * 4, 16);
+  p.bars = off; off += 256;
+  p.xch = off;
+  p.xch_stride = 2;
+  off += 2 * 4 * TILE_M * 8;       // [2][4 column groups][TILE_M] (row sum, sum of squares)
+  off += 4 * TILE_M * L.DP * 4;    // [4][TILE_M][DP] output-projector partials
+  p.ring = (uint32_t)align_up(off, 128);
+  int n = (int)((SMEM_LIMIT - p.ring) / p.stage_bytes);
+  if (n > 8) n = 8;
+  p.n_stage = n;
+  p.total = p.ring + (n > 0 ? n : 0) * p.stage_bytes;
+  return p;
+}
+
+// two-tile ping-pong schedule with the folded single-pass epilogue (bfk_sampler_fold.cuh)
+__host__ __device__ inline SmemPlan make_fold_plan(const bfk_net_config& c) {
+  SmemPlan p{};
+  PackedLayout L = make_layout(c);
+  p.a_bytes = TILE_M * c.W * 2;
+  p.stage_bytes = KC * c.W * 2;
+  p.film_bytes = (uint32_t)align_up((size_t)table_stride(c) * 4, 16);
+  uint32_t off = 0;
+  p.a_tile = off; off += TILES_PER_CTA * p.a_bytes;
+  p.film = off; off += 2 * p.film_bytes;
+  p.cvec = off; off += (uint32_t)align_up((size_t)L.cvec_floats * 4, 16);
+  p.bars = off; off += 256;
+  p.xch = off;
+  p.xch_stride = 2;
+  off += 2 * 2 * 2 * TILE_M * 8;       // [2 buffers][2 tiles][2 column halves][TILE_M] (row sum, sum of squares)
+  off += 2 * 2 * TILE_M * L.DP * 4;    // [2 tiles][2 halves][TILE_M][DP] output-projector partials
   p.ring = (uint32_t)align_up(off, 128);
   int n = (int)((SMEM_LIMIT - p.ring) / p.stage_bytes);
   if (n > 8) n = 8;

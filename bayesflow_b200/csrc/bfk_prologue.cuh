@@ -39,14 +39,15 @@ __device__ __forceinline__ float act_rt(int act, float x) {
 
 // (K,N) fp32 row-major (Keras (in,out))  ->  [K/8][N][8] 16-bit: the K-major no-swizzle UMMA operand image, so that any
 // slab of K rows is one contiguous byte range (bulk-copyable) and LBO = N*16, SBO = 128.
-__global__ void pack_gemm_kernel(const float* __restrict__ src, int K, int N, int bf16, uint16_t* __restrict__ dst) {
+__global__ void pack_gemm_kernel(const float* __restrict__ src, int K, int N, int bf16, uint16_t* __restrict__ dst,
+                                 float scale = 1.f) {
   int idx = blockIdx.x * blockDim.x + threadIdx.x;  // one thread per (k8, n)
   if (idx >= (K / 8) * N) return;
   int n = idx % N, k8 = idx / N;
   uint16_t out[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    float v = src[(size_t)(k8 * 8 + i) * N + n];
+    float v = src[(size_t)(k8 * 8 + i) * N + n] * scale;
     if (bf16) {
       __nv_bfloat16 b = __float2bfloat16_rn(v);
       out[i] = *reinterpret_cast<uint16_t*>(&b);
@@ -61,6 +62,10 @@ __global__ void pack_gemm_kernel(const float* __restrict__ src, int K, int N, in
 __global__ void copy_f32_kernel(const float* __restrict__ src, float* __restrict__ dst, size_t n) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) dst[i] = src ? src[i] : 0.f;
+}
+__global__ void scale_f32_kernel(float* __restrict__ dst, float s, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] *= s;
 }
 __global__ void fill_f32_kernel(float* __restrict__ dst, float v, size_t n) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -93,12 +98,47 @@ __global__ void fold_proj_kernel(const float* __restrict__ out_k, const float* _
   s0s1[DP + d] = (float)a1;
 }
 
+// Chase layout (bfk_sampler_chase.cuh): the Dense kernel of block l >= 1 consumes the UN-normalised output v of block l-1,
+// so LayerNorm's affine moves into the weights:  W' = gamma_prev o W (rows scaled, then rounded to the operand type),
+// g_j = sum_k W'_kj (of the ROUNDED values: exactly what the tensor core multiplies mu by), c_j = b_j + sum_k beta_prev_k W_kj.
+// One thread per output column.  gamma_prev == nullptr (block 0): plain pack, g = 0, gamma image = 1.
+__global__ void chase_fold_kernel(const float* __restrict__ Wk, const float* __restrict__ bd, const float* __restrict__ gamma_prev,
+                                  const float* __restrict__ beta_prev, int K, int N, int bf16, uint16_t* __restrict__ dst,
+                                  float* __restrict__ c_out, float* __restrict__ g_out, float* __restrict__ gam_out) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float g = 0.f;
+  double cacc = 0.0;
+  for (int k = 0; k < K; ++k) {
+    const float w = Wk[(size_t)k * N + n];
+    const float s = gamma_prev ? gamma_prev[k] * w : w;
+    uint16_t h;
+    float back;
+    if (bf16) {
+      __nv_bfloat16 b = __float2bfloat16_rn(s);
+      h = *reinterpret_cast<uint16_t*>(&b);
+      back = __bfloat162float(b);
+    } else {
+      __half b = __float2half_rn(s);
+      h = *reinterpret_cast<uint16_t*>(&b);
+      back = __half2float(b);
+    }
+    dst[((size_t)(k >> 3) * N + n) * 8 + (k & 7)] = h;
+    g += back;
+    if (beta_prev) cacc += (double)beta_prev[k] * (double)w;
+  }
+  c_out[n] = (bd[n] + (float)cacc) * 1.4426950408889634f;  // pre-activations are carried times log2(e) (chase kernel)
+  g_out[n] = gamma_prev ? g : 0.f;
+  gam_out[n] = gamma_prev ? gamma_prev[n] : 1.f;
+}
+
 // conditions (G,C) -> pre_add (G,W), post_add (G,W)   [time_mlp.py:133-139 hoisted; SURVEY §7.3-2]
 //   concat: post = bm + act(c Wc + bc) Wm[W:2W,:],  pre = (unused)
 //   add   : pre  = c Wc + bc,                         post = bm
+// out_scale: 1, or log2(e) for the chase kernel, whose pre-activations are carried times log2(e)
 __global__ void cond_prologue_kernel(bfk_net_config cfg, const unsigned char* __restrict__ packed, PackedLayout L,
                                      const float* __restrict__ cond, long long G, float* __restrict__ pre_add,
-                                     float* __restrict__ post_add) {
+                                     float* __restrict__ post_add, float out_scale) {
   extern __shared__ float sh[];  // [C] conditions, [W] act(hc)
   const int W = cfg.W, C = cfg.C;
   float* sc = sh;
@@ -115,8 +155,8 @@ __global__ void cond_prologue_kernel(bfk_net_config cfg, const unsigned char* __
       float hc = cb[k];
       for (int i = 0; i < C; ++i) hc = fmaf(sc[i], ck[(size_t)i * W + k], hc);
       if (cfg.merge == BFK_MERGE_ADD) {
-        pre_add[g * W + k] = hc;
-        post_add[g * W + k] = mb[k];
+        pre_add[g * W + k] = hc * out_scale;
+        post_add[g * W + k] = mb[k] * out_scale;
       } else {
         sa[k] = act_rt(cfg.activation, hc);
       }
@@ -126,7 +166,7 @@ __global__ void cond_prologue_kernel(bfk_net_config cfg, const unsigned char* __
       for (int k = threadIdx.x; k < W; k += blockDim.x) {
         float acc = mb[k];
         for (int j = 0; j < W; ++j) acc = fmaf(sa[j], mc[(size_t)j * W + k], acc);
-        post_add[g * W + k] = acc;
+        post_add[g * W + k] = acc * out_scale;
       }
     }
   }
@@ -190,9 +230,10 @@ __host__ __device__ inline void schedule_coefs(const bfk_schedule& s, double t, 
 }
 
 // times (n) -> table (n, stride): [L][W] FiLM beta, ([L][W] FiLM gamma), TABLE_SCALARS scalars
+// chase != 0: the FiLM shift of block l >= 1 also carries LayerNorm beta of block l-1 (bfk_sampler_chase.cuh)
 __global__ void eval_table_kernel(bfk_net_config cfg, const unsigned char* __restrict__ packed, PackedLayout L,
                                   bfk_schedule sched, const float* __restrict__ times, long long n, int stride,
-                                  float* __restrict__ table) {
+                                  float* __restrict__ table, int chase) {
   __shared__ float emb[80];
   __shared__ float sc[4];
   const int W = cfg.W, T = cfg.T;
@@ -229,7 +270,9 @@ __global__ void eval_table_kernel(bfk_net_config cfg, const unsigned char* __res
       const float* fb = reinterpret_cast<const float*>(packed + (which ? L.film_g_b : L.film_b_b)) + (size_t)l * W;
       float acc = 0.f;
       for (int j = 0; j < T; ++j) acc = fmaf(emb[j], fk[(size_t)j * W + k], acc);
-      row[idx] = acc + fb[k];
+      acc = acc + fb[k];
+      if (chase && which == 0 && l > 0) acc += reinterpret_cast<const float*>(packed + L.ln_beta)[(size_t)(l - 1) * W + k];
+      row[idx] = acc;
     }
     if (threadIdx.x < TABLE_SCALARS) row[nv * cfg.L * W + threadIdx.x] = threadIdx.x < 4 ? sc[threadIdx.x] : 0.f;
   }

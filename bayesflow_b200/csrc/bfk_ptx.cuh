@@ -189,15 +189,27 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 }
 
 // ------------------------------------------------------------------ math
+// BFK_EXP: compile-time timing experiments (tools/gpu_chase_exp.sh); results are garbage, only the time matters.
+#ifndef BFK_EXP
+#define BFK_EXP 0
+#endif
 __device__ __forceinline__ float ex2_approx(float x) {
+#if (BFK_EXP & 1)
+  return fmaf(x, 0.5f, 1.f);  // experiment: no MUFU
+#else
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+#endif
 }
 __device__ __forceinline__ float rcp_approx(float x) {
+#if (BFK_EXP & 1)
+  return fmaf(x, 0.25f, 0.5f);
+#else
   float y;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+#endif
 }
 
 }  // namespace bfk

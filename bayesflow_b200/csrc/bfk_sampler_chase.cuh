@@ -1,0 +1,619 @@
+// The fused on-chip sampler, "chase" schedule, for the reference's default block shape (LayerNorm + residual + FiLM
+// shift, networks/defaults.py:13-26; time_mlp.py:125-147, conditional_dense_block.py:114-131).
+//
+// One persistent CTA per SM advances ONE 128-draw tile through every velocity evaluation of every ODE step:
+//   * 16 epilogue warps (TMEM lane quarter = w & 3, column group = w >> 2; group cg owns the 16-column chunks
+//     cg, cg+4, cg+8, ...), one UMMA issuer warp, one bulk-copy producer warp;
+//   * the accumulator is DOUBLE-BUFFERED in TMEM (2 x W fp32 columns) and every epilogue is a SINGLE pass that writes
+//     the next layer's A operand 32-column K-slab by K-slab, each slab announced on its own mbarrier: the UMMAs of
+//     layer g+1 chase the epilogue of layer g slab by slab, so the tensor pipe runs underneath the epilogue of the same
+//     tile and the weight ring (up to 8 x 16 KB, > one whole layer) never drains;
+//   * the single pass is possible because LayerNorm is folded into its consumer: with v the un-normalised block output
+//     and (mu, r) its row statistics,  LN(v) W + b = r (v (gamma o W)) - r mu g + c,  g_j = sum_k fp16(gamma_k W_kj),
+//     c_j = b_j + sum_k beta_k W_kj  (bfk_pack writes gamma o W, g, c), so the A operand is the raw fp16 image of v
+//     and the next epilogue applies one row scale and one rank-1 correction; the skip connection h = LN(v) is rebuilt
+//     from the same image, with beta folded into the per-evaluation FiLM table.
+//
+// Per block and row (thread == draw == TMEM lane), 16 columns at a time, packed f32x2:
+//   t  = log2(e) (r acc - r mu g + c)             (= log2(e) (h W + b) of conditional_dense_block.py:117)
+//   v' = t * actw(t) + [gamma (v r - r mu) + (beta + film(t))]        (:118-127; act(u) = t * actw(t))
+//   row sum / sum of squares of v' in fp32; fp16(v') -> A tile; slab barrier.
+#pragma once
+#include "bfk_fast_epilogue.cuh"
+#include "bfk_sampler.cuh"
+
+// -DBFK_PROFILE: per-warp cycle accounting into a device buffer (read with bfk_debug_read_prof); compiled out otherwise
+#ifdef BFK_PROFILE
+__device__ long long g_bfk_prof[148 * 18 * 8];
+#define PROF_DECL long long pf_[8] = {0, 0, 0, 0, 0, 0, 0, 0}; long long pt_ = clock64();
+#define PROF_ADD(slot) { const long long n_ = clock64(); pf_[slot] += n_ - pt_; pt_ = n_; }
+#define PROF_FLUSH(warp) if ((threadIdx.x & 31) == 0) { for (int i_ = 0; i_ < 8; ++i_) g_bfk_prof[(blockIdx.x * 18 + (warp)) * 8 + i_] = pf_[i_]; }
+#else
+#define PROF_DECL
+#define PROF_ADD(slot)
+#define PROF_FLUSH(warp)
+#endif
+
+namespace bfk {
+
+constexpr int C_EPI_WARPS = 16, C_MMA_WARP = 16, C_LOAD_WARP = 17, C_NUM_THREADS = 576;
+constexpr int C_MAX_STAGE = 8;
+
+struct ChaseBars {
+  uint32_t base;
+  __device__ uint32_t w_full(int s) const { return base + 8 * s; }
+  __device__ uint32_t w_empty(int s) const { return base + 8 * (8 + s); }
+  __device__ uint32_t a_slab(int s) const { return base + 8 * (16 + s); }
+  __device__ uint32_t acc_ready(int b) const { return base + 8 * (24 + b); }
+  __device__ uint32_t film_full(int b) const { return base + 8 * (26 + b); }
+  __device__ uint32_t film_empty(int b) const { return base + 8 * (28 + b); }
+  __device__ uint32_t stats() const { return base + 8 * 30; }
+  __device__ uint32_t tmem_slot() const { return base + 8 * 31; }
+};
+
+// Pre-activations are carried times log2(e) (bfk_pack scales the weights / biases): with t = x log2(e),
+// act(x) = t * actw(t), actw(t) = ln2 * tanh(softplus(x)) = ln2 - 2 ln2 / ((1 + 2^t)^2 + 1) for mish, ln2 / (1 + 2^-t) for
+// silu: the multiply by log2(e) in front of ex2 disappears.  All MUFU of the chunk issued back to back.
+template <int ACT>
+__device__ __forceinline__ void actw2x8(const float2* t, float2* w) {
+  if (ACT == BFK_ACT_MISH) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { w[i].x = ex2_approx(t[i].x); w[i].y = ex2_approx(t[i].y); }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float2 q = __fadd2_rn(w[i], f2(1.f));
+      w[i] = __ffma2_rn(q, q, f2(1.f));
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { w[i].x = rcp_approx(w[i].x); w[i].y = rcp_approx(w[i].y); }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] = __ffma2_rn(w[i], f2(-1.3862943611198906f), f2(0.6931471805599453f));
+  } else {  // silu
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { w[i].x = ex2_approx(-t[i].x); w[i].y = ex2_approx(-t[i].y); }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] = __fadd2_rn(w[i], f2(1.f));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { w[i].x = rcp_approx(w[i].x); w[i].y = rcp_approx(w[i].y); }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] = __fmul2_rn(w[i], f2(0.6931471805599453f));
+  }
+}
+// t (pre-activation times log2(e)) -> act(x), 16 values
+template <int ACT>
+__device__ __forceinline__ void act_scaled2x8(float2* t) {
+  if (ACT == BFK_ACT_MISH || ACT == BFK_ACT_SILU) {
+    float2 w[8];
+    actw2x8<ACT>(t, w);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t[i] = __fmul2_rn(t[i], w[i]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      t[i] = make_float2(act_fn<ACT>(t[i].x * 0.6931471805599453f), act_fn<ACT>(t[i].y * 0.6931471805599453f));
+  }
+}
+
+__device__ __forceinline__ void ld4x2(const float* p, float2* o) {  // 8 floats -> 4 float2
+#if (BFK_EXP & 32)
+  o[0] = o[1] = o[2] = o[3] = make_float2(0.001f, 0.002f);  // experiment: no shared-memory vector loads
+  return;
+#endif
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  o[0] = make_float2(a.x, a.y); o[1] = make_float2(a.z, a.w); o[2] = make_float2(b.x, b.y); o[3] = make_float2(b.z, b.w);
+}
+
+// One 16-column chunk of a ConditionalDenseBlock epilogue in the folded form (see the header).  v: 8 float2 accumulators
+// in, block output v' out.  rs = r, nm = -r*mu of the INPUT rows (1, 0 for the first block).
+template <int ACT, bool BF16>
+__device__ __forceinline__ void chase_block_chunk(float2* v, int col, float2 rs, float2 nm, float2 rsL, float2 nmL,
+                                                  const float* __restrict__ cl,
+                                                  const float* __restrict__ gl, const float* __restrict__ gam,
+                                                  const float* __restrict__ fbeta, const unsigned char* sA_row,
+                                                  float2* sum2, float2* sq2) {
+#pragma unroll
+  for (int jj = 0; jj < 2; ++jj) {
+    float2 g4[4], c4[4];
+    ld4x2(gl + col + jj * 8, g4);
+    ld4x2(cl + col + jj * 8, c4);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) v[jj * 4 + p] = __ffma2_rn(v[jj * 4 + p], rsL, __ffma2_rn(nmL, g4[p], c4[p]));
+  }
+  float2 w[8];  // v = t = u log2(e);  act(u) = t * w
+  if (ACT == BFK_ACT_MISH || ACT == BFK_ACT_SILU) {
+    actw2x8<ACT>(v, w);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      v[i] = make_float2(act_fn<ACT>(v[i].x * 0.6931471805599453f), act_fn<ACT>(v[i].y * 0.6931471805599453f));
+      w[i] = f2(1.f);
+    }
+  }
+#pragma unroll
+  for (int jj = 0; jj < 2; ++jj) {  // 8 columns = one 16-byte K chunk of the A tile
+#if (BFK_EXP & 4)
+    const uint4 sk = make_uint4(0, 0, 0, 0);
+#else
+    const uint4 sk = *reinterpret_cast<const uint4*>(sA_row + (size_t)((col >> 3) + jj) * (TILE_M * 16));
+#endif
+    const uint32_t su[4] = {sk.x, sk.y, sk.z, sk.w};
+    float2 ga[4], fb[4];
+    ld4x2(gam + col + jj * 8, ga);
+    ld4x2(fbeta + col + jj * 8, fb);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      const int i = jj * 4 + p;
+      const float2 xh = __ffma2_rn(unpack2f<BF16>(su[p]), rs, nm);
+      const float2 h = __ffma2_rn(xh, ga[p], fb[p]);
+      const float2 u = __ffma2_rn(v[i], w[i], h);
+      sum2[p] = __fadd2_rn(sum2[p], u);
+      sq2[p] = __ffma2_rn(u, u, sq2[p]);
+      v[i] = u;
+    }
+  }
+}
+
+template <bool BF16>
+__device__ __forceinline__ void store_chunk16(const float2* v, int col, unsigned char* sA_row) {
+#pragma unroll
+  for (int jj = 0; jj < 2; ++jj)
+    *reinterpret_cast<uint4*>(sA_row + (size_t)((col >> 3) + jj) * (TILE_M * 16)) =
+        make_uint4(pack2f<BF16>(v[jj * 4 + 0]), pack2f<BF16>(v[jj * 4 + 1]), pack2f<BF16>(v[jj * 4 + 2]),
+                   pack2f<BF16>(v[jj * 4 + 3]));
+}
+
+// generic-proxy A-tile stores of this warp -> visible to the UMMA (async proxy); then one arrive on the slab barrier
+__device__ __forceinline__ void announce_slab(uint32_t bar, int lane) {
+#if !(BFK_EXP & 2)
+  fence_proxy_async_smem();
+#endif
+  __syncwarp();
+  if (lane == 0) mbar_arrive(bar);
+}
+
+// ------------------------------------------------------------------------------------------------ issuer / producer
+__device__ __forceinline__ void chase_issuer_loop(const SamplerArgs& a, const ChaseBars& bars, uint32_t smem_base,
+                                                  uint32_t tmem_base, long long n_tiles, long long n_evals, int lane) {
+  const int W = a.W, n_slabs = W / KC;
+  if (lane == 0) {
+    PROF_DECL
+    uint32_t ph_full = 0;
+    int stage = 0;
+    long long kk = 0;  // running GEMM counter: accumulator buffer kk & 1, slab-barrier parity kk & 1
+    const uint32_t a_lbo = TILE_M * 16, b_lbo = (uint32_t)W * 16;
+    const uint32_t a_base = smem_base + a.plan.a_tile;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      for (long long e = 0; e < n_evals; ++e) {
+        for (int g = 0; g < a.NG; ++g, ++kk) {
+          const uint32_t d_tmem = tmem_base + (uint32_t)(kk & 1) * W;
+          for (int s = 0; s < n_slabs; ++s) {
+            PROF_ADD(0)
+            mbar_wait(bars.w_full(stage), (ph_full >> stage) & 1, a.err_flag, 4);  // the ring runs ahead: normally complete
+            PROF_ADD(2)
+            ph_full ^= (1u << stage);
+            mbar_wait(bars.a_slab(s), (uint32_t)(kk & 1), a.err_flag, 3);
+            PROF_ADD(1)
+            tc_fence_after();
+            const uint32_t b_base = smem_base + a.plan.ring + stage * a.plan.stage_bytes;
+#pragma unroll
+            for (int k2 = 0; k2 < KC / 16; ++k2) {
+              const uint64_t ad = umma_smem_desc(a_base + (uint32_t)(s * (KC / 8) + k2 * 2) * a_lbo, a_lbo, 128);
+              const uint64_t bd = umma_smem_desc(b_base + (uint32_t)(k2 * 2) * b_lbo, b_lbo, 128);
+              umma_f16(d_tmem, ad, bd, a.idesc, (uint32_t)((s | k2) != 0));
+            }
+            umma_commit(bars.w_empty(stage));
+            stage = (stage + 1 == a.plan.n_stage) ? 0 : stage + 1;
+          }
+          umma_commit(bars.acc_ready((int)(kk & 1)));
+        }
+      }
+    }
+    PROF_ADD(0)
+    PROF_FLUSH(C_MMA_WARP)
+  }
+  __syncwarp();
+}
+
+__device__ __forceinline__ void chase_producer_loop(const SamplerArgs& a, const ChaseBars& bars, uint32_t smem_base,
+                                                    long long n_tiles, long long n_evals, int lane) {
+  const int W = a.W, n_slabs = W / KC;
+  if (lane == 0) {
+    PROF_DECL
+    uint32_t ph_empty = 0;
+    int stage = 0;
+    long long my_tiles = 0;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) ++my_tiles;
+    const long long Q = my_tiles * n_evals;
+    auto load_film = [&](long long qq) {
+      const int fb = (int)(qq & 1);
+      mbar_wait(bars.film_empty(fb), (uint32_t)(((qq >> 1) & 1) ^ 1), a.err_flag, 5);
+      mbar_arrive_expect_tx(bars.film_full(fb), (uint32_t)a.tstride * 4);
+      bulk_g2s(smem_base + a.plan.film + fb * a.plan.film_bytes, a.table + (qq % n_evals) * a.tstride,
+               (uint32_t)a.tstride * 4, bars.film_full(fb));
+    };
+    if (Q > 0) load_film(0);
+    for (long long q = 0; q < Q; ++q) {
+      for (int g = 0; g < a.NG; ++g) {
+        for (int c = 0; c < n_slabs; ++c) {
+          PROF_ADD(0)
+          mbar_wait(bars.w_empty(stage), ((ph_empty >> stage) & 1) ^ 1, a.err_flag, 6);
+          PROF_ADD(1)
+          ph_empty ^= (1u << stage);
+          mbar_arrive_expect_tx(bars.w_full(stage), a.plan.stage_bytes);
+          bulk_g2s(smem_base + a.plan.ring + stage * a.plan.stage_bytes,
+                   a.wg + ((size_t)g * W * W + (size_t)c * KC * W) * 2, a.plan.stage_bytes, bars.w_full(stage));
+          stage = (stage + 1 == a.plan.n_stage) ? 0 : stage + 1;
+        }
+        PROF_ADD(0)
+        if (g == 0 && q + 1 < Q) load_film(q + 1);
+        PROF_ADD(2)
+      }
+    }
+    PROF_FLUSH(C_LOAD_WARP)
+  }
+  __syncwarp();
+}
+
+// ------------------------------------------------------------------------------------------------ the kernel
+template <int ACT, int DP, bool BF16>
+__global__ void __launch_bounds__(C_NUM_THREADS, 1) sampler_chase_kernel(const SamplerArgs a) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  if (a.mode == 2 && a.ctrl[BFK_CTRL_SKIP] != 0.f) return;  // controller says: loop finished, nothing to do
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int W = a.W;
+  const uint32_t smem_base = smem_u32(smem);
+  ChaseBars bars{smem_base + a.plan.bars};
+  float* s_cvec = reinterpret_cast<float*>(smem + a.plan.cvec);
+  volatile uint32_t* s_tmem = reinterpret_cast<volatile uint32_t*>(smem + a.plan.bars + 8 * 31);
+
+  // ---------------- one-time setup
+  for (int i = threadIdx.x; i < a.cvec_floats; i += C_NUM_THREADS) s_cvec[i] = a.cvec[i];
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C_MAX_STAGE; ++s) {
+      mbar_init(bars.w_full(s), 1);
+      mbar_init(bars.w_empty(s), 1);
+      mbar_init(bars.a_slab(s), 8);  // 4 lane quarters x the 2 column groups that own the slab's two chunks
+    }
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(bars.acc_ready(t), 1);     // tcgen05.commit
+      mbar_init(bars.film_full(t), 1);     // producer arrive + tx bytes
+      mbar_init(bars.film_empty(t), C_EPI_WARPS);
+    }
+    mbar_init(bars.stats(), C_EPI_WARPS);
+    fence_barrier_init();
+  }
+  const uint32_t tmem_cols = (2 * W <= 32) ? 32 : (2 * W <= 64) ? 64 : (2 * W <= 128) ? 128 : (2 * W <= 256) ? 256 : 512;
+  if (warp == C_MMA_WARP) tmem_alloc(bars.tmem_slot(), tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  const long long n_tiles = (a.B + TILE_M - 1) / TILE_M;
+  const long long n_evals = a.n_steps * (a.S - a.s0);
+
+  if (warp < C_EPI_WARPS) {
+    // =========================================================== EPILOGUE / ODE warps
+    const int quarter = warp & 3, cg = warp >> 2;
+    const int r = quarter * 32 + lane;  // row inside the tile == TMEM lane
+    const int n_chunks = W / 16;
+    unsigned char* sA = smem + a.plan.a_tile + r * 16;
+    const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    float2* xst = reinterpret_cast<float2*>(smem + a.plan.xch);        // [2][4][TILE_M] (sum, sum of squares)
+    float* xpr = reinterpret_cast<float*>(smem + a.plan.xch + 2 * 4 * TILE_M * 8);  // [4][TILE_M][DP] projector partials
+    const float* c_wx = s_cvec + a.cv_wx;
+    const float* c_bx = s_cvec + a.cv_bx;
+    const float* c_blk = s_cvec + a.cv_blk;  // per block: c_l, g_l, gamma_{l-1}
+    const float* c_wo = s_cvec + a.cv_wo;    // [DP][W] gamma_L * Wo
+    const float* c_bo = s_cvec + a.cv_bo;    // s0[DP], s1[DP]
+    const float inv_w = 1.f / (float)W;
+    PROF_DECL
+    uint32_t ph_acc = 0;  // bit b = parity of accumulator buffer b
+    long long kk = 0;     // running GEMM counter (same sequence as the issuer)
+    long long nb = 0;     // running block-epilogue counter (stats exchange buffer / barrier parity)
+    long long q = 0;      // evaluation sequence number of this CTA (film double buffer)
+
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      const long long row = tile * TILE_M + r;
+      const bool valid = row < a.B;
+      const long long grp = valid ? row / a.rows_per_group : 0;
+      const float* g_pre = a.pre_add ? a.pre_add + grp * W : nullptr;
+      const float* g_post = a.post_add ? a.post_add + grp * W : nullptr;
+      // all four column groups carry the (identical) ODE state of the row; group 0 writes results
+      float y[DP], xs[DP], kst[BFK_MAX_STAGES][DP], msk[DP], ynew[DP];
+      const int sel = (a.mode == 2) ? (int)a.ctrl[BFK_CTRL_SEL] : 0;
+      const float* y_src = (a.mode == 2) ? a.ybuf + (size_t)sel * a.B * a.D : a.x_in;
+#pragma unroll
+      for (int d = 0; d < DP; ++d) {
+        y[d] = (valid && d < a.D) ? y_src[row * a.D + d] : 0.f;
+        msk[d] = (a.tmask && d < a.D) ? a.tmask[d] : 1.f;
+        ynew[d] = 0.f;
+        if (a.mode == 2) kst[0][d] = (valid && d < a.D) ? a.kbuf[(size_t)sel * a.B * a.D + row * a.D + d] : 0.f;
+      }
+
+      float h_next = (a.mode == 2) ? a.ctrl[BFK_CTRL_H] : a.step_h[0];
+      for (long long step = 0; step < a.n_steps; ++step) {
+#if (BFK_EXP & 16)
+        const float h = 0.01f;
+#else
+        const float h = h_next;
+        if (a.mode != 2 && step + 1 < a.n_steps) h_next = a.step_h[step + 1];  // in flight under the whole step
+#endif
+        for (int s = a.s0; s < a.S; ++s, ++q) {
+          // ---- stage input (integrate.py:47-54 add_scaled: acc = sum c_j k_j ; y + h*acc)
+#if (BFK_EXP & 16)
+          for (int d = 0; d < DP; ++d) xs[d] = y[d];
+          if (false) {
+#else
+          if (s == 6) {
+#endif  // FSAL evaluation at the candidate state (integrate.py:94-102, 184-198)
+#pragma unroll
+            for (int d = 0; d < DP; ++d) {
+              float acc = 0.f;
+              for (int j = 0; j < 6; ++j) acc = acc + a.rk_b[j] * kst[j][d];
+              ynew[d] = y[d] + h * acc;
+              xs[d] = ynew[d];
+            }
+          } else {
+#pragma unroll
+            for (int d = 0; d < DP; ++d) {
+              float acc = 0.f;
+              for (int j = 0; j < s; ++j) acc = acc + a.rk_a[s][j] * kst[j][d];
+              xs[d] = (s == 0) ? y[d] : y[d] + h * acc;
+            }
+          }
+          const int fb = (int)(q & 1);
+          const float* s_film = reinterpret_cast<const float*>(smem + a.plan.film + fb * a.plan.film_bytes);
+          PROF_ADD(0)
+          mbar_wait(bars.film_full(fb), (uint32_t)((q >> 1) & 1), a.err_flag, 1);
+          PROF_ADD(1)
+
+          // ---- x_proj (+ conditions for merge="add") + activation -> A tile, slab by slab   time_mlp.py:131,137,140
+          {
+            float2 xb[DP];
+#pragma unroll
+            for (int d = 0; d < DP; ++d) xb[d] = f2(xs[d]);
+            for (int ch = cg; ch < n_chunks; ch += 4) {
+              const int col = ch * 16;
+              float2 v8[8];
+              ld4x2(c_bx + col, v8);
+              ld4x2(c_bx + col + 8, v8 + 4);
+              if (a.has_merge && g_pre) {
+#pragma unroll
+                for (int jj = 0; jj < 2; ++jj) {
+                  const float4 p0 = __ldg(reinterpret_cast<const float4*>(g_pre + col + jj * 8));
+                  const float4 p1 = __ldg(reinterpret_cast<const float4*>(g_pre + col + jj * 8 + 4));
+                  float2* v4 = v8 + jj * 4;
+                  v4[0] = __fadd2_rn(v4[0], make_float2(p0.x, p0.y)); v4[1] = __fadd2_rn(v4[1], make_float2(p0.z, p0.w));
+                  v4[2] = __fadd2_rn(v4[2], make_float2(p1.x, p1.y)); v4[3] = __fadd2_rn(v4[3], make_float2(p1.z, p1.w));
+                }
+              }
+#pragma unroll
+              for (int d = 0; d < DP; ++d) {
+                float2 w8[8];
+                ld4x2(c_wx + d * W + col, w8);
+                ld4x2(c_wx + d * W + col + 8, w8 + 4);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v8[i] = __ffma2_rn(xb[d], w8[i], v8[i]);
+              }
+              act_scaled2x8<ACT>(v8);
+              store_chunk16<BF16>(v8, col, sA);
+              announce_slab(bars.a_slab(ch >> 1), lane);
+            }
+          }
+
+          PROF_ADD(2)
+          float pred[DP];
+          // row scale / shift of the current A image (identity before block 1); *L = times log2(e)
+          float2 rs = f2(1.f), nm = f2(0.f), rsL = f2(1.4426950408889634f), nmL = f2(0.f);
+          bool stats_pending = false;
+          // statistics of the previous block epilogue: every warp has arrived on the stats barrier by the time the next
+          // accumulator is ready (its K slabs were announced after the partial sums were written)
+          auto read_stats = [&]() {
+            mbar_wait(bars.stats(), (uint32_t)(nb & 1), a.err_flag, 7);
+            const float2* xs_buf = xst + (size_t)(nb & 1) * 4 * TILE_M;
+            const float2 p0 = xs_buf[0 * TILE_M + r], p1 = xs_buf[1 * TILE_M + r];
+            const float2 p2 = xs_buf[2 * TILE_M + r], p3 = xs_buf[3 * TILE_M + r];
+            const float mean = ((p0.x + p1.x) + (p2.x + p3.x)) * inv_w;  // identical expression in every group
+            const float var = fmaxf(((p0.y + p1.y) + (p2.y + p3.y)) * inv_w - mean * mean, 0.f);
+            const float rstd = rsqrtf(var + 1e-3f);  // keras LayerNormalization epsilon
+            rs = f2(rstd);
+            nm = f2(-mean * rstd);
+            rsL = f2(rstd * 1.4426950408889634f);
+            nmL = f2(-mean * rstd * 1.4426950408889634f);
+            ++nb;
+            stats_pending = false;
+          };
+          for (int g = 0; g < a.NG; ++g, ++kk) {
+            const int ab = (int)(kk & 1);
+            mbar_wait(bars.acc_ready(ab), (ph_acc >> ab) & 1, a.err_flag, 2);
+            PROF_ADD(3)
+            if (stats_pending) read_stats();
+            ph_acc ^= (1u << ab);
+            tc_fence_after();
+            const uint32_t t_acc = t_lane + (uint32_t)ab * W;
+            const bool last = (g == a.NG - 1);
+            float2 va[8], vb[8];
+            if (a.has_merge && g == 0) {
+              // ---- merge_proj epilogue: h = act(acc + [m_c + bm])                      time_mlp.py:139-140
+              auto merge_chunk = [&](float2* v, int ch) {
+                const int col = ch * 16;
+#pragma unroll
+                for (int jj = 0; jj < 2; ++jj) {
+                  const float4 p0 = __ldg(reinterpret_cast<const float4*>(g_post + col + jj * 8));
+                  const float4 p1 = __ldg(reinterpret_cast<const float4*>(g_post + col + jj * 8 + 4));
+                  v[jj * 4 + 0] = __fadd2_rn(v[jj * 4 + 0], make_float2(p0.x, p0.y));
+                  v[jj * 4 + 1] = __fadd2_rn(v[jj * 4 + 1], make_float2(p0.z, p0.w));
+                  v[jj * 4 + 2] = __fadd2_rn(v[jj * 4 + 2], make_float2(p1.x, p1.y));
+                  v[jj * 4 + 3] = __fadd2_rn(v[jj * 4 + 3], make_float2(p1.z, p1.w));
+                }
+                act_scaled2x8<ACT>(v);
+                store_chunk16<BF16>(v, col, sA);
+                announce_slab(bars.a_slab(ch >> 1), lane);
+              };
+              if (cg < n_chunks) tmem_ld16(t_acc + cg * 16, reinterpret_cast<float*>(va));
+              for (int ch = cg; ch < n_chunks; ch += 8) {
+                tmem_ld_wait16(reinterpret_cast<float*>(va));
+                if (ch + 4 < n_chunks) tmem_ld16(t_acc + (ch + 4) * 16, reinterpret_cast<float*>(vb));
+                merge_chunk(va, ch);
+                if (ch + 4 < n_chunks) {
+                  tmem_ld_wait16(reinterpret_cast<float*>(vb));
+                  if (ch + 8 < n_chunks) tmem_ld16(t_acc + (ch + 8) * 16, reinterpret_cast<float*>(va));
+                  merge_chunk(vb, ch + 4);
+                }
+              }
+              PROF_ADD(4)
+            } else {
+              // ---- ConditionalDenseBlock epilogue, folded LayerNorm                conditional_dense_block.py:114-131
+              const int l = g - a.has_merge;
+              const float* cl = c_blk + (3 * l + 0) * W;
+              const float* gl = c_blk + (3 * l + 1) * W;
+              const float* gam = c_blk + (3 * l + 2) * W;
+              const float* fbeta = s_film + l * W;
+              float2 sum2[4], sq2[4], pa[DP];
+#pragma unroll
+              for (int p = 0; p < 4; ++p) { sum2[p] = f2(0.f); sq2[p] = f2(0.f); }
+#pragma unroll
+              for (int d = 0; d < DP; ++d) pa[d] = f2(0.f);
+              auto blk = [&](float2* v, int ch) {
+                const int col = ch * 16;
+                chase_block_chunk<ACT, BF16>(v, col, rs, nm, rsL, nmL, cl, gl, gam, fbeta, sA, sum2, sq2);
+                if (last) {
+#pragma unroll
+                  for (int d = 0; d < DP; ++d) {
+                    float2 w8[8];
+                    ld4x2(c_wo + d * W + col, w8);
+                    ld4x2(c_wo + d * W + col + 8, w8 + 4);
+                    float2 t0 = __fmul2_rn(v[0], w8[0]), t1 = __fmul2_rn(v[1], w8[1]);
+                    t0 = __ffma2_rn(v[2], w8[2], t0); t1 = __ffma2_rn(v[3], w8[3], t1);
+                    t0 = __ffma2_rn(v[4], w8[4], t0); t1 = __ffma2_rn(v[5], w8[5], t1);
+                    t0 = __ffma2_rn(v[6], w8[6], t0); t1 = __ffma2_rn(v[7], w8[7], t1);
+                    pa[d] = __fadd2_rn(pa[d], __fadd2_rn(t0, t1));
+                  }
+                } else {
+                  store_chunk16<BF16>(v, col, sA);
+                  PROF_ADD(6)
+                  announce_slab(bars.a_slab(ch >> 1), lane);
+                  PROF_ADD(7)
+                }
+              };
+              if (cg < n_chunks) tmem_ld16(t_acc + cg * 16, reinterpret_cast<float*>(va));
+              for (int ch = cg; ch < n_chunks; ch += 8) {
+                PROF_ADD(6)
+                tmem_ld_wait16(reinterpret_cast<float*>(va));
+                PROF_ADD(5)
+                if (ch + 4 < n_chunks) tmem_ld16(t_acc + (ch + 4) * 16, reinterpret_cast<float*>(vb));
+                blk(va, ch);
+                if (ch + 4 < n_chunks) {
+                  PROF_ADD(6)
+                  tmem_ld_wait16(reinterpret_cast<float*>(vb));
+                  PROF_ADD(5)
+                  if (ch + 8 < n_chunks) tmem_ld16(t_acc + (ch + 8) * 16, reinterpret_cast<float*>(va));
+                  blk(vb, ch + 4);
+                }
+              }
+              PROF_ADD(6)
+              // ---- row statistics of v' (all four column groups, through shared memory + the stats mbarrier)
+              const float2 s01 = __fadd2_rn(__fadd2_rn(sum2[0], sum2[1]), __fadd2_rn(sum2[2], sum2[3]));
+              const float2 q01 = __fadd2_rn(__fadd2_rn(sq2[0], sq2[1]), __fadd2_rn(sq2[2], sq2[3]));
+              xst[(size_t)(nb & 1) * 4 * TILE_M + cg * TILE_M + r] = make_float2(s01.x + s01.y, q01.x + q01.y);
+              if (last) {
+#pragma unroll
+                for (int d = 0; d < DP; ++d) xpr[(cg * TILE_M + r) * DP + d] = pa[d].x + pa[d].y;
+              }
+              PROF_ADD(6)
+              __syncwarp();
+              if (lane == 0) mbar_arrive(bars.stats());
+              stats_pending = true;
+              if (last) {
+                // output projector folded through the LayerNorm affine (flow_matching.py:229-230): needs every column now
+                read_stats();
+#pragma unroll
+                for (int d = 0; d < DP; ++d) {
+                  const float dot = (xpr[(0 * TILE_M + r) * DP + d] + xpr[(1 * TILE_M + r) * DP + d]) +
+                                    (xpr[(2 * TILE_M + r) * DP + d] + xpr[(3 * TILE_M + r) * DP + d]);
+                  pred[d] = fmaf(rs.x, dot, fmaf(nm.x, c_bo[DP + d], c_bo[d]));  // rstd (dot - mean s1) + s0
+                }
+              }
+              PROF_ADD(1)
+            }
+          }
+          // ---- velocity of this evaluation (FM: pred; DM: coefZ*z + coefP*pred), inference-time target mask
+          const float coefZ = s_film[a.tstride - TABLE_SCALARS + 0], coefP = s_film[a.tstride - TABLE_SCALARS + 1];
+#pragma unroll
+#if (BFK_EXP & 16)
+          for (int d = 0; d < DP; ++d) y[d] = y[d] + h * (coefZ * xs[d] + coefP * pred[d]) * msk[d];
+#else
+          for (int d = 0; d < DP; ++d) kst[s][d] = (coefZ * xs[d] + coefP * pred[d]) * msk[d];
+#endif
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bars.film_empty(fb));
+        }
+#if !(BFK_EXP & 16)
+        if (a.mode == 0) {
+#pragma unroll
+          for (int d = 0; d < DP; ++d) {
+            float acc = 0.f;
+            for (int j = 0; j < a.S; ++j) acc = acc + a.rk_b[j] * kst[j][d];
+            y[d] = y[d] + h * acc;
+          }
+        }
+#endif
+      }
+      if (a.mode == 2) {
+        // ---- embedded error estimate, row-wise L2 norm, max over rows (integrate.py:104-118, 199-212); max|state|
+        const float h = a.ctrl[BFK_CTRL_H];
+        float e2 = 0.f, mabs = 0.f;
+        bool nonnan = false;
+#pragma unroll
+        for (int d = 0; d < DP; ++d) {
+          float acc = 0.f, e;
+          for (int j = 0; j < 7; ++j) acc = acc + a.rk_e[j] * kst[j][d];
+          if (a.err_kind == 0) e = ynew[d] - (y[d] + h * acc);
+          else e = h * acc;
+          if (d < a.D) {
+            e2 = fmaf(e, e, e2);
+            mabs = (y[d] != y[d]) ? y[d] : ((mabs != mabs) ? mabs : fmaxf(mabs, fabsf(y[d])));
+            nonnan = nonnan || (ynew[d] == ynew[d]);
+          }
+        }
+        float en = valid ? sqrtf(e2) : 0.f;
+        if (!valid) { mabs = 0.f; nonnan = false; }
+        bool isnan_row = (en != en) || (mabs != mabs);
+        if (isnan_row) { en = 0.f; if (mabs != mabs) mabs = 0.f; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          en = fmaxf(en, __shfl_xor_sync(0xffffffffu, en, o));
+          mabs = fmaxf(mabs, __shfl_xor_sync(0xffffffffu, mabs, o));
+        }
+        const bool any_nan = __any_sync(0xffffffffu, isnan_row), any_nonnan = __any_sync(0xffffffffu, nonnan);
+        if (lane == 0 && cg == 0) {
+          int* acc_i = reinterpret_cast<int*>(a.ctrl + BFK_CTRL_ACC);
+          atomicMax(acc_i + 0, __float_as_int(en));
+          atomicMax(acc_i + 1, __float_as_int(mabs));
+          if (any_nan) atomicMax(acc_i + 2, __float_as_int(1.f));
+          if (any_nonnan) atomicMax(acc_i + 3, __float_as_int(1.f));
+        }
+        if (valid && cg == 0) {
+          const size_t o = (size_t)(1 - sel) * a.B * a.D + row * a.D;
+          for (int d = 0; d < a.D; ++d) { a.ybuf[o + d] = ynew[d]; a.kbuf[o + d] = kst[6][d]; }
+        }
+      } else if (valid && cg == 0) {
+        for (int d = 0; d < a.D; ++d) a.x_out[row * a.D + d] = (a.mode == 1) ? kst[0][d] : y[d];
+      }
+    }
+    PROF_ADD(0)
+    PROF_FLUSH(warp)
+    tc_fence_before();
+  } else if (warp == C_MMA_WARP) {
+    chase_issuer_loop(a, bars, smem_base, tmem_base, n_tiles, n_evals, lane);
+  } else {
+    chase_producer_loop(a, bars, smem_base, n_tiles, n_evals, lane);
+  }
+
+  __syncthreads();
+  tc_fence_after();
+  if (warp == C_MMA_WARP) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+}  // namespace bfk
