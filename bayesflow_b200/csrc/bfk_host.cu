@@ -5,8 +5,6 @@
 #include <stdlib.h>
 
 #include "bfk_sampler.cuh"
-#include "bfk_sampler_fast.cuh"
-#include "bfk_sampler_chase.cuh"
 #include "bfk_sampler_fold.cuh"
 #include "bfk_adaptive.cuh"
 #include "bfk_gemm.cuh"
@@ -53,25 +51,16 @@ static sampler_fn pick_kernel(const bfk_net_config* c, int* threads);
 // Which fused kernel serves the reference's default block shape: the chase schedule (bfk_sampler_chase.cuh, default) or
 // the two-tile ping-pong kernel it replaced (BFK_SAMPLER=fast, kept for A/B timing).  Read once per process: the packed
 // blob and the per-evaluation table are laid out for the kernel that will read them.
-// BFK_SAMPLER: "fold" (default: two-tile ping-pong, folded single-pass epilogue), "chase" (one tile, UMMAs chase the
-// epilogue slab by slab), "fast" (the round-1 two-pass kernel).  fold and chase share the folded weight / table layout.
-static int sampler_variant() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("BFK_SAMPLER");
-    v = (e && strcmp(e, "fast") == 0) ? 0 : (e && strcmp(e, "chase") == 0) ? 1 : 2;
-  }
-  return v;
-}
-static bool use_chase(const bfk_net_config* c) { return is_fast(*c) && sampler_variant() != 0; }  // folded layout
-static bool one_tile(const bfk_net_config* c) { return is_fast(*c) && sampler_variant() == 1; }
+// The reference's default block shape (LayerNorm + residual + FiLM shift) runs on the folded single-pass kernel
+// (bfk_sampler_fold.cuh); bfk_pack and bfk_eval_table lay the weights and the per-evaluation table out for it.
+static bool use_fold(const bfk_net_config* c) { return is_fast(*c) != 0; }
 
 extern "C" int bfk_fused_supported(const bfk_net_config* c) {
   if (check_cfg(c)) return 0;
   if (c->D > BFK_MAX_D) return 0;
   if (c->W > 256 || (c->W % 32) != 0) return 0;
   if (c->precision != BFK_PREC_FP16 && c->precision != BFK_PREC_BF16) return 0;
-  SmemPlan p = one_tile(c) ? make_chase_plan(*c) : use_chase(c) ? make_fold_plan(*c) : make_smem_plan(*c);
+  SmemPlan p = use_fold(c) ? make_fold_plan(*c) : make_smem_plan(*c);
   if (p.n_stage < 2) return 0;
   int threads = 0;
   return pick_kernel(c, &threads) != nullptr;  // configurations without an instantiation take the layer-wise path
@@ -101,23 +90,24 @@ extern "C" int bfk_pack(const bfk_net_config* c, const bfk_weights* w, void* pac
   int g = 0;
   if (L.has_merge) {
     if (!w->m_k || !w->m_b || !w->c_k || !w->c_b) return fail(-12, "conditional net needs c_proj and merge_proj");
-    // x half / whole (add); the chase kernel carries pre-activations times log2(e)
-    pack_gemm_kernel<<<cdiv((size_t)W / 8 * W, 256), 256, 0, st>>>(w->m_k, W, W, bf, (uint16_t*)(P + L.gemm),
-                                                                  use_chase(c) ? 1.4426950408889634f : 1.f);
+    // x half / whole (add); the folded layout carries pre-activations times log2(e) and has XK extra (zero) K rows
+    if (use_fold(c))
+      pack_gemm_kernel<<<cdiv((size_t)W / 8 * W, 256), 256, 0, st>>>(w->m_k, W, W, bf, (uint16_t*)(P + L.gemm_x), 1.4426950408889634f);
+    else
+      pack_gemm_kernel<<<cdiv((size_t)W / 8 * W, 256), 256, 0, st>>>(w->m_k, W, W, bf, (uint16_t*)(P + L.gemm));
     ++g;
   }
-  const bool chase = use_chase(c);
+  const bool chase = use_fold(c);
   float* cv = (float*)(P + L.cvec);
   for (int l = 0; l < c->L; ++l, ++g) {
     if (!w->dense_k[l] || !w->dense_b[l] || !w->film_b_k[l] || !w->film_b_b[l]) return fail(-13, "missing block weights");
     if (chase) {
-      // LayerNorm of block l-1 folded into the Dense kernel of block l (see chase_fold_kernel)
+      // LayerNorm of block l-1 folded into the Dense kernel of block l (see fold_pack_kernel)
       if (!w->norm_g[l] || !w->norm_b[l]) return fail(-15, "LayerNorm weights missing");
-      chase_fold_kernel<<<cdiv(W, 128), 128, 0, st>>>(w->dense_k[l], w->dense_b[l], l ? w->norm_g[l - 1] : nullptr,
-                                                     l ? w->norm_b[l - 1] : nullptr, W, W, bf,
-                                                     (uint16_t*)(P + L.gemm + (size_t)g * W * W * 2),
-                                                     cv + L.cv_blk + (3 * l + 0) * W, cv + L.cv_blk + (3 * l + 1) * W,
-                                                     cv + L.cv_blk + (3 * l + 2) * W);
+      fold_pack_kernel<<<cdiv(W, 128), 128, 0, st>>>(w->dense_k[l], w->dense_b[l], l ? w->norm_g[l - 1] : nullptr,
+                                                    l ? w->norm_b[l - 1] : nullptr, W, W, bf,
+                                                    (uint16_t*)(P + L.gemm_x + (size_t)g * (W + XK) * W * 2),
+                                                    cv + L.cv_blk + (size_t)l * W);
       copy_f32_kernel<<<cdiv(W, 256), 256, 0, st>>>(w->norm_b[l], (float*)(P + L.ln_beta) + (size_t)l * W, W);
     } else {
       pack_gemm_kernel<<<cdiv((size_t)W / 8 * W, 256), 256, 0, st>>>(w->dense_k[l], W, W, bf,
@@ -178,7 +168,7 @@ extern "C" int bfk_cond_prologue(const bfk_net_config* c, const void* packed, co
   const unsigned grid = (unsigned)(G < 148 * 16 ? G : 148 * 16);
   const size_t sh = (size_t)(c->C + c->W) * 4;
   cond_prologue_kernel<<<grid, 256, sh, (cudaStream_t)stream_>>>(*c, (const unsigned char*)packed, L, cond, G, pre_add, post_add,
-                                                                use_chase(c) ? 1.4426950408889634f : 1.f);
+                                                                use_fold(c) ? 1.4426950408889634f : 1.f);
   CK(cudaGetLastError());
   return 0;
 }
@@ -190,7 +180,7 @@ extern "C" int bfk_eval_table(const bfk_net_config* c, const void* packed, const
   const PackedLayout L = make_layout(*c);
   const unsigned grid = (unsigned)(n < 148 * 8 ? n : 148 * 8);
   eval_table_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>(*c, (const unsigned char*)packed, L, *sched, times, n,
-                                                           table_stride(*c), table, use_chase(c) ? 1 : 0);
+                                                           table_stride(*c), table, use_fold(c) ? 1 : 0);
   CK(cudaGetLastError());
   return 0;
 }
@@ -254,7 +244,7 @@ static StageC stage_c(int method) {
 static sampler_fn pick_kernel(const bfk_net_config* c, int* threads) {
   const int dp = dp_of(c->D);
   const bool bf = c->precision == BFK_PREC_BF16;
-  if (use_chase(c) && !one_tile(c)) {
+  if (use_fold(c)) {
     *threads = F_NUM_THREADS;
 #define PICKD(ACT_, DP_, BF_) \
   if (c->activation == ACT_ && dp == DP_ && bf == BF_) return sampler_fold_kernel<ACT_, DP_, BF_>;
@@ -268,39 +258,6 @@ static sampler_fn pick_kernel(const bfk_net_config* c, int* threads) {
     PICKD(BFK_ACT_TANH, 2, false) PICKD(BFK_ACT_TANH, 4, false) PICKD(BFK_ACT_TANH, 8, false)
 #endif
 #undef PICKD
-    return nullptr;
-  }
-  if (one_tile(c)) {
-    *threads = C_NUM_THREADS;
-#define PICKC(ACT_, DP_, BF_) \
-  if (c->activation == ACT_ && dp == DP_ && bf == BF_) return sampler_chase_kernel<ACT_, DP_, BF_>;
-    PICKC(BFK_ACT_MISH, 2, false)
-#ifndef BFK_DEV_BUILD
-    PICKC(BFK_ACT_MISH, 4, false) PICKC(BFK_ACT_MISH, 8, false)
-    PICKC(BFK_ACT_MISH, 2, true) PICKC(BFK_ACT_MISH, 4, true) PICKC(BFK_ACT_MISH, 8, true)
-    PICKC(BFK_ACT_SILU, 2, false) PICKC(BFK_ACT_SILU, 4, false) PICKC(BFK_ACT_SILU, 8, false)
-    PICKC(BFK_ACT_RELU, 2, false) PICKC(BFK_ACT_RELU, 4, false) PICKC(BFK_ACT_RELU, 8, false)
-    PICKC(BFK_ACT_GELU, 2, false) PICKC(BFK_ACT_GELU, 4, false) PICKC(BFK_ACT_GELU, 8, false)
-    PICKC(BFK_ACT_TANH, 2, false) PICKC(BFK_ACT_TANH, 4, false) PICKC(BFK_ACT_TANH, 8, false)
-#endif
-#undef PICKC
-    return nullptr;
-  }
-  if (is_fast(*c)) {
-    // the reference's default block shape: 18-warp packed-f32x2 kernel
-    *threads = F_NUM_THREADS;
-#define PICKF(ACT_, DP_, BF_) \
-  if (c->activation == ACT_ && dp == DP_ && bf == BF_) return sampler_fast_kernel<ACT_, DP_, BF_>;
-    PICKF(BFK_ACT_MISH, 2, false)
-#ifndef BFK_DEV_BUILD
-    PICKF(BFK_ACT_MISH, 4, false) PICKF(BFK_ACT_MISH, 8, false)
-    PICKF(BFK_ACT_MISH, 2, true) PICKF(BFK_ACT_MISH, 4, true)
-    PICKF(BFK_ACT_SILU, 2, false) PICKF(BFK_ACT_SILU, 4, false) PICKF(BFK_ACT_SILU, 8, false)
-    PICKF(BFK_ACT_RELU, 2, false) PICKF(BFK_ACT_RELU, 4, false)
-    PICKF(BFK_ACT_GELU, 2, false) PICKF(BFK_ACT_GELU, 4, false)
-    PICKF(BFK_ACT_TANH, 2, false) PICKF(BFK_ACT_TANH, 4, false)
-#endif
-#undef PICKF
     return nullptr;
   }
   // non-default options (norm None/rms, no residual, FiLM gamma): generic 10-warp kernel
@@ -352,8 +309,8 @@ static int launch_sampler(const bfk_net_config* c, const void* packed, const flo
   a.tstride = table_stride(*c); a.cvec_floats = L.cvec_floats;
   a.cv_wx = L.cv_wx; a.cv_bx = L.cv_bx; a.cv_blk = L.cv_blk; a.cv_wo = L.cv_wo; a.cv_bo = L.cv_bo;
   a.idesc = umma_idesc_f16(TILE_M, c->W, c->precision == BFK_PREC_BF16 ? 1 : 0);
-  const bool chase = one_tile(c);
-  a.plan = chase ? make_chase_plan(*c) : use_chase(c) ? make_fold_plan(*c) : make_smem_plan(*c);
+  a.plan = use_fold(c) ? make_fold_plan(*c) : make_smem_plan(*c);
+  if (use_fold(c)) a.wg = (const unsigned char*)packed + L.gemm_x;
   a.err_flag = nullptr;
   { const char* e = getenv("BFK_DEBUG"); a.dbg = e ? atoi(e) : 0; }
   fill_tableau(method, a);
@@ -364,7 +321,7 @@ static int launch_sampler(const bfk_net_config* c, const void* packed, const flo
   CK(cudaGetDevice(&dev));
   CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   CK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a.plan.total));
-  const long long rows_per_cta = chase ? TILE_M : TILES_PER_CTA * TILE_M;  // chase: one tile per CTA
+  const long long rows_per_cta = TILES_PER_CTA * TILE_M;
   const long long n_pairs = (B + rows_per_cta - 1) / rows_per_cta;
   const unsigned grid = (unsigned)(n_pairs < sms ? n_pairs : sms);
   fn<<<grid, threads, a.plan.total, st>>>(a);

@@ -10,6 +10,9 @@ namespace bfk {
 constexpr int TILE_M = 128;       // rows (draws) per tile = UMMA M = TMEM lanes
 constexpr int TILES_PER_CTA = 2;  // two tiles ping-pong through TMEM
 constexpr int KC = 32;            // K rows of a weight stage (2 UMMAs of K=16)
+constexpr int XK = 16;            // folded layout: extra K rows per layer (one more UMMA): -g, c as fp16 hi/lo pairs
+constexpr int FKC = 32;           // folded kernel: K rows of a full weight stage (16-row stages, 6 of them, measured slower:
+                                  // the issuer pays one mbarrier wait per stage); the XK tail is one more, half-filled stage
 constexpr int EPI_WARPS = 8, MMA_WARP = 8, LOAD_WARP = 9, NUM_THREADS = 320;
 // fast kernel: 16 epilogue warps (tile = (w>>2)&1, TMEM lane quarter = w&3, column half = w>>3) + issuer + producer
 constexpr int F_EPI_WARPS = 16, F_MMA_WARP = 16, F_LOAD_WARP = 17, F_NUM_THREADS = 576;
@@ -37,7 +40,8 @@ struct PackedLayout {
   size_t film_g_k, film_g_b;  // same, only if film_use_gamma
   size_t c_k, c_b;            // [C][W], [W]
   size_t m_c, m_b;            // conditions half of merge_proj [W][W] (concat only), [W]
-  size_t ln_beta;             // [L][W] LayerNorm beta of every block (chase layout: folded into the per-evaluation table)
+  size_t ln_beta;             // [L][W] LayerNorm beta of every block (folded layout: goes into the per-evaluation table)
+  size_t gemm_x;              // folded layout: [NG][(W+XK)/8][W][8] 16-bit, XK extra K rows per layer (rank-1 + bias terms)
   size_t total;
 };
 
@@ -53,7 +57,7 @@ __host__ __device__ inline PackedLayout make_layout(const bfk_net_config& c) {
   L.cv_wx = 0;
   L.cv_bx = L.cv_wx + L.DP * c.W;
   L.cv_blk = L.cv_bx + c.W;
-  L.cv_wo = L.cv_blk + 3 * c.L * c.W;
+  L.cv_wo = L.cv_blk + (is_fast(c) ? 1 : 3) * c.L * c.W;  // folded layout: only gamma_{l-1} per block
   L.cv_bo = L.cv_wo + c.W * L.DP;
   L.cvec_floats = L.cv_bo + 2 * L.DP;
   L.cvec = off; off += (size_t)L.cvec_floats * 4; off = align_up(off, 256);
@@ -67,6 +71,8 @@ __host__ __device__ inline PackedLayout make_layout(const bfk_net_config& c) {
   L.m_c = off; off += W * W * 4;
   L.m_b = off; off += W * 4;
   L.ln_beta = off; off += (size_t)c.L * W * 4;
+  off = align_up(off, 256);
+  L.gemm_x = off; off += (size_t)L.NG * (W + XK) * W * 2;
   L.total = align_up(off, 256);
   return L;
 }
@@ -104,37 +110,12 @@ __host__ __device__ inline SmemPlan make_smem_plan(const bfk_net_config& c) {
   return p;
 }
 
-// "chase" schedule (bfk_sampler_chase.cuh): ONE tile per CTA, double-buffered accumulator, slab barriers; the ring takes
-// what is left (up to 8 stages: more than one whole layer at W = 256).
-__host__ __device__ inline SmemPlan make_chase_plan(const bfk_net_config& c) {
-  SmemPlan p{};
-  PackedLayout L = make_layout(c);
-  p.a_bytes = TILE_M * c.W * 2;
-  p.stage_bytes = KC * c.W * 2;
-  p.film_bytes = (uint32_t)align_up((size_t)table_stride(c) * 4, 16);
-  uint32_t off = 0;
-  p.a_tile = off; off += p.a_bytes;
-  p.film = off; off += 2 * p.film_bytes;
-  p.cvec = off; off += (uint32_t)align_up((size_t)L.cvec_floats * 4, 16);
-  p.bars = off; off += 256;
-  p.xch = off;
-  p.xch_stride = 2;
-  off += 2 * 4 * TILE_M * 8;       // [2][4 column groups][TILE_M] (row sum, sum of squares)
-  off += 4 * TILE_M * L.DP * 4;    // [4][TILE_M][DP] output-projector partials
-  p.ring = (uint32_t)align_up(off, 128);
-  int n = (int)((SMEM_LIMIT - p.ring) / p.stage_bytes);
-  if (n > 8) n = 8;
-  p.n_stage = n;
-  p.total = p.ring + (n > 0 ? n : 0) * p.stage_bytes;
-  return p;
-}
-
 // two-tile ping-pong schedule with the folded single-pass epilogue (bfk_sampler_fold.cuh)
 __host__ __device__ inline SmemPlan make_fold_plan(const bfk_net_config& c) {
   SmemPlan p{};
   PackedLayout L = make_layout(c);
-  p.a_bytes = TILE_M * c.W * 2;
-  p.stage_bytes = KC * c.W * 2;
+  p.a_bytes = TILE_M * (c.W + XK) * 2;  // K-chunks W/8, W/8+1 of each tile: per-row (mu, 1/r) as fp16 hi/lo pairs
+  p.stage_bytes = FKC * c.W * 2;
   p.film_bytes = (uint32_t)align_up((size_t)table_stride(c) * 4, 16);
   uint32_t off = 0;
   p.a_tile = off; off += TILES_PER_CTA * p.a_bytes;

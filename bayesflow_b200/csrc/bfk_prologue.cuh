@@ -98,44 +98,51 @@ __global__ void fold_proj_kernel(const float* __restrict__ out_k, const float* _
   s0s1[DP + d] = (float)a1;
 }
 
-// Chase layout (bfk_sampler_chase.cuh): the Dense kernel of block l >= 1 consumes the UN-normalised output v of block l-1,
-// so LayerNorm's affine moves into the weights:  W' = gamma_prev o W (rows scaled, then rounded to the operand type),
-// g_j = sum_k W'_kj (of the ROUNDED values: exactly what the tensor core multiplies mu by), c_j = b_j + sum_k beta_prev_k W_kj.
+// Folded layout (bfk_sampler_fold.cuh): the Dense kernel of block l >= 1 consumes the UN-normalised output v of block
+// l-1, so LayerNorm's affine moves into the weights: W' = gamma_prev o W (rows scaled, then rounded to the operand type).
+// With (mu, r) the row statistics of v:  log2(e) (LN(v) W + b) = log2(e) r [ v W' - mu g + (1 / (log2(e) r)) cL ],
+// g_j = sum_k W'_kj (of the ROUNDED values: exactly what the tensor core multiplies v by), cL_j = log2(e) (b_j +
+// sum_k beta_prev_k W_kj).  The bracket is ONE accumulation: XK extra K rows carry -g and cL as 16-bit hi/lo pairs
+// against per-row A entries (mu_hi, mu_lo, mu_hi, ir_hi, ir_lo, ir_hi), ir = 1 / (log2(e) r), written by the epilogue:
+//   rows K+0..2 = (-g_hi, -g_hi, -g_lo)   rows K+3..5 = (cL_hi, cL_hi, cL_lo)   rest 0
 // One thread per output column.  gamma_prev == nullptr (block 0): plain pack, g = 0, gamma image = 1.
-__global__ void chase_fold_kernel(const float* __restrict__ Wk, const float* __restrict__ bd, const float* __restrict__ gamma_prev,
-                                  const float* __restrict__ beta_prev, int K, int N, int bf16, uint16_t* __restrict__ dst,
-                                  float* __restrict__ c_out, float* __restrict__ g_out, float* __restrict__ gam_out) {
+__device__ __forceinline__ uint16_t round16(float x, int bf16, float* back) {
+  if (bf16) {
+    __nv_bfloat16 b = __float2bfloat16_rn(x);
+    *back = __bfloat162float(b);
+    return *reinterpret_cast<uint16_t*>(&b);
+  }
+  __half b = __float2half_rn(x);
+  *back = __half2float(b);
+  return *reinterpret_cast<uint16_t*>(&b);
+}
+__global__ void fold_pack_kernel(const float* __restrict__ Wk, const float* __restrict__ bd, const float* __restrict__ gamma_prev,
+                                 const float* __restrict__ beta_prev, int K, int N, int bf16, uint16_t* __restrict__ dst,
+                                 float* __restrict__ gam_out) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   float g = 0.f;
   double cacc = 0.0;
   for (int k = 0; k < K; ++k) {
     const float w = Wk[(size_t)k * N + n];
-    const float s = gamma_prev ? gamma_prev[k] * w : w;
-    uint16_t h;
     float back;
-    if (bf16) {
-      __nv_bfloat16 b = __float2bfloat16_rn(s);
-      h = *reinterpret_cast<uint16_t*>(&b);
-      back = __bfloat162float(b);
-    } else {
-      __half b = __float2half_rn(s);
-      h = *reinterpret_cast<uint16_t*>(&b);
-      back = __half2float(b);
-    }
+    const uint16_t h = round16(gamma_prev ? gamma_prev[k] * w : w, bf16, &back);
     dst[((size_t)(k >> 3) * N + n) * 8 + (k & 7)] = h;
     g += back;
     if (beta_prev) cacc += (double)beta_prev[k] * (double)w;
   }
-  c_out[n] = (bd[n] + (float)cacc) * 1.4426950408889634f;  // pre-activations are carried times log2(e) (chase kernel)
-  g_out[n] = gamma_prev ? g : 0.f;
+  const float cL = (bd[n] + (float)cacc) * 1.4426950408889634f;
+  const float gg = gamma_prev ? -g : 0.f;
+  float g_hi, g_lo, c_hi, c_lo;
+  const uint16_t gh = round16(gg, bf16, &g_hi), gl = round16(gg - g_hi, bf16, &g_lo);
+  const uint16_t ch = round16(cL, bf16, &c_hi), cl = round16(cL - c_hi, bf16, &c_lo);
+  const uint16_t x[6] = {gh, gh, gl, ch, ch, cl};
+  uint16_t* e = dst + ((size_t)(K >> 3) * N + n) * 8;  // K-chunk K/8 of this column (K-chunk K/8+1 stays zero)
+  for (int i = 0; i < 6; ++i) e[i] = x[i];
   gam_out[n] = gamma_prev ? gamma_prev[n] : 1.f;
 }
 
-// conditions (G,C) -> pre_add (G,W), post_add (G,W)   [time_mlp.py:133-139 hoisted; SURVEY §7.3-2]
-//   concat: post = bm + act(c Wc + bc) Wm[W:2W,:],  pre = (unused)
-//   add   : pre  = c Wc + bc,                         post = bm
-// out_scale: 1, or log2(e) for the chase kernel, whose pre-activations are carried times log2(e)
+// out_scale: 1, or log2(e) for the folded layout, whose pre-activations are carried times log2(e)
 __global__ void cond_prologue_kernel(bfk_net_config cfg, const unsigned char* __restrict__ packed, PackedLayout L,
                                      const float* __restrict__ cond, long long G, float* __restrict__ pre_add,
                                      float* __restrict__ post_add, float out_scale) {
@@ -230,7 +237,7 @@ __host__ __device__ inline void schedule_coefs(const bfk_schedule& s, double t, 
 }
 
 // times (n) -> table (n, stride): [L][W] FiLM beta, ([L][W] FiLM gamma), TABLE_SCALARS scalars
-// chase != 0: the FiLM shift of block l >= 1 also carries LayerNorm beta of block l-1 (bfk_sampler_chase.cuh)
+// chase != 0 (folded layout): the FiLM shift of block l >= 1 also carries LayerNorm beta of block l-1 (bfk_sampler_fold.cuh)
 __global__ void eval_table_kernel(bfk_net_config cfg, const unsigned char* __restrict__ packed, PackedLayout L,
                                   bfk_schedule sched, const float* __restrict__ times, long long n, int stride,
                                   float* __restrict__ table, int chase) {

@@ -1,18 +1,242 @@
-// The fused on-chip sampler, two-tile ping-pong schedule with the SINGLE-PASS folded-LayerNorm epilogue, for the
-// reference's default block shape (LayerNorm + residual + FiLM shift, networks/defaults.py:13-26).
+// The fused on-chip sampler for the reference's default block shape (LayerNorm + residual + FiLM shift,
+// networks/defaults.py:13-26; time_mlp.py:125-147, conditional_dense_block.py:114-131): two 128-draw tiles per
+// persistent CTA ping-pong through 2 x W TMEM columns (while one tile is in its epilogue the tensor pipe runs the other
+// tile's layer), and every epilogue is ONE pass over the accumulator.
 //
-// Protocol, UMMA issuer and bulk-copy producer are bfk_sampler.cuh's (one persistent CTA per SM, two 128-draw tiles
-// ping-ponging through 2 x W TMEM columns: while one tile is in its epilogue the tensor pipe runs the other tile's
-// layer, and the two tiles' epilogues are out of phase, so their MUFU and FMA sections interleave).  The epilogue is
-// bfk_sampler_chase.cuh's: LayerNorm folded into the consuming Dense kernel (bfk_pack: gamma o W, g, c), activations
-// carried times log2(e), one pass over the accumulator that writes the next A operand as the raw fp16 image of v.
-//
-// Warp roles (576 threads): w in 0..15 epilogue (tile = (w>>2)&1, TMEM lane quarter = w&3, column half = w>>3),
-// warp 16 UMMA issuer + TMEM owner, warp 17 bulk-copy producer.
+// Protocol as in bfk_sampler.cuh (16 epilogue warps: tile = (w>>2)&1, TMEM lane quarter = w&3, column half = w>>3; warp
+// 16 UMMA issuer + TMEM owner; warp 17 bulk-copy producer).  What makes the single pass possible is that LayerNorm is
+// folded into its consumer.  With v the un-normalised output of a block and (mu, r) its row statistics,
+//     log2(e) (LN(v) W + b) = log2(e) r [ v (gamma o W) - mu g + cL / (log2(e) r) ]
+// (g_j = sum_k fp16(gamma_k W_kj), cL = log2(e) (b + beta W): bfk_pack / fold_pack_kernel), and the whole bracket is
+// accumulated by the tensor core: the A operand is the raw fp16 image of v plus XK = 16 extra K columns per row holding
+// (mu, 1/(log2(e) r)) as fp16 hi/lo pairs, against XK extra weight rows holding -g and cL (one more UMMA per layer).
+// Per block and element the epilogue is then
+//     t  = (log2(e) r) * acc                                   pre-activation times log2(e)
+//     v' = t * actw(t) + [gamma (v r - r mu) + (beta + film(t))]      act(u) = t * actw(t); skip h = LN(v) rebuilt from
+//                                                                     the same fp16 image; beta rides in the FiLM table
+//     row sum / sum of squares of v' in fp32; fp16(v') -> A tile
+// with only two per-column vectors (gamma, beta + film) read from shared memory per element instead of four, no
+// second pass over TMEM, and no multiply in front of ex2.
 #pragma once
-#include "bfk_sampler_chase.cuh"
+#include "bfk_fast_epilogue.cuh"
+#include "bfk_sampler.cuh"
+
+// -DBFK_PROFILE: per-warp cycle accounting into a device buffer (read with bfk_debug_read_prof); compiled out otherwise
+#ifdef BFK_PROFILE
+__device__ long long g_bfk_prof[148 * 18 * 8];
+#define PROF_DECL long long pf_[8] = {0, 0, 0, 0, 0, 0, 0, 0}; long long pt_ = clock64();
+#define PROF_ADD(slot) { const long long n_ = clock64(); pf_[slot] += n_ - pt_; pt_ = n_; }
+#define PROF_FLUSH(warp) if ((threadIdx.x & 31) == 0) { for (int i_ = 0; i_ < 8; ++i_) g_bfk_prof[(blockIdx.x * 18 + (warp)) * 8 + i_] = pf_[i_]; }
+#else
+#define PROF_DECL
+#define PROF_ADD(slot)
+#define PROF_FLUSH(warp)
+#endif
 
 namespace bfk {
+
+// Pre-activations are carried times log2(e) (bfk_pack scales the weights / biases): with t = x log2(e),
+// act(x) = t * actw(t), actw(t) = ln2 * tanh(softplus(x)) = ln2 - 2 ln2 / ((1 + 2^t)^2 + 1) for mish, ln2 / (1 + 2^-t) for
+// silu: the multiply by log2(e) in front of ex2 disappears.  All MUFU of the chunk issued back to back.
+template <int ACT>
+__device__ __forceinline__ void actw2x8(const float2* t, float2* w) {
+  if (ACT == BFK_ACT_MISH) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { w[i].x = ex2_approx(t[i].x); w[i].y = ex2_approx(t[i].y); }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float2 q = __fadd2_rn(w[i], f2(1.f));
+      w[i] = __ffma2_rn(q, q, f2(1.f));
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { w[i].x = rcp_approx(w[i].x); w[i].y = rcp_approx(w[i].y); }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] = __ffma2_rn(w[i], f2(-1.3862943611198906f), f2(0.6931471805599453f));
+  } else {  // silu
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { w[i].x = ex2_approx(-t[i].x); w[i].y = ex2_approx(-t[i].y); }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] = __fadd2_rn(w[i], f2(1.f));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { w[i].x = rcp_approx(w[i].x); w[i].y = rcp_approx(w[i].y); }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] = __fmul2_rn(w[i], f2(0.6931471805599453f));
+  }
+}
+// t (pre-activation times log2(e)) -> act(x), 16 values
+template <int ACT>
+__device__ __forceinline__ void act_scaled2x8(float2* t) {
+  if (ACT == BFK_ACT_MISH || ACT == BFK_ACT_SILU) {
+    float2 w[8];
+    actw2x8<ACT>(t, w);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t[i] = __fmul2_rn(t[i], w[i]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      t[i] = make_float2(act_fn<ACT>(t[i].x * 0.6931471805599453f), act_fn<ACT>(t[i].y * 0.6931471805599453f));
+  }
+}
+
+__device__ __forceinline__ void ld4x2(const float* p, float2* o) {  // 8 floats -> 4 float2
+#if (BFK_EXP & 32)
+  o[0] = o[1] = o[2] = o[3] = make_float2(0.001f, 0.002f);  // experiment: no shared-memory vector loads
+  return;
+#endif
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  o[0] = make_float2(a.x, a.y); o[1] = make_float2(a.z, a.w); o[2] = make_float2(b.x, b.y); o[3] = make_float2(b.z, b.w);
+}
+
+template <bool BF16>
+__device__ __forceinline__ void store_chunk16(const float2* v, int col, unsigned char* sA_row) {
+#pragma unroll
+  for (int jj = 0; jj < 2; ++jj)
+    *reinterpret_cast<uint4*>(sA_row + (size_t)((col >> 3) + jj) * (TILE_M * 16)) =
+        make_uint4(pack2f<BF16>(v[jj * 4 + 0]), pack2f<BF16>(v[jj * 4 + 1]), pack2f<BF16>(v[jj * 4 + 2]),
+                   pack2f<BF16>(v[jj * 4 + 3]));
+}
+
+// One 16-column chunk of a ConditionalDenseBlock epilogue in the folded form (see the header).  v: 8 float2 accumulators
+// in, block output v' out.  rs = r, nm = -r*mu of the INPUT rows (1, 0 for the first block); rsL = log2(e) r.
+template <int ACT, bool BF16>
+__device__ __forceinline__ void fold_block_chunk(float2* v, int col, float2 rs, float2 nm, float2 rsL,
+                                                 const float* __restrict__ gam, const float* __restrict__ fbeta,
+                                                 const unsigned char* sA_row, float2* sum2, float2* sq2) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __fmul2_rn(v[i], rsL);
+  float2 w[8];  // v = t = u log2(e);  act(u) = t * w
+  if (ACT == BFK_ACT_MISH || ACT == BFK_ACT_SILU) {
+    actw2x8<ACT>(v, w);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      v[i] = make_float2(act_fn<ACT>(v[i].x * 0.6931471805599453f), act_fn<ACT>(v[i].y * 0.6931471805599453f));
+      w[i] = f2(1.f);
+    }
+  }
+#pragma unroll
+  for (int jj = 0; jj < 2; ++jj) {  // 8 columns = one 16-byte K chunk of the A tile
+    const uint4 sk = *reinterpret_cast<const uint4*>(sA_row + (size_t)((col >> 3) + jj) * (TILE_M * 16));
+    const uint32_t su[4] = {sk.x, sk.y, sk.z, sk.w};
+    float2 ga[4], fb[4];
+    ld4x2(gam + col + jj * 8, ga);
+    ld4x2(fbeta + col + jj * 8, fb);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      const int i = jj * 4 + p;
+      const float2 xh = __ffma2_rn(unpack2f<BF16>(su[p]), rs, nm);
+      const float2 h = __ffma2_rn(xh, ga[p], fb[p]);
+      const float2 u = __ffma2_rn(v[i], w[i], h);
+      sum2[p] = __fadd2_rn(sum2[p], u);
+      sq2[p] = __ffma2_rn(u, u, sq2[p]);
+      v[i] = u;
+    }
+  }
+}
+
+// per-row extra K entries of the A tile: (mu_hi, mu_lo, mu_hi, ir_hi, ir_lo, ir_hi, 0, 0), ir = 1 / (log2(e) r)
+template <bool BF16>
+__device__ __forceinline__ uint4 fold_extras(float mu, float ir) {
+  float mh, ih, dummy;
+  uint32_t m_hi, m_lo, i_hi, i_lo;
+  if (BF16) {
+    __nv_bfloat16 a = __float2bfloat16_rn(mu); mh = __bfloat162float(a); __nv_bfloat16 b = __float2bfloat16_rn(mu - mh);
+    __nv_bfloat16 c = __float2bfloat16_rn(ir); ih = __bfloat162float(c); __nv_bfloat16 d = __float2bfloat16_rn(ir - ih);
+    m_hi = *reinterpret_cast<uint16_t*>(&a); m_lo = *reinterpret_cast<uint16_t*>(&b);
+    i_hi = *reinterpret_cast<uint16_t*>(&c); i_lo = *reinterpret_cast<uint16_t*>(&d);
+  } else {
+    __half a = __float2half_rn(mu); mh = __half2float(a); __half b = __float2half_rn(mu - mh);
+    __half c = __float2half_rn(ir); ih = __half2float(c); __half d = __float2half_rn(ir - ih);
+    m_hi = *reinterpret_cast<uint16_t*>(&a); m_lo = *reinterpret_cast<uint16_t*>(&b);
+    i_hi = *reinterpret_cast<uint16_t*>(&c); i_lo = *reinterpret_cast<uint16_t*>(&d);
+  }
+  (void)dummy;
+  return make_uint4(m_hi | (m_lo << 16), m_hi | (i_hi << 16), i_lo | (i_hi << 16), 0u);
+}
+
+// UMMA issuer: for every evaluation and GEMM layer, for each of the two tiles, wait for the tile's A operand, stream the
+// W / FKC weight stages + the XK-row tail stage through the ring, commit to acc_ready.
+__device__ __forceinline__ void fold_issuer_loop(const SamplerArgs& a, const Bars& bars, uint32_t smem_base,
+                                                 uint32_t tmem_base, long long n_pairs, long long n_evals, int lane) {
+  const int W = a.W;
+  const int n_chunks = W / FKC;
+  if (lane == 0) {
+    uint32_t ph_a[2] = {0, 0};
+    uint32_t ph_full = 0;  // bit s = parity of stage s
+    int stage = 0;
+    const uint32_t a_lbo = TILE_M * 16, b_lbo = (uint32_t)W * 16;
+    for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+      for (long long e = 0; e < n_evals; ++e) {
+        for (int g = 0; g < a.NG; ++g) {
+          for (int t = 0; t < TILES_PER_CTA; ++t) {
+            mbar_wait(bars.a_ready(t), ph_a[t], a.err_flag, 3);
+            ph_a[t] ^= 1;
+            tc_fence_after();
+            const uint32_t a_base = smem_base + a.plan.a_tile + t * a.plan.a_bytes;
+            const uint32_t d_tmem = tmem_base + t * W;
+            for (int c = 0; c <= n_chunks; ++c) {
+              mbar_wait(bars.w_full(stage), (ph_full >> stage) & 1, a.err_flag, 4);
+              ph_full ^= (1u << stage);
+              tc_fence_after();
+              const uint32_t b_base = smem_base + a.plan.ring + stage * a.plan.stage_bytes;
+              const int nk = (c < n_chunks) ? FKC / 16 : XK / 16;
+              for (int kk = 0; kk < nk; ++kk) {
+                const uint64_t ad = umma_smem_desc(a_base + (uint32_t)(c * (FKC / 8) + kk * 2) * a_lbo, a_lbo, 128);
+                const uint64_t bd = umma_smem_desc(b_base + (uint32_t)(kk * 2) * b_lbo, b_lbo, 128);
+                umma_f16(d_tmem, ad, bd, a.idesc, (uint32_t)((c | kk) != 0));
+              }
+              umma_commit(bars.w_empty(stage));
+              stage = (stage + 1 == a.plan.n_stage) ? 0 : stage + 1;
+            }
+            umma_commit(bars.acc_ready(t));
+          }
+        }
+      }
+    }
+  }
+  __syncwarp();
+}
+
+// Bulk-copy producer: per tile and layer W / FKC full stages + the XK-row tail (the layer is one contiguous byte range)
+__device__ __forceinline__ void fold_producer_loop(const SamplerArgs& a, const Bars& bars, uint32_t smem_base,
+                                                   long long n_pairs, long long n_evals, int lane) {
+  const int W = a.W;
+  const int n_chunks = W / FKC;
+  if (lane == 0) {
+    uint32_t ph_empty = 0;
+    int stage = 0;
+    long long q = 0, q_film = 0;
+    long long my_pairs = 0;
+    for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) ++my_pairs;
+    const long long Q = my_pairs * n_evals;
+    const size_t layer_bytes = (size_t)(W + XK) * W * 2;
+    auto load_film = [&](long long qq) {
+      const int fb = (int)(qq & 1);
+      mbar_wait(bars.film_empty(fb), (uint32_t)(((qq >> 1) & 1) ^ 1), a.err_flag, 5);
+      mbar_arrive_expect_tx(bars.film_full(fb), (uint32_t)a.tstride * 4);
+      bulk_g2s(smem_base + a.plan.film + fb * a.plan.film_bytes, a.table + (qq % n_evals) * a.tstride,
+               (uint32_t)a.tstride * 4, bars.film_full(fb));
+    };
+    if (Q > 0) { load_film(0); q_film = 1; }
+    for (; q < Q; ++q) {
+      for (int g = 0; g < a.NG; ++g) {
+        for (int t = 0; t < TILES_PER_CTA; ++t) {
+          for (int c = 0; c <= n_chunks; ++c) {
+            mbar_wait(bars.w_empty(stage), ((ph_empty >> stage) & 1) ^ 1, a.err_flag, 6);
+            ph_empty ^= (1u << stage);
+            const uint32_t bytes = (c < n_chunks) ? a.plan.stage_bytes : (uint32_t)(XK * W * 2);
+            mbar_arrive_expect_tx(bars.w_full(stage), bytes);
+            bulk_g2s(smem_base + a.plan.ring + stage * a.plan.stage_bytes,
+                     a.wg + (size_t)g * layer_bytes + (size_t)c * FKC * W * 2, bytes, bars.w_full(stage));
+            stage = (stage + 1 == a.plan.n_stage) ? 0 : stage + 1;
+          }
+        }
+        if (g == 0 && q_film < Q && q_film == q + 1) { load_film(q_film); ++q_film; }
+      }
+    }
+  }
+  __syncwarp();
+}
 
 template <int ACT, int DP, bool BF16>
 __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const SamplerArgs a) {
@@ -61,13 +285,15 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
     float* xpr = reinterpret_cast<float*>(smem + a.plan.xch + 2 * 2 * 2 * TILE_M * 8);
     const float* c_wx = s_cvec + a.cv_wx;
     const float* c_bx = s_cvec + a.cv_bx;
-    const float* c_blk = s_cvec + a.cv_blk;  // per block: c_l, g_l, gamma_{l-1}
+    const float* c_blk = s_cvec + a.cv_blk;  // per block: gamma_{l-1}
     const float* c_wo = s_cvec + a.cv_wo;    // [DP][W] gamma_L * Wo
     const float* c_bo = s_cvec + a.cv_bo;    // s0[DP], s1[DP]
     const float inv_w = 1.f / (float)W;
     PROF_DECL
     uint32_t ph_acc = 0;
     long long nb = 0;  // running block-epilogue counter (stats exchange buffer)
+    unsigned char* sX = sA + (size_t)(W >> 3) * (TILE_M * 16);  // my row's extra K entries (K-chunks W/8, W/8+1)
+    if (half == 0) *reinterpret_cast<uint4*>(sX + TILE_M * 16) = make_uint4(0u, 0u, 0u, 0u);
     long long q = 0;   // evaluation sequence number of this CTA (film double buffer)
 
     for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
@@ -147,6 +373,8 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
               act_scaled2x8<ACT>(v8);
               store_chunk16<BF16>(v8, col, sA);
             }
+            // the operand of the first GEMMs is not normalised: mu = 0, 1/(log2(e) r) = ln 2
+            if (half == 0) *reinterpret_cast<uint4*>(sX) = fold_extras<BF16>(0.f, 0.6931471805599453f);
           }
           PROF_ADD(2)
           fence_proxy_async_smem();
@@ -156,33 +384,14 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
           PROF_ADD(7)
 
           float pred[DP];
-          // row scale / shift of the current A image (identity before block 1); *L = times log2(e)
-          float2 rs = f2(1.f), nm = f2(0.f), rsL = f2(1.4426950408889634f), nmL = f2(0.f);
-          bool stats_pending = false;
-          auto read_stats = [&]() {
-            named_bar_sync(bar_id, 64);  // my column-half partner wrote its partial sums before arriving here
-            const float2* xb2 = xst + ((size_t)(nb & 1) * 4 + tile * 2) * TILE_M;
-            const float2 p0 = xb2[r], p1 = xb2[TILE_M + r];
-            const float mean = (p0.x + p1.x) * inv_w;  // identical expression in both halves
-            const float var = fmaxf((p0.y + p1.y) * inv_w - mean * mean, 0.f);
-            const float rstd = rsqrtf(var + 1e-3f);  // keras LayerNormalization epsilon
-            rs = f2(rstd);
-            nm = f2(-mean * rstd);
-            rsL = f2(rstd * 1.4426950408889634f);
-            nmL = f2(-mean * rstd * 1.4426950408889634f);
-            ++nb;
-            stats_pending = false;
-          };
+          // row scale / shift of the current A image (identity before block 1); rsL = log2(e) r
+          float2 rs = f2(1.f), nm = f2(0.f), rsL = f2(1.4426950408889634f);
           for (int g = 0; g < a.NG; ++g) {
             mbar_wait(bars.acc_ready(tile), ph_acc, a.err_flag, 2);
             PROF_ADD(3)
             ph_acc ^= 1;
             tc_fence_after();
-            if (stats_pending) read_stats();
             PROF_ADD(6)
-#ifdef BFK_STAGGER_NS
-            if (half) __nanosleep(BFK_STAGGER_NS);  // experiment: de-phase the two column halves of a tile
-#endif
             const bool last = (g == a.NG - 1);
             float2 va[8], vb[8];
             if (a.has_merge && g == 0) {
@@ -216,9 +425,7 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
             } else {
               // ---- ConditionalDenseBlock epilogue, folded LayerNorm, single pass     conditional_dense_block.py:114-131
               const int l = g - a.has_merge;
-              const float* cl = c_blk + (3 * l + 0) * W;
-              const float* gl = c_blk + (3 * l + 1) * W;
-              const float* gam = c_blk + (3 * l + 2) * W;
+              const float* gam = c_blk + l * W;
               const float* fbeta = s_film + l * W;
               float2 sum2[4], sq2[4], pa[DP];
 #pragma unroll
@@ -227,7 +434,7 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
               for (int d = 0; d < DP; ++d) pa[d] = f2(0.f);
               auto blk = [&](float2* v, int ch) {
                 const int col = ch * 16;
-                chase_block_chunk<ACT, BF16>(v, col, rs, nm, rsL, nmL, cl, gl, gam, fbeta, sA, sum2, sq2);
+                fold_block_chunk<ACT, BF16>(v, col, rs, nm, rsL, gam, fbeta, sA, sum2, sq2);
                 if (last) {
 #pragma unroll
                   for (int d = 0; d < DP; ++d) {
@@ -255,25 +462,38 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
                   blk(vb, ch0 + c + 1);
                 }
               }
-              // ---- row statistics of v': my half's partial sums; the exchange completes at the next epilogue's start
+              // ---- row statistics of v': my half's partial sums + the other half's (shared memory, 64-thread barrier)
               const float2 s01 = __fadd2_rn(__fadd2_rn(sum2[0], sum2[1]), __fadd2_rn(sum2[2], sum2[3]));
               const float2 q01 = __fadd2_rn(__fadd2_rn(sq2[0], sq2[1]), __fadd2_rn(sq2[2], sq2[3]));
-              xst[((size_t)(nb & 1) * 4 + tile * 2 + half) * TILE_M + r] = make_float2(s01.x + s01.y, q01.x + q01.y);
-              stats_pending = true;
-              PROF_ADD(5)
+              float2* xb2 = xst + ((size_t)(nb & 1) * 4 + tile * 2) * TILE_M;
+              xb2[(size_t)half * TILE_M + r] = make_float2(s01.x + s01.y, q01.x + q01.y);
+              float* xp = xpr + (size_t)(tile * 2) * TILE_M * DP;
               if (last) {
-                // output projector folded through the LayerNorm affine (flow_matching.py:229-230): needs every column now
-                float* xp = xpr + (size_t)(tile * 2) * TILE_M * DP;
 #pragma unroll
                 for (int d = 0; d < DP; ++d) xp[((size_t)half * TILE_M + r) * DP + d] = pa[d].x + pa[d].y;
-                read_stats();
+              }
+              PROF_ADD(5)
+              named_bar_sync(bar_id, 64);
+              ++nb;
+              const float2 p0 = xb2[r], p1 = xb2[TILE_M + r];
+              const float mean = (p0.x + p1.x) * inv_w;  // identical expression in both halves
+              const float var = fmaxf((p0.y + p1.y) * inv_w - mean * mean, 0.f);
+              const float rstd = rsqrtf(var + 1e-3f);  // keras LayerNormalization epsilon
+              rs = f2(rstd);
+              nm = f2(-mean * rstd);
+              rsL = f2(rstd * 1.4426950408889634f);
+              if (last) {
+                // output projector folded through the LayerNorm affine (flow_matching.py:229-230)
 #pragma unroll
                 for (int d = 0; d < DP; ++d) {
                   const float dot = xp[(size_t)r * DP + d] + xp[((size_t)TILE_M + r) * DP + d];
-                  pred[d] = fmaf(rs.x, dot, fmaf(nm.x, c_bo[DP + d], c_bo[d]));  // rstd (dot - mean s1) + s0
+                  pred[d] = fmaf(rstd, dot, fmaf(-mean * rstd, c_bo[DP + d], c_bo[d]));  // rstd (dot - mean s1) + s0
                 }
-                PROF_ADD(6)
+              } else if (half == 0) {
+                // the next Dense consumes v' raw: its rank-1 and bias terms need (mu, 1 / (log2(e) r)) of this row
+                *reinterpret_cast<uint4*>(sX) = fold_extras<BF16>(mean, 0.6931471805599453f * (var + 1e-3f) * rstd);
               }
+              PROF_ADD(6)
             }
             if (!last) {
               fence_proxy_async_smem();
@@ -345,9 +565,9 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
     PROF_FLUSH(warp)
     tc_fence_before();
   } else if (warp == F_MMA_WARP) {
-    mma_issuer_loop(a, bars, smem_base, tmem_base, n_pairs, n_evals, lane);
+    fold_issuer_loop(a, bars, smem_base, tmem_base, n_pairs, n_evals, lane);
   } else {
-    producer_loop(a, bars, smem_base, n_pairs, n_evals, lane);
+    fold_producer_loop(a, bars, smem_base, n_pairs, n_evals, lane);
   }
 
   __syncthreads();
