@@ -114,17 +114,18 @@ __host__ __device__ inline SmemPlan make_smem_plan(const bfk_net_config& c) {
 __host__ __device__ inline SmemPlan make_fold_plan(const bfk_net_config& c) {
   SmemPlan p{};
   PackedLayout L = make_layout(c);
-  p.a_bytes = TILE_M * (c.W + XK) * 2;  // K-chunks W/8, W/8+1 of each tile: per-row (mu, 1/r) as fp16 hi/lo pairs
+  p.a_bytes = TILE_M * (c.W + 8) * 2;  // K-chunk W/8 of each tile: per-row (mu, 1/r) as fp16 hi/lo pairs; the second
+                                       // K-chunk of the XK tail is all zero and shared by both tiles (after the tiles)
   p.stage_bytes = FKC * c.W * 2;
   p.film_bytes = (uint32_t)align_up((size_t)table_stride(c) * 4, 16);
   uint32_t off = 0;
-  p.a_tile = off; off += TILES_PER_CTA * p.a_bytes;
+  p.a_tile = off; off += TILES_PER_CTA * p.a_bytes + TILE_M * 16;
   p.film = off; off += 2 * p.film_bytes;
   p.cvec = off; off += (uint32_t)align_up((size_t)L.cvec_floats * 4, 16);
   p.bars = off; off += 256;
   p.xch = off;
   p.xch_stride = 2;
-  off += 2 * 2 * 2 * TILE_M * 8;       // [2 buffers][2 tiles][2 column halves][TILE_M] (row sum, sum of squares)
+  off += 2 * 2 * TILE_M * 8;           // [2 tiles][2 column halves][TILE_M] (row sum, sum of squares)
   off += 2 * 2 * TILE_M * L.DP * 4;    // [2 tiles][2 halves][TILE_M][DP] output-projector partials
   p.ring = (uint32_t)align_up(off, 128);
   int n = (int)((SMEM_LIMIT - p.ring) / p.stage_bytes);

@@ -165,6 +165,7 @@ __device__ __forceinline__ void fold_issuer_loop(const SamplerArgs& a, const Bar
     uint32_t ph_full = 0;  // bit s = parity of stage s
     int stage = 0;
     const uint32_t a_lbo = TILE_M * 16, b_lbo = (uint32_t)W * 16;
+    const uint32_t z_base = smem_base + a.plan.a_tile + TILES_PER_CTA * a.plan.a_bytes;  // shared zero K-chunk
     for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
       for (long long e = 0; e < n_evals; ++e) {
         for (int g = 0; g < a.NG; ++g) {
@@ -179,11 +180,19 @@ __device__ __forceinline__ void fold_issuer_loop(const SamplerArgs& a, const Bar
               ph_full ^= (1u << stage);
               tc_fence_after();
               const uint32_t b_base = smem_base + a.plan.ring + stage * a.plan.stage_bytes;
-              const int nk = (c < n_chunks) ? FKC / 16 : XK / 16;
-              for (int kk = 0; kk < nk; ++kk) {
-                const uint64_t ad = umma_smem_desc(a_base + (uint32_t)(c * (FKC / 8) + kk * 2) * a_lbo, a_lbo, 128);
-                const uint64_t bd = umma_smem_desc(b_base + (uint32_t)(kk * 2) * b_lbo, b_lbo, 128);
-                umma_f16(d_tmem, ad, bd, a.idesc, (uint32_t)((c | kk) != 0));
+              if (c < n_chunks) {
+#pragma unroll
+                for (int kk = 0; kk < FKC / 16; ++kk) {
+                  const uint64_t ad = umma_smem_desc(a_base + (uint32_t)(c * (FKC / 8) + kk * 2) * a_lbo, a_lbo, 128);
+                  const uint64_t bd = umma_smem_desc(b_base + (uint32_t)(kk * 2) * b_lbo, b_lbo, 128);
+                  umma_f16(d_tmem, ad, bd, a.idesc, (uint32_t)((c | kk) != 0));
+                }
+              } else {
+                // XK tail: K-chunk W/8 of the tile holds (mu, 1/r); its second K-chunk is the shared all-zero chunk
+                const uint32_t x_base = a_base + (uint32_t)(W / 8) * a_lbo;
+                const uint64_t ad = umma_smem_desc(x_base, z_base - x_base, 128);
+                const uint64_t bd = umma_smem_desc(b_base, b_lbo, 128);
+                umma_f16(d_tmem, ad, bd, a.idesc, 1u);
               }
               umma_commit(bars.w_empty(stage));
               stage = (stage + 1 == a.plan.n_stage) ? 0 : stage + 1;
@@ -251,6 +260,9 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
 
   // ---------------- one-time setup
   for (int i = threadIdx.x; i < a.cvec_floats; i += F_NUM_THREADS) s_cvec[i] = a.cvec[i];
+  if (threadIdx.x < TILE_M)  // the all-zero K-chunk both tiles' XK tails point at
+    *reinterpret_cast<uint4*>(smem + a.plan.a_tile + TILES_PER_CTA * a.plan.a_bytes + threadIdx.x * 16) = make_uint4(0u, 0u, 0u, 0u);
+  fence_proxy_async_smem();
   if (threadIdx.x == 0) {
     for (int s = 0; s < a.plan.n_stage; ++s) { mbar_init(bars.w_full(s), 1); mbar_init(bars.w_empty(s), 1); }
     for (int t = 0; t < 2; ++t) {
@@ -280,9 +292,9 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
     unsigned char* sA = smem + a.plan.a_tile + tile * a.plan.a_bytes + r * 16;
     const uint32_t t_acc = tmem_base + ((uint32_t)(quarter * 32) << 16) + tile * W;
     const int bar_id = 1 + tile * 4 + quarter;  // the two column halves of the same 32 rows
-    // exchange between the two column halves: [buf 2][tile 2][half 2][TILE_M] (sum, sumsq); [tile][half][TILE_M][DP]
+    // exchange between the two column halves: [tile 2][half 2][TILE_M] (sum, sumsq); [tile][half][TILE_M][DP]
     float2* xst = reinterpret_cast<float2*>(smem + a.plan.xch);
-    float* xpr = reinterpret_cast<float*>(smem + a.plan.xch + 2 * 2 * 2 * TILE_M * 8);
+    float* xpr = reinterpret_cast<float*>(smem + a.plan.xch + 2 * 2 * TILE_M * 8);
     const float* c_wx = s_cvec + a.cv_wx;
     const float* c_bx = s_cvec + a.cv_bx;
     const float* c_blk = s_cvec + a.cv_blk;  // per block: gamma_{l-1}
@@ -291,9 +303,7 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
     const float inv_w = 1.f / (float)W;
     PROF_DECL
     uint32_t ph_acc = 0;
-    long long nb = 0;  // running block-epilogue counter (stats exchange buffer)
-    unsigned char* sX = sA + (size_t)(W >> 3) * (TILE_M * 16);  // my row's extra K entries (K-chunks W/8, W/8+1)
-    if (half == 0) *reinterpret_cast<uint4*>(sX + TILE_M * 16) = make_uint4(0u, 0u, 0u, 0u);
+    unsigned char* sX = sA + (size_t)(W >> 3) * (TILE_M * 16);  // my row's extra K entries (K-chunk W/8)
     long long q = 0;   // evaluation sequence number of this CTA (film double buffer)
 
     for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
@@ -465,7 +475,8 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
               // ---- row statistics of v': my half's partial sums + the other half's (shared memory, 64-thread barrier)
               const float2 s01 = __fadd2_rn(__fadd2_rn(sum2[0], sum2[1]), __fadd2_rn(sum2[2], sum2[3]));
               const float2 q01 = __fadd2_rn(__fadd2_rn(sq2[0], sq2[1]), __fadd2_rn(sq2[2], sq2[3]));
-              float2* xb2 = xst + ((size_t)(nb & 1) * 4 + tile * 2) * TILE_M;
+              // (single buffer: my partner has read these before it announced the A tile of the previous layer)
+              float2* xb2 = xst + (size_t)(tile * 2) * TILE_M;
               xb2[(size_t)half * TILE_M + r] = make_float2(s01.x + s01.y, q01.x + q01.y);
               float* xp = xpr + (size_t)(tile * 2) * TILE_M * DP;
               if (last) {
@@ -474,7 +485,6 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
               }
               PROF_ADD(5)
               named_bar_sync(bar_id, 64);
-              ++nb;
               const float2 p0 = xb2[r], p1 = xb2[TILE_M + r];
               const float mean = (p0.x + p1.x) * inv_w;  // identical expression in both halves
               const float var = fmaxf((p0.y + p1.y) * inv_w - mean * mean, 0.f);
