@@ -339,6 +339,38 @@ __global__ void __launch_bounds__(256) lincomb3_kernel(float* __restrict__ out, 
   }
 }
 
+
+// FlowMatching.compute_metrics' sampling step (flow_matching.py:143-163) in ONE kernel: x0 ~ N(0, 1) (the Philox stream of
+// bfk_normal_fill for the same seed: counter = GLOBAL element index / 4), u ~ U(0, 1) (a second stream keyed by
+// seed ^ 0x5851F42D4C957F2D, one word per GLOBAL row), t = u^(1 + alpha), x = t x1 + (1 - t) x0, target = x1 - x0.
+// A data-parallel rank passes the global index of its first row, so the batch is the single-GPU batch.
+__global__ void __launch_bounds__(256) fm_train_batch_kernel(const float* __restrict__ x1, long long B, int D, long long row0,
+                                                             unsigned long long seed, const uint32_t* __restrict__ seed_dev,
+                                                             float alpha, float* __restrict__ x0_out, float* __restrict__ t_out,
+                                                             float* __restrict__ x, float* __restrict__ target) {
+  if (seed_dev) seed = ((unsigned long long)seed_dev[1] << 32) | seed_dev[0];
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= B) return;
+  const unsigned long long gr = (unsigned long long)(row0 + r);
+  uint32_t c[4] = {(uint32_t)(gr >> 2), (uint32_t)(gr >> 34), 0u, 0u};
+  const unsigned long long s2 = seed ^ 0x5851F42D4C957F2Dull;
+  philox4x32_10(c, (uint32_t)s2, (uint32_t)(s2 >> 32));
+  const float u = u01(c[gr & 3]);
+  const float t = alpha == 0.f ? u : powf(u, 1.f + alpha);
+  t_out[r] = t;
+  unsigned long long qprev = ~0ull;
+  float z[4];
+  for (int d = 0; d < D; ++d) {
+    const unsigned long long e = gr * (unsigned long long)D + d;
+    if ((e >> 2) != qprev) { qprev = e >> 2; normal_quad(qprev, seed, z); }
+    const float a0 = z[e & 3], a1 = x1[r * D + d];
+    if (x0_out) x0_out[r * D + d] = a0;
+    x[r * D + d] = t * a1 + (1.f - t) * a0;
+    target[r * D + d] = a1 - a0;
+  }
+}
+
+
 }  // namespace bfk
 
 // ---- C ABI ------------------------------------------------------------------------------------------------------------
@@ -428,6 +460,15 @@ extern "C" int bfk_lincomb3(float* out, float a, const float* x, float b, const 
   long long blocks = (numel + 255) / 256, cap = (long long)sms * 8;
   if (blocks > cap) blocks = cap;
   bfk::lincomb3_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(out, a, x, b, y, c, z, numel);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_fm_train_batch(const float* x1, int64_t B, int32_t D, int64_t row_offset, uint64_t seed, const uint32_t* seed_dev,
+                                  float alpha, float* x0_out, float* t_out, float* x, float* target, void* stream_) {
+  if (!x1 || !t_out || !x || !target || B <= 0 || D <= 0 || row_offset < 0) return fail(-83, "bfk_fm_train_batch: bad arguments");
+  bfk::fm_train_batch_kernel<<<cdiv((size_t)B, 256), 256, 0, (cudaStream_t)stream_>>>(x1, B, D, row_offset, (unsigned long long)seed, seed_dev,
+                                                                               alpha, x0_out, t_out, x, target);
   CK(cudaGetLastError());
   return 0;
 }

@@ -56,14 +56,22 @@ __device__ __forceinline__ float t_act(int act, float x, float& d) {
   }
 }
 
-// counter-based keep mask for Dropout (conditional_dense_block.py:120-121): identical in forward and backward
-__device__ __forceinline__ float drop_scale(unsigned long long seed, int layer, long long row, int col, float rate, float inv_keep) {
-  uint32_t h = (uint32_t)(row * 1024 + col) ^ (uint32_t)seed;
-  h *= 0x9E3779B1u; h ^= h >> 15;
-  h *= 0x85EBCA77u; h ^= h >> 13;
-  h += (uint32_t)(seed >> 32) + (uint32_t)layer * 0xC2B2AE3Du;
-  h *= 0x27D4EB2Fu; h ^= h >> 16;
-  const float u = (float)(h >> 8) * (1.f / 16777216.f);
+// Counter-based keep mask for Dropout (conditional_dense_block.py:120-121): identical in forward and backward, a function
+// of (seed, layer, GLOBAL row, column) only, so a data-parallel shard draws the mask of the same rows of the whole batch.
+// The seed and layer are avalanched into a 64-bit key first (splitmix64), so consecutive seeds give unrelated masks; the
+// element index then goes through two multiply-xorshift rounds.
+__device__ __forceinline__ unsigned long long drop_key(unsigned long long seed, const uint32_t* seed_dev, int layer) {
+  if (seed_dev) seed = ((unsigned long long)seed_dev[1] << 32) | seed_dev[0];  // graph replay: the seed lives in HBM
+  unsigned long long z = seed + 0x9E3779B97F4A7C15ull * (unsigned long long)(layer + 1);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+__device__ __forceinline__ float drop_scale(unsigned long long key, long long row, int col, float rate, float inv_keep) {
+  unsigned long long x = ((unsigned long long)row * 1024ull + (unsigned long long)col) ^ key;
+  x *= 0xD6E8FEB86659FD93ull; x ^= x >> 32;
+  x *= 0xD6E8FEB86659FD93ull; x ^= x >> 32;
+  const float u = (float)((uint32_t)x >> 8) * (1.f / 16777216.f);
   return u >= rate ? inv_keep : 0.f;
 }
 
@@ -217,11 +225,12 @@ struct BlockFwdArgs {
   float* out_f32;       // optional fp32 copy of the block output
   long long B, R_pad;
   int W, act, norm, layer;
-  float drop_rate, inv_keep; unsigned long long seed;
+  float drop_rate, inv_keep; unsigned long long seed; const uint32_t* seed_dev; long long row0;
 };
 
 template <int NJ>
 __global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
+  const unsigned long long dkey = a.drop_rate > 0.f ? drop_key(a.seed, a.seed_dev, a.layer) : 0ull;
   const int lane = threadIdx.x & 31;
   const long long warp0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
@@ -249,7 +258,7 @@ __global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
         for (int i = 0; i < 8; ++i) {
           float d;
           float u = t_act(a.act, p[i], d);
-          if (a.drop_rate > 0.f) u *= drop_scale(a.seed, a.layer, r, c0 + i, a.drop_rate, a.inv_keep);
+          if (a.drop_rate > 0.f) u *= drop_scale(dkey, a.row0 + r, c0 + i, a.drop_rate, a.inv_keep);
           v[j][i] = u;
         }
         if (a.FG) {
@@ -333,6 +342,7 @@ __global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
 // at W = 1024 (108 registers, 2.3 rows per warp at 8192 rows): measured 46 us per 8192 x 1024 panel, 1.4 TB/s (r01w).
 template <int WPR>
 __global__ void __launch_bounds__(256) block_fwd_wide_kernel(const BlockFwdArgs a) {
+  const unsigned long long dkey = a.drop_rate > 0.f ? drop_key(a.seed, a.seed_dev, a.layer) : 0ull;
   __shared__ float s_sum[8], s_sq[8];
   constexpr int GPB = 8 / WPR;  // rows in flight per block
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -366,7 +376,7 @@ __global__ void __launch_bounds__(256) block_fwd_wide_kernel(const BlockFwdArgs 
       for (int i = 0; i < 8; ++i) {
         float d;
         float u = t_act(a.act, p[i], d);
-        if (a.drop_rate > 0.f) u *= drop_scale(a.seed, a.layer, r, c0 + i, a.drop_rate, a.inv_keep);
+        if (a.drop_rate > 0.f) u *= drop_scale(dkey, a.row0 + r, c0 + i, a.drop_rate, a.inv_keep);
         v[i] = u + f[i];
       }
       if (a.prev) {
@@ -450,12 +460,13 @@ struct BlockBwdArgs {
   float* d_gamma; float* d_beta; float* d_bd; float* d_bfilm;
   long long B, R_pad;
   int W, act, norm, layer;
-  float drop_rate, inv_keep; unsigned long long seed;
+  float drop_rate, inv_keep; unsigned long long seed; const uint32_t* seed_dev; long long row0;
   float gscale;
 };
 
 template <int NJ>
 __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
+  const unsigned long long dkey = a.drop_rate > 0.f ? drop_key(a.seed, a.seed_dev, a.layer) : 0ull;
   extern __shared__ float s_red[];  // [4][W]
   const int lane = threadIdx.x & 31;
   const long long warp0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -533,7 +544,7 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
           dv[i] = a.norm == BFK_NORM_LAYER ? rs * (g[j][i] - m1 - xh[j][i] * m2) : g[j][i];
           float d;
           t_act(a.act, pp[j][i], d);
-          if (a.drop_rate > 0.f) d *= drop_scale(a.seed, a.layer, r, c0 + i, a.drop_rate, a.inv_keep);
+          if (a.drop_rate > 0.f) d *= drop_scale(dkey, a.row0 + r, c0 + i, a.drop_rate, a.inv_keep);
           dp[i] = dv[i] * d;
           ad[j][i] += dp[i];
           af[j][i] += dv[i];
@@ -779,7 +790,8 @@ __global__ void seg_sqnorm_kernel(const float* __restrict__ g, const long long* 
 }
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                             const long long* __restrict__ seg_off, const float* __restrict__ sq, float clipnorm, float lr_t,
-                            float b1, float b2, float eps, float wd_lr) {
+                            float b1, float b2, float eps, float wd_lr, const float* __restrict__ hyper_dev) {
+  if (hyper_dev) { lr_t = hyper_dev[0]; wd_lr = hyper_dev[1]; }  // graph replay: step-dependent scalars live in HBM
   const int s = blockIdx.x;
   const long long a = seg_off[s], b = seg_off[s + 1];
   float clip = 1.f;
@@ -797,5 +809,6 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
     p[i] = pi - lr_t * mi / (sqrtf(vi) + eps);
   }
 }
+
 
 }  // namespace bfk

@@ -3,7 +3,6 @@
 // time_mlp.py:125-147, conditional_dense_block.py:114-131, torch_approximator.py:88-99 (autograd + optimizer step).
 #pragma once
 #include "bfk_train.cuh"
-#include "bfk_train_fused.cuh"
 
 namespace {
 
@@ -21,8 +20,7 @@ struct TrainBufs {
   int KU, KT, KTN, N1, NO, has_merge;
   long long Rp;
   unsigned char *u_img, *te_img, *w1_pk, *a1_img, *wm_f, *wm_b, *h0_img, *wo_f, *wo_b, *dout_img, *dP_img, *dV_img, *dh0pre_img;
-  float *w1, *b1, *h0pre, *m, *h0, *FB, *bo_pad, *out, *dH, *dte, *da1, *dW1, *db1, *stats;
-  unsigned char* v_img;  // fused forward (bfk_train_fused.cuh): un-normalised block output + row statistics
+  float *w1, *b1, *h0pre, *m, *h0, *FB, *bo_pad, *out, *dH, *dte, *da1, *dW1, *db1;
   unsigned char *wd_f[BFK_MAX_BLOCKS], *wd_b[BFK_MAX_BLOCKS], *wb_f[BFK_MAX_BLOCKS], *wb_b[BFK_MAX_BLOCKS], *h_img[BFK_MAX_BLOCKS];
   float *P[BFK_MAX_BLOCKS], *xhat[BFK_MAX_BLOCKS], *rstd[BFK_MAX_BLOCKS];
 };
@@ -66,8 +64,6 @@ void plan_train(const bfk_net_config* c, long long B, bool backward, Arena& ar, 
     b.h_img[l] = (unsigned char*)ar.take(Rp * W * 2);
   }
   b.FB = (float*)ar.take(Bs * W * 4);
-  b.v_img = (unsigned char*)ar.take(Rp * W * 2);
-  b.stats = (float*)ar.take(Rp * 2 * 4);
   b.wo_f = (unsigned char*)ar.take((size_t)b.NO * W * 2);
   b.wo_b = (unsigned char*)ar.take((size_t)W * b.NO * 2);
   b.bo_pad = (float*)ar.take((size_t)b.NO * 4);
@@ -209,41 +205,6 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
     act_pack_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.h0pre, W, B, n_tiles, W / 8, act, b.h0_img, b.h0);
   }
   CK(cudaGetLastError());
-  // Opt-in (BFK_TRAIN_FUSED=1): one tcgen05 kernel per block (Dense + FiLM contractions, block epilogue) + a normalisation
-  // pass, bfk_train_fused.cuh.  Parity-green but NOT faster yet (r01an/r01ao: 82.7 + 37.3 us per block against
-  // 25.6 + 25.6 + 71.5 us: the 16-warp epilogue issues 69 instructions per element), and its row statistics are fp32
-  // atomics (run-to-run bit differences) - so the three-kernel forward stays the default.
-  const char* fused_env = getenv("BFK_TRAIN_FUSED");
-  const int fused_fwd = fused_env ? atoi(fused_env) : 0;
-  const bool use_fused = fused_fwd && (W % TF_NT) == 0 && KT == TF_KC && !c->film_use_gamma;
-  if (use_fused) {
-    static bool attr = false;
-    if (!attr) {
-      CK(cudaFuncSetAttribute(train_block_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)train_fused_smem_bytes()));
-      attr = true;
-    }
-    int sms = bfk_num_sms();
-    if (sms <= 0) sms = 148;
-    const long long tiles = n_tiles * (W / TF_NT);
-    const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
-    for (int l = 0; l < L; ++l) {
-      RC(bfk_pack_kmajor_t(w->dense_k[l], W, W, W, W, TF_NT, P16, b.wd_f[l], st));
-      RC(bfk_pack_kmajor_t(w->film_b_k[l], W, T, KT, W, TF_NT, P16, b.wb_f[l], st));
-      CK(cudaMemsetAsync(b.stats, 0, (size_t)Rp * 2 * 4, st));
-      TrainFusedArgs fa{};
-      fa.A = l == 0 ? b.h0_img : b.h_img[l - 1]; fa.Bd = b.wd_f[l]; fa.T = b.te_img; fa.Bf = b.wb_f[l];
-      fa.bias_d = w->dense_b[l]; fa.bias_f = w->film_b_b[l]; fa.P = b.P[l]; fa.v_img = b.v_img; fa.stats = b.stats;
-      fa.M = B; fa.W = W; fa.act = act; fa.residual = c->residual ? 1 : 0; fa.layer = l;
-      fa.drop_rate = ta->dropout; fa.inv_keep = inv_keep; fa.seed = ta->seed;
-      fa.idesc = umma_idesc_f16(G_TM, TF_NT, 0);
-      train_block_gemm_kernel<<<grid, TF_THREADS, train_fused_smem_bytes(), st>>>(fa);
-      const bool lnl = c->norm == BFK_NORM_LAYER;
-      train_norm_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.v_img, b.stats, lnl ? w->norm_g[l] : nullptr,
-                                                            lnl ? w->norm_b[l] : nullptr, B, n_tiles, W / 8, c->norm, b.xhat[l],
-                                                            b.rstd[l], b.h_img[l]);
-      CK(cudaGetLastError());
-    }
-  } else
   for (int l = 0; l < L; ++l) {
     RC(bfk_pack_kmajor_t(w->dense_k[l], W, W, W, W, NTW, P16, b.wd_f[l], st));
     RC(bfk_pack_kmajor_t(w->film_b_k[l], W, T, KT, W, NTW, P16, b.wb_f[l], st));
@@ -258,7 +219,7 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
     a.beta = c->norm == BFK_NORM_LAYER ? w->norm_b[l] : nullptr;
     a.xhat = b.xhat[l]; a.rstd = b.rstd[l]; a.img = b.h_img[l]; a.out_f32 = nullptr;
     a.B = B; a.R_pad = Rp; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
-    a.drop_rate = ta->dropout; a.inv_keep = inv_keep; a.seed = ta->seed;
+    a.drop_rate = ta->dropout; a.inv_keep = inv_keep; a.seed = ta->seed; a.seed_dev = ta->seed_dev; a.row0 = ta->row_offset;
     RC(launch_block_fwd(a, st));
   }
   RC(bfk_pack_kmajor_t(w->out_k, D, W, W, D, 64, P16, b.wo_f, st));
@@ -286,7 +247,7 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
     a.dP_img = b.dP_img; a.dV_img = b.dV_img;
     a.d_gamma = GP(g->norm_g[l]); a.d_beta = GP(g->norm_b[l]); a.d_bd = GP(g->dense_b[l]); a.d_bfilm = GP(g->film_b_b[l]);
     a.B = B; a.R_pad = Rp; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
-    a.drop_rate = ta->dropout; a.inv_keep = inv_keep; a.seed = ta->seed; a.gscale = gs;
+    a.drop_rate = ta->dropout; a.inv_keep = inv_keep; a.seed = ta->seed; a.seed_dev = ta->seed_dev; a.row0 = ta->row_offset; a.gscale = gs;
     RC(launch_block_bwd(a, st));
     RC(launch_gemm_dw(l == 0 ? b.h0_img : b.h_img[l - 1], W / 8, b.dP_img, W / 8, GP(g->dense_k[l]), W, W, W, Rp, gs, sw, st));
     RC(launch_gemm_dw(b.te_img, KT / 8, b.dV_img, W / 8, GP(g->film_b_k[l]), W, T, W, Rp, gs, sw, st));
@@ -352,7 +313,7 @@ extern "C" int bfk_train_vjp(const bfk_net_config* c, const bfk_weights* w, cons
     a.dP_img = b.dP_img; a.dV_img = b.dV_img;
     a.d_gamma = a.d_beta = a.d_bd = a.d_bfilm = nullptr;
     a.B = B; a.R_pad = Rp; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
-    a.drop_rate = 0.f; a.inv_keep = 1.f; a.seed = 0; a.gscale = 1.f;
+    a.drop_rate = 0.f; a.inv_keep = 1.f; a.seed = 0; a.seed_dev = nullptr; a.row0 = 0; a.gscale = 1.f;
     RC(launch_block_bwd(a, st));
     if (!c->residual) CK(cudaMemsetAsync(b.dH, 0, (size_t)B * W * 4, st));
     RC(bfk_pack_kmajor(w->dense_k[l], W, W, W, W, NTW, P16, b.wd_b[l], st));
@@ -412,9 +373,9 @@ extern "C" int bfk_fm_interpolate(const float* x0, const float* x1, const float*
   return 0;
 }
 
-extern "C" int bfk_adam_step(float* params, const float* grads, float* m, float* v, const int64_t* seg_offsets, int32_t n_seg,
-                             float* seg_sqnorm, float clipnorm, float lr_t, float beta1, float beta2, float eps, float wd_lr,
-                             void* stream_) {
+static int adam_step_impl(float* params, const float* grads, float* m, float* v, const int64_t* seg_offsets, int32_t n_seg,
+                          float* seg_sqnorm, float clipnorm, float lr_t, float beta1, float beta2, float eps, float wd_lr,
+                          const float* hyper_dev, void* stream_) {
   if (!params || !grads || !m || !v || !seg_offsets || n_seg <= 0 || !seg_sqnorm) return fail(-81, "bfk_adam_step: bad arguments");
   cudaStream_t st = (cudaStream_t)stream_;
   static_assert(sizeof(long long) == sizeof(int64_t), "");
@@ -423,7 +384,19 @@ extern "C" int bfk_adam_step(float* params, const float* grads, float* m, float*
     seg_sqnorm_kernel<<<dim3(n_seg, 16), 256, 0, st>>>(grads, (const long long*)seg_offsets, n_seg, seg_sqnorm);
   }
   adam_kernel<<<dim3(n_seg, 16), 256, 0, st>>>(params, grads, m, v, (const long long*)seg_offsets, seg_sqnorm, clipnorm, lr_t, beta1,
-                                              beta2, eps, wd_lr);
+                                              beta2, eps, wd_lr, hyper_dev);
   CK(cudaGetLastError());
   return 0;
 }
+extern "C" int bfk_adam_step(float* params, const float* grads, float* m, float* v, const int64_t* seg_offsets, int32_t n_seg,
+                             float* seg_sqnorm, float clipnorm, float lr_t, float beta1, float beta2, float eps, float wd_lr,
+                             void* stream_) {
+  return adam_step_impl(params, grads, m, v, seg_offsets, n_seg, seg_sqnorm, clipnorm, lr_t, beta1, beta2, eps, wd_lr, nullptr, stream_);
+}
+extern "C" int bfk_adam_step_dev(float* params, const float* grads, float* m, float* v, const int64_t* seg_offsets, int32_t n_seg,
+                                 float* seg_sqnorm, float clipnorm, const float* hyper_dev, float beta1, float beta2, float eps,
+                                 void* stream_) {
+  if (!hyper_dev) return fail(-82, "bfk_adam_step_dev: null hyper-parameter buffer");
+  return adam_step_impl(params, grads, m, v, seg_offsets, n_seg, seg_sqnorm, clipnorm, 0.f, beta1, beta2, eps, 0.f, hyper_dev, stream_);
+}
+

@@ -138,7 +138,7 @@ def _all_nans(state):
 
 
 def integrate_density(fn, state, start_time=None, stop_time=None, min_steps: int = 50, max_steps: int = 10_000,
-                      steps=100, method: str = "rk45", info: dict | None = None, **kwargs):
+                      steps=100, method: str = "rk45", info: dict | None = None, group=None, **kwargs):
     """bayesflow.utils.integrate (integrate.py:455-489) for the two-key state (xz, trace)."""
     if isinstance(steps, str) and steps in ["adaptive", "dynamic"]:
         if start_time is None or stop_time is None:
@@ -147,7 +147,7 @@ def integrate_density(fn, state, start_time=None, stop_time=None, min_steps: int
         if method == "scipy":
             raise NotImplementedError("method='scipy' runs the network on the host; outside the accelerated path")
         return _integrate_adaptive(fn, state, float(start_time), float(stop_time), int(min_steps), int(max_steps), method,
-                                   info, atol=kwargs.get("atol", 1e-6), rtol=kwargs.get("rtol", 1e-4))
+                                   info, atol=kwargs.get("atol", 1e-6), rtol=kwargs.get("rtol", 1e-4), group=group)
     if isinstance(steps, (int, np.integer)) and not isinstance(steps, bool):
         if start_time is None or stop_time is None:
             raise ValueError("Please provide start_time and stop_time for the integration, was "

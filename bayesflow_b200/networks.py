@@ -608,6 +608,9 @@ class InferenceNetwork(nn.Module):
             loss = _LossWithGrads.apply(loss, eng, *eng.params)
         return {"loss": loss}
 
+    def _graphable_training(self):
+        return False
+
     def _dropout_seed(self, seed):
         if seed is None:
             self._drop_calls = getattr(self, "_drop_calls", 0) + 1
@@ -674,7 +677,8 @@ class InferenceNetwork(nn.Module):
         ik = {k: v for k, v in integrate_kwargs.items() if k in self._INTEGRATE_KEYS}
         info = {}
         state = (x, torch.zeros(x.shape[0], 1, device=x.device, dtype=torch.float32))
-        xz, trace = integrate_density(fn, state, info=info, **ik)
+        # rows sharded over ranks (parallel.log_prob_sharded): the adaptive controller's maxima are all-reduced
+        xz, trace = integrate_density(fn, state, info=info, group=getattr(self, "step_control_group", None), **ik)
         info["evals"] = fn.evals
         self.last_integration_info = info
         return xz, trace.squeeze(-1)
@@ -742,8 +746,18 @@ class FlowMatching(InferenceNetwork):
         return run.velocity(xz, float(np.float32(time)))
 
     # -- training (flow_matching.py:132-178) ------------------------------------------------------------------------------
+    def _graphable_training(self):
+        """the training step has no host-side decisions: Trainer(cuda_graph=True) may capture it"""
+        bd = self.base_distribution
+        standard = (isinstance(bd, DiagonalNormal) and not torch.is_tensor(bd.mean) and not torch.is_tensor(bd.std)
+                    and float(bd.mean) == 0.0 and float(bd.std) == 1.0)
+        return standard and not self.use_optimal_transport and self.drop_cond_prob == 0 and self.drop_target_prob == 0
+
     def _loss_and_grads(self, x, conditions=None, sample_weight=None, stage="training", seed=None, world=1, backward=True,
-                        **kwargs):
+                        row_offset=0, noise_seed=None, seed_dev=None, loss_into_slot=False, **kwargs):
+        """`row_offset`: global index of this shard's first row; `noise_seed`: keys x0 / t of the step (Philox streams that
+        are functions of the GLOBAL row, so data-parallel ranks draw disjoint rows of ONE batch); `seed_dev`: two device
+        words that override the seeds (CUDA-graph replay)."""
         from .training import train_engine
         if self.drop_cond_prob > 0 or self.drop_target_prob > 0:
             raise NotImplementedError("drop_cond_prob / drop_target_prob > 0 are outside the accelerated training path")
@@ -756,20 +770,40 @@ class FlowMatching(InferenceNetwork):
             x1 = x
             if not x1.is_cuda:
                 raise RuntimeError("bayesflow_b200 runs on CUDA tensors only (no CPU fallback)")
-            x0 = self.base_distribution.sample(tuple(x1.shape[:-1]))
-            if self.use_optimal_transport:
-                # flow_matching.py:146-157: x1 (and its conditions) are re-drawn along the transport plan, x0 is kept
-                from .optimal_transport import optimal_transport
-                x0, x1, conditions = optimal_transport(x0, x1, conditions=conditions, seed=kwargs.get("ot_seed"),
-                                                       **self.optimal_transport_kwargs)
-            u = torch.rand((x0.shape[0],), device=x1.device)
-            t = u ** (1 + self.time_power_law_alpha)
-            x, target = eng.interpolate(x0, x1, t)
+            if noise_seed is None:
+                noise_seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+            if self._graphable_training():
+                # flow_matching.py:143-163 in one launch: x0, t = u^(1+alpha), x and the target velocity
+                x1 = eng._f32(x1)
+                x, target = torch.empty_like(x1), torch.empty_like(x1)
+                t = torch.empty(x1.shape[0], device=x1.device, dtype=torch.float32)
+                with torch.cuda.device(x1.device):
+                    _lib.check(eng.L.bfk_fm_train_batch(_lib.ptr(x1), x1.shape[0], x1.shape[1], int(row_offset),
+                                                        C.c_uint64(int(noise_seed) & (2 ** 64 - 1)), _lib.ptr(seed_dev),
+                                                        float(self.time_power_law_alpha), None, _lib.ptr(t), _lib.ptr(x),
+                                                        _lib.ptr(target), _lib.stream_ptr()), "bfk_fm_train_batch")
+                eng.launches += 1
+            else:
+                x0 = self.base_distribution.sample(tuple(x1.shape[:-1]), seed=noise_seed, row_offset=row_offset)
+                if self.use_optimal_transport:
+                    # flow_matching.py:146-157: x1 (and its conditions) are re-drawn along the transport plan, x0 is kept
+                    from .optimal_transport import optimal_transport
+                    x0, x1, conditions = optimal_transport(x0, x1, conditions=conditions, seed=kwargs.get("ot_seed"),
+                                                           **self.optimal_transport_kwargs)
+                # u by GLOBAL row: Phi(z) of a second Philox normal stream
+                zu = DiagonalNormal().to(x1.device)
+                zu.build((None, 1))
+                zu = zu.to(x1.device).sample((x0.shape[0],), seed=(int(noise_seed) ^ 0x2545F4914F6CDD1D) & (2 ** 63 - 1),
+                                             row_offset=row_offset).reshape(-1)
+                u = 0.5 * (1.0 + torch.erf(zu * (1.0 / math.sqrt(2.0))))
+                t = u ** (1 + self.time_power_law_alpha)
+                x, target = eng.interpolate(x0, x1, t)
         training = stage == "training"
         rate = float(self.subnet.dropout or 0.0) if training else 0.0
         seed = self._dropout_seed(seed)
         loss, _ = eng.step(x, t, conditions, target, row_weight=sample_weight, loss=self.loss_fn, dropout=rate, seed=seed,
-                           global_batch=x.shape[0] * world, backward=backward)
+                           global_batch=x.shape[0] * world, backward=backward, row_offset=row_offset, seed_dev=seed_dev,
+                           loss_into_slot=loss_into_slot)
         return loss
 
     def _forward(self, x, conditions=None, density=False, training=False, **kwargs):
@@ -938,7 +972,7 @@ class DiffusionModel(InferenceNetwork):
         return sigma ** 2 / alpha, 1 / alpha  # score
 
     def _loss_and_grads(self, x, conditions=None, sample_weight=None, stage="training", seed=None, world=1, backward=True,
-                        fixed=None, row_offset=0, **kwargs):
+                        fixed=None, row_offset=0, noise_seed=None, seed_dev=None, loss_into_slot=False, **kwargs):
         """One DM training step through bfk_train_step.  Every loss_type is `w * mean_d (a*pred - target)^2` with a
         per-row scalar `a` and a per-element target assembled here from the schedule; the network forward/backward,
         the loss reduction and all parameter gradients are the C-ABI kernels.  `fixed=(u0, eps_t)` bypasses the RNG
@@ -956,10 +990,17 @@ class DiffusionModel(InferenceNetwork):
         B = x.shape[0]
         Bg = B * world
         if fixed is None:
-            u0 = torch.rand((1,), device=dev, dtype=torch.float32)
-            if world > 1:
-                torch.distributed.broadcast(u0, src=0)
-            eps = torch.randn(x.shape, device=dev, dtype=torch.float32)
+            if noise_seed is None:
+                noise_seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+                if world > 1:  # every rank must key the same global streams
+                    sd = torch.tensor([noise_seed], device=dev, dtype=torch.int64)
+                    torch.distributed.broadcast(sd, src=0)
+                    noise_seed = int(sd.item())
+            # u0: one uniform for the whole (global) batch; eps: Philox normals of the GLOBAL rows (bfk_normal_fill)
+            u0 = torch.rand((1,), device="cpu", dtype=torch.float32,
+                            generator=torch.Generator().manual_seed(int(noise_seed) & (2 ** 62 - 1))).to(dev)
+            eps = self.base_distribution.sample((B,), seed=(int(noise_seed) ^ 0x2545F4914F6CDD1D) & (2 ** 63 - 1),
+                                                row_offset=row_offset)
         else:
             u0, eps = (torch.as_tensor(v, device=dev, dtype=torch.float32) for v in fixed)
         sched_training = stage in ("training", "validation")
@@ -993,7 +1034,7 @@ class DiffusionModel(InferenceNetwork):
         loss, _ = eng.step(z, t_net.reshape(-1).to(torch.float32), conditions, target.to(torch.float32),
                            pred_scale=a.reshape(-1).to(torch.float32), row_weight=row_w.contiguous(), loss="mse",
                            dropout=rate, seed=self._dropout_seed(seed), global_batch=Bg, backward=backward,
-                           cotangent_scale=cot_scale)
+                           cotangent_scale=cot_scale, row_offset=row_offset, loss_into_slot=loss_into_slot)
         return loss
 
     def _cotangent_scale(self, stage):

@@ -55,6 +55,42 @@ def sample_sharded(net, num_samples: int, conditions: torch.Tensor, *, group=Non
     return gather_rows(out, N, group=group)
 
 
+def log_prob_sharded(net, samples: torch.Tensor, conditions: torch.Tensor | None = None, *, group=None, gather: bool = False,
+                     global_step_control: bool = True, **kwargs):
+    """`InferenceNetwork.log_prob` (networks/inference/inference_network.py:127-129) for one rank.
+
+    samples: (N, S, D) draws of N datasets (or (N, D)); conditions: (N, C) for ALL datasets (every rank passes the same
+    tensors) - only this rank's datasets are evaluated.  Rows are independent (utils/integrate.py:31-44), except that an
+    adaptive solver's step controller takes maxima over ALL rows (:117-118, 353-358): with global_step_control the two
+    maxima are MAX-all-reduced per trial step, so every rank walks the step sequence of the single-GPU call.
+    Returns (n_local, S) log-densities, or all (N, S) with gather=True."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    squeeze = samples.ndim == 2
+    if squeeze:
+        samples = samples.unsqueeze(1)
+    N, S, D = samples.shape
+    lo, hi = dataset_shard(N, rank, world)
+    n_local = hi - lo
+    prev = getattr(net, "step_control_group", None)
+    if world > 1 and global_step_control:
+        net.step_control_group = group if group is not None else dist.group.WORLD
+    try:
+        if n_local > 0:
+            x = samples[lo:hi].reshape(n_local * S, D).contiguous()
+            c = None if conditions is None else conditions[lo:hi].repeat_interleave(S, dim=0).contiguous()
+            out = net.log_prob(x, conditions=c, **kwargs).reshape(n_local, S)
+        else:
+            out = samples.new_zeros((0, S))
+            if world > 1 and global_step_control and kwargs.get("steps", net.integrate_kwargs.get("steps")) in ("adaptive", "dynamic"):
+                raise ValueError("log_prob_sharded with global step control needs at least one dataset per rank")
+    finally:
+        net.step_control_group = prev
+    if gather and world > 1:
+        out = gather_rows(out, N, group=group)
+    return out.squeeze(1) if squeeze else out
+
+
 def gather_rows(local: torch.Tensor, num_datasets: int, *, group=None) -> torch.Tensor:
     """all_gather of ragged dataset shards (sizes from dataset_shard) into one (N, ...) tensor on every rank."""
     world = dist.get_world_size(group)

@@ -26,7 +26,7 @@ class TrainArgs(C.Structure):
     _fields_ = [("x", C.c_void_p), ("t", C.c_void_p), ("cond", C.c_void_p), ("target", C.c_void_p),
                 ("pred_scale", C.c_void_p), ("row_weight", C.c_void_p), ("B", C.c_int64), ("loss", C.c_int32),
                 ("dw_swap", C.c_int32), ("dropout", C.c_float), ("loss_scale", C.c_float), ("grad_scale", C.c_float),
-                ("seed", C.c_uint64), ("huber_c", C.c_float)]
+                ("seed", C.c_uint64), ("huber_c", C.c_float), ("seed_dev", C.c_void_p), ("row_offset", C.c_int64)]
 
 
 def _bind(L):
@@ -40,6 +40,10 @@ def _bind(L):
                                      C.c_void_p]
     L.bfk_adam_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
                                 C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p]
+    L.bfk_adam_step_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
+                                    C.c_float, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_void_p]
+    L.bfk_fm_train_batch.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_uint64, C.c_void_p, C.c_float,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.bfk_train_vjp.argtypes = [C.POINTER(_lib.NetConfig), C.POINTER(_lib.Weights), C.POINTER(TrainArgs), C.c_void_p,
                                 C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     L.bfk_rk_combine.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_float, C.c_int64, C.c_void_p,
@@ -91,7 +95,11 @@ class TrainEngine:
         for n in sizes:
             offs.append(offs[-1] + n)
         self.flat = torch.empty(offs[-1], device=dev, dtype=torch.float32)
-        self.grad = torch.zeros_like(self.flat)
+        # gradients + ONE more float: the loss rides in the same buffer, so the data-parallel exchange is one all-reduce
+        self.grad_ext = torch.zeros(offs[-1] + 1, device=dev, dtype=torch.float32)
+        self.grad = self.grad_ext[:offs[-1]]
+        self.loss_slot = self.grad_ext[offs[-1]:].view(())
+        self.version = 0  # bumped whenever step() overwrites the gradient buffer (see _LossWithGrads)
         self._gviews = {}
         for p, a, b in zip(params, offs[:-1], offs[1:]):
             self.flat[a:b].copy_(p.data.reshape(-1).to(torch.float32))
@@ -135,7 +143,7 @@ class TrainEngine:
 
     def step(self, x, t, conditions, target, *, pred_scale=None, row_weight=None, loss="mse", dropout=0.0, seed=0,
              global_batch=None, backward=True, zero_grad=True, want_pred=False, want_loss=True, _dw_swap=0,
-             cotangent_scale=1.0, huber_c=0.0):
+             cotangent_scale=1.0, huber_c=0.0, row_offset=0, seed_dev=None, loss_into_slot=False):
         """One forward (+ loss, + backward).  Gradients are accumulated into ``self.grad`` (zeroed first unless
         ``zero_grad=False``) scaled by 1/(global_batch*D).  Returns (loss 0-d device tensor or None, pred or None)."""
         net = self.net
@@ -162,14 +170,22 @@ class TrainEngine:
         a.B, a.loss, a.dw_swap = B, {"mse": 0, "mae": 1, "pseudo_huber": 2}[loss], int(_dw_swap)
         a.dropout, a.seed = float(dropout), int(seed) & (2 ** 64 - 1)
         a.huber_c = float(huber_c)
+        a.row_offset = int(row_offset)
+        a.seed_dev = seed_dev.data_ptr() if seed_dev is not None else None
         # `cotangent_scale` (a power of two already folded into row_weight by the caller) keeps the fp16 cotangent image
         # in range; loss and gradients are un-scaled here
         a.loss_scale = 1.0 / (gb * (D if loss in ("mse", "mae", "pseudo_huber") else 1)) / cotangent_scale
         a.grad_scale = 1.0 / (gb * D) / cotangent_scale
         ws = self._workspace(B, backward)
         if backward and zero_grad:
-            self.grad.zero_()
-        loss_t = torch.zeros((), device=self.device, dtype=torch.float32) if want_loss else None
+            self.grad_ext.zero_()
+            self.version += 1
+        if loss_into_slot:
+            if not (backward and zero_grad):
+                self.loss_slot.zero_()
+            loss_t = self.loss_slot
+        else:
+            loss_t = torch.zeros((), device=self.device, dtype=torch.float32) if want_loss else None
         pred = torch.empty(B, D, device=self.device, dtype=torch.float32) if want_pred else None
         rc = self.L.bfk_train_step(C.byref(self.cfg), C.byref(self.w), C.byref(self.g) if backward else None, C.byref(a),
                                    _lib.ptr(loss_t), _lib.ptr(pred), _lib.ptr(ws), ws.numel(), _lib.stream_ptr())
@@ -212,10 +228,7 @@ class TrainEngine:
     def launches_per_step(self, backward=True):
         """Kernels bfk_train_step enqueues (counted from csrc/bfk_train_host.cuh)."""
         Lb, merge = self.cfg.L, 1 if self.net._C else 0
-        import os
-        fused = (os.environ.get("BFK_TRAIN_FUSED", "0") not in ("", "0") and self.cfg.W % 128 == 0
-                 and (self.cfg.T + 31) // 32 * 32 == 64 and not self.cfg.film_use_gamma)
-        fwd = 2 + 2 + (4 if merge else 1) + (4 if fused else 5) * Lb + 2 + 1  # fused: 2 packs + block GEMM + norm per block
+        fwd = 2 + 2 + (4 if merge else 1) + 5 * Lb + 2 + 1
         if not backward:
             return fwd
         bwd = 3 + Lb * 7 + (5 if merge else 1) + 3
@@ -238,11 +251,16 @@ class _LossWithGrads(torch.autograd.Function):
     def forward(ctx, loss, eng, *params):
         ctx.eng = eng
         ctx.n = len(params)
+        ctx.version = eng.version
         return loss.clone()
 
     @staticmethod
     def backward(ctx, grad_out):
         eng = ctx.eng
+        if ctx.version != eng.version:
+            raise RuntimeError("bayesflow_b200: another compute_metrics call overwrote this loss' gradients before "
+                               "backward() ran; call backward() right after each compute_metrics (the engine keeps ONE "
+                               "gradient buffer)")
         return (None, None) + tuple(eng.grad_of(p) * grad_out for p in eng.params)
 
 
@@ -268,6 +286,22 @@ class Adam:
         self._sq = torch.zeros(self.eng.n_seg, device=self.eng.device, dtype=torch.float32)
         self.iterations = 0
 
+    def hyper(self):
+        """(lr_t, weight_decay * lr) of the NEXT step"""
+        t = self.iterations + 1
+        lr = self.learning_rate(self.iterations) if callable(self.learning_rate) else self.learning_rate
+        return lr * math.sqrt(1.0 - self.beta_2 ** t) / (1.0 - self.beta_1 ** t), float(self.weight_decay) * lr
+
+    def step_dev(self, hyper_dev):
+        """the same update with (lr_t, wd*lr) read from `hyper_dev` (2 device floats): capturable in a CUDA graph;
+        the caller advances `iterations`"""
+        e = self.eng
+        _lib.check(e.L.bfk_adam_step_dev(_lib.ptr(e.flat), _lib.ptr(e.grad), _lib.ptr(self.m), _lib.ptr(self.v),
+                                         C.c_void_p(e.seg_offsets.data_ptr()), e.n_seg, _lib.ptr(self._sq),
+                                         float(self.clipnorm or 0.0), _lib.ptr(hyper_dev), self.beta_1, self.beta_2,
+                                         self.epsilon, _lib.stream_ptr()), "bfk_adam_step_dev")
+        e.launches += 2 if self.clipnorm else 1
+
     def step(self):
         e = self.eng
         t = self.iterations + 1
@@ -292,29 +326,114 @@ def cosine_decay(initial_learning_rate, decay_steps, alpha=0.0):
 
 class Trainer:
     """TorchApproximator.train_step for the accelerated network (torch_approximator.py:62-113): zero grads,
-    compute_metrics, backward, (all-reduce), optimizer step - without autograd in the loop."""
+    compute_metrics, backward, (all-reduce), optimizer step - without autograd in the loop.
 
-    def __init__(self, net, optimizer=None, process_group=None, world_size=None):
+    cuda_graph=True captures the whole step (noise, forward, loss, backward, the NCCL all-reduce, Adam) once per batch
+    shape and replays it: ~85 kernel launches become one graph launch.  What changes from step to step (the noise / dropout
+    seed, lr_t of the schedule) is read by the kernels from a small device buffer that the host refreshes before each
+    replay.  Graph mode covers FlowMatching on tensor input with the default sampling (no optimal transport, no
+    sample_weight); anything else takes the eager path."""
+
+    def __init__(self, net, optimizer=None, process_group=None, world_size=None, cuda_graph=False, seed=None):
         self.net, self.eng = net, train_engine(net)
         self.opt = optimizer or Adam(net, 5e-4, clipnorm=1.5)
         self.group = process_group
         if world_size is None:
             world_size = torch.distributed.get_world_size(process_group) if torch.distributed.is_initialized() else 1
         self.world = world_size
+        self.rank = torch.distributed.get_rank(process_group) if self.world > 1 else 0
+        self.cuda_graph = bool(cuda_graph)
+        # one noise seed per step, identical on every rank: rank r draws rows [r*B, (r+1)*B) of the GLOBAL batch
+        self._seed0 = int(seed if seed is not None else torch.initial_seed()) & (2 ** 62 - 1)
+        self._step_no = 0
+        self._graphs = {}
+
+    def _step_seed(self):
+        return (self._seed0 * 0x9E3779B1 + 0x632BE59BD9B4E019 * (self._step_no + 1)) & (2 ** 63 - 1)
 
     def train_step(self, x, conditions=None, sample_weight=None, seed=None):
         """x: this rank's shard of the batch (or the (x0, x1, t, x, target) tuple).  Returns the GLOBAL mean loss as a
         0-d device tensor (after the all-reduce when world_size > 1)."""
+        if self.cuda_graph and torch.is_tensor(x) and sample_weight is None and seed is None \
+                and self.net._graphable_training():
+            return self._train_step_graph(x, conditions)
         net, eng = self.net, self.eng
         extra = {}
-        if self.world > 1 and torch.is_tensor(x):
-            # global row index of this rank's first row (DiffusionModel's low-discrepancy times, diffusion_model.py:159-161)
-            extra["row_offset"] = torch.distributed.get_rank(self.group) * x.shape[0]
-        loss = net._loss_and_grads(x, conditions, sample_weight, stage="training", seed=seed, world=self.world, **extra)
+        if torch.is_tensor(x):
+            # global row index of this rank's first row: noise, dropout masks and DiffusionModel's low-discrepancy times
+            # (diffusion_model.py:159-161) are functions of the GLOBAL row
+            extra["row_offset"] = self.rank * x.shape[0]
+            extra["noise_seed"] = self._step_seed()
+            if seed is None:
+                seed = self._step_seed()  # dropout masks: keyed by the step seed and the GLOBAL row (as in graph replay)
+        self._step_no += 1
+        loss = net._loss_and_grads(x, conditions, sample_weight, stage="training", seed=seed, world=self.world,
+                                   loss_into_slot=True, **extra)
         if self.world > 1:
-            # ONE bucket: gradients and the loss ride the same all-reduce (SUM); scaling by 1/B_global happened on device
-            buf = eng.grad
-            torch.distributed.all_reduce(buf, op=torch.distributed.ReduceOp.SUM, group=self.group)
-            torch.distributed.all_reduce(loss, op=torch.distributed.ReduceOp.SUM, group=self.group)
+            # ONE bucket: the gradients and the loss (last element) ride the same all-reduce (SUM); the scaling by
+            # 1/B_global happened on device
+            torch.distributed.all_reduce(eng.grad_ext, op=torch.distributed.ReduceOp.SUM, group=self.group)
         self.opt.step()
         return loss
+
+    # -- CUDA-graph replay ------------------------------------------------------------------------------------------------
+    def _train_step_graph(self, x, conditions):
+        net, eng, opt = self.net, self.eng, self.opt
+        key = (tuple(x.shape), None if conditions is None else tuple(conditions.shape))
+        g = self._graphs.get(key)
+        if g is None:
+            dev = eng.device
+            g = {"x": torch.empty_like(x, dtype=torch.float32),
+                 "c": None if conditions is None else torch.empty_like(conditions, dtype=torch.float32),
+                 # device words the kernels read: [0:2] seed (lo, hi), [2:4] lr_t, wd*lr; one pinned host mirror, one copy a step
+                 "params": torch.zeros(4, device=dev, dtype=torch.float32),
+                 "host": torch.zeros(4, dtype=torch.float32).pin_memory()}
+            g["seed_dev"], g["hyper_dev"] = g["params"][0:2], g["params"][2:4]
+
+            def body():
+                loss = net._loss_and_grads(g["x"], g["c"], None, stage="training", world=self.world, loss_into_slot=True,
+                                           row_offset=self.rank * x.shape[0], noise_seed=0, seed_dev=g["seed_dev"])
+                if self.world > 1:
+                    torch.distributed.all_reduce(eng.grad_ext, op=torch.distributed.ReduceOp.SUM, group=self.group)
+                opt.step_dev(g["hyper_dev"])
+                return loss
+
+            g["x"].copy_(x)
+            if conditions is not None:
+                g["c"].copy_(conditions)
+            self._refresh(g)
+            # warm-up on a side stream (workspace allocation, function attributes, NCCL), optimizer state restored after
+            saved = (eng.flat.clone(), opt.m.clone(), opt.v.clone())
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                for _ in range(2):
+                    body()
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            eng.flat.copy_(saved[0])
+            opt.m.copy_(saved[1])
+            opt.v.copy_(saved[2])
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                g["loss"] = body()
+            g["graph"] = graph
+            self._graphs[key] = g
+        g["x"].copy_(x, non_blocking=True)
+        if conditions is not None:
+            g["c"].copy_(conditions, non_blocking=True)
+        self._refresh(g)
+        g["graph"].replay()
+        self._step_no += 1
+        opt.iterations += 1
+        net._engine._key = None  # parameters changed in place: the sampler must re-pack its weight blob
+        return g["loss"]
+
+    def _refresh(self, g):
+        seed = self._step_seed()
+        lr_t, wd_lr = self.opt.hyper()
+        words = g["host"].view(torch.int32)
+        for i, w in enumerate((seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)):
+            words[i] = w - (1 << 32) if w >= (1 << 31) else w
+        g["host"][2], g["host"][3] = lr_t, wd_lr
+        g["params"].copy_(g["host"], non_blocking=True)

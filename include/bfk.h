@@ -180,6 +180,9 @@ typedef struct bfk_train_args {
   float loss_scale, grad_scale;
   uint64_t seed;
   float huber_c;           /* loss == 2 only */
+  const uint32_t* seed_dev; /* NULL, or 2 device words (lo, hi) that override `seed`: lets a captured CUDA graph of the step
+                               be replayed with a new dropout mask */
+  int64_t row_offset;      /* global index of row 0 (data-parallel shard): the dropout mask is a function of the global row */
 } bfk_train_args;
 size_t bfk_train_workspace_bytes(const bfk_net_config* cfg, int64_t B, int32_t backward);
 int bfk_train_step(const bfk_net_config* cfg, const bfk_weights* weights, const bfk_weights* grads,
@@ -211,6 +214,16 @@ int bfk_fm_interpolate(const float* x0, const float* x1, const float* t, int64_t
 int bfk_adam_step(float* params, const float* grads, float* m, float* v, const int64_t* seg_offsets, int32_t n_seg,
                   float* seg_sqnorm, float clipnorm, float lr_t, float beta1, float beta2, float eps, float wd_lr,
                   void* stream);
+/* the same step with the step-dependent scalars read from HBM (hyper_dev[0] = lr_t, hyper_dev[1] = weight_decay * lr),
+ * so that a captured CUDA graph of the whole training step can be replayed while the learning-rate schedule advances */
+int bfk_adam_step_dev(float* params, const float* grads, float* m, float* v, const int64_t* seg_offsets, int32_t n_seg,
+                      float* seg_sqnorm, float clipnorm, const float* hyper_dev, float beta1, float beta2, float eps,
+                      void* stream);
+/* FlowMatching.compute_metrics' sampling step (flow_matching.py:143-163) in one launch: x0 ~ N(0,1) (the bfk_normal_fill
+ * stream of `seed`), u ~ U(0,1) per GLOBAL row (row_offset + r), t = u^(1+alpha), x = t*x1 + (1-t)*x0, target = x1 - x0.
+ * seed_dev: NULL or 2 device words overriding seed (graph replay).  x0_out optional. */
+int bfk_fm_train_batch(const float* x1, int64_t B, int32_t D, int64_t row_offset, uint64_t seed, const uint32_t* seed_dev,
+                       float alpha, float* x0_out, float* t_out, float* x, float* target, void* stream);
 
 /* ---- layer-wise sampler: networks the fused on-chip kernel cannot hold (W > 256 or D > 8; BASELINE configs[3]) --------
  * Same contract as bfk_sample_fixed (integrate.py:217-288 driven by flow_matching.py:254-337 / diffusion_model.py:782-869)

@@ -232,19 +232,3 @@ def test_diffusion_validation_and_rng_paths():
     assert abs(got_i - ref_i) <= 2e-3 * abs(ref_i)
     loss = net.compute_metrics(x.cuda(), conditions=c.cuda())["loss"]  # device RNG path
     assert math.isfinite(float(loss)) and float(loss) > 0
-
-
-def test_fused_block_forward_is_parity_green_too(monkeypatch):
-    """BFK_TRAIN_FUSED=1 routes the block forward through train_block_gemm_kernel + train_norm_kernel
-    (csrc/bfk_train_fused.cuh); same gates as the default three-kernel forward."""
-    monkeypatch.setenv("BFK_TRAIN_FUSED", "1")
-    for D, C, widths, B in [(2, 32, (256,) * 5, 1000), (64, 32, (1024,) * 2, 300)]:
-        net, orc = make_pair(D, C, widths)
-        tup, c = make_batch(B, D, C)
-        ref_loss, ref = oracle_loss_and_grads(orc, tup, c)
-        loss = net.compute_metrics(cuda_tuple(tup), conditions=c.cuda(), stage="training")["loss"]
-        loss.backward()
-        assert abs(float(loss) - ref_loss) <= 2e-3 * abs(ref_loss)
-        for name, p in net.named_parameters():
-            if name in ref and ref[name] is not None:
-                assert rel_l2(p.grad, ref[name]) < TOL, (name, rel_l2(p.grad, ref[name]))
