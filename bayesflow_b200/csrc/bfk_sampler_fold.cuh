@@ -157,7 +157,7 @@ __device__ __forceinline__ uint4 fold_extras(float mu, float ir) {
 // UMMA issuer: for every evaluation and GEMM layer, for each of the two tiles, wait for the tile's A operand, stream the
 // W / FKC weight stages + the XK-row tail stage through the ring, commit to acc_ready.
 __device__ __forceinline__ void fold_issuer_loop(const SamplerArgs& a, const Bars& bars, uint32_t smem_base,
-                                                 uint32_t tmem_base, long long n_pairs, long long n_evals, int lane) {
+                                                 uint32_t tmem_base, long long my_tiles, long long n_evals, int lane) {
   const int W = a.W;
   const int n_chunks = W / FKC;
   if (lane == 0) {
@@ -166,10 +166,11 @@ __device__ __forceinline__ void fold_issuer_loop(const SamplerArgs& a, const Bar
     int stage = 0;
     const uint32_t a_lbo = TILE_M * 16, b_lbo = (uint32_t)W * 16;
     const uint32_t z_base = smem_base + a.plan.a_tile + TILES_PER_CTA * a.plan.a_bytes;  // shared zero K-chunk
-    for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+    for (long long j = 0; 2 * j < my_tiles; ++j) {
+      const int nt = (my_tiles - 2 * j) >= 2 ? 2 : 1;  // the last round of a CTA may hold a lone tile
       for (long long e = 0; e < n_evals; ++e) {
         for (int g = 0; g < a.NG; ++g) {
-          for (int t = 0; t < TILES_PER_CTA; ++t) {
+          for (int t = 0; t < nt; ++t) {
             mbar_wait(bars.a_ready(t), ph_a[t], a.err_flag, 3);
             ph_a[t] ^= 1;
             tc_fence_after();
@@ -208,16 +209,14 @@ __device__ __forceinline__ void fold_issuer_loop(const SamplerArgs& a, const Bar
 
 // Bulk-copy producer: per tile and layer W / FKC full stages + the XK-row tail (the layer is one contiguous byte range)
 __device__ __forceinline__ void fold_producer_loop(const SamplerArgs& a, const Bars& bars, uint32_t smem_base,
-                                                   long long n_pairs, long long n_evals, int lane) {
+                                                   long long my_tiles, long long n_evals, int lane) {
   const int W = a.W;
   const int n_chunks = W / FKC;
   if (lane == 0) {
     uint32_t ph_empty = 0;
     int stage = 0;
     long long q = 0, q_film = 0;
-    long long my_pairs = 0;
-    for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) ++my_pairs;
-    const long long Q = my_pairs * n_evals;
+    const long long Q = ((my_tiles + 1) / 2) * n_evals;
     const size_t layer_bytes = (size_t)(W + XK) * W * 2;
     auto load_film = [&](long long qq) {
       const int fb = (int)(qq & 1);
@@ -228,8 +227,9 @@ __device__ __forceinline__ void fold_producer_loop(const SamplerArgs& a, const B
     };
     if (Q > 0) { load_film(0); q_film = 1; }
     for (; q < Q; ++q) {
+      const int nt = (my_tiles - 2 * (q / n_evals)) >= 2 ? 2 : 1;
       for (int g = 0; g < a.NG; ++g) {
-        for (int t = 0; t < TILES_PER_CTA; ++t) {
+        for (int t = 0; t < nt; ++t) {
           for (int c = 0; c <= n_chunks; ++c) {
             mbar_wait(bars.w_empty(stage), ((ph_empty >> stage) & 1) ^ 1, a.err_flag, 6);
             ph_empty ^= (1u << stage);
@@ -280,8 +280,10 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
 
-  const long long rows_per_pair = TILES_PER_CTA * TILE_M;
-  const long long n_pairs = (a.B + rows_per_pair - 1) / rows_per_pair;
+  // 128-row tiles are dealt round-robin to the CTAs (tile ids c, c + G, c + 2G, ...) and taken two at a time, so CTA
+  // loads differ by at most ONE tile; a lone last tile runs without its ping-pong partner
+  const long long n_tiles = (a.B + TILE_M - 1) / TILE_M;
+  const long long my_tiles = (long long)blockIdx.x < n_tiles ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
   const long long n_evals = a.n_steps * (a.S - a.s0);
 
   if (warp < F_EPI_WARPS) {
@@ -306,8 +308,18 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
     unsigned char* sX = sA + (size_t)(W >> 3) * (TILE_M * 16);  // my row's extra K entries (K-chunk W/8)
     long long q = 0;   // evaluation sequence number of this CTA (film double buffer)
 
-    for (long long pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
-      const long long row = pair * rows_per_pair + tile * TILE_M + r;
+    for (long long j = 0; 2 * j < my_tiles; ++j) {
+      if (2 * j + tile >= my_tiles) {
+        // lone last tile of this CTA: my tile slot is empty; keep the per-evaluation table hand-shake going
+        for (long long e = 0; e < n_evals; ++e, ++q) {
+          const int fb = (int)(q & 1);
+          mbar_wait(bars.film_full(fb), (uint32_t)((q >> 1) & 1), a.err_flag, 1);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bars.film_empty(fb));
+        }
+        continue;
+      }
+      const long long row = ((long long)blockIdx.x + (2 * j + tile) * gridDim.x) * TILE_M + r;
       const bool valid = row < a.B;
       const long long grp = valid ? row / a.rows_per_group : 0;
       const float* g_pre = a.pre_add ? a.pre_add + grp * W : nullptr;
@@ -575,9 +587,9 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
     PROF_FLUSH(warp)
     tc_fence_before();
   } else if (warp == F_MMA_WARP) {
-    fold_issuer_loop(a, bars, smem_base, tmem_base, n_pairs, n_evals, lane);
+    fold_issuer_loop(a, bars, smem_base, tmem_base, my_tiles, n_evals, lane);
   } else {
-    fold_producer_loop(a, bars, smem_base, n_pairs, n_evals, lane);
+    fold_producer_loop(a, bars, smem_base, my_tiles, n_evals, lane);
   }
 
   __syncthreads();
