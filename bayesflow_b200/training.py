@@ -415,15 +415,18 @@ class Trainer:
             opt.m.copy_(saved[1])
             opt.v.copy_(saved[2])
             graph = torch.cuda.CUDAGraph()
+            l0 = eng.launches
             with torch.cuda.graph(graph):
                 g["loss"] = body()
-            g["graph"] = graph
+            g["graph"], g["launches"] = graph, eng.launches - l0  # kernels one replay executes
+            eng.launches = l0
             self._graphs[key] = g
         g["x"].copy_(x, non_blocking=True)
         if conditions is not None:
             g["c"].copy_(conditions, non_blocking=True)
         self._refresh(g)
         g["graph"].replay()
+        eng.launches += g["launches"]
         self._step_no += 1
         opt.iterations += 1
         net._engine._key = None  # parameters changed in place: the sampler must re-pack its weight blob

@@ -40,12 +40,19 @@ DEFAULT_WORKLOAD = "cfg2_sir_fm_euler100"
 EVALS_PER_STEP = {"euler": 1, "rk45": 6, "tsit5": 6}
 
 
-def workload_config(name, w, n_gpus):
-    return {"workload": name, "network": "FlowMatching" if w["model"] == "fm" else "DiffusionModel(edm,F)",
-            "subnet": f"time_mlp widths={w['widths'][0]}x{len(w['widths'])}", "D": w["D"], "C": w["C"],
-            "datasets_per_gpu": w["N"], "draws_per_dataset": w["S"], "solver": f"{w['method']} fixed {w['ode_steps']} steps",
-            "sharding": f"rows split by dataset over {n_gpus} GPU(s), no collective",
-            "l2": "state+conditions stream once per step; weights are L2-resident by design; 256 MB L2 flush between steps"}
+def workload_config(name, w, n_gpus, scaling="strong"):
+    cfg = {"workload": name, "network": "FlowMatching" if w["model"] == "fm" else "DiffusionModel(edm,F)",
+           "subnet": f"time_mlp widths={w['widths'][0]}x{len(w['widths'])}", "D": w["D"], "C": w["C"],
+           "draws_per_dataset": w["S"], "solver": f"{w['method']} fixed {w['ode_steps']} steps",
+           "l2": "state+conditions stream once per step; weights are L2-resident by design; 256 MB L2 flush between steps"}
+    if scaling == "strong":
+        cfg["datasets_total"] = w["N"]
+        cfg["sharding"] = (f"the {w['N']} datasets of the stated problem split over {n_gpus} GPU(s) by "
+                           "bayesflow_b200.parallel.sample_sharded (dataset_shard), no data-path collective")
+    else:
+        cfg["datasets_per_gpu"] = w["N"]
+        cfg["sharding"] = f"{w['N']} datasets per GPU on {n_gpus} GPU(s), no collective"
+    return cfg
 
 
 class ClockSampler:
@@ -194,13 +201,23 @@ def cpu_state_dict(w):
     return oracle.init_params(w["D"], w["C"] or None, w["widths"])
 
 
+CPU_SAMPLE_DATASETS = 16   # the SAME bounded sample in `cpu_baseline` and in `--impl reference`: the port's rate depends on
+                            # the working set (activations of n*S rows x 512 columns: 16 datasets = 33 MB per op), so the
+                            # sample is fixed, not calibrated to a time budget
+
+
+def cpu_sample_datasets(w):
+    # cfg3 (4000 draws per dataset) and cfg4 (wide net) are ~4x / ~20x heavier per dataset
+    per_ds = w["S"] * count_flops_per_eval(w["D"], w["C"], w["widths"])
+    return max(1, min(CPU_SAMPLE_DATASETS, int(CPU_SAMPLE_DATASETS * 1000 * 1020416 / per_ds)))
+
+
 def run_cpu_baseline(w, state_dict, budget_s=15.0):
     orc = make_oracle(w, state_dict)
     threads = os.cpu_count() or 1
-    rate, dt = cpu_rate(w, orc, 1, threads)  # calibration: one dataset
-    n = int(max(1, min(64, budget_s * rate / w["S"])))
-    if n > 1:
-        rate, dt = cpu_rate(w, orc, n, threads)
+    cpu_rate(w, orc, 1, threads)  # warm-up: one dataset
+    n = cpu_sample_datasets(w)
+    rate, dt = cpu_rate(w, orc, n, threads)
     return {"value": rate, "unit": "draws/s", "cores": threads, "kind": "port",
             "sample": f"{n} dataset(s) x {w['S']} draws of {w['method']}-{w['ode_steps']} ({dt:.1f} s); torch fp32 eager, "
                       f"torch.set_num_threads({threads})"}
@@ -213,9 +230,8 @@ def run_reference_arm(args, name, w):
     sd = cpu_state_dict(w)
     orc = make_oracle(w, sd)
     threads = os.cpu_count() or 1
-    rate, dt = cpu_rate(w, orc, 1, threads)
-    n = int(max(1, min(32, 10.0 * rate / w["S"])))  # ~10 s per step
-    for _ in range(max(args.warmup - 1, 0)):
+    n = cpu_sample_datasets(w)  # the same bounded sample as the `cpu_baseline` leg of the GPU arm
+    for _ in range(max(args.warmup, 1)):
         cpu_rate(w, orc, 1, threads)
     tot_rows, tot_t = 0, 0.0
     for _ in range(args.steps):
@@ -225,8 +241,8 @@ def run_reference_arm(args, name, w):
     value = tot_rows / tot_t
     line = {"impl": "reference", "metric": "posterior draws/sec", "value": value, "unit": "draws/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(name, w, args.gpus),
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(name, w, args.gpus, args.scaling),
             "cpu_baseline": {"value": value, "unit": "draws/s", "cores": threads, "kind": "port",
                              "sample": f"each step = {n} dataset(s) x {w['S']} draws of the workload on the host cores; the "
                                        "reference needs Keras (absent), so this is the oracle port of its torch-CPU path"},
@@ -261,28 +277,59 @@ def run_ours(args, name, w):
     state_cpu = {k: v.detach().clone() for k, v in net.state_dict().items() if "base_distribution" not in k}
     net.to(dev)
 
-    # ---- synthetic inputs: this rank's datasets (weak scaling: N datasets per GPU)
+    # ---- synthetic inputs
     N, S, D, Cd = w["N"], w["S"], w["D"], w["C"]
-    g = torch.Generator().manual_seed(2345 + rank)
-    cond_host = torch.randn(N, Cd, generator=g).pin_memory() if Cd else None
-    z_host = torch.randn(N * S, D, generator=g).pin_memory()
-    out_host = torch.empty(N * S, D).pin_memory()
-    cond_dev = cond_host.to(dev) if Cd else None
-    z_dev = z_host.to(dev)
+    strong = args.scaling == "strong"
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     ikw = dict(method=w["method"], steps=w["ode_steps"])
+    if strong:
+        # the STATED problem (N datasets x S draws) split over the ranks by dataset: every rank holds the (N, C) conditions
+        # (identical on all ranks) and draws its datasets' rows through bayesflow_b200.parallel.sample_sharded, i.e.
+        # InferenceNetwork.sample: z is generated in HBM (Philox keyed by the GLOBAL row) inside the timed call
+        from bayesflow_b200.parallel import dataset_shard, sample_sharded
+        lo, hi = dataset_shard(N, rank, world)
+        n_local = hi - lo
+        g = torch.Generator().manual_seed(2345)
+        cond_host = torch.randn(N, Cd, generator=g).pin_memory() if Cd else None
+        cond_dev = cond_host.to(dev) if Cd else None
+        out_host = torch.empty(max(n_local, 1) * S, D).pin_memory()
+        z_host = None
+        if not Cd:
+            raise SystemExit("bench.py: --scaling strong shards by dataset and needs a conditional workload")
 
-    def step_resident():
-        # the reference-facing call (InferenceNetwork.call(inverse=True)); conditions stay (N, C) + repeat count instead
-        # of the (N*S, C) tensor samplers.py:51-63 materialises
-        return net(z_dev, conditions=cond_dev, conditions_repeats=S if Cd else None, inverse=True, **ikw)
+        def step_resident():
+            return sample_sharded(net, S, cond_dev, seed=1234, global_step_control=False, **ikw)
 
-    def step_e2e():
-        c = cond_host.to(dev, non_blocking=True) if Cd else None
-        z = z_host.to(dev, non_blocking=True)
-        out = net(z, conditions=c, conditions_repeats=S if Cd else None, inverse=True, **ikw)
-        out_host.copy_(out, non_blocking=True)
-        return out
+        def step_e2e():
+            c = cond_host.to(dev, non_blocking=True)
+            out = sample_sharded(net, S, c, seed=1234, global_step_control=False, **ikw)
+            out_host[: n_local * S].copy_(out.reshape(-1, D), non_blocking=True)
+            return out
+        h2d_bytes = int(cond_host.numel() * 4)
+        d2h_bytes = int(n_local * S * D * 4)
+    else:
+        # weak scaling: N datasets per GPU, fixed z fed through InferenceNetwork.call(inverse=True)
+        n_local = N
+        g = torch.Generator().manual_seed(2345 + rank)
+        cond_host = torch.randn(N, Cd, generator=g).pin_memory() if Cd else None
+        z_host = torch.randn(N * S, D, generator=g).pin_memory()
+        out_host = torch.empty(N * S, D).pin_memory()
+        cond_dev = cond_host.to(dev) if Cd else None
+        z_dev = z_host.to(dev)
+
+        def step_resident():
+            # the reference-facing call (InferenceNetwork.call(inverse=True)); conditions stay (N, C) + repeat count instead
+            # of the (N*S, C) tensor samplers.py:51-63 materialises
+            return net(z_dev, conditions=cond_dev, conditions_repeats=S if Cd else None, inverse=True, **ikw)
+
+        def step_e2e():
+            c = cond_host.to(dev, non_blocking=True) if Cd else None
+            z = z_host.to(dev, non_blocking=True)
+            out = net(z, conditions=c, conditions_repeats=S if Cd else None, inverse=True, **ikw)
+            out_host.copy_(out, non_blocking=True)
+            return out
+        h2d_bytes = int(z_host.numel() * 4 + (cond_host.numel() * 4 if Cd else 0))
+        d2h_bytes = int(out_host.numel() * 4)
 
     def barrier():
         torch.cuda.synchronize()
@@ -329,7 +376,7 @@ def run_ours(args, name, w):
     # the approximator-shaped call: Sampler.sample with HOST (N, C) conditions, z drawn in HBM by
     # bfk_normal_fill, draws mapped back to the data scale by bfk_standardize, result copied to pinned host memory
     sampler_api = None
-    if Cd:
+    if Cd and world == 1 and not args.no_train:
         try:
             import bayesflow_b200 as bf
             stdz = bf.Standardize()
@@ -346,19 +393,19 @@ def run_ours(args, name, w):
                 return out
             s_ms, _, s_launches, _ = timed(step_sampler, args.steps, max(1, args.warmup // 2))
             sampler_api = {"call": "Sampler.sample(net, num_samples, conditions=(N, C) host) -> (N, S, D) host",
-                           "value": rows_total_fn(world, N, S, args.steps) / (s_ms * 1e-3), "unit": "draws/s",
+                           "value": world * N * S * args.steps / (s_ms * 1e-3), "unit": "draws/s",
                            "ms_per_step": s_ms / args.steps, "h2d_bytes_per_step": int(cond_host.numel() * 4),
                            "d2h_bytes_per_step": int(out3_host.numel() * 4), "gpu_launches": s_launches + 2 * args.steps}
         except Exception as exc:  # the headline line must not depend on the secondary one
             sampler_api = {"unavailable": repr(exc)[:200]}
 
-    rows_total = world * N * S * args.steps
+    rows_total = (N if strong else world * N) * S * args.steps
     value = rows_total / (total_ms * 1e-3)
     e2e_value = rows_total / (e2e_ms * 1e-3)
     fpd = flops_per_draw(w)
     peaks = measured_peaks()
     k_avg_ms = sum(kern_ms) / max(len(kern_ms), 1)
-    achieved = (N * S * fpd) / (k_avg_ms * 1e-3) / 1e12 if kern_ms else None
+    achieved = (n_local * S * fpd) / (k_avg_ms * 1e-3) / 1e12 if kern_ms else None
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -374,6 +421,22 @@ def run_ours(args, name, w):
         train["metric"] = "FlowMatching train samples/sec"
     is_layerwise = bool(net._engine.layerwise)
     wide = None
+    train_wide = None
+    if not args.no_train and world > 1 and name == DEFAULT_WORKLOAD:
+        # configs[3] and the wide training net at every N: same process group, same timing rules
+        del net
+        torch.cuda.empty_cache()
+        try:
+            wide = measure_sampling_simple(WORKLOADS["cfg4_wide_fm_euler100"], "cfg4_wide_fm_euler100", dev, world, rank, args.scaling)
+        except Exception as exc:
+            wide = {"unavailable": repr(exc)[:200]}
+        try:
+            torch.cuda.empty_cache()
+            tww = TRAIN_WORKLOADS["cfg5_fm_train_wide"]
+            train_wide = measure_training(tww, dev, world, rank, 5, 3, False)
+            train_wide["config"] = train_config("cfg5_fm_train_wide", tww, world)
+        except Exception as exc:
+            train_wide = {"unavailable": repr(exc)[:200]}
     if not args.no_train and world == 1 and name == DEFAULT_WORKLOAD:
         # configs[3] (wide subnet, 1M draws) measured in the same run as a secondary line: a fresh process of this script
         # with the same timing rules (3 warm-ups, L2 flush, device events), 2 timed steps of ~2.6 s
@@ -396,25 +459,77 @@ def run_ours(args, name, w):
             edge = {"unavailable": repr(exc)[:200]}
     if rank == 0:
         line = {"metric": "posterior draws/sec", "value": value, "unit": "draws/s", "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": args.scaling,
                 "vs_baseline": None, "dtype": "f16 tensor-core operands, f32 accumulate/state", "data": "synthetic",
-                "config": workload_config(name, w, world),
+                "config": workload_config(name, w, world, args.scaling),
                 "clocks": clk,
-                "e2e": {"value": e2e_value, "unit": "draws/s", "h2d_bytes_per_step": int(z_host.numel() * 4 + (cond_host.numel() * 4 if Cd else 0)),
-                        "d2h_bytes_per_step": int(out_host.numel() * 4), "ms_per_step": e2e_ms / args.steps},
+                "e2e": {"value": e2e_value, "unit": "draws/s", "h2d_bytes_per_step": h2d_bytes,
+                        "d2h_bytes_per_step": d2h_bytes, "ms_per_step": e2e_ms / args.steps,
+                        "call": ("bayesflow_b200.parallel.sample_sharded (InferenceNetwork.sample on this rank's datasets)"
+                                 if strong else "InferenceNetwork.call(z, conditions, inverse=True)")},
                 "gpu_launches": launches,
                 "roofline": {"bound": "tensor", "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",
                              "frac": (achieved / peaks["tflops"]) if achieved else None, "traffic": ncu_traffic(name),
                              "kernel": ("bfk::lw_block_gemm_kernel<0> (fused Dense+block epilogue, 83 % of the call) + x_proj/merge/out stages: all launches of one bfk_sample_layerwise call"
-                                        if is_layerwise else "bfk::sampler_kernel"), "kernel_ms": k_avg_ms, "kernel_share_of_step": k_avg_ms * args.steps / total_ms,
+                                        if is_layerwise else "bfk::sampler_fold_kernel"), "kernel_ms": k_avg_ms, "kernel_share_of_step": k_avg_ms * args.steps / total_ms,
                              "flop_per_draw_naive": fpd, "peak_source": peaks["source"],
-                             "hbm_gbs_algorithmic": (N * S * D * 8) / (k_avg_ms * 1e-3) / 1e9 if kern_ms else None},
+                             "hbm_gbs_algorithmic": (n_local * S * D * 8) / (k_avg_ms * 1e-3) / 1e9 if kern_ms else None},
                 "cpu_baseline": cpu,
                 "integration": info, "wall_s_timed_region": wall, "train": train, "wide_cfg4": wide,
+                "cfg5_fm_train_wide": train_wide,
                 "sampler_api": sampler_api, "edge_kernels": edge}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def measure_sampling_simple(w, name, dev, world, rank, scaling, steps=2, warmup=3):
+    """Secondary sampling line inside an existing process group (cfg4 at N > 1): device-timed, max over ranks."""
+    import torch
+    import torch.distributed as dist
+    import bayesflow_b200 as bf
+    from bayesflow_b200.parallel import dataset_shard, sample_sharded
+    torch.manual_seed(1234)
+    net = bf.FlowMatching(subnet_kwargs={"dropout": 0.0, "widths": w["widths"]})
+    net.build((None, w["D"]), (None, w["C"]))
+    net.to(dev)
+    N, S = w["N"], w["S"]
+    g = torch.Generator().manual_seed(2345)
+    cond = torch.randn(N, w["C"], generator=g).to(dev)
+    ikw = dict(method=w["method"], steps=w["ode_steps"])
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    if scaling == "strong":
+        fn = lambda: sample_sharded(net, S, cond, seed=1234, global_step_control=False, **ikw)  # noqa: E731
+        rows = N * S
+    else:
+        fn = lambda: bf.Sampler().sample(net, S, conditions=cond, seed=1234 + rank, **ikw)  # noqa: E731
+        rows = world * N * S
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    pairs = []
+    for _ in range(steps):
+        flush.fill_(1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        pairs.append((a, b))
+    torch.cuda.synchronize()
+    ms = sum(a.elapsed_time(b) for a, b in pairs)
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    fpd = flops_per_draw(w)
+    peaks = measured_peaks()
+    achieved = rows * steps * fpd / (ms * 1e-3) / 1e12 / world
+    return {"metric": "posterior draws/sec", "value": rows * steps / (ms * 1e-3), "unit": "draws/s", "ms_per_step": ms / steps,
+            "steps": steps, "warmup": warmup, "scaling": scaling, "config": workload_config(name, w, world, scaling),
+            "roofline": {"bound": "tensor", "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",
+                         "frac": achieved / peaks["tflops"], "note": "per GPU, whole call (all launches of bfk_sample_layerwise)"}}
 
 
 # --------------------------------------------------------------------------------------------------- training arms
@@ -483,7 +598,8 @@ def measure_training(w, dev, world, rank, steps, warmup, want_cpu):
     net = bf.FlowMatching(subnet_kwargs={"dropout": w["dropout"], "widths": w["widths"]})
     net.build((None, w["D"]), (None, w["C"]))
     net.to(dev)
-    tr = Trainer(net, Adam(net, cosine_decay(5e-4, 10000), clipnorm=1.5), world_size=world)
+    tr = Trainer(net, Adam(net, cosine_decay(5e-4, 10000), clipnorm=1.5), world_size=world,
+                 cuda_graph=os.environ.get("BFK_TRAIN_GRAPH", "1") != "0")
     Bl = w["batch"] // world
     g = torch.Generator().manual_seed(4567 + rank)
     x_host = torch.randn(Bl, w["D"], generator=g).pin_memory()
@@ -586,6 +702,9 @@ def main():
     ap.add_argument("--no-train", action="store_true", help="skip the short training measurement added to the default line")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="strong (default): the stated N x S problem is split over the ranks by dataset (sample_sharded); "
+                         "weak: N datasets per GPU")
     args = ap.parse_args()
     if args.workload in TRAIN_WORKLOADS:
         w = TRAIN_WORKLOADS[args.workload]
