@@ -90,6 +90,7 @@ def lib():
                                     C.c_void_p, C.c_void_p]
     L.bfk_gemm.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
                            C.c_int32, C.c_int32, C.c_void_p, C.c_float, C.c_int32, C.c_void_p]
+    L.bfk_detect_repeats.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]
     L.bfk_normal_fill.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_uint64,
                                   C.c_void_p, C.c_void_p]
     L.bfk_standardize.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
@@ -108,6 +109,9 @@ def lib():
     L.bfk_ot_init.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_float, C.c_int64, C.c_void_p]
     L.bfk_ot_log_sinkhorn_step.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
+    L.bfk_ot_plain_mode.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+    L.bfk_ot_sample_plan.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
+                                     C.c_uint64, C.c_void_p, C.c_void_p]
     L.bfk_ot_sample.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_uint64, C.c_void_p, C.c_void_p]
     _lib = L
     return L

@@ -371,6 +371,32 @@ __global__ void __launch_bounds__(256) fm_train_batch_kernel(const float* __rest
 }
 
 
+
+// conditions (B, C) as the reference's Sampler materialises them (samplers.py:51-63: each dataset's row repeated
+// num_samples times): find the repeat count WITHOUT a sort / unique pass.  out[0] = index of the first row that differs
+// from row 0 (B if none); out[1] = 0 iff every row equals the first row of its length-out[0] group.
+__global__ void first_diff_kernel(const float* __restrict__ c, long long B, int C, long long* __restrict__ out) {
+  long long best = B;
+  for (long long r = 1 + (long long)blockIdx.x * blockDim.x + threadIdx.x; r < B; r += (long long)gridDim.x * blockDim.x) {
+    if (r >= best) break;
+    bool diff = false;
+    for (int j = 0; j < C; ++j) diff |= (c[r * C + j] != c[j]);
+    if (diff) { best = r; break; }
+  }
+  if (best < B) atomicMin(reinterpret_cast<unsigned long long*>(out), (unsigned long long)best);
+}
+__global__ void verify_groups_kernel(const float* __restrict__ c, long long B, int C, long long* __restrict__ out) {
+  const long long R = out[0];
+  if (R <= 0 || R >= B || (B % R) != 0) { if (blockIdx.x == 0 && threadIdx.x == 0 && R < B) out[1] = 1; return; }
+  bool bad = false;
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < B; r += (long long)gridDim.x * blockDim.x) {
+    const long long g0 = (r / R) * R;
+    if (g0 == r) continue;
+    for (int j = 0; j < C; ++j) bad |= (c[r * C + j] != c[g0 * C + j]);
+  }
+  if (bad) out[1] = 1;
+}
+
 }  // namespace bfk
 
 // ---- C ABI ------------------------------------------------------------------------------------------------------------
@@ -469,6 +495,20 @@ extern "C" int bfk_fm_train_batch(const float* x1, int64_t B, int32_t D, int64_t
   if (!x1 || !t_out || !x || !target || B <= 0 || D <= 0 || row_offset < 0) return fail(-83, "bfk_fm_train_batch: bad arguments");
   bfk::fm_train_batch_kernel<<<cdiv((size_t)B, 256), 256, 0, (cudaStream_t)stream_>>>(x1, B, D, row_offset, (unsigned long long)seed, seed_dev,
                                                                                alpha, x0_out, t_out, x, target);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_detect_repeats(const float* cond, int64_t B, int32_t C, int64_t* out2, void* stream_) {
+  if (!cond || !out2 || B <= 0 || C <= 0) return fail(-84, "bfk_detect_repeats: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream_;
+  const long long init[2] = {(long long)B, 0};
+  CK(cudaMemcpyAsync(out2, init, sizeof(init), cudaMemcpyHostToDevice, st));
+  int sms = bfk_num_sms();
+  if (sms <= 0) sms = 148;
+  const unsigned grid = (unsigned)((B + 255) / 256 < (long long)sms * 8 ? (B + 255) / 256 : (long long)sms * 8);
+  bfk::first_diff_kernel<<<grid, 256, 0, st>>>(cond, B, C, (long long*)out2);
+  bfk::verify_groups_kernel<<<grid, 256, 0, st>>>(cond, B, C, (long long*)out2);
   CK(cudaGetLastError());
   return 0;
 }

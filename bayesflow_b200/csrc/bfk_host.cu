@@ -77,6 +77,14 @@ extern "C" size_t bfk_table_stride(const bfk_net_config* c) {
 
 static inline unsigned cdiv(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
 
+// cudaFuncSetAttribute is per device: cache "already set" per device id, not per process
+static inline bool* attr_flag(bool* flags) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+  return flags + dev;
+}
+
+
 extern "C" int bfk_pack(const bfk_net_config* c, const bfk_weights* w, void* packed, void* stream_) {
   if (int r = check_cfg(c)) return r;
   if (!w || !packed) return fail(-10, "null pointer");
@@ -449,7 +457,8 @@ extern "C" int bfk_gemm(const void* A, const void* B, float* Cm, int64_t ldc, in
   if (use_persist < 0) { const char* e = getenv("BFK_GEMM_PERSIST"); use_persist = e ? atoi(e) : 1; }
   if (use_persist && k_splits == 1 && !(flags & GEMM_ATOMIC) && (K % P_KC) == 0) {
     // persistent, double-buffered-accumulator kernel: whenever there is no split-K
-    static bool p_attr = false;
+    static bool p_attr_dev[64] = {};
+    bool& p_attr = *attr_flag(p_attr_dev);
     if (!p_attr) {
       CK(cudaFuncSetAttribute(gemm_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_persist_smem_bytes(256)));
       p_attr = true;
@@ -463,7 +472,8 @@ extern "C" int bfk_gemm(const void* A, const void* B, float* Cm, int64_t ldc, in
     return 0;
   }
   const size_t sh = gemm_smem_bytes(NT);
-  static bool attr_set = false;
+  static bool attr_set_dev[64] = {};
+  bool& attr_set = *attr_flag(attr_set_dev);
   if (!attr_set) {
     CK(cudaFuncSetAttribute(gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_smem_bytes(256)));
     attr_set = true;

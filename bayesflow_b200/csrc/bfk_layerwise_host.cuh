@@ -114,7 +114,8 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
                                                                        ln ? w->norm_b[L - 1] : nullptr, w->out_b, 64, b.wo_pk,
                                                                        b.gcol_o, b.ccol_o);
     CK(cudaGetLastError());
-    static bool attr = false;
+    static bool attr_dev[64] = {};
+    bool& attr = *attr_flag(attr_dev);
     if (!attr) {
       const int sm = (int)lw_fused_smem_bytes(256);
       CK(cudaFuncSetAttribute(lw_block_gemm_kernel<LWF_BLOCK, -1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));

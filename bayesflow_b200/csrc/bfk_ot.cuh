@@ -11,7 +11,18 @@
 
 namespace bfk {
 
-enum { OT_ERR = 0, OT_STEPS = 1, OT_DONE = 2, OT_ATOL = 3, OT_MAX_STEPS = 4, OT_ACC = 5, OT_CTRL_FLOATS = 8 };
+enum { OT_ERR = 0, OT_STEPS = 1, OT_DONE = 2, OT_ATOL = 3, OT_MAX_STEPS = 4, OT_ACC = 5, OT_PLAIN = 6, OT_SHIFT = 7,
+       OT_CTRL_FLOATS = 8 };
+// Plain Sinkhorn-Knopp (utils/optimal_transport/sinkhorn.py:117-160) on the same sweeps: the multiplicative scalings u, v
+// are kept as logs (U = log u, V = log v; K = exp(S - max S)), so nothing under- or overflows, and the reference's `tiny`
+// terms and its error metric are applied exactly:  sum_j K_ij v_j + tiny = exp(logaddexp(L_i - shift, log tiny)),
+// err = max(max_i |log((u' + tiny)/(u + tiny))|, max_j |log((v' + tiny)/(v + tiny))|).
+__device__ __forceinline__ float log_add_exp(float a, float b) {
+  const float hi = fmaxf(a, b), lo = fminf(a, b);
+  if (hi == -INFINITY) return -INFINITY;
+  return hi + log1pf(__expf(lo - hi));
+}
+#define OT_LOG_TINY (-27.631021115928547f) /* log(1e-12) */
 
 // M[i,j] = max(|a_i|^2 + |b_j|^2 - 2 a_i.b_j, 0)  (ot_utils.py:6-16);  cosine: 1 - clip(a_i.b_j / ((|a_i|+eps)(|b_j|+eps)))
 template <bool COSINE>
@@ -110,8 +121,15 @@ __global__ void __launch_bounds__(256) ot_row_lse_kernel(const float* __restrict
     mx = a, sm = b;
   }
   if (lane == 0) {
-    const float un = (log_a_vec ? log_a_vec[i] : log_a) - (mx + logf(sm));
-    const float d = fabsf(un - u[i]);
+    const float la = log_a_vec ? log_a_vec[i] : log_a;
+    float un, d;
+    if (ctrl[OT_PLAIN] != 0.f) {
+      un = la - log_add_exp(mx + logf(sm) - ctrl[OT_SHIFT], OT_LOG_TINY);
+      d = fabsf(log_add_exp(un, OT_LOG_TINY) - log_add_exp(u[i], OT_LOG_TINY));
+    } else {
+      un = la - (mx + logf(sm));
+      d = fabsf(un - u[i]);
+    }
     u[i] = un;
     atomicMax(reinterpret_cast<unsigned int*>(ctrl + OT_ACC), __float_as_uint(d == d ? d : INFINITY));
   }
@@ -138,13 +156,33 @@ __global__ void __launch_bounds__(256) ot_col_partial_kernel(const float* __rest
 // stage 2: chunks merged in index order; v_next[j] = log_b - logsumexp  (log_sinkhorn.py:133)
 __global__ void __launch_bounds__(256) ot_col_finish_kernel(const float* __restrict__ part, int chunks, long long m, float log_b,
                                                             const float* __restrict__ log_b_vec, float* __restrict__ v,
-                                                            const float* __restrict__ ctrl) {
+                                                            float* __restrict__ ctrl) {
   if (ctrl[OT_DONE] != 0.f) return;
   const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= m) return;
   float mx = -INFINITY, sm = 0.f;
   for (int c = 0; c < chunks; ++c) lse_merge(mx, sm, part[((long long)c * 2) * m + j], part[((long long)c * 2 + 1) * m + j]);
-  v[j] = (log_b_vec ? log_b_vec[j] : log_b) - (mx + logf(sm));
+  const float lb = log_b_vec ? log_b_vec[j] : log_b;
+  if (ctrl[OT_PLAIN] != 0.f) {
+    const float vn = lb - log_add_exp(mx + logf(sm) - ctrl[OT_SHIFT], OT_LOG_TINY);
+    const float d = fabsf(log_add_exp(vn, OT_LOG_TINY) - log_add_exp(v[j], OT_LOG_TINY));
+    v[j] = vn;
+    atomicMax(reinterpret_cast<unsigned int*>(ctrl + OT_ACC), __float_as_uint(d == d ? d : INFINITY));
+  } else {
+    v[j] = lb - (mx + logf(sm));
+  }
+}
+// max of a matrix into ctrl[OT_SHIFT] and the plain-mode flag (the shift of K = exp(S - max S), sinkhorn.py:119)
+__global__ void __launch_bounds__(256) ot_max_kernel(const float* __restrict__ S, long long numel, float* __restrict__ ctrl) {
+  float mx = -INFINITY;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < numel; e += (long long)gridDim.x * blockDim.x)
+    mx = fmaxf(mx, S[e]);
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if ((threadIdx.x & 31) == 0) {  // float max through the ordered-int trick (values may be negative)
+    int* addr = reinterpret_cast<int*>(ctrl + OT_SHIFT);
+    if (mx >= 0.f) atomicMax(addr, __float_as_int(mx));
+    else atomicMin(reinterpret_cast<unsigned int*>(addr), __float_as_uint(mx));
+  }
 }
 // loop bookkeeping of keras.ops.while_loop(cond, body, ..., maximum_iterations)  (log_sinkhorn.py:125-141)
 __global__ void ot_ctrl_kernel(float* __restrict__ ctrl) {
@@ -158,9 +196,12 @@ __global__ void ot_ctrl_kernel(float* __restrict__ ctrl) {
 
 // assignments[i] ~ Categorical(softmax_j(S[i,j] + u[i] + v[j]))  (log_sinkhorn.py:33-35) by the Gumbel-max trick:
 // argmax_j S[i,j] + v[j] - log(-log U_ij), U_ij = word (i*m+j) of the Philox stream keyed by seed; ties -> smallest j.
+// u == nullptr: logits S_ij + v_j (+ a per-row constant).  u != nullptr (plain Sinkhorn, sinkhorn.py:60-62): logits
+// log(plan_ij + 1e-10) with plan_ij = exp(u_i + S_ij - shift + v_j).
 __global__ void __launch_bounds__(256) ot_sample_kernel(const float* __restrict__ S, long long ld, const float* __restrict__ v,
                                                         long long n, long long m, unsigned long long seed,
-                                                        long long* __restrict__ out) {
+                                                        long long* __restrict__ out, const float* __restrict__ u = nullptr,
+                                                        const float* __restrict__ ctrl = nullptr) {
   const int lane = threadIdx.x & 31;
   const long long i = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (i >= n) return;
@@ -171,7 +212,9 @@ __global__ void __launch_bounds__(256) ot_sample_kernel(const float* __restrict_
     uint32_t c[4] = {(uint32_t)(e >> 2), (uint32_t)(e >> 34), 0u, 0u};
     philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
     const float g = -logf(-logf(u01(c[e & 3])));
-    const float val = S[i * ld + j] + v[j] + g;
+    float val = S[i * ld + j] + v[j];
+    if (u) val = logf(__expf(val + u[i] - ctrl[OT_SHIFT]) + 1e-10f);
+    val += g;
     if (val > best) { best = val; arg = j; }
   }
   for (int o = 16; o > 0; o >>= 1) {
@@ -257,6 +300,30 @@ extern "C" int bfk_ot_log_sinkhorn_step(const float* S, int64_t n, int64_t m, co
     bfk::ot_col_finish_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(work, chunks, m, log_b, log_b_vec, v, ctrl);
     bfk::ot_ctrl_kernel<<<1, 1, 0, st>>>(ctrl);
   }
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_ot_plain_mode(const float* S, int64_t numel, float* ctrl, void* stream) {
+  if (!S || !ctrl || numel < 1) return fail(-92, "bfk_ot_plain_mode: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  const float init[2] = {1.0f, -INFINITY};  // ctrl[OT_PLAIN] = 1, ctrl[OT_SHIFT] = -inf (max identity)
+  CK(cudaMemcpyAsync(ctrl + bfk::OT_PLAIN, init, sizeof(init), cudaMemcpyHostToDevice, st));
+  CK(cudaStreamSynchronize(st));
+  const int sms = bfk_num_sms();
+  long long blocks = (numel + 255) / 256, cap = (long long)(sms > 0 ? sms : 148) * 8;
+  if (blocks > cap) blocks = cap;
+  bfk::ot_max_kernel<<<(unsigned)blocks, 256, 0, st>>>(S, numel, ctrl);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_ot_sample_plan(const float* S, int64_t ld, const float* u, const float* v, const float* ctrl, int64_t n,
+                                  int64_t m, uint64_t seed, int64_t* assignments, void* stream) {
+  if (n < 1 || m < 1 || ld < m) return fail(-90, "bfk_ot_sample_plan: bad n/m/ld");
+  if (!S || !u || !v || !ctrl || !assignments) return fail(-91, "bfk_ot_sample_plan: null pointer");
+  bfk::ot_sample_kernel<<<(unsigned)((n + 7) / 8), 256, 0, (cudaStream_t)stream>>>(S, ld, v, n, m, (unsigned long long)seed,
+                                                                                  (long long*)assignments, u, ctrl);
   CK(cudaGetLastError());
   return 0;
 }

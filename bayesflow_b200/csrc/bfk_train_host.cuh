@@ -106,7 +106,8 @@ int launch_gemm_dw(const unsigned char* X, int XK8, const unsigned char* Y, int 
   a.tiles_per_split = (a.n_btiles + splits - 1) / splits;
   splits = (a.n_btiles + a.tiles_per_split - 1) / a.tiles_per_split;
   a.idesc = umma_idesc_f16_mn(G_TM, a.NT, 0);
-  static bool attr_set = false;
+  static bool attr_set_dev[64] = {};
+  bool& attr_set = *attr_flag(attr_set_dev);
   if (!attr_set) {
     CK(cudaFuncSetAttribute(gemm_dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_dw_smem_bytes(128)));
     attr_set = true;

@@ -13,6 +13,7 @@ can be exchanged with a Keras ``FlowMatching`` via get_weights()/set_weights() (
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import math
 from collections.abc import Sequence
@@ -308,9 +309,17 @@ class _Engine:
                 raise ValueError(f"conditions has {cond.shape[0]} rows, expected {B}")
             repeats = 1
             if net.detect_repeats and B > 1:
-                uniq, counts = torch.unique_consecutive(cond, dim=0, return_counts=True)
-                if uniq.shape[0] < B and bool((counts == counts[0]).all()):
-                    cond, repeats = uniq, int(counts[0])
+                # the reference's Sampler hands over each dataset's conditions repeated num_samples times: recover
+                # (datasets, repeats) with two streaming launches (no sort / unique pass over the (N*S, C) tensor)
+                cond = cond.contiguous()
+                out2 = torch.empty(2, device=cond.device, dtype=torch.int64)
+                with torch.cuda.device(cond.device):
+                    _lib.check(_lib.lib().bfk_detect_repeats(_lib.ptr(cond), B, net._C, _lib.ptr(out2), _lib.stream_ptr()),
+                               "bfk_detect_repeats")
+                self.launches += 2
+                R, bad = (int(v) for v in out2.tolist())
+                if not bad and 1 < R <= B and B % R == 0:
+                    cond, repeats = cond[::R], R
         elif cond.shape[0] * repeats != B:
             raise ValueError(f"conditions rows ({cond.shape[0]}) x repeats ({repeats}) != batch ({B})")
         return cond.contiguous(), repeats
@@ -561,10 +570,23 @@ class InferenceNetwork(nn.Module):
         self._metrics = []
         self._engine = _Engine(self)
 
+    def _device_guard(self, *tensors):
+        """The C ABI launches on the CURRENT device's stream: make the tensors' device current for the call, so a
+        network on cuda:1 works while cuda:0 is current (one process driving several GPUs)."""
+        for t in tensors:
+            if torch.is_tensor(t) and t.is_cuda:
+                return torch.cuda.device(t.device)
+        for p in self.parameters():
+            if p.is_cuda:
+                return torch.cuda.device(p.device)
+            break
+        return contextlib.nullcontext()
+
     def call(self, xz, conditions=None, inverse=False, density=False, training=False, **kwargs):
-        if inverse:
-            return self._inverse(xz, conditions=conditions, density=density, training=training, **kwargs)
-        return self._forward(xz, conditions=conditions, density=density, training=training, **kwargs)
+        with self._device_guard(xz):
+            if inverse:
+                return self._inverse(xz, conditions=conditions, density=density, training=training, **kwargs)
+            return self._forward(xz, conditions=conditions, density=density, training=training, **kwargs)
 
     forward = call
 
@@ -600,9 +622,10 @@ class InferenceNetwork(nn.Module):
         gradient; ``loss.backward()`` then fills ``p.grad`` exactly like the reference's autograd path."""
         from .training import _LossWithGrads, train_engine
         backward = torch.is_grad_enabled() and stage == "training"
-        extra = {k: kwargs[k] for k in ("fixed", "row_offset", "ot_seed") if k in kwargs}
-        loss = self._loss_and_grads(x, conditions, sample_weight, stage=stage, seed=kwargs.get("seed"), backward=backward,
-                                    **extra)
+        extra = {k: kwargs[k] for k in ("fixed", "row_offset", "ot_seed", "noise_seed") if k in kwargs}
+        with self._device_guard(x[1] if isinstance(x, (tuple, list)) else x):
+            loss = self._loss_and_grads(x, conditions, sample_weight, stage=stage, seed=kwargs.get("seed"),
+                                        backward=backward, **extra)
         if backward:
             eng = train_engine(self)
             loss = _LossWithGrads.apply(loss, eng, *eng.params)
@@ -742,8 +765,9 @@ class FlowMatching(InferenceNetwork):
             if time.numel() != 1 and not bool((time == time.reshape(-1)[0]).all()):
                 raise NotImplementedError("per-row time is only used by the training path (compute_metrics)")
             time = float(time.reshape(-1)[0])
-        run = self._run(conditions, xz.shape[0], kwargs)
-        return run.velocity(xz, float(np.float32(time)))
+        with self._device_guard(xz):
+            run = self._run(conditions, xz.shape[0], kwargs)
+            return run.velocity(xz, float(np.float32(time)))
 
     # -- training (flow_matching.py:132-178) ------------------------------------------------------------------------------
     def _graphable_training(self):

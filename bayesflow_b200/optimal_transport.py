@@ -3,7 +3,8 @@ and log_sinkhorn.py:14-172 behind the same names and arguments, on the `bfk_ot_*
 
 Supported: method "log_sinkhorn" / "log_sinkhorn_knopp" (the FlowMatching default, networks/defaults.py:54-63), balanced
 and partial (`partial_factor < 1`, ot_utils.py:37-92) marginals, squared-Euclidean cost, conditional cost weighting
-(`condition_ratio < 0.5`, ot_utils.py:95-164).  The un-stabilised "sinkhorn" method raises NotImplementedError."""
+(`condition_ratio < 0.5`, ot_utils.py:95-164), and the multiplicative "sinkhorn" / "sinkhorn_knopp" method
+(sinkhorn.py:14-186) on the same device sweeps."""
 from __future__ import annotations
 
 import ctypes as C
@@ -64,8 +65,9 @@ def search_for_conditional_weight(M, Cm, condition_ratio, initial_w=1.0, max_ite
 
 
 def log_sinkhorn_plan(x1, x2, conditions=None, regularization: float = 1.0, atol: float = 1e-5, max_steps: int = 1000,
-                      condition_ratio: float = 0.5, partial_factor: float = 1.0, _parts=False, **kwargs):
-    """log_sinkhorn.py:38-172 -> (n, m) log transport plan."""
+                      condition_ratio: float = 0.5, partial_factor: float = 1.0, _parts=False, _plain=False, **kwargs):
+    """log_sinkhorn.py:38-172 -> (n, m) log transport plan.  `_plain`: the multiplicative Sinkhorn-Knopp of
+    sinkhorn.py:65-186 (same sweeps, its `tiny` terms and error metric; see csrc/bfk_ot.cuh)."""
     if not (0.0 < partial_factor <= 1.0):
         raise ValueError(f"s must be in (0, 1] for partial OT, got {partial_factor}")
     partial = partial_factor < 1.0
@@ -104,6 +106,8 @@ def log_sinkhorn_plan(x1, x2, conditions=None, regularization: float = 1.0, atol
     work = torch.empty(max(1, L.bfk_ot_work_floats(n, m)), device=dev, dtype=torch.float32)
     _lib.check(L.bfk_ot_init(_lib.ptr(ctrl), _lib.ptr(u), _lib.ptr(v), n, m, float(atol), int(max_steps), _lib.stream_ptr()),
                "bfk_ot_init")
+    if _plain:
+        _lib.check(L.bfk_ot_plain_mode(_lib.ptr(S), S.numel(), _lib.ptr(ctrl), _lib.stream_ptr()), "bfk_ot_plain_mode")
     done = max_steps <= 0
     enq = 0
     while not done:
@@ -115,7 +119,9 @@ def log_sinkhorn_plan(x1, x2, conditions=None, regularization: float = 1.0, atol
         done = state[2] != 0.0 or enq >= max_steps
     log_sinkhorn_plan.last_info = {"steps": int(ctrl[1].item()), "err": float(ctrl[0].item()), "w": w}
     if _parts:
-        return S, u, v, n0, m0
+        return (S, u, v, n0, m0, ctrl) if _plain else (S, u, v, n0, m0)
+    if _plain:
+        return (S - ctrl[7] + u.unsqueeze(1) + v.unsqueeze(0))[:n0, :m0]
     return (S + u.unsqueeze(1) + v.unsqueeze(0))[:n0, :m0]
 
 
@@ -133,12 +139,26 @@ def log_sinkhorn(x1, x2, conditions=None, seed=None, **kwargs):
     return out
 
 
-def _not_on_path(*args, **kwargs):
-    raise NotImplementedError('method "sinkhorn" (un-stabilised) is outside the accelerated path; use "log_sinkhorn", the '
-                              "FlowMatching default")
+def sinkhorn_plan(x1, x2, conditions=None, **kwargs):
+    """sinkhorn.py:65-186 -> (n, m) transport plan (probabilities)."""
+    return torch.exp(log_sinkhorn_plan(x1, x2, conditions=conditions, _plain=True, **kwargs))
 
 
-methods = {"sinkhorn": _not_on_path, "sinkhorn_knopp": _not_on_path, "log_sinkhorn": log_sinkhorn,
+def sinkhorn(x1, x2, conditions=None, seed=None, **kwargs):
+    """sinkhorn.py:14-62 -> (n,) int64 indices into x2, drawn from Categorical(log(plan + 1e-10))."""
+    S, u, v, n, m, ctrl = log_sinkhorn_plan(x1, x2, conditions=conditions, _parts=True, _plain=True, **kwargs)
+    if isinstance(seed, torch.Generator):
+        seed = int(torch.randint(0, 2 ** 62, (1,), generator=seed, device=seed.device).item())
+    elif seed is None:
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+    out = torch.empty(n, device=S.device, dtype=torch.int64)
+    _lib.check(_lib.lib().bfk_ot_sample_plan(_lib.ptr(S), S.shape[1], _lib.ptr(u), _lib.ptr(v), _lib.ptr(ctrl), n, m,
+                                             C.c_uint64(int(seed) & (2 ** 64 - 1)), C.c_void_p(out.data_ptr()),
+                                             _lib.stream_ptr()), "bfk_ot_sample_plan")
+    return out
+
+
+methods = {"sinkhorn": sinkhorn, "sinkhorn_knopp": sinkhorn, "log_sinkhorn": log_sinkhorn,
            "log_sinkhorn_knopp": log_sinkhorn}
 
 

@@ -354,6 +354,10 @@ class Trainer:
     def train_step(self, x, conditions=None, sample_weight=None, seed=None):
         """x: this rank's shard of the batch (or the (x0, x1, t, x, target) tuple).  Returns the GLOBAL mean loss as a
         0-d device tensor (after the all-reduce when world_size > 1)."""
+        with torch.cuda.device(self.eng.device):
+            return self._train_step(x, conditions, sample_weight, seed)
+
+    def _train_step(self, x, conditions, sample_weight, seed):
         if self.cuda_graph and torch.is_tensor(x) and sample_weight is None and seed is None \
                 and self.net._graphable_training():
             return self._train_step_graph(x, conditions)

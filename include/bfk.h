@@ -265,6 +265,10 @@ int bfk_standardize(const float* x, float* out, int64_t rows, int32_t F, const f
 /* out[i] = a*x[i] + b*y[i] + c*z[i] (y, z may be NULL; out may alias any input): the state updates of the
  * ConsistencyModel multistep sampler (consistency_model.py:300-306: x_n = x + sqrt(t_n^2 - eps^2) * noise) and of its
  * consistency function (:336-342: c_skip(t) * x + c_out(t) * f). */
+/* conditions (B, C) with each dataset's row repeated (samplers.py:51-63): out2[0] = rows per dataset (index of the first
+ * row that differs from row 0; B if all rows are equal), out2[1] = 0 iff every row equals the first row of its group and
+ * out2[0] divides B.  Two streaming launches; replaces a sort-based unique pass over the materialised conditions. */
+int bfk_detect_repeats(const float* conditions, int64_t B, int32_t C, int64_t* out2, void* stream);
 int bfk_lincomb3(float* out, float a, const float* x, float b, const float* y, float c, const float* z, int64_t numel,
                  void* stream);
 size_t bfk_moments_workspace_floats(int64_t rows, int32_t F);
@@ -294,6 +298,13 @@ size_t bfk_ot_work_floats(int64_t n, int64_t m);
 int bfk_ot_init(float* ctrl, float* u, float* v, int64_t n, int64_t m, float atol, int64_t max_steps, void* stream);
 int bfk_ot_log_sinkhorn_step(const float* S, int64_t n, int64_t m, const float* log_a_vec, const float* log_b_vec,
                              float* u, float* v, float* ctrl, float* work, int32_t n_steps, void* stream);
+/* Plain Sinkhorn-Knopp (utils/optimal_transport/sinkhorn.py:65-186) on the same sweeps: after bfk_ot_init,
+ * bfk_ot_plain_mode(S, numel, ctrl) records max(S) and switches bfk_ot_log_sinkhorn_step to the multiplicative algorithm's
+ * arithmetic (scalings kept as logs, the reference's `tiny` = 1e-12 terms and its log-relative-change error);
+ * bfk_ot_sample_plan draws assignments ~ Categorical(log(plan + 1e-10)) (sinkhorn.py:60-62). */
+int bfk_ot_plain_mode(const float* S, int64_t numel, float* ctrl, void* stream);
+int bfk_ot_sample_plan(const float* S, int64_t ld, const float* u, const float* v, const float* ctrl, int64_t n, int64_t m,
+                       uint64_t seed, int64_t* assignments, void* stream);
 int bfk_ot_sample(const float* S, int64_t ld, const float* v, int64_t n, int64_t m, uint64_t seed, int64_t* assignments,
                   void* stream);
 

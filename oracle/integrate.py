@@ -294,7 +294,7 @@ def integrate(fn, state, start_time=None, stop_time=None, min_steps=50, max_step
 
 
 # ---------------------------------------------------------------------------------------------------------------------
-# Stochastic half (integrate.py:495-743, 964-1165, 1254-1451): euler_maruyama and two_step_adaptive, no corrector.
+# Stochastic half (integrate.py:495-1451): euler_maruyama, two_step_adaptive, sea, shark, langevin and the corrector.
 # `noise_fn(i, state) -> dict` replaces generate_noise (what the reference's z_history does on the JAX backend) so that a
 # parity run can feed the SAME normals to the oracle and to the CUDA path; default: torch.randn from `generator`.
 STOCHASTIC_METHODS = ["euler_maruyama", "sea", "shark", "two_step_adaptive", "langevin"]
@@ -379,9 +379,117 @@ def two_step_adaptive_step(drift_fn, diffusion_fn, state, time, step_size, noise
     return state, time, new_step_size, state
 
 
+def compute_levy_area(state, diffusion, noise, noise_aux, step_size):
+    # integrate.py:746-762
+    step_size_abs = torch.abs(torch.as_tensor(step_size, dtype=torch.float32))
+    sqrt_step_size = torch.sqrt(step_size_abs)
+    inv_sqrt3 = torch.tensor(1.0 / np.sqrt(3.0), dtype=torch.float32)
+    H = {}
+    for k in state:
+        if k in diffusion:
+            H[k] = 0.5 * step_size_abs * noise[k] + 0.5 * step_size_abs * sqrt_step_size * inv_sqrt3 * noise_aux[k]
+        else:
+            H[k] = torch.zeros_like(state[k])
+    return H
+
+
+def sea_step(drift_fn, diffusion_fn, state, time, step_size, noise, noise_aux, **_):
+    # integrate.py:765-822 (shifted Euler for additive noise)
+    diffusion = diffusion_fn(time, **state)
+    sqrt_step_size = torch.sqrt(torch.abs(torch.as_tensor(step_size, dtype=torch.float32)))
+    la = compute_levy_area(state, diffusion, noise, noise_aux, step_size)
+    shifted = {k: (x + diffusion[k] * (0.5 * sqrt_step_size * noise[k] + la[k])) if k in diffusion else x
+               for k, x in state.items()}
+    drift_shifted = drift_fn(time, **shifted)
+    new_state = {}
+    for key, d in drift_shifted.items():
+        base = state[key] + step_size * d
+        if key in diffusion:
+            base = base + diffusion[key] * sqrt_step_size * noise[key]
+        new_state[key] = base
+    return new_state, time + step_size, step_size
+
+
+def shark_step(drift_fn, diffusion_fn, state, time, step_size, noise, noise_aux, **_):
+    # integrate.py:825-921 (shifted additive-noise Runge-Kutta, two drift evaluations per step)
+    h, t = step_size, time
+    sqrt_h_mag = torch.sqrt(torch.abs(torch.as_tensor(h, dtype=torch.float32)))
+    diffusion = diffusion_fn(t, **state)
+    la = compute_levy_area(state, diffusion, noise, noise_aux, step_size)
+    y_tilde_k = {k: (state[k] + diffusion[k] * la[k]) if k in diffusion else state[k] for k in state}
+    f_tilde_k = drift_fn(t, **y_tilde_k)
+    g_tilde_k = diffusion_fn(t, **y_tilde_k)
+    y_tilde_mid = {}
+    for k in state:
+        drift_part = (5.0 / 6.0) * f_tilde_k[k] * h
+        sto_part = (5.0 / 6.0) * g_tilde_k[k] * sqrt_h_mag * noise[k] if k in g_tilde_k else torch.zeros_like(state[k])
+        y_tilde_mid[k] = y_tilde_k[k] + drift_part + sto_part
+    f_tilde_mid = drift_fn(t + 5.0 / 6.0 * h, **y_tilde_mid)
+    g_tilde_mid = diffusion_fn(t + 5.0 / 6.0 * h, **y_tilde_mid)
+    new_state = {}
+    for k in state:
+        det = state[k] + (2.0 / 5.0) * f_tilde_k[k] * h + (3.0 / 5.0) * f_tilde_mid[k] * h
+        sto1 = g_tilde_k[k] * ((2.0 / 5.0) * sqrt_h_mag * noise[k] + (6.0 / 5.0) * la[k]) if k in g_tilde_k else torch.zeros_like(det)
+        sto2 = g_tilde_mid[k] * ((3.0 / 5.0) * sqrt_h_mag * noise[k] - (6.0 / 5.0) * la[k]) if k in g_tilde_mid else torch.zeros_like(det)
+        new_state[k] = det + sto1 + sto2
+    return new_state, t + h, h
+
+
+def _apply_corrector(new_state, new_time, corrector_steps, score_fn, draw, step_size_factor=0.01, noise_schedule=None):
+    # integrate.py:924-961 (annealed Langevin corrector, Song et al. 2020)
+    for _ in range(corrector_steps):
+        score = score_fn(new_time, **new_state)
+        z_corr = draw(new_state)
+        log_snr_t = noise_schedule.get_log_snr(torch.as_tensor(new_time, dtype=torch.float32), training=False)
+        alpha_t, _ = noise_schedule.get_alpha_sigma(log_snr_t)
+        for k in new_state:
+            if k in score:
+                z_norm = torch.linalg.vector_norm(z_corr[k], dim=-1, keepdim=True)
+                score_norm = torch.clamp_min(torch.linalg.vector_norm(score[k], dim=-1, keepdim=True), 1e-8)
+                e = 2.0 * alpha_t * (step_size_factor * z_norm / score_norm) ** 2
+                new_state[k] = new_state[k] + e * score[k] + torch.sqrt(2.0 * e) * z_corr[k]
+    return new_state
+
+
+def integrate_langevin(state, start_time, stop_time, steps, score_fn, noise_schedule, draw, step_size_factor=0.01,
+                       corrector_steps=0):
+    # integrate.py:1167-1251 (annealed Langevin dynamics on a linear time grid)
+    if steps <= 0:
+        raise ValueError("Number of Langevin steps must be positive.")
+    if score_fn is None or noise_schedule is None:
+        raise ValueError("score_fn and noise_schedule must be provided.")
+    dt = (stop_time - start_time) / float(steps)
+    effective_factor = step_size_factor * 100 / np.sqrt(steps)
+    i, time = 0, start_time
+    while i < steps and not _check_all_nans(state):
+        score = score_fn(time, **state)
+        log_snr_t = noise_schedule.get_log_snr(torch.as_tensor(time, dtype=torch.float32), training=False)
+        _, sigma_t = noise_schedule.get_alpha_sigma(log_snr_t)
+        z = draw(state)
+        new_state = {}
+        for k in state:
+            s_k = score.get(k)
+            if s_k is None:
+                new_state[k] = state[k]
+                continue
+            e = effective_factor * sigma_t ** 2
+            new_state[k] = state[k] + e * s_k + torch.sqrt(2.0 * e) * z[k]
+        time = time + dt
+        if corrector_steps > 0:
+            new_state = _apply_corrector(new_state, time, corrector_steps, score_fn, draw, step_size_factor, noise_schedule)
+        state = new_state
+        i += 1
+    if _check_all_nans(state):
+        raise RuntimeError(f"All values are NaNs in state during integration at {time}.")
+    return state
+
+
 def integrate_stochastic(drift_fn, diffusion_fn, state, start_time, stop_time, generator=None, steps=100,
-                         method="euler_maruyama", min_steps=50, max_steps=1_000, noise_fn=None, info=None, **kwargs):
-    # integrate.py:1254-1451 (dispatch), :964-1046 (fixed), :1049-1164 (adaptive); corrector_steps = 0
+                         method="euler_maruyama", min_steps=50, max_steps=1_000, noise_fn=None, info=None, score_fn=None,
+                         corrector_steps=0, noise_schedule=None, step_size_factor=0.01, **kwargs):
+    # integrate.py:1254-1451 (dispatch), :964-1046 (fixed), :1049-1164 (adaptive).  `noise_fn(k, state)` is the k-th draw
+    # of standard normals of the call, in the reference's order (per step: dW, then the auxiliary normals of sea / shark,
+    # then one draw per corrector step)
     is_adaptive = isinstance(steps, str) and steps in ["adaptive", "dynamic"]
     if is_adaptive:
         if start_time is None or stop_time is None:
@@ -396,16 +504,32 @@ def integrate_stochastic(drift_fn, diffusion_fn, state, start_time, stop_time, g
             raise ValueError("Number of steps must be positive.")
         initial_step = (stop_time - start_time) / float(int(steps))
         min_step_size = max_step_size = initial_step
+    if corrector_steps > 0 and (score_fn is None or noise_schedule is None):
+        raise ValueError("Please provide both score_fn and noise_schedule when using corrector_steps > 0.")
+    counter = [0]
+
+    def draw(st):
+        k = counter[0]
+        counter[0] += 1
+        return noise_fn(k, st) if noise_fn is not None else generate_noise(st, generator)
+
     if method == "euler_maruyama":
         step_fn = euler_maruyama_step
     elif method == "two_step_adaptive":
         step_fn = two_step_adaptive_step
-    elif method in ("sea", "shark", "langevin"):
-        raise NotImplementedError(f"oracle: method {method!r} is outside the restated subset")
+    elif method in ("sea", "shark"):
+        if is_adaptive:
+            raise ValueError(f"{method.upper()} SDE solver does not support adaptive steps.")
+        step_fn = sea_step if method == "sea" else shark_step
+    elif method == "langevin":
+        if is_adaptive:
+            raise ValueError("Langevin sampling does not support adaptive steps.")
+        return integrate_langevin(state, start_time, stop_time, int(steps), score_fn, noise_schedule, draw, step_size_factor,
+                                  corrector_steps)
     else:
         raise TypeError(f"Invalid integration method: {method!r}")
+    two_noise = method in ("sea", "shark")
     skw = {k: v for k, v in kwargs.items() if k in ("e_rel", "e_abs", "r", "adapt_safety")}
-    noise_of = noise_fn if noise_fn is not None else (lambda i, s: generate_noise(s, generator))
     f32 = torch.float32
     sign_dir = float(np.sign(stop_time - start_time))
     i, time, step, last = 0, start_time, initial_step, state
@@ -413,12 +537,18 @@ def integrate_stochastic(drift_fn, diffusion_fn, state, start_time, stop_time, g
         while i < int(steps) and not _check_all_nans(state):
             remaining = abs(stop_time - float(time))
             dt = float(np.sign(float(step))) * min(abs(float(step)), remaining)
-            state, time, _ = step_fn(drift_fn, diffusion_fn, state, time, dt, noise_of(i, state), use_adaptive_step_size=False,
-                                     min_step_size=min_step_size, max_step_size=min(max_step_size, remaining), **skw)[:3]
+            noise = draw(state)
+            extra = {"noise_aux": draw(state)} if two_noise else {}
+            state, time, _ = step_fn(drift_fn, diffusion_fn, state, time, dt, noise, use_adaptive_step_size=False,
+                                     min_step_size=min_step_size, max_step_size=min(max_step_size, remaining), **extra, **skw)[:3]
+            if corrector_steps > 0:
+                state = _apply_corrector(state, time, corrector_steps, score_fn, draw, step_size_factor, noise_schedule)
             step = initial_step
             i += 1
         if _check_all_nans(state):
             raise RuntimeError(f"All values are NaNs in state during integration at {time}.")
+        if info is not None:
+            info["steps"] = i
         return state
     while True:
         time_remaining = sign_dir * (stop_time - (float(time) + float(step)))
@@ -426,15 +556,17 @@ def integrate_stochastic(drift_fn, diffusion_fn, state, start_time, stop_time, g
             break
         remaining = abs(stop_time - float(time))
         dt = float(np.sign(float(step))) * min(abs(float(step)), remaining)
-        state, time, step, last = step_fn(drift_fn, diffusion_fn, state, time, torch.tensor(dt, dtype=f32), noise_of(i, state),
+        state, time, step, last = step_fn(drift_fn, diffusion_fn, state, time, torch.tensor(dt, dtype=f32), draw(state),
                                           last_state=last, use_adaptive_step_size=True, min_step_size=min_step_size,
                                           max_step_size=min(max_step_size, remaining), **skw)
+        if corrector_steps > 0:
+            state = _apply_corrector(state, time, corrector_steps, score_fn, draw, step_size_factor, noise_schedule)
         i += 1
     if _check_all_nans(state):
         raise RuntimeError(f"All values are NaNs in state during integration at {time}.")
     time_diff = stop_time - float(time)
     if sign_dir * time_diff > 0:
-        state = step_fn(drift_fn, diffusion_fn, state, time, time_diff, noise_of(i, state), last_state=last,
+        state = step_fn(drift_fn, diffusion_fn, state, time, time_diff, draw(state), last_state=last,
                         use_adaptive_step_size=False, min_step_size=min_step_size, max_step_size=sign_dir * time_diff, **skw)[0]
         i += 1
     if info is not None:

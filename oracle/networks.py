@@ -541,7 +541,7 @@ class OracleDiffusionModel:
             x, trace = self._density_integrate(z, conditions, ik)
             return x, self.base_distribution.log_prob(z) - trace
         if ik["method"] not in ("euler", "rk45", "tsit5"):
-            # SDE branch, diffusion_model.py:830-856 (no corrector)
+            # SDE branch, diffusion_model.py:830-856
             from .integrate import integrate_stochastic
 
             def sde_drift(time, xz):
@@ -550,8 +550,16 @@ class OracleDiffusionModel:
 
             def sde_diffusion(time, xz):
                 return {"xz": self.diffusion_term(xz, time=time, target_mask=kwargs.get("target_mask"))}
-            extra = {k: kwargs[k] for k in ("noise_fn", "generator", "e_rel", "e_abs", "r", "adapt_safety") if k in kwargs}
-            return integrate_stochastic(sde_drift, sde_diffusion, {"xz": z}, **ik, **extra)["xz"]
+            extra = {k: kwargs[k] for k in ("noise_fn", "generator", "e_rel", "e_abs", "r", "adapt_safety", "corrector_steps",
+                                            "step_size_factor") if k in kwargs}
+            score_fn = None
+            if "corrector_steps" in kwargs or ik["method"] == "langevin":  # :845-849
+                def score_fn(time, xz):
+                    lam = self.noise_schedule.get_log_snr(torch.as_tensor(time, dtype=torch.float32), training=False)
+                    lam = torch.broadcast_to(lam.reshape((1,) * xz.ndim), xz.shape[:-1] + (1,))
+                    return {"xz": self.score(xz, lam, conditions=conditions)}
+            return integrate_stochastic(sde_drift, sde_diffusion, {"xz": z}, score_fn=score_fn,
+                                        noise_schedule=self.noise_schedule, **ik, **extra)["xz"]
 
         def deltas(time, xz):
             return {"xz": self.velocity(xz, time=time, stochastic_solver=False, conditions=conditions,

@@ -105,6 +105,41 @@ def log_sinkhorn_plan(x1, x2, conditions=None, regularization=1.0, atol=1e-5, ma
     return log_plan[:-1, :-1] if partial else log_plan
 
 
+def sinkhorn_plan(x1, x2, conditions=None, regularization=1.0, max_steps=1000, atol=1e-5, condition_ratio=0.5,
+                  partial_factor=1.0, info=None, **kwargs):
+    # sinkhorn.py:65-186 (the multiplicative Sinkhorn-Knopp: Gaussian kernel exp(S - max S), scalings u, v, `tiny` = 1e-12)
+    if not (0.0 < partial_factor <= 1.0):
+        raise ValueError(f"s must be in (0, 1] for partial OT, got {partial_factor}")
+    partial = partial_factor < 1.0
+    cost = squared_euclidean(x1, x2)
+    if regularization <= 0.0:
+        raise ValueError(f"regularization must be positive, got {regularization}")
+    w = 0.0
+    if conditions is not None and condition_ratio < 0.5:
+        cost, w = search_for_conditional_weight(cost, cosine_distance(conditions, conditions), condition_ratio)
+    S = -cost / regularization
+    if partial:
+        S, a, b = augment_for_partial_ot(S, regularization, partial_factor, kwargs.get("dummy_cost"))
+    else:
+        n, m = S.shape
+        a = torch.ones(n, dtype=S.dtype) / n
+        b = torch.ones(m, dtype=S.dtype) / m
+    plan = torch.exp(S - S.max())
+    u, v = torch.ones_like(a), torch.ones_like(b)
+    tiny = 1e-12
+    err, steps = 1e30, 0
+    while err > atol and steps < max_steps:
+        u_new = a / (plan @ v + tiny)
+        v_new = b / (plan.T @ u_new + tiny)
+        du = float(torch.log((u_new + tiny) / (u + tiny)).abs().max())
+        dv = float(torch.log((v_new + tiny) / (v + tiny)).abs().max())
+        err, u, v, steps = max(du, dv), u_new, v_new, steps + 1
+    if info is not None:
+        info.update(steps=steps, err=err, w=w)
+    plan = (u.unsqueeze(1) * plan) * v.unsqueeze(0)
+    return plan[:-1, :-1] if partial else plan
+
+
 def gumbel_argmax(log_plan, seed):
     """Categorical draw per row: argmax_j log_plan[i,j] - log(-log U_ij), U from Philox word i*m + j."""
     n, m = log_plan.shape

@@ -226,6 +226,10 @@ for _name, _fn in {
     "trace": lambda x, offset=0, axis1=0, axis2=1: torch.diagonal(_t(x), offset, axis1, axis2).sum(-1),
     "inv": lambda x: torch.linalg.inv(_t(x)), "solve": lambda a, b: torch.linalg.solve(_t(a), _t(b)),
     "expm": lambda x: torch.linalg.matrix_exp(_t(x)),
+    "transpose": lambda x, axes=None: _t(x).permute(*axes) if axes is not None else _t(x).T,
+    "logsumexp": lambda x, axis=None, keepdims=False: torch.logsumexp(_t(x), dim=axis if axis is not None else tuple(range(_t(x).ndim)), keepdim=keepdims),
+    "diagonal": lambda x, offset=0, axis1=0, axis2=1: torch.diagonal(_t(x), offset, axis1, axis2),
+    "log10": lambda x: torch.log10(_t(x)), "floor": lambda x: torch.floor(_t(x)), "round": lambda x: torch.round(_t(x)),
     "cond": _cond, "while_loop": _while_loop, "fori_loop": _fori_loop,
     "stop_gradient": lambda x: _t(x).detach(),
 }.items():
@@ -272,6 +276,8 @@ random.normal = lambda shape, mean=0.0, stddev=1.0, dtype=None, seed=None: (
     mean + stddev * torch.randn(tuple(shape), dtype=_to_dtype(dtype) or torch.float32, generator=_gen(seed)))
 random.uniform = lambda shape, minval=0.0, maxval=1.0, dtype=None, seed=None: (
     minval + (maxval - minval) * torch.rand(tuple(shape), dtype=_to_dtype(dtype) or torch.float32, generator=_gen(seed)))
+random.categorical = lambda logits, num_samples, dtype="int32", seed=None: torch.multinomial(
+    torch.softmax(_t(logits).double(), dim=-1), num_samples, replacement=True, generator=_gen(seed))
 random.shuffle = lambda x, axis=0, seed=None: torch.index_select(
     _t(x), axis, torch.randperm(_t(x).shape[axis], generator=_gen(seed)))
 

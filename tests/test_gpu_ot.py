@@ -45,8 +45,6 @@ def test_reference_closed_form_tests_on_the_kernels():
     assert torch.isfinite(ox).all() and torch.isfinite(oy).all() and int(a.min()) >= 0 and int(a.max()) < 64
     with pytest.raises(ValueError):
         bf.log_sinkhorn_plan(x.cuda(), z.cuda(), regularization=0.0)
-    with pytest.raises(NotImplementedError):
-        bf.optimal_transport(x.cuda(), z.cuda(), method="sinkhorn")
     with pytest.raises(ValueError):
         bf.log_sinkhorn_plan(x.cuda(), z.cuda(), partial_factor=1.5)
     with pytest.raises(RuntimeError):
@@ -106,3 +104,28 @@ def test_partial_ot_matches_oracle_and_leaves_unmatched_mass(s):
                                       return_assignments=True)
     a_ref = oot.gumbel_argmax(oot.log_sinkhorn_plan(x, y, regularization=0.1, partial_factor=s), seed=2)
     assert int(a.min()) >= 0 and int(a.max()) < 20 and float((a.cpu() == a_ref).float().mean()) >= 0.9
+
+
+@pytest.mark.parametrize("n,m,D,reg,partial", [(10, 20, 2, 1.0, 1.0), (100, 200, 3, 0.5, 1.0), (257, 257, 8, 1.0, 1.0),
+                                               (64, 64, 2, 1.0, 0.8), (1, 7, 2, 1.0, 1.0)])
+def test_plain_sinkhorn_plan_matches_oracle(n, m, D, reg, partial):
+    """the multiplicative Sinkhorn-Knopp (utils/optimal_transport/sinkhorn.py:65-186, `method="sinkhorn"`) on the kernels"""
+    import bayesflow_b200 as bf
+    from bayesflow_b200.optimal_transport import sinkhorn_plan
+    g = torch.Generator().manual_seed(3 * n + m)
+    x1, x2 = torch.randn(n, D, generator=g), torch.randn(m, D, generator=g)
+    info = {}
+    ref = oot.sinkhorn_plan(x1.double(), x2.double(), regularization=reg, atol=1e-5, max_steps=300, partial_factor=partial,
+                            info=info)
+    plan = sinkhorn_plan(x1.cuda(), x2.cuda(), regularization=reg, atol=1e-5, max_steps=300, partial_factor=partial).cpu()
+    steps = bf.log_sinkhorn_plan.last_info["steps"]
+    assert abs(steps - info["steps"]) <= max(2, info["steps"] // 10), (steps, info["steps"])
+    np.testing.assert_allclose(plan.numpy(), ref.numpy(), rtol=2e-3, atol=1e-7)
+    if steps < 300 and partial == 1.0:
+        np.testing.assert_allclose(plan.sum(0).numpy(), np.full(m, 1.0 / m), rtol=2e-3)
+    # the dispatcher's default method is "sinkhorn" (optimal_transport.py:12-72)
+    y = torch.randn(16, 2)
+    p = torch.randperm(16)
+    _, y2, _, a = bf.optimal_transport(y[p].cuda(), y.cuda(), regularization=0.05, seed=0, max_steps=5000,
+                                       return_assignments=True)
+    assert int((a.cpu() == p).sum()) >= 14 and torch.equal(y2.cpu(), y[a.cpu()])

@@ -303,3 +303,50 @@ def test_reference_sources_are_the_files_on_disk(R):
     for m in ("bayesflow.utils.tensor_utils", "bayesflow.utils.jacobian.jacobian_trace", "bayesflow.utils.dict_utils",
               "bayesflow.networks.inference.inference_network", "bayesflow.networks.defaults"):
         assert sys.modules[m].__file__.startswith(ref_loader.PKG_DIR), m
+
+
+@pytest.mark.parametrize("method", ["log_sinkhorn", "sinkhorn"])
+@pytest.mark.parametrize("partial,cond", [(1.0, False), (0.8, False), (1.0, True)])
+def test_optimal_transport_plans(R, method, partial, cond):
+    """utils/optimal_transport/{log_sinkhorn,sinkhorn,ot_utils}.py executed from the reference tree vs oracle/"""
+    import importlib
+    import oracle.optimal_transport as oot
+    mod = importlib.import_module("bayesflow.utils.optimal_transport." + method)
+    g = torch.Generator().manual_seed(5)
+    x1, x2 = torch.randn(24, 3, generator=g), torch.randn(24, 3, generator=g)
+    c = torch.randn(24, 4, generator=g) if cond else None
+    kw = dict(regularization=0.5, atol=1e-6, max_steps=200, partial_factor=partial, condition_ratio=0.1 if cond else 0.5)
+    ref = getattr(mod, method + "_plan")(x1, x2, conditions=c, **kw)
+    orc = getattr(oot, method + "_plan")(x1, x2, conditions=c, **kw)
+    if method == "log_sinkhorn":
+        ref, orc = torch.exp(ref), torch.exp(orc)
+    assert rel(orc, ref) < 1e-4
+
+
+@pytest.mark.parametrize("method,kw", [
+    ("euler_maruyama", {"steps": 12}),
+    ("euler_maruyama", {"steps": "adaptive", "min_steps": 4, "max_steps": 30}),
+    ("two_step_adaptive", {"steps": "adaptive", "min_steps": 4, "max_steps": 40}),   # the DiffusionModel default method
+    ("two_step_adaptive", {"steps": 8}),
+    ("sea", {"steps": 10}),
+    ("shark", {"steps": 8}),
+    ("langevin", {"steps": 15}),
+    ("langevin", {"steps": 6, "corrector_steps": 2}),
+    ("euler_maruyama", {"steps": 7, "corrector_steps": 1}),
+    ("shark", {"steps": 5, "corrector_steps": 1, "step_size_factor": 0.02}),
+])
+def test_dm_stochastic_samplers_same_noise(R, method, kw, monkeypatch):
+    """utils/integrate.py:495-1451 (every SDE method, the corrector, the Langevin sampler) through DiffusionModel._inverse
+    (diffusion_model.py:830-856), fed the SAME sequence of standard normals as the oracle."""
+    import keras
+    ref, orc, _ = pair(R, 3, 5, (32,) * 2, dm=True)
+    z, c = batch(23, 3, 5)
+    g = torch.Generator().manual_seed(99)
+    draws = [torch.randn(23, 3, generator=g) for _ in range(400)]
+    it = iter(draws)
+    monkeypatch.setattr(keras.random, "normal", lambda shape, *a, **k: next(it).reshape(tuple(shape)).clone())
+    with torch.no_grad():
+        x_ref = ref(z, conditions=c, inverse=True, method=method, **kw)
+        x_orc = orc.inverse(z, c, method=method, noise_fn=lambda k, st: {"xz": draws[k]}, **kw)
+    assert torch.isfinite(x_ref).all()
+    assert rel(x_orc, x_ref) < 5e-5
