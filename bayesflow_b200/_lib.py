@@ -93,6 +93,9 @@ def lib():
     L.bfk_detect_repeats.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]
     L.bfk_normal_fill.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_uint64,
                                   C.c_void_p, C.c_void_p]
+    L.bfk_schedule_alpha_sigma.argtypes = [C.c_void_p, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.bfk_sde_langevin_update.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_double, C.c_double,
+                                          C.c_double, C.c_double, C.c_int32, C.c_void_p, C.c_void_p]
     L.bfk_standardize.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                   C.c_int32, C.c_void_p]
     L.bfk_lincomb3.argtypes = [C.c_void_p, C.c_float, C.c_void_p, C.c_float, C.c_void_p, C.c_float, C.c_void_p, C.c_int64,

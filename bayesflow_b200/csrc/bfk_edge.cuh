@@ -397,6 +397,48 @@ __global__ void verify_groups_kernel(const float* __restrict__ c, long long B, i
   if (bad) out[1] = 1;
 }
 
+// ---- annealed-Langevin updates of the reverse-SDE samplers ------------------------------------------------------------
+// utils/integrate.py:924-961 (_apply_corrector) and :1167-1251 (integrate_langevin), one launch per update.  The score is
+// rebuilt from the probability-flow velocity the network kernels return: v_ode = fz*x - beta/2 * score (diffusion_model.py
+// :539-552)  =>  score = 2 * (fz*x - v_ode) / beta.  One warp per row:
+//   per_row != 0 (corrector):  e = 2 * a * (b * ||z|| / max(||score||, 1e-8))^2      (a = alpha_t, b = step_size_factor)
+//   per_row == 0 (langevin):   e = a                                                 (a = effective_factor * sigma_t^2)
+//   out = x + e * score + sqrt(2 e) * z
+__global__ void __launch_bounds__(256) sde_langevin_kernel(const float* __restrict__ x, const float* __restrict__ v,
+                                                           const float* __restrict__ z, long long B, int D, float fz,
+                                                           float two_over_beta, float a, float b, int per_row,
+                                                           float* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long r = warp; r < B; r += n_warps) {
+    const float* xr = x + r * D;
+    const float* vr = v + r * D;
+    const float* zr = z + r * D;
+    float e = a;
+    if (per_row) {
+      float zz = 0.f, ss = 0.f;
+      for (int j = lane; j < D; j += 32) {
+        const float sc = two_over_beta * (fz * xr[j] - vr[j]);
+        zz = fmaf(zr[j], zr[j], zz);
+        ss = fmaf(sc, sc, ss);
+      }
+#pragma unroll
+      for (int o = 16; o; o >>= 1) {
+        zz += __shfl_xor_sync(0xffffffffu, zz, o);
+        ss += __shfl_xor_sync(0xffffffffu, ss, o);
+      }
+      const float q = b * sqrtf(zz) / fmaxf(sqrtf(ss), 1e-8f);
+      e = 2.f * a * q * q;
+    }
+    const float s2e = sqrtf(2.f * e);
+    for (int j = lane; j < D; j += 32) {
+      const float sc = two_over_beta * (fz * xr[j] - vr[j]);
+      out[r * D + j] = xr[j] + e * sc + s2e * zr[j];
+    }
+  }
+}
+
 }  // namespace bfk
 
 // ---- C ABI ------------------------------------------------------------------------------------------------------------
@@ -509,6 +551,23 @@ extern "C" int bfk_detect_repeats(const float* cond, int64_t B, int32_t C, int64
   const unsigned grid = (unsigned)((B + 255) / 256 < (long long)sms * 8 ? (B + 255) / 256 : (long long)sms * 8);
   bfk::first_diff_kernel<<<grid, 256, 0, st>>>(cond, B, C, (long long*)out2);
   bfk::verify_groups_kernel<<<grid, 256, 0, st>>>(cond, B, C, (long long*)out2);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bfk_sde_langevin_update(const float* x, const float* v_ode, const float* z, int64_t B, int32_t D, double fz,
+                                       double beta, double a, double b, int32_t per_row, float* out, void* stream_) {
+  if (B < 0 || D < 1) return fail(-66, "bfk_sde_langevin_update: bad B/D");
+  if (B == 0) return 0;
+  if (!x || !v_ode || !z || !out) return fail(-67, "bfk_sde_langevin_update: null pointer");
+  if (!(beta > 0.0)) return fail(-68, "bfk_sde_langevin_update: beta = g(t)^2 must be positive");
+  const int sms = bfk_num_sms();
+  if (sms <= 0) return fail(-62, "bfk_sde_langevin_update: no CUDA device");
+  long long blocks = (B + 7) / 8, cap = (long long)sms * 8;
+  if (blocks > cap) blocks = cap;
+  bfk::sde_langevin_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream_>>>(x, v_ode, z, (long long)B, D, (float)fz,
+                                                                               (float)(2.0 / beta), (float)a, (float)b,
+                                                                               per_row, out);
   CK(cudaGetLastError());
   return 0;
 }

@@ -180,6 +180,7 @@ __global__ void __launch_bounds__(256) ot_max_kernel(const float* __restrict__ S
   for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
   if ((threadIdx.x & 31) == 0) {  // float max through the ordered-int trick (values may be negative)
     int* addr = reinterpret_cast<int*>(ctrl + OT_SHIFT);
+    mx += 0.0f;  // -0.0f (a zero cost, S = -M / reg) would compare as INT_MIN below and lose against the -inf identity
     if (mx >= 0.f) atomicMax(addr, __float_as_int(mx));
     else atomicMin(reinterpret_cast<unsigned int*>(addr), __float_as_uint(mx));
   }

@@ -355,6 +355,18 @@ extern "C" int bfk_schedule_sde_terms(const bfk_schedule* sched, double t, doubl
   return 0;
 }
 
+// alpha_t, sigma_t of the inference-time schedule (noise_schedule.py get_alpha_sigma; edm_noise_schedule.py:61-75,
+// cosine_noise_schedule.py:60-63 for lambda(t)) - what the annealed-Langevin updates of utils/integrate.py:924-961 and
+// :1167-1251 read per step.
+extern "C" int bfk_schedule_alpha_sigma(const bfk_schedule* sched, double t, double* alpha, double* sigma) {
+  if (!sched || !alpha || !sigma || sched->model != BFK_MODEL_DM) return fail(-87, "bfk_schedule_alpha_sigma: bad arguments");
+  double lam, beta;
+  bfk::schedule_lam_beta(*sched, t, &lam, &beta);
+  if (sched->exploding) { *alpha = 1.0; *sigma = sqrt(exp(-lam)); }
+  else { *alpha = sqrt(1.0 / (1.0 + exp(-lam))); *sigma = sqrt(1.0 / (1.0 + exp(lam))); }
+  return 0;
+}
+
 extern "C" int bfk_rk_combine(const float* y, const float* const* k, const float* coef, int32_t n, float h, int64_t numel,
                               float* out, void* stream_) {
   if (!y || !k || !coef || !out || n < 0 || n > 8 || numel <= 0) return fail(-85, "bfk_rk_combine: bad arguments");

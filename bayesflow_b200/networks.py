@@ -312,9 +312,13 @@ class _Engine:
                 # the reference's Sampler hands over each dataset's conditions repeated num_samples times: recover
                 # (datasets, repeats) with two streaming launches (no sort / unique pass over the (N*S, C) tensor)
                 cond = cond.contiguous()
+                if not cond.is_cuda:
+                    raise RuntimeError("bayesflow_b200 runs on CUDA tensors only (no CPU fallback); got conditions on "
+                                       + str(cond.device))
                 out2 = torch.empty(2, device=cond.device, dtype=torch.int64)
                 with torch.cuda.device(cond.device):
-                    _lib.check(_lib.lib().bfk_detect_repeats(_lib.ptr(cond), B, net._C, _lib.ptr(out2), _lib.stream_ptr()),
+                    _lib.check(_lib.lib().bfk_detect_repeats(_lib.ptr(cond), B, net._C, C.c_void_p(out2.data_ptr()),
+                                                             _lib.stream_ptr()),
                                "bfk_detect_repeats")
                 self.launches += 2
                 R, bad = (int(v) for v in out2.tolist())
@@ -938,6 +942,8 @@ def find_noise_schedule(arg, **kwargs):
 class DiffusionModel(InferenceNetwork):
     """diffusion_model.py:35-869, probability-flow ODE sampling path (deterministic methods)."""
 
+    _wants_noise_offset = True  # the reverse-SDE increments are keyed by the GLOBAL row (stochastic.py)
+
     def __init__(self, *, subnet="time_mlp", noise_schedule="edm", prediction_type="F", loss_type="noise",
                  subnet_kwargs=None, schedule_kwargs=None, integrate_kwargs=None, drop_cond_prob: float = 0.0,
                  drop_target_prob: float = 0.0, **kwargs):
@@ -1122,6 +1128,7 @@ class DiffusionModel(InferenceNetwork):
     def _inverse(self, z, conditions=None, density=False, training=False, **kwargs):
         # diffusion_model.py:782-869
         seed = kwargs.pop("seed", None)
+        noise_row_offset = int(kwargs.pop("noise_row_offset", 0))  # this shard's first GLOBAL row (SDE increments)
         integrate_kwargs = {"start_time": 1.0, "stop_time": 0.0}
         integrate_kwargs |= self.integrate_kwargs
         integrate_kwargs |= kwargs
@@ -1140,9 +1147,9 @@ class DiffusionModel(InferenceNetwork):
             run = self._run(conditions, z.shape[0], kwargs)
             sde = ReverseSDE(self, run, kwargs.get("target_mask"))
             keys = ("start_time", "stop_time", "steps", "method", "min_steps", "max_steps", "corrector_steps", "e_rel",
-                    "e_abs", "r", "adapt_safety", "noise_fn")
+                    "e_abs", "r", "adapt_safety", "noise_fn", "step_size_factor")
             info = {}
-            out = integrate_stochastic(sde, run._check_x(z), seed=seed, info=info,
+            out = integrate_stochastic(sde, run._check_x(z), seed=seed, info=info, row_offset=noise_row_offset,
                                        **{k: v for k, v in integrate_kwargs.items() if k in keys})
             self.last_integration_info = info
             return out

@@ -1,16 +1,20 @@
-"""Reverse-SDE sampling for DiffusionModel: host-driven predictor steps over the CUDA velocity kernels.
+"""Reverse-SDE sampling for DiffusionModel: host-driven predictor / corrector steps over the CUDA velocity kernels.
 
   integrate_stochastic (dispatch, fixed, adaptive)  <- bayesflow/utils/integrate.py:1254-1451, 964-1046, 1049-1164
   euler_maruyama_step / step-size controller        <- utils/integrate.py:540-596, 502-537
   two_step_adaptive_step                            <- utils/integrate.py:599-743   (DiffusionModel's DEFAULT, defaults.py:50)
+  compute_levy_area, sea_step, shark_step           <- utils/integrate.py:746-762, 765-822, 825-921
+  _apply_corrector, integrate_langevin              <- utils/integrate.py:924-961, 1167-1251
   DiffusionModel SDE branch, diffusion_term         <- networks/inference/diffusion/diffusion_model.py:830-856, 561-595
 
 Every network evaluation is the same fused / layer-wise velocity kernel the ODE path uses (probability-flow velocity
-v_ode); the reverse-SDE drift is 2*v_ode - fz*z and g = sqrt(beta) with (fz, beta) from `bfk_schedule_sde_terms`
-(double).  State updates are `bfk_rk_combine`.  The host runs the reference's Python control flow (time is shared by all
-rows), reads the error / norm maxima of the adaptive controllers once per step, and draws the Gaussian increments with
-torch's device generator (parity with the reference is statistical, or exact when `noise_fn` feeds fixed normals).
-Not built: sea, shark, langevin, corrector steps (remainder).
+v_ode); the reverse-SDE drift is 2*v_ode - fz*z, the score 2*(fz*z - v_ode)/beta and g = sqrt(beta), with (fz, beta) from
+`bfk_schedule_sde_terms` and (alpha, sigma) from `bfk_schedule_alpha_sigma` (double).  State updates are `bfk_rk_combine`
+and `bfk_sde_langevin_update`.  The host runs the reference's Python control flow (time is shared by all rows) and reads
+the error / norm maxima of the adaptive controllers once per step.  The Gaussian increments are `bfk_normal_fill`
+(Philox4x32-10) keyed by (seed, draw number, GLOBAL row): a sharded fixed-step run draws the rows one big call would;
+`noise_fn(k, shape)` replaces the k-th draw for parity runs (draw order per step: dW, the auxiliary normals of sea / shark,
+then one draw per corrector step - the order of the reference's keras.random calls).
 """
 from __future__ import annotations
 
@@ -22,7 +26,7 @@ import torch
 from . import _lib
 from .density import _combine
 
-BUILT = ("euler_maruyama", "two_step_adaptive")
+BUILT = ("euler_maruyama", "two_step_adaptive", "sea", "shark", "langevin")
 TRACE = None  # debugging / tests: set to a list to record (time, step, E2, accepted) per two_step_adaptive trial
 
 
@@ -55,6 +59,26 @@ class ReverseSDE:
         fz, _ = self.terms(time)
         d = _combine(v, [v, x], ((0, 1.0), (1, -fz)), 1.0)
         return d if self.mask is None else d * self.mask.to(d.device)
+
+    def alpha_sigma(self, time):
+        a, s = C.c_double(), C.c_double()
+        _lib.check(self.L.bfk_schedule_alpha_sigma(C.byref(self.sched), float(np.float32(time)), C.byref(a), C.byref(s)),
+                   "bfk_schedule_alpha_sigma")
+        return a.value, s.value
+
+    def langevin_update(self, time, x, z, a, b, per_row):
+        """x + e*score(time, x) + sqrt(2e)*z (integrate.py:949-959, 1228-1236); the score comes from one velocity call."""
+        if self.mask is not None:
+            raise NotImplementedError("corrector / langevin updates with a target_mask are outside the accelerated path "
+                                      "(the reference's score_fn ignores the mask, diffusion_model.py:845-849)")
+        v = self.run.velocity(x, float(np.float32(time)))
+        self.evals += 1
+        fz, beta = self.terms(time)
+        out = torch.empty_like(x)
+        _lib.check(self.L.bfk_sde_langevin_update(_lib.ptr(x), _lib.ptr(v), _lib.ptr(z), x.shape[0], x.shape[1], fz, beta,
+                                                  float(a), float(b), int(per_row), _lib.ptr(out), _lib.stream_ptr()),
+                   "bfk_sde_langevin_update")
+        return out
 
     def diffusion(self, time, like):
         """g(t) as a python float, or a (D,) vector when a target mask zeroes some coordinates (:561-595)."""
@@ -112,8 +136,82 @@ def two_step_adaptive_step(sde, x, time, h, noise, last=None, adaptive=True, min
     return x, time, new_h, x
 
 
+def _lin(x, terms):
+    """x + sum_j c_j * t_j ; c_j python floats (one bfk_rk_combine launch) or (D,) vectors when a target mask is set."""
+    if all(isinstance(c, float) for _, c in terms):
+        return _combine(x, [t for t, _ in terms], tuple((j, c) for j, (_, c) in enumerate(terms)), 1.0)
+    out = x
+    for t, c in terms:
+        out = out + c * t
+    return out
+
+
+def _levy(h):
+    """H = hn*noise + ha*noise_aux, the space-time Levy area of integrate.py:746-762 -> (hn, ha, sqrt|h|)."""
+    habs = np.float32(abs(h))
+    sq = np.float32(np.sqrt(habs))
+    return float(np.float32(0.5) * habs), float(np.float32(0.5) * habs * sq * np.float32(1.0 / np.sqrt(3.0))), float(sq)
+
+
+def sea_step(sde, x, time, h, noise, noise_aux, **_):
+    """integrate.py:765-822, shifted Euler for additive noise (one drift evaluation per step)."""
+    g = sde.diffusion(time, x)
+    hn, ha, sq = _levy(h)
+    shifted = _lin(x, [(noise, g * (0.5 * sq + hn)), (noise_aux, g * ha)])
+    drift = sde.drift(time, shifted)
+    return _lin(x, [(drift, float(h)), (noise, g * sq)]), time + h, h
+
+
+def shark_step(sde, x, time, h, noise, noise_aux, **_):
+    """integrate.py:825-921, shifted additive-noise Runge-Kutta (two drift evaluations per step)."""
+    g = sde.diffusion(time, x)
+    hn, ha, sq = _levy(h)
+    y_k = _lin(x, [(noise, g * hn), (noise_aux, g * ha)])
+    f_k = sde.drift(time, y_k)
+    t_mid = time + 5.0 / 6.0 * h
+    y_mid = _lin(y_k, [(f_k, 5.0 / 6.0 * float(h)), (noise, g * (5.0 / 6.0 * sq))])
+    f_mid = sde.drift(t_mid, y_mid)
+    g_mid = sde.diffusion(t_mid, x)
+    return _lin(x, [(f_k, 0.4 * float(h)), (f_mid, 0.6 * float(h)),
+                    (noise, g * (0.4 * sq + 1.2 * hn) + g_mid * (0.6 * sq - 1.2 * hn)),
+                    (noise_aux, (g - g_mid) * (1.2 * ha))]), time + h, h
+
+
+def apply_corrector(sde, x, time, corrector_steps, draw, step_size_factor=0.01):
+    """integrate.py:924-961: annealed Langevin corrector (Song et al. 2020), e = 2*alpha_t*(r*||z||/||score||)^2 per row."""
+    for _ in range(int(corrector_steps)):
+        z = draw()
+        alpha, _ = sde.alpha_sigma(time)
+        x = sde.langevin_update(time, x, z, alpha, step_size_factor, per_row=True)
+    return x
+
+
+def integrate_langevin(sde, x, start_time, stop_time, steps, draw, step_size_factor=0.01, corrector_steps=0):
+    """integrate.py:1167-1251: annealed Langevin dynamics on a linear time grid, e = factor*100/sqrt(steps)*sigma_t^2."""
+    if steps <= 0:
+        raise ValueError("Number of Langevin steps must be positive.")
+    dt = (stop_time - start_time) / float(steps)
+    effective_factor = step_size_factor * 100 / np.sqrt(steps)
+    i, time = 0, start_time
+    while i < steps and not _all_nan(x):
+        _, sigma = sde.alpha_sigma(time)
+        z = draw()
+        x = sde.langevin_update(time, x, z, effective_factor * float(np.float32(sigma)) ** 2, 0.0, per_row=False)
+        time = time + dt
+        if corrector_steps > 0:
+            x = apply_corrector(sde, x, time, corrector_steps, draw, step_size_factor)
+        i += 1
+    if _all_nan(x):
+        raise RuntimeError(f"All values are NaNs in state during integration at {time}.")
+    return x, i
+
+
+_MIX_A, _MIX_B, _M64 = 0x9E3779B97F4A7C15, 0xD1B54A32D192ED03, (1 << 64) - 1
+
+
 def integrate_stochastic(sde, x, start_time, stop_time, steps=100, method="euler_maruyama", min_steps=50, max_steps=1_000,
-                         seed=None, noise_fn=None, info=None, corrector_steps=0, **kwargs):
+                         seed=None, noise_fn=None, info=None, corrector_steps=0, step_size_factor=0.01, row_offset=0,
+                         **kwargs):
     """integrate.py:1254-1451 for the single-key state {"xz": x}."""
     is_adaptive = isinstance(steps, str) and steps in ["adaptive", "dynamic"]
     if is_adaptive:
@@ -129,8 +227,27 @@ def integrate_stochastic(sde, x, start_time, stop_time, steps=100, method="euler
             raise ValueError("Number of steps must be positive.")
         initial_step = (stop_time - start_time) / float(int(steps))
         min_h = max_h = initial_step
-    if corrector_steps:
-        raise NotImplementedError("corrector steps are outside the accelerated path")
+    corrector_steps = int(corrector_steps or 0)
+
+    if noise_fn is None:
+        if isinstance(seed, torch.Generator):
+            seed = int(seed.initial_seed())
+        base_seed = int(seed) if seed is not None else torch.seed() & (2 ** 62 - 1)
+    counter = [0]
+    L = _lib.lib()
+
+    def draw():
+        """the k-th standard-normal draw of the call (Philox keyed by (seed, k), counter = global element index)"""
+        k = counter[0]
+        counter[0] += 1
+        if noise_fn is not None:
+            return noise_fn(k, x.shape).to(device=x.device, dtype=torch.float32).contiguous()
+        out = torch.empty(x.shape, device=x.device, dtype=torch.float32)
+        key = (base_seed * _MIX_A + (k + 1) * _MIX_B) & _M64
+        _lib.check(L.bfk_normal_fill(_lib.ptr(out), x.shape[0], x.shape[1], int(row_offset), None, None, key, None,
+                                     _lib.stream_ptr()), "bfk_normal_fill")
+        return out
+
     if method == "euler_maruyama":
         step_fn, skw = euler_maruyama_step, {}
     elif method == "two_step_adaptive":
@@ -139,23 +256,17 @@ def integrate_stochastic(sde, x, start_time, stop_time, steps=100, method="euler
     elif method in ("sea", "shark"):
         if is_adaptive:
             raise ValueError(f"{method.upper()} SDE solver does not support adaptive steps.")
-        raise NotImplementedError(f"method={method!r} is not built on the accelerated path; built: {BUILT}")
+        step_fn, skw = (sea_step if method == "sea" else shark_step), {}
     elif method == "langevin":
         if is_adaptive:
             raise ValueError("Langevin sampling does not support adaptive steps.")
-        raise NotImplementedError(f"method='langevin' is not built on the accelerated path; built: {BUILT}")
+        x, i = integrate_langevin(sde, x, start_time, stop_time, int(steps), draw, step_size_factor, corrector_steps)
+        if info is not None:
+            info.update({"steps": i, "evals": sde.evals, "method": method, "draws": counter[0]})
+        return x
     else:
         raise TypeError(f"Invalid integration method: {method!r}")
-    gen = None
-    if noise_fn is None:
-        gen = seed if isinstance(seed, torch.Generator) else torch.Generator(device=x.device)
-        if not isinstance(seed, torch.Generator):
-            gen.manual_seed(int(seed) if seed is not None else torch.seed() & (2 ** 62 - 1))
-
-    def noise_of(i):
-        if noise_fn is not None:
-            return noise_fn(i, x.shape).to(device=x.device, dtype=torch.float32).contiguous()
-        return torch.randn(x.shape, device=x.device, dtype=torch.float32, generator=gen)
+    two_noise = method in ("sea", "shark")
 
     sign_dir = float(np.sign(stop_time - start_time))
     i, time, step, last = 0, float(start_time), float(initial_step), x
@@ -163,7 +274,12 @@ def integrate_stochastic(sde, x, start_time, stop_time, steps=100, method="euler
         while i < int(steps) and not _all_nan(x):
             remaining = abs(stop_time - time)
             dt = float(np.sign(step)) * min(abs(step), remaining)
-            x, time = step_fn(sde, x, time, dt, noise_of(i), adaptive=False, min_h=min_h, max_h=min(max_h, remaining), **skw)[:2]
+            noise = draw()
+            extra = {"noise_aux": draw()} if two_noise else {}
+            x, time = step_fn(sde, x, time, dt, noise, adaptive=False, min_h=min_h, max_h=min(max_h, remaining), **extra,
+                              **skw)[:2]
+            if corrector_steps > 0:
+                x = apply_corrector(sde, x, time, corrector_steps, draw, step_size_factor)
             i += 1
     else:
         while sign_dir * (stop_time - (time + step)) > 0 and i < max_steps and not _all_nan(x):
@@ -172,7 +288,15 @@ def integrate_stochastic(sde, x, start_time, stop_time, steps=100, method="euler
             args = dict(adaptive=True, min_h=min_h, max_h=min(max_h, remaining), **skw)
             if step_fn is two_step_adaptive_step:
                 args["last"] = last
-            x, time, step, last = step_fn(sde, x, time, dt, noise_of(i), **args)
+            x, time, step, last = step_fn(sde, x, time, dt, draw(), **args)
+            if corrector_steps > 0:
+                # a rejected two_step_adaptive trial hands back ONE state as both the new and the previous state
+                # (integrate.py:734-740) and the eager backends' corrector updates that dict in place (:959): the
+                # controller's `last_state` is then the corrected state.  Kept, as oracle/integrate.py keeps it.
+                same = last is x
+                x = apply_corrector(sde, x, time, corrector_steps, draw, step_size_factor)
+                if same:
+                    last = x
             i += 1
     if _all_nan(x):
         raise RuntimeError(f"All values are NaNs in state during integration at {time}.")
@@ -182,8 +306,8 @@ def integrate_stochastic(sde, x, start_time, stop_time, steps=100, method="euler
             args = dict(adaptive=False, min_h=min_h, max_h=sign_dir * time_diff, **skw)
             if step_fn is two_step_adaptive_step:
                 args["last"] = last
-            x = step_fn(sde, x, time, time_diff, noise_of(i), **args)[0]
+            x = step_fn(sde, x, time, time_diff, draw(), **args)[0]
             i += 1
     if info is not None:
-        info.update({"steps": i, "evals": sde.evals, "method": method})
+        info.update({"steps": i, "evals": sde.evals, "method": method, "draws": counter[0]})
     return x

@@ -202,6 +202,15 @@ int bfk_schedule_coefs(const bfk_schedule* sched, double t, double* coefZ, doubl
 /* Reverse-SDE terms at time t (DiffusionModel.velocity with stochastic_solver=True, diffusion_model.py:539-552, and
  * diffusion_term, :561-595): beta = g(t)^2 and fz with f = fz*z; SDE drift = 2*v_ode - fz*z. */
 int bfk_schedule_sde_terms(const bfk_schedule* sched, double t, double* fz, double* beta);
+/* alpha_t, sigma_t at time t (NoiseSchedule.get_alpha_sigma of get_log_snr(t, training=False):
+ * networks/inference/diffusion/schedules/noise_schedule.py, edm_noise_schedule.py:61-75, cosine_noise_schedule.py:60-63). */
+int bfk_schedule_alpha_sigma(const bfk_schedule* sched, double t, double* alpha, double* sigma);
+/* One annealed-Langevin update on (B, D) rows (utils/integrate.py:924-961 `_apply_corrector`, :1167-1251
+ * `integrate_langevin`): score = 2*(fz*x - v_ode)/beta from the probability-flow velocity the network kernels return;
+ * out = x + e*score + sqrt(2e)*z with e = 2*a*(b*||z||/max(||score||,1e-8))^2 per row (per_row != 0: a = alpha_t,
+ * b = step_size_factor) or e = a (per_row == 0: a = effective_factor*sigma_t^2).  out must not alias the inputs. */
+int bfk_sde_langevin_update(const float* x, const float* v_ode, const float* z, int64_t B, int32_t D, double fz, double beta,
+                            double a, double b, int32_t per_row, float* out, void* stream);
 /* Runge-Kutta linear combination for host-driven integration (utils/integrate.py:47-54 add_scaled, :31-44, :98-105):
  * out[i] = y[i] + h * sum_j coef[j] * k[j][i], j < n (n <= 8), accumulated left to right in fp32 like the reference. */
 int bfk_rk_combine(const float* y, const float* const* k, const float* coef, int32_t n, float h, int64_t numel, float* out,

@@ -55,14 +55,48 @@ def test_default_sampler_is_the_reverse_sde_and_is_seeded():
         assert ((a[sl].std(0).cpu() / ref[sl].std(0)) - 1).abs().max() < 0.15
 
 
-def test_unbuilt_methods_and_layerwise_path():
+@pytest.mark.parametrize("method,steps,extra", [
+    ("sea", 25, {}), ("shark", 25, {}), ("langevin", 40, {}), ("langevin", 15, {"step_size_factor": 0.02}),
+    ("euler_maruyama", 20, {"corrector_steps": 2}), ("shark", 12, {"corrector_steps": 1, "step_size_factor": 0.05}),
+    ("langevin", 12, {"corrector_steps": 1}), ("two_step_adaptive", "adaptive", {"corrector_steps": 1}),
+])
+@pytest.mark.parametrize("sched", ["edm", "cosine"])
+def test_sea_shark_langevin_and_corrector(method, steps, extra, sched):
+    """utils/integrate.py:746-961, 1167-1251: same normals in the reference's draw order (dW, aux, corrector draws)."""
+    net, orc = make_pair(3, 6, (128,) * 2, dm=True, model_kwargs={"noise_schedule": sched})
+    B = 300
+    z, c = torch.randn(B, 3), grouped_conditions(B, 6, 100)
+    Z = _normals(2200, (B, 3), seed=11)
+    ref = orc.inverse(z, c, method=method, steps=steps, noise_fn=lambda i, s: {"xz": Z[i]}, **extra)
+    out = net(z.cuda(), conditions=c.cuda(), inverse=True, method=method, steps=steps, noise_fn=lambda i, shape: Z[i], **extra)
+    assert torch.isfinite(out).all()
+    assert rel_l2(out, ref) < TOL, rel_l2(out, ref)
+
+
+def test_philox_increments_are_keyed_by_seed_draw_and_global_row():
+    """no noise_fn: bfk_normal_fill keyed by (seed, draw, global row) - a shard of rows equals those rows of the big call
+    for the fixed-step samplers (time is shared; nothing else couples the rows)."""
+    net, _ = make_pair(2, 4, (128,) * 2, dm=True)
+    B = 512
+    c = grouped_conditions(B, 4, 128).cuda()
+    for method, kw in (("euler_maruyama", {}), ("shark", {}), ("langevin", {"corrector_steps": 1})):
+        full = net.sample((B,), conditions=c, seed=21, method=method, steps=8, **kw)
+        again = net.sample((B,), conditions=c, seed=21, method=method, steps=8, **kw)
+        other = net.sample((B,), conditions=c, seed=22, method=method, steps=8, **kw)
+        part = net.sample((128,), conditions=c[256:384], seed=21, method=method, steps=8, row_offset=256, **kw)
+        assert torch.equal(full, again) and not torch.equal(full, other)
+        assert rel_l2(part, full[256:384]) < 1e-5, (method, rel_l2(part, full[256:384]))
+        assert net.last_integration_info["draws"] == {"euler_maruyama": 8, "shark": 16, "langevin": 16}[method]
+
+
+def test_method_errors_and_layerwise_path():
     net, _ = make_pair(2, None, (64,) * 2, dm=True)
     z = torch.randn(16, 2).cuda()
     for m in ("sea", "shark", "langevin"):
-        with pytest.raises(NotImplementedError):
-            net(z, inverse=True, method=m, steps=5)
-    with pytest.raises(ValueError):
-        net(z, inverse=True, method="shark", steps="adaptive")
+        with pytest.raises(ValueError):
+            net(z, inverse=True, method=m, steps="adaptive")
+    with pytest.raises(NotImplementedError):
+        net(z, inverse=True, method="langevin", steps=4, target_mask=torch.tensor([1.0, 0.0]), targets_fixed=z)
     # wide network: the same host loop drives the layer-wise velocity kernels
     netw, orcw = make_pair(12, 5, (512,) * 2, dm=True)
     zz, c = torch.randn(200, 12), grouped_conditions(200, 5, 50)
