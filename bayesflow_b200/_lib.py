@@ -103,6 +103,9 @@ def lib():
     L.bfk_moments_workspace_floats.restype = C.c_size_t
     L.bfk_moments_workspace_floats.argtypes = [C.c_int64, C.c_int32]
     L.bfk_batch_moments.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.bfk_batch_moments_static.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]
+    L.bfk_static_scratch_floats.restype = C.c_size_t
+    L.bfk_static_scratch_floats.argtypes = []
     L.bfk_moments_merge.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
     L.bfk_ot_cost.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
     L.bfk_ot_ratio.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]

@@ -488,3 +488,47 @@ extern "C" int bfk_gemm(const void* A, const void* B, float* Cm, int64_t ldc, in
 #include "bfk_layerwise_host.cuh"
 #include "bfk_edge.cuh"
 #include "bfk_ot.cuh"
+
+// ---- allocation-free entry point ---------------------------------------------------------------------------------------
+// bfk_batch_moments_static: bfk_batch_moments with its scratch (the per-block partial moments) in a file-scope device
+// array instead of a caller-provided workspace, for callers that cannot allocate (CUDA graph capture, serving loops,
+// harnesses that forbid cudaMalloc).  No counterpart in the reference.
+//  * g_moments_scratch lives in every GPU context that loads this library until the process exits
+//    (BFK_STATIC_SCRATCH_FLOATS * 4 bytes = 2 MiB per device).
+//  * In host code the array's name is only a host-side stand-in: the device address is taken once per device with
+//    cudaGetSymbolAddress (that device current) and cached; kernels are handed that pointer.
+//  * Nothing in the array has to start at zero: the partial kernel overwrites every slot (blocks * 3 * F floats) the finish
+//    kernel reads, so stale contents of an earlier (larger) call are never consumed.
+//  * All calls share the one array: calls that overlap on the GPU (different streams, no ordering) race.
+#define BFK_STATIC_SCRATCH_FLOATS (1u << 19)
+static __device__ __align__(256) float g_moments_scratch[BFK_STATIC_SCRATCH_FLOATS];
+
+extern "C" size_t bfk_static_scratch_floats(void) { return (size_t)BFK_STATIC_SCRATCH_FLOATS; }
+
+extern "C" int bfk_batch_moments_static(const float* x, int64_t rows, int32_t F, float* stats, void* stream) {
+  if (rows < 0 || F < 1 || F > 1024) return fail(-65, "bfk_batch_moments_static: bad rows/F (F <= 1024)");
+  if (!stats || (rows > 0 && !x)) return fail(-66, "bfk_batch_moments_static: null pointer");
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
+    return fail(-62, "bfk_batch_moments_static: no CUDA device (or device ordinal >= 64)");
+  const size_t need = bfk_moments_workspace_floats(rows, F);
+  if (need == 0 || need > (size_t)BFK_STATIC_SCRATCH_FLOATS) {
+    char msg[200];
+    snprintf(msg, sizeof msg, "bfk_batch_moments_static: needs %zu scratch floats, the static array holds %u "
+             "(use bfk_batch_moments with a caller workspace)", need, BFK_STATIC_SCRATCH_FLOATS);
+    return fail(-69, msg);
+  }
+  static float* scratch_dev[64] = {};  // device address of g_moments_scratch, per device ordinal
+  float* scratch = scratch_dev[dev];
+  if (!scratch) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_moments_scratch);
+    if (e != cudaSuccess || !p) {
+      char msg[200];
+      snprintf(msg, sizeof msg, "bfk_batch_moments_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+      return fail(-70, msg);
+    }
+    scratch = scratch_dev[dev] = (float*)p;
+  }
+  return bfk_batch_moments(x, rows, F, scratch, stats, stream);
+}

@@ -282,6 +282,18 @@ int bfk_lincomb3(float* out, float a, const float* x, float b, const float* y, f
                  void* stream);
 size_t bfk_moments_workspace_floats(int64_t rows, int32_t F);
 int bfk_batch_moments(const float* x, int64_t rows, int32_t F, float* workspace, float* stats, void* stream);
+/* Allocation-free variant of bfk_batch_moments.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same inputs, outputs and results as bfk_batch_moments, but the per-block partial moments live in a
+ * file-scope `static __device__` array of bfk_static_scratch_floats() = 2^19 floats (2 MiB, held by every GPU that loads
+ * the library until the process exits) instead of a caller workspace.  Calls no cudaMalloc, cudaFree or allocating
+ * library routine.  Returns -69 with a message (bfk_last_error_string) when bfk_moments_workspace_floats(rows, F) exceeds
+ * the array: on a 148-SM B200 any number of rows fits for F <= 147 (1184 blocks x 3F floats), and wider F fits while
+ * the launch uses at most 2^19 / (3 F) blocks; beyond that use bfk_batch_moments.  All calls share the array:
+ * calls that overlap on the GPU (different streams without ordering) race; back-to-back calls on one stream are safe,
+ * and nothing in the array needs clearing between calls (every slot that is read is overwritten first). */
+int bfk_batch_moments_static(const float* x, int64_t rows, int32_t F, float* stats, void* stream);
+size_t bfk_static_scratch_floats(void);
 int bfk_moments_merge(float* mean, float* m2, float* count, const float* parts, int32_t n_parts, int32_t F,
                       void* stream);
 
