@@ -15,7 +15,14 @@ constexpr int FKC = 32;           // folded kernel: K rows of a full weight stag
                                   // the issuer pays one mbarrier wait per stage); the XK tail is one more, half-filled stage
 constexpr int EPI_WARPS = 8, MMA_WARP = 8, LOAD_WARP = 9, NUM_THREADS = 320;
 // fast kernel: 16 epilogue warps (tile = (w>>2)&1, TMEM lane quarter = w&3, column half = w>>3) + issuer + producer
-constexpr int F_EPI_WARPS = 16, F_MMA_WARP = 16, F_LOAD_WARP = 17, F_NUM_THREADS = 576;
+// BFK_EPI_REGS (setmaxnreg): 20 warps are launched (two idle ones complete the fifth warpgroup); after set-up the four
+// epilogue warpgroups raise their register file share to BFK_EPI_REGS and the issuer / producer warpgroup drops to what is
+// left of the 20 x 96 pool.  0 = 18 warps, 96 registers each (ptxas rounds 576 threads up to 640 for the register cap).
+#ifndef BFK_EPI_REGS
+#define BFK_EPI_REGS 104
+#endif
+constexpr int F_EPI_WARPS = 16, F_MMA_WARP = 16, F_LOAD_WARP = 17, F_NUM_THREADS = BFK_EPI_REGS ? 640 : 576;
+constexpr int F_AUX_REGS = BFK_EPI_REGS ? (20 * 96 - 16 * BFK_EPI_REGS) / 4 : 0;
 constexpr int TABLE_SCALARS = 8;  // per-evaluation scalars after the FiLM vectors: coefZ, coefP, time, norm-time, ...
 constexpr size_t SMEM_LIMIT = 232448;
 

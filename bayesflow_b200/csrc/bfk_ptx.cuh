@@ -21,14 +21,28 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
   asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(bar), "r"(bytes)
                : "memory");
 }
+// The waiting warps (epilogue warps during their tile's MMA, issuer, producer) share their SM sub-partition's issue port
+// with the working ones: without a suspend-time hint try_wait comes back every ~40 cycles and the spin loop was 46 % of
+// all issued instructions (profiles/r02e); with it the kernel is 4.6 % faster (r02f; 500 ns ... 1 ms all the same).
+#ifndef BFK_WAIT_HINT_NS
+#define BFK_WAIT_HINT_NS 2000
+#endif
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
+#if BFK_WAIT_HINT_NS
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"  // suspend-time hint: fewer spin iterations
+#else
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+#endif
       "selp.u32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
+#if BFK_WAIT_HINT_NS
+      : "r"(bar), "r"(parity), "r"((uint32_t)BFK_WAIT_HINT_NS)
+#else
       : "r"(bar), "r"(parity)
+#endif
       : "memory");
   return ok != 0;
 }
@@ -198,7 +212,11 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return fmaf(x, 0.5f, 1.f);  // experiment: no MUFU
 #else
   float y;
+#ifdef BFK_MUFU_VOLATILE  // keeps the source order of the MUFU ops (the compiler otherwise serialises pair by pair)
+  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+#else
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+#endif
   return y;
 #endif
 }
@@ -207,9 +225,54 @@ __device__ __forceinline__ float rcp_approx(float x) {
   return fmaf(x, 0.25f, 0.5f);
 #else
   float y;
+#ifdef BFK_MUFU_VOLATILE
+  asm volatile("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+#else
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+#endif
   return y;
 #endif
+}
+
+// ---- MUFU relief: the epilogues are bound by the 16-lane XU pipe (ex2 + rcp per element), so a compile-time share of
+// the element PAIRS takes the FMA pipe instead (the FlashAttention-4 remedy).  Masks are over the 8 float2 of a 16-column
+// chunk; 0 = MUFU.
+#ifndef BFK_RCP_NEWTON_MASK
+#define BFK_RCP_NEWTON_MASK 0
+#endif
+#ifndef BFK_EX2_POLY_MASK
+#define BFK_EX2_POLY_MASK 0
+#endif
+#ifndef BFK_EX2_POLY_DEG
+#define BFK_EX2_POLY_DEG 4
+#endif
+// 1 / d for d in [1, 2^100]: exponent-flip seed (5 % off) and two Newton steps on packed FMAs -> 7e-6 relative
+__device__ __forceinline__ float2 rcp_newton2(float2 d) {
+  float2 y = make_float2(__int_as_float(0x7EF311C7 - __float_as_int(d.x)), __int_as_float(0x7EF311C7 - __float_as_int(d.y)));
+  const float2 nd = make_float2(-d.x, -d.y);  // folded into the FFMA2 operand negation
+  float2 r = __ffma2_rn(nd, y, make_float2(1.f, 1.f));
+  y = __ffma2_rn(y, r, y);
+  r = __ffma2_rn(nd, y, make_float2(1.f, 1.f));
+  return __ffma2_rn(y, r, y);
+}
+// 2^t for t in [-120, 120]: round-to-nearest split by the 1.5 * 2^23 trick, minimax polynomial on [-0.5, 0.5] (degree 4:
+// 4e-6 relative, degree 3: 1e-4), exponent added to the bit pattern ((bits(z) << 23) keeps only the integer part)
+__device__ __forceinline__ float2 ex2_poly2(float2 t) {
+  const float2 magic = make_float2(12582912.f, 12582912.f);
+  const float2 z = __fadd2_rn(t, magic);
+  const float2 fr = __fadd2_rn(t, __fadd2_rn(magic, make_float2(-z.x, -z.y)));  // t - (z - magic)
+#if BFK_EX2_POLY_DEG == 3
+  float2 p = __ffma2_rn(fr, make_float2(0.05592203512787819f, 0.05592203512787819f), make_float2(0.24264007806777954f, 0.24264007806777954f));
+  p = __ffma2_rn(p, fr, make_float2(0.6931210160255432f, 0.6931210160255432f));
+  p = __ffma2_rn(p, fr, make_float2(0.9999244809150696f, 0.9999244809150696f));
+#else
+  float2 p = __ffma2_rn(fr, make_float2(0.009676037356257439f, 0.009676037356257439f), make_float2(0.05592203512787819f, 0.05592203512787819f));
+  p = __ffma2_rn(p, fr, make_float2(0.2402210682630539f, 0.2402210682630539f));
+  p = __ffma2_rn(p, fr, make_float2(0.6931210160255432f, 0.6931210160255432f));
+  p = __ffma2_rn(p, fr, make_float2(1.0000001192092896f, 1.0000001192092896f));
+#endif
+  return make_float2(__int_as_float(__float_as_int(p.x) + (__float_as_int(z.x) << 23)),
+                     __int_as_float(__float_as_int(p.y) + (__float_as_int(z.y) << 23)));
 }
 
 }  // namespace bfk

@@ -40,25 +40,42 @@ namespace bfk {
 // silu: the multiply by log2(e) in front of ex2 disappears.  All MUFU of the chunk issued back to back.
 template <int ACT>
 __device__ __forceinline__ void actw2x8(const float2* t, float2* w) {
-  if (ACT == BFK_ACT_MISH) {
+  constexpr bool ANY_ALT = (BFK_RCP_NEWTON_MASK | BFK_EX2_POLY_MASK) != 0;
+  constexpr float SGN = ACT == BFK_ACT_MISH ? 1.f : -1.f;  // mish: 2^t, silu: 2^-t
+  // exponent argument, clamped where a pair leaves the MUFU (inf would poison the Newton steps / the exponent add)
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { w[i].x = ex2_approx(t[i].x); w[i].y = ex2_approx(t[i].y); }
+  for (int i = 0; i < 8; ++i) {
+    float2 a = make_float2(SGN * t[i].x, SGN * t[i].y);
+    if (ANY_ALT && (((BFK_RCP_NEWTON_MASK | BFK_EX2_POLY_MASK) >> i) & 1))
+      a = make_float2(fminf(fmaxf(a.x, -100.f), 40.f), fminf(fmaxf(a.y, -100.f), 40.f));
+    if ((BFK_EX2_POLY_MASK >> i) & 1) w[i] = ex2_poly2(a);
+    else { w[i].x = ex2_approx(a.x); w[i].y = ex2_approx(a.y); }
+  }
+  if (ACT == BFK_ACT_MISH) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const float2 q = __fadd2_rn(w[i], f2(1.f));
-      w[i] = __ffma2_rn(q, q, f2(1.f));
+      w[i] = __ffma2_rn(q, q, f2(1.f));  // d = (1 + 2^t)^2 + 1
     }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { w[i].x = rcp_approx(w[i].x); w[i].y = rcp_approx(w[i].y); }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) w[i] = __ffma2_rn(w[i], f2(-1.3862943611198906f), f2(0.6931471805599453f));
+    for (int i = 0; i < 8; ++i) {
+      if ((BFK_RCP_NEWTON_MASK >> i) & 1) {
+        // ln2 * (d - 2) / d: no cancellation against ln2, so the 7e-6 of the Newton reciprocal stays relative
+        const float2 n = __ffma2_rn(w[i], f2(0.6931471805599453f), f2(-1.3862943611198906f));
+        w[i] = __fmul2_rn(n, rcp_newton2(w[i]));
+      } else {
+        w[i].x = rcp_approx(w[i].x); w[i].y = rcp_approx(w[i].y);
+        w[i] = __ffma2_rn(w[i], f2(-1.3862943611198906f), f2(0.6931471805599453f));
+      }
+    }
   } else {  // silu
-#pragma unroll
-    for (int i = 0; i < 8; ++i) { w[i].x = ex2_approx(-t[i].x); w[i].y = ex2_approx(-t[i].y); }
 #pragma unroll
     for (int i = 0; i < 8; ++i) w[i] = __fadd2_rn(w[i], f2(1.f));
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { w[i].x = rcp_approx(w[i].x); w[i].y = rcp_approx(w[i].y); }
+    for (int i = 0; i < 8; ++i) {
+      if ((BFK_RCP_NEWTON_MASK >> i) & 1) w[i] = rcp_newton2(w[i]);
+      else { w[i].x = rcp_approx(w[i].x); w[i].y = rcp_approx(w[i].y); }
+    }
 #pragma unroll
     for (int i = 0; i < 8; ++i) w[i] = __fmul2_rn(w[i], f2(0.6931471805599453f));
   }
@@ -233,7 +250,11 @@ __device__ __forceinline__ void fold_producer_loop(const SamplerArgs& a, const B
           for (int c = 0; c <= n_chunks; ++c) {
             mbar_wait(bars.w_empty(stage), ((ph_empty >> stage) & 1) ^ 1, a.err_flag, 6);
             ph_empty ^= (1u << stage);
+#if (BFK_EXP & 64)
+            const uint32_t bytes = 128;  // experiment: (almost) no weight streaming, stale operands
+#else
             const uint32_t bytes = (c < n_chunks) ? a.plan.stage_bytes : (uint32_t)(XK * W * 2);
+#endif
             mbar_arrive_expect_tx(bars.w_full(stage), bytes);
             bulk_g2s(smem_base + a.plan.ring + stage * a.plan.stage_bytes,
                      a.wg + (size_t)g * layer_bytes + (size_t)c * FKC * W * 2, bytes, bars.w_full(stage));
@@ -288,6 +309,9 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
 
   if (warp < F_EPI_WARPS) {
     // =========================================================== EPILOGUE / ODE warps
+#if BFK_EPI_REGS
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(BFK_EPI_REGS));
+#endif
     const int tile = (warp >> 2) & 1, quarter = warp & 3, half = warp >> 3;
     const int r = quarter * 32 + lane;  // row inside the tile == TMEM lane
     const int nch = W / 32, ch0 = half * nch;  // this warp's 16-column chunks: ch0 .. ch0 + nch - 1
@@ -587,9 +611,19 @@ __global__ void __launch_bounds__(F_NUM_THREADS, 1) sampler_fold_kernel(const Sa
     PROF_FLUSH(warp)
     tc_fence_before();
   } else if (warp == F_MMA_WARP) {
+#if BFK_EPI_REGS
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(F_AUX_REGS));
+#endif
     fold_issuer_loop(a, bars, smem_base, tmem_base, my_tiles, n_evals, lane);
-  } else {
+  } else if (warp == F_LOAD_WARP) {
+#if BFK_EPI_REGS
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(F_AUX_REGS));
+#endif
     fold_producer_loop(a, bars, smem_base, my_tiles, n_evals, lane);
+  } else {
+#if BFK_EPI_REGS
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(F_AUX_REGS));  // the two idle warps of the fifth warpgroup
+#endif
   }
 
   __syncthreads();

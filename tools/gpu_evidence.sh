@@ -1,0 +1,18 @@
+#!/bin/bash
+# one gpurun call: GPU suite, smoke, both bench arms, ncu launch list + one full capture of the dominant kernel
+# usage (on the GPU box, from the repo root): bash tools/gpu_evidence.sh r02e
+tag=${1:-r02x}
+out=gpurun_out
+mkdir -p $out
+python -m pytest tests -q -m gpu > $out/${tag}_pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a $out/${tag}_pytest_gpu.log
+python -c "import __graft_entry__ as g; g.smoke()" > $out/${tag}_smoke.log 2>&1; echo "smoke rc=$?" | tee -a $out/${tag}_smoke.log
+python bench.py --impl reference --steps 3 --warmup 1 > $out/${tag}_ref.json 2> $out/${tag}_ref.err; echo "ref rc=$?"
+python bench.py > $out/${tag}_bench.json 2> $out/${tag}_bench.err; echo "bench rc=$?"
+tail -c 1500 $out/${tag}_bench.json
+short="python bench.py --steps 2 --warmup 1 --no-train --no-cpu-baseline"
+$short > $out/${tag}_plain.log 2>&1 || exit 0
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/${tag}_launches.csv $short > $out/${tag}_ncu_launch.log 2>&1
+echo "launch list rc=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:sampler_fold -s 1 -c 1 -f -o $out/${tag}_fold $short > $out/${tag}_ncu_full.log 2>&1
+echo "full capture rc=$?"
+ls -la $out | tail -12
