@@ -275,7 +275,10 @@ static sampler_fn pick_kernel(const bfk_net_config* c, int* threads) {
   PICK(BFK_ACT_MISH, 2, false)
 #ifndef BFK_DEV_BUILD
   PICK(BFK_ACT_MISH, 4, false) PICK(BFK_ACT_MISH, 8, false)
-  PICK(BFK_ACT_SILU, 2, false) PICK(BFK_ACT_SILU, 4, false)
+  PICK(BFK_ACT_SILU, 2, false) PICK(BFK_ACT_SILU, 4, false) PICK(BFK_ACT_SILU, 8, false)
+  PICK(BFK_ACT_RELU, 2, false) PICK(BFK_ACT_RELU, 4, false) PICK(BFK_ACT_RELU, 8, false)
+  PICK(BFK_ACT_GELU, 2, false) PICK(BFK_ACT_GELU, 4, false) PICK(BFK_ACT_GELU, 8, false)
+  PICK(BFK_ACT_TANH, 2, false) PICK(BFK_ACT_TANH, 4, false) PICK(BFK_ACT_TANH, 8, false)
 #endif
 #undef PICK
   return nullptr;

@@ -71,11 +71,21 @@ class VelocityTrace:
                 cond = torch.zeros_like(cond)
             self.cond = cond.contiguous()
         self.max_steps = max_steps
+        # Hutchinson probes (jacobian_trace.py:58-89): bfk_normal_fill (Philox) keyed by (seed, probe number, GLOBAL row),
+        # so a dataset shard draws the probes of the same rows of the single-GPU call
         self.gen = None
         if max_steps is not None and self.D > max_steps:
-            self.gen = torch.Generator(device=self.eng.device)
-            self.gen.manual_seed(int(seed) if seed is not None else torch.initial_seed())
+            self.gen = (int(seed) if seed is not None else torch.initial_seed()) & (2 ** 62 - 1)
+        self.probe, self.row_offset = 0, 0
         self.evals = 0
+
+    def _probe(self, like):
+        out = torch.empty(self.B, self.D, device=like.device, dtype=torch.float32)
+        key = (self.gen * 0x9E3779B97F4A7C15 + (self.probe + 1) * 0xD1B54A32D192ED03) & (2 ** 64 - 1)
+        self.probe += 1
+        _lib.check(_lib.lib().bfk_normal_fill(_lib.ptr(out), self.B, self.D, int(self.row_offset), None, None, key, None,
+                                              _lib.stream_ptr()), "bfk_normal_fill")
+        return out
 
     def affine(self, time: float):
         """velocity = cZ * xz + cP * pred(xz, t_net): (cZ, cP, t_net).  FlowMatching: (0, 1, time)."""
@@ -92,7 +102,7 @@ class VelocityTrace:
                 eng.vjp(args, ws, col=d, trace=trace)
         else:  # Hutchinson (jacobian_trace.py:58-89)
             for _ in range(self.max_steps):
-                proj = torch.randn(self.B, D, device=xz.device, dtype=torch.float32, generator=self.gen)
+                proj = self._probe(xz)
                 dx = eng.vjp(args, ws, dout=proj, want_dx=True)
                 trace += (dx * proj).sum(-1)
         self.evals += 1

@@ -457,6 +457,13 @@ def run_ours(args, name, w):
             edge = measure_edge(dev, peaks["hbm_gbs"])
         except Exception as exc:
             edge = {"unavailable": repr(exc)[:200]}
+    adaptive = None
+    if rank == 0 and world == 1 and not args.no_train:
+        try:
+            torch.cuda.empty_cache()
+            adaptive = measure_adaptive(dev)
+        except Exception as exc:
+            adaptive = {"unavailable": repr(exc)[:200]}
     if rank == 0:
         line = {"metric": "posterior draws/sec", "value": value, "unit": "draws/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": args.scaling,
@@ -477,7 +484,7 @@ def run_ours(args, name, w):
                 "cpu_baseline": cpu,
                 "integration": info, "wall_s_timed_region": wall, "train": train, "wide_cfg4": wide,
                 "cfg5_fm_train_wide": train_wide,
-                "sampler_api": sampler_api, "edge_kernels": edge}
+                "sampler_api": sampler_api, "edge_kernels": edge, "adaptive_cfg1": adaptive}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -530,6 +537,42 @@ def measure_sampling_simple(w, name, dev, world, rank, scaling, steps=2, warmup=
             "steps": steps, "warmup": warmup, "scaling": scaling, "config": workload_config(name, w, world, scaling),
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",
                          "frac": achieved / peaks["tflops"], "note": "per GPU, whole call (all launches of bfk_sample_layerwise)"}}
+
+
+def measure_adaptive(dev, steps=3, warmup=3):
+    """BASELINE.json configs[0]'s solver at configs[0]'s shape: FlowMatching.sample with the network's DEFAULT integrator
+    (tsit5, steps="adaptive", utils/integrate.py:291-406; networks/defaults.py:44-48) on 512 x 1000 two-moons-shaped rows.
+    The step controller is global (max error over all rows), so the evaluation count is data dependent and is reported."""
+    import torch
+    import bayesflow_b200 as bf
+    w = WORKLOADS["cfg1_twomoons_fm_euler100"]
+    torch.manual_seed(1234)
+    net = bf.FlowMatching(subnet_kwargs={"dropout": 0.0, "widths": w["widths"]})
+    net.build((None, w["D"]), (None, w["C"]))
+    net.to(dev)
+    N, S = w["N"], w["S"]
+    cond = torch.randn(N, w["C"], generator=torch.Generator().manual_seed(2345)).to(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    fn = lambda: bf.Sampler().sample(net, S, conditions=cond, seed=1234)  # noqa: E731  (no integrate kwargs: the default)
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    pairs = []
+    for _ in range(steps):
+        flush.fill_(1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        pairs.append((a, b))
+    torch.cuda.synchronize()
+    ms = sum(a.elapsed_time(b) for a, b in pairs) / steps
+    info = dict(getattr(net, "last_integration_info", {}) or {})
+    return {"metric": "posterior draws/sec", "value": N * S / (ms * 1e-3), "unit": "draws/s", "ms_per_step": ms, "steps": steps,
+            "warmup": warmup, "config": {"workload": "cfg1_twomoons_fm_tsit5_adaptive", "D": w["D"], "C": w["C"],
+                                         "datasets": N, "draws_per_dataset": S,
+                                         "solver": "tsit5 steps='adaptive' (the network default), global step control"},
+            "integration": {k: info.get(k) for k in ("method", "steps", "rejected", "evals") if k in info}}
 
 
 # --------------------------------------------------------------------------------------------------- training arms

@@ -6,11 +6,14 @@ import oracle
 _PKEYS = ("merge", "film_use_gamma", "norm", "residual", "time_embedding_dim")
 
 
-def make_pair(D, C, widths=(256,) * 5, dm=False, net_kwargs=None, model_kwargs=None, **sk):
-    """-> (bayesflow_b200 network on cuda:0, oracle on CPU), same perturbed weights."""
+def make_pair(D, C, widths=(256,) * 5, dm=False, net_kwargs=None, model_kwargs=None, params_fn=None, **sk):
+    """-> (bayesflow_b200 network on cuda:0, oracle on CPU), same perturbed weights.
+    `params_fn(params) -> params` edits the shared weights first (range stress tests)."""
     import bayesflow_b200 as bf
 
     params = oracle.perturb_params(oracle.init_params(D, C, widths, **{k: v for k, v in sk.items() if k in _PKEYS}))
+    if params_fn is not None:
+        params = params_fn(params)
     kw = {"dropout": 0.0, "widths": widths} | sk
     mk = model_kwargs or {}
     if dm:
