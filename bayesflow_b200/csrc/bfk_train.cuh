@@ -587,7 +587,8 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
 __global__ void loss_kernel(const float* __restrict__ pred, long long ldp, const float* __restrict__ target,
                             const float* __restrict__ a_row, const float* __restrict__ w_row, long long B, long long R_pad,
                             int D, int kind, unsigned char* __restrict__ dout_img, int KO8, float* __restrict__ loss,
-                            float loss_scale, float* __restrict__ d_bo, float gscale, float huber_c) {
+                            float loss_scale, float* __restrict__ d_bo, float gscale, float huber_c,
+                            const float* __restrict__ elem_mask = nullptr) {
   __shared__ float s_loss;
   __shared__ float s_db[64];
   if (threadIdx.x == 0) s_loss = 0.f;
@@ -606,7 +607,9 @@ __global__ void loss_kernel(const float* __restrict__ pred, long long ldp, const
         const int k = k8 * 8 + i;
         float g = 0.f;
         if (valid && k < D) {
-          const float res = av * pred[r * ldp + k] - target[r * D + k];
+          // elem_mask: the 0 / 1 target-dropout mask of flow_matching.py:170-175 / diffusion_model.py:177-216 (loss of
+          // mask * target against mask * prediction)
+          const float res = (av * pred[r * ldp + k] - target[r * D + k]) * (elem_mask ? elem_mask[r * D + k] : 1.f);
           if (kind == 1) { lrow += fabsf(res); g = wv * av * (res > 0.f ? 1.f : (res < 0.f ? -1.f : 0.f)); }
           else if (kind == 2) {
             const float rt = sqrtf(fmaf(res, res, huber_c * huber_c));

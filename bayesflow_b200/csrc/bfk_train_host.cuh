@@ -231,7 +231,8 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   if (!loss && !bwd) return 0;
   float* loss_dst = loss ? loss : b.FB;  // FB is free by now: scratch float when the caller does not want the loss
   loss_kernel<<<(unsigned)((Rp + 255) / 256), 256, 0, st>>>(b.out, NO, ta->target, ta->pred_scale, ta->row_weight, B, Rp, D, ta->loss,
-                                                           b.dout_img, NO / 8, loss_dst, ta->loss_scale, bwd ? GP(g->out_b) : (float*)nullptr, gs, ta->huber_c);
+                                                           b.dout_img, NO / 8, loss_dst, ta->loss_scale, bwd ? GP(g->out_b) : (float*)nullptr, gs, ta->huber_c,
+                                                           ta->elem_mask);
   CK(cudaGetLastError());
   if (!bwd) return 0;
 

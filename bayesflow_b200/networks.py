@@ -626,7 +626,8 @@ class InferenceNetwork(nn.Module):
         gradient; ``loss.backward()`` then fills ``p.grad`` exactly like the reference's autograd path."""
         from .training import _LossWithGrads, train_engine
         backward = torch.is_grad_enabled() and stage == "training"
-        extra = {k: kwargs[k] for k in ("fixed", "row_offset", "ot_seed", "noise_seed") if k in kwargs}
+        extra = {k: kwargs[k] for k in ("fixed", "row_offset", "ot_seed", "noise_seed", "cond_keep", "target_keep")
+                 if k in kwargs}
         with self._device_guard(x[1] if isinstance(x, (tuple, list)) else x):
             loss = self._loss_and_grads(x, conditions, sample_weight, stage=stage, seed=kwargs.get("seed"),
                                         backward=backward, **extra)
@@ -637,6 +638,36 @@ class InferenceNetwork(nn.Module):
 
     def _graphable_training(self):
         return False
+
+    @staticmethod
+    def _keep_mask(rows, cols, drop_prob, seed, row_offset, device):
+        """0 / 1 keep mask with P(keep) = 1 - drop_prob (utils/tensor_utils.py:445-470 `random_mask`: uniform > drop_prob),
+        drawn as z > Phi^-1(drop_prob) from the Philox normal stream keyed by (seed, GLOBAL row): data-parallel ranks
+        mask disjoint rows of one batch."""
+        from statistics import NormalDist
+        if drop_prob >= 1.0:
+            return torch.zeros(rows, cols, device=device, dtype=torch.float32)
+        z = torch.empty(rows, cols, device=device, dtype=torch.float32)
+        with torch.cuda.device(device):
+            _lib.check(_lib.lib().bfk_normal_fill(_lib.ptr(z), rows, cols, int(row_offset), None, None,
+                                                  C.c_uint64(int(seed) & (2 ** 64 - 1)), None, _lib.stream_ptr()),
+                       "bfk_normal_fill")
+        return (z > NormalDist().inv_cdf(float(drop_prob))).to(torch.float32)
+
+    def _dropout_masks(self, B, D, conditions, noise_seed, row_offset, kwargs, device):
+        """-> (conditions with dropped rows zeroed, (B,D) target keep mask or None).  `cond_keep` (B,1) / `target_keep`
+        (B,D) in kwargs replace the draws (parity runs)."""
+        keep_t = kwargs.get("target_keep")
+        if self.drop_cond_prob > 0 and conditions is not None:
+            keep_c = kwargs.get("cond_keep")
+            if keep_c is None:
+                keep_c = self._keep_mask(B, 1, self.drop_cond_prob, int(noise_seed) ^ 0x6A09E667F3BCC908, row_offset, device)
+            conditions = conditions.to(torch.float32) * torch.as_tensor(keep_c, device=device, dtype=torch.float32).reshape(B, 1)
+        if self.drop_target_prob > 0 and keep_t is None:
+            keep_t = self._keep_mask(B, D, self.drop_target_prob, int(noise_seed) ^ 0x3C6EF372FE94F82B, row_offset, device)
+        if keep_t is not None:
+            keep_t = torch.as_tensor(keep_t, device=device, dtype=torch.float32).reshape(B, D).contiguous()
+        return conditions, keep_t
 
     def _dropout_seed(self, seed):
         if seed is None:
@@ -787,8 +818,6 @@ class FlowMatching(InferenceNetwork):
         are functions of the GLOBAL row, so data-parallel ranks draw disjoint rows of ONE batch); `seed_dev`: two device
         words that override the seeds (CUDA-graph replay)."""
         from .training import train_engine
-        if self.drop_cond_prob > 0 or self.drop_target_prob > 0:
-            raise NotImplementedError("drop_cond_prob / drop_target_prob > 0 are outside the accelerated training path")
         if (conditions is None) != (self._C is None):
             raise ValueError("network was built " + ("without" if self._C is None else "with") + " conditions")
         eng = train_engine(self)
@@ -826,12 +855,23 @@ class FlowMatching(InferenceNetwork):
                 u = 0.5 * (1.0 + torch.erf(zu * (1.0 / math.sqrt(2.0))))
                 t = u ** (1 + self.time_power_law_alpha)
                 x, target = eng.interpolate(x0, x1, t)
+        keep_t = None
+        if self.drop_cond_prob > 0 or self.drop_target_prob > 0 or "target_keep" in kwargs:
+            # flow_matching.py:167-175: conditions of dropped rows zeroed (classifier-free guidance); dropped target entries
+            # see the clean x1 and leave the loss (the loss kernel multiplies the residual by the mask)
+            if noise_seed is None:
+                noise_seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+            x = eng._f32(x)
+            conditions, keep_t = self._dropout_masks(x.shape[0], x.shape[1], conditions, noise_seed, row_offset, kwargs,
+                                                     x.device)
+            if keep_t is not None:
+                x = keep_t * x + (1.0 - keep_t) * eng._f32(x1)
         training = stage == "training"
         rate = float(self.subnet.dropout or 0.0) if training else 0.0
         seed = self._dropout_seed(seed)
         loss, _ = eng.step(x, t, conditions, target, row_weight=sample_weight, loss=self.loss_fn, dropout=rate, seed=seed,
                            global_batch=x.shape[0] * world, backward=backward, row_offset=row_offset, seed_dev=seed_dev,
-                           loss_into_slot=loss_into_slot)
+                           loss_into_slot=loss_into_slot, elem_mask=keep_t)
         return loss
 
     def _forward(self, x, conditions=None, density=False, training=False, **kwargs):
@@ -1009,8 +1049,6 @@ class DiffusionModel(InferenceNetwork):
         (parity runs); `row_offset` is this rank's first GLOBAL row (low-discrepancy t uses the global index,
         diffusion_model.py:159-161)."""
         from .training import train_engine
-        if self.drop_cond_prob > 0 or self.drop_target_prob > 0:
-            raise NotImplementedError("drop_cond_prob / drop_target_prob > 0 are outside the accelerated training path")
         if (conditions is None) != (self._C is None):
             raise ValueError("network was built " + ("without" if self._C is None else "with") + " conditions")
         if not torch.is_tensor(x) or not x.is_cuda:
@@ -1042,6 +1080,15 @@ class DiffusionModel(InferenceNetwork):
         alpha, sigma = ns.get_alpha_sigma(lam)
         x64, eps64 = x.to(f64), eps.to(f64)
         z = (alpha * x64 + sigma * eps64).to(torch.float32)
+        keep_t = None
+        if self.drop_cond_prob > 0 or self.drop_target_prob > 0 or "target_keep" in kwargs:
+            # diffusion_model.py:155-156, 177-178: dropped rows lose their conditions; dropped target entries see the clean x
+            # and leave the loss (the loss kernel multiplies the residual by the mask, :209-224)
+            if noise_seed is None:
+                noise_seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+            conditions, keep_t = self._dropout_masks(B, x.shape[1], conditions, noise_seed, row_offset, kwargs, dev)
+            if keep_t is not None:
+                z = keep_t * z + (1.0 - keep_t) * x.to(torch.float32)
         z64 = z.to(f64)
         cP, cZ = self._x_pred_coefs(alpha, sigma, lam)
         if self._loss_type == "noise":
@@ -1064,7 +1111,7 @@ class DiffusionModel(InferenceNetwork):
         loss, _ = eng.step(z, t_net.reshape(-1).to(torch.float32), conditions, target.to(torch.float32),
                            pred_scale=a.reshape(-1).to(torch.float32), row_weight=row_w.contiguous(), loss="mse",
                            dropout=rate, seed=self._dropout_seed(seed), global_batch=Bg, backward=backward,
-                           cotangent_scale=cot_scale, row_offset=row_offset, loss_into_slot=loss_into_slot)
+                           cotangent_scale=cot_scale, row_offset=row_offset, loss_into_slot=loss_into_slot, elem_mask=keep_t)
         return loss
 
     def _cotangent_scale(self, stage):

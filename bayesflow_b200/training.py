@@ -26,7 +26,8 @@ class TrainArgs(C.Structure):
     _fields_ = [("x", C.c_void_p), ("t", C.c_void_p), ("cond", C.c_void_p), ("target", C.c_void_p),
                 ("pred_scale", C.c_void_p), ("row_weight", C.c_void_p), ("B", C.c_int64), ("loss", C.c_int32),
                 ("dw_swap", C.c_int32), ("dropout", C.c_float), ("loss_scale", C.c_float), ("grad_scale", C.c_float),
-                ("seed", C.c_uint64), ("huber_c", C.c_float), ("seed_dev", C.c_void_p), ("row_offset", C.c_int64)]
+                ("seed", C.c_uint64), ("huber_c", C.c_float), ("seed_dev", C.c_void_p), ("row_offset", C.c_int64),
+                ("elem_mask", C.c_void_p)]
 
 
 def _bind(L):
@@ -143,7 +144,7 @@ class TrainEngine:
 
     def step(self, x, t, conditions, target, *, pred_scale=None, row_weight=None, loss="mse", dropout=0.0, seed=0,
              global_batch=None, backward=True, zero_grad=True, want_pred=False, want_loss=True, _dw_swap=0,
-             cotangent_scale=1.0, huber_c=0.0, row_offset=0, seed_dev=None, loss_into_slot=False):
+             cotangent_scale=1.0, huber_c=0.0, row_offset=0, seed_dev=None, loss_into_slot=False, elem_mask=None):
         """One forward (+ loss, + backward).  Gradients are accumulated into ``self.grad`` (zeroed first unless
         ``zero_grad=False``) scaled by 1/(global_batch*D).  Returns (loss 0-d device tensor or None, pred or None)."""
         net = self.net
@@ -172,6 +173,8 @@ class TrainEngine:
         a.huber_c = float(huber_c)
         a.row_offset = int(row_offset)
         a.seed_dev = seed_dev.data_ptr() if seed_dev is not None else None
+        elem_mask = self._f32(elem_mask, (B, D)) if elem_mask is not None else None  # kept alive until the launch below
+        a.elem_mask = elem_mask.data_ptr() if elem_mask is not None else None
         # `cotangent_scale` (a power of two already folded into row_weight by the caller) keeps the fp16 cotangent image
         # in range; loss and gradients are un-scaled here
         a.loss_scale = 1.0 / (gb * (D if loss in ("mse", "mae", "pseudo_huber") else 1)) / cotangent_scale

@@ -183,6 +183,8 @@ typedef struct bfk_train_args {
   const uint32_t* seed_dev; /* NULL, or 2 device words (lo, hi) that override `seed`: lets a captured CUDA graph of the step
                                be replayed with a new dropout mask */
   int64_t row_offset;      /* global index of row 0 (data-parallel shard): the dropout mask is a function of the global row */
+  const float* elem_mask;  /* (B,D) of 0 / 1 or NULL: loss of mask*target against mask*prediction (drop_target_prob,
+                              flow_matching.py:170-175, diffusion_model.py:177-216) */
 } bfk_train_args;
 size_t bfk_train_workspace_bytes(const bfk_net_config* cfg, int64_t B, int32_t backward);
 int bfk_train_step(const bfk_net_config* cfg, const bfk_weights* weights, const bfk_weights* grads,

@@ -242,8 +242,23 @@ def _mask(data, mask=None, replacement=None):
     return mask * data + (1 - mask) * replacement
 
 
+def random_mask(shape, drop_prob, generator=None):
+    # utils/tensor_utils.py:445-470: 1 (keep) where uniform > drop_prob; the python float 1.0 when drop_prob <= 0
+    if drop_prob <= 0:
+        return 1.0
+    return (torch.rand(tuple(shape), generator=generator) > drop_prob).to(torch.float32)
+
+
+def randomly_mask_along_axis(x, drop_prob, generator=None):
+    # utils/tensor_utils.py:473-504 (axis 0): whole rows zeroed, the classifier-free-guidance dropout
+    if drop_prob <= 0:
+        return x
+    return random_mask((x.shape[0],) + (1,) * (x.ndim - 1), drop_prob, generator) * x
+
+
 class OracleFlowMatching:
-    def __init__(self, params, D, subnet_kwargs=None, integrate_kwargs=None, time_power_law_alpha=0.0):
+    def __init__(self, params, D, subnet_kwargs=None, integrate_kwargs=None, time_power_law_alpha=0.0,
+                 drop_cond_prob=0.0, drop_target_prob=0.0):
         kw = dict(TIME_MLP_DEFAULTS) | (subnet_kwargs or {})  # flow_matching.py:122-125
         self.p = params
         self.D = D
@@ -251,6 +266,7 @@ class OracleFlowMatching:
         self.integrate_kwargs = {"method": "tsit5", "steps": "adaptive"} | (integrate_kwargs or {})  # defaults.py:52
         self.base_distribution = DiagonalNormal(D)
         self.time_power_law_alpha = float(time_power_law_alpha)
+        self.drop_cond_prob, self.drop_target_prob = float(drop_cond_prob), float(drop_target_prob)
         self.unconditional_mode = False
 
     def velocity(self, xz, time, conditions=None, training=False, dropout_masks=None, **kwargs):
@@ -318,8 +334,9 @@ class OracleFlowMatching:
         return self._integrate(z, conditions, False, 0.0, 1.0, **kwargs)
 
     def compute_metrics(self, x, conditions=None, sample_weight=None, stage="training", generator=None,
-                        dropout_masks=None):
-        # flow_matching.py:132-178 (optimal transport / cond dropout / target dropout at their default 0)
+                        dropout_masks=None, cond_keep=None, target_keep=None):
+        # flow_matching.py:132-178 (optimal transport at its default off).  `cond_keep` (B,1) / `target_keep` (B,D): fixed
+        # 0 / 1 masks in place of the RNG draws of :167-170 (parity runs)
         if isinstance(x, (tuple, list)):
             x0, x1, t, x, target_velocity = x
         else:
@@ -331,8 +348,14 @@ class OracleFlowMatching:
                 t = t.unsqueeze(-1)
             x = t * x1 + (1 - t) * x0
             target_velocity = x1 - x0
+        if self.drop_cond_prob > 0 and conditions is not None:  # :167-168
+            conditions = (cond_keep * conditions) if cond_keep is not None else \
+                randomly_mask_along_axis(conditions, self.drop_cond_prob, generator)
+        mask_x = target_keep if target_keep is not None else random_mask(x.shape, self.drop_target_prob, generator)  # :170
+        if not isinstance(mask_x, float):
+            x = mask_x * x + (1 - mask_x) * x1  # :171 maybe_mask_tensor(x, mask, replacement=x1)
         pred = self.velocity(x, time=t, conditions=conditions, training=stage == "training", dropout_masks=dropout_masks)
-        loss = torch.mean((pred - target_velocity) ** 2, dim=-1)  # keras "mse"
+        loss = torch.mean((mask_x * pred - mask_x * target_velocity) ** 2, dim=-1)  # keras "mse" of the masked pair, :175
         loss = torch.mean(loss * sample_weight if sample_weight is not None else loss)  # weighted_mean
         return {"loss": loss}
 
@@ -428,7 +451,8 @@ class CosineNoiseSchedule(EDMNoiseSchedule):
 
 class OracleDiffusionModel:
     def __init__(self, params, D, subnet_kwargs=None, integrate_kwargs=None, noise_schedule="edm",
-                 prediction_type="F", loss_type="noise", schedule_kwargs=None):
+                 prediction_type="F", loss_type="noise", schedule_kwargs=None, drop_cond_prob=0.0, drop_target_prob=0.0):
+        self.drop_cond_prob, self.drop_target_prob = float(drop_cond_prob), float(drop_target_prob)
         kw = dict(TIME_MLP_DEFAULTS) | (subnet_kwargs or {})
         self.p, self.D = params, D
         self.subnet = OracleTimeMLP(params, **kw)
@@ -567,10 +591,14 @@ class OracleDiffusionModel:
         return integrate(deltas, {"xz": z}, **ik)["xz"]
 
     def compute_metrics(self, x, conditions=None, sample_weight=None, stage="training", fixed=None, generator=None,
-                        dropout_masks=None):
-        # diffusion_model.py:142-232; `fixed=(u0, eps_t)` bypasses the RNG for parity runs
+                        dropout_masks=None, cond_keep=None, target_keep=None):
+        # diffusion_model.py:142-232; `fixed=(u0, eps_t)` bypasses the RNG for parity runs, `cond_keep` (B,1) /
+        # `target_keep` (B,D) are fixed 0 / 1 masks in place of the draws of :155-156 / :177
         training = stage == "training"
         B = x.shape[0]
+        if conditions is not None and self.drop_cond_prob > 0:
+            conditions = (cond_keep * conditions) if cond_keep is not None else \
+                randomly_mask_along_axis(conditions, self.drop_cond_prob, generator)
         if fixed is None:
             u0 = torch.rand((1,), generator=generator, dtype=x.dtype)
             eps_t = None
@@ -586,20 +614,23 @@ class OracleDiffusionModel:
         if eps_t is None:
             eps_t = torch.randn(x.shape, generator=generator, dtype=x.dtype)
         diffused_x = alpha_t * x + sigma_t * eps_t
+        mask_x = target_keep if target_keep is not None else random_mask(x.shape, self.drop_target_prob, generator)  # :177
+        if not isinstance(mask_x, float):
+            diffused_x = mask_x * diffused_x + (1 - mask_x) * x  # :178
         pred = self._subnet_pred(diffused_x, self._transform_log_snr(log_snr_t), conditions, training, dropout_masks)
         x_pred = self.convert_prediction_to_x(pred, diffused_x, alpha_t, sigma_t, log_snr_t, self._prediction_type)
         if self._loss_type == "noise":
             noise_pred = (diffused_x - alpha_t * x_pred) / sigma_t
-            per_row = torch.mean((noise_pred - eps_t) ** 2, dim=-1)
+            per_row = torch.mean(mask_x * (noise_pred - eps_t) ** 2, dim=-1)
         elif self._loss_type == "velocity":
             velocity_pred = (alpha_t * diffused_x - x_pred) / sigma_t
             v_t = alpha_t * eps_t - sigma_t * x
-            per_row = torch.mean((velocity_pred - v_t) ** 2, dim=-1)
+            per_row = torch.mean(mask_x * (velocity_pred - v_t) ** 2, dim=-1)
         else:
             sd = getattr(self.noise_schedule, "sigma_data", 1.0)
             x1 = torch.sqrt(torch.exp(-log_snr_t) + sd ** 2) / (torch.exp(-log_snr_t / 2) * sd)
             x2 = (sd * alpha_t) / (torch.exp(-log_snr_t / 2) * torch.sqrt(torch.exp(-log_snr_t) + sd ** 2))
-            per_row = torch.mean((x1 * x_pred - x2 * diffused_x - (x1 * x - x2 * diffused_x)) ** 2, dim=-1)
+            per_row = torch.mean(mask_x * (x1 * x_pred - x2 * diffused_x - (x1 * x - x2 * diffused_x)) ** 2, dim=-1)
         # Reference quirk kept on purpose (diffusion_model.py:212): weights_for_snr is (B,1) (log_snr_t was
         # right-expanded at :165) while ops.mean(..., axis=-1) is (B,), so the product broadcasts to (B,B) and
         # weighted_mean averages the outer product, i.e. mean(w) * mean(per-row mse).

@@ -262,6 +262,42 @@ def test_dm_compute_metrics_loss_and_gradients(R, schedule, ptype, ltype, monkey
 
 
 @pytest.mark.parametrize("dm", [False, True])
+@pytest.mark.parametrize("p_cond,p_target", [(0.3, 0.0), (0.0, 0.4), (0.25, 0.35)])
+def test_condition_and_target_dropout(R, dm, p_cond, p_target, monkeypatch):
+    """drop_cond_prob / drop_target_prob (flow_matching.py:167-175, diffusion_model.py:155-156, 177-216;
+    utils/tensor_utils.py:445-504): the reference draws its masks from keras.random.uniform - feed the same uniforms to
+    both sides (the oracle takes the resulting 0 / 1 masks)."""
+    mk = {"drop_cond_prob": p_cond, "drop_target_prob": p_target}
+    D, C, B = 4, 20, 64
+    ref, orc, params = pair(R, D, C, (64,) * 3, dm=dm, model_kwargs=mk)
+    g = torch.Generator().manual_seed(17)
+    x, c = torch.randn(B, D, generator=g), torch.randn(B, C, generator=g)
+    u_c, u_t = torch.rand(B, 1, generator=g), torch.rand(B, D, generator=g)
+    u0, eps = torch.rand((1,), generator=g), torch.randn(B, D, generator=g)
+    by_shape = {(B, 1): u_c, (B, D): u_t, (1,): u0}
+    import keras
+    monkeypatch.setattr(keras.random, "uniform", lambda shape, *a, **k: by_shape[tuple(shape)].clone())
+    monkeypatch.setattr(keras.random, "normal", lambda shape, *a, **k: eps.reshape(tuple(shape)).clone())
+    keep_c = (u_c > p_cond).float() if p_cond > 0 else None
+    keep_t = (u_t > p_target).float() if p_target > 0 else None
+    if dm:
+        ref_call = lambda: ref.compute_metrics(x, conditions=c, stage="training")["loss"]  # noqa: E731
+        orc_call = lambda: orc.compute_metrics(x, conditions=c, stage="training", fixed=(u0, eps), cond_keep=keep_c,  # noqa: E731
+                                               target_keep=keep_t)["loss"]
+    else:
+        x0, t = torch.randn(B, D, generator=g), torch.rand(B, 1, generator=g)
+        tup = (x0, x, t, t * x + (1 - t) * x0, x - x0)
+        ref_call = lambda: ref.compute_metrics(tup, conditions=c, stage="training")["loss"]  # noqa: E731
+        orc_call = lambda: orc.compute_metrics(tup, conditions=c, stage="training", cond_keep=keep_c, target_keep=keep_t)["loss"]  # noqa: E731
+    l_ref, _ = _ref_loss_and_grads(ref, ref_call)
+    l_orc, ps = _orc_loss_and_grads(orc, orc_call)
+    assert abs(l_ref - l_orc) <= 2e-6 * abs(l_ref)
+    ref_by_name = _grads_by_name(ref, params)
+    for name, p in ps.items():
+        assert rel(p.grad, ref_by_name[name]) < 2e-5, name
+
+
+@pytest.mark.parametrize("dm", [False, True])
 @pytest.mark.parametrize("method,kw", [("euler", {"steps": 6}), ("rk45", {"steps": 3}),
                                         ("tsit5", {"steps": "adaptive", "min_steps": 2, "max_steps": 12})])
 def test_log_prob_density_path(R, dm, method, kw):
