@@ -450,6 +450,13 @@ def run_ours(args, name, w):
                                          "gpu_launches", "roofline", "clocks")}
         except Exception as exc:  # the headline line must not depend on the secondary one
             wide = {"unavailable": repr(exc)[:200]}
+        try:  # the wide training net at N = 1 too, so that the scaling of cfg5_fm_train_wide has its base point
+            torch.cuda.empty_cache()
+            tww = TRAIN_WORKLOADS["cfg5_fm_train_wide"]
+            train_wide = measure_training(tww, dev, world, rank, 5, 3, False)
+            train_wide["config"] = train_config("cfg5_fm_train_wide", tww, world)
+        except Exception as exc:
+            train_wide = {"unavailable": repr(exc)[:200]}
     edge = None
     if rank == 0 and world == 1 and not args.no_train:
         try:
