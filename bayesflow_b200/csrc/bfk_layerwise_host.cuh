@@ -60,8 +60,16 @@ int launch_pairs(Kern kernel, unsigned grid, size_t smem, cudaStream_t st, const
 
 }  // namespace
 
+// the layer-wise SAMPLER takes its FiLM shift from the per-evaluation table (one vector per block); the FiLM scale of
+// film_use_gamma is only built on the fused sampler (W <= 256) and in training
+static int check_lw_cfg(const bfk_net_config* c) {
+  if (int r = check_train_cfg(c)) return r;
+  if (c->film_use_gamma) return fail(-73, "layer-wise sampler: film_use_gamma is not supported (fused sampler and training are)");
+  return 0;
+}
+
 extern "C" size_t bfk_layerwise_workspace_bytes(const bfk_net_config* c, int64_t chunk_rows, int64_t n_evals, int64_t G) {
-  if (check_train_cfg(c) || chunk_rows <= 0 || n_evals <= 0) return 0;
+  if (check_lw_cfg(c) || chunk_rows <= 0 || n_evals <= 0) return 0;
   Arena ar{nullptr, 0, 0};
   LwBufs b{};
   plan_lw(c, chunk_rows, n_evals, G > 0 ? G : 1, ar, b);
@@ -73,7 +81,7 @@ extern "C" int bfk_sample_layerwise(const bfk_net_config* c, const bfk_weights* 
                                     const float* conditions, int64_t G, int64_t rpg, const float* tmask, const float* x_in,
                                     float* x_out, int64_t B, int32_t velocity_only, int64_t chunk_rows, void* workspace,
                                     size_t workspace_bytes, void* stream_) {
-  RC(check_train_cfg(c));
+  RC(check_lw_cfg(c));
   if (!w || !sched || !times || !x_in || !x_out || !workspace || B <= 0 || n_steps <= 0 || chunk_rows <= 0)
     return fail(-90, "bfk_sample_layerwise: bad arguments");
   if (!velocity_only && !step_h) return fail(-90, "bfk_sample_layerwise: step sizes missing");

@@ -352,12 +352,13 @@ __global__ void __launch_bounds__(256) block_fwd_wide_kernel(const BlockFwdArgs 
   const long long stride = (long long)gridDim.x * GPB;
   // software pipeline: the loads of row r+stride are issued before the reductions / barriers of row r, otherwise every
   // row costs two exposed memory round trips (measured 2.3 TB/s on L2-resident panels, r01x)
-  float p[8], f[8], sk[8];
+  float p[8], f[8], sk[8], fg[8];
   uint4 raw = make_uint4(0, 0, 0, 0);
   auto fetch = [&](long long r) {
     if (on && r < a.B) {
       ld8(a.P + r * a.W + c0, p);
       ld8(a.FB + r * a.fb_stride + c0, f);
+      if (a.FG) ld8(a.FG + r * a.fb_stride + c0, fg);
       if (a.prev) ld8(a.prev + r * a.W + c0, sk);
       if (a.prev_img) raw = *reinterpret_cast<const uint4*>(a.prev_img + img_off(r, o, K8));
     }
@@ -377,7 +378,7 @@ __global__ void __launch_bounds__(256) block_fwd_wide_kernel(const BlockFwdArgs 
         float d;
         float u = t_act(a.act, p[i], d);
         if (a.drop_rate > 0.f) u *= drop_scale(dkey, a.row0 + r, c0 + i, a.drop_rate, a.inv_keep);
-        v[i] = u + f[i];
+        v[i] = a.FG ? fmaf(1.f + fg[i], u, f[i]) : u + f[i];  // (1 + gamma) * u + beta, featurewise_linear_modulation.py:25-33
       }
       if (a.prev) {
         if (a.pg) {
@@ -458,27 +459,34 @@ struct BlockBwdArgs {
   const float* gamma;
   unsigned char* dP_img; unsigned char* dV_img;
   float* d_gamma; float* d_beta; float* d_bd; float* d_bfilm;
+  // film_use_gamma: FG (B,W) = the FiLM scale to_gamma(t_emb) of this block (the forward applied 1 + FG); dG_img gets the
+  // cotangent of FG (= dV * u), d_bgfilm the gradient of to_gamma's bias
+  const float* FG; unsigned char* dG_img; float* d_bgfilm;
   long long B, R_pad;
   int W, act, norm, layer;
   float drop_rate, inv_keep; unsigned long long seed; const uint32_t* seed_dev; long long row0;
   float gscale;
 };
 
-template <int NJ>
+template <int NJ, bool FGAM = false>
 __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
   const unsigned long long dkey = a.drop_rate > 0.f ? drop_key(a.seed, a.seed_dev, a.layer) : 0ull;
-  extern __shared__ float s_red[];  // [4][W]
+  extern __shared__ float s_red[];  // [4 (+1 with FGAM)][W]
   const int lane = threadIdx.x & 31;
   const long long warp0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
   const int K8 = a.W / 8, W = a.W;
-  for (int i = threadIdx.x; i < 4 * W; i += blockDim.x) s_red[i] = 0.f;
+  for (int i = threadIdx.x; i < (FGAM ? 5 : 4) * W; i += blockDim.x) s_red[i] = 0.f;
   __syncthreads();
-  float ag[NJ][8], ab[NJ][8], ad[NJ][8], af[NJ][8];
+  float ag[NJ][8], ab[NJ][8], ad[NJ][8], af[NJ][8], aq[FGAM ? NJ : 1][8];
 #pragma unroll
   for (int j = 0; j < NJ; ++j)
 #pragma unroll
     for (int i = 0; i < 8; ++i) ag[j][i] = ab[j][i] = ad[j][i] = af[j][i] = 0.f;
+#pragma unroll
+  for (int j = 0; j < (FGAM ? NJ : 1); ++j)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) aq[j][i] = 0.f;
 
   for (long long r = warp0; r < a.R_pad; r += nwarps) {
     if (r >= a.B) {
@@ -488,6 +496,7 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
         if (o < K8) {
           *reinterpret_cast<uint4*>(a.dP_img + img_off(r, o, K8)) = make_uint4(0, 0, 0, 0);
           *reinterpret_cast<uint4*>(a.dV_img + img_off(r, o, K8)) = make_uint4(0, 0, 0, 0);
+          if (FGAM && a.dG_img) *reinterpret_cast<uint4*>(a.dG_img + img_off(r, o, K8)) = make_uint4(0, 0, 0, 0);
         }
       }
       continue;
@@ -538,13 +547,23 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
       const int o = j * 32 + lane;
       if (o < K8) {
         const int c0 = o * 8;
-        float dv[8], dp[8];
+        float dv[8], dp[8], dq[8], fg[8];
+        if (FGAM) ld8(a.FG + r * W + c0, fg);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           dv[i] = a.norm == BFK_NORM_LAYER ? rs * (g[j][i] - m1 - xh[j][i] * m2) : g[j][i];
           float d;
-          t_act(a.act, pp[j][i], d);
-          if (a.drop_rate > 0.f) d *= drop_scale(dkey, a.row0 + r, c0 + i, a.drop_rate, a.inv_keep);
+          float u = t_act(a.act, pp[j][i], d);
+          if (a.drop_rate > 0.f) {
+            const float ds = drop_scale(dkey, a.row0 + r, c0 + i, a.drop_rate, a.inv_keep);
+            d *= ds;
+            u *= ds;
+          }
+          if (FGAM) {  // v = skip + (1 + FG) u + FB:  dU = dV (1 + FG),  dFG = dV u
+            dq[i] = dv[i] * u;
+            aq[j][i] += dq[i];
+            d *= 1.f + fg[i];
+          }
           dp[i] = dv[i] * d;
           ad[j][i] += dp[i];
           af[j][i] += dv[i];
@@ -552,6 +571,7 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
         st8(a.dH + r * W + c0, dv);
         *reinterpret_cast<uint4*>(a.dP_img + img_off(r, o, K8)) = pack8(dp);
         *reinterpret_cast<uint4*>(a.dV_img + img_off(r, o, K8)) = pack8(dv);
+        if (FGAM && a.dG_img) *reinterpret_cast<uint4*>(a.dG_img + img_off(r, o, K8)) = pack8(dq);
       }
     }
   }
@@ -565,6 +585,7 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
         if (a.gamma) { atomicAdd(&s_red[c], ag[j][i]); atomicAdd(&s_red[W + c], ab[j][i]); }
         atomicAdd(&s_red[2 * W + c], ad[j][i]);
         atomicAdd(&s_red[3 * W + c], af[j][i]);
+        if (FGAM) atomicAdd(&s_red[4 * W + c], aq[j][i]);
       }
     }
   }
@@ -574,6 +595,7 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
     if (a.gamma) { atomicAdd(a.d_gamma + c, a.gscale * s_red[c]); atomicAdd(a.d_beta + c, a.gscale * s_red[W + c]); }
     atomicAdd(a.d_bd + c, a.gscale * s_red[2 * W + c]);
     atomicAdd(a.d_bfilm + c, a.gscale * s_red[3 * W + c]);
+    if (FGAM && a.d_bgfilm) atomicAdd(a.d_bgfilm + c, a.gscale * s_red[4 * W + c]);
   }
 }
 

@@ -21,6 +21,8 @@ struct TrainBufs {
   long long Rp;
   unsigned char *u_img, *te_img, *w1_pk, *a1_img, *wm_f, *wm_b, *h0_img, *wo_f, *wo_b, *dout_img, *dP_img, *dV_img, *dh0pre_img;
   float *w1, *b1, *h0pre, *m, *h0, *FB, *bo_pad, *out, *dH, *dte, *da1, *dW1, *db1;
+  float* FG;                        // film_use_gamma: FiLM scale of the current block (recomputed in the backward)
+  unsigned char *wg_f, *wg_b, *dG_img;  // film_use_gamma: to_gamma operand images (forward / dte), cotangent image of FG
   unsigned char *wd_f[BFK_MAX_BLOCKS], *wd_b[BFK_MAX_BLOCKS], *wb_f[BFK_MAX_BLOCKS], *wb_b[BFK_MAX_BLOCKS], *h_img[BFK_MAX_BLOCKS];
   float *P[BFK_MAX_BLOCKS], *xhat[BFK_MAX_BLOCKS], *rstd[BFK_MAX_BLOCKS];
 };
@@ -64,6 +66,12 @@ void plan_train(const bfk_net_config* c, long long B, bool backward, Arena& ar, 
     b.h_img[l] = (unsigned char*)ar.take(Rp * W * 2);
   }
   b.FB = (float*)ar.take(Bs * W * 4);
+  if (c->film_use_gamma) {
+    b.FG = (float*)ar.take(Bs * W * 4);
+    b.wg_f = (unsigned char*)ar.take((size_t)W * b.KT * 2);
+    b.wg_b = (unsigned char*)ar.take((size_t)r64(c->T) * W * 2);
+    if (backward) b.dG_img = (unsigned char*)ar.take(Rp * W * 2);
+  }
   b.wo_f = (unsigned char*)ar.take((size_t)b.NO * W * 2);
   b.wo_b = (unsigned char*)ar.take((size_t)W * b.NO * 2);
   b.bo_pad = (float*)ar.take((size_t)b.NO * 4);
@@ -86,7 +94,6 @@ int check_train_cfg(const bfk_net_config* c) {
   if ((c->W % 64) != 0 || c->W > 1024) return fail(-70, "layer-wise path: W must be a multiple of 64, <= 1024");
   if (c->D > 64) return fail(-71, "layer-wise path: D <= 64");
   if (c->norm == BFK_NORM_RMS) return fail(-72, "layer-wise path: norm must be 'layer' or None");
-  if (c->film_use_gamma) return fail(-73, "layer-wise path: film_use_gamma is not supported");
   if (c->precision != BFK_PREC_FP16) return fail(-74, "layer-wise path: fp16 operands only (bf16 cannot meet the 2e-3 gradient gate)");
   return 0;
 }
@@ -134,7 +141,6 @@ int launch_block_fwd(const BlockFwdArgs& a, cudaStream_t st) {
     grid[1] = resident_grid(block_fwd_wide_kernel<2>, 256, 0);
     grid[2] = resident_grid(block_fwd_wide_kernel<4>, 256, 0);
   }
-  if (a.FG) return fail(-73, "layer-wise path: film_use_gamma is not supported");
   if (nj == 1) block_fwd_kernel<1><<<grid[0], 256, 0, st>>>(a);
   else if (nj == 2) block_fwd_wide_kernel<2><<<grid[1], 256, 0, st>>>(a);
   else block_fwd_wide_kernel<4><<<grid[2], 256, 0, st>>>(a);
@@ -143,9 +149,13 @@ int launch_block_fwd(const BlockFwdArgs& a, cudaStream_t st) {
 }
 int launch_block_bwd(const BlockBwdArgs& a, cudaStream_t st) {
   const int nj = (a.W / 8 + 31) / 32;
-  const size_t sh = (size_t)4 * a.W * 4;
+  const size_t sh = (size_t)(a.FG ? 5 : 4) * a.W * 4;
   unsigned grid;
-  if (nj == 1) { grid = resident_grid(block_bwd_kernel<1>, 256, sh); block_bwd_kernel<1><<<grid, 256, sh, st>>>(a); }
+  if (a.FG) {  // film_use_gamma
+    if (nj == 1) { grid = resident_grid(block_bwd_kernel<1, true>, 256, sh); block_bwd_kernel<1, true><<<grid, 256, sh, st>>>(a); }
+    else if (nj == 2) { grid = resident_grid(block_bwd_kernel<2, true>, 256, sh); block_bwd_kernel<2, true><<<grid, 256, sh, st>>>(a); }
+    else { grid = resident_grid(block_bwd_kernel<4, true>, 256, sh); block_bwd_kernel<4, true><<<grid, 256, sh, st>>>(a); }
+  } else if (nj == 1) { grid = resident_grid(block_bwd_kernel<1>, 256, sh); block_bwd_kernel<1><<<grid, 256, sh, st>>>(a); }
   else if (nj == 2) { grid = resident_grid(block_bwd_kernel<2>, 256, sh); block_bwd_kernel<2><<<grid, 256, sh, st>>>(a); }
   else { grid = resident_grid(block_bwd_kernel<4>, 256, sh); block_bwd_kernel<4><<<grid, 256, sh, st>>>(a); }
   CK(cudaGetLastError());
@@ -211,8 +221,12 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
     RC(bfk_pack_kmajor_t(w->film_b_k[l], W, T, KT, W, NTW, P16, b.wb_f[l], st));
     RC(bfk_gemm(l == 0 ? b.h0_img : b.h_img[l - 1], b.wd_f[l], b.P[l], W, B, W, W, NTW, 1, 0, w->dense_b[l], 1.f, P16, st));
     RC(bfk_gemm(b.te_img, b.wb_f[l], b.FB, W, B, W, KT, NTW, 1, 0, w->film_b_b[l], 1.f, P16, st));
+    if (c->film_use_gamma) {  // FiLM scale to_gamma(t_emb): one more K = T GEMM per block
+      RC(bfk_pack_kmajor_t(w->film_g_k[l], W, T, KT, W, NTW, P16, b.wg_f, st));
+      RC(bfk_gemm(b.te_img, b.wg_f, b.FG, W, B, W, KT, NTW, 1, 0, w->film_g_b[l], 1.f, P16, st));
+    }
     BlockFwdArgs a{};
-    a.P = b.P[l]; a.FB = b.FB; a.FG = nullptr; a.fb_stride = W;
+    a.P = b.P[l]; a.FB = b.FB; a.FG = c->film_use_gamma ? b.FG : nullptr; a.fb_stride = W;
     a.prev = c->residual ? (l == 0 ? b.h0 : b.xhat[l - 1]) : nullptr;
     a.pg = (l > 0 && c->norm == BFK_NORM_LAYER) ? w->norm_g[l - 1] : nullptr;
     a.pb = (l > 0 && c->norm == BFK_NORM_LAYER) ? w->norm_b[l - 1] : nullptr;
@@ -250,12 +264,22 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
     a.d_gamma = GP(g->norm_g[l]); a.d_beta = GP(g->norm_b[l]); a.d_bd = GP(g->dense_b[l]); a.d_bfilm = GP(g->film_b_b[l]);
     a.B = B; a.R_pad = Rp; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
     a.drop_rate = ta->dropout; a.inv_keep = inv_keep; a.seed = ta->seed; a.seed_dev = ta->seed_dev; a.row0 = ta->row_offset; a.gscale = gs;
+    if (c->film_use_gamma) {  // the forward kept only the last block's FiLM scale: rebuild this block's
+      RC(bfk_pack_kmajor_t(w->film_g_k[l], W, T, KT, W, NTW, P16, b.wg_f, st));
+      RC(bfk_gemm(b.te_img, b.wg_f, b.FG, W, B, W, KT, NTW, 1, 0, w->film_g_b[l], 1.f, P16, st));
+      a.FG = b.FG; a.dG_img = b.dG_img; a.d_bgfilm = GP(g->film_g_b[l]);
+    }
     RC(launch_block_bwd(a, st));
     RC(launch_gemm_dw(l == 0 ? b.h0_img : b.h_img[l - 1], W / 8, b.dP_img, W / 8, GP(g->dense_k[l]), W, W, W, Rp, gs, sw, st));
     RC(launch_gemm_dw(b.te_img, KT / 8, b.dV_img, W / 8, GP(g->film_b_k[l]), W, T, W, Rp, gs, sw, st));
+    if (c->film_use_gamma) RC(launch_gemm_dw(b.te_img, KT / 8, b.dG_img, W / 8, GP(g->film_g_k[l]), W, T, W, Rp, gs, sw, st));
     if (want_dte) {
       RC(bfk_pack_kmajor(w->film_b_k[l], W, T, W, W, 64, P16, b.wb_b[l], st));
       RC(bfk_gemm(b.dV_img, b.wb_b[l], b.dte, KTN, B, KTN, W, 64, 1, l == L - 1 ? 0 : GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
+      if (c->film_use_gamma) {
+        RC(bfk_pack_kmajor(w->film_g_k[l], W, T, W, W, 64, P16, b.wg_b, st));
+        RC(bfk_gemm(b.dG_img, b.wg_b, b.dte, KTN, B, KTN, W, 64, 1, GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
+      }
     }
     if (!c->residual) CK(cudaMemsetAsync(b.dH, 0, (size_t)B * W * 4, st));
     RC(bfk_pack_kmajor(w->dense_k[l], W, W, W, W, NTW, P16, b.wd_b[l], st));
@@ -316,6 +340,11 @@ extern "C" int bfk_train_vjp(const bfk_net_config* c, const bfk_weights* w, cons
     a.d_gamma = a.d_beta = a.d_bd = a.d_bfilm = nullptr;
     a.B = B; a.R_pad = Rp; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
     a.drop_rate = 0.f; a.inv_keep = 1.f; a.seed = 0; a.seed_dev = nullptr; a.row0 = 0; a.gscale = 1.f;
+    if (c->film_use_gamma) {  // dU = dV (1 + FG): rebuild this block's FiLM scale (time does not depend on x: no dG needed)
+      RC(bfk_pack_kmajor_t(w->film_g_k[l], W, c->T, b.KT, W, NTW, P16, b.wg_f, st));
+      RC(bfk_gemm(b.te_img, b.wg_f, b.FG, W, B, W, b.KT, NTW, 1, 0, w->film_g_b[l], 1.f, P16, st));
+      a.FG = b.FG; a.dG_img = nullptr; a.d_bgfilm = nullptr;
+    }
     RC(launch_block_bwd(a, st));
     if (!c->residual) CK(cudaMemsetAsync(b.dH, 0, (size_t)B * W * 4, st));
     RC(bfk_pack_kmajor(w->dense_k[l], W, W, W, W, NTW, P16, b.wd_b[l], st));

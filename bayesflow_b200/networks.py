@@ -243,7 +243,9 @@ class _Engine:
             # W > 256 or D > 8: the layer-wise tcgen05 path (bfk_sample_layerwise) reads the fp32 weights directly
             from .training import _bind, fill_weights
             _bind(L)
-            if L.bfk_train_workspace_bytes(C.byref(cfg), 128, 0) == 0:
+            L.bfk_layerwise_workspace_bytes.restype = C.c_size_t
+            L.bfk_layerwise_workspace_bytes.argtypes = [C.POINTER(_lib.NetConfig), C.c_int64, C.c_int64, C.c_int64]
+            if L.bfk_layerwise_workspace_bytes(C.byref(cfg), 128, 1, 1) == 0:
                 raise NotImplementedError(f"config D={cfg.D} W={cfg.W} L={cfg.L}: neither the fused sampler (D<=8, W<=256, "
                                           f"W%32==0) nor the layer-wise path covers it: " + L.bfk_last_error_string().decode())
             self.w, self._keep_w = fill_weights(net, lambda p: p.detach())

@@ -73,6 +73,8 @@ def fill_weights(net, get):
     for i, b in enumerate(sub.blocks):
         w.dense_k[i], w.dense_b[i] = P(b.dense.kernel), P(b.dense.bias)
         w.film_b_k[i], w.film_b_b[i] = P(b.film.to_beta.kernel), P(b.film.to_beta.bias)
+        if sub.film_use_gamma:
+            w.film_g_k[i], w.film_g_b[i] = P(b.film.to_gamma.kernel), P(b.film.to_gamma.bias)
         if sub.norm == "layer":
             w.norm_g[i], w.norm_b[i] = P(b.norm.gamma), P(b.norm.beta)
     w.out_k, w.out_b = P(net.output_projector.kernel), P(net.output_projector.bias)

@@ -56,6 +56,9 @@ def cuda_tuple(tup):
     (2, 6, (128,) * 2, 300, {"time_embedding_dim": 8}),
     (2, 6, (128,) * 2, 300, {"time_embedding_dim": 1}),
     (2, 6, (128,) * 2, 300, {"activation": "relu"}),
+    (2, 6, (128,) * 3, 300, {"film_use_gamma": True}),                       # FiLM scale: (1 + gamma(t)) * h + beta(t)
+    (4, 5, (512,) * 2, 260, {"film_use_gamma": True, "activation": "silu"}),  # ... on the wide block kernels
+    (3, None, (1024,) * 2, 200, {"film_use_gamma": True, "time_embedding_dim": 1}),
     (64, 32, (1024,) * 2, 512, {}),          # cfg4 block shape
     (5, 3, (512,) * 2, 384, {}),
 ])
