@@ -65,6 +65,7 @@ int launch_pairs(Kern kernel, unsigned grid, size_t smem, cudaStream_t st, const
 static int check_lw_cfg(const bfk_net_config* c) {
   if (int r = check_train_cfg(c)) return r;
   if (c->film_use_gamma) return fail(-73, "layer-wise sampler: film_use_gamma is not supported (fused sampler and training are)");
+  if (c->norm == BFK_NORM_RMS) return fail(-72, "layer-wise sampler: norm must be 'layer' or None (fused sampler and training have 'rms')");
   return 0;
 }
 

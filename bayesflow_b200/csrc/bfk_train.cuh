@@ -17,6 +17,7 @@
 namespace bfk {
 
 constexpr float LN_EPS = 1e-3f;  // keras.layers.LayerNormalization default epsilon
+constexpr float RMS_EPS = 1e-6f; // keras.layers.RMSNormalization (ops.rms_normalization): x * rsqrt(mean(x^2) + eps) * scale
 
 // value and derivative of the Keras activation (time_mlp.py:106-109), fp32
 __device__ __forceinline__ float t_act(int act, float x, float& d) {
@@ -275,7 +276,11 @@ __global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
           if (a.pg) {
             float g[8], b[8];
             ld8(a.pg + c0, g);
-            ld8(a.pb + c0, b);
+            if (a.pb) ld8(a.pb + c0, b);
+            else {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) b[i] = 0.f;
+            }
 #pragma unroll
             for (int i = 0; i < 8; ++i) s[i] = fmaf(s[i], g[i], b[i]);
           }
@@ -299,8 +304,8 @@ __global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
       }
     }
     float mean = 0.f, rs = 1.f;
-    if (a.norm == BFK_NORM_LAYER) {
-      mean = warp_sum(sum) / (float)a.W;
+    if (a.norm != BFK_NORM_NONE) {  // layer: centred; rms: mean stays 0
+      if (a.norm == BFK_NORM_LAYER) mean = warp_sum(sum) / (float)a.W;
       float sq = 0.f;
 #pragma unroll
       for (int j = 0; j < NJ; ++j)
@@ -308,7 +313,7 @@ __global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
 #pragma unroll
           for (int i = 0; i < 8; ++i) { const float d = v[j][i] - mean; sq = fmaf(d, d, sq); }
         }
-      rs = rsqrtf(warp_sum(sq) / (float)a.W + LN_EPS);
+      rs = rsqrtf(warp_sum(sq) / (float)a.W + (a.norm == BFK_NORM_LAYER ? LN_EPS : RMS_EPS));
     }
     if (a.rstd && lane == 0) a.rstd[r] = rs;
 #pragma unroll
@@ -323,7 +328,11 @@ __global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
         if (a.gamma) {
           float g[8], b[8];
           ld8(a.gamma + c0, g);
-          ld8(a.beta + c0, b);
+          if (a.beta) ld8(a.beta + c0, b);
+          else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) b[i] = 0.f;  // rms: scale only
+          }
 #pragma unroll
           for (int i = 0; i < 8; ++i) h[i] = fmaf(xh[i], g[i], b[i]);
         } else {
@@ -384,7 +393,11 @@ __global__ void __launch_bounds__(256) block_fwd_wide_kernel(const BlockFwdArgs 
         if (a.pg) {
           float g[8], b[8];
           ld8(a.pg + c0, g);
-          ld8(a.pb + c0, b);
+          if (a.pb) ld8(a.pb + c0, b);
+          else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) b[i] = 0.f;
+          }
 #pragma unroll
           for (int i = 0; i < 8; ++i) sk[i] = fmaf(sk[i], g[i], b[i]);
         }
@@ -407,14 +420,14 @@ __global__ void __launch_bounds__(256) block_fwd_wide_kernel(const BlockFwdArgs 
     }
     fetch(r + stride);  // in place (img == prev_img) is safe: another row
     float mean = 0.f, rs = 1.f;
-    if (a.norm == BFK_NORM_LAYER) {
+    if (a.norm != BFK_NORM_NONE) {  // layer: centred; rms: mean stays 0 (the first exchange is kept: it also orders s_sq)
       sum = warp_sum(sum);
       if (lane == 0) s_sum[warp] = sum;
       named_bar_sync(1 + grp, WPR * 32);
       float ts = 0.f;
 #pragma unroll
       for (int w = 0; w < WPR; ++w) ts += s_sum[grp * WPR + w];
-      mean = ts / (float)a.W;
+      mean = a.norm == BFK_NORM_LAYER ? ts / (float)a.W : 0.f;
       float sq = 0.f;
       if (on) {
 #pragma unroll
@@ -426,7 +439,7 @@ __global__ void __launch_bounds__(256) block_fwd_wide_kernel(const BlockFwdArgs 
       float tq = 0.f;
 #pragma unroll
       for (int w = 0; w < WPR; ++w) tq += s_sq[grp * WPR + w];
-      rs = rsqrtf(tq / (float)a.W + LN_EPS);
+      rs = rsqrtf(tq / (float)a.W + (a.norm == BFK_NORM_LAYER ? LN_EPS : RMS_EPS));
     }
     if (a.rstd && wig == 0 && lane == 0) a.rstd[r] = rs;
     if (on) {
@@ -437,7 +450,11 @@ __global__ void __launch_bounds__(256) block_fwd_wide_kernel(const BlockFwdArgs 
       if (a.gamma) {
         float g[8], b[8];
         ld8(a.gamma + c0, g);
-        ld8(a.beta + c0, b);
+        if (a.beta) ld8(a.beta + c0, b);
+        else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) b[i] = 0.f;  // rms: scale only
+        }
 #pragma unroll
         for (int i = 0; i < 8; ++i) h[i] = fmaf(xh[i], g[i], b[i]);
       } else {
@@ -537,8 +554,8 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
       }
     }
     float m1 = 0.f, m2 = 0.f, rs = 1.f;
-    if (a.norm == BFK_NORM_LAYER) {
-      m1 = warp_sum(s1) / (float)W;
+    if (a.norm != BFK_NORM_NONE) {  // rms: no centring, so the m1 term is absent
+      if (a.norm == BFK_NORM_LAYER) m1 = warp_sum(s1) / (float)W;
       m2 = warp_sum(s2) / (float)W;
       rs = a.rstd[r];
     }
@@ -551,7 +568,7 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
         if (FGAM) ld8(a.FG + r * W + c0, fg);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          dv[i] = a.norm == BFK_NORM_LAYER ? rs * (g[j][i] - m1 - xh[j][i] * m2) : g[j][i];
+          dv[i] = a.norm != BFK_NORM_NONE ? rs * (g[j][i] - m1 - xh[j][i] * m2) : g[j][i];
           float d;
           float u = t_act(a.act, pp[j][i], d);
           if (a.drop_rate > 0.f) {
@@ -592,7 +609,10 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
   __syncthreads();
   if (!a.d_bd) return;  // cotangent-only pass (bfk_train_vjp): no parameter gradients
   for (int c = threadIdx.x; c < W; c += blockDim.x) {
-    if (a.gamma) { atomicAdd(a.d_gamma + c, a.gscale * s_red[c]); atomicAdd(a.d_beta + c, a.gscale * s_red[W + c]); }
+    if (a.gamma) {
+      atomicAdd(a.d_gamma + c, a.gscale * s_red[c]);
+      if (a.d_beta) atomicAdd(a.d_beta + c, a.gscale * s_red[W + c]);
+    }
     atomicAdd(a.d_bd + c, a.gscale * s_red[2 * W + c]);
     atomicAdd(a.d_bfilm + c, a.gscale * s_red[3 * W + c]);
     if (FGAM && a.d_bgfilm) atomicAdd(a.d_bgfilm + c, a.gscale * s_red[4 * W + c]);

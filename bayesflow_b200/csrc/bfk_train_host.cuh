@@ -93,7 +93,6 @@ int check_train_cfg(const bfk_net_config* c) {
   if (int r = check_cfg(c)) return r;
   if ((c->W % 64) != 0 || c->W > 1024) return fail(-70, "layer-wise path: W must be a multiple of 64, <= 1024");
   if (c->D > 64) return fail(-71, "layer-wise path: D <= 64");
-  if (c->norm == BFK_NORM_RMS) return fail(-72, "layer-wise path: norm must be 'layer' or None");
   if (c->precision != BFK_PREC_FP16) return fail(-74, "layer-wise path: fp16 operands only (bf16 cannot meet the 2e-3 gradient gate)");
   return 0;
 }
@@ -228,9 +227,9 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
     BlockFwdArgs a{};
     a.P = b.P[l]; a.FB = b.FB; a.FG = c->film_use_gamma ? b.FG : nullptr; a.fb_stride = W;
     a.prev = c->residual ? (l == 0 ? b.h0 : b.xhat[l - 1]) : nullptr;
-    a.pg = (l > 0 && c->norm == BFK_NORM_LAYER) ? w->norm_g[l - 1] : nullptr;
+    a.pg = (l > 0 && c->norm != BFK_NORM_NONE) ? w->norm_g[l - 1] : nullptr;  // rms: scale only (pb stays null)
     a.pb = (l > 0 && c->norm == BFK_NORM_LAYER) ? w->norm_b[l - 1] : nullptr;
-    a.gamma = c->norm == BFK_NORM_LAYER ? w->norm_g[l] : nullptr;
+    a.gamma = c->norm != BFK_NORM_NONE ? w->norm_g[l] : nullptr;
     a.beta = c->norm == BFK_NORM_LAYER ? w->norm_b[l] : nullptr;
     a.xhat = b.xhat[l]; a.rstd = b.rstd[l]; a.img = b.h_img[l]; a.out_f32 = nullptr;
     a.B = B; a.R_pad = Rp; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
@@ -259,9 +258,10 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   for (int l = L - 1; l >= 0; --l) {
     BlockBwdArgs a{};
     a.dH = b.dH; a.xhat = b.xhat[l]; a.rstd = b.rstd[l]; a.P = b.P[l];
-    a.gamma = c->norm == BFK_NORM_LAYER ? w->norm_g[l] : nullptr;
+    a.gamma = c->norm != BFK_NORM_NONE ? w->norm_g[l] : nullptr;
     a.dP_img = b.dP_img; a.dV_img = b.dV_img;
-    a.d_gamma = GP(g->norm_g[l]); a.d_beta = GP(g->norm_b[l]); a.d_bd = GP(g->dense_b[l]); a.d_bfilm = GP(g->film_b_b[l]);
+    a.d_gamma = GP(g->norm_g[l]); a.d_beta = c->norm == BFK_NORM_LAYER ? GP(g->norm_b[l]) : nullptr;
+    a.d_bd = GP(g->dense_b[l]); a.d_bfilm = GP(g->film_b_b[l]);
     a.B = B; a.R_pad = Rp; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
     a.drop_rate = ta->dropout; a.inv_keep = inv_keep; a.seed = ta->seed; a.seed_dev = ta->seed_dev; a.row0 = ta->row_offset; a.gscale = gs;
     if (c->film_use_gamma) {  // the forward kept only the last block's FiLM scale: rebuild this block's
@@ -335,7 +335,7 @@ extern "C" int bfk_train_vjp(const bfk_net_config* c, const bfk_weights* w, cons
   for (int l = L - 1; l >= 0; --l) {
     BlockBwdArgs a{};
     a.dH = b.dH; a.xhat = b.xhat[l]; a.rstd = b.rstd[l]; a.P = b.P[l];
-    a.gamma = c->norm == BFK_NORM_LAYER ? w->norm_g[l] : nullptr;
+    a.gamma = c->norm != BFK_NORM_NONE ? w->norm_g[l] : nullptr;
     a.dP_img = b.dP_img; a.dV_img = b.dV_img;
     a.d_gamma = a.d_beta = a.d_bd = a.d_bfilm = nullptr;
     a.B = B; a.R_pad = Rp; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;

@@ -77,6 +77,8 @@ def fill_weights(net, get):
             w.film_g_k[i], w.film_g_b[i] = P(b.film.to_gamma.kernel), P(b.film.to_gamma.bias)
         if sub.norm == "layer":
             w.norm_g[i], w.norm_b[i] = P(b.norm.gamma), P(b.norm.beta)
+        elif sub.norm == "rms":
+            w.norm_g[i] = P(b.norm.scale)
     w.out_k, w.out_b = P(net.output_projector.kernel), P(net.output_projector.bias)
     return w, keep
 

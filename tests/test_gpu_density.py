@@ -30,6 +30,7 @@ def _data(B, D, C, seed=11):
     (5, 6, (64,) * 2, 77, {"activation": "silu", "norm": None}),
     (16, 8, (512,) * 2, 64, {}),             # wide block, D > 8
     (3, 6, (128,) * 2, 90, {"film_use_gamma": True}),   # the reverse pass scales dU by (1 + gamma(t))
+    (3, 6, (128,) * 2, 90, {"norm": "rms"}),
 ])
 def test_velocity_and_exact_trace(D, C, widths, B, sk):
     net, orc = make_pair(D, C, widths, **sk)

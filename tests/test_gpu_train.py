@@ -56,6 +56,8 @@ def cuda_tuple(tup):
     (2, 6, (128,) * 2, 300, {"time_embedding_dim": 8}),
     (2, 6, (128,) * 2, 300, {"time_embedding_dim": 1}),
     (2, 6, (128,) * 2, 300, {"activation": "relu"}),
+    (2, 6, (128,) * 3, 300, {"norm": "rms"}),                                # RMSNormalization: scale only, eps 1e-6
+    (4, 5, (512,) * 2, 260, {"norm": "rms", "activation": "relu"}),
     (2, 6, (128,) * 3, 300, {"film_use_gamma": True}),                       # FiLM scale: (1 + gamma(t)) * h + beta(t)
     (4, 5, (512,) * 2, 260, {"film_use_gamma": True, "activation": "silu"}),  # ... on the wide block kernels
     (3, None, (1024,) * 2, 200, {"film_use_gamma": True, "time_embedding_dim": 1}),
@@ -287,4 +289,5 @@ def test_dropout_masks_are_bernoulli_and_keyed_by_the_global_row():
     a = float(net.compute_metrics(x, conditions=c, stage="training", noise_seed=3, seed=1)["loss"])
     b = float(net.compute_metrics(x, conditions=c, stage="training", noise_seed=3, seed=1)["loss"])
     d = float(net.compute_metrics(x, conditions=c, stage="training", noise_seed=4, seed=1)["loss"])
-    assert a == b and a != d and math.isfinite(a)
+    # (the loss reduction uses float atomics: equal seeds agree to round-off, not bit for bit)
+    assert abs(a - b) <= 1e-6 * abs(a) and abs(a - d) > 1e-4 * abs(a) and math.isfinite(a)
