@@ -49,7 +49,13 @@ struct LwFusedArgs {
 enum { LWF_BLOCK = 0, LWF_ACT = 1, LWF_OUT = 2 };
 
 constexpr int F_VEC = 5;  // g, c, film, gamma_prev, beta_prev
-constexpr int LWF_EPI_WARPS = 16, LWF_THREADS = (LWF_EPI_WARPS + 2) * 32;  // + UMMA issuer warp + producer warp
+// BFK_LW_EPI_REGS (setmaxnreg, as in bfk_sampler_fold.cuh): 20 warps are launched, the four epilogue warpgroups raise their
+// register share, the issuer / producer warpgroup (with two idle warps) drops to the rest of the 20 x 96 pool.  0 = 18 warps.
+#ifndef BFK_LW_EPI_REGS
+#define BFK_LW_EPI_REGS 112
+#endif
+constexpr int LWF_EPI_WARPS = 16, LWF_THREADS = BFK_LW_EPI_REGS ? 640 : (LWF_EPI_WARPS + 2) * 32;  // + UMMA issuer + producer
+constexpr int LWF_AUX_REGS = BFK_LW_EPI_REGS ? (20 * 96 - 16 * BFK_LW_EPI_REGS) / 4 : 0;
 __host__ __device__ inline size_t lw_fused_smem_bytes(int NT) {
   return (size_t)P_STAGES * (P_KC * G_TM * 2 + P_KC * NT * 2) + (size_t)2 * F_VEC * NT * 4 + 256;
 }
@@ -186,6 +192,9 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
   const uint32_t tmem_base = *s_tmem;
 
   if (warp == LWF_EPI_WARPS + 1) {
+#if BFK_LW_EPI_REGS
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(LWF_AUX_REGS));
+#endif
     if (lane == 0) {
       uint32_t g = 0;
       for (long long t = w_first; t < total; t += w_step) {
@@ -209,6 +218,9 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
     }
     __syncwarp();
   } else if (warp == LWF_EPI_WARPS) {
+#if BFK_LW_EPI_REGS
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(LWF_AUX_REGS));
+#endif
     if (lane == 0) {
       uint32_t g = 0, j = 0;
       for (long long t = w_first; t < total; t += w_step, ++j) {
@@ -234,7 +246,14 @@ __global__ void __launch_bounds__(LWF_THREADS, 1) lw_block_gemm_kernel(const LwF
       }
     }
     __syncwarp();
+  } else if (warp > LWF_EPI_WARPS + 1) {
+#if BFK_LW_EPI_REGS
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(LWF_AUX_REGS));  // the two idle warps of the fifth warpgroup
+#endif
   } else {
+#if BFK_LW_EPI_REGS
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(BFK_LW_EPI_REGS));
+#endif
     // ---- epilogue warps 0-15: TMEM lane quarter = warp % 4, 64-column panel = warp / 4; 16-column chunks, the TMEM and
     // skip loads of chunk i+1 in flight under the arithmetic of chunk i ------------------------------------------------
     const int q = warp & 3, pq = warp >> 2;
