@@ -7,7 +7,7 @@ from .networks import (  # noqa: F401
 from .integrate import integrate  # noqa: F401
 from .standardization import Standardize, Standardization  # noqa: F401
 from .samplers import Sampler  # noqa: F401
-from .consistency import ConsistencyModel  # noqa: F401
+from .consistency import ConsistencyModel, StableConsistencyModel  # noqa: F401
 from .optimal_transport import optimal_transport, log_sinkhorn, log_sinkhorn_plan  # noqa: F401
 from .parallel import dataset_shard, sample_sharded, log_prob_sharded, gather_rows  # noqa: F401
 

@@ -189,3 +189,110 @@ class ConsistencyModel(InferenceNetwork):
                            pred_scale=out2.reshape(-1).contiguous(), row_weight=lam.contiguous(), loss="pseudo_huber",
                            huber_c=self.c_huber, dropout=rate, seed=dseed, global_batch=B * world, backward=backward)
         return loss
+
+
+class StableConsistencyModel(InferenceNetwork):
+    """stable_consistency_model.py:27-314 — the SAMPLING side on the CUDA velocity kernels: consistency function
+    `cos(t) x - sin(t) sigma F(x / sigma, t, c)` (:238-260), time discretisation (:111-122), multistep sampling (:163-236;
+    per-step noise from `bfk_normal_fill`, Philox keyed by (seed, step, GLOBAL row)).  The continuous-time consistency
+    TRAINING (:262-314) needs a forward-mode derivative of the subnet along (x, t) and is not built: `compute_metrics`
+    raises NotImplementedError (weights trained with the reference load through `load_state_dict`)."""
+
+    _wants_noise_offset = True
+    EPS_WARN = 0.1
+
+    def __init__(self, subnet="time_mlp", sigma: float = 1.0, subnet_kwargs=None, weight_mlp_kwargs=None,
+                 drop_cond_prob: float = 0.0, **kwargs):
+        self.p_mean = float(kwargs.pop("p_mean", -1.0))
+        self.p_std = float(kwargs.pop("p_std", 1.6))
+        self.c = float(kwargs.pop("c", 0.1))
+        self.drop_target_prob = float(kwargs.pop("drop_target_prob", 0.0))
+        super().__init__("normal", **kwargs)
+        subnet_kwargs = subnet_kwargs or {}
+        if subnet == "time_mlp":
+            subnet_kwargs = TIME_MLP_DEFAULTS | subnet_kwargs
+        self.subnet = find_network(subnet, **subnet_kwargs)
+        self.output_projector = None  # the reference's `subnet_projector` (its variable is named "output_projector", :134-138)
+        self.weight_mlp_kwargs = dict(weight_mlp_kwargs or {})  # the adaptive-weight MLP only exists in training
+        self.sigma = float(sigma)
+        self.drop_cond_prob = drop_cond_prob
+        self.unconditional_mode = False
+
+    def _schedule_struct(self):
+        s = _lib.Schedule()
+        s.model = 0  # the kernels return the raw projected subnet output F
+        return s
+
+    def get_config(self):
+        return {"subnet": self.subnet.get_config(), "sigma": self.sigma, "p_mean": self.p_mean, "p_std": self.p_std,
+                "c": self.c, "drop_cond_prob": self.drop_cond_prob, "drop_target_prob": self.drop_target_prob}
+
+    @staticmethod
+    def _discretize_time(num_steps: int, rho: float = 3.5) -> torch.Tensor:
+        # :111-122, fp32 like keras.ops; times[1] is read before the loop (steps = 1 fails in the reference too)
+        if int(num_steps) < 2:
+            raise IndexError("StableConsistencyModel needs steps >= 2 (stable_consistency_model.py:126 reads times[1])")
+        t = torch.linspace(0.0, math.pi / 2, int(num_steps), dtype=torch.float32)
+        times = torch.exp((t - math.pi / 2) * rho) * math.pi / 2
+        return torch.cat([torch.zeros(1), times[1:]])
+
+    def build(self, xz_shape, conditions_shape=None):
+        if self.built:
+            return
+        self._build_common(xz_shape, conditions_shape)
+        self.built = True
+
+    def consistency_function(self, x, t, conditions=None, training=False, **kwargs):
+        """cos(t) x - sin(t) sigma F(x / sigma, t, c); t shared by all rows (a float or a constant tensor)."""
+        if training:
+            raise NotImplementedError("StableConsistencyModel training (a JVP through the subnet) is not built")
+        if torch.is_tensor(t):
+            if t.numel() != 1 and not bool((t == t.reshape(-1)[0]).all()):
+                raise NotImplementedError("per-row time only occurs in training, which is not built")
+            t = float(t.reshape(-1)[0])
+        run = self._run(conditions, x.shape[0], {k: v for k, v in kwargs.items() if k == "conditions_repeats"})
+        return self._cf(run, run._check_x(x), float(np.float32(t)))
+
+    def _cf(self, run, x, t: float):
+        xs = x if self.sigma == 1.0 else _lincomb(torch.empty_like(x), 1.0 / self.sigma, x)
+        f = run.velocity(xs, float(np.float32(t)))
+        ct, st = float(np.cos(np.float32(t))), float(np.sin(np.float32(t)))
+        return _lincomb(f, ct, x, -st * self.sigma, f)
+
+    def _forward(self, x, conditions=None, **kwargs):
+        raise NotImplementedError("Consistency Models are not invertible")
+
+    def _inverse(self, z, conditions=None, density=False, training=False, **kwargs):
+        if density:
+            raise NotImplementedError("Consistency Models are not invertible")
+        seed = kwargs.pop("seed", None)
+        if seed is None:
+            seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        row_offset = int(kwargs.pop("noise_row_offset", 0))
+        noise_fn = kwargs.pop("noise_fn", None)
+        steps, rho = int(kwargs.get("steps", 15)), float(kwargs.get("rho", 3.5))
+        run = self._run(conditions, z.shape[0], {k: v for k, v in kwargs.items() if k == "conditions_repeats"})
+        z = run._check_x(z)
+        times = torch.flip(self._discretize_time(steps, rho), dims=(-1,)).tolist()
+        x = _lincomb(torch.empty_like(z), self.sigma, z)
+        x = self._apply_targets(x, kwargs)
+        x = self._apply_targets(self._cf(run, x, times[0]), kwargs)
+        B, D = x.shape
+        t = times[0]
+        for n in range(1, steps):
+            if noise_fn is not None:
+                noise = noise_fn(n, (B, D)).to(device=x.device, dtype=torch.float32).contiguous()
+            else:
+                noise = torch.empty_like(x)
+                _lib.check(_lib.lib().bfk_normal_fill(_lib.ptr(noise), B, D, row_offset, None, None,
+                                                      _lib.C.c_uint64((int(seed) + n * _GOLDEN) & (2 ** 64 - 1)), None,
+                                                      _lib.stream_ptr()), "bfk_normal_fill")
+            ct, st = float(np.cos(np.float32(t))), float(np.sin(np.float32(t)))
+            x_n = self._apply_targets(_lincomb(torch.empty_like(x), ct, x, st, noise), kwargs)
+            t = times[n]
+            x = self._apply_targets(self._cf(run, x_n, t), kwargs)
+        return x
+
+    def _loss_and_grads(self, *args, **kwargs):
+        raise NotImplementedError("StableConsistencyModel training (continuous-time consistency training, "
+                                  "stable_consistency_model.py:262-314: a JVP through the subnet) is not built on the CUDA path")

@@ -21,4 +21,4 @@ from .networks import (  # noqa: F401
 from .edge import (  # noqa: F401
     OracleStandardize, philox4x32_10, philox_words, normal_stream, repeat_and_flatten_conditions, unflatten_samples,
 )
-from .consistency import OracleConsistencyModel  # noqa: F401
+from .consistency import OracleConsistencyModel, OracleStableConsistencyModel  # noqa: F401

@@ -96,3 +96,51 @@ class OracleConsistencyModel:
         if sample_weight is not None:
             loss = loss * sample_weight.reshape(-1, 1).to(x.dtype)
         return {"loss": loss.mean()}
+
+
+class OracleStableConsistencyModel:
+    """stable_consistency_model.py:27-314 — the sampling side (consistency function :238-260, multistep sampling :163-236,
+    time discretisation :111-122).  Pinned on the reference's own class (tests/test_reference_pin.py).  The
+    continuous-time consistency TRAINING (:262-314) differentiates the subnet in forward mode (a JVP along (x, t)); it is
+    not restated and not built on the CUDA path."""
+
+    def __init__(self, params, D, subnet_kwargs=None, sigma=1.0):
+        kw = dict(TIME_MLP_DEFAULTS) | (subnet_kwargs or {})  # :81-84
+        self.p, self.D, self.sigma = params, D, float(sigma)
+        self.subnet = OracleTimeMLP(params, **kw)
+
+    @staticmethod
+    def discretize_time(num_steps, rho=3.5):
+        # :111-122 (fp32 like keras.ops)
+        t = torch.linspace(0.0, math.pi / 2, num_steps, dtype=torch.float32)
+        times = torch.exp((t - math.pi / 2) * rho) * math.pi / 2
+        return torch.cat([torch.zeros(1), times[1:]])
+
+    def consistency_function(self, x, t, conditions=None):
+        # :238-260
+        t = torch.as_tensor(t, dtype=x.dtype)
+        if t.ndim == 0:
+            t = t.expand(x.shape[0], 1)
+        subnet_out = self.subnet((x / self.sigma, t, conditions), training=False)
+        f = subnet_out @ self.p["output_projector.kernel"].to(x.dtype) + self.p["output_projector.bias"].to(x.dtype)
+        return torch.cos(t) * x - torch.sin(t) * self.sigma * f
+
+    def inverse(self, z, conditions=None, steps=15, rho=3.5, noise_fn=None, target_mask=None, targets_fixed=None):
+        """:163-236.  noise_fn(n, shape) supplies the step-n noise."""
+        x = z.clone() * self.sigma
+        dt = torch.flip(self.discretize_time(steps, rho), dims=(-1,))
+        t = torch.full(x.shape[:-1] + (1,), float(dt[0]), dtype=x.dtype)
+        if target_mask is not None:
+            target_mask = torch.broadcast_to(target_mask, x.shape)
+            targets_fixed = torch.broadcast_to(targets_fixed, x.shape)
+            x = _mask(x, target_mask, targets_fixed)
+        x = self.consistency_function(x, t, conditions)
+        x = _mask(x, target_mask, targets_fixed) if target_mask is not None else x
+        for n in range(1, steps):
+            noise = noise_fn(n, x.shape) if noise_fn is not None else torch.randn(x.shape)
+            x_n = torch.cos(t) * x + torch.sin(t) * noise.to(x.dtype)
+            t = torch.full_like(t, float(dt[n]))
+            x_n = _mask(x_n, target_mask, targets_fixed) if target_mask is not None else x_n
+            x = self.consistency_function(x_n, t, conditions)
+            x = _mask(x, target_mask, targets_fixed) if target_mask is not None else x
+        return x

@@ -219,6 +219,9 @@ for _name, _fn in {
     "tile": lambda x, reps: torch.tile(_t(x), tuple(reps)),
     "repeat": lambda x, repeats, axis=None: torch.repeat_interleave(_t(x), repeats, dim=axis),
     "flip": lambda x, axis=None: torch.flip(_t(x), dims=[axis] if isinstance(axis, int) else list(axis)),
+    "linspace": lambda start, stop, num=50, dtype=None: torch.linspace(float(start), float(stop), int(num),
+                                                                        dtype=_to_dtype(dtype) or torch.float32),
+    "full_like": lambda x, v, dtype=None: torch.full_like(_t(x), float(v), dtype=_to_dtype(dtype)),
     "take": lambda x, idx, axis=None: torch.take(_t(x), _t(idx).long()) if axis is None else
     torch.index_select(_t(x), axis, _t(idx).long().reshape(-1)),
     "take_along_axis": lambda x, idx, axis=None: torch.take_along_dim(_t(x), _t(idx).long(), dim=axis),

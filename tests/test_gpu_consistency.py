@@ -118,3 +118,57 @@ def test_training_loss_and_all_gradients(D, C, widths, B):
             assert rel_l2(p.grad, ref[name]) < 2e-2, (name, rel_l2(p.grad, ref[name]))
             checked += 1
     assert checked >= 10
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# StableConsistencyModel, sampling side (stable_consistency_model.py:111-122, 163-260); the oracle is pinned on the
+# reference's own class (tests/test_reference_pin.py::test_stable_consistency_model_sampling)
+def make_scm(D, C, widths, sigma):
+    import bayesflow_b200 as bf
+    params = oracle.perturb_params(oracle.init_params(D, C, widths))
+    kw = {"dropout": 0.0, "widths": widths}
+    net = bf.StableConsistencyModel(subnet_kwargs=kw, sigma=sigma)
+    orc = oracle.OracleStableConsistencyModel(params, D, subnet_kwargs=kw, sigma=sigma)
+    net.build((None, D), (None, C) if C else None)
+    res = net.load_state_dict(params, strict=False)
+    assert not res.unexpected_keys and not [k for k in res.missing_keys if "base_distribution" not in k], res
+    return net.cuda(), orc
+
+
+@pytest.mark.parametrize("D,C,widths,sigma", [(2, 32, (256,) * 5, 1.0), (4, None, (128,) * 3, 1.3), (16, 8, (512,) * 2, 0.7)])
+def test_stable_consistency_function_and_multistep_sampling(D, C, widths, sigma):
+    net, orc = make_scm(D, C, widths, sigma)
+    B = 300
+    g = torch.Generator().manual_seed(31)
+    x = torch.randn(B, D, generator=g) * 2
+    c = torch.randn(3, C, generator=g).repeat_interleave(100, 0) if C else None
+    cc = c.cuda() if C else None
+    for t in (1.5, 0.4, 0.03):
+        assert rel_l2(net.consistency_function(x.cuda(), t, conditions=cc), orc.consistency_function(x, t, c)) < TOL, t
+    assert rel_l2(net.consistency_function(x.cuda(), 0.0, conditions=cc), x) < 1e-6      # f(x, 0) = x
+    for steps, rho in ((15, 3.5), (7, 3.0), (2, 3.5)):
+        Z = [torch.randn(B, D, generator=g) for _ in range(steps)]
+        ref = orc.inverse(x, c, steps=steps, rho=rho, noise_fn=lambda n, s: Z[n - 1])
+        out = net(x.cuda(), conditions=cc, inverse=True, steps=steps, rho=rho, noise_fn=lambda n, shape: Z[n - 1])
+        assert rel_l2(out, ref) < TOL, (steps, rel_l2(out, ref))
+
+
+def test_stable_consistency_surface():
+    import bayesflow_b200 as bf
+    net, orc = make_scm(2, 3, (64, 64), 1.0)
+    x, c = torch.randn(6, 2).cuda(), torch.randn(6, 3).cuda()
+    with pytest.raises(NotImplementedError):
+        net(x, conditions=c)                                               # not invertible (:156-159)
+    with pytest.raises(NotImplementedError):
+        net.compute_metrics(x, conditions=c)                               # training is not built
+    a = net.sample((9,), conditions=torch.randn(9, 3).cuda(), seed=3)
+    b = net.sample((9,), conditions=torch.randn(9, 3).cuda(), seed=3)
+    assert a.shape == (9, 2) and torch.isfinite(a).all() and b.shape == (9, 2)
+    z = torch.randn(64, 2).cuda()
+    cc = torch.randn(64, 3).cuda()
+    full = net(z, conditions=cc, inverse=True, steps=5, seed=11)
+    assert torch.equal(full, net(z, conditions=cc, inverse=True, steps=5, seed=11))   # seeded Philox noise
+    mask, fixed = torch.tensor([1.0, 0.0]).cuda(), torch.tensor([0.0, 0.25]).cuda()
+    out = net(z, conditions=cc, inverse=True, steps=4, seed=1, target_mask=mask, targets_fixed=fixed)
+    assert torch.allclose(out[:, 1], torch.full((64,), 0.25, device="cuda"))
+    assert isinstance(bf.StableConsistencyModel(sigma=2.0).get_config()["sigma"], float)

@@ -386,3 +386,45 @@ def test_dm_stochastic_samplers_same_noise(R, method, kw, monkeypatch):
         x_orc = orc.inverse(z, c, method=method, noise_fn=lambda k, st: {"xz": draws[k]}, **kw)
     assert torch.isfinite(x_ref).all()
     assert rel(x_orc, x_ref) < 5e-5
+
+
+@pytest.mark.parametrize("sigma,steps,rho", [(1.0, 15, 3.5), (1.3, 7, 3.0), (0.7, 2, 3.5)])  # (steps = 1 fails in the reference: times[1])
+def test_stable_consistency_model_sampling(R, sigma, steps, rho, monkeypatch):
+    """StableConsistencyModel (stable_consistency_model.py): consistency function :238-260, time discretisation :111-122 and
+    multistep sampling :163-236 of the reference's own class against oracle.OracleStableConsistencyModel, same normals."""
+    import importlib
+    import keras
+    SCM = importlib.import_module("bayesflow.networks.inference.consistency.stable_consistency_model").StableConsistencyModel
+    D, C, widths, B = 3, 5, (64,) * 2, 19
+    params = oracle.perturb_params(oracle.init_params(D, C, widths))
+    kw = {"dropout": 0.0, "widths": widths}
+    ref = SCM(subnet_kwargs=kw, sigma=sigma)
+    ref.build((None, D), (None, C))
+    alias = {"norm": "norm_layer", "frequencies": "w", "output_projector": "subnet_projector"}
+    for name, value in params.items():
+        obj, parts = ref, name.split(".")
+        for part in parts[:-1]:
+            part = alias.get(part, part)
+            obj = obj[int(part)] if part.isdigit() else getattr(obj, part)
+        with torch.no_grad():
+            getattr(obj, alias.get(parts[-1], parts[-1])).copy_(value)
+    orc = oracle.OracleStableConsistencyModel(params, D, subnet_kwargs=kw, sigma=sigma)
+    g = torch.Generator().manual_seed(23)
+    x, c = torch.randn(B, D, generator=g), torch.randn(B, C, generator=g)
+    with torch.no_grad():
+        for t in (1.5, 0.4, 0.0):
+            tt = torch.full((B, 1), t)
+            assert rel(orc.consistency_function(x, tt, c), ref.consistency_function(x, tt, conditions=c)) < TOL
+        assert torch.allclose(orc.discretize_time(max(steps, 2), rho), ref._discretize_time(max(steps, 2), rho=rho), atol=1e-7)
+        Z = [torch.randn(B, D, generator=g) for _ in range(steps)]
+        it = iter(Z)
+        monkeypatch.setattr(keras.random, "normal", lambda shape, *a, **k: next(it).clone())
+        out_ref = ref(x, conditions=c, inverse=True, steps=steps, rho=rho)
+        out_orc = orc.inverse(x, c, steps=steps, rho=rho, noise_fn=lambda n, s: Z[n - 1])
+        assert rel(out_orc, out_ref) < TOL
+        # target mask (:199-216)
+        mask, fixed = torch.tensor([1.0, 0.0, 1.0]), torch.tensor([0.0, 0.25, 0.0])
+        it = iter(Z)
+        m_ref = ref(x, conditions=c, inverse=True, steps=steps, rho=rho, target_mask=mask, targets_fixed=fixed)
+        m_orc = orc.inverse(x, c, steps=steps, rho=rho, noise_fn=lambda n, s: Z[n - 1], target_mask=mask, targets_fixed=fixed)
+        assert rel(m_orc, m_ref) < TOL
