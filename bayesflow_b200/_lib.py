@@ -28,7 +28,7 @@ _fp = C.POINTER(C.c_float)
 class NetConfig(C.Structure):
     _fields_ = [(n, C.c_int32) for n in
                 ("D", "C", "W", "L", "T", "activation", "merge", "norm", "residual", "film_use_gamma", "precision")] + \
-               [("fourier_scale", C.c_float)]
+               [("fourier_scale", C.c_float), ("block_width", C.c_int32 * BFK_MAX_BLOCKS)]
 
 
 class Weights(C.Structure):
@@ -36,7 +36,8 @@ class Weights(C.Structure):
                 ("m_k", C.c_void_p), ("m_b", C.c_void_p)] + \
                [(n, C.c_void_p * BFK_MAX_BLOCKS) for n in
                 ("dense_k", "dense_b", "film_g_k", "film_g_b", "film_b_k", "film_b_b", "norm_g", "norm_b")] + \
-               [("out_k", C.c_void_p), ("out_b", C.c_void_p)]
+               [("out_k", C.c_void_p), ("out_b", C.c_void_p)] + \
+               [(n, C.c_void_p * BFK_MAX_BLOCKS) for n in ("proj_k", "proj_b")]
 
 
 class Schedule(C.Structure):
@@ -96,6 +97,8 @@ def lib():
     L.bfk_schedule_alpha_sigma.argtypes = [C.c_void_p, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.bfk_sde_langevin_update.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_double, C.c_double,
                                           C.c_double, C.c_double, C.c_int32, C.c_void_p, C.c_void_p]
+    L.bfk_pad2d.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
+    L.bfk_unpad2d.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
     L.bfk_standardize.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                   C.c_int32, C.c_void_p]
     L.bfk_lincomb3.argtypes = [C.c_void_p, C.c_float, C.c_void_p, C.c_float, C.c_void_p, C.c_float, C.c_void_p, C.c_int64,

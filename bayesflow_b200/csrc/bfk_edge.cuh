@@ -571,3 +571,26 @@ extern "C" int bfk_sde_langevin_update(const float* x, const float* v_ode, const
   CK(cudaGetLastError());
   return 0;
 }
+
+// ---- parameter staging for unequal hidden widths (bfk_net_config.block_width) -------------------------------------------
+namespace bfk {
+__global__ void unpad2d_kernel(const float* __restrict__ src, int scols, float* __restrict__ dst, int rows, int cols) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= rows * cols) return;
+  dst[i] = src[(size_t)(i / cols) * scols + (i % cols)];
+}
+}  // namespace bfk
+extern "C" int bfk_pad2d(const float* src, int32_t rows, int32_t cols, float* dst, int32_t rows_pad, int32_t cols_pad, void* stream) {
+  if (!src || !dst || rows < 1 || cols < 1 || rows_pad < rows || cols_pad < cols) return fail(-93, "bfk_pad2d: bad arguments");
+  const size_t n = (size_t)rows_pad * cols_pad;
+  bfk::pad2d_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(src, rows, cols, dst, rows_pad, cols_pad);
+  CK(cudaGetLastError());
+  return 0;
+}
+extern "C" int bfk_unpad2d(const float* src, int32_t cols_pad, float* dst, int32_t rows, int32_t cols, void* stream) {
+  if (!src || !dst || rows < 1 || cols < 1 || cols_pad < cols) return fail(-94, "bfk_unpad2d: bad arguments");
+  const size_t n = (size_t)rows * cols;
+  bfk::unpad2d_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(src, cols_pad, dst, rows, cols);
+  CK(cudaGetLastError());
+  return 0;
+}

@@ -59,6 +59,8 @@ extern "C" int bfk_fused_supported(const bfk_net_config* c) {
   if (check_cfg(c)) return 0;
   if (c->D > BFK_MAX_D) return 0;
   if (c->W > 256 || (c->W % 32) != 0) return 0;
+  for (int l = 0; l < c->L; ++l)
+    if (c->block_width[l] != 0) return 0;  // unequal hidden widths: the layer-wise training / density kernels only
   if (c->precision != BFK_PREC_FP16 && c->precision != BFK_PREC_BF16) return 0;
   SmemPlan p = use_fold(c) ? make_fold_plan(*c) : make_smem_plan(*c);
   if (p.n_stage < 2) return 0;

@@ -65,6 +65,9 @@ int launch_pairs(Kern kernel, unsigned grid, size_t smem, cudaStream_t st, const
 static int check_lw_cfg(const bfk_net_config* c) {
   if (int r = check_train_cfg(c)) return r;
   if (c->film_use_gamma) return fail(-73, "layer-wise sampler: film_use_gamma is not supported (fused sampler and training are)");
+  for (int l = 0; l < c->L; ++l)
+    if (c->block_width[l] != 0)
+      return fail(-69, "layer-wise sampler: unequal hidden widths are served by the training / density kernels (host-driven sampling)");
   if (c->norm == BFK_NORM_RMS) return fail(-72, "layer-wise sampler: norm must be 'layer' or None (fused sampler and training have 'rms')");
   return 0;
 }

@@ -227,6 +227,8 @@ struct BlockFwdArgs {
   long long B, R_pad;
   int W, act, norm, layer;
   float drop_rate, inv_keep; unsigned long long seed; const uint32_t* seed_dev; long long row0;
+  int Weff;             // true width of this block when W is a padded common width (0: W); the padded columns of v are
+                        // exactly zero (zero-padded weights, act(0) = 0), so only the norm's divisor and variance change
 };
 
 template <int NJ>
@@ -305,7 +307,8 @@ __global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
     }
     float mean = 0.f, rs = 1.f;
     if (a.norm != BFK_NORM_NONE) {  // layer: centred; rms: mean stays 0
-      if (a.norm == BFK_NORM_LAYER) mean = warp_sum(sum) / (float)a.W;
+      const float we = (float)(a.Weff > 0 ? a.Weff : a.W);
+      if (a.norm == BFK_NORM_LAYER) mean = warp_sum(sum) / we;
       float sq = 0.f;
 #pragma unroll
       for (int j = 0; j < NJ; ++j)
@@ -313,7 +316,8 @@ __global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
 #pragma unroll
           for (int i = 0; i < 8; ++i) { const float d = v[j][i] - mean; sq = fmaf(d, d, sq); }
         }
-      rs = rsqrtf(warp_sum(sq) / (float)a.W + (a.norm == BFK_NORM_LAYER ? LN_EPS : RMS_EPS));
+      // the W - Weff padded columns hold v = 0 and each added mean^2 to the sum of squares
+      rs = rsqrtf((warp_sum(sq) - ((float)a.W - we) * mean * mean) / we + (a.norm == BFK_NORM_LAYER ? LN_EPS : RMS_EPS));
     }
     if (a.rstd && lane == 0) a.rstd[r] = rs;
 #pragma unroll
@@ -427,7 +431,8 @@ __global__ void __launch_bounds__(256) block_fwd_wide_kernel(const BlockFwdArgs 
       float ts = 0.f;
 #pragma unroll
       for (int w = 0; w < WPR; ++w) ts += s_sum[grp * WPR + w];
-      mean = a.norm == BFK_NORM_LAYER ? ts / (float)a.W : 0.f;
+      const float we = (float)(a.Weff > 0 ? a.Weff : a.W);
+      mean = a.norm == BFK_NORM_LAYER ? ts / we : 0.f;
       float sq = 0.f;
       if (on) {
 #pragma unroll
@@ -439,7 +444,7 @@ __global__ void __launch_bounds__(256) block_fwd_wide_kernel(const BlockFwdArgs 
       float tq = 0.f;
 #pragma unroll
       for (int w = 0; w < WPR; ++w) tq += s_sq[grp * WPR + w];
-      rs = rsqrtf(tq / (float)a.W + (a.norm == BFK_NORM_LAYER ? LN_EPS : RMS_EPS));
+      rs = rsqrtf((tq - ((float)a.W - we) * mean * mean) / we + (a.norm == BFK_NORM_LAYER ? LN_EPS : RMS_EPS));
     }
     if (a.rstd && wig == 0 && lane == 0) a.rstd[r] = rs;
     if (on) {
@@ -479,6 +484,8 @@ struct BlockBwdArgs {
   // film_use_gamma: FG (B,W) = the FiLM scale to_gamma(t_emb) of this block (the forward applied 1 + FG); dG_img gets the
   // cotangent of FG (= dV * u), d_bgfilm the gradient of to_gamma's bias
   const float* FG; unsigned char* dG_img; float* d_bgfilm;
+  int Weff;        // true width when W is a padded common width (0: W): the divisor of the norm backward
+  float* d_bskip;  // bias gradient of the residual projector (= column sums of dV, like d_bfilm) or null
   long long B, R_pad;
   int W, act, norm, layer;
   float drop_rate, inv_keep; unsigned long long seed; const uint32_t* seed_dev; long long row0;
@@ -555,8 +562,9 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
     }
     float m1 = 0.f, m2 = 0.f, rs = 1.f;
     if (a.norm != BFK_NORM_NONE) {  // rms: no centring, so the m1 term is absent
-      if (a.norm == BFK_NORM_LAYER) m1 = warp_sum(s1) / (float)W;
-      m2 = warp_sum(s2) / (float)W;
+      const float we = (float)(a.Weff > 0 ? a.Weff : W);
+      if (a.norm == BFK_NORM_LAYER) m1 = warp_sum(s1) / we;
+      m2 = warp_sum(s2) / we;
       rs = a.rstd[r];
     }
 #pragma unroll
@@ -615,6 +623,7 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
     }
     atomicAdd(a.d_bd + c, a.gscale * s_red[2 * W + c]);
     atomicAdd(a.d_bfilm + c, a.gscale * s_red[3 * W + c]);
+    if (a.d_bskip) atomicAdd(a.d_bskip + c, a.gscale * s_red[3 * W + c]);
     if (FGAM && a.d_bgfilm) atomicAdd(a.d_bgfilm + c, a.gscale * s_red[4 * W + c]);
   }
 }

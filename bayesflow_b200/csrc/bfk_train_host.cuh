@@ -21,6 +21,8 @@ struct TrainBufs {
   long long Rp;
   unsigned char *u_img, *te_img, *w1_pk, *a1_img, *wm_f, *wm_b, *h0_img, *wo_f, *wo_b, *dout_img, *dP_img, *dV_img, *dh0pre_img;
   float *w1, *b1, *h0pre, *m, *h0, *FB, *bo_pad, *out, *dH, *dte, *da1, *dW1, *db1;
+  float* skip;                      // residual projector output of the current block (unequal widths), (B, W)
+  unsigned char *wp_f, *wp_b;       // projector operand images (forward / dX)
   float* FG;                        // film_use_gamma: FiLM scale of the current block (recomputed in the backward)
   unsigned char *wg_f, *wg_b, *dG_img;  // film_use_gamma: to_gamma operand images (forward / dte), cotangent image of FG
   unsigned char *wd_f[BFK_MAX_BLOCKS], *wd_b[BFK_MAX_BLOCKS], *wb_f[BFK_MAX_BLOCKS], *wb_b[BFK_MAX_BLOCKS], *h_img[BFK_MAX_BLOCKS];
@@ -66,6 +68,13 @@ void plan_train(const bfk_net_config* c, long long B, bool backward, Arena& ar, 
     b.h_img[l] = (unsigned char*)ar.take(Rp * W * 2);
   }
   b.FB = (float*)ar.take(Bs * W * 4);
+  bool ragged = false;
+  for (int l = 0; l < c->L; ++l) ragged = ragged || (c->block_width[l] != 0);
+  if (ragged) {  // a projector may sit in any block
+    b.skip = (float*)ar.take(Bs * W * 4);
+    b.wp_f = (unsigned char*)ar.take((size_t)W * W * 2);
+    b.wp_b = (unsigned char*)ar.take((size_t)W * W * 2);
+  }
   if (c->film_use_gamma) {
     b.FG = (float*)ar.take(Bs * W * 4);
     b.wg_f = (unsigned char*)ar.take((size_t)W * b.KT * 2);
@@ -94,6 +103,9 @@ int check_train_cfg(const bfk_net_config* c) {
   if ((c->W % 64) != 0 || c->W > 1024) return fail(-70, "layer-wise path: W must be a multiple of 64, <= 1024");
   if (c->D > 64) return fail(-71, "layer-wise path: D <= 64");
   if (c->precision != BFK_PREC_FP16) return fail(-74, "layer-wise path: fp16 operands only (bf16 cannot meet the 2e-3 gradient gate)");
+  for (int l = 0; l < c->L; ++l)
+    if (c->block_width[l] < 0 || c->block_width[l] > c->W || (c->block_width[l] % 8) != 0)
+      return fail(-69, "layer-wise path: block_width[l] must be 0 or a multiple of 8 that is <= W (the padded common width)");
   return 0;
 }
 
@@ -224,11 +236,17 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
       RC(bfk_pack_kmajor_t(w->film_g_k[l], W, T, KT, W, NTW, P16, b.wg_f, st));
       RC(bfk_gemm(b.te_img, b.wg_f, b.FG, W, B, W, KT, NTW, 1, 0, w->film_g_b[l], 1.f, P16, st));
     }
+    const bool proj = c->residual && w->proj_k[l] != nullptr;
+    if (proj) {  // unequal in / out widths: skip = x Wp + bp (conditional_dense_block.py:125-127)
+      RC(bfk_pack_kmajor_t(w->proj_k[l], W, W, W, W, NTW, P16, b.wp_f, st));
+      RC(bfk_gemm(l == 0 ? b.h0_img : b.h_img[l - 1], b.wp_f, b.skip, W, B, W, W, NTW, 1, 0, w->proj_b[l], 1.f, P16, st));
+    }
     BlockFwdArgs a{};
     a.P = b.P[l]; a.FB = b.FB; a.FG = c->film_use_gamma ? b.FG : nullptr; a.fb_stride = W;
-    a.prev = c->residual ? (l == 0 ? b.h0 : b.xhat[l - 1]) : nullptr;
-    a.pg = (l > 0 && c->norm != BFK_NORM_NONE) ? w->norm_g[l - 1] : nullptr;  // rms: scale only (pb stays null)
-    a.pb = (l > 0 && c->norm == BFK_NORM_LAYER) ? w->norm_b[l - 1] : nullptr;
+    a.Weff = c->block_width[l];
+    a.prev = c->residual ? (proj ? b.skip : (l == 0 ? b.h0 : b.xhat[l - 1])) : nullptr;
+    a.pg = (!proj && l > 0 && c->norm != BFK_NORM_NONE) ? w->norm_g[l - 1] : nullptr;  // rms: scale only (pb stays null)
+    a.pb = (!proj && l > 0 && c->norm == BFK_NORM_LAYER) ? w->norm_b[l - 1] : nullptr;
     a.gamma = c->norm != BFK_NORM_NONE ? w->norm_g[l] : nullptr;
     a.beta = c->norm == BFK_NORM_LAYER ? w->norm_b[l] : nullptr;
     a.xhat = b.xhat[l]; a.rstd = b.rstd[l]; a.img = b.h_img[l]; a.out_f32 = nullptr;
@@ -264,6 +282,9 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
     a.d_bd = GP(g->dense_b[l]); a.d_bfilm = GP(g->film_b_b[l]);
     a.B = B; a.R_pad = Rp; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
     a.drop_rate = ta->dropout; a.inv_keep = inv_keep; a.seed = ta->seed; a.seed_dev = ta->seed_dev; a.row0 = ta->row_offset; a.gscale = gs;
+    const bool proj = c->residual && w->proj_k[l] != nullptr;
+    a.Weff = c->block_width[l];
+    a.d_bskip = proj ? GP(g->proj_b[l]) : nullptr;
     if (c->film_use_gamma) {  // the forward kept only the last block's FiLM scale: rebuild this block's
       RC(bfk_pack_kmajor_t(w->film_g_k[l], W, T, KT, W, NTW, P16, b.wg_f, st));
       RC(bfk_gemm(b.te_img, b.wg_f, b.FG, W, B, W, KT, NTW, 1, 0, w->film_g_b[l], 1.f, P16, st));
@@ -281,9 +302,14 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
         RC(bfk_gemm(b.dG_img, b.wg_b, b.dte, KTN, B, KTN, W, 64, 1, GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
       }
     }
-    if (!c->residual) CK(cudaMemsetAsync(b.dH, 0, (size_t)B * W * 4, st));
+    if (proj) RC(launch_gemm_dw(l == 0 ? b.h0_img : b.h_img[l - 1], W / 8, b.dV_img, W / 8, GP(g->proj_k[l]), W, W, W, Rp, gs, sw, st));
+    if (!c->residual || proj) CK(cudaMemsetAsync(b.dH, 0, (size_t)B * W * 4, st));  // no identity skip into the input
     RC(bfk_pack_kmajor(w->dense_k[l], W, W, W, W, NTW, P16, b.wd_b[l], st));
     RC(bfk_gemm(b.dP_img, b.wd_b[l], b.dH, W, B, W, W, NTW, 1, GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
+    if (proj) {  // the skip's cotangent dV goes back through the projector
+      RC(bfk_pack_kmajor(w->proj_k[l], W, W, W, W, NTW, P16, b.wp_b, st));
+      RC(bfk_gemm(b.dV_img, b.wp_b, b.dH, W, B, W, W, NTW, 1, GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
+    }
   }
   CK(cudaMemsetAsync(b.db1, 0, (size_t)N1 * 4, st));
   if (b.has_merge) {
@@ -340,15 +366,21 @@ extern "C" int bfk_train_vjp(const bfk_net_config* c, const bfk_weights* w, cons
     a.d_gamma = a.d_beta = a.d_bd = a.d_bfilm = nullptr;
     a.B = B; a.R_pad = Rp; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
     a.drop_rate = 0.f; a.inv_keep = 1.f; a.seed = 0; a.seed_dev = nullptr; a.row0 = 0; a.gscale = 1.f;
+    const bool proj = c->residual && w->proj_k[l] != nullptr;
+    a.Weff = c->block_width[l];
     if (c->film_use_gamma) {  // dU = dV (1 + FG): rebuild this block's FiLM scale (time does not depend on x: no dG needed)
       RC(bfk_pack_kmajor_t(w->film_g_k[l], W, c->T, b.KT, W, NTW, P16, b.wg_f, st));
       RC(bfk_gemm(b.te_img, b.wg_f, b.FG, W, B, W, b.KT, NTW, 1, 0, w->film_g_b[l], 1.f, P16, st));
       a.FG = b.FG; a.dG_img = nullptr; a.d_bgfilm = nullptr;
     }
     RC(launch_block_bwd(a, st));
-    if (!c->residual) CK(cudaMemsetAsync(b.dH, 0, (size_t)B * W * 4, st));
+    if (!c->residual || proj) CK(cudaMemsetAsync(b.dH, 0, (size_t)B * W * 4, st));
     RC(bfk_pack_kmajor(w->dense_k[l], W, W, W, W, NTW, P16, b.wd_b[l], st));
     RC(bfk_gemm(b.dP_img, b.wd_b[l], b.dH, W, B, W, W, NTW, 1, GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
+    if (proj) {
+      RC(bfk_pack_kmajor(w->proj_k[l], W, W, W, W, NTW, P16, b.wp_b, st));
+      RC(bfk_gemm(b.dV_img, b.wp_b, b.dH, W, B, W, W, NTW, 1, GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
+    }
   }
   if (b.has_merge) {
     act_bwd_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.dH, b.m, W, B, n_tiles, W / 8, act, b.dP_img, nullptr, 1.f);

@@ -102,7 +102,7 @@ class DiagonalNormal(nn.Module):
 
 
 class _Block(nn.Module):
-    def __init__(self, fan_in, width, T, film_use_gamma, norm):
+    def __init__(self, fan_in, width, T, film_use_gamma, norm, projector=False):
         super().__init__()
         self.dense = _Dense(fan_in, width)
         self.film = nn.Module()
@@ -116,6 +116,8 @@ class _Block(nn.Module):
         elif norm == "rms":
             self.norm = nn.Module()
             self.norm.scale = nn.Parameter(torch.ones(width))
+        if projector:  # residual projector for unequal in / out widths (conditional_dense_block.py:152-156)
+            self.projector = _Dense(fan_in, width)
 
 
 class TimeMLP(nn.Module):
@@ -168,9 +170,11 @@ class TimeMLP(nn.Module):
             self.merge_proj = _Dense(2 * W0 if self.merge == "concat" else W0, W0)
         blocks, prev = [], W0
         for w in self.widths:
-            if w != prev:
-                raise NotImplementedError("the accelerated path needs all hidden widths equal (no residual projector)")
-            blocks.append(_Block(prev, w, self.T, self.film_use_gamma, self.norm))
+            # unequal widths: zero-padded to one common width inside the kernels, with a residual projector where a
+            # block changes the width (served by the layer-wise training / density kernels, see _RunTE)
+            if w != prev and (w % 8 or prev % 8):
+                raise NotImplementedError("unequal hidden widths must be multiples of 8 on the accelerated path")
+            blocks.append(_Block(prev, w, self.T, self.film_use_gamma, self.norm, projector=bool(self.residual and w != prev)))
             prev = w
         self.blocks = nn.ModuleList(blocks)
         self.built = True
@@ -210,6 +214,7 @@ class _Engine:
         self._key = None
         self.cfg = None
         self.layerwise = False
+        self.train_engine_sampler = False
         self.kernel_events = None  # set to a list to have CUDA events recorded around the sampler kernel
         self.launches = 0          # kernels launched so far (bench.py reports it as gpu_launches)
 
@@ -219,6 +224,11 @@ class _Engine:
         cfg = _lib.NetConfig()
         cfg.D, cfg.C = net._D, (net._C or 0)
         cfg.W, cfg.L, cfg.T = sub.widths[0], len(sub.widths), sub.T
+        if any(w != sub.widths[0] for w in sub.widths):
+            # unequal hidden widths: W = the common padded width, block_width[l] = the true widths (include/bfk.h)
+            cfg.W = (max(sub.widths) + 63) // 64 * 64
+            for l, w in enumerate(sub.widths):
+                cfg.block_width[l] = int(w)
         cfg.activation = _lib.ACT[sub.activation]
         cfg.merge = _lib.MERGE[sub.merge] if net._C else 0
         cfg.norm = _lib.NORM[sub.norm]
@@ -238,6 +248,12 @@ class _Engine:
         if dev.type != "cuda":
             raise RuntimeError("bayesflow_b200: move the network to a CUDA device first (no CPU fallback)")
         self.cfg = cfg = self._make_cfg()
+        self.train_engine_sampler = any(cfg.block_width[l] for l in range(cfg.L))
+        if self.train_engine_sampler:
+            # unequal hidden widths: every velocity evaluation is a forward pass of the training kernels (_RunTE)
+            self.layerwise = False
+            self._packed, self._key = torch.empty(1, dtype=torch.uint8, device=dev), key
+            return
         self.layerwise = not L.bfk_fused_supported(C.byref(cfg))
         if self.layerwise:
             # W > 256 or D > 8: the layer-wise tcgen05 path (bfk_sample_layerwise) reads the fp32 weights directly
@@ -547,6 +563,72 @@ class _RunLW:
         return out
 
 
+class _RunTE:
+    """Sampling for networks with unequal hidden widths (residual projector): every velocity evaluation is one forward
+    pass of the layer-wise TRAINING kernels (`bfk_train_step`, forward only, zero-padded common width), the Runge-Kutta
+    combinations are `bfk_rk_combine`, and the host runs the reference's integrators (utils/integrate.py:31-406) - the
+    machinery of the density path without the Jacobian trace."""
+
+    def __init__(self, net, conditions, B, repeats, target_mask):
+        from .training import train_engine
+        self.net, self.eng = net, train_engine(net)
+        self.cond = None
+        if net._C:
+            cond = conditions.detach().to(torch.float32)
+            if repeats:
+                cond = cond.repeat_interleave(int(repeats), dim=0)
+            if cond.ndim != 2 or cond.shape != (B, net._C):
+                raise ValueError(f"conditions must have shape ({B}, {net._C}), got {tuple(cond.shape)}")
+            self.cond = cond.contiguous()
+        self.affine = net._velocity_trace_fn(self.cond, B, {}).affine  # DiffusionModel: v = cZ x + cP pred at net-time
+        self.tmask = None
+        if target_mask is not None:
+            tm = torch.as_tensor(target_mask, dtype=torch.float32, device=self.eng.device)
+            if tm.numel() != net._D:
+                raise NotImplementedError("target_mask must be feature-level, shape (D,), on the accelerated path")
+            self.tmask = tm.reshape(1, -1).contiguous()
+        self.info, self.evals = {}, 0
+
+    def _check_x(self, x):
+        if not x.is_cuda:
+            raise RuntimeError("bayesflow_b200 runs on CUDA tensors only (no CPU fallback)")
+        if x.ndim != 2 or x.shape[-1] != self.net._D:
+            raise ValueError(f"expected (rows, {self.net._D}) state, got {tuple(x.shape)}")
+        return x.detach().to(torch.float32).contiguous()
+
+    def velocity(self, x, time: float):
+        x = self._check_x(x)
+        cZ, cP, t_net = self.affine(float(time))
+        tvec = torch.full((x.shape[0],), float(np.float32(t_net)), device=x.device, dtype=torch.float32)
+        _, pred = self.eng.step(x, tvec, self.cond, None, backward=False, want_pred=True, want_loss=False)
+        self.evals += 1
+        if cZ != 0.0 or cP != 1.0:
+            pred = float(np.float32(cZ)) * x + float(np.float32(cP)) * pred
+        return pred if self.tmask is None else pred * self.tmask
+
+    def run_fixed(self, x, times, hs, method):
+        from .density import _step
+        x = self._check_x(x)
+        per = len(times) // max(len(hs), 1)
+        state = (x,)
+        for i, h in enumerate(hs):
+            state, _, _, _ = _step(lambda t, xz: (self.velocity(xz, float(np.float32(t))),), state, float(times[i * per]),
+                                   float(h), method)
+        self.info = {"steps": len(hs), "evals": self.evals, "rejected": 0, "path": "train-engine"}
+        return state[0]
+
+    def run_adaptive(self, x, start_time, stop_time, min_steps, max_steps, method, atol=1e-6, rtol=1e-4):
+        from .density import _integrate_adaptive
+        x = self._check_x(x)
+        info = {}
+        (out,) = _integrate_adaptive(lambda t, xz: (self.velocity(xz, float(np.float32(t))),), (x,), float(start_time),
+                                     float(stop_time), int(min_steps), int(max_steps), method, info, atol, rtol,
+                                     group=getattr(self.net, "step_control_group", None))
+        self.info = {"steps": int(info["steps"]), "rejected": int(info["rejected"]), "evals": self.evals,
+                     "path": "train-engine"}
+        return out
+
+
 def _as_shape(batch_shape, kwargs):
     # utils/decorators.py:102-114 allow_batch_size
     if batch_shape is None and "batch_size" in kwargs:
@@ -698,6 +780,8 @@ class InferenceNetwork(nn.Module):
         self._engine.prepare()
         if self.unconditional_mode and conditions is not None:
             conditions = torch.zeros_like(conditions)
+        if self._engine.train_engine_sampler:
+            return _RunTE(self, conditions, B, kwargs.get("conditions_repeats"), kwargs.get("target_mask"))
         if self._engine.layerwise:
             cond, rpg = self._engine.group_conditions(conditions, B, kwargs.get("conditions_repeats"))
             return _RunLW(self._engine, cond, rpg, kwargs.get("target_mask"))
@@ -812,7 +896,8 @@ class FlowMatching(InferenceNetwork):
         bd = self.base_distribution
         standard = (isinstance(bd, DiagonalNormal) and not torch.is_tensor(bd.mean) and not torch.is_tensor(bd.std)
                     and float(bd.mean) == 0.0 and float(bd.std) == 1.0)
-        return standard and not self.use_optimal_transport and self.drop_cond_prob == 0 and self.drop_target_prob == 0
+        ragged = any(w != self.subnet.widths[0] for w in self.subnet.widths)  # padded staging launches around the step
+        return standard and not ragged and not self.use_optimal_transport and self.drop_cond_prob == 0 and self.drop_target_prob == 0
 
     def _loss_and_grads(self, x, conditions=None, sample_weight=None, stage="training", seed=None, world=1, backward=True,
                         row_offset=0, noise_seed=None, seed_dev=None, loss_into_slot=False, **kwargs):

@@ -71,6 +71,8 @@ def fill_weights(net, get):
         w.c_k, w.c_b = P(sub.c_proj.kernel), P(sub.c_proj.bias)
         w.m_k, w.m_b = P(sub.merge_proj.kernel), P(sub.merge_proj.bias)
     for i, b in enumerate(sub.blocks):
+        if hasattr(b, "projector"):
+            w.proj_k[i], w.proj_b[i] = P(b.projector.kernel), P(b.projector.bias)
         w.dense_k[i], w.dense_b[i] = P(b.dense.kernel), P(b.dense.bias)
         w.film_b_k[i], w.film_b_b[i] = P(b.film.to_beta.kernel), P(b.film.to_beta.bias)
         if sub.film_use_gamma:
@@ -116,10 +118,81 @@ class TrainEngine:
         self.cfg = net._engine._make_cfg()
         if net.precision != "fp16":
             raise NotImplementedError("the training path uses fp16 operands (bf16 cannot meet the 2e-3 gradient tolerance)")
-        self.w, self._keep_w = fill_weights(net, lambda p: p.data)
-        self.g, self._keep_g = fill_weights(net, lambda p: self._gviews[p])
+        self.ragged = any(self.cfg.block_width[l] for l in range(self.cfg.L))
+        if self.ragged:
+            self._build_padded_arena()
+        else:
+            self.w, self._keep_w = fill_weights(net, lambda p: p.data)
+            self.g, self._keep_g = fill_weights(net, lambda p: self._gviews[p])
         self._ws, self._ws_key = None, None
         self.launches = 0
+
+    # -- unequal hidden widths: the kernels see every weight zero-padded to the common width cfg.W ------------------------
+    def _build_padded_arena(self):
+        """Padded twins of the parameters and of their gradients (include/bfk.h `block_width`).  `_pad_params` refreshes
+        the twins before a step (`bfk_pad2d`), `_unpad_grads` copies the valid gradient regions back (`bfk_unpad2d`)."""
+        net, sub, Wm = self.net, self.net.subnet, int(self.cfg.W)
+        jobs, shapes = [], {}
+
+        def padded_shape(p, rows_pad=None):
+            if p.ndim == 1:
+                return (1, p.shape[0]), (1, Wm)
+            return tuple(p.shape), (rows_pad if rows_pad is not None else p.shape[0], Wm)
+
+        def add(p, rows_pad=None, halves=1):
+            (R, Cc), (Rp, Cp) = padded_shape(p, rows_pad)
+            shapes[p] = (R, Cc, Rp, Cp, halves)
+
+        W0 = sub.widths[0]
+        add(sub.x_proj.kernel), add(sub.x_proj.bias)
+        if net._C:
+            add(sub.c_proj.kernel), add(sub.c_proj.bias)
+            concat = sub.merge == "concat"
+            add(sub.merge_proj.kernel, rows_pad=(2 * Wm if concat else Wm), halves=2 if concat else 1)
+            add(sub.merge_proj.bias)
+        for b in sub.blocks:
+            add(b.dense.kernel, rows_pad=Wm), add(b.dense.bias)
+            add(b.film.to_beta.kernel), add(b.film.to_beta.bias)
+            if sub.film_use_gamma:
+                add(b.film.to_gamma.kernel), add(b.film.to_gamma.bias)
+            if sub.norm == "layer":
+                add(b.norm.gamma), add(b.norm.beta)
+            elif sub.norm == "rms":
+                add(b.norm.scale)
+            if hasattr(b, "projector"):
+                add(b.projector.kernel, rows_pad=Wm), add(b.projector.bias)
+        # the output projector reads W rows (the padded last block output); its D columns stay as they are
+        pk = net.output_projector.kernel
+        shapes[pk] = (pk.shape[0], pk.shape[1], Wm, pk.shape[1], 1)
+        total = sum(Rp * Cp for (_, _, Rp, Cp, _) in shapes.values())
+        self.pflat = torch.zeros(total, device=self.device, dtype=torch.float32)
+        self.pgrad = torch.zeros(total, device=self.device, dtype=torch.float32)
+        self._pviews, self._pgviews, off = {}, {}, 0
+        for p, (R, Cc, Rp, Cp, halves) in shapes.items():
+            self._pviews[p] = self.pflat[off:off + Rp * Cp]
+            self._pgviews[p] = self.pgrad[off:off + Rp * Cp]
+            if halves == 2:  # concat merge kernel: the h0 rows and the condition rows are padded separately
+                h, hp = R // 2, Rp // 2
+                jobs.append((p, 0, h, Cc, off, hp, Cp))
+                jobs.append((p, h * Cc, h, Cc, off + hp * Cp, hp, Cp))
+            else:
+                jobs.append((p, 0, R, Cc, off, Rp, Cp))
+            off += Rp * Cp
+        self._pad_jobs = jobs
+        self.w, self._keep_w = fill_weights(net, lambda p: self._pviews[p] if p in self._pviews else p.data)
+        self.g, self._keep_g = fill_weights(net, lambda p: self._pgviews[p] if p in self._pgviews else self._gviews[p])
+
+    def _pad_params(self):
+        st = _lib.stream_ptr()
+        for p, src_off, R, Cc, dst_off, Rp, Cp in self._pad_jobs:
+            _lib.check(self.L.bfk_pad2d(C.c_void_p(p.data.data_ptr() + 4 * src_off), R, Cc,
+                                        C.c_void_p(self.pflat.data_ptr() + 4 * dst_off), Rp, Cp, st), "bfk_pad2d")
+
+    def _unpad_grads(self):
+        st = _lib.stream_ptr()
+        for p, src_off, R, Cc, dst_off, Rp, Cp in self._pad_jobs:
+            _lib.check(self.L.bfk_unpad2d(C.c_void_p(self.pgrad.data_ptr() + 4 * dst_off), Cp,
+                                          C.c_void_p(self._gviews[p].data_ptr() + 4 * src_off), R, Cc, st), "bfk_unpad2d")
 
     def grad_of(self, p):
         return self._gviews[p]
@@ -184,6 +257,12 @@ class TrainEngine:
         a.loss_scale = 1.0 / (gb * (D if loss in ("mse", "mae", "pseudo_huber") else 1)) / cotangent_scale
         a.grad_scale = 1.0 / (gb * D) / cotangent_scale
         ws = self._workspace(B, backward)
+        if self.ragged:
+            self._pad_params()
+            if backward:
+                if not zero_grad:
+                    raise NotImplementedError("gradient accumulation over several steps is not built for unequal hidden widths")
+                self.pgrad.zero_()
         if backward and zero_grad:
             self.grad_ext.zero_()
             self.version += 1
@@ -197,6 +276,8 @@ class TrainEngine:
         rc = self.L.bfk_train_step(C.byref(self.cfg), C.byref(self.w), C.byref(self.g) if backward else None, C.byref(a),
                                    _lib.ptr(loss_t), _lib.ptr(pred), _lib.ptr(ws), ws.numel(), _lib.stream_ptr())
         _lib.check(rc, "bfk_train_step")
+        if self.ragged and backward:
+            self._unpad_grads()
         self.launches += self.launches_per_step(backward)
         return loss_t, pred
 
@@ -215,6 +296,8 @@ class TrainEngine:
         a.dropout, a.loss_scale, a.grad_scale = 0.0, 1.0, 1.0
         a._keep = (x, t, cond)
         ws = self._workspace(B, True)
+        if self.ragged:
+            self._pad_params()
         pred = torch.empty(B, D, device=self.device, dtype=torch.float32)
         _lib.check(self.L.bfk_train_step(C.byref(self.cfg), C.byref(self.w), None, C.byref(a), None, _lib.ptr(pred),
                                          _lib.ptr(ws), ws.numel(), _lib.stream_ptr()), "bfk_train_step")

@@ -57,6 +57,11 @@ typedef struct bfk_net_config {
   int32_t film_use_gamma; /* 0/1 */
   int32_t precision;      /* BFK_PREC_*: tensor-core operand type, fp32 accumulate */
   float fourier_scale;
+  /* Unequal hidden widths (time_mlp.py:100-120 with widths like (64, 96, 32)): W is then the common PADDED width (a
+   * multiple of 64, every weight zero-padded to it) and block_width[l] the true output width of block l, over which its
+   * normalisation runs; all zero = every block has width W.  Blocks whose input and output widths differ carry a
+   * residual projector (bfk_weights.proj_k / proj_b).  Served by the layer-wise training / density kernels only. */
+  int32_t block_width[BFK_MAX_BLOCKS];
 } bfk_net_config;
 
 /* fp32 device pointers in the reference's variable order; Dense kernels are (in,out) row-major */
@@ -70,6 +75,8 @@ typedef struct bfk_weights {
   const float* film_b_k[BFK_MAX_BLOCKS]; const float* film_b_b[BFK_MAX_BLOCKS]; /* (T,W),(W) */
   const float* norm_g[BFK_MAX_BLOCKS]; const float* norm_b[BFK_MAX_BLOCKS];     /* (W),(W) or NULL */
   const float* out_k; const float* out_b; /* (W,D),(D) */
+  /* residual projector of block l, skip = x Wp + bp (conditional_dense_block.py:125-127, 152-156), or NULL: identity skip */
+  const float* proj_k[BFK_MAX_BLOCKS]; const float* proj_b[BFK_MAX_BLOCKS]; /* (W,W),(W) */
 } bfk_weights;
 
 typedef struct bfk_schedule {
@@ -282,6 +289,10 @@ int bfk_standardize(const float* x, float* out, int64_t rows, int32_t F, const f
 int bfk_detect_repeats(const float* conditions, int64_t B, int32_t C, int64_t* out2, void* stream);
 int bfk_lincomb3(float* out, float a, const float* x, float b, const float* y, float c, const float* z, int64_t numel,
                  void* stream);
+/* dst (rows_pad, cols_pad) = src (rows, cols) zero-padded; and the inverse copy of the valid region.  Parameter staging for
+ * networks with unequal hidden widths (bfk_net_config.block_width): the kernels see zero-padded weights of one common width. */
+int bfk_pad2d(const float* src, int32_t rows, int32_t cols, float* dst, int32_t rows_pad, int32_t cols_pad, void* stream);
+int bfk_unpad2d(const float* src, int32_t cols_pad, float* dst, int32_t rows, int32_t cols, void* stream);
 size_t bfk_moments_workspace_floats(int64_t rows, int32_t F);
 int bfk_batch_moments(const float* x, int64_t rows, int32_t F, float* workspace, float* stats, void* stream);
 /* Allocation-free variant of bfk_batch_moments.  NO COUNTERPART IN THE REFERENCE: added

@@ -31,6 +31,7 @@ def _data(B, D, C, seed=11):
     (16, 8, (512,) * 2, 64, {}),             # wide block, D > 8
     (3, 6, (128,) * 2, 90, {"film_use_gamma": True}),   # the reverse pass scales dU by (1 + gamma(t))
     (3, 6, (128,) * 2, 90, {"norm": "rms"}),
+    (3, 6, (64, 96, 32), 90, {}),                      # unequal widths: residual projector in the reverse pass
 ])
 def test_velocity_and_exact_trace(D, C, widths, B, sk):
     net, orc = make_pair(D, C, widths, **sk)

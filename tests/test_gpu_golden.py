@@ -25,14 +25,7 @@ def build(g, dm=False):
 def test_fm_cuda_equals_reference_golden(name):
     g = load(name)
     assert g["params_ok"], "torch's RNG stream changed: regenerate tests/golden with tools/make_golden.py"
-    if len(set(g["widths"])) > 1:
-        # unequal hidden widths need the residual projector (conditional_dense_block.py:152-156): NOT built on the CUDA
-        # path (DESIGN.md "out of scope / gaps"); the golden vectors pin the oracle (tests/test_golden_oracle.py) and the
-        # product must refuse loudly rather than compute something else
-        with pytest.raises(NotImplementedError, match="residual projector"):
-            build(g)
-        return
-    net = build(g)
+    net = build(g)  # (fm_small_projector: unequal hidden widths -> residual projector, conditional_dense_block.py:152-156)
     z, c = g["z"].cuda(), g["conditions"].cuda()
     for t in (0.0, 0.37, 1.0):
         assert rel_l2(net.velocity(z, t, conditions=c), g[f"velocity_t{t}"]) < TOL

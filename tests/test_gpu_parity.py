@@ -21,6 +21,7 @@ def _need_cuda():
     (2, 32, (256,) * 5, 1), (2, 32, (256,) * 5, 127), (2, 32, (256,) * 5, 128), (2, 32, (256,) * 5, 4097),
     (2, 2, (256,) * 5, 1000), (4, 20, (256,) * 5, 513), (2, None, (256,) * 5, 300), (4, 20, (128,) * 3, 777),
     (2, 2, (64,) * 2, 257), (8, 5, (256,) * 2, 260), (3, 7, (96,) * 4, 99),
+    (2, 6, (64, 96, 32), 150), (4, 20, (256, 128, 256), 300), (2, None, (32, 64), 77),   # unequal widths (projector)
 ])
 def test_fm_velocity(D, C, widths, B):
     net, orc = make_pair(D, C, widths)

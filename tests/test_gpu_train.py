@@ -56,6 +56,10 @@ def cuda_tuple(tup):
     (2, 6, (128,) * 2, 300, {"time_embedding_dim": 8}),
     (2, 6, (128,) * 2, 300, {"time_embedding_dim": 1}),
     (2, 6, (128,) * 2, 300, {"activation": "relu"}),
+    (2, 6, (64, 96, 32), 300, {}),                                           # unequal widths: residual projector, padded to 128
+    (3, 5, (128, 64, 64, 256), 260, {"merge": "add", "activation": "silu"}),
+    (2, None, (96, 160), 200, {"norm": "rms"}),
+    (2, 6, (64, 128), 200, {"norm": None, "film_use_gamma": True}),
     (2, 6, (128,) * 3, 300, {"norm": "rms"}),                                # RMSNormalization: scale only, eps 1e-6
     (4, 5, (512,) * 2, 260, {"norm": "rms", "activation": "relu"}),
     (2, 6, (128,) * 3, 300, {"film_use_gamma": True}),                       # FiLM scale: (1 + gamma(t)) * h + beta(t)
