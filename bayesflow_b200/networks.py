@@ -262,8 +262,15 @@ class _Engine:
             L.bfk_layerwise_workspace_bytes.restype = C.c_size_t
             L.bfk_layerwise_workspace_bytes.argtypes = [C.POINTER(_lib.NetConfig), C.c_int64, C.c_int64, C.c_int64]
             if L.bfk_layerwise_workspace_bytes(C.byref(cfg), 128, 1, 1) == 0:
+                why = L.bfk_last_error_string().decode()
+                if L.bfk_train_workspace_bytes(C.byref(cfg), 128, 0) != 0:
+                    # e.g. film_use_gamma or norm="rms" with W > 256 / D > 8: no sampler kernel, but the training forward
+                    # has it -> host-driven sampling over bfk_train_step (_RunTE), a coverage path
+                    self.train_engine_sampler, self.layerwise = True, False
+                    self._packed, self._key = torch.empty(1, dtype=torch.uint8, device=dev), key
+                    return
                 raise NotImplementedError(f"config D={cfg.D} W={cfg.W} L={cfg.L}: neither the fused sampler (D<=8, W<=256, "
-                                          f"W%32==0) nor the layer-wise path covers it: " + L.bfk_last_error_string().decode())
+                                          f"W%32==0) nor the layer-wise path covers it: " + why)
             self.w, self._keep_w = fill_weights(net, lambda p: p.detach())
             self._packed, self._key = torch.empty(1, dtype=torch.uint8, device=dev), key
             self._ws = None
@@ -1280,6 +1287,11 @@ class DiffusionModel(InferenceNetwork):
                 raise RuntimeError("bayesflow_b200 runs on CUDA tensors only (no CPU fallback)")
             run = self._run(conditions, z.shape[0], kwargs)
             sde = ReverseSDE(self, run, kwargs.get("target_mask"))
+            if kwargs.get("target_mask") is not None and (integrate_kwargs.get("corrector_steps") or
+                                                           integrate_kwargs["method"] == "langevin"):
+                # the reference's score_fn ignores the target mask (diffusion_model.py:845-849): the Langevin updates use
+                # the unmasked velocity
+                sde.score_run = self._run(conditions, z.shape[0], {k: v for k, v in kwargs.items() if k != "target_mask"})
             keys = ("start_time", "stop_time", "steps", "method", "min_steps", "max_steps", "corrector_steps", "e_rel",
                     "e_abs", "r", "adapt_safety", "noise_fn", "step_size_factor")
             info = {}

@@ -68,10 +68,12 @@ class ReverseSDE:
 
     def langevin_update(self, time, x, z, a, b, per_row):
         """x + e*score(time, x) + sqrt(2e)*z (integrate.py:949-959, 1228-1236); the score comes from one velocity call."""
-        if self.mask is not None:
-            raise NotImplementedError("corrector / langevin updates with a target_mask are outside the accelerated path "
-                                      "(the reference's score_fn ignores the mask, diffusion_model.py:845-849)")
-        v = self.run.velocity(x, float(np.float32(time)))
+        # with a target mask the reference's score_fn still sees the UNMASKED score (diffusion_model.py:845-849), so the
+        # velocity comes from a run built without the mask (networks.py sets `score_run`)
+        run = getattr(self, "score_run", None) or self.run
+        if self.mask is not None and run is self.run:
+            raise RuntimeError("ReverseSDE: a target mask needs `score_run` (the unmasked velocity) for Langevin updates")
+        v = run.velocity(x, float(np.float32(time)))
         self.evals += 1
         fz, beta = self.terms(time)
         out = torch.empty_like(x)

@@ -559,6 +559,9 @@ class OracleDiffusionModel:
         kwargs.pop("seed", None)
         ik = {"start_time": 1.0, "stop_time": 0.0} | self.integrate_kwargs | kwargs
         ik = {k: v for k, v in ik.items() if k in self._IK}
+        if kwargs.get("target_mask") is not None:  # :793-798: the fixed coordinates start at their targets
+            tm = torch.broadcast_to(kwargs["target_mask"], z.shape)
+            z = _mask(z, tm, torch.broadcast_to(kwargs["targets_fixed"], z.shape))
         if density:
             if ik["method"] not in ("euler", "rk45", "tsit5"):
                 ik["method"] = "tsit5"

@@ -110,3 +110,17 @@ def test_full_size_launch_against_oracle_on_a_strided_row_sample(name, D, C, wid
     # per-row check too: no single row may be far off (a mis-addressed tile would hide in an L2 norm over 1000 rows)
     err = (got.cpu().double() - ref.double()).norm(dim=1) / ref.double().norm(dim=1).clamp_min(1e-3)
     assert float(err.max()) < 20 * TOL, (name, float(err.max()))
+
+
+@pytest.mark.parametrize("sk", [{"film_use_gamma": True}, {"norm": "rms"}])
+def test_wide_nets_without_a_sampler_kernel_sample_through_the_training_forward(sk):
+    """W > 256 with film_use_gamma / norm='rms': no sampler kernel has these options, the training forward does -> the
+    host-driven coverage path (_RunTE) instead of NotImplementedError"""
+    net, orc = make_pair(4, 6, (512,) * 2, **sk)
+    B = 200
+    z, c = torch.randn(B, 4), grouped_conditions(B, 6, 100)
+    assert rel_l2(net.velocity(z.cuda(), 0.4, conditions=c.cuda()), orc.velocity(z, 0.4, c)) < TOL
+    ref = orc.inverse(z, c, method="rk45", steps=4)
+    out = net(z.cuda(), conditions=c.cuda(), inverse=True, method="rk45", steps=4)
+    assert rel_l2(out, ref) < TOL
+    assert net.last_integration_info["path"] == "train-engine"

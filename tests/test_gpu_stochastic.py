@@ -95,8 +95,18 @@ def test_method_errors_and_layerwise_path():
     for m in ("sea", "shark", "langevin"):
         with pytest.raises(ValueError):
             net(z, inverse=True, method=m, steps="adaptive")
-    with pytest.raises(NotImplementedError):
-        net(z, inverse=True, method="langevin", steps=4, target_mask=torch.tensor([1.0, 0.0]), targets_fixed=z)
+    # corrector / langevin with a target mask: the reference's score_fn ignores the mask (diffusion_model.py:845-849)
+    net3, orc3 = make_pair(3, 6, (128,) * 2, dm=True)
+    B = 200
+    zz, c = torch.randn(B, 3), grouped_conditions(B, 6, 100)
+    Z = _normals(40, (B, 3), seed=13)
+    mask, fixed = torch.tensor([1.0, 0.0, 1.0]), torch.tensor([0.0, 0.25, 0.0])
+    for method, kw in (("langevin", {}), ("euler_maruyama", {"corrector_steps": 1})):
+        ref = orc3.inverse(zz, c, method=method, steps=8, noise_fn=lambda i, s: {"xz": Z[i]}, target_mask=mask,
+                           targets_fixed=fixed, **kw)
+        out = net3(zz.cuda(), conditions=c.cuda(), inverse=True, method=method, steps=8, noise_fn=lambda i, shape: Z[i],
+                   target_mask=mask.cuda(), targets_fixed=fixed.cuda(), **kw)
+        assert rel_l2(out, ref) < TOL, (method, rel_l2(out, ref))
     # wide network: the same host loop drives the layer-wise velocity kernels
     netw, orcw = make_pair(12, 5, (512,) * 2, dm=True)
     zz, c = torch.randn(200, 12), grouped_conditions(200, 5, 50)

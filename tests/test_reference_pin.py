@@ -388,6 +388,25 @@ def test_dm_stochastic_samplers_same_noise(R, method, kw, monkeypatch):
     assert rel(x_orc, x_ref) < 5e-5
 
 
+@pytest.mark.parametrize("method,kw", [("euler", {"steps": 6}), ("euler_maruyama", {"steps": 6}), ("langevin", {"steps": 6}),
+                                       ("euler_maruyama", {"steps": 5, "corrector_steps": 1})])
+def test_dm_sampling_with_a_target_mask(R, method, kw, monkeypatch):
+    """diffusion_model.py:793-798 (fixed coordinates start at their targets), :556-557 / :592-593 (masked velocity and
+    diffusion), :845-849 (the score of corrector / langevin ignores the mask)"""
+    import keras
+    ref, orc, _ = pair(R, 3, 5, (32,) * 2, dm=True)
+    z, c = batch(23, 3, 5)
+    g = torch.Generator().manual_seed(77)
+    draws = [torch.randn(23, 3, generator=g) for _ in range(60)]
+    it = iter(draws)
+    monkeypatch.setattr(keras.random, "normal", lambda shape, *a, **k: next(it).reshape(tuple(shape)).clone())
+    mask, fixed = torch.tensor([1.0, 0.0, 1.0]), torch.tensor([0.0, 0.25, 0.0])
+    with torch.no_grad():
+        x_ref = ref(z, conditions=c, inverse=True, method=method, target_mask=mask, targets_fixed=fixed, **kw)
+        x_orc = orc.inverse(z, c, method=method, noise_fn=lambda k, st: {"xz": draws[k]}, target_mask=mask, targets_fixed=fixed, **kw)
+    assert rel(x_orc, x_ref) < 5e-5
+
+
 @pytest.mark.parametrize("sigma,steps,rho", [(1.0, 15, 3.5), (1.3, 7, 3.0), (0.7, 2, 3.5)])  # (steps = 1 fails in the reference: times[1])
 def test_stable_consistency_model_sampling(R, sigma, steps, rho, monkeypatch):
     """StableConsistencyModel (stable_consistency_model.py): consistency function :238-260, time discretisation :111-122 and
