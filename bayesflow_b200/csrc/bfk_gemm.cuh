@@ -450,4 +450,46 @@ __global__ void pack_kmajor_t_kernel(const float* __restrict__ src, long long ld
   *reinterpret_cast<uint4*>(dst + (size_t)idx * 8) = *reinterpret_cast<uint4*>(out);
 }
 
+// Several weight images in ONE launch (the training step re-packs ~25 small matrices every step; as separate launches they
+// are a quarter of the step's launch count).  blockIdx.y = job; the bodies are the two kernels above.
+struct PackJob {
+  const float* src; uint16_t* dst;
+  long long ld, a, b, n;   // t == 0: a = R, b = R_pad;  t == 1: a = Kc_valid, b = Kc;  n = 16-byte outputs of the job
+  int c, d, RT, t;         // t == 0: c = Kc_valid, d = Kc;  t == 1: c = F, d = F_pad
+};
+constexpr int PACK_MAX_JOBS = 68;  // 4 * BFK_MAX_BLOCKS + 4 (needs the > 4 KB kernel-parameter space of CUDA 12.1+)
+struct PackBatch { PackJob j[PACK_MAX_JOBS]; int n; };
+__global__ void pack_batch_kernel(const PackBatch pb) {
+  const PackJob& q = pb.j[blockIdx.y];
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= q.n) return;
+  uint16_t out[8];
+  if (q.t == 0) {
+    const int K8 = q.d / 8;
+    const long long tile = idx / ((long long)K8 * q.RT), rem = idx % ((long long)K8 * q.RT);
+    const int k8 = (int)(rem / q.RT), rin = (int)(rem % q.RT);
+    const long long r = tile * q.RT + rin;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int k = k8 * 8 + i;
+      const float v = (r < q.a && k < q.c) ? q.src[r * q.ld + k] : 0.f;
+      __half h = __float2half_rn(v);
+      out[i] = *reinterpret_cast<uint16_t*>(&h);
+    }
+  } else {
+    const long long K8 = q.b / 8;
+    const long long tile = idx / (K8 * q.RT), rem = idx % (K8 * q.RT);
+    const long long k8 = rem / q.RT;
+    const int f = (int)(tile * q.RT + (int)(rem % q.RT));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const long long k = k8 * 8 + i;
+      const float v = (f < q.c && k < q.a) ? q.src[k * q.ld + f] : 0.f;
+      __half h = __float2half_rn(v);
+      out[i] = *reinterpret_cast<uint16_t*>(&h);
+    }
+  }
+  *reinterpret_cast<uint4*>(q.dst + (size_t)idx * 8) = *reinterpret_cast<uint4*>(out);
+}
+
 }  // namespace bfk

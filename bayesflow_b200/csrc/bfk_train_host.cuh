@@ -173,6 +173,33 @@ int launch_block_bwd(const BlockBwdArgs& a, cudaStream_t st) {
   return 0;
 }
 
+// fp16 weight images of one training step, collected and packed by ONE launch (pack_batch_kernel)
+struct PackList {
+  PackBatch pb{};
+  long long max_n = 0;
+  static long long rup(long long x, long long m) { return (x + m - 1) / m * m; }
+  // bfk_pack_kmajor(src, ld, R, k_valid, k_pad, row_tile) -> dst
+  void add(const float* src, long long ld, long long R, int k_valid, int k_pad, int RT, void* dst) {
+    PackJob& q = pb.j[pb.n++];
+    q.src = src; q.dst = (uint16_t*)dst; q.ld = ld; q.a = R; q.b = rup(R, RT); q.c = k_valid; q.d = k_pad; q.RT = RT; q.t = 0;
+    q.n = q.b * (k_pad / 8);
+    if (q.n > max_n) max_n = q.n;
+  }
+  // bfk_pack_kmajor_t(src, ld, k_valid, k_pad, F, row_tile) -> dst
+  void add_t(const float* src, long long ld, long long k_valid, long long k_pad, int F, int RT, void* dst) {
+    PackJob& q = pb.j[pb.n++];
+    q.src = src; q.dst = (uint16_t*)dst; q.ld = ld; q.a = k_valid; q.b = k_pad; q.c = F; q.d = (int)rup(F, RT); q.RT = RT; q.t = 1;
+    q.n = (long long)q.d * (k_pad / 8);
+    if (q.n > max_n) max_n = q.n;
+  }
+  int launch(cudaStream_t st) {
+    if (pb.n == 0) return 0;
+    pack_batch_kernel<<<dim3((unsigned)((max_n + 255) / 256), (unsigned)pb.n), 256, 0, st>>>(pb);
+    CK(cudaGetLastError());
+    return 0;
+  }
+};
+
 #define GP(p) const_cast<float*>(p) /* `grads` shares the layout of bfk_weights; its tensors are written */
 #define RC(call)            \
   do {                      \
@@ -209,6 +236,27 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   const int KU = b.KU, KT = b.KT, KTN = b.KTN, N1 = b.N1, NO = b.NO, NTW = nt_of(W), NT1 = nt_of(N1);
   const unsigned tchunks = (unsigned)(n_tiles < 64 ? n_tiles : 64);
   const float gs = ta->grad_scale, inv_keep = 1.f / (1.f - ta->dropout);
+  {
+    // every weight image with a buffer of its own, forward and (when gradients are wanted) backward, in one launch; the
+    // images that share a scratch buffer across blocks (FiLM scale, residual projector) and w1 (assembled below) stay inline
+    PackList pl;
+    if ((c->C > 0 ? 2 : 0) + 4 * L + 2 > PACK_MAX_JOBS) return fail(-79, "bfk_train_step: too many blocks for the pack batch");
+    if (b.has_merge) pl.add_t(w->m_k, W, N1, N1, W, NTW, b.wm_f);
+    for (int l = 0; l < L; ++l) {
+      pl.add_t(w->dense_k[l], W, W, W, W, NTW, b.wd_f[l]);
+      pl.add_t(w->film_b_k[l], W, T, KT, W, NTW, b.wb_f[l]);
+    }
+    pl.add_t(w->out_k, D, W, W, D, 64, b.wo_f);
+    if (bwd) {
+      pl.add(w->out_k, D, W, D, NO, NTW, b.wo_b);
+      for (int l = 0; l < L; ++l) {
+        if (T > 1) pl.add(w->film_b_k[l], W, T, W, W, 64, b.wb_b[l]);
+        pl.add(w->dense_k[l], W, W, W, W, NTW, b.wd_b[l]);
+      }
+      if (b.has_merge) pl.add(w->m_k, W, N1, W, W, NT1, b.wm_b);
+    }
+    RC(pl.launch(st));
+  }
 
   // ---- forward ---------------------------------------------------------------------------------------------------
   train_input_kernel<<<(unsigned)((Rp + 127) / 128), 128, 0, st>>>(ta->x, ta->cond, ta->t, w->freq, c->fourier_scale, B, Rp, D, C, T,
@@ -220,7 +268,6 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   RC(bfk_gemm(b.u_img, b.w1_pk, b.h0pre, N1, B, N1, KU, NT1, 1, 0, b.b1, 1.f, P16, st));
   if (b.has_merge) {
     act_pack_kernel<<<dim3(N1 / 8, tchunks), 128, 0, st>>>(b.h0pre, N1, B, n_tiles, N1 / 8, act, b.a1_img, nullptr);
-    RC(bfk_pack_kmajor_t(w->m_k, W, N1, N1, W, NTW, P16, b.wm_f, st));
     RC(bfk_gemm(b.a1_img, b.wm_f, b.m, W, B, W, N1, NTW, 1, 0, w->m_b, 1.f, P16, st));
     act_pack_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.m, W, B, n_tiles, W / 8, act, b.h0_img, b.h0);
   } else {
@@ -228,8 +275,6 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   }
   CK(cudaGetLastError());
   for (int l = 0; l < L; ++l) {
-    RC(bfk_pack_kmajor_t(w->dense_k[l], W, W, W, W, NTW, P16, b.wd_f[l], st));
-    RC(bfk_pack_kmajor_t(w->film_b_k[l], W, T, KT, W, NTW, P16, b.wb_f[l], st));
     RC(bfk_gemm(l == 0 ? b.h0_img : b.h_img[l - 1], b.wd_f[l], b.P[l], W, B, W, W, NTW, 1, 0, w->dense_b[l], 1.f, P16, st));
     RC(bfk_gemm(b.te_img, b.wb_f[l], b.FB, W, B, W, KT, NTW, 1, 0, w->film_b_b[l], 1.f, P16, st));
     if (c->film_use_gamma) {  // FiLM scale to_gamma(t_emb): one more K = T GEMM per block
@@ -254,7 +299,6 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
     a.drop_rate = ta->dropout; a.inv_keep = inv_keep; a.seed = ta->seed; a.seed_dev = ta->seed_dev; a.row0 = ta->row_offset;
     RC(launch_block_fwd(a, st));
   }
-  RC(bfk_pack_kmajor_t(w->out_k, D, W, W, D, 64, P16, b.wo_f, st));
   CK(cudaMemsetAsync(b.bo_pad, 0, (size_t)NO * 4, st));
   CK(cudaMemcpyAsync(b.bo_pad, w->out_b, (size_t)D * 4, cudaMemcpyDeviceToDevice, st));
   RC(bfk_gemm(b.h_img[L - 1], b.wo_f, b.out, NO, B, NO, W, 64, 1, 0, b.bo_pad, 1.f, P16, st));
@@ -270,7 +314,6 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   // ---- backward --------------------------------------------------------------------------------------------------
   const int sw = ta->dw_swap;
   RC(launch_gemm_dw(b.h_img[L - 1], W / 8, b.dout_img, NO / 8, GP(g->out_k), D, W, D, Rp, gs, sw, st));
-  RC(bfk_pack_kmajor(w->out_k, D, W, D, NO, NTW, P16, b.wo_b, st));
   RC(bfk_gemm(b.dout_img, b.wo_b, b.dH, W, B, W, NO, NTW, 1, 0, nullptr, 1.f, P16, st));
   const bool want_dte = T > 1;
   for (int l = L - 1; l >= 0; --l) {
@@ -295,7 +338,6 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
     RC(launch_gemm_dw(b.te_img, KT / 8, b.dV_img, W / 8, GP(g->film_b_k[l]), W, T, W, Rp, gs, sw, st));
     if (c->film_use_gamma) RC(launch_gemm_dw(b.te_img, KT / 8, b.dG_img, W / 8, GP(g->film_g_k[l]), W, T, W, Rp, gs, sw, st));
     if (want_dte) {
-      RC(bfk_pack_kmajor(w->film_b_k[l], W, T, W, W, 64, P16, b.wb_b[l], st));
       RC(bfk_gemm(b.dV_img, b.wb_b[l], b.dte, KTN, B, KTN, W, 64, 1, l == L - 1 ? 0 : GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
       if (c->film_use_gamma) {
         RC(bfk_pack_kmajor(w->film_g_k[l], W, T, W, W, 64, P16, b.wg_b, st));
@@ -304,7 +346,6 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
     }
     if (proj) RC(launch_gemm_dw(l == 0 ? b.h0_img : b.h_img[l - 1], W / 8, b.dV_img, W / 8, GP(g->proj_k[l]), W, W, W, Rp, gs, sw, st));
     if (!c->residual || proj) CK(cudaMemsetAsync(b.dH, 0, (size_t)B * W * 4, st));  // no identity skip into the input
-    RC(bfk_pack_kmajor(w->dense_k[l], W, W, W, W, NTW, P16, b.wd_b[l], st));
     RC(bfk_gemm(b.dP_img, b.wd_b[l], b.dH, W, B, W, W, NTW, 1, GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
     if (proj) {  // the skip's cotangent dV goes back through the projector
       RC(bfk_pack_kmajor(w->proj_k[l], W, W, W, W, NTW, P16, b.wp_b, st));
@@ -315,7 +356,6 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   if (b.has_merge) {
     act_bwd_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.dH, b.m, W, B, n_tiles, W / 8, act, b.dP_img, GP(g->m_b), gs);
     RC(launch_gemm_dw(b.a1_img, N1 / 8, b.dP_img, W / 8, GP(g->m_k), W, N1, W, Rp, gs, sw, st));
-    RC(bfk_pack_kmajor(w->m_k, W, N1, W, W, NT1, P16, b.wm_b, st));
     RC(bfk_gemm(b.dP_img, b.wm_b, b.da1, N1, B, N1, W, NT1, 1, 0, nullptr, 1.f, P16, st));
     act_bwd_kernel<<<dim3(N1 / 8, tchunks), 128, 0, st>>>(b.da1, b.h0pre, N1, B, n_tiles, N1 / 8, act, b.dh0pre_img, b.db1, 1.f);
   } else {

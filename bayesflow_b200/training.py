@@ -318,10 +318,11 @@ class TrainEngine:
     def launches_per_step(self, backward=True):
         """Kernels bfk_train_step enqueues (counted from csrc/bfk_train_host.cuh)."""
         Lb, merge = self.cfg.L, 1 if self.net._C else 0
-        fwd = 2 + 2 + (4 if merge else 1) + 5 * Lb + 2 + 1
+        # one batched weight-pack launch (pack_batch_kernel) replaces the 2 L + 2 forward and 2 L + 2 backward pack launches
+        fwd = 1 + 2 + 2 + (3 if merge else 1) + 3 * Lb + 1 + 1
         if not backward:
             return fwd
-        bwd = 3 + Lb * 7 + (5 if merge else 1) + 3
+        bwd = 2 + Lb * 5 + (4 if merge else 1) + 3
         return fwd + bwd
 
     def interpolate(self, x0, x1, t):
