@@ -21,6 +21,7 @@ struct TrainBufs {
   long long Rp;
   unsigned char *u_img, *te_img, *w1_pk, *a1_img, *wm_f, *wm_b, *h0_img, *wo_f, *wo_b, *dout_img, *dP_img, *dV_img, *dh0pre_img;
   float *w1, *b1, *h0pre, *m, *h0, *FB, *bo_pad, *out, *dH, *dte, *da1, *dW1, *db1;
+  unsigned char *dP_img2, *dV_img2;  // second cotangent-image pair: lets the dW GEMMs of block l overlap block l-1's chain
   float* skip;                      // residual projector output of the current block (unequal widths), (B, W)
   unsigned char *wp_f, *wp_b;       // projector operand images (forward / dX)
   float* FG;                        // film_use_gamma: FiLM scale of the current block (recomputed in the backward)
@@ -90,6 +91,8 @@ void plan_train(const bfk_net_config* c, long long B, bool backward, Arena& ar, 
     b.dH = (float*)ar.take(Bs * W * 4);
     b.dP_img = (unsigned char*)ar.take(Rp * W * 2);
     b.dV_img = (unsigned char*)ar.take(Rp * W * 2);
+    b.dP_img2 = (unsigned char*)ar.take(Rp * W * 2);
+    b.dV_img2 = (unsigned char*)ar.take(Rp * W * 2);
     b.dte = (float*)ar.take(Bs * b.KTN * 4);
     if (b.has_merge) b.da1 = (float*)ar.take(Bs * b.N1 * 4);
     b.dh0pre_img = (unsigned char*)ar.take(Rp * b.N1 * 2);
@@ -171,6 +174,29 @@ int launch_block_bwd(const BlockBwdArgs& a, cudaStream_t st) {
   else { grid = resident_grid(block_bwd_kernel<4>, 256, sh); block_bwd_kernel<4><<<grid, 256, sh, st>>>(a); }
   CK(cudaGetLastError());
   return 0;
+}
+
+// Side stream of the backward pass: the parameter-gradient GEMMs of a block (dW of Dense and FiLM, the time-embedding
+// cotangent) do not feed the next block's chain (block_bwd -> dX GEMM), so they run beside it; fork / join with events,
+// which is also how a stream capture of the step (training.py Trainer, CUDA graph) picks the side stream up.
+struct SideCtx {
+  cudaStream_t s = nullptr;
+  cudaEvent_t main_ev[BFK_MAX_BLOCKS + 1] = {}, side_ev[BFK_MAX_BLOCKS + 1] = {};
+  bool ok = false;
+};
+static SideCtx* side_ctx() {
+  static SideCtx ctx[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  SideCtx& c = ctx[dev];
+  if (!c.ok) {
+    if (cudaStreamCreateWithFlags(&c.s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    for (int i = 0; i <= BFK_MAX_BLOCKS; ++i)
+      if (cudaEventCreateWithFlags(&c.main_ev[i], cudaEventDisableTiming) != cudaSuccess ||
+          cudaEventCreateWithFlags(&c.side_ev[i], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    c.ok = true;
+  }
+  return &c;
 }
 
 // fp16 weight images of one training step, collected and packed by ONE launch (pack_batch_kernel)
@@ -313,14 +339,27 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
 
   // ---- backward --------------------------------------------------------------------------------------------------
   const int sw = ta->dw_swap;
-  RC(launch_gemm_dw(b.h_img[L - 1], W / 8, b.dout_img, NO / 8, GP(g->out_k), D, W, D, Rp, gs, sw, st));
+  // overlap (default block shape only): ss = side stream, else everything stays on st
+  bool ragged_cfg = false;
+  for (int l = 0; l < L; ++l) ragged_cfg = ragged_cfg || (c->block_width[l] != 0);
+  SideCtx* sc = (!c->film_use_gamma && !ragged_cfg && !getenv("BFK_TRAIN_NO_OVERLAP")) ? side_ctx() : nullptr;
+  cudaStream_t ss = sc ? sc->s : st;
+  if (sc) {  // fork: the side stream starts after everything enqueued so far (loss kernel, zeroed gradients)
+    CK(cudaEventRecord(sc->main_ev[L], st));
+    CK(cudaStreamWaitEvent(ss, sc->main_ev[L], 0));
+  }
+  RC(launch_gemm_dw(b.h_img[L - 1], W / 8, b.dout_img, NO / 8, GP(g->out_k), D, W, D, Rp, gs, sw, ss));
   RC(bfk_gemm(b.dout_img, b.wo_b, b.dH, W, B, W, NO, NTW, 1, 0, nullptr, 1.f, P16, st));
   const bool want_dte = T > 1;
   for (int l = L - 1; l >= 0; --l) {
+    // the cotangent images alternate between two buffer pairs; the pair of block l was last read by the side work of l + 2
+    unsigned char* dP_img = (sc && (l & 1)) ? b.dP_img2 : b.dP_img;
+    unsigned char* dV_img = (sc && (l & 1)) ? b.dV_img2 : b.dV_img;
+    if (sc && l + 2 <= L - 1) CK(cudaStreamWaitEvent(st, sc->side_ev[l + 2], 0));
     BlockBwdArgs a{};
     a.dH = b.dH; a.xhat = b.xhat[l]; a.rstd = b.rstd[l]; a.P = b.P[l];
     a.gamma = c->norm != BFK_NORM_NONE ? w->norm_g[l] : nullptr;
-    a.dP_img = b.dP_img; a.dV_img = b.dV_img;
+    a.dP_img = dP_img; a.dV_img = dV_img;
     a.d_gamma = GP(g->norm_g[l]); a.d_beta = c->norm == BFK_NORM_LAYER ? GP(g->norm_b[l]) : nullptr;
     a.d_bd = GP(g->dense_b[l]); a.d_bfilm = GP(g->film_b_b[l]);
     a.B = B; a.R_pad = Rp; a.W = W; a.act = act; a.norm = c->norm; a.layer = l;
@@ -334,24 +373,32 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
       a.FG = b.FG; a.dG_img = b.dG_img; a.d_bgfilm = GP(g->film_g_b[l]);
     }
     RC(launch_block_bwd(a, st));
-    RC(launch_gemm_dw(l == 0 ? b.h0_img : b.h_img[l - 1], W / 8, b.dP_img, W / 8, GP(g->dense_k[l]), W, W, W, Rp, gs, sw, st));
-    RC(launch_gemm_dw(b.te_img, KT / 8, b.dV_img, W / 8, GP(g->film_b_k[l]), W, T, W, Rp, gs, sw, st));
+    if (sc) {
+      CK(cudaEventRecord(sc->main_ev[l], st));
+      CK(cudaStreamWaitEvent(ss, sc->main_ev[l], 0));
+    }
+    RC(launch_gemm_dw(l == 0 ? b.h0_img : b.h_img[l - 1], W / 8, dP_img, W / 8, GP(g->dense_k[l]), W, W, W, Rp, gs, sw, ss));
+    RC(launch_gemm_dw(b.te_img, KT / 8, dV_img, W / 8, GP(g->film_b_k[l]), W, T, W, Rp, gs, sw, ss));
     if (c->film_use_gamma) RC(launch_gemm_dw(b.te_img, KT / 8, b.dG_img, W / 8, GP(g->film_g_k[l]), W, T, W, Rp, gs, sw, st));
     if (want_dte) {
-      RC(bfk_gemm(b.dV_img, b.wb_b[l], b.dte, KTN, B, KTN, W, 64, 1, l == L - 1 ? 0 : GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
+      RC(bfk_gemm(dV_img, b.wb_b[l], b.dte, KTN, B, KTN, W, 64, 1, l == L - 1 ? 0 : GEMM_ADD_EXISTING, nullptr, 1.f, P16, ss));
       if (c->film_use_gamma) {
         RC(bfk_pack_kmajor(w->film_g_k[l], W, T, W, W, 64, P16, b.wg_b, st));
         RC(bfk_gemm(b.dG_img, b.wg_b, b.dte, KTN, B, KTN, W, 64, 1, GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
       }
     }
-    if (proj) RC(launch_gemm_dw(l == 0 ? b.h0_img : b.h_img[l - 1], W / 8, b.dV_img, W / 8, GP(g->proj_k[l]), W, W, W, Rp, gs, sw, st));
+    if (sc) CK(cudaEventRecord(sc->side_ev[l], ss));
+    if (proj) RC(launch_gemm_dw(l == 0 ? b.h0_img : b.h_img[l - 1], W / 8, dV_img, W / 8, GP(g->proj_k[l]), W, W, W, Rp, gs, sw, st));
     if (!c->residual || proj) CK(cudaMemsetAsync(b.dH, 0, (size_t)B * W * 4, st));  // no identity skip into the input
-    RC(bfk_gemm(b.dP_img, b.wd_b[l], b.dH, W, B, W, W, NTW, 1, GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
+    RC(bfk_gemm(dP_img, b.wd_b[l], b.dH, W, B, W, W, NTW, 1, GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
     if (proj) {  // the skip's cotangent dV goes back through the projector
       RC(bfk_pack_kmajor(w->proj_k[l], W, W, W, W, NTW, P16, b.wp_b, st));
-      RC(bfk_gemm(b.dV_img, b.wp_b, b.dH, W, B, W, W, NTW, 1, GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
+      RC(bfk_gemm(dV_img, b.wp_b, b.dH, W, B, W, W, NTW, 1, GEMM_ADD_EXISTING, nullptr, 1.f, P16, st));
     }
   }
+  // join: the input-side backward reuses the first image pair (last read by block 0's or block 1's side work) and the
+  // frequency gradient needs the finished time-embedding cotangent
+  if (sc) CK(cudaStreamWaitEvent(st, sc->side_ev[0], 0));
   CK(cudaMemsetAsync(b.db1, 0, (size_t)N1 * 4, st));
   if (b.has_merge) {
     act_bwd_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.dH, b.m, W, B, n_tiles, W / 8, act, b.dP_img, GP(g->m_b), gs);
