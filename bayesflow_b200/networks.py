@@ -484,8 +484,10 @@ class _RunLW:
 
     # rows per chunk = 16 x 4736: at W = 1024 a chunk is 592 x 4 output tiles per layer = a whole number of waves of the
     # 148 persistent CTAs, and enough tiles per CTA to hide the pipeline fill / last-epilogue tail (r01ae sweep: 439 us
-    # per evaluation per 8192 rows at 8192-row chunks, 300 us at 75776)
-    CHUNK_ROWS = 75776
+    # per evaluation per 8192 rows at 8192-row chunks, 300 us at 75776).  r02 sweep (1M rows, W = 1024, after the
+    # setmaxnreg change): 18,944 rows (L2-resident images) 404 k draws/s, 75,776 426 k, 151,552 446 k, 200 k .. 500 k rows
+    # 451-463 k: fewer, longer launches win over L2 residency (DRAM is not the bound), so 64 x 4736
+    CHUNK_ROWS = 303104
 
     def __init__(self, engine, cond, rpg, target_mask):
         self.e, self.cond, self.rpg = engine, cond, rpg
