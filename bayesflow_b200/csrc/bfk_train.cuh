@@ -16,6 +16,16 @@
 
 namespace bfk {
 
+#ifndef BFK_BWD_MINB
+#define BFK_BWD_MINB 2  // resident CTAs per SM asked of ptxas for the W <= 256 block kernels: 3 / 4 spill and measured
+                        // slower (profiles/r02ab_train_variants.md)
+#endif
+#ifndef BFK_BLOCK_PREFETCH
+#define BFK_BLOCK_PREFETCH 1  // W <= 256 block kernels: next row's streams fetched under this row's reductions
+#endif
+#ifndef BFK_FWD_MINB
+#define BFK_FWD_MINB 3
+#endif
 constexpr float LN_EPS = 1e-3f;  // keras.layers.LayerNormalization default epsilon
 constexpr float RMS_EPS = 1e-6f; // keras.layers.RMSNormalization (ops.rms_normalization): x * rsqrt(mean(x^2) + eps) * scale
 
@@ -57,10 +67,26 @@ __device__ __forceinline__ float t_act(int act, float x, float& d) {
   }
 }
 
+// 8 values at once with the (warp-uniform, run-time) activation switch taken ONCE: inside the unrolled element loop the
+// switch was re-evaluated per element (7 % of block_fwd_kernel's instructions)
+__device__ __forceinline__ void t_act8(int act, const float* x, float* u, float* d) {
+#define BFK_ACT8(A)                                              \
+  _Pragma("unroll") for (int i = 0; i < 8; ++i) u[i] = t_act(A, x[i], d[i]); \
+  break;
+  switch (act) {
+    case BFK_ACT_MISH: BFK_ACT8(BFK_ACT_MISH)
+    case BFK_ACT_SILU: BFK_ACT8(BFK_ACT_SILU)
+    case BFK_ACT_RELU: BFK_ACT8(BFK_ACT_RELU)
+    case BFK_ACT_GELU: BFK_ACT8(BFK_ACT_GELU)
+    default: BFK_ACT8(BFK_ACT_TANH)
+  }
+#undef BFK_ACT8
+}
+
 // Counter-based keep mask for Dropout (conditional_dense_block.py:120-121): identical in forward and backward, a function
 // of (seed, layer, GLOBAL row, column) only, so a data-parallel shard draws the mask of the same rows of the whole batch.
 // The seed and layer are avalanched into a 64-bit key first (splitmix64), so consecutive seeds give unrelated masks; the
-// element index then goes through two multiply-xorshift rounds.
+// index of a column pair then goes through two multiply-xorshift rounds.
 __device__ __forceinline__ unsigned long long drop_key(unsigned long long seed, const uint32_t* seed_dev, int layer) {
   if (seed_dev) seed = ((unsigned long long)seed_dev[1] << 32) | seed_dev[0];  // graph replay: the seed lives in HBM
   unsigned long long z = seed + 0x9E3779B97F4A7C15ull * (unsigned long long)(layer + 1);
@@ -68,12 +94,22 @@ __device__ __forceinline__ unsigned long long drop_key(unsigned long long seed, 
   z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
   return z ^ (z >> 31);
 }
-__device__ __forceinline__ float drop_scale(unsigned long long key, long long row, int col, float rate, float inv_keep) {
-  unsigned long long x = ((unsigned long long)row * 1024ull + (unsigned long long)col) ^ key;
-  x *= 0xD6E8FEB86659FD93ull; x ^= x >> 32;
-  x *= 0xD6E8FEB86659FD93ull; x ^= x >> 32;
-  const float u = (float)((uint32_t)x >> 8) * (1.f / 16777216.f);
-  return u >= rate ? inv_keep : 0.f;
+// Keep scales of the 8 consecutive columns c0 .. c0+7 (c0 a multiple of 8).  One hash serves a PAIR of columns (the top
+// 24 bits of each 32-bit half), and the uniform is compared as an integer: k / 2^24 >= rate  <=>  k >= ceil(rate * 2^24),
+// exact because both sides are exact in fp32.  Per-element hashing with an int->float convert was a third of the
+// instructions of block_fwd_kernel / block_bwd_kernel (profiles/r02aa_train_blocks.md).
+__device__ __forceinline__ void drop_scale8(unsigned long long key, long long row, int c0, float rate, float inv_keep,
+                                            float* ds) {
+  const uint32_t thr = (uint32_t)ceilf(rate * 16777216.f);
+  const unsigned long long base = (unsigned long long)row * 512ull + (unsigned long long)(c0 >> 1);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    unsigned long long x = (base + (unsigned long long)q) ^ key;
+    x *= 0xD6E8FEB86659FD93ull; x ^= x >> 32;
+    x *= 0xD6E8FEB86659FD93ull; x ^= x >> 32;
+    ds[2 * q] = ((uint32_t)x >> 8) >= thr ? inv_keep : 0.f;
+    ds[2 * q + 1] = (uint32_t)(x >> 40) >= thr ? inv_keep : 0.f;
+  }
 }
 
 __device__ __forceinline__ uint32_t h2pack(float a, float b) {
@@ -154,9 +190,10 @@ __global__ void act_pack_kernel(const float* __restrict__ P, long long ld, long 
     float v[8];
     if (r < B) {
       ld8(P + r * ld + k8 * 8, v);
-      float d;
+      float pv[8], d[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) v[i] = t_act(act, v[i], d);
+      for (int i = 0; i < 8; ++i) pv[i] = v[i];
+      t_act8(act, pv, v, d);
       if (out_f32) st8(out_f32 + r * ld + k8 * 8, v);
     } else {
 #pragma unroll
@@ -182,11 +219,11 @@ __global__ void act_bwd_kernel(const float* __restrict__ dY, const float* __rest
       float p[8];
       ld8(P + r * ld + k8 * 8, p);
       ld8(dY + r * ld + k8 * 8, v);
+      float uu[8], d[8];
+      t_act8(act, p, uu, d);
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        float d;
-        t_act(act, p[i], d);
-        v[i] *= d;
+        v[i] *= d[i];
         cs[i] += v[i];
       }
     } else {
@@ -232,12 +269,24 @@ struct BlockFwdArgs {
 };
 
 template <int NJ>
-__global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
+__global__ void __launch_bounds__(256, NJ == 1 ? BFK_FWD_MINB : 1) block_fwd_kernel(const BlockFwdArgs a) {
   const unsigned long long dkey = a.drop_rate > 0.f ? drop_key(a.seed, a.seed_dev, a.layer) : 0ull;
   const int lane = threadIdx.x & 31;
   const long long warp0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
   const int K8 = a.W / 8;
+  // NJ == 1 (W <= 256, the only instantiation launched): the three row streams of the NEXT row are in flight under this
+  // row's two warp reductions and its stores - one row per warp at a time left the kernel at half the HBM rate
+  constexpr bool PF = NJ == 1 && BFK_BLOCK_PREFETCH;
+  float pn[8], fn[8], sn[8];
+  auto fetch = [&](long long rr) {
+    if (PF && lane < K8 && rr < a.B) {
+      ld8(a.P + rr * a.W + lane * 8, pn);
+      ld8(a.FB + rr * a.fb_stride + lane * 8, fn);
+      if (a.prev) ld8(a.prev + rr * a.W + lane * 8, sn);
+    }
+  };
+  fetch(warp0);
   for (long long r = warp0; r < a.R_pad; r += nwarps) {
     if (r >= a.B) {
 #pragma unroll
@@ -255,14 +304,19 @@ __global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
       if (o < K8) {
         const int c0 = o * 8;
         float p[8], f[8];
-        ld8(a.P + r * a.W + c0, p);
-        ld8(a.FB + r * a.fb_stride + c0, f);
+        if (PF) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          float d;
-          float u = t_act(a.act, p[i], d);
-          if (a.drop_rate > 0.f) u *= drop_scale(dkey, a.row0 + r, c0 + i, a.drop_rate, a.inv_keep);
-          v[j][i] = u;
+          for (int i = 0; i < 8; ++i) { p[i] = pn[i]; f[i] = fn[i]; }
+        } else {
+          ld8(a.P + r * a.W + c0, p);
+          ld8(a.FB + r * a.fb_stride + c0, f);
+        }
+        float ds[8], ud[8];
+        if (a.drop_rate > 0.f) drop_scale8(dkey, a.row0 + r, c0, a.drop_rate, a.inv_keep, ds);
+        t_act8(a.act, p, v[j], ud);
+        if (a.drop_rate > 0.f) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[j][i] *= ds[i];
         }
         if (a.FG) {
           float g[8];
@@ -274,7 +328,12 @@ __global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
         for (int i = 0; i < 8; ++i) v[j][i] += f[i];
         if (a.prev) {
           float s[8];
-          ld8(a.prev + r * a.W + c0, s);
+          if (PF) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) s[i] = sn[i];
+          } else {
+            ld8(a.prev + r * a.W + c0, s);
+          }
           if (a.pg) {
             float g[8], b[8];
             ld8(a.pg + c0, g);
@@ -305,6 +364,7 @@ __global__ void __launch_bounds__(256) block_fwd_kernel(const BlockFwdArgs a) {
         for (int i = 0; i < 8; ++i) v[j][i] = 0.f;
       }
     }
+    fetch(r + nwarps);
     float mean = 0.f, rs = 1.f;
     if (a.norm != BFK_NORM_NONE) {  // layer: centred; rms: mean stays 0
       const float we = (float)(a.Weff > 0 ? a.Weff : a.W);
@@ -386,11 +446,13 @@ __global__ void __launch_bounds__(256) block_fwd_wide_kernel(const BlockFwdArgs 
     float v[8];
     float sum = 0.f;
     if (on) {
+      float ds[8], uu[8], ud[8];
+      if (a.drop_rate > 0.f) drop_scale8(dkey, a.row0 + r, c0, a.drop_rate, a.inv_keep, ds);
+      t_act8(a.act, p, uu, ud);
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        float d;
-        float u = t_act(a.act, p[i], d);
-        if (a.drop_rate > 0.f) u *= drop_scale(dkey, a.row0 + r, c0 + i, a.drop_rate, a.inv_keep);
+        float u = uu[i];
+        if (a.drop_rate > 0.f) u *= ds[i];
         v[i] = a.FG ? fmaf(1.f + fg[i], u, f[i]) : u + f[i];  // (1 + gamma) * u + beta, featurewise_linear_modulation.py:25-33
       }
       if (a.prev) {
@@ -493,7 +555,7 @@ struct BlockBwdArgs {
 };
 
 template <int NJ, bool FGAM = false>
-__global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
+__global__ void __launch_bounds__(256, (NJ == 1 && !FGAM) ? BFK_BWD_MINB : 1) block_bwd_kernel(const BlockBwdArgs a) {
   const unsigned long long dkey = a.drop_rate > 0.f ? drop_key(a.seed, a.seed_dev, a.layer) : 0ull;
   extern __shared__ float s_red[];  // [4 (+1 with FGAM)][W]
   const int lane = threadIdx.x & 31;
@@ -512,6 +574,18 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) aq[j][i] = 0.f;
 
+  // NJ == 1: the next row's three streams are fetched under this row's reductions and stores (see block_fwd_kernel);
+  // dH is rewritten in place for row r only, the prefetch reads another row
+  constexpr bool PF = NJ == 1 && BFK_BLOCK_PREFETCH;
+  float ppn[8], dhn[8], xhn[8];
+  auto fetch = [&](long long rr) {
+    if (PF && lane < K8 && rr < a.B) {
+      ld8(a.P + rr * W + lane * 8, ppn);
+      ld8(a.dH + rr * W + lane * 8, dhn);
+      ld8(a.xhat + rr * W + lane * 8, xhn);
+    }
+  };
+  fetch(warp0);
   for (long long r = warp0; r < a.R_pad; r += nwarps) {
     if (r >= a.B) {
 #pragma unroll
@@ -530,7 +604,14 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
 #pragma unroll
     for (int j = 0; j < NJ; ++j) {  // all three streams of this row in flight before the first reduction
       const int o = j * 32 + lane;
-      if (o < K8) ld8(a.P + r * W + o * 8, pp[j]);
+      if (o < K8) {
+        if (PF) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) pp[j][i] = ppn[i];
+        } else {
+          ld8(a.P + r * W + o * 8, pp[j]);
+        }
+      }
     }
 #pragma unroll
     for (int j = 0; j < NJ; ++j) {
@@ -538,8 +619,13 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
       if (o < K8) {
         const int c0 = o * 8;
         float dh[8];
-        ld8(a.dH + r * W + c0, dh);
-        ld8(a.xhat + r * W + c0, xh[j]);
+        if (PF) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { dh[i] = dhn[i]; xh[j][i] = xhn[i]; }
+        } else {
+          ld8(a.dH + r * W + c0, dh);
+          ld8(a.xhat + r * W + c0, xh[j]);
+        }
         if (a.gamma) {
           float gm[8];
           ld8(a.gamma + c0, gm);
@@ -560,6 +646,7 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
         for (int i = 0; i < 8; ++i) g[j][i] = xh[j][i] = 0.f;
       }
     }
+    fetch(r + nwarps);
     float m1 = 0.f, m2 = 0.f, rs = 1.f;
     if (a.norm != BFK_NORM_NONE) {  // rms: no centring, so the m1 term is absent
       const float we = (float)(a.Weff > 0 ? a.Weff : W);
@@ -572,17 +659,18 @@ __global__ void __launch_bounds__(256) block_bwd_kernel(const BlockBwdArgs a) {
       const int o = j * 32 + lane;
       if (o < K8) {
         const int c0 = o * 8;
-        float dv[8], dp[8], dq[8], fg[8];
+        float dv[8], dp[8], dq[8], fg[8], ds[8];
         if (FGAM) ld8(a.FG + r * W + c0, fg);
+        if (a.drop_rate > 0.f) drop_scale8(dkey, a.row0 + r, c0, a.drop_rate, a.inv_keep, ds);
+        float uu[8], ud[8];
+        t_act8(a.act, pp[j], uu, ud);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           dv[i] = a.norm != BFK_NORM_NONE ? rs * (g[j][i] - m1 - xh[j][i] * m2) : g[j][i];
-          float d;
-          float u = t_act(a.act, pp[j][i], d);
+          float d = ud[i], u = uu[i];
           if (a.drop_rate > 0.f) {
-            const float ds = drop_scale(dkey, a.row0 + r, c0 + i, a.drop_rate, a.inv_keep);
-            d *= ds;
-            u *= ds;
+            d *= ds[i];
+            u *= ds[i];
           }
           if (FGAM) {  // v = skip + (1 + FG) u + FB:  dU = dV (1 + FG),  dFG = dV u
             dq[i] = dv[i] * u;

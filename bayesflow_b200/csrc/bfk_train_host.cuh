@@ -485,6 +485,37 @@ extern "C" int bfk_train_vjp(const bfk_net_config* c, const bfk_weights* w, cons
   return 0;
 }
 
+// The keep scales (0 or 1/(1-rate)) block `layer` of bfk_train_step multiplies its activation with, for rows
+// row_offset .. row_offset+B-1 and columns 0 .. W-1: makes the counter-based mask observable (tests/test_gpu_train.py
+// restates the hash in numpy and checks the statistics).  Same device function as the block kernels.
+namespace bfk {
+__global__ void drop_mask_kernel(unsigned long long seed, const uint32_t* seed_dev, int layer, long long row0, long long B, int W,
+                                 float rate, float inv_keep, float* __restrict__ out) {
+  const unsigned long long key = drop_key(seed, seed_dev, layer);
+  const int K8 = W / 8;
+  const long long n = B * K8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / K8;
+    const int c0 = (int)(i % K8) * 8;
+    float ds[8];
+    drop_scale8(key, row0 + r, c0, rate, inv_keep, ds);
+    st8(out + r * W + c0, ds);
+  }
+}
+}  // namespace bfk
+extern "C" int bfk_train_dropout_mask(uint64_t seed, const uint32_t* seed_dev, int32_t layer, int64_t row_offset, int64_t B,
+                                      int32_t W, float rate, float* out, void* stream) {
+  if (!out || B < 0 || W <= 0 || (W % 8) != 0 || W > 1024 || layer < 0 || !(rate >= 0.f) || !(rate < 1.f))
+    return fail(-87, "bfk_train_dropout_mask: bad arguments (W a multiple of 8 <= 1024, 0 <= rate < 1)");
+  if (B == 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long n = (long long)B * (W / 8);
+  const unsigned grid = (unsigned)std::min<long long>((n + 255) / 256, 148 * 8);
+  bfk::drop_mask_kernel<<<grid, 256, 0, st>>>(seed, seed_dev, layer, row_offset, B, W, rate, 1.f / (1.f - rate), out);
+  CK(cudaGetLastError());
+  return 0;
+}
+
 // Host-side evaluation of the same double-precision schedule algebra the evaluation tables use (density path of
 // DiffusionModel: velocity = coefZ*z + coefP*pred, so trace(dv/dz) = D*coefZ + coefP*trace(dpred/dz)).
 extern "C" int bfk_schedule_coefs(const bfk_schedule* sched, double t, double* coefZ, double* coefP, double* net_time) {

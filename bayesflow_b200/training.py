@@ -49,8 +49,24 @@ def _bind(L):
                                 C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     L.bfk_rk_combine.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_float, C.c_int64, C.c_void_p,
                                  C.c_void_p]
+    L.bfk_train_dropout_mask.argtypes = [C.c_uint64, C.c_void_p, C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_float,
+                                         C.c_void_p, C.c_void_p]
     L._train_bound = True
     return L
+
+
+def dropout_mask(seed, layer, rows, width, rate, row_offset=0, device="cuda"):
+    """The keep scales (0 or 1/(1-rate)) `bfk_train_step` applies in block `layer` for global rows
+    row_offset .. row_offset+rows-1 (`bfk_train_dropout_mask`): a counter-based function of (seed, layer, row, column)."""
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise RuntimeError("dropout_mask runs on a CUDA device (there is no CPU path)")
+    L = _bind(_lib.lib())
+    out = torch.empty(rows, width, device=dev, dtype=torch.float32)
+    with torch.cuda.device(dev):
+        _lib.check(L.bfk_train_dropout_mask(int(seed), None, int(layer), int(row_offset), int(rows), int(width),
+                                            float(rate), _lib.ptr(out), _lib.stream_ptr()), "bfk_train_dropout_mask")
+    return out
 
 
 def fill_weights(net, get):

@@ -197,6 +197,12 @@ size_t bfk_train_workspace_bytes(const bfk_net_config* cfg, int64_t B, int32_t b
 int bfk_train_step(const bfk_net_config* cfg, const bfk_weights* weights, const bfk_weights* grads,
                    const bfk_train_args* args, float* loss, float* pred_out, void* workspace, size_t workspace_bytes,
                    void* stream);
+/* The Dropout keep scales bfk_train_step applies in block `layer` (0-based) for global rows row_offset .. row_offset+B-1:
+ * out (B,W) of 0 or 1/(1-rate).  Keras draws its mask from the backend RNG (conditional_dense_block.py:120-121, not
+ * reproducible across backends); here it is a counter-based function of (seed, layer, global row, column) so that forward,
+ * backward and every data-parallel shard agree.  Exposed for tests and for users who want the mask of a step. */
+int bfk_train_dropout_mask(uint64_t seed, const uint32_t* seed_dev, int32_t layer, int64_t row_offset, int64_t B, int32_t W,
+                           float rate, float* out, void* stream);
 /* Vector-Jacobian product of the velocity network w.r.t. its input, for the density path
  * (FlowMatching._velocity_trace, flow_matching.py:238-252 -> utils/jacobian/jacobian_trace.py:10-55 -> utils/jacobian/vjp.py:44-68;
  * the reference runs D torch.autograd.grad passes per evaluation).  Consumes the activations the preceding

@@ -135,6 +135,92 @@ def test_dropout_is_a_training_only_inverted_mask():
     assert l_a == pytest.approx(l_b, rel=1e-5) and l_a != l_eval and l_a != l_c
 
 
+def _np_drop_mask(seed, layer, row0, B, W, rate):
+    """numpy restatement of drop_key / drop_scale8 (bfk_train.cuh): splitmix64 key, two multiply-xorshift rounds per
+    column PAIR, the top 24 bits of each half against ceil(rate * 2^24)."""
+    import numpy as np
+    M64 = (1 << 64) - 1
+    z = (seed + 0x9E3779B97F4A7C15 * (layer + 1)) & M64
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & M64
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & M64
+    key = np.uint64(z ^ (z >> 31))
+    rows = np.arange(row0, row0 + B, dtype=np.uint64)[:, None]
+    pairs = np.arange(W // 2, dtype=np.uint64)[None, :]
+    with np.errstate(over="ignore"):
+        x = (rows * np.uint64(512) + pairs) ^ key
+        for _ in range(2):
+            x = x * np.uint64(0xD6E8FEB86659FD93)
+            x ^= x >> np.uint64(32)
+    thr = int(math.ceil(float(np.float32(rate)) * 16777216.0))
+    lo = ((x & np.uint64(0xFFFFFFFF)) >> np.uint64(8)).astype(np.int64)
+    hi = (x >> np.uint64(40)).astype(np.int64)
+    keep = np.empty((B, W), dtype=bool)
+    keep[:, 0::2] = lo >= thr
+    keep[:, 1::2] = hi >= thr
+    return keep
+
+
+@pytest.mark.parametrize("rate,W", [(0.05, 256), (0.3, 128), (0.5, 8)])
+def test_hidden_dropout_mask_is_the_documented_counter_hash_and_bernoulli(rate, W):
+    """conditional_dense_block.py:120-121 (keras Dropout: Bernoulli(1 - rate) keep, inverted scaling).  The kernel's mask
+    is bit-equal to the numpy restatement of its hash, has the right keep rate per column and per row parity, is
+    uncorrelated between the two columns that share a hash and between neighbouring rows, and a shard reproduces the
+    rows of the whole batch."""
+    import numpy as np
+    from bayesflow_b200.training import dropout_mask
+    B, row0 = 60_000, 123_456_789
+    m = dropout_mask(seed=7, layer=2, rows=B, width=W, rate=rate, row_offset=row0)
+    scale = float(np.float32(1.0) / (np.float32(1.0) - np.float32(rate)))
+    vals = sorted(m.unique().tolist())
+    assert len(vals) == 2 and vals[0] == 0.0 and vals[1] == pytest.approx(scale, rel=1e-6)
+    keep = (m > 0).cpu().numpy()
+    assert np.array_equal(keep, _np_drop_mask(7, 2, row0, B, W, rate))
+    p = 1.0 - rate
+    se = math.sqrt(p * (1 - p) / B)
+    assert np.abs(keep.mean(0) - p).max() < 5.5 * se                            # every column
+    assert abs(keep.mean() - p) < 5 * se / math.sqrt(W)
+    k = keep.astype(np.float64) - p
+    var = p * (1 - p)
+    n = k[:, 0::2].size
+    assert abs((k[:, 0::2] * k[:, 1::2]).mean() / var) < 5 / math.sqrt(n)       # the two halves of one hash
+    assert abs((k[:-1] * k[1:]).mean() / var) < 5 / math.sqrt(k[1:].size)       # neighbouring rows
+    assert abs((k[:, :-1] * k[:, 1:]).mean() / var) < 5 / math.sqrt(k[:, 1:].size)
+    # other layer / other seed: unrelated masks
+    for other in (dropout_mask(7, 3, B, W, rate, row0), dropout_mask(8, 2, B, W, rate, row0)):
+        o = (other > 0).cpu().numpy().astype(np.float64) - p
+        assert abs((k * o).mean() / var) < 5 / math.sqrt(k.size)
+    part = dropout_mask(7, 2, 100, W, rate, row_offset=row0 + 31_000)
+    assert torch.equal(part, m[31_000:31_100])
+
+
+def test_hidden_dropout_mask_is_the_one_the_training_step_uses():
+    """Loss and every parameter gradient of a training step WITH hidden Dropout against the oracle run with the exported
+    masks (oracle/networks.py `dropout_masks`): the mask entry point returns what the forward AND backward kernels use."""
+    from bayesflow_b200.training import dropout_mask
+    D, C, B, W, rate = 2, 4, 700, 128, 0.25
+    net, orc = make_pair(D, C, (W,) * 2, dropout=rate)
+    tup, c = make_batch(B, D, C)
+    masks = [dropout_mask(seed=21, layer=l, rows=B, width=W, rate=rate).cpu() for l in range(2)]
+    ps = {k: v.clone().requires_grad_(True) for k, v in orc.p.items()}
+    orc.p = orc.subnet.p = ps
+    ref_loss = orc.compute_metrics(tup, conditions=c, stage="training", dropout_masks=masks)["loss"]
+    loss = net.compute_metrics(cuda_tuple(tup), conditions=c.cuda(), stage="training", seed=21)["loss"]
+    ref, got = float(ref_loss), float(loss)
+    assert abs(got - ref) <= 2e-3 * abs(ref), (got, ref)
+    ref_loss.backward()
+    loss.backward()  # the backward kernels regenerate the same mask
+    checked = 0
+    for name, p in net.named_parameters():
+        if name in ps and ps[name].grad is not None:
+            tol = 5e-3 if name.endswith("time_emb.frequencies") else TOL
+            assert rel_l2(p.grad, ps[name].grad) < tol, (name, rel_l2(p.grad, ps[name].grad))
+            checked += 1
+    assert checked >= 10
+    with torch.no_grad():
+        other = float(net.compute_metrics(cuda_tuple(tup), conditions=c.cuda(), stage="training", seed=22)["loss"])
+    assert abs(other - ref) > 1e-4 * abs(ref)
+
+
 def test_adam_step_matches_keras_formula():
     """keras Adam with per-variable clipnorm (basic_workflow.py:524) restated in torch fp64 on the same gradients."""
     from bayesflow_b200.training import Adam, train_engine
