@@ -496,9 +496,12 @@ class Trainer:
             dev = eng.device
             g = {"x": torch.empty_like(x, dtype=torch.float32),
                  "c": None if conditions is None else torch.empty_like(conditions, dtype=torch.float32),
-                 # device words the kernels read: [0:2] seed (lo, hi), [2:4] lr_t, wd*lr; one pinned host mirror, one copy a step
+                 # device words the kernels read: [0:2] seed (lo, hi), [2:4] lr_t, wd*lr; one copy a step from a RING of
+                 # pinned host rows - the copy is asynchronous, so a row is rewritten only after the copy that read it has
+                 # run (one shared row let a host that runs ahead of the GPU hand many steps the same seed / lr)
                  "params": torch.zeros(4, device=dev, dtype=torch.float32),
-                 "host": torch.zeros(4, dtype=torch.float32).pin_memory()}
+                 "host": torch.zeros(self.HOST_RING, 4, dtype=torch.float32).pin_memory(),
+                 "host_ev": [None] * self.HOST_RING, "slot": 0}
             g["seed_dev"], g["hyper_dev"] = g["params"][0:2], g["params"][2:4]
 
             def body():
@@ -543,11 +546,21 @@ class Trainer:
         net._engine._key = None  # parameters changed in place: the sampler must re-pack its weight blob
         return g["loss"]
 
+    HOST_RING = 32  # steps the host may run ahead of the GPU before `_refresh` waits for a pinned row to be free
+
     def _refresh(self, g):
         seed = self._step_seed()
         lr_t, wd_lr = self.opt.hyper()
-        words = g["host"].view(torch.int32)
+        slot = g["slot"]
+        g["slot"] = (slot + 1) % self.HOST_RING
+        if g["host_ev"][slot] is not None:
+            g["host_ev"][slot].synchronize()  # the copy that last read this row has completed
+        row = g["host"][slot]
+        words = row.view(torch.int32)
         for i, w in enumerate((seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)):
             words[i] = w - (1 << 32) if w >= (1 << 31) else w
-        g["host"][2], g["host"][3] = lr_t, wd_lr
-        g["params"].copy_(g["host"], non_blocking=True)
+        row[2], row[3] = lr_t, wd_lr
+        g["params"].copy_(row, non_blocking=True)
+        if g["host_ev"][slot] is None:
+            g["host_ev"][slot] = torch.cuda.Event()
+        g["host_ev"][slot].record()
