@@ -144,11 +144,14 @@ __device__ __forceinline__ void st8(float* p, const float* v) {
 __global__ void train_input_kernel(const float* __restrict__ x, const float* __restrict__ cond, const float* __restrict__ t,
                                    const float* __restrict__ freq, float fscale, long long B, long long R_pad, int D, int C,
                                    int T, int KU8, int KT8, unsigned char* __restrict__ u_img, unsigned char* __restrict__ te_img) {
+  // grid (row blocks, KU8 + KT8): one 8-column group of one row per thread (one thread per ROW left a 8192-row shard
+  // with 64 CTAs each walking ~70 columns serially)
   const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= R_pad) return;
   const bool valid = r < B;
-  for (int k8 = 0; k8 < KU8; ++k8) {
-    float v[8];
+  int k8 = blockIdx.y;
+  float v[8];
+  if (k8 < KU8) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int k = k8 * 8 + i;
@@ -160,25 +163,24 @@ __global__ void train_input_kernel(const float* __restrict__ x, const float* __r
       v[i] = e;
     }
     *reinterpret_cast<uint4*>(u_img + img_off(r, k8, KU8)) = pack8(v);
+    return;
   }
+  k8 -= KU8;
   const float tt = valid ? t[r] : 0.f;
   const int Th = (T - 1) / 2;
-  for (int k8 = 0; k8 < KT8; ++k8) {
-    float v[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int k = k8 * 8 + i;
-      float e = 0.f;
-      if (valid) {
-        if (T == 1) e = k == 0 ? tt : 0.f;
-        else if (k == 0) e = tt;
-        else if (k <= Th) e = sinf(tt * freq[k - 1] * 2.f * 3.14159265358979323846f * fscale);
-        else if (k < T) e = cosf(tt * freq[k - 1 - Th] * 2.f * 3.14159265358979323846f * fscale);
-      }
-      v[i] = e;
+  for (int i = 0; i < 8; ++i) {
+    const int k = k8 * 8 + i;
+    float e = 0.f;
+    if (valid) {
+      if (T == 1) e = k == 0 ? tt : 0.f;
+      else if (k == 0) e = tt;
+      else if (k <= Th) e = sinf(tt * freq[k - 1] * 2.f * 3.14159265358979323846f * fscale);
+      else if (k < T) e = cosf(tt * freq[k - 1 - Th] * 2.f * 3.14159265358979323846f * fscale);
     }
-    *reinterpret_cast<uint4*>(te_img + img_off(r, k8, KT8)) = pack8(v);
+    v[i] = e;
   }
+  *reinterpret_cast<uint4*>(te_img + img_off(r, k8, KT8)) = pack8(v);
 }
 
 // out = act(P): packed image (+ optional fp32 copy).  grid (K8, chunks), 128 threads = the rows of one 128-row tile.
@@ -688,31 +690,39 @@ __global__ void __launch_bounds__(256, (NJ == 1 && !FGAM) ? BFK_BWD_MINB : 1) bl
       }
     }
   }
+  if (!a.d_bd) return;  // cotangent-only pass (bfk_train_vjp): no parameter gradients
+  // column sums across the CTA's warps: the warps take turns on s_red (no shared float atomics: those are CAS loops, and
+  // 8 warps on one address cost ~6 us per CTA - a third of the kernel on a 8192-row shard).  Column c = o*8 + i lives at
+  // [i*K8 + o], so a warp's 32 lanes touch consecutive words.
+  for (int wv = 0; wv < (int)(blockDim.x >> 5); ++wv) {
+    if ((int)(threadIdx.x >> 5) == wv) {
 #pragma unroll
-  for (int j = 0; j < NJ; ++j) {
-    const int o = j * 32 + lane;
-    if (o < K8) {
+      for (int j = 0; j < NJ; ++j) {
+        const int o = j * 32 + lane;
+        if (o < K8) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int c = o * 8 + i;
-        if (a.gamma) { atomicAdd(&s_red[c], ag[j][i]); atomicAdd(&s_red[W + c], ab[j][i]); }
-        atomicAdd(&s_red[2 * W + c], ad[j][i]);
-        atomicAdd(&s_red[3 * W + c], af[j][i]);
-        if (FGAM) atomicAdd(&s_red[4 * W + c], aq[j][i]);
+          for (int i = 0; i < 8; ++i) {
+            const int c = i * K8 + o;
+            if (a.gamma) { s_red[c] += ag[j][i]; s_red[W + c] += ab[j][i]; }
+            s_red[2 * W + c] += ad[j][i];
+            s_red[3 * W + c] += af[j][i];
+            if (FGAM) s_red[4 * W + c] += aq[j][i];
+          }
+        }
       }
     }
+    __syncthreads();
   }
-  __syncthreads();
-  if (!a.d_bd) return;  // cotangent-only pass (bfk_train_vjp): no parameter gradients
   for (int c = threadIdx.x; c < W; c += blockDim.x) {
+    const int sc = (c & 7) * K8 + (c >> 3);
     if (a.gamma) {
-      atomicAdd(a.d_gamma + c, a.gscale * s_red[c]);
-      if (a.d_beta) atomicAdd(a.d_beta + c, a.gscale * s_red[W + c]);
+      atomicAdd(a.d_gamma + c, a.gscale * s_red[sc]);
+      if (a.d_beta) atomicAdd(a.d_beta + c, a.gscale * s_red[W + sc]);
     }
-    atomicAdd(a.d_bd + c, a.gscale * s_red[2 * W + c]);
-    atomicAdd(a.d_bfilm + c, a.gscale * s_red[3 * W + c]);
-    if (a.d_bskip) atomicAdd(a.d_bskip + c, a.gscale * s_red[3 * W + c]);
-    if (FGAM && a.d_bgfilm) atomicAdd(a.d_bgfilm + c, a.gscale * s_red[4 * W + c]);
+    atomicAdd(a.d_bd + c, a.gscale * s_red[2 * W + sc]);
+    atomicAdd(a.d_bfilm + c, a.gscale * s_red[3 * W + sc]);
+    if (a.d_bskip) atomicAdd(a.d_bskip + c, a.gscale * s_red[3 * W + sc]);
+    if (FGAM && a.d_bgfilm) atomicAdd(a.d_bgfilm + c, a.gscale * s_red[4 * W + sc]);
   }
 }
 
@@ -756,7 +766,10 @@ __global__ void loss_kernel(const float* __restrict__ pred, long long ldp, const
             g = wv * av * res / rt;
           }
           else { lrow = fmaf(res, res, lrow); g = 2.f * wv * av * res; }
-          atomicAdd(&s_db[k], g);
+        }
+        if (d_bo && k < D) {  // (uniform) one shared atomic per warp and column: 256 threads on one address is a CAS storm
+          const float gs = warp_sum(g);
+          if ((threadIdx.x & 31) == 0) atomicAdd(&s_db[k], gs);
         }
         v[i] = g;
       }
@@ -775,23 +788,23 @@ __global__ void loss_kernel(const float* __restrict__ pred, long long ldp, const
 __global__ void freq_bwd_kernel(const float* __restrict__ dte, long long ld, const float* __restrict__ t,
                                 const float* __restrict__ freq, float fscale, long long B, int Th, float* __restrict__ dfreq,
                                 float gscale) {
-  __shared__ float s[32];
-  if (threadIdx.x < 32) s[threadIdx.x] = 0.f;
+  // grid (row blocks, Th): one frequency per blockIdx.y
+  __shared__ float s;
+  if (threadIdx.x == 0) s = 0.f;
   __syncthreads();
   const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const float c = 2.f * 3.14159265358979323846f * fscale;
-  for (int j = 0; j < Th; ++j) {
-    float g = 0.f;
-    if (r < B) {
-      const float tt = t[r];
-      const float p = tt * freq[j] * 2.f * 3.14159265358979323846f * fscale;
-      g = tt * c * (dte[r * ld + 1 + j] * cosf(p) - dte[r * ld + 1 + Th + j] * sinf(p));
-    }
-    g = warp_sum(g);
-    if ((threadIdx.x & 31) == 0) atomicAdd(&s[j], g);
+  const int j = blockIdx.y;
+  float g = 0.f;
+  if (r < B) {
+    const float tt = t[r];
+    const float p = tt * freq[j] * 2.f * 3.14159265358979323846f * fscale;
+    g = tt * c * (dte[r * ld + 1 + j] * cosf(p) - dte[r * ld + 1 + Th + j] * sinf(p));
   }
+  g = warp_sum(g);
+  if ((threadIdx.x & 31) == 0) atomicAdd(&s, g);
   __syncthreads();
-  if (threadIdx.x < Th) atomicAdd(dfreq + threadIdx.x, gscale * s[threadIdx.x]);
+  if (threadIdx.x == 0) atomicAdd(dfreq + j, gscale * s);
 }
 
 // First layer as ONE contraction over u = [x | c]:  concat: W1 = blockdiag(Wx, Wc) (KU x 2W), b1 = [bx, bc];
@@ -941,6 +954,7 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
     const float nrm = sqrtf(sq[s]);
     if (nrm > clipnorm) clip = clipnorm / nrm;
   }
+#pragma unroll 4
   for (long long i = a + blockIdx.y * blockDim.x + threadIdx.x; i < b; i += (long long)gridDim.y * blockDim.x) {
     const float gi = g[i] * clip;
     const float mi = m[i] + (gi - m[i]) * (1.f - b1);

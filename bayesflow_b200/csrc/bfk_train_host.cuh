@@ -285,7 +285,7 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   }
 
   // ---- forward ---------------------------------------------------------------------------------------------------
-  train_input_kernel<<<(unsigned)((Rp + 127) / 128), 128, 0, st>>>(ta->x, ta->cond, ta->t, w->freq, c->fourier_scale, B, Rp, D, C, T,
+  train_input_kernel<<<dim3((unsigned)((Rp + 127) / 128), (unsigned)(KU / 8 + KT / 8)), 128, 0, st>>>(ta->x, ta->cond, ta->t, w->freq, c->fourier_scale, B, Rp, D, C, T,
                                                                  KU / 8, KT / 8, b.u_img, b.te_img);
   build_w1_kernel<<<cdiv((size_t)KU * N1, 256), 256, 0, st>>>(w->x_k, w->x_b, w->c_k, w->c_b, D, C, W, b.has_merge ? c->merge : 0, KU, N1,
                                                              b.w1, b.b1);
@@ -413,8 +413,8 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   RC(launch_gemm_dw(b.u_img, KU / 8, b.dh0pre_img, N1 / 8, b.dW1, N1, D + C, N1, Rp, 1.f, sw, st));
   scatter_w1_grad_kernel<<<cdiv((size_t)(D + C) * W, 256), 256, 0, st>>>(b.dW1, b.db1, D, C, W, b.has_merge ? c->merge : 0, N1, gs,
                                                                         GP(g->x_k), GP(g->x_b), GP(g->c_k), GP(g->c_b));
-  if (want_dte && GP(g->freq))
-    freq_bwd_kernel<<<(unsigned)((B + 255) / 256), 256, 0, st>>>(b.dte, KTN, ta->t, w->freq, c->fourier_scale, B, (T - 1) / 2, GP(g->freq), gs);
+  if (want_dte && GP(g->freq) && T > 1)
+    freq_bwd_kernel<<<dim3((unsigned)((B + 255) / 256), (unsigned)((T - 1) / 2)), 256, 0, st>>>(b.dte, KTN, ta->t, w->freq, c->fourier_scale, B, (T - 1) / 2, GP(g->freq), gs);
   CK(cudaGetLastError());
   return 0;
 }
@@ -574,9 +574,9 @@ static int adam_step_impl(float* params, const float* grads, float* m, float* v,
   static_assert(sizeof(long long) == sizeof(int64_t), "");
   if (clipnorm > 0.f) {
     CK(cudaMemsetAsync(seg_sqnorm, 0, (size_t)n_seg * 4, st));
-    seg_sqnorm_kernel<<<dim3(n_seg, 16), 256, 0, st>>>(grads, (const long long*)seg_offsets, n_seg, seg_sqnorm);
+    seg_sqnorm_kernel<<<dim3(n_seg, 64), 256, 0, st>>>(grads, (const long long*)seg_offsets, n_seg, seg_sqnorm);
   }
-  adam_kernel<<<dim3(n_seg, 16), 256, 0, st>>>(params, grads, m, v, (const long long*)seg_offsets, seg_sqnorm, clipnorm, lr_t, beta1,
+  adam_kernel<<<dim3(n_seg, 64), 256, 0, st>>>(params, grads, m, v, (const long long*)seg_offsets, seg_sqnorm, clipnorm, lr_t, beta1,
                                               beta2, eps, wd_lr, hyper_dev);
   CK(cudaGetLastError());
   return 0;
