@@ -154,8 +154,13 @@ def integrate_density(fn, state, start_time=None, stop_time=None, min_steps: int
         if start_time is None or stop_time is None:
             raise ValueError("Please provide start_time and stop_time for the integration, was "
                              f"'start_time={start_time}', 'stop_time={stop_time}'.")
-        if method == "scipy":
-            raise NotImplementedError("method='scipy' runs the network on the host; outside the accelerated path")
+        if method == "scipy":  # integrate.py:409-452: keys flattened and concatenated in order (xz, trace)
+            from .integrate import _warn_scipy_step_args, solve_ivp_flat
+            _warn_scipy_step_args(min_steps, max_steps)
+            out, res = solve_ivp_flat(lambda t, xz, tr: fn(t, xz), list(state), start_time, stop_time)
+            if info is not None:
+                info.update({"nfev": int(res.nfev), "steps": int(res.t.shape[0]) - 1})
+            return tuple(out)
         return _integrate_adaptive(fn, state, float(start_time), float(stop_time), int(min_steps), int(max_steps), method,
                                    info, atol=kwargs.get("atol", 1e-6), rtol=kwargs.get("rtol", 1e-4), group=group)
     if isinstance(steps, (int, np.integer)) and not isinstance(steps, bool):

@@ -270,15 +270,48 @@ def integrate_adaptive(fn, state, start_time, stop_time, min_steps, max_steps, m
     return state
 
 
+def integrate_scipy(fn, state, start_time, stop_time, scipy_kwargs=None, info=None):
+    # integrate.py:409-452.  The reference's Adapter().concatenate(keys, into="x", axis=-1).convert_dtype(float32, float64)
+    # is: every key flattened, concatenated in key order, float64 on the way to scipy and float32 on the way back.
+    import scipy.integrate
+    scipy_kwargs = scipy_kwargs or {}
+    keys = list(state.keys())
+    shapes = {k: tuple(torch.as_tensor(state[k]).shape) for k in keys}
+    sizes = {k: int(np.prod(shapes[k])) for k in keys}
+
+    def state_to_vector(st):
+        return np.concatenate([torch.as_tensor(st[k]).detach().cpu().numpy().reshape(-1) for k in keys],
+                              axis=-1).astype(np.float32).astype(np.float64)
+
+    def vector_to_state(x):
+        out, o = {}, 0
+        for k in keys:
+            out[k] = torch.from_numpy(np.ascontiguousarray(x[o:o + sizes[k]].astype(np.float32))).reshape(shapes[k])
+            o += sizes[k]
+        return out
+
+    def scipy_wrapper_fn(time, x):
+        st = vector_to_state(x)
+        time = torch.tensor(time, dtype=torch.float32)
+        return state_to_vector(fn(time, **st))
+
+    result = scipy.integrate.solve_ivp(scipy_wrapper_fn, (start_time, stop_time), state_to_vector(state), **scipy_kwargs)
+    if info is not None:
+        info["steps"], info["evals"] = int(result.t.shape[0]) - 1, int(result.nfev)
+    return vector_to_state(result.y[:, -1])
+
+
 def integrate(fn, state, start_time=None, stop_time=None, min_steps=50, max_steps=10_000, steps=100, method="rk45",
               **kwargs):
-    # integrate.py:455-489 (scipy branch omitted: out of scope)
+    # integrate.py:455-489
     if isinstance(steps, str) and steps in ["adaptive", "dynamic"]:
         if start_time is None or stop_time is None:
             raise ValueError(
                 "Please provide start_time and stop_time for the integration, was "
                 f"'start_time={start_time}', 'stop_time={stop_time}'."
             )
+        if method == "scipy":  # :473-478 (the two "has no effect" warnings are log lines only)
+            return integrate_scipy(fn, state, start_time, stop_time, info=kwargs.get("info"))
         return integrate_adaptive(fn, state, start_time, stop_time, min_steps, max_steps, method, **kwargs)
     elif isinstance(steps, int):
         if start_time is None or stop_time is None:

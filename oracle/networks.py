@@ -137,6 +137,10 @@ def count_flops_per_eval(D, C, widths, T=33):
 
 
 # --------------------------------------------------------------------------------------------------------------
+# integrate.py STOCHASTIC_METHODS (diffusion_model.py:733, 805, 830 test membership in THIS list, so method="scipy"
+# takes the ODE branch)
+_STOCHASTIC = ("euler_maruyama", "sea", "shark", "two_step_adaptive", "langevin")
+
 class OracleTimeMLP:
     def __init__(self, params, *, widths, time_embedding_dim=32, fourier_scale=30.0, activation="mish", residual=True,
                  dropout=0.0, norm="layer", merge="concat", film_use_gamma=False, **_):
@@ -543,7 +547,7 @@ class OracleDiffusionModel:
     def forward(self, x, conditions=None, density=False, **kwargs):
         # diffusion_model.py:719-780
         ik = {"start_time": 0.0, "stop_time": 1.0} | self.integrate_kwargs | kwargs
-        if ik["method"] not in ("euler", "rk45", "tsit5"):
+        if ik["method"] in _STOCHASTIC:
             ik["method"] = "tsit5"  # :733-739
         ik = {k: v for k, v in ik.items() if k in self._IK}
         if density:
@@ -563,11 +567,11 @@ class OracleDiffusionModel:
             tm = torch.broadcast_to(kwargs["target_mask"], z.shape)
             z = _mask(z, tm, torch.broadcast_to(kwargs["targets_fixed"], z.shape))
         if density:
-            if ik["method"] not in ("euler", "rk45", "tsit5"):
+            if ik["method"] in _STOCHASTIC:
                 ik["method"] = "tsit5"
             x, trace = self._density_integrate(z, conditions, ik)
             return x, self.base_distribution.log_prob(z) - trace
-        if ik["method"] not in ("euler", "rk45", "tsit5"):
+        if ik["method"] in _STOCHASTIC:
             # SDE branch, diffusion_model.py:830-856
             from .integrate import integrate_stochastic
 

@@ -59,6 +59,29 @@ def test_flow_matching_log_prob(method, steps):
         assert abs(net.last_integration_info["steps"] - info["steps"]) <= max(2, 0.1 * info["steps"])
 
 
+@pytest.mark.parametrize("dm", [False, True])
+def test_scipy_method_sampling_and_log_prob(dm):
+    """method="scipy" (utils/integrate.py:409-452, dispatcher :473-478): scipy's RK45 controller on the host over the whole
+    flattened batch, every right-hand side through the velocity / trace kernels.  Against the oracle's restatement (pinned
+    on the reference, tests/test_reference_pin.py); the tolerance is the solver's own rtol = 1e-3 regime, since an fp16
+    operand perturbation may move an accepted step."""
+    net, orc = make_pair(2, 6, (128,) * 2, dm=dm)
+    x, c = _data(150, 2, 6)
+    z = torch.randn(150, 2, generator=torch.Generator().manual_seed(8))
+    info = {}
+    x_ref = orc.inverse(z, c, method="scipy", steps="adaptive", info=info)
+    got = net(z.cuda(), conditions=c.cuda(), inverse=True, method="scipy", steps="adaptive")
+    assert rel_l2(got, x_ref) < 5e-3, rel_l2(got, x_ref)
+    li = net.last_integration_info
+    assert li["path"] == "scipy" and abs(li["evals"] - info["evals"]) <= max(12, 0.2 * info["evals"]), (li, info)
+    # and close to the built-in adaptive solver at tight tolerances
+    tight = net(z.cuda(), conditions=c.cuda(), inverse=True, method="rk45", steps="adaptive", atol=1e-7, rtol=1e-6)
+    assert rel_l2(got, tight) < 1e-2
+    z_ref, lp_ref = orc.forward(x, c, density=True, method="scipy", steps="adaptive")
+    zz, lp = net(x.cuda(), conditions=c.cuda(), density=True, method="scipy", steps="adaptive")
+    assert rel_l2(zz, z_ref) < 5e-3 and rel_l2(lp, lp_ref) < 5e-3, (rel_l2(zz, z_ref), rel_l2(lp, lp_ref))
+
+
 def test_flow_matching_inverse_density_and_scheduled_steps():
     net, orc = make_pair(3, None, (128,) * 2)
     z, _ = _data(150, 3, None)

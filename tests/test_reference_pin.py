@@ -188,6 +188,67 @@ def test_adaptive_sampling_same_step_sequence(R, method, kw):
         assert counts[1] > 0, "this case is meant to exercise rejected trial steps"
 
 
+class _ConcatAdapter:
+    """Test stand-in for bayesflow.adapters.Adapter as integrate_scipy uses it (integrate.py:422): concatenate the keys
+    along the last axis into one entry and convert float32 <-> float64; forward / inverse on dicts of numpy arrays.  (The
+    adapter package is numpy-only bookkeeping outside the hot path; its two transforms are restated here, every other
+    line of integrate_scipy - flattening, key order, the solve_ivp call and its defaults, the float32 time, the last
+    column of the solution - is the reference's own code.)"""
+
+    def concatenate(self, keys, into, axis=-1):
+        self.keys, self.into, self.axis = list(keys), into, axis
+        return self
+
+    def convert_dtype(self, from_dtype, to_dtype):
+        self.from_dtype, self.to_dtype = from_dtype, to_dtype
+        return self
+
+    def forward(self, data):
+        import numpy as np
+        parts = [np.asarray(data[k]) for k in self.keys]
+        self.sizes = [p.shape[self.axis] for p in parts]
+        return {self.into: np.concatenate(parts, axis=self.axis).astype(self.to_dtype)}
+
+    def inverse(self, data):
+        import numpy as np
+        x = np.asarray(data[self.into]).astype(self.from_dtype)
+        out, o = {}, 0
+        for k, n in zip(self.keys, self.sizes):
+            out[k] = x[..., o:o + n]
+            o += n
+        return out
+
+
+@pytest.mark.parametrize("dm", [False, True])
+def test_scipy_method_same_solution_and_evaluation_count(R, monkeypatch, dm):
+    """integrate(..., steps="adaptive", method="scipy") -> integrate_scipy (utils/integrate.py:409-452, dispatcher
+    :473-478) through FlowMatching._inverse / _forward: the oracle's restatement makes the same solve_ivp call, so the
+    solutions agree to round-off and the number of right-hand-side evaluations is identical."""
+    monkeypatch.setitem(R.integrate.__globals__, "Adapter", _ConcatAdapter)
+    ref, orc, _ = pair(R, 2, 6, (64,) * 2, dm=dm)   # DM: "scipy" is not in STOCHASTIC_METHODS -> ODE branch (:830, 857-866)
+    z, c = batch(19, 2, 6)
+    calls = {"n": 0}
+    orig = ref.velocity
+
+    def counting(*a, **k):
+        calls["n"] += 1
+        return orig(*a, **k)
+
+    monkeypatch.setattr(ref, "velocity", counting)
+    with torch.no_grad():
+        x_ref = ref(z, conditions=c, inverse=True, method="scipy", steps="adaptive")
+        n_inv = calls["n"]
+        info = {}
+        x_orc = orc.inverse(z, c, method="scipy", steps="adaptive", info=info)
+        assert info["evals"] == n_inv and n_inv > 10
+        assert rel(x_orc, x_ref) < 2e-5
+        z_ref = ref(x_ref, conditions=c, inverse=False, method="scipy", steps="adaptive")
+        z_orc = orc.forward(x_ref, c, method="scipy", steps="adaptive")
+        assert rel(z_orc, z_ref) < 2e-5
+        if not dm:
+            assert rel(z_ref, z) < 2e-2      # round trip at scipy's default rtol = 1e-3
+
+
 def _ref_loss_and_grads(ref, fn):
     ws = ref.subnet.weights + ref.output_projector.weights
     for w in ws:
