@@ -183,68 +183,86 @@ __global__ void train_input_kernel(const float* __restrict__ x, const float* __r
   *reinterpret_cast<uint4*>(te_img + img_off(r, k8, KT8)) = pack8(v);
 }
 
-// out = act(P): packed image (+ optional fp32 copy).  grid (K8, chunks), 128 threads = the rows of one 128-row tile.
-__global__ void act_pack_kernel(const float* __restrict__ P, long long ld, long long B, long long n_tiles, int K8, int act,
-                                unsigned char* __restrict__ img, float* __restrict__ out_f32) {
-  const int k8 = blockIdx.x;
-  for (long long tile = blockIdx.y; tile < n_tiles; tile += gridDim.y) {
-    const long long r = tile * 128 + threadIdx.x;
-    float v[8];
-    if (r < B) {
-      ld8(P + r * ld + k8 * 8, v);
-      float pv[8], d[8];
+// act(P) -> packed fp16 image (+ optional fp32 copy).  One WARP per row, a lane per 8 columns: the row is read as one
+// contiguous kilobyte (thread == row read 32 lanes x 32 B spread over 32 KB and ran at a third of the HBM rate).
+__global__ void __launch_bounds__(256) act_pack_kernel(const float* __restrict__ P, long long ld, long long B, long long R_pad,
+                                                       int K8, int act, unsigned char* __restrict__ img,
+                                                       float* __restrict__ out_f32) {
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long r = warp0; r < R_pad; r += nwarps) {
+    for (int o = lane; o < K8; o += 32) {
+      float v[8];
+      if (r < B) {
+        float pv[8], d[8];
+        ld8(P + r * ld + o * 8, pv);
+        t_act8(act, pv, v, d);
+        if (out_f32) st8(out_f32 + r * ld + o * 8, v);
+      } else {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) pv[i] = v[i];
-      t_act8(act, pv, v, d);
-      if (out_f32) st8(out_f32 + r * ld + k8 * 8, v);
-    } else {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) v[i] = 0.f;
+        for (int i = 0; i < 8; ++i) v[i] = 0.f;
+      }
+      *reinterpret_cast<uint4*>(img + img_off(r, o, K8)) = pack8(v);
     }
-    *reinterpret_cast<uint4*>(img + img_off(r, k8, K8)) = pack8(v);
   }
 }
 
-// dP = dY * act'(P): packed image, column sums of dP -> bias gradient (scaled).  Same grid as act_pack_kernel.
-__global__ void act_bwd_kernel(const float* __restrict__ dY, const float* __restrict__ P, long long ld, long long B,
-                               long long n_tiles, int K8, int act, unsigned char* __restrict__ img, float* __restrict__ dbias,
-                               float gscale) {
-  __shared__ float red[4][8];
-  const int k8 = blockIdx.x;
-  float cs[8];
+// dP = dY * act'(P): packed image, column sums of dP -> bias gradient (scaled).  Same row-per-warp form; NJ = columns / 256.
+template <int NJ>
+__global__ void __launch_bounds__(256) act_bwd_kernel(const float* __restrict__ dY, const float* __restrict__ P, long long ld,
+                                                      long long B, long long R_pad, int K8, int act,
+                                                      unsigned char* __restrict__ img, float* __restrict__ dbias, float gscale) {
+  extern __shared__ float s_cs[];  // [K8 * 8], column c = o*8 + i at [i*K8 + o]
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
+  float cs[NJ][8];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) cs[i] = 0.f;
-  for (long long tile = blockIdx.y; tile < n_tiles; tile += gridDim.y) {
-    const long long r = tile * 128 + threadIdx.x;
-    float v[8];
-    if (r < B) {
-      float p[8];
-      ld8(P + r * ld + k8 * 8, p);
-      ld8(dY + r * ld + k8 * 8, v);
-      float uu[8], d[8];
-      t_act8(act, p, uu, d);
+  for (int j = 0; j < NJ; ++j)
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        v[i] *= d[i];
-        cs[i] += v[i];
+    for (int i = 0; i < 8; ++i) cs[j][i] = 0.f;
+  for (long long r = warp0; r < R_pad; r += nwarps) {
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+      const int o = j * 32 + lane;
+      if (o < K8) {
+        float v[8];
+        if (r < B) {
+          float p[8], uu[8], d[8];
+          ld8(P + r * ld + o * 8, p);
+          ld8(dY + r * ld + o * 8, v);
+          t_act8(act, p, uu, d);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            v[i] *= d[i];
+            cs[j][i] += v[i];
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = 0.f;
+        }
+        *reinterpret_cast<uint4*>(img + img_off(r, o, K8)) = pack8(v);
       }
-    } else {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) v[i] = 0.f;
     }
-    *reinterpret_cast<uint4*>(img + img_off(r, k8, K8)) = pack8(v);
   }
-  if (dbias) {
+  if (!dbias) return;
+  for (int i = threadIdx.x; i < K8 * 8; i += blockDim.x) s_cs[i] = 0.f;
+  __syncthreads();
+  for (int wv = 0; wv < (int)(blockDim.x >> 5); ++wv) {  // the warps take turns (no shared float atomics)
+    if ((int)(threadIdx.x >> 5) == wv) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) cs[i] = warp_sum(cs[i]);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (lane == 0) {
+      for (int j = 0; j < NJ; ++j) {
+        const int o = j * 32 + lane;
+        if (o < K8) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) red[warp][i] = cs[i];
+          for (int i = 0; i < 8; ++i) s_cs[i * K8 + o] += cs[j][i];
+        }
+      }
     }
     __syncthreads();
-    if (threadIdx.x < 8) atomicAdd(dbias + k8 * 8 + threadIdx.x, gscale * (red[0][threadIdx.x] + red[1][threadIdx.x] + red[2][threadIdx.x] + red[3][threadIdx.x]));
   }
+  for (int c = threadIdx.x; c < K8 * 8; c += blockDim.x) atomicAdd(dbias + c, gscale * s_cs[(c & 7) * K8 + (c >> 3)]);
 }
 
 // ---------------------------------------------------------------------------------------------------------------

@@ -147,6 +147,34 @@ unsigned resident_grid(K kernel, int threads, size_t smem) {
   int sms = bfk_num_sms();
   return (unsigned)((sms > 0 ? sms : 148) * per_sm);
 }
+static unsigned row_grid(unsigned resident, long long rows) {  // 8 row-warps per CTA; no more CTAs than rows need
+  const long long need = (rows + 7) / 8;
+  return (unsigned)(need < (long long)resident ? (need < 1 ? 1 : need) : resident);
+}
+int launch_act_pack(const float* P, long long ld, long long B, long long Rp, int K8, int act, unsigned char* img, float* out_f32,
+                    cudaStream_t st) {
+  static unsigned res = 0;
+  if (!res) res = resident_grid(act_pack_kernel, 256, 0);
+  act_pack_kernel<<<row_grid(res, Rp), 256, 0, st>>>(P, ld, B, Rp, K8, act, img, out_f32);
+  CK(cudaGetLastError());
+  return 0;
+}
+int launch_act_bwd(const float* dY, const float* P, long long ld, long long B, long long Rp, int K8, int act, unsigned char* img,
+                   float* dbias, float gscale, cudaStream_t st) {
+  const int nj = (K8 + 31) / 32;
+  const size_t sh = (size_t)K8 * 8 * 4;
+  if (nj > 8) return fail(-79, "bfk_train_step: first-layer width above 2048 columns");
+#define BFK_ACT_BWD(NJ)                                                                                         \
+  {                                                                                                              \
+    static unsigned res = 0;                                                                                     \
+    if (!res) res = resident_grid(act_bwd_kernel<NJ>, 256, 8192);                                                \
+    act_bwd_kernel<NJ><<<row_grid(res, Rp), 256, sh, st>>>(dY, P, ld, B, Rp, K8, act, img, dbias, gscale);       \
+  }
+  if (nj == 1) BFK_ACT_BWD(1) else if (nj == 2) BFK_ACT_BWD(2) else if (nj <= 4) BFK_ACT_BWD(4) else BFK_ACT_BWD(8)
+#undef BFK_ACT_BWD
+  CK(cudaGetLastError());
+  return 0;
+}
 int launch_block_fwd(const BlockFwdArgs& a, cudaStream_t st) {
   const int nj = (a.W / 8 + 31) / 32;
   static unsigned grid[3] = {0, 0, 0};
@@ -258,9 +286,8 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   TrainBufs b{};
   plan_train(c, B, bwd, ar, b);
   if (ar.off > workspace_bytes) return fail(-79, "bfk_train_step: workspace too small (bfk_train_workspace_bytes)");
-  const long long Rp = b.Rp, n_tiles = Rp / 128;
+  const long long Rp = b.Rp;
   const int KU = b.KU, KT = b.KT, KTN = b.KTN, N1 = b.N1, NO = b.NO, NTW = nt_of(W), NT1 = nt_of(N1);
-  const unsigned tchunks = (unsigned)(n_tiles < 64 ? n_tiles : 64);
   const float gs = ta->grad_scale, inv_keep = 1.f / (1.f - ta->dropout);
   {
     // every weight image with a buffer of its own, forward and (when gradients are wanted) backward, in one launch; the
@@ -293,11 +320,11 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   RC(bfk_pack_kmajor_t(b.w1, N1, D + C, KU, N1, NT1, P16, b.w1_pk, st));
   RC(bfk_gemm(b.u_img, b.w1_pk, b.h0pre, N1, B, N1, KU, NT1, 1, 0, b.b1, 1.f, P16, st));
   if (b.has_merge) {
-    act_pack_kernel<<<dim3(N1 / 8, tchunks), 128, 0, st>>>(b.h0pre, N1, B, n_tiles, N1 / 8, act, b.a1_img, nullptr);
+    RC(launch_act_pack(b.h0pre, N1, B, Rp, N1 / 8, act, b.a1_img, nullptr, st));
     RC(bfk_gemm(b.a1_img, b.wm_f, b.m, W, B, W, N1, NTW, 1, 0, w->m_b, 1.f, P16, st));
-    act_pack_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.m, W, B, n_tiles, W / 8, act, b.h0_img, b.h0);
+    RC(launch_act_pack(b.m, W, B, Rp, W / 8, act, b.h0_img, b.h0, st));
   } else {
-    act_pack_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.h0pre, W, B, n_tiles, W / 8, act, b.h0_img, b.h0);
+    RC(launch_act_pack(b.h0pre, W, B, Rp, W / 8, act, b.h0_img, b.h0, st));
   }
   CK(cudaGetLastError());
   for (int l = 0; l < L; ++l) {
@@ -401,12 +428,12 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   if (sc) CK(cudaStreamWaitEvent(st, sc->side_ev[0], 0));
   CK(cudaMemsetAsync(b.db1, 0, (size_t)N1 * 4, st));
   if (b.has_merge) {
-    act_bwd_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.dH, b.m, W, B, n_tiles, W / 8, act, b.dP_img, GP(g->m_b), gs);
+    RC(launch_act_bwd(b.dH, b.m, W, B, Rp, W / 8, act, b.dP_img, GP(g->m_b), gs, st));
     RC(launch_gemm_dw(b.a1_img, N1 / 8, b.dP_img, W / 8, GP(g->m_k), W, N1, W, Rp, gs, sw, st));
     RC(bfk_gemm(b.dP_img, b.wm_b, b.da1, N1, B, N1, W, NT1, 1, 0, nullptr, 1.f, P16, st));
-    act_bwd_kernel<<<dim3(N1 / 8, tchunks), 128, 0, st>>>(b.da1, b.h0pre, N1, B, n_tiles, N1 / 8, act, b.dh0pre_img, b.db1, 1.f);
+    RC(launch_act_bwd(b.da1, b.h0pre, N1, B, Rp, N1 / 8, act, b.dh0pre_img, b.db1, 1.f, st));
   } else {
-    act_bwd_kernel<<<dim3(N1 / 8, tchunks), 128, 0, st>>>(b.dH, b.h0pre, N1, B, n_tiles, N1 / 8, act, b.dh0pre_img, b.db1, 1.f);
+    RC(launch_act_bwd(b.dH, b.h0pre, N1, B, Rp, N1 / 8, act, b.dh0pre_img, b.db1, 1.f, st));
   }
   CK(cudaGetLastError());
   CK(cudaMemsetAsync(b.dW1, 0, (size_t)KU * N1 * 4, st));
@@ -437,9 +464,8 @@ extern "C" int bfk_train_vjp(const bfk_net_config* c, const bfk_weights* w, cons
   TrainBufs b{};
   plan_train(c, B, true, ar, b);
   if (ar.off > workspace_bytes) return fail(-79, "bfk_train_vjp: workspace too small (bfk_train_workspace_bytes, backward=1)");
-  const long long Rp = b.Rp, n_tiles = Rp / 128;
+  const long long Rp = b.Rp;
   const int N1 = b.N1, NO = b.NO, NTW = nt_of(W), NT1 = nt_of(N1);
-  const unsigned tchunks = (unsigned)(n_tiles < 64 ? n_tiles : 64);
   cotangent_pack_kernel<<<(unsigned)((Rp + 127) / 128), 128, 0, st>>>(dout, col, B, Rp, D, NO / 8, b.dout_img);
   CK(cudaGetLastError());
   // wo_b / wd_b / wm_b: the MN-major weight images; packed here so the pass does not depend on an earlier backward
@@ -470,12 +496,12 @@ extern "C" int bfk_train_vjp(const bfk_net_config* c, const bfk_weights* w, cons
     }
   }
   if (b.has_merge) {
-    act_bwd_kernel<<<dim3(W / 8, tchunks), 128, 0, st>>>(b.dH, b.m, W, B, n_tiles, W / 8, act, b.dP_img, nullptr, 1.f);
+    RC(launch_act_bwd(b.dH, b.m, W, B, Rp, W / 8, act, b.dP_img, nullptr, 1.f, st));
     RC(bfk_pack_kmajor(w->m_k, W, N1, W, W, NT1, P16, b.wm_b, st));
     RC(bfk_gemm(b.dP_img, b.wm_b, b.da1, N1, B, N1, W, NT1, 1, 0, nullptr, 1.f, P16, st));
-    act_bwd_kernel<<<dim3(N1 / 8, tchunks), 128, 0, st>>>(b.da1, b.h0pre, N1, B, n_tiles, N1 / 8, act, b.dh0pre_img, nullptr, 1.f);
+    RC(launch_act_bwd(b.da1, b.h0pre, N1, B, Rp, N1 / 8, act, b.dh0pre_img, nullptr, 1.f, st));
   } else {
-    act_bwd_kernel<<<dim3(N1 / 8, tchunks), 128, 0, st>>>(b.dH, b.h0pre, N1, B, n_tiles, N1 / 8, act, b.dh0pre_img, nullptr, 1.f);
+    RC(launch_act_bwd(b.dH, b.h0pre, N1, B, Rp, N1 / 8, act, b.dh0pre_img, nullptr, 1.f, st));
   }
   CK(cudaGetLastError());
   const unsigned gb = (unsigned)((B + 127) / 128);
