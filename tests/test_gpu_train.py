@@ -193,11 +193,12 @@ def test_hidden_dropout_mask_is_the_documented_counter_hash_and_bernoulli(rate, 
     assert torch.equal(part, m[31_000:31_100])
 
 
-def test_hidden_dropout_mask_is_the_one_the_training_step_uses():
+@pytest.mark.parametrize("W", [128, 512, 1024])   # block_fwd_kernel<1> / block_fwd_wide_kernel<2> / <4> and their backward twins
+def test_hidden_dropout_mask_is_the_one_the_training_step_uses(W):
     """Loss and every parameter gradient of a training step WITH hidden Dropout against the oracle run with the exported
     masks (oracle/networks.py `dropout_masks`): the mask entry point returns what the forward AND backward kernels use."""
     from bayesflow_b200.training import dropout_mask
-    D, C, B, W, rate = 2, 4, 700, 128, 0.25
+    D, C, B, rate = 2, 4, 700, 0.25
     net, orc = make_pair(D, C, (W,) * 2, dropout=rate)
     tup, c = make_batch(B, D, C)
     masks = [dropout_mask(seed=21, layer=l, rows=B, width=W, rate=rate).cpu() for l in range(2)]
