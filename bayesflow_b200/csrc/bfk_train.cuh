@@ -744,6 +744,131 @@ __global__ void __launch_bounds__(256, (NJ == 1 && !FGAM) ? BFK_BWD_MINB : 1) bl
   }
 }
 
+// Wide rows (W > 256) without film_use_gamma: block_bwd_kernel<4> keeps 4 x 32 column accumulators per lane (255
+// registers, ONE 8-warp CTA per SM) and ran at 44 % of the HBM rate.  Here a row is shared by CW warps (CW * 256 columns),
+// each lane owns ONE octet like the W <= 256 kernel (two CTAs per SM), and the two row sums of the norm backward cross the
+// warps through shared memory and one named barrier per row (double-buffered slots).  Same arithmetic as
+// block_bwd_kernel; rows of a CTA: 8 / CW at a time.
+template <int CW>
+__global__ void __launch_bounds__(256, 2) block_bwd_split_kernel(const BlockBwdArgs a) {
+  const unsigned long long dkey = a.drop_rate > 0.f ? drop_key(a.seed, a.seed_dev, a.layer) : 0ull;
+  extern __shared__ float s_red[];  // [4][W]
+  constexpr int RG = 8 / CW;        // row groups (rows in flight) per CTA
+  __shared__ float2 s_part[2][RG][CW];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int rg = warp / CW, cw = warp % CW;
+  const int K8 = a.W / 8, W = a.W;
+  const int o = cw * 32 + lane;
+  const bool on = o < K8;
+  const int c0 = o * 8;
+  for (int i = threadIdx.x; i < 4 * W; i += blockDim.x) s_red[i] = 0.f;
+  __syncthreads();
+  float ag[8], ab[8], ad[8], af[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) ag[i] = ab[i] = ad[i] = af[i] = 0.f;
+  const long long grp0 = (long long)blockIdx.x * RG + rg, ngrp = (long long)gridDim.x * RG;
+  float ppn[8], dhn[8], xhn[8];
+  auto fetch = [&](long long rr) {
+    if (on && rr < a.B) {
+      ld8(a.P + rr * W + c0, ppn);
+      ld8(a.dH + rr * W + c0, dhn);
+      ld8(a.xhat + rr * W + c0, xhn);
+    }
+  };
+  fetch(grp0);
+  float gm[8];
+  if (a.gamma && on) ld8(a.gamma + c0, gm);
+  uint32_t it = 0;
+  for (long long r = grp0; r < a.R_pad; r += ngrp) {
+    if (r >= a.B) {  // (uniform over the row's warps)
+      if (on) {
+        *reinterpret_cast<uint4*>(a.dP_img + img_off(r, o, K8)) = make_uint4(0, 0, 0, 0);
+        *reinterpret_cast<uint4*>(a.dV_img + img_off(r, o, K8)) = make_uint4(0, 0, 0, 0);
+      }
+      continue;
+    }
+    float g[8], xh[8], pp[8];
+    float s1 = 0.f, s2 = 0.f;
+    if (on) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        pp[i] = ppn[i];
+        xh[i] = xhn[i];
+        const float dh = dhn[i];
+        if (a.gamma) {
+          ag[i] = fmaf(dh, xh[i], ag[i]);
+          ab[i] += dh;
+          g[i] = dh * gm[i];
+        } else {
+          g[i] = dh;
+        }
+        s1 += g[i];
+        s2 = fmaf(g[i], xh[i], s2);
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) g[i] = xh[i] = pp[i] = 0.f;
+    }
+    fetch(r + ngrp);
+    float m1 = 0.f, m2 = 0.f, rs = 1.f;
+    if (a.norm != BFK_NORM_NONE) {
+      s1 = warp_sum(s1);
+      s2 = warp_sum(s2);
+      const uint32_t slot = it & 1;
+      if (lane == 0) s_part[slot][rg][cw] = make_float2(s1, s2);
+      asm volatile("bar.sync %0, %1;" ::"r"(1 + rg), "r"(CW * 32) : "memory");
+      float t1 = 0.f, t2 = 0.f;
+#pragma unroll
+      for (int q = 0; q < CW; ++q) { const float2 pq = s_part[slot][rg][q]; t1 += pq.x; t2 += pq.y; }
+      const float we = (float)(a.Weff > 0 ? a.Weff : W);
+      if (a.norm == BFK_NORM_LAYER) m1 = t1 / we;
+      m2 = t2 / we;
+      rs = a.rstd[r];
+      ++it;
+    }
+    if (on) {
+      float dv[8], dp[8], ds[8], uu[8], ud[8];
+      if (a.drop_rate > 0.f) drop_scale8(dkey, a.row0 + r, c0, a.drop_rate, a.inv_keep, ds);
+      t_act8(a.act, pp, uu, ud);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        dv[i] = a.norm != BFK_NORM_NONE ? rs * (g[i] - m1 - xh[i] * m2) : g[i];
+        float d = ud[i];
+        if (a.drop_rate > 0.f) d *= ds[i];
+        dp[i] = dv[i] * d;
+        ad[i] += dp[i];
+        af[i] += dv[i];
+      }
+      st8(a.dH + r * W + c0, dv);
+      *reinterpret_cast<uint4*>(a.dP_img + img_off(r, o, K8)) = pack8(dp);
+      *reinterpret_cast<uint4*>(a.dV_img + img_off(r, o, K8)) = pack8(dv);
+    }
+  }
+  if (!a.d_bd) return;  // cotangent-only pass (bfk_train_vjp)
+  for (int wv = 0; wv < RG; ++wv) {  // the row groups take turns on s_red; the CW warps of a group own disjoint columns
+    if (rg == wv && on) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int c = i * K8 + o;
+        if (a.gamma) { s_red[c] += ag[i]; s_red[W + c] += ab[i]; }
+        s_red[2 * W + c] += ad[i];
+        s_red[3 * W + c] += af[i];
+      }
+    }
+    __syncthreads();
+  }
+  for (int c = threadIdx.x; c < W; c += blockDim.x) {
+    const int sc = (c & 7) * K8 + (c >> 3);
+    if (a.gamma) {
+      atomicAdd(a.d_gamma + c, a.gscale * s_red[sc]);
+      if (a.d_beta) atomicAdd(a.d_beta + c, a.gscale * s_red[W + sc]);
+    }
+    atomicAdd(a.d_bd + c, a.gscale * s_red[2 * W + sc]);
+    atomicAdd(a.d_bfilm + c, a.gscale * s_red[3 * W + sc]);
+    if (a.d_bskip) atomicAdd(a.d_bskip + c, a.gscale * s_red[3 * W + sc]);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // Loss head.  resid = a_b*pred - target;  loss_b = w_b * mean_i resid^2 (mse) | mean_i |resid| (mae)
 //   | mean_i (sqrt(resid^2 + c^2) - c) (kind 2, pseudo-Huber: ConsistencyModel, consistency_model.py:413-414 with

@@ -198,8 +198,15 @@ int launch_block_bwd(const BlockBwdArgs& a, cudaStream_t st) {
     else if (nj == 2) { grid = resident_grid(block_bwd_kernel<2, true>, 256, sh); block_bwd_kernel<2, true><<<grid, 256, sh, st>>>(a); }
     else { grid = resident_grid(block_bwd_kernel<4, true>, 256, sh); block_bwd_kernel<4, true><<<grid, 256, sh, st>>>(a); }
   } else if (nj == 1) { grid = resident_grid(block_bwd_kernel<1>, 256, sh); block_bwd_kernel<1><<<grid, 256, sh, st>>>(a); }
-  else if (nj == 2) { grid = resident_grid(block_bwd_kernel<2>, 256, sh); block_bwd_kernel<2><<<grid, 256, sh, st>>>(a); }
-  else { grid = resident_grid(block_bwd_kernel<4>, 256, sh); block_bwd_kernel<4><<<grid, 256, sh, st>>>(a); }
+  else {
+    // W > 256: a row shared by 2 / 4 warps (block_bwd_split_kernel); BFK_BWD_SPLIT=0 keeps the one-warp-per-row kernel
+    static int split = -1;
+    if (split < 0) { const char* e = getenv("BFK_BWD_SPLIT"); split = e ? atoi(e) : 1; }
+    if (split && nj == 2) { grid = resident_grid(block_bwd_split_kernel<2>, 256, sh); block_bwd_split_kernel<2><<<grid, 256, sh, st>>>(a); }
+    else if (split) { grid = resident_grid(block_bwd_split_kernel<4>, 256, sh); block_bwd_split_kernel<4><<<grid, 256, sh, st>>>(a); }
+    else if (nj == 2) { grid = resident_grid(block_bwd_kernel<2>, 256, sh); block_bwd_kernel<2><<<grid, 256, sh, st>>>(a); }
+    else { grid = resident_grid(block_bwd_kernel<4>, 256, sh); block_bwd_kernel<4><<<grid, 256, sh, st>>>(a); }
+  }
   CK(cudaGetLastError());
   return 0;
 }
