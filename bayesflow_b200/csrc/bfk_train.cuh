@@ -192,18 +192,29 @@ __global__ void __launch_bounds__(256) act_pack_kernel(const float* __restrict__
   const long long warp0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
   for (long long r = warp0; r < R_pad; r += nwarps) {
-    for (int o = lane; o < K8; o += 32) {
-      float v[8];
-      if (r < B) {
-        float pv[8], d[8];
-        ld8(P + r * ld + o * 8, pv);
-        t_act8(act, pv, v, d);
-        if (out_f32) st8(out_f32 + r * ld + o * 8, v);
-      } else {
+    for (int ob = 0; ob < K8; ob += 128) {  // up to 4 octets per lane with all their loads in flight first
+      float pv[4][8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) v[i] = 0.f;
+      for (int q = 0; q < 4; ++q) {
+        const int o = ob + q * 32 + lane;
+        if (o < K8 && r < B) ld8(P + r * ld + o * 8, pv[q]);
       }
-      *reinterpret_cast<uint4*>(img + img_off(r, o, K8)) = pack8(v);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int o = ob + q * 32 + lane;
+        if (o < K8) {
+          float v[8];
+          if (r < B) {
+            float d[8];
+            t_act8(act, pv[q], v, d);
+            if (out_f32) st8(out_f32 + r * ld + o * 8, v);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = 0.f;
+          }
+          *reinterpret_cast<uint4*>(img + img_off(r, o, K8)) = pack8(v);
+        }
+      }
     }
   }
 }
