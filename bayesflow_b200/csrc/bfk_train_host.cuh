@@ -609,7 +609,7 @@ static int adam_step_impl(float* params, const float* grads, float* m, float* v,
     CK(cudaMemsetAsync(seg_sqnorm, 0, (size_t)n_seg * 4, st));
     seg_sqnorm_kernel<<<dim3(n_seg, 64), 256, 0, st>>>(grads, (const long long*)seg_offsets, n_seg, seg_sqnorm);
   }
-  adam_kernel<<<dim3(n_seg, 64), 256, 0, st>>>(params, grads, m, v, (const long long*)seg_offsets, seg_sqnorm, clipnorm, lr_t, beta1,
+  adam_kernel<<<dim3(n_seg, 256), 256, 0, st>>>(params, grads, m, v, (const long long*)seg_offsets, seg_sqnorm, clipnorm, lr_t, beta1,
                                               beta2, eps, wd_lr, hyper_dev);
   CK(cudaGetLastError());
   return 0;
