@@ -91,6 +91,45 @@ def test_integrate_errors_match_reference():
         integrate(None, torch.zeros(1, 1), start_time=0.0, stop_time=1.0, steps=1.5)
 
 
+def test_scipy_driver_host_logic():
+    """`method="scipy"` (utils/integrate.py:409-452, the reference's own check tests/test_utils/test_integrate.py:28-44):
+    the host driver with a stand-in engine - float64 flattened state, float32 time, last column back as float32, the two
+    'has no effect' log lines of the dispatcher (:474-477)."""
+    import logging
+
+    class Engine:
+        info = {}
+
+        def _check_x(self, x):
+            return x.to(torch.float32)
+
+        def velocity(self, x, time):
+            assert x.dtype == torch.float32 and isinstance(time, float) and time == float(np.float32(time))
+            return torch.full_like(x, float(np.exp(time)))
+
+    eng = Engine()
+    records = []
+    h = logging.Handler()
+    h.emit = lambda r: records.append(r.getMessage())
+    log = logging.getLogger("bayesflow_b200")
+    log.addHandler(h)
+    try:
+        out = integrate(eng, torch.zeros(3, 2), start_time=-1.0, stop_time=1.0, steps="adaptive", method="scipy", max_steps=77)
+    finally:
+        log.removeHandler(h)
+    assert out.dtype == torch.float32 and out.shape == (3, 2)
+    np.testing.assert_allclose(out.numpy(), np.exp(1.0) - np.exp(-1.0), atol=1e-6, rtol=1e-6)
+    assert eng.info["path"] == "scipy" and eng.info["evals"] > 6
+    assert any("min_steps has no effect" in m for m in records) and any("max_steps has no effect" in m for m in records)
+    # two-key state of the density path: keys flattened and concatenated in order
+    from bayesflow_b200.integrate import solve_ivp_flat
+    (a, b), res = solve_ivp_flat(lambda t, x, tr: (torch.ones_like(x) * 2.0 * t, torch.ones_like(tr)),
+                                 [torch.ones(4, 3), torch.zeros(4, 1)], 0.0, 1.0)
+    np.testing.assert_allclose(a.numpy(), 2.0, atol=1e-5)
+    np.testing.assert_allclose(b.numpy(), 1.0, atol=1e-5)
+    assert a.shape == (4, 3) and b.shape == (4, 1) and res.nfev >= 8
+
+
 def test_surface_defaults_and_kwargs_merge():
     fm = bf.FlowMatching()
     assert fm.integrate_kwargs == {"method": "tsit5", "steps": "adaptive"}  # defaults.py:52

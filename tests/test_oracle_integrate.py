@@ -52,6 +52,17 @@ def test_analytical_backward_integration(method, atol):
     np.testing.assert_allclose(result_adaptive, 1.0, atol=max(atol, 1.1e-2) if method == "euler" else atol, rtol=0.1)
 
 
+def test_scipy_integration():
+    """tests/test_utils/test_integrate.py:28-44: d x / d t = exp(t) over [-1, 1] through method="scipy" (the dispatcher drops
+    `scipy_kwargs`, integrate.py:478, so solve_ivp runs with its defaults)."""
+    def fn(t, x):
+        return {"x": torch.exp(t)}
+
+    result = integrate(fn, {"x": torch.tensor(0.0)}, start_time=-1.0, stop_time=1.0, steps="adaptive", method="scipy",
+                       scipy_kwargs={"atol": 1e-6, "rtol": 1e-6})["x"]
+    np.testing.assert_allclose(float(result), np.exp(1.0) - np.exp(-1.0), atol=1e-6, rtol=1e-6)
+
+
 def test_argument_errors():
     fn = lambda t, x: {"x": x}
     s = {"x": torch.ones(1)}
