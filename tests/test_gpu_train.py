@@ -67,6 +67,13 @@ def cuda_tuple(tup):
     (3, None, (1024,) * 2, 200, {"film_use_gamma": True, "time_embedding_dim": 1}),
     (64, 32, (1024,) * 2, 512, {}),          # cfg4 block shape
     (5, 3, (512,) * 2, 384, {}),
+    # block_bwd_split_kernel: 768 columns on the 4-warp form (one idle column warp), norm None / rms (no row-sum exchange /
+    # no centring), unequal wide widths (padded to 768, effective-width norm), a single row, one row beyond a tile
+    (3, 4, (768,) * 2, 130, {}),
+    (3, 4, (768, 512), 129, {"activation": "silu"}),
+    (2, 6, (512,) * 2, 1, {"norm": None}),
+    (2, 6, (1024,) * 2, 257, {"norm": "rms", "activation": "gelu"}),
+    (2, None, (512,) * 3, 300, {"residual": False}),
 ])
 def test_loss_and_all_gradients(D, C, widths, B, sk):
     net, orc = make_pair(D, C, widths, **sk)
