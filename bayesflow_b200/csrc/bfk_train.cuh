@@ -283,7 +283,8 @@ struct BlockFwdArgs {
   const float* P;       // (B,W) dense output incl. bias
   const float* FB;      // FiLM shift: (B,W) per row, or one vector (fb_stride 0)
   const float* FG;      // FiLM scale (film_use_gamma) or null
-  long long fb_stride;
+  long long fb_stride;  // row stride of FB (the training step keeps the shifts of ALL blocks side by side: L * W)
+  long long fg_stride;  // row stride of FG
   const float* prev;    // (B,W) skip source: previous block's normalised activations (or h0), or null (residual off)
   const float* pg; const float* pb;  // affine of the previous LayerNorm applied to prev (null: prev is used as is)
   const unsigned char* prev_img;     // inference: skip source = the fp16 operand image itself (may equal img: in place)
@@ -351,7 +352,7 @@ __global__ void __launch_bounds__(256, NJ == 1 ? BFK_FWD_MINB : 1) block_fwd_ker
         }
         if (a.FG) {
           float g[8];
-          ld8(a.FG + r * a.fb_stride + c0, g);
+          ld8(a.FG + r * a.fg_stride + c0, g);
 #pragma unroll
           for (int i = 0; i < 8; ++i) v[j][i] *= 1.f + g[i];
         }
@@ -462,7 +463,7 @@ __global__ void __launch_bounds__(256) block_fwd_wide_kernel(const BlockFwdArgs 
     if (on && r < a.B) {
       ld8(a.P + r * a.W + c0, p);
       ld8(a.FB + r * a.fb_stride + c0, f);
-      if (a.FG) ld8(a.FG + r * a.fb_stride + c0, fg);
+      if (a.FG) ld8(a.FG + r * a.fg_stride + c0, fg);
       if (a.prev) ld8(a.prev + r * a.W + c0, sk);
       if (a.prev_img) raw = *reinterpret_cast<const uint4*>(a.prev_img + img_off(r, o, K8));
     }

@@ -19,6 +19,7 @@ struct Arena {
 struct TrainBufs {
   int KU, KT, KTN, N1, NO, has_merge;
   long long Rp;
+  float* fbb_all;  // [L * W]: the FiLM shift biases side by side (bias vector of the one batched FiLM GEMM)
   unsigned char *u_img, *te_img, *w1_pk, *a1_img, *wm_f, *wm_b, *h0_img, *wo_f, *wo_b, *dout_img, *dP_img, *dV_img, *dh0pre_img;
   float *w1, *b1, *h0pre, *m, *h0, *FB, *bo_pad, *out, *dH, *dte, *da1, *dW1, *db1;
   unsigned char *dP_img2, *dV_img2;  // second cotangent-image pair: lets the dW GEMMs of block l overlap block l-1's chain
@@ -58,17 +59,21 @@ void plan_train(const bfk_net_config* c, long long B, bool backward, Arena& ar, 
   }
   b.h0 = (float*)ar.take(Bs * W * 4);
   b.h0_img = (unsigned char*)ar.take(Rp * W * 2);
+  // the FiLM shift images of all blocks are contiguous: together they are the B operand of ONE GEMM with N = L * W (an image
+  // is W / NT column tiles of KT * NT * 2 bytes, so concatenated images are concatenated tiles)
+  unsigned char* wb_all = (unsigned char*)ar.take((size_t)c->L * W * b.KT * 2);
+  b.fbb_all = (float*)ar.take((size_t)c->L * W * 4);
   for (int l = 0; l < c->L; ++l) {
     b.wd_f[l] = (unsigned char*)ar.take((size_t)W * W * 2);
     b.wd_b[l] = (unsigned char*)ar.take((size_t)W * W * 2);
-    b.wb_f[l] = (unsigned char*)ar.take((size_t)W * b.KT * 2);
+    b.wb_f[l] = wb_all ? wb_all + (size_t)l * W * b.KT * 2 : nullptr;
     b.wb_b[l] = (unsigned char*)ar.take((size_t)r64(c->T) * W * 2);
     b.P[l] = (float*)ar.take(Bs * W * 4);
     b.xhat[l] = (float*)ar.take(Bs * W * 4);
     b.rstd[l] = (float*)ar.take(Bs * 4);
     b.h_img[l] = (unsigned char*)ar.take(Rp * W * 2);
   }
-  b.FB = (float*)ar.take(Bs * W * 4);
+  b.FB = (float*)ar.take(Bs * (size_t)c->L * W * 4);  // (B, L * W): block l reads columns l*W .. with row stride L*W
   bool ragged = false;
   for (int l = 0; l < c->L; ++l) ragged = ragged || (c->block_width[l] != 0);
   if (ragged) {  // a projector may sit in any block
@@ -321,6 +326,19 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   // ---- forward ---------------------------------------------------------------------------------------------------
   train_input_kernel<<<dim3((unsigned)((Rp + 127) / 128), (unsigned)(KU / 8 + KT / 8)), 128, 0, st>>>(ta->x, ta->cond, ta->t, w->freq, c->fourier_scale, B, Rp, D, C, T,
                                                                  KU / 8, KT / 8, b.u_img, b.te_img);
+  // FiLM shifts of ALL blocks in one GEMM (N = L * W) beside the input chain: they depend on the time embedding only
+  SideCtx* fsc = getenv("BFK_TRAIN_NO_OVERLAP") ? nullptr : side_ctx();
+  {
+    cudaStream_t fs = fsc ? fsc->s : st;
+    if (fsc) {
+      CK(cudaEventRecord(fsc->main_ev[L], st));
+      CK(cudaStreamWaitEvent(fs, fsc->main_ev[L], 0));
+    }
+    for (int l = 0; l < L; ++l)
+      CK(cudaMemcpyAsync(b.fbb_all + (size_t)l * W, w->film_b_b[l], (size_t)W * 4, cudaMemcpyDeviceToDevice, fs));
+    RC(bfk_gemm(b.te_img, b.wb_f[0], b.FB, (long long)L * W, B, L * W, KT, NTW, 1, 0, b.fbb_all, 1.f, P16, fs));
+    if (fsc) CK(cudaEventRecord(fsc->side_ev[L], fs));
+  }
   build_w1_kernel<<<cdiv((size_t)KU * N1, 256), 256, 0, st>>>(w->x_k, w->x_b, w->c_k, w->c_b, D, C, W, b.has_merge ? c->merge : 0, KU, N1,
                                                              b.w1, b.b1);
   CK(cudaGetLastError());
@@ -336,7 +354,6 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   CK(cudaGetLastError());
   for (int l = 0; l < L; ++l) {
     RC(bfk_gemm(l == 0 ? b.h0_img : b.h_img[l - 1], b.wd_f[l], b.P[l], W, B, W, W, NTW, 1, 0, w->dense_b[l], 1.f, P16, st));
-    RC(bfk_gemm(b.te_img, b.wb_f[l], b.FB, W, B, W, KT, NTW, 1, 0, w->film_b_b[l], 1.f, P16, st));
     if (c->film_use_gamma) {  // FiLM scale to_gamma(t_emb): one more K = T GEMM per block
       RC(bfk_pack_kmajor_t(w->film_g_k[l], W, T, KT, W, NTW, P16, b.wg_f, st));
       RC(bfk_gemm(b.te_img, b.wg_f, b.FG, W, B, W, KT, NTW, 1, 0, w->film_g_b[l], 1.f, P16, st));
@@ -347,7 +364,9 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
       RC(bfk_gemm(l == 0 ? b.h0_img : b.h_img[l - 1], b.wp_f, b.skip, W, B, W, W, NTW, 1, 0, w->proj_b[l], 1.f, P16, st));
     }
     BlockFwdArgs a{};
-    a.P = b.P[l]; a.FB = b.FB; a.FG = c->film_use_gamma ? b.FG : nullptr; a.fb_stride = W;
+    a.P = b.P[l]; a.FB = b.FB + (size_t)l * W; a.FG = c->film_use_gamma ? b.FG : nullptr; a.fb_stride = (long long)L * W;
+    a.fg_stride = W;
+    if (l == 0 && fsc) CK(cudaStreamWaitEvent(st, fsc->side_ev[L], 0));  // join: the batched FiLM GEMM
     a.Weff = c->block_width[l];
     a.prev = c->residual ? (proj ? b.skip : (l == 0 ? b.h0 : b.xhat[l - 1])) : nullptr;
     a.pg = (!proj && l > 0 && c->norm != BFK_NORM_NONE) ? w->norm_g[l - 1] : nullptr;  // rms: scale only (pb stays null)

@@ -335,7 +335,8 @@ class TrainEngine:
         """Kernels bfk_train_step enqueues (counted from csrc/bfk_train_host.cuh)."""
         Lb, merge = self.cfg.L, 1 if self.net._C else 0
         # one batched weight-pack launch (pack_batch_kernel) replaces the 2 L + 2 forward and 2 L + 2 backward pack launches
-        fwd = 1 + 2 + 2 + (3 if merge else 1) + 3 * Lb + 1 + 1
+        # per block: Dense GEMM + block kernel; the FiLM shifts of all blocks are ONE GEMM (N = L * W) on the side stream
+        fwd = 1 + 2 + 2 + (3 if merge else 1) + 2 * Lb + 1 + 1 + 1
         if not backward:
             return fwd
         bwd = 2 + Lb * 5 + (4 if merge else 1) + 3
