@@ -401,6 +401,9 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
     CK(cudaEventRecord(sc->main_ev[L], st));
     CK(cudaStreamWaitEvent(ss, sc->main_ev[L], 0));
   }
+  // zeroed early, off the dependent chain: the accumulators of the input-side backward (first touched after the join)
+  CK(cudaMemsetAsync(b.db1, 0, (size_t)N1 * 4, ss));
+  CK(cudaMemsetAsync(b.dW1, 0, (size_t)KU * N1 * 4, ss));
   RC(launch_gemm_dw(b.h_img[L - 1], W / 8, b.dout_img, NO / 8, GP(g->out_k), D, W, D, Rp, gs, sw, ss));
   RC(bfk_gemm(b.dout_img, b.wo_b, b.dH, W, B, W, NO, NTW, 1, 0, nullptr, 1.f, P16, st));
   const bool want_dte = T > 1;
@@ -452,23 +455,32 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
   // join: the input-side backward reuses the first image pair (last read by block 0's or block 1's side work) and the
   // frequency gradient needs the finished time-embedding cotangent
   if (sc) CK(cudaStreamWaitEvent(st, sc->side_ev[0], 0));
-  CK(cudaMemsetAsync(b.db1, 0, (size_t)N1 * 4, st));
+  // the frequency gradient only needs the time-embedding cotangent, complete on the side stream in stream order; the
+  // merge layer's dW joins it there, so the dependent chain on `st` is act_bwd -> dX -> act_bwd -> dW1 -> scatter
+  if (want_dte && GP(g->freq) && T > 1)
+    freq_bwd_kernel<<<dim3((unsigned)((B + 255) / 256), (unsigned)((T - 1) / 2)), 256, 0, ss>>>(b.dte, KTN, ta->t, w->freq, c->fourier_scale, B, (T - 1) / 2, GP(g->freq), gs);
+  CK(cudaGetLastError());
   if (b.has_merge) {
     RC(launch_act_bwd(b.dH, b.m, W, B, Rp, W / 8, act, b.dP_img, GP(g->m_b), gs, st));
-    RC(launch_gemm_dw(b.a1_img, N1 / 8, b.dP_img, W / 8, GP(g->m_k), W, N1, W, Rp, gs, sw, st));
+    if (sc) {
+      CK(cudaEventRecord(sc->main_ev[0], st));
+      CK(cudaStreamWaitEvent(ss, sc->main_ev[0], 0));
+    }
+    RC(launch_gemm_dw(b.a1_img, N1 / 8, b.dP_img, W / 8, GP(g->m_k), W, N1, W, Rp, gs, sw, ss));
     RC(bfk_gemm(b.dP_img, b.wm_b, b.da1, N1, B, N1, W, NT1, 1, 0, nullptr, 1.f, P16, st));
     RC(launch_act_bwd(b.da1, b.h0pre, N1, B, Rp, N1 / 8, act, b.dh0pre_img, b.db1, 1.f, st));
   } else {
     RC(launch_act_bwd(b.dH, b.h0pre, N1, B, Rp, N1 / 8, act, b.dh0pre_img, b.db1, 1.f, st));
   }
   CK(cudaGetLastError());
-  CK(cudaMemsetAsync(b.dW1, 0, (size_t)KU * N1 * 4, st));
   RC(launch_gemm_dw(b.u_img, KU / 8, b.dh0pre_img, N1 / 8, b.dW1, N1, D + C, N1, Rp, 1.f, sw, st));
   scatter_w1_grad_kernel<<<cdiv((size_t)(D + C) * W, 256), 256, 0, st>>>(b.dW1, b.db1, D, C, W, b.has_merge ? c->merge : 0, N1, gs,
                                                                         GP(g->x_k), GP(g->x_b), GP(g->c_k), GP(g->c_b));
-  if (want_dte && GP(g->freq) && T > 1)
-    freq_bwd_kernel<<<dim3((unsigned)((B + 255) / 256), (unsigned)((T - 1) / 2)), 256, 0, st>>>(b.dte, KTN, ta->t, w->freq, c->fourier_scale, B, (T - 1) / 2, GP(g->freq), gs);
   CK(cudaGetLastError());
+  if (sc) {  // final join
+    CK(cudaEventRecord(sc->side_ev[1], ss));
+    CK(cudaStreamWaitEvent(st, sc->side_ev[1], 0));
+  }
   return 0;
 }
 
