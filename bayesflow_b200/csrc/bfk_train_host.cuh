@@ -336,6 +336,8 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
     }
     for (int l = 0; l < L; ++l)
       CK(cudaMemcpyAsync(b.fbb_all + (size_t)l * W, w->film_b_b[l], (size_t)W * 4, cudaMemcpyDeviceToDevice, fs));
+    CK(cudaMemsetAsync(b.bo_pad, 0, (size_t)NO * 4, fs));  // zero-padded output bias, off the dependent chain as well
+    CK(cudaMemcpyAsync(b.bo_pad, w->out_b, (size_t)D * 4, cudaMemcpyDeviceToDevice, fs));
     RC(bfk_gemm(b.te_img, b.wb_f[0], b.FB, (long long)L * W, B, L * W, KT, NTW, 1, 0, b.fbb_all, 1.f, P16, fs));
     if (fsc) CK(cudaEventRecord(fsc->side_ev[L], fs));
   }
@@ -378,8 +380,6 @@ extern "C" int bfk_train_step(const bfk_net_config* c, const bfk_weights* w, con
     a.drop_rate = ta->dropout; a.inv_keep = inv_keep; a.seed = ta->seed; a.seed_dev = ta->seed_dev; a.row0 = ta->row_offset;
     RC(launch_block_fwd(a, st));
   }
-  CK(cudaMemsetAsync(b.bo_pad, 0, (size_t)NO * 4, st));
-  CK(cudaMemcpyAsync(b.bo_pad, w->out_b, (size_t)D * 4, cudaMemcpyDeviceToDevice, st));
   RC(bfk_gemm(b.h_img[L - 1], b.wo_f, b.out, NO, B, NO, W, 64, 1, 0, b.bo_pad, 1.f, P16, st));
   if (pred_out) CK(cudaMemcpy2DAsync(pred_out, (size_t)D * 4, b.out, (size_t)NO * 4, (size_t)D * 4, (size_t)B, cudaMemcpyDeviceToDevice, st));
   if (!loss && !bwd) return 0;
