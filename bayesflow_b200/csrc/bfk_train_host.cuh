@@ -33,7 +33,13 @@ struct TrainBufs {
 
 inline int r32(int x) { return (x + 31) / 32 * 32; }
 inline int r64(int x) { return (x + 63) / 64 * 64; }
-inline int nt_of(int N) { return (N % 256) == 0 ? 256 : ((N % 128) == 0 ? 128 : 64); }
+inline int nt_of(int N) {
+  static int cap = -1;  // BFK_NT_MAX=128 / 64: narrower column tiles (more, smaller output tiles per GEMM)
+  if (cap < 0) { const char* e = getenv("BFK_NT_MAX"); cap = e ? atoi(e) : 256; }
+  if (cap >= 256 && (N % 256) == 0) return 256;
+  if (cap >= 128 && (N % 128) == 0) return 128;
+  return 64;
+}
 
 void plan_train(const bfk_net_config* c, long long B, bool backward, Arena& ar, TrainBufs& b) {
   const int W = c->W;
